@@ -1,0 +1,153 @@
+/*
+ * paths_b200.h -- C ABI of libpaths_b200.so: the B200-native (sm_100a) implementation of the PATHS hierarchical
+ * slide-level forward/backward pass.
+ *
+ * The reference (zzbuzzard/PATHS) is pure Python/PyTorch and has no plugin / FFI interface; its
+ * boundary is its Python module API.  This header is the boundary *below* that API: the functions the Python mirror
+ * (paths_b200/utils.py:inference_end2end, paths_b200/model/*) binds through ctypes.  Each entry cites the reference
+ * code it replaces (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - extern "C", plain C types only; every pointer is a caller-owned DEVICE pointer unless named `h_*`.
+ *   - every call takes the CUDA stream it must enqueue on (`void* stream` = cudaStream_t) and never synchronises.
+ *   - return 0 on success, non-zero on failure; the message is available from paths_last_error().  No exceptions
+ *     cross the ABI.  There is no CPU fallback: without a CUDA device every compute entry fails.
+ *   - no allocation inside: the caller provides one workspace (size from paths_engine_workspace_bytes).
+ *   - row tables are "packed varlen": rows of all slides of a level concatenated, seg[B+1] offsets, no padding.
+ */
+#ifndef PATHS_B200_H_
+#define PATHS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PATHS_MAX_LEVELS 8
+#define PATHS_MAX_LAYERS 4
+#define PATHS_ABI_VERSION 1
+
+/* model_config + the train_config fields the hot path reads (config.py:19-79). */
+typedef struct paths_dims {
+  int32_t D;              /* patch_embed_dim */
+  int32_t C;              /* hierarchical_ctx_mlp_hidden_dim (LSTM memory width) */
+  int32_t d;              /* trans_dim */
+  int32_t heads;          /* trans_heads */
+  int32_t layers;         /* trans_layers (decoder layers; the encoder of nn.Transformer sees an empty sequence) */
+  int32_t I;              /* importance_mlp_hidden_dim */
+  int32_t F;              /* dim_feedforward = 4 * trans_dim (aggregator.py:30) */
+  int32_t nl;             /* logits: nbins or len(filter_to_subtypes) (paths.py:25) */
+  int32_t L;              /* num_levels */
+  int32_t K[PATHS_MAX_LEVELS];  /* top_k_patches[l] for l < L-1; -1 keeps all (slide.py:294) */
+  int32_t imp_mul;        /* importance_mode == "mul" */
+  int32_t pe_mode;        /* 1 = "1d", 2 = "2d" */
+  int32_t residual;       /* slide_ctx_mode == "residual" (1) or "none" (0) */
+  int32_t task;           /* 0 survival NLL (utils.py:283), 1 cross-entropy (utils.py:277) */
+  int32_t precision;      /* 0 fp32 SIMT, 1 tcgen05 bf16x3 (fp32-parity), 2 tcgen05 bf16 (fast) */
+} paths_dims_t;
+
+/* Offsets (in floats) of every live parameter inside the flat parameter / gradient buffers.  The stacked matrices
+ * must be contiguous: Wg = [forget_gate; remember_gate; remember_map; out_select_gate].weight ([3C+D, 2D]),
+ * bg likewise, Wuv = [importance_mlp.0.weight; global_agg.proj_in.weight] ([I+d, D]).  State-dict names: SURVEY §8b. */
+enum paths_lstm_param { PATHS_P_WG = 0, PATHS_P_BG, PATHS_P_WMO, PATHS_P_BMO, PATHS_P_LSTM_COUNT };
+enum paths_level_param {
+  PATHS_P_WUV = 0, PATHS_P_B1, PATHS_P_W2, PATHS_P_B2, PATHS_P_BIN, PATHS_P_SPECIAL, PATHS_P_NFW, PATHS_P_NFB,
+  PATHS_P_WC, PATHS_P_BC, PATHS_P_LEVEL_HEAD_COUNT
+};
+enum paths_layer_param {
+  PATHS_P_WQKV = 0, PATHS_P_BQKV, PATHS_P_WO, PATHS_P_BO, PATHS_P_BCROSS, PATHS_P_FW1, PATHS_P_FB1, PATHS_P_FW2,
+  PATHS_P_FB2, PATHS_P_N1W, PATHS_P_N1B, PATHS_P_N2W, PATHS_P_N2B, PATHS_P_N3W, PATHS_P_N3B, PATHS_P_LAYER_COUNT
+};
+#define PATHS_LEVEL_STRIDE (PATHS_P_LEVEL_HEAD_COUNT + PATHS_MAX_LAYERS * PATHS_P_LAYER_COUNT)
+#define PATHS_NUM_OFFSETS (PATHS_P_LSTM_COUNT + PATHS_MAX_LEVELS * PATHS_LEVEL_STRIDE)
+/* offsets[PATHS_P_LSTM_COUNT + l * PATHS_LEVEL_STRIDE + PATHS_P_LEVEL_HEAD_COUNT + j * PATHS_P_LAYER_COUNT + k] */
+
+/* The feature-pyramid store: every slide's L grids resident in device (or mapped pinned host) memory, as written by the
+ * reference preprocessor ([W, H, D] float32, all-zero vector = background; preprocess/preprocess.py:89,105,
+ * preprocess/loader.py:14-18), plus a per-grid occupancy bitmap (bit x*H+y set iff the cell is tissue; replaces the
+ * `fts[x, y].sum() != 0` probe of data_utils/slide.py:324).  Arrays are indexed [slide * L + level]. */
+typedef struct paths_store {
+  const float* const* grid_ptr;   /* device array of device pointers */
+  const int32_t* gw;              /* grid extent in x */
+  const int32_t* gh;              /* grid extent in y */
+  const uint32_t* occ;            /* bitmap words */
+  const uint64_t* occ_off;        /* word offset of each grid's bitmap */
+  const int32_t* nonbg;           /* number of set bits of each grid (fallback of slide.py:336-352) */
+} paths_store_t;
+
+typedef struct paths_engine paths_engine_t;
+
+/* named internal buffers, for tests, per-level API and teacher forcing (paths_engine_buffer) */
+enum paths_buffer {
+  PATHS_BUF_COUNT = 0, PATHS_BUF_NTOK, PATHS_BUF_SEG, PATHS_BUF_ROW_SLIDE, PATHS_BUF_ROW_XY, PATHS_BUF_ROW_PARENT,
+  PATHS_BUF_PARENT_LOCAL, PATHS_BUF_SEL, PATHS_BUF_SEL_COUNT, PATHS_BUF_CHILD_OF, PATHS_BUF_TSEG,
+  PATHS_BUF_X, PATHS_BUF_G, PATHS_BUF_CN, PATHS_BUF_PT, PATHS_BUF_H, PATHS_BUF_Y, PATHS_BUF_UV, PATHS_BUF_ALPHA,
+  PATHS_BUF_TOK, PATHS_BUF_Z, PATHS_BUF_F, PATHS_BUF_LOGITS,
+  PATHS_BUF_HAZARDS, PATHS_BUF_LOSS, PATHS_BUF_DLOGITS, PATHS_BUF_OVERFLOW, PATHS_BUF_DF_IN, PATHS_BUF_DHROW, PATHS_BUF_DCROW,
+  PATHS_BUF_LOSS_PER,
+  PATHS_BUF__COUNT
+};
+
+const char* paths_last_error(void);
+int paths_abi_version(void);
+
+/* Bytes of workspace an engine for a batch of B slides needs.  caps[l] = row capacity of level l (level 0: total grid
+ * cells of the batch; l >= 1: normally 4*K[l-1]*B), maxseg[l] = upper bound on one slide's rows at level l. */
+size_t paths_engine_workspace_bytes(const paths_dims_t* dims, int B, const int32_t* h_caps, const int32_t* h_maxseg);
+int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, const int32_t* h_caps, const int32_t* h_maxseg,
+                        void* workspace, size_t workspace_bytes);
+void paths_engine_destroy(paths_engine_t* e);
+
+/* params / grads: flat fp32 buffers of n_floats floats; h_offsets: PATHS_NUM_OFFSETS host int64 values (floats).  div: sinusoid frequencies,
+ * d/4 values for "2d" (utils.py:56), d/2 for "1d" (utils.py:19), computed by the caller exactly as the reference does. */
+int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grads, int64_t n_floats, const int64_t* h_offsets,
+                             const float* div);
+int paths_engine_bind_store(paths_engine_t* e, const paths_store_t* h_store);
+
+/* Level-0 row tables for the batch (slide.py:258-271: every cell of grid 0, x-major) and their feature gather.
+ * slide_ids[B]: index of each batch slot into the store (device int32). */
+int paths_engine_begin(paths_engine_t* e, const int32_t* slide_ids, void* stream);
+/* Same, but level-0 features are packed from the collated zero-padded batch["fts"] [B, N, D] (data_utils/dataset.py:217,
+ * utils.py:240 from_batch) already copied to the device, instead of being read from the store. */
+int paths_engine_begin_padded(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, void* stream);
+/* One level: LSTM cell step, importance, token projection + positional encoding, varlen transformer aggregator,
+ * residual slide context, classifier.  Replaces PATHSProcessor.process (model/paths.py:66-146), LSTMCell.forward
+ * (model/interface.py:31-58), TransformerAggregator.forward (model/aggregator.py:58-76). */
+int paths_engine_level_forward(paths_engine_t* e, int level, void* stream);
+/* Top-K select + child expansion + gather into level+1.  Replaces PreprocessedSlide.iter (data_utils/slide.py:277-360)
+ * and collate_fn (data_utils/dataset.py:206-243). */
+int paths_engine_select(paths_engine_t* e, int level, void* stream);
+/* hazards/loss (+ dlogits) on the last level's logits: utils.py:263-277, nll_loss utils.py:283-305.
+ * scale = 1 / global batch size (the loss is a batch mean). */
+int paths_engine_loss(paths_engine_t* e, const int32_t* ybin, const int32_t* censored, float scale, void* stream);
+/* Backward of one level (autograd of the above); accumulates into the bound grad buffer.  use_dlogits: take the
+ * level's PATHS_BUF_DLOGITS as upstream gradient of its logits (set for the last level by paths_engine_loss). */
+int paths_engine_level_backward(paths_engine_t* e, int level, int use_dlogits, void* stream);
+
+/* Whole step: begin, L x (level_forward, select), loss.  utils.inference_end2end (utils.py:228-279). */
+int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int32_t* ybin, const int32_t* censored, float scale,
+                         int with_loss, void* stream);
+/* loss.backward() of train.py:65: levels L-1..0.  zero_grads: clear the grad buffer first. */
+int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream);
+
+int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, size_t* bytes);
+int paths_engine_set_precision(paths_engine_t* e, int precision);
+/* number of kernel launches issued by this engine since creation (for bench.py's gpu_launches) */
+int64_t paths_engine_launch_count(paths_engine_t* e);
+
+/* Occupancy bitmap of one [W*H, D] grid: bit c set iff any of the D floats of cell c is non-zero; *count += popcount. */
+int paths_build_occupancy(const float* grid, int cells, int D, uint32_t* bits, int32_t* count, void* stream);
+
+/* Stand-alone dense contractions (tests; the engine uses the same kernels).
+ * C[M,N] (+)= act(A[M,K] . B^T + bias) with B [N,K] (b_kn = 0) or [K,N] (b_kn = 1); flags: 1 relu, 2 accumulate. */
+int paths_gemm_nt(int precision, const float* A, int lda, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias,
+                  int M, int N, int K, int flags, void* stream);
+/* C[NI,NJ] += P[M,NI]^T . Q[M,NJ] */
+int paths_gemm_tn(int precision, const float* P, int ldp, const float* Q, int ldq, float* C, int ldc, int M, int NI, int NJ, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PATHS_B200_H_ */

@@ -1,0 +1,94 @@
+// Shared device/host helpers for the PATHS B200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+namespace paths {
+
+void set_error(const char* fmt, ...);          // records a message for paths_last_error()
+
+#define PATHS_CK(expr)                                                                           \
+  do {                                                                                           \
+    cudaError_t _e = (expr);                                                                     \
+    if (_e != cudaSuccess) {                                                                     \
+      ::paths::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));  \
+      return -1;                                                                                 \
+    }                                                                                            \
+  } while (0)
+
+#define PATHS_LAUNCH_CK() PATHS_CK(cudaGetLastError())
+
+#define PATHS_REQUIRE(cond, ...)                 \
+  do {                                           \
+    if (!(cond)) {                               \
+      ::paths::set_error(__VA_ARGS__);           \
+      return -2;                                 \
+    }                                            \
+  } while (0)
+
+constexpr int kNumSMs = 148;                     // B200
+
+// A-operand row source: logical row m of a [M, K] matrix whose columns [0,k0) come from table p0 and
+// columns [k0,K) from table p1, each optionally through a row-index array (idx < 0 => zero row).
+// This is how [x || h_parent] (model/interface.py:49) and packed-token gathers reach a GEMM without
+// a materialised concat/gather.
+struct RowSrc {
+  const float* p0; int ld0; const int* idx0; int k0;
+  const float* p1; int ld1; const int* idx1;
+};
+
+inline RowSrc row_src(const float* p, int ld, int K, const int* idx = nullptr) {
+  RowSrc r; r.p0 = p; r.ld0 = ld; r.idx0 = idx; r.k0 = K; r.p1 = nullptr; r.ld1 = 0; r.idx1 = nullptr; return r;
+}
+inline RowSrc row_src2(const float* p0, int ld0, const int* idx0, int k0, const float* p1, int ld1, const int* idx1) {
+  RowSrc r; r.p0 = p0; r.ld0 = ld0; r.idx0 = idx0; r.k0 = k0; r.p1 = p1; r.ld1 = ld1; r.idx1 = idx1; return r;
+}
+
+// Returns pointer to 4 consecutive floats (m, k..k+3) or nullptr for a zero row.  k must not straddle k0.
+__device__ __forceinline__ const float* rowsrc_ptr(const RowSrc& s, int m, int k) {
+  if (k < s.k0) {
+    int r = s.idx0 ? s.idx0[m] : m;
+    return r < 0 ? nullptr : s.p0 + (size_t)r * s.ld0 + k;
+  }
+  int r = s.idx1 ? s.idx1[m] : m;
+  return r < 0 ? nullptr : s.p1 + (size_t)r * s.ld1 + (k - s.k0);
+}
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+enum GemmFlags { GEMM_RELU = 1, GEMM_ACCUM = 2 };
+
+// Precision modes of the dense contractions.
+//   0: fp32 SIMT FFMA (exact fp32 semantics, the parity anchor)
+//   1: tcgen05 bf16x3 split (hi*hi + hi*lo + lo*hi, fp32 accumulate in TMEM; ~2^-17 relative)
+//   2: tcgen05 bf16 single pass (fast mode, stated 1e-2)
+enum Precision { PREC_FP32_SIMT = 0, PREC_BF16X3_TC = 1, PREC_BF16_TC = 2 };
+
+// ---- dense contraction entry points (gemm_simt.cu / gemm_tc.cu) -------------------------------------------
+// C[m, n] (+)= act( sum_k A(m,k) * B(n,k) + bias[n] ),  m < M (M read from *M_dev when M_dev != nullptr, else M_host)
+// b_kn == 0: B is [N, K] row-major with leading dim ldb (weight as stored by nn.Linear)
+// b_kn == 1: B is [K, N] row-major with leading dim ldb (used for dX = dY . W)
+int gemm_nt(int prec, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias,
+            int M_host, const int* M_dev, int N, int K, int flags, cudaStream_t st);
+
+// C[i, j] += sum_m P[m, i] * Q(m, j)   (dW = dY^T . X).  P is [M, NI] with leading dim ldp, Q a RowSrc with NJ columns.
+// Accumulates with fp32 atomics (split over m); C must be initialised (zeroed grads).
+int gemm_tn(int prec, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev,
+            int NI, int NJ, cudaStream_t st);
+
+// out[n] += sum_m X[m, n]
+int colsum_accum(const float* X, int ld, float* out, int M_host, const int* M_dev, int N, cudaStream_t st);
+
+}  // namespace paths

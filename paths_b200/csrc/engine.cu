@@ -1,0 +1,572 @@
+// The level engine: owns the packed row tables and activation buffers of every magnification level inside one
+// caller-provided workspace and sequences the kernels of the hierarchical forward/backward pass
+// (utils.py:228-279 inference_end2end + loss.backward()).  All row counts live on the device: nothing here
+// synchronises with the host, so a whole step is one uninterrupted stream of launches.
+#include <stdarg.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/paths_b200.h"
+#include "common.cuh"
+#include "rowops.cuh"
+
+namespace paths {
+
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int gemm_nt_simt(const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
+                 const int* M_dev, int N, int K, int flags, cudaStream_t st);
+int gemm_tn_simt(const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
+                 cudaStream_t st);
+int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
+               const int* M_dev, int N, int K, int flags, cudaStream_t st);
+int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
+               cudaStream_t st);
+bool gemm_tc_supported_nt(const RowSrc& A, int ldb, int b_kn, int ldc, int N, int K);
+bool gemm_tc_supported_tn(int ldp, const RowSrc& Q, int ldc, int NI, int NJ);
+
+int gemm_nt(int prec, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
+            const int* M_dev, int N, int K, int flags, cudaStream_t st) {
+  if (prec != PREC_FP32_SIMT && gemm_tc_supported_nt(A, ldb, b_kn, ldc, N, K))
+    return gemm_nt_tc(prec == PREC_BF16X3_TC ? 3 : 1, A, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
+  return gemm_nt_simt(A, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
+}
+int gemm_tn(int prec, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
+            cudaStream_t st) {
+  if (prec != PREC_FP32_SIMT && gemm_tc_supported_tn(ldp, Q, ldc, NI, NJ))
+    return gemm_tn_tc(prec == PREC_BF16X3_TC ? 3 : 1, P, ldp, Q, C, ldc, M_host, M_dev, NI, NJ, st);
+  return gemm_tn_simt(P, ldp, Q, C, ldc, M_host, M_dev, NI, NJ, st);
+}
+
+namespace {
+
+struct Bump {                       // two-pass workspace carver: base == nullptr only measures
+  char* base; size_t off;
+  template <typename T> T* take(size_t n) {
+    off = (off + 255) & ~size_t(255);
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * sizeof(T);
+    return p;
+  }
+};
+
+struct LayerBuf { float *qkv, *O, *lse, *y1, *xh1, *rs1, *y2, *xh2, *rs2, *Hf, *y3, *xh3, *rs3; };
+
+struct Level {
+  int cap, maxseg, kcap, ncap_tok;
+  int *count, *ntok, *seg, *tseg, *row_slide, *row_xy, *row_parent, *parent_local, *sel, *sel_count, *child_of;
+  float *X, *G, *Cn, *Pt, *H, *Y, *UV, *alpha, *tok;
+  LayerBuf layer[PATHS_MAX_LAYERS];
+  float *xhf, *rsf, *z, *F, *logits, *dlogits, *dHrow, *dCrow;
+};
+
+struct LayerP { const float *Wqkv, *bqkv, *Wo, *bo, *bcross, *W1, *b1, *W2, *b2, *n1w, *n1b, *n2w, *n2b, *n3w, *n3b; };
+struct LevelP { const float *Wuv, *b1, *w2, *b2, *bin, *special, *nfw, *nfb, *Wc, *bc; LayerP layer[PATHS_MAX_LAYERS]; };
+struct Params { const float *Wg, *bg, *Wmo, *bmo; LevelP level[PATHS_MAX_LEVELS]; };
+
+__global__ void tseg_kernel(const int* __restrict__ seg, int* __restrict__ tseg, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B) tseg[i] = seg[i] + i;
+}
+
+}  // namespace
+}  // namespace paths
+
+using namespace paths;
+
+struct paths_engine {
+  paths_dims_t dm;
+  int B;
+  Level lv[PATHS_MAX_LEVELS];
+  // shared scratch
+  int maxcap, maxtok;
+  float *A1, *Fo;                                       // forward temporaries [maxtok, d]
+  float *dY, *dP, *dG, *dCn, *dHc, *dCc, *dUV;          // backward, row-shaped
+  float *ga, *gb, *gO, *gt, *dqkv, *dHf, *Dvec;         // backward, token-shaped
+  float *dF, *dz, *dy3s;                                 // [B, d]
+  float *hazards, *loss, *loss_per;
+  int *overflow, *slide_cnt, *slide_fb;
+  const int* slide_ids;
+  Params P, Gr;                                          // parameters and their gradients (same layout)
+  float* grads_base; size_t grads_floats;
+  const float* div;
+  paths_store_t store;
+  bool have_params, have_store;
+  int64_t launches;
+  size_t ws_bytes;
+  char* ws_base;
+};
+
+namespace {
+
+size_t carve(paths_engine* e, char* base) {
+  const paths_dims_t& dm = e->dm;
+  const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F;
+  Bump b{base, 0};
+  int maxcap = 0;
+  for (int l = 0; l < dm.L; ++l) {
+    Level& v = e->lv[l];
+    const size_t cap = v.cap, tokcap = (size_t)v.cap + B;
+    v.ncap_tok = (int)tokcap;
+    if (v.cap > maxcap) maxcap = v.cap;
+    v.count = b.take<int>(1); v.ntok = b.take<int>(1);
+    v.seg = b.take<int>(B + 1); v.tseg = b.take<int>(B);
+    v.row_slide = b.take<int>(cap); v.row_xy = b.take<int>(2 * cap); v.row_parent = b.take<int>(cap);
+    v.parent_local = b.take<int>(cap);
+    v.sel = b.take<int>((size_t)B * (v.kcap > 0 ? v.kcap : 1)); v.sel_count = b.take<int>(B);
+    v.child_of = b.take<int>(4 * cap);
+    v.X = b.take<float>(cap * D); v.G = b.take<float>(cap * (3 * C + D)); v.Cn = b.take<float>(cap * C);
+    v.Pt = b.take<float>(cap * D); v.H = b.take<float>(cap * D); v.Y = b.take<float>(cap * D);
+    v.UV = b.take<float>(cap * (I + d)); v.alpha = b.take<float>(cap); v.tok = b.take<float>(tokcap * d);
+    for (int j = 0; j < dm.layers; ++j) {
+      LayerBuf& y = v.layer[j];
+      const size_t rows = (j == dm.layers - 1) ? (size_t)B : tokcap;
+      y.qkv = b.take<float>(tokcap * 3 * d);
+      y.O = b.take<float>(rows * d); y.lse = b.take<float>(rows * dm.heads);
+      y.y1 = b.take<float>(rows * d); y.xh1 = b.take<float>(rows * d); y.rs1 = b.take<float>(rows);
+      y.y2 = b.take<float>(rows * d); y.xh2 = b.take<float>(rows * d); y.rs2 = b.take<float>(rows);
+      y.Hf = b.take<float>(rows * F);
+      y.y3 = b.take<float>(rows * d); y.xh3 = b.take<float>(rows * d); y.rs3 = b.take<float>(rows);
+    }
+    v.xhf = b.take<float>((size_t)B * d); v.rsf = b.take<float>(B); v.z = b.take<float>((size_t)B * d);
+    v.F = b.take<float>((size_t)B * d); v.logits = b.take<float>((size_t)B * dm.nl); v.dlogits = b.take<float>((size_t)B * dm.nl);
+    v.dHrow = b.take<float>(cap * D); v.dCrow = b.take<float>(cap * C);
+  }
+  e->maxcap = maxcap; e->maxtok = maxcap + B;
+  const size_t mc = maxcap, mt = (size_t)maxcap + B;
+  e->A1 = b.take<float>(mt * d); e->Fo = b.take<float>(mt * d);
+  e->dY = b.take<float>(mc * D); e->dP = b.take<float>(mc * D); e->dG = b.take<float>(mc * (3 * C + D));
+  e->dCn = b.take<float>(mc * C); e->dHc = b.take<float>(mc * D); e->dCc = b.take<float>(mc * C);
+  e->dUV = b.take<float>(mc * (I + d));
+  e->ga = b.take<float>(mt * d); e->gb = b.take<float>(mt * d); e->gO = b.take<float>(mt * d); e->gt = b.take<float>(mt * d);
+  e->dqkv = b.take<float>(mt * 3 * d); e->dHf = b.take<float>(mt * F); e->Dvec = b.take<float>(mt * dm.heads);
+  e->dF = b.take<float>((size_t)B * d); e->dz = b.take<float>((size_t)B * d); e->dy3s = b.take<float>((size_t)B * d);
+  e->hazards = b.take<float>((size_t)B * dm.nl); e->loss = b.take<float>(1); e->loss_per = b.take<float>(B);
+  e->overflow = b.take<int>(2); e->slide_cnt = b.take<int>(B); e->slide_fb = b.take<int>(B);
+  return (b.off + 255) & ~size_t(255);
+}
+
+int check_dims(const paths_dims_t* dm, int B, const int32_t* caps, const int32_t* maxseg) {
+  PATHS_REQUIRE(dm && caps && maxseg, "null argument");
+  PATHS_REQUIRE(dm->L >= 1 && dm->L <= PATHS_MAX_LEVELS, "num_levels %d outside [1, %d]", dm->L, PATHS_MAX_LEVELS);
+  PATHS_REQUIRE(dm->layers >= 1 && dm->layers <= PATHS_MAX_LAYERS, "trans_layers %d outside [1, %d]", dm->layers, PATHS_MAX_LAYERS);
+  PATHS_REQUIRE(dm->D % 4 == 0 && dm->C % 4 == 0 && dm->d % 4 == 0 && dm->I % 4 == 0 && dm->F % 4 == 0,
+                "feature dims must be multiples of 4 (D=%d C=%d d=%d I=%d F=%d)", dm->D, dm->C, dm->d, dm->I, dm->F);
+  PATHS_REQUIRE(dm->d % dm->heads == 0 && dm->d / dm->heads <= 64, "head_dim must be <= 64");
+  PATHS_REQUIRE(dm->d <= 256 && dm->I <= 256 && dm->nl <= 32, "trans_dim / importance hidden dim above 256 unsupported");
+  PATHS_REQUIRE(dm->pe_mode == 1 || dm->pe_mode == 2, "pos_encoding_mode must be 1d or 2d");
+  PATHS_REQUIRE(B >= 1, "empty batch");
+  for (int l = 0; l < dm->L; ++l) {
+    PATHS_REQUIRE(caps[l] >= 1 && maxseg[l] >= 1, "level %d: capacity must be positive", l);
+    PATHS_REQUIRE(l == dm->L - 1 || dm->K[l] < 0 || maxseg[l] <= 65536, "level %d: bags above 65536 rows need top_k = -1", l);
+  }
+  return 0;
+}
+
+void fill_level_meta(paths_engine* e, const int32_t* caps, const int32_t* maxseg) {
+  for (int l = 0; l < e->dm.L; ++l) {
+    Level& v = e->lv[l];
+    v.cap = caps[l]; v.maxseg = maxseg[l];
+    const int K = e->dm.K[l];
+    v.kcap = (l == e->dm.L - 1) ? 1 : (K < 0 ? maxseg[l] : (K < maxseg[l] ? K : maxseg[l]));
+  }
+}
+
+void bind(Params& P, const float* base, const int64_t* off, const paths_dims_t& dm) {
+  auto at = [&](int64_t o) { return o < 0 ? nullptr : base + o; };
+  P.Wg = at(off[PATHS_P_WG]); P.bg = at(off[PATHS_P_BG]); P.Wmo = at(off[PATHS_P_WMO]); P.bmo = at(off[PATHS_P_BMO]);
+  for (int l = 0; l < dm.L; ++l) {
+    const int64_t* o = off + PATHS_P_LSTM_COUNT + (size_t)l * PATHS_LEVEL_STRIDE;
+    LevelP& q = P.level[l];
+    q.Wuv = at(o[PATHS_P_WUV]); q.b1 = at(o[PATHS_P_B1]); q.w2 = at(o[PATHS_P_W2]); q.b2 = at(o[PATHS_P_B2]);
+    q.bin = at(o[PATHS_P_BIN]); q.special = at(o[PATHS_P_SPECIAL]); q.nfw = at(o[PATHS_P_NFW]); q.nfb = at(o[PATHS_P_NFB]);
+    q.Wc = at(o[PATHS_P_WC]); q.bc = at(o[PATHS_P_BC]);
+    for (int j = 0; j < dm.layers; ++j) {
+      const int64_t* p = o + PATHS_P_LEVEL_HEAD_COUNT + (size_t)j * PATHS_P_LAYER_COUNT;
+      LayerP& y = q.layer[j];
+      y.Wqkv = at(p[PATHS_P_WQKV]); y.bqkv = at(p[PATHS_P_BQKV]); y.Wo = at(p[PATHS_P_WO]); y.bo = at(p[PATHS_P_BO]);
+      y.bcross = at(p[PATHS_P_BCROSS]); y.W1 = at(p[PATHS_P_FW1]); y.b1 = at(p[PATHS_P_FB1]); y.W2 = at(p[PATHS_P_FW2]);
+      y.b2 = at(p[PATHS_P_FB2]); y.n1w = at(p[PATHS_P_N1W]); y.n1b = at(p[PATHS_P_N1B]); y.n2w = at(p[PATHS_P_N2W]);
+      y.n2b = at(p[PATHS_P_N2B]); y.n3w = at(p[PATHS_P_N3W]); y.n3b = at(p[PATHS_P_N3B]);
+    }
+  }
+}
+
+#define RUN(call)            \
+  do {                       \
+    int _r = (call);         \
+    if (_r) return _r;       \
+    e->launches++;           \
+  } while (0)
+
+inline float* W_(const float* p) { return const_cast<float*>(p); }   // gradient views share the Params struct
+
+int level_forward(paths_engine* e, int l, cudaStream_t st) {
+  const paths_dims_t& dm = e->dm;
+  const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F, prec = dm.precision;
+  Level& v = e->lv[l];
+  const LevelP& p = e->P.level[l];
+  const int M = v.cap;
+  const int* Md = v.count;
+  const int ldg = 3 * C + D;
+
+  // ---- LSTM cell step for every patch (interface.py:49-56); [x || h_parent] is gathered inside the GEMM loader
+  const bool has_parent = l > 0;
+  RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
+  RUN(gemm_nt(prec, Axh, e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, has_parent ? 2 * D : D, 0, st));
+  RUN(lstm_point1_fwd(v.G, has_parent ? e->lv[l - 1].Cn : nullptr, has_parent ? v.row_parent : nullptr, v.Cn, D, C, M, Md, st));
+  RUN(gemm_nt(prec, row_src(v.Cn, C, C), e->P.Wmo, C, 0, v.Pt, D, e->P.bmo, M, Md, D, C, 0, st));
+  RUN(lstm_point2_fwd(v.Pt, v.G, v.X, v.H, v.Y, D, C, M, Md, st));
+
+  // ---- importance + token projection share one contraction over Y (paths.py:95-98, aggregator.py:48)
+  RUN(gemm_nt(prec, row_src(v.Y, D, D), p.Wuv, D, 0, v.UV, I + d, nullptr, M, Md, I + d, D, 0, st));
+  RUN(imp_tok_fwd(v.UV, p.b1, p.w2, p.b2, p.bin, e->div, v.row_slide, v.row_xy, v.seg, v.alpha, v.tok, I, d, dm.imp_mul,
+                  dm.pe_mode, M, Md, st));
+  RUN(special_fill(p.special, v.seg, v.tok, d, B, st));
+
+  // ---- transformer aggregator: decoder layers over packed tokens, last layer evaluated at the special token only
+  const int Mt = v.ncap_tok;
+  const int* Mtd = v.ntok;
+  const float* t_in = v.tok;
+  for (int j = 0; j < dm.layers; ++j) {
+    const LayerP& w = p.layer[j];
+    LayerBuf& y = v.layer[j];
+    const bool last = j == dm.layers - 1;
+    const int R = last ? B : Mt;
+    const int* Rd = last ? nullptr : Mtd;
+    RUN(gemm_nt(prec, row_src(t_in, d, d), w.Wqkv, d, 0, y.qkv, 3 * d, w.bqkv, Mt, Mtd, 3 * d, d, 0, st));
+    RUN(attn_fwd(y.qkv, v.seg, y.O, y.lse, d, dm.heads, B, v.maxseg + 1, last ? 1 : 0, st));
+    RUN(gemm_nt(prec, row_src(y.O, d, d), w.Wo, d, 0, e->A1, d, nullptr, R, Rd, d, d, 0, st));
+    RUN(res_ln_fwd(t_in, last ? v.tseg : nullptr, e->A1, w.bo, w.n1w, w.n1b, y.y1, y.xh1, y.rs1, d, 1e-5f, last ? B : Mt, Rd, 0, st));
+    RUN(res_ln_fwd(y.y1, nullptr, nullptr, w.bcross, w.n2w, w.n2b, y.y2, y.xh2, y.rs2, d, 1e-5f, last ? B : Mt, Rd, 0, st));
+    RUN(gemm_nt(prec, row_src(y.y2, d, d), w.W1, d, 0, y.Hf, F, w.b1, R, Rd, F, d, GEMM_RELU, st));
+    RUN(gemm_nt(prec, row_src(y.Hf, F, F), w.W2, F, 0, e->Fo, d, nullptr, R, Rd, d, F, 0, st));
+    RUN(res_ln_fwd(y.y2, nullptr, e->Fo, w.b2, w.n3w, w.n3b, y.y3, y.xh3, y.rs3, d, 1e-5f, last ? B : Mt, Rd, 0, st));
+    t_in = y.y3;
+  }
+  RUN(res_ln_fwd(t_in, nullptr, nullptr, nullptr, p.nfw, p.nfb, v.z, v.xhf, v.rsf, d, 1e-5f, B, nullptr, 0, st));
+  // ---- residual slide context + classifier (paths.py:130-139)
+  RUN(head_fwd(v.z, (dm.residual && l > 0) ? e->lv[l - 1].F : nullptr, p.Wc, p.bc, v.F, v.logits, d, dm.nl, B, st));
+  return 0;
+}
+
+int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
+  const paths_dims_t& dm = e->dm;
+  const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F, prec = dm.precision;
+  Level& v = e->lv[l];
+  const LevelP& p = e->P.level[l];
+  const LevelP& g = e->Gr.level[l];
+  const int M = v.cap;
+  const int* Md = v.count;
+  const int Mt = v.ncap_tok;
+  const int* Mtd = v.ntok;
+  const int ldg = 3 * C + D;
+  const bool last_level = l == dm.L - 1;
+
+  // ---- head: dF = dF(l+1) + dlogits.Wc
+  const float* dF_in = (dm.residual && !last_level) ? e->dF : nullptr;
+  const float* dlog = use_dlogits ? v.dlogits : nullptr;
+  RUN(head_bwd(dlog, dF_in, p.Wc, e->dF, d, dm.nl, B, st));
+  if (dlog) {
+    RUN(gemm_tn(prec, dlog, dm.nl, row_src(v.F, d, d), W_(g.Wc), d, B, nullptr, dm.nl, d, st));
+    RUN(colsum_accum(dlog, dm.nl, W_(g.bc), B, nullptr, dm.nl, st));
+  }
+  // ---- final LayerNorm at the special tokens
+  RUN(ln_bwd(e->dF, nullptr, v.xhf, v.rsf, p.nfw, e->dy3s, nullptr, 0, W_(g.nfw), W_(g.nfb), nullptr, d, B, nullptr, 0, st));
+
+  const float* dy3 = e->dy3s;
+  for (int j = dm.layers - 1; j >= 0; --j) {
+    const LayerP& w = p.layer[j];
+    const LayerP& gw = g.layer[j];
+    LayerBuf& y = v.layer[j];
+    const bool last = j == dm.layers - 1;
+    const int R = last ? B : Mt;
+    const int* Rd = last ? nullptr : Mtd;
+    const float* t_in = j == 0 ? v.tok : v.layer[j - 1].y3;
+    // LN3 -> ga = d(y2 + ffn); db2
+    RUN(ln_bwd(dy3, nullptr, y.xh3, y.rs3, w.n3w, e->ga, nullptr, 0, W_(gw.n3w), W_(gw.n3b), W_(gw.b2), d, R, Rd, 0, st));
+    RUN(gemm_nt(prec, row_src(e->ga, d, d), w.W2, F, 1, e->dHf, F, nullptr, R, Rd, F, d, 0, st));
+    RUN(gemm_tn(prec, e->ga, d, row_src(y.Hf, F, F), W_(gw.W2), F, R, Rd, d, F, st));
+    RUN(relu_bwd(e->dHf, y.Hf, F, R, Rd, 0, st));
+    RUN(gemm_tn(prec, e->dHf, F, row_src(y.y2, d, d), W_(gw.W1), d, R, Rd, F, d, st));
+    RUN(colsum_accum(e->dHf, F, W_(gw.b1), R, Rd, F, st));
+    RUN(gemm_nt(prec, row_src(e->dHf, F, F), w.W1, d, 1, e->ga, d, nullptr, R, Rd, d, F, GEMM_ACCUM, st));     // ga = dy2
+    // LN2 (cross-attention over an empty memory contributes only its output bias), then LN1
+    RUN(ln_bwd(e->ga, nullptr, y.xh2, y.rs2, w.n2w, e->gb, nullptr, 0, W_(gw.n2w), W_(gw.n2b), W_(gw.bcross), d, R, Rd, 0, st));
+    RUN(ln_bwd(e->gb, nullptr, y.xh1, y.rs1, w.n1w, e->ga, nullptr, 0, W_(gw.n1w), W_(gw.n1b), W_(gw.bo), d, R, Rd, 0, st));  // ga = da
+    RUN(gemm_nt(prec, row_src(e->ga, d, d), w.Wo, d, 1, e->gO, d, nullptr, R, Rd, d, d, 0, st));
+    RUN(gemm_tn(prec, e->ga, d, row_src(y.O, d, d), W_(gw.Wo), d, R, Rd, d, d, st));
+    if (last) RUN(zero_rows(e->dqkv, 3 * d, Mt, Mtd, 0, st));
+    RUN(attn_bwd(y.qkv, v.seg, y.O, y.lse, e->gO, e->dqkv, e->Dvec, d, dm.heads, B, v.maxseg + 1, last ? 1 : 0, st));
+    RUN(gemm_tn(prec, e->dqkv, 3 * d, row_src(t_in, d, d), W_(gw.Wqkv), d, Mt, Mtd, 3 * d, d, st));
+    RUN(colsum_accum(e->dqkv, 3 * d, W_(gw.bqkv), Mt, Mtd, 3 * d, st));
+    if (last) {
+      RUN(gemm_nt(prec, row_src(e->dqkv, 3 * d, 3 * d), w.Wqkv, d, 1, e->gt, d, nullptr, Mt, Mtd, d, 3 * d, 0, st));
+      RUN(scatter_add_rows(e->ga, v.tseg, e->gt, d, B, st));
+      dy3 = e->gt;
+    } else {
+      // ga holds da (the residual branch); add the attention branch, then hand the buffer over as the next layer's dy3
+      RUN(gemm_nt(prec, row_src(e->dqkv, 3 * d, 3 * d), w.Wqkv, d, 1, e->ga, d, nullptr, Mt, Mtd, d, 3 * d, GEMM_ACCUM, st));
+      float* tmp = e->ga; e->ga = e->gt; e->gt = tmp;
+      dy3 = e->gt;
+    }
+  }
+  const float* dtok = dy3;
+  // ---- special token, importance / projection
+  RUN(special_grad(dtok, v.seg, W_(g.special), d, B, st));
+  RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, e->dUV, W_(g.b1), W_(g.w2), W_(g.b2), W_(g.bin), I, d, dm.imp_mul, M, Md, st));
+  RUN(gemm_nt(prec, row_src(e->dUV, I + d, I + d), p.Wuv, D, 1, e->dY, D, nullptr, M, Md, D, I + d, 0, st));
+  RUN(gemm_tn(prec, e->dUV, I + d, row_src(v.Y, D, D), W_(g.Wuv), D, M, Md, I + d, D, st));
+  // ---- state gradients arriving from the children of this level's selected rows
+  const bool has_children = !last_level;
+  if (has_children)
+    RUN(parent_sum(v.child_of, e->lv[l + 1].dHrow, e->lv[l + 1].dCrow, e->dHc, e->dCc, D, C, M, Md, st));
+  // ---- LSTM cell
+  RUN(lstm_point2_bwd(e->dY, has_children ? e->dHc : nullptr, v.Pt, v.G, e->dP, e->dG, D, C, M, Md, st));
+  RUN(gemm_nt(prec, row_src(e->dP, D, D), e->P.Wmo, C, 1, e->dCn, C, nullptr, M, Md, C, D, 0, st));
+  RUN(gemm_tn(prec, e->dP, D, row_src(v.Cn, C, C), W_(e->Gr.Wmo), C, M, Md, D, C, st));
+  RUN(colsum_accum(e->dP, D, W_(e->Gr.bmo), M, Md, D, st));
+  const bool has_parent = l > 0;
+  RUN(lstm_point1_bwd(e->dCn, has_children ? e->dCc : nullptr, v.G, has_parent ? e->lv[l - 1].Cn : nullptr,
+                      has_parent ? v.row_parent : nullptr, e->dG, has_parent ? v.dCrow : nullptr, D, C, M, Md, st));
+  if (has_parent)
+    RUN(gemm_nt(prec, row_src(e->dG, ldg, ldg), e->P.Wg + D, 2 * D, 1, v.dHrow, D, nullptr, M, Md, D, ldg, 0, st));
+  RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
+  RUN(gemm_tn(prec, e->dG, ldg, Axh, W_(e->Gr.Wg), 2 * D, M, Md, ldg, has_parent ? 2 * D : D, st));
+  RUN(colsum_accum(e->dG, ldg, W_(e->Gr.bg), M, Md, ldg, st));
+  return 0;
+}
+
+int do_select(paths_engine* e, int l, cudaStream_t st) {
+  const paths_dims_t& dm = e->dm;
+  PATHS_REQUIRE(l >= 0 && l < dm.L - 1, "select: level %d has no successor", l);
+  PATHS_REQUIRE(e->have_store, "select: no pyramid store bound");
+  Level& v = e->lv[l];
+  Level& n = e->lv[l + 1];
+  SelectArgs a;
+  a.alpha = v.alpha; a.seg = v.seg; a.row_xy = v.row_xy; a.count = v.count; a.B = e->B; a.cap = v.cap;
+  a.keep = dm.K[l]; a.kcap = v.kcap;
+  a.gw = e->store.gw; a.gh = e->store.gh; a.occ_off = reinterpret_cast<const unsigned long long*>(e->store.occ_off);
+  a.occ = e->store.occ; a.nonbg = e->store.nonbg; a.level = l; a.L = dm.L; a.slide_ids = e->slide_ids;
+  a.sel = v.sel; a.sel_count = v.sel_count; a.child_of = v.child_of;
+  a.n_count = n.count; a.n_seg = n.seg; a.n_row_slide = n.row_slide; a.n_row_xy = n.row_xy; a.n_row_parent = n.row_parent;
+  a.n_parent_local = n.parent_local; a.n_cap = n.cap; a.n_ntok = n.ntok;
+  a.overflow = e->overflow; a.slide_cnt = e->slide_cnt; a.slide_fb = e->slide_fb;
+  RUN(select_expand(a, st)); e->launches += 2;
+  tseg_kernel<<<(e->B + 255) / 256, 256, 0, st>>>(n.seg, n.tseg, e->B);
+  PATHS_LAUNCH_CK(); e->launches++;
+  RUN(gather_rows(e->store.grid_ptr, e->store.gh, l + 1, dm.L, e->slide_ids, n.row_slide, n.row_xy, n.X, dm.D, n.cap, n.count, st));
+  return 0;
+}
+
+int do_begin(paths_engine* e, const int32_t* slide_ids, const float* fts_padded, int N, cudaStream_t st) {
+  PATHS_REQUIRE(e->have_store, "begin: no pyramid store bound");
+  e->slide_ids = slide_ids;
+  Level& v = e->lv[0];
+  PATHS_CK(cudaMemsetAsync(e->overflow, 0, 2 * sizeof(int), st));
+  RUN(level0_rows(e->store.gw, e->store.gh, e->dm.L, slide_ids, e->B, v.cap, v.count, v.ntok, v.seg, v.row_slide, v.row_xy,
+                  v.row_parent, v.parent_local, e->overflow, st));
+  e->launches++;
+  tseg_kernel<<<(e->B + 255) / 256, 256, 0, st>>>(v.seg, v.tseg, e->B);
+  PATHS_LAUNCH_CK(); e->launches++;
+  if (fts_padded) RUN(pack_padded_rows(fts_padded, N, v.seg, v.row_slide, v.X, e->dm.D, v.cap, v.count, st));
+  else RUN(gather_rows(e->store.grid_ptr, e->store.gh, 0, e->dm.L, slide_ids, v.row_slide, v.row_xy, v.X, e->dm.D, v.cap, v.count, st));
+  return 0;
+}
+
+int do_loss(paths_engine* e, const int32_t* ybin, const int32_t* cens, float scale, cudaStream_t st) {
+  Level& v = e->lv[e->dm.L - 1];
+  RUN(loss_fwd_bwd(v.logits, ybin, cens, e->hazards, e->loss_per, e->loss, v.dlogits, e->dm.nl, e->B, e->dm.task, scale, st));
+  e->launches++;
+  return 0;
+}
+
+}  // namespace
+
+// ---- C ABI ---------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* paths_last_error(void) { return paths::g_err; }
+int paths_abi_version(void) { return PATHS_ABI_VERSION; }
+
+size_t paths_engine_workspace_bytes(const paths_dims_t* dims, int B, const int32_t* h_caps, const int32_t* h_maxseg) {
+  if (check_dims(dims, B, h_caps, h_maxseg)) return 0;
+  paths_engine tmp;
+  memset(&tmp, 0, sizeof(tmp));
+  tmp.dm = *dims; tmp.B = B;
+  fill_level_meta(&tmp, h_caps, h_maxseg);
+  return carve(&tmp, nullptr);
+}
+
+int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, const int32_t* h_caps, const int32_t* h_maxseg,
+                        void* workspace, size_t workspace_bytes) {
+  PATHS_REQUIRE(out && workspace, "null argument");
+  if (int r = check_dims(dims, B, h_caps, h_maxseg)) return r;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    set_error("no CUDA device: paths_b200 has no CPU fallback");
+    return -3;
+  }
+  paths_engine* e = new (std::nothrow) paths_engine;
+  PATHS_REQUIRE(e, "out of host memory");
+  memset(e, 0, sizeof(*e));
+  e->dm = *dims; e->B = B;
+  fill_level_meta(e, h_caps, h_maxseg);
+  const size_t need = carve(e, nullptr);
+  if (need > workspace_bytes || (reinterpret_cast<uintptr_t>(workspace) & 255) != 0) {
+    set_error("workspace too small or misaligned: need %zu bytes (256-byte aligned), got %zu", need, workspace_bytes);
+    delete e;
+    return -2;
+  }
+  carve(e, static_cast<char*>(workspace));
+  e->ws_base = static_cast<char*>(workspace); e->ws_bytes = need;
+  *out = e;
+  return 0;
+}
+
+void paths_engine_destroy(paths_engine_t* e) { delete e; }
+
+int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grads, int64_t n_floats, const int64_t* h_offsets,
+                             const float* div) {
+  PATHS_REQUIRE(e && params && h_offsets && div, "null argument");
+  bind(e->P, params, h_offsets, e->dm);
+  if (grads) bind(e->Gr, grads, h_offsets, e->dm);
+  e->grads_base = grads;
+  e->grads_floats = (size_t)n_floats;
+  e->div = div;
+  e->have_params = true;
+  return 0;
+}
+
+int paths_engine_bind_store(paths_engine_t* e, const paths_store_t* h_store) {
+  PATHS_REQUIRE(e && h_store, "null argument");
+  e->store = *h_store;
+  e->have_store = true;
+  return 0;
+}
+
+int paths_engine_begin(paths_engine_t* e, const int32_t* slide_ids, void* stream) {
+  PATHS_REQUIRE(e, "null engine");
+  return do_begin(e, slide_ids, nullptr, 0, static_cast<cudaStream_t>(stream));
+}
+
+int paths_engine_begin_padded(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, void* stream) {
+  PATHS_REQUIRE(e && fts_padded, "null argument");
+  return do_begin(e, slide_ids, fts_padded, N, static_cast<cudaStream_t>(stream));
+}
+
+int paths_engine_level_forward(paths_engine_t* e, int level, void* stream) {
+  PATHS_REQUIRE(e && e->have_params, "level_forward: engine has no parameters bound");
+  PATHS_REQUIRE(level >= 0 && level < e->dm.L, "level %d out of range", level);
+  return level_forward(e, level, static_cast<cudaStream_t>(stream));
+}
+
+int paths_engine_select(paths_engine_t* e, int level, void* stream) {
+  PATHS_REQUIRE(e, "null engine");
+  return do_select(e, level, static_cast<cudaStream_t>(stream));
+}
+
+int paths_engine_loss(paths_engine_t* e, const int32_t* ybin, const int32_t* censored, float scale, void* stream) {
+  PATHS_REQUIRE(e && ybin, "null argument");
+  return do_loss(e, ybin, censored, scale, static_cast<cudaStream_t>(stream));
+}
+
+int paths_engine_level_backward(paths_engine_t* e, int level, int use_dlogits, void* stream) {
+  PATHS_REQUIRE(e && e->have_params && e->grads_base, "level_backward: no gradient buffer bound");
+  PATHS_REQUIRE(level >= 0 && level < e->dm.L, "level %d out of range", level);
+  return level_backward(e, level, use_dlogits, static_cast<cudaStream_t>(stream));
+}
+
+int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int32_t* ybin, const int32_t* censored, float scale,
+                         int with_loss, void* stream) {
+  PATHS_REQUIRE(e && e->have_params, "forward: engine has no parameters bound");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (int r = do_begin(e, slide_ids, nullptr, 0, st)) return r;
+  for (int l = 0; l < e->dm.L; ++l) {
+    if (int r = level_forward(e, l, st)) return r;
+    if (l < e->dm.L - 1)
+      if (int r = do_select(e, l, st)) return r;
+  }
+  if (with_loss) return do_loss(e, ybin, censored, scale, st);
+  return 0;
+}
+
+int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream) {
+  PATHS_REQUIRE(e && e->have_params && e->grads_base, "backward: no gradient buffer bound");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (zero_grads) PATHS_CK(cudaMemsetAsync(e->grads_base, 0, e->grads_floats * sizeof(float), st));
+  for (int l = e->dm.L - 1; l >= 0; --l)
+    if (int r = level_backward(e, l, l == e->dm.L - 1, st)) return r;
+  return 0;
+}
+
+int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, size_t* bytes) {
+  PATHS_REQUIRE(e && ptr && bytes, "null argument");
+  PATHS_REQUIRE(level >= 0 && level < e->dm.L, "level %d out of range", level);
+  const paths_dims_t& dm = e->dm;
+  Level& v = e->lv[level];
+  const size_t cap = v.cap, B = e->B, f = sizeof(float), i4 = sizeof(int);
+  void* p = nullptr; size_t n = 0;
+  switch (which) {
+    case PATHS_BUF_COUNT: p = v.count; n = i4; break;
+    case PATHS_BUF_NTOK: p = v.ntok; n = i4; break;
+    case PATHS_BUF_SEG: p = v.seg; n = (B + 1) * i4; break;
+    case PATHS_BUF_TSEG: p = v.tseg; n = B * i4; break;
+    case PATHS_BUF_ROW_SLIDE: p = v.row_slide; n = cap * i4; break;
+    case PATHS_BUF_ROW_XY: p = v.row_xy; n = 2 * cap * i4; break;
+    case PATHS_BUF_ROW_PARENT: p = v.row_parent; n = cap * i4; break;
+    case PATHS_BUF_PARENT_LOCAL: p = v.parent_local; n = cap * i4; break;
+    case PATHS_BUF_SEL: p = v.sel; n = B * (size_t)(v.kcap > 0 ? v.kcap : 1) * i4; break;
+    case PATHS_BUF_SEL_COUNT: p = v.sel_count; n = B * i4; break;
+    case PATHS_BUF_CHILD_OF: p = v.child_of; n = 4 * cap * i4; break;
+    case PATHS_BUF_X: p = v.X; n = cap * dm.D * f; break;
+    case PATHS_BUF_G: p = v.G; n = cap * (3 * (size_t)dm.C + dm.D) * f; break;
+    case PATHS_BUF_CN: p = v.Cn; n = cap * dm.C * f; break;
+    case PATHS_BUF_PT: p = v.Pt; n = cap * dm.D * f; break;
+    case PATHS_BUF_H: p = v.H; n = cap * dm.D * f; break;
+    case PATHS_BUF_Y: p = v.Y; n = cap * dm.D * f; break;
+    case PATHS_BUF_UV: p = v.UV; n = cap * ((size_t)dm.I + dm.d) * f; break;
+    case PATHS_BUF_ALPHA: p = v.alpha; n = cap * f; break;
+    case PATHS_BUF_TOK: p = v.tok; n = (cap + B) * dm.d * f; break;
+    case PATHS_BUF_Z: p = v.z; n = B * dm.d * f; break;
+    case PATHS_BUF_F: p = v.F; n = B * dm.d * f; break;
+    case PATHS_BUF_LOGITS: p = v.logits; n = B * dm.nl * f; break;
+    case PATHS_BUF_DLOGITS: p = v.dlogits; n = B * dm.nl * f; break;
+    case PATHS_BUF_HAZARDS: p = e->hazards; n = B * dm.nl * f; break;
+    case PATHS_BUF_LOSS: p = e->loss; n = f; break;
+    case PATHS_BUF_LOSS_PER: p = e->loss_per; n = B * f; break;
+    case PATHS_BUF_OVERFLOW: p = e->overflow; n = 2 * i4; break;
+    case PATHS_BUF_DF_IN: p = e->dF; n = B * dm.d * f; break;
+    case PATHS_BUF_DHROW: p = v.dHrow; n = cap * dm.D * f; break;
+    case PATHS_BUF_DCROW: p = v.dCrow; n = cap * dm.C * f; break;
+    default: set_error("unknown buffer id %d", which); return -2;
+  }
+  *ptr = p; *bytes = n;
+  return 0;
+}
+
+int paths_engine_set_precision(paths_engine_t* e, int precision) {
+  PATHS_REQUIRE(e && precision >= 0 && precision <= 2, "precision must be 0, 1 or 2");
+  e->dm.precision = precision;
+  return 0;
+}
+
+int64_t paths_engine_launch_count(paths_engine_t* e) { return e ? e->launches : 0; }
+
+int paths_gemm_nt(int precision, const float* A, int lda, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias,
+                  int M, int N, int K, int flags, void* stream) {
+  return gemm_nt(precision, row_src(A, lda, K), B, ldb, b_kn, C, ldc, bias, M, nullptr, N, K, flags, static_cast<cudaStream_t>(stream));
+}
+
+int paths_gemm_tn(int precision, const float* P, int ldp, const float* Q, int ldq, float* C, int ldc, int M, int NI, int NJ, void* stream) {
+  return gemm_tn(precision, P, ldp, row_src(Q, ldq, NJ), C, ldc, M, nullptr, NI, NJ, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

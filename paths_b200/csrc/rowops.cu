@@ -1,0 +1,675 @@
+// Row-wise (HBM-bound) kernels of the PATHS level: feature gather, LSTM gate math, importance + positional
+// encoding, residual LayerNorms, the classifier head and the survival loss -- forward and backward.
+// One warp per packed row, lanes striding the feature dimension (coalesced 128 B per access).
+#include "common.cuh"
+#include "rowops.cuh"
+
+namespace paths {
+
+namespace {
+
+constexpr int WPB = 8;                 // warps per block
+constexpr int TPB = WPB * 32;
+
+__device__ __forceinline__ int row_count(int M_host, const int* M_dev) { return M_dev ? *M_dev : M_host; }
+
+#define ROW_LOOP(m, M)                                                                  \
+  const int lane = threadIdx.x & 31;                                                    \
+  for (int m = blockIdx.x * WPB + (threadIdx.x >> 5); m < (M); m += gridDim.x * WPB)
+
+// ---------------------------------------------------------------------------------------------------------
+// gather: X[m,:] = grid(slide, level)[x*H + y, :]         (data_utils/slide.py:331 `fts[new_locs[:,0], new_locs[:,1]]`)
+__global__ void __launch_bounds__(TPB) gather_rows_kernel(const float* const* __restrict__ grid_ptr, const int* __restrict__ gh,
+                                                          int level, int L, const int* __restrict__ slide_ids,
+                                                          const int* __restrict__ row_slide, const int* __restrict__ row_xy,
+                                                          float* __restrict__ X, int D, int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  ROW_LOOP(m, M) {
+    const int s = row_slide[m];
+    const int sid = slide_ids ? slide_ids[s] : s;
+    const float* src = grid_ptr[(size_t)sid * L + level] + ((size_t)row_xy[2 * m] * gh[(size_t)sid * L + level] + row_xy[2 * m + 1]) * D;
+    float4* dst = reinterpret_cast<float4*>(X + (size_t)m * D);
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    for (int c = lane; c < D / 4; c += 32) dst[c] = __ldg(s4 + c);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// LSTM cell, model/interface.py:49-56.  G holds the pre-activations [f | r | m | o] (+bias) of one row.
+__global__ void __launch_bounds__(TPB) lstm_point1_fwd_kernel(float* __restrict__ G, const float* __restrict__ Cprev,
+                                                              const int* __restrict__ parent, float* __restrict__ Cn,
+                                                              int D, int C, int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ldg = 3 * C + D;
+  ROW_LOOP(m, M) {
+    float* g = G + (size_t)m * ldg;
+    const int p = parent ? parent[m] : -1;
+    const float* cp = (Cprev && p >= 0) ? Cprev + (size_t)p * C : nullptr;
+    for (int c = lane; c < C; c += 32) {
+      const float f = sigmoidf_(g[c]), r = sigmoidf_(g[C + c]), mm = tanhf(g[2 * C + c]);
+      g[c] = f; g[C + c] = r; g[2 * C + c] = mm;
+      const float cprev = cp ? cp[c] : 0.f;
+      Cn[(size_t)m * C + c] = cprev * f + r * mm;
+    }
+    for (int j = lane; j < D; j += 32) g[3 * C + j] = sigmoidf_(g[3 * C + j]);
+  }
+}
+
+// t = tanh(P), h' = o * t, Y = X + h'                       (interface.py:56, paths.py:89)
+__global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(float* __restrict__ Pt, const float* __restrict__ G,
+                                                              const float* __restrict__ X, float* __restrict__ H,
+                                                              float* __restrict__ Y, int D, int C, int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ldg = 3 * C + D;
+  ROW_LOOP(m, M) {
+    for (int j = lane; j < D; j += 32) {
+      const float t = tanhf(Pt[(size_t)m * D + j]);
+      Pt[(size_t)m * D + j] = t;
+      const float h = G[(size_t)m * ldg + 3 * C + j] * t;
+      H[(size_t)m * D + j] = h;
+      Y[(size_t)m * D + j] = X[(size_t)m * D + j] + h;
+    }
+  }
+}
+
+// dH = dY + dHc;  do = dH*t, dP = dH*o*(1-t^2), dGo = do*o*(1-o)
+__global__ void __launch_bounds__(TPB) lstm_point2_bwd_kernel(const float* __restrict__ dY, const float* __restrict__ dHc,
+                                                              const float* __restrict__ Pt, const float* __restrict__ G,
+                                                              float* __restrict__ dP, float* __restrict__ dG, int D, int C,
+                                                              int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ldg = 3 * C + D;
+  ROW_LOOP(m, M) {
+    for (int j = lane; j < D; j += 32) {
+      float dh = dY ? dY[(size_t)m * D + j] : 0.f;
+      if (dHc) dh += dHc[(size_t)m * D + j];
+      const float t = Pt[(size_t)m * D + j], o = G[(size_t)m * ldg + 3 * C + j];
+      dP[(size_t)m * D + j] = dh * o * (1.f - t * t);
+      dG[(size_t)m * ldg + 3 * C + j] = dh * t * o * (1.f - o);
+    }
+  }
+}
+
+// dc' = dCn + dCc;  df, dr, dm -> dG[:, :3C];  dCrow = dc' * f (gradient w.r.t. the inherited c of this row)
+__global__ void __launch_bounds__(TPB) lstm_point1_bwd_kernel(const float* __restrict__ dCn, const float* __restrict__ dCc,
+                                                              const float* __restrict__ G, const float* __restrict__ Cprev,
+                                                              const int* __restrict__ parent, float* __restrict__ dG,
+                                                              float* __restrict__ dCrow, int D, int C, int M_host,
+                                                              const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ldg = 3 * C + D;
+  ROW_LOOP(m, M) {
+    const float* g = G + (size_t)m * ldg;
+    float* dg = dG + (size_t)m * ldg;
+    const int p = parent ? parent[m] : -1;
+    const float* cp = (Cprev && p >= 0) ? Cprev + (size_t)p * C : nullptr;
+    for (int c = lane; c < C; c += 32) {
+      float dc = dCn[(size_t)m * C + c];
+      if (dCc) dc += dCc[(size_t)m * C + c];
+      const float f = g[c], r = g[C + c], mm = g[2 * C + c];
+      const float cprev = cp ? cp[c] : 0.f;
+      dg[c] = dc * cprev * f * (1.f - f);
+      dg[C + c] = dc * mm * r * (1.f - r);
+      dg[2 * C + c] = dc * r * (1.f - mm * mm);
+      if (dCrow) dCrow[(size_t)m * C + c] = dc * f;
+    }
+  }
+}
+
+// Deterministic child -> parent sum of state gradients (autograd of `torch.cat((ctx_patch,)*4)[filter]`, slide.py:318-329).
+__global__ void __launch_bounds__(TPB) parent_sum_kernel(const int* __restrict__ child_of, const float* __restrict__ dHrow,
+                                                         const float* __restrict__ dCrow, float* __restrict__ dHc,
+                                                         float* __restrict__ dCc, int D, int C, int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  ROW_LOOP(m, M) {
+    int ch[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ch[j] = child_of[4 * m + j];
+    for (int c = lane; c < D; c += 32) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) if (ch[j] >= 0) s += dHrow[(size_t)ch[j] * D + c];
+      dHc[(size_t)m * D + c] = s;
+    }
+    for (int c = lane; c < C; c += 32) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) if (ch[j] >= 0) s += dCrow[(size_t)ch[j] * C + c];
+      dCc[(size_t)m * C + c] = s;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// importance + token: u = relu(U+b1); alpha = sigmoid(u.w2+b2); tok = alpha*V + b_in + PE      (paths.py:95-98,120-124;
+// aggregator.py:43-56; utils.py:47-67).  UV = Y.[W1;Win]^T is produced by the preceding GEMM (row scaling commutes).
+__device__ __forceinline__ float pos_enc(int pe_mode, const float* __restrict__ div, int d, int c, int x, int y, int i) {
+  if (pe_mode == 2) {                       // 2-D: first half from x, second half from y; d/4 frequencies
+    const int half = d / 2;
+    const int cc = c < half ? c : c - half;
+    const float pos = (float)(c < half ? x : y);
+    const float a = pos * div[cc >> 1];
+    return (cc & 1) ? cosf(a) : sinf(a);
+  }
+  const float a = (float)i * div[c >> 1];    // 1-D over the row index inside the bag (utils.py:16-23)
+  return (c & 1) ? cosf(a) : sinf(a);
+}
+
+__global__ void __launch_bounds__(TPB) imp_tok_fwd_kernel(float* __restrict__ UV, const float* __restrict__ b1,
+                                                          const float* __restrict__ w2, const float* __restrict__ b2,
+                                                          const float* __restrict__ bin, const float* __restrict__ div,
+                                                          const int* __restrict__ row_slide, const int* __restrict__ row_xy,
+                                                          const int* __restrict__ seg, float* __restrict__ alpha,
+                                                          float* __restrict__ tok, int I, int d, int imp_mul, int pe_mode,
+                                                          int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ld = I + d;
+  ROW_LOOP(m, M) {
+    float* uv = UV + (size_t)m * ld;
+    float s = 0.f;
+    for (int j = lane; j < I; j += 32) {
+      const float u = fmaxf(uv[j] + b1[j], 0.f);
+      uv[j] = u;
+      s += u * w2[j];
+    }
+    s = warp_sum(s) + b2[0];
+    const float a = sigmoidf_(s);
+    if (lane == 0) alpha[m] = a;
+    const int sl = row_slide[m];
+    const int x = row_xy[2 * m], y = row_xy[2 * m + 1], i = m - seg[sl];
+    float* t = tok + (size_t)(m + sl + 1) * d;
+    const float sc = imp_mul ? a : 1.f;
+    for (int c = lane; c < d; c += 32) t[c] = sc * uv[I + c] + bin[c] + pos_enc(pe_mode, div, d, c, x, y, i);
+  }
+}
+
+__global__ void __launch_bounds__(TPB) special_fill_kernel(const float* __restrict__ special, const int* __restrict__ seg,
+                                                           float* __restrict__ tok, int d, int B) {
+  ROW_LOOP(s, B) {
+    float* t = tok + (size_t)(seg[s] + s) * d;
+    for (int c = lane; c < d; c += 32) t[c] = special[c];
+  }
+}
+
+// backward of imp_tok: dUV = [du | dV]; accumulates db1, dw2, db2, dbin.  Columns are lane-strided so every lane
+// keeps private partial sums for its columns across the rows its warp visits (d, I <= 256).
+__global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restrict__ dtok, const float* __restrict__ UV,
+                                                          const float* __restrict__ alpha, const float* __restrict__ w2,
+                                                          const int* __restrict__ row_slide, float* __restrict__ dUV,
+                                                          float* __restrict__ db1, float* __restrict__ dw2, float* __restrict__ db2,
+                                                          float* __restrict__ dbin, int I, int d, int imp_mul, int M_host,
+                                                          const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ld = I + d;
+  float a_b1[8], a_w2[8], a_bin[8], a_b2 = 0.f;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) a_b1[q] = a_w2[q] = a_bin[q] = 0.f;
+  ROW_LOOP(m, M) {
+    const float* uv = UV + (size_t)m * ld;
+    const float* dt = dtok + (size_t)(m + row_slide[m] + 1) * d;
+    float* duv = dUV + (size_t)m * ld;
+    const float a = alpha[m];
+    float da = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int c = lane + 32 * q;
+      if (c < d) {
+        const float g = dt[c];
+        a_bin[q] += g;
+        da += g * uv[I + c];
+        duv[I + c] = imp_mul ? a * g : g;
+      }
+    }
+    float ds = 0.f;
+    if (imp_mul) { da = warp_sum(da); ds = da * a * (1.f - a); }
+    a_b2 += ds;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int j = lane + 32 * q;
+      if (j < I) {
+        const float u = uv[j];
+        a_w2[q] += ds * u;
+        const float du = (u > 0.f) ? ds * w2[j] : 0.f;
+        a_b1[q] += du;
+        duv[j] = du;
+      }
+    }
+  }
+  // block reduction through shared memory, then one atomic per column per block
+  __shared__ float red[WPB][3][256];
+  const int w = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    red[w][0][lane + 32 * q] = a_b1[q]; red[w][1][lane + 32 * q] = a_w2[q]; red[w][2][lane + 32 * q] = a_bin[q];
+  }
+  __shared__ float red_b2[WPB];
+  if (lane == 0) red_b2[w] = a_b2;
+  __syncthreads();
+  for (int c = threadIdx.x; c < 256; c += TPB) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < WPB; ++ww) { s0 += red[ww][0][c]; s1 += red[ww][1][c]; s2 += red[ww][2][c]; }
+    if (c < I) { if (s0 != 0.f) atomicAdd(db1 + c, s0); if (s1 != 0.f) atomicAdd(dw2 + c, s1); }
+    if (c < d && s2 != 0.f) atomicAdd(dbin + c, s2);
+  }
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < WPB; ++ww) s += red_b2[ww];
+    if (s != 0.f) atomicAdd(db2, s);
+  }
+}
+
+__global__ void __launch_bounds__(256) special_grad_kernel(const float* __restrict__ dtok, const int* __restrict__ seg,
+                                                           float* __restrict__ dspecial, int d, int B) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= d) return;
+  float s = 0.f;
+  for (int b = 0; b < B; ++b) s += dtok[(size_t)(seg[b] + b) * d + c];
+  atomicAdd(dspecial + c, s);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// y = LayerNorm(res[ridx] + add + bias) (post-norm residual block of nn.TransformerDecoderLayer), saving xhat and rstd.
+__global__ void __launch_bounds__(TPB) res_ln_fwd_kernel(const float* __restrict__ res, const int* __restrict__ ridx,
+                                                         const float* __restrict__ add, const float* __restrict__ bias,
+                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                         float* __restrict__ y, float* __restrict__ xhat, float* __restrict__ rstd,
+                                                         int d, float eps, int M_host, const int* M_dev, int M_extra) {
+  const int M = row_count(M_host, M_dev) + M_extra;
+  ROW_LOOP(m, M) {
+    const float* r = res ? res + (size_t)(ridx ? ridx[m] : m) * d : nullptr;
+    float v[8];
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int c = lane + 32 * q;
+      float x = 0.f;
+      if (c < d) {
+        if (r) x = r[c];
+        if (add) x += add[(size_t)m * d + c];
+        if (bias) x += bias[c];
+      }
+      v[q] = x; s += x;
+    }
+    const float mean = warp_sum(s) / d;
+    float var = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) { const int c = lane + 32 * q; if (c < d) { const float t = v[q] - mean; var += t * t; } }
+    var = warp_sum(var) / d;
+    const float rs = rsqrtf(var + eps);
+    if (lane == 0) rstd[m] = rs;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int c = lane + 32 * q;
+      if (c < d) {
+        const float xh = (v[q] - mean) * rs;
+        xhat[(size_t)m * d + c] = xh;
+        y[(size_t)m * d + c] = xh * gamma[c] + beta[c];
+      }
+    }
+  }
+}
+
+// dx = rstd * (g - mean(g) - xhat*mean(g*xhat)), g = dy*gamma.  dx is written (or accumulated) to dx[didx[m]];
+// dgamma/dbeta and (optionally) colsum(dx) -> dbias are accumulated.
+__global__ void __launch_bounds__(TPB) ln_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ dy2,
+                                                     const float* __restrict__ xhat, const float* __restrict__ rstd,
+                                                     const float* __restrict__ gamma, float* __restrict__ dx, const int* __restrict__ didx,
+                                                     int accum, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                     float* __restrict__ dbias, int d, int M_host, const int* M_dev, int M_extra) {
+  const int M = row_count(M_host, M_dev) + M_extra;
+  float a_g[8], a_b[8], a_x[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) a_g[q] = a_b[q] = a_x[q] = 0.f;
+  ROW_LOOP(m, M) {
+    float g[8], xh[8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int c = lane + 32 * q;
+      g[q] = 0.f; xh[q] = 0.f;
+      if (c < d) {
+        float dyv = dy[(size_t)m * d + c];
+        if (dy2) dyv += dy2[(size_t)m * d + c];
+        xh[q] = xhat[(size_t)m * d + c];
+        a_g[q] += dyv * xh[q]; a_b[q] += dyv;
+        g[q] = dyv * gamma[c];
+        s1 += g[q]; s2 += g[q] * xh[q];
+      }
+    }
+    s1 = warp_sum(s1) / d; s2 = warp_sum(s2) / d;
+    const float rs = rstd[m];
+    float* o = dx + (size_t)(didx ? didx[m] : m) * d;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int c = lane + 32 * q;
+      if (c < d) {
+        const float v = rs * (g[q] - s1 - xh[q] * s2);
+        a_x[q] += v;
+        o[c] = accum ? o[c] + v : v;
+      }
+    }
+  }
+  __shared__ float red[WPB][3][256];
+  const int w = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    red[w][0][lane + 32 * q] = a_g[q]; red[w][1][lane + 32 * q] = a_b[q]; red[w][2][lane + 32 * q] = a_x[q];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < d; c += TPB) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < WPB; ++ww) { s0 += red[ww][0][c]; s1 += red[ww][1][c]; s2 += red[ww][2][c]; }
+    if (s0 != 0.f) atomicAdd(dgamma + c, s0);
+    if (s1 != 0.f) atomicAdd(dbeta + c, s1);
+    if (dbias && s2 != 0.f) atomicAdd(dbias + c, s2);
+  }
+}
+
+// relu backward in place: dH *= (H > 0)
+__global__ void relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, size_t ld, int M_host, const int* M_dev, int M_extra) {
+  const size_t n = (size_t)(row_count(M_host, M_dev) + M_extra) * ld;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    if (!(H[i] > 0.f)) dH[i] = 0.f;
+}
+
+__global__ void zero_rows_kernel(float* __restrict__ X, size_t ld, int M_host, const int* M_dev, int M_extra) {
+  const size_t n = (size_t)(row_count(M_host, M_dev) + M_extra) * ld;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) X[i] = 0.f;
+}
+
+// dst[idx[m], :] += src[m, :]   (m < B rows; idx unique)
+__global__ void __launch_bounds__(TPB) scatter_add_rows_kernel(const float* __restrict__ src, const int* __restrict__ idx,
+                                                               float* __restrict__ dst, int d, int B) {
+  ROW_LOOP(m, B) {
+    float* o = dst + (size_t)idx[m] * d;
+    for (int c = lane; c < d; c += 32) o[c] += src[(size_t)m * d + c];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// head: F = z (+ Fprev);  logits = F.Wc^T + bc                         (paths.py:130-139)
+__global__ void __launch_bounds__(TPB) head_fwd_kernel(const float* __restrict__ z, const float* __restrict__ Fprev,
+                                                       const float* __restrict__ Wc, const float* __restrict__ bc,
+                                                       float* __restrict__ F, float* __restrict__ logits, int d, int nl, int B) {
+  ROW_LOOP(s, B) {
+    float v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int c = lane + 32 * q;
+      v[q] = 0.f;
+      if (c < d) { v[q] = z[(size_t)s * d + c] + (Fprev ? Fprev[(size_t)s * d + c] : 0.f); F[(size_t)s * d + c] = v[q]; }
+    }
+    for (int k = 0; k < nl; ++k) {
+      float acc = 0.f;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) { const int c = lane + 32 * q; if (c < d) acc += v[q] * Wc[(size_t)k * d + c]; }
+      acc = warp_sum(acc);
+      if (lane == 0) logits[(size_t)s * nl + k] = acc + bc[k];
+    }
+  }
+}
+
+// dF = dF_in + dlogits.Wc      (dWc, dbc come from gemm_tn / colsum_accum in the engine)
+__global__ void __launch_bounds__(TPB) head_bwd_kernel(const float* __restrict__ dlogits, const float* __restrict__ dF_in,
+                                                       const float* __restrict__ Wc, float* __restrict__ dF, int d, int nl, int B) {
+  ROW_LOOP(s, B) {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int c = lane + 32 * q;
+      if (c < d) {
+        float g = dF_in ? dF_in[(size_t)s * d + c] : 0.f;
+        if (dlogits)
+          for (int k = 0; k < nl; ++k) g += dlogits[(size_t)s * nl + k] * Wc[(size_t)k * d + c];
+        dF[(size_t)s * d + c] = g;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// survival NLL (utils.py:283-305, alpha=0.4, eps=1e-7, mean over the batch) on hazards = sigmoid(logits) (utils.py:269),
+// and its gradient w.r.t. the logits.  task 1: cross-entropy (utils.py:277).
+__global__ void loss_kernel(const float* __restrict__ logits, const int* __restrict__ ybin, const int* __restrict__ cens,
+                            float* __restrict__ hazards, float* __restrict__ loss_per, float* __restrict__ dlogits,
+                            int nl, int B, int task, float alpha, float eps, float scale /* 1 / global batch */) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= B) return;
+  const float* lg = logits + (size_t)s * nl;
+  const int y = ybin[s];
+  if (task == 0) {
+    const float c = (float)cens[s];
+    float surv_y = 1.f, surv_y1 = 1.f, hy = 0.f;
+    for (int k = 0; k < nl; ++k) {
+      const float h = sigmoidf_(lg[k]);
+      hazards[(size_t)s * nl + k] = h;
+      if (k < y) surv_y *= (1.f - h);
+      if (k <= y) surv_y1 *= (1.f - h);
+      if (k == y) hy = h;
+    }
+    const float unc = -(1.f - c) * (logf(fmaxf(surv_y, eps)) + logf(fmaxf(hy, eps)));
+    const float cen = -c * logf(fmaxf(surv_y1, eps));
+    loss_per[s] = (1.f - alpha) * (cen + unc) + alpha * unc;
+    // d loss / d unc = 1 ; d loss / d cen = (1 - alpha)
+    if (dlogits) {
+      const float w_sy = (surv_y > eps) ? -(1.f - c) : 0.f;              // coefficient of log S_pad[y]
+      const float w_hy = (hy > eps) ? -(1.f - c) : 0.f;                  // coefficient of log h[y]
+      const float w_sy1 = (surv_y1 > eps) ? -(1.f - alpha) * c : 0.f;    // coefficient of log S_pad[y+1]
+      for (int k = 0; k < nl; ++k) {
+        const float h = hazards[(size_t)s * nl + k];
+        float dh = 0.f;                                                   // d/dh_k
+        if (k < y) dh += w_sy * (-1.f / (1.f - h));
+        if (k <= y) dh += w_sy1 * (-1.f / (1.f - h));
+        if (k == y) dh += w_hy / h;
+        dlogits[(size_t)s * nl + k] = scale * dh * h * (1.f - h);
+      }
+    }
+  } else {
+    float mx = -INFINITY;
+    for (int k = 0; k < nl; ++k) mx = fmaxf(mx, lg[k]);
+    float se = 0.f;
+    for (int k = 0; k < nl; ++k) se += expf(lg[k] - mx);
+    const float lse = mx + logf(se);
+    loss_per[s] = lse - lg[y];
+    for (int k = 0; k < nl; ++k) {
+      hazards[(size_t)s * nl + k] = lg[k];
+      if (dlogits) dlogits[(size_t)s * nl + k] = scale * (expf(lg[k] - lse) - (k == y ? 1.f : 0.f));
+    }
+  }
+}
+
+__global__ void loss_reduce_kernel(const float* __restrict__ loss_per, float* __restrict__ loss, int B, float scale) {
+  __shared__ float red[256];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < B; i += 256) s += loss_per[i];
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) loss[0] = red[0] * scale;
+}
+
+inline int row_grid(int M) { int g = (M + WPB - 1) / WPB; if (g > 8 * kNumSMs) g = 8 * kNumSMs; return g < 1 ? 1 : g; }
+
+}  // namespace
+
+// ---- host launchers -----------------------------------------------------------------------------------------
+int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, const int* slide_ids, const int* row_slide,
+                const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st) {
+  PATHS_REQUIRE(D % 4 == 0, "gather_rows: D must be a multiple of 4");
+  if (M_host <= 0) return 0;
+  gather_rows_kernel<<<row_grid(M_host), TPB, 0, st>>>(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  lstm_point1_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(G, Cprev, parent, Cn, D, C, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  lstm_point2_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(Pt, G, X, H, Y, D, C, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int lstm_point2_bwd(const float* dY, const float* dHc, const float* Pt, const float* G, float* dP, float* dG, int D, int C, int M_host,
+                    const int* M_dev, cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  lstm_point2_bwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(dY, dHc, Pt, G, dP, dG, D, C, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int lstm_point1_bwd(const float* dCn, const float* dCc, const float* G, const float* Cprev, const int* parent, float* dG, float* dCrow,
+                    int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  lstm_point1_bwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(dCn, dCc, G, Cprev, parent, dG, dCrow, D, C, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int parent_sum(const int* child_of, const float* dHrow, const float* dCrow, float* dHc, float* dCc, int D, int C, int M_host,
+               const int* M_dev, cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  parent_sum_kernel<<<row_grid(M_host), TPB, 0, st>>>(child_of, dHrow, dCrow, dHc, dCc, D, C, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int imp_tok_fwd(float* UV, const float* b1, const float* w2, const float* b2, const float* bin, const float* div, const int* row_slide,
+                const int* row_xy, const int* seg, float* alpha, float* tok, int I, int d, int imp_mul, int pe_mode, int M_host,
+                const int* M_dev, cudaStream_t st) {
+  PATHS_REQUIRE(I <= 256 && d <= 256, "imp_tok: hidden dims above 256 are not supported (I=%d, d=%d)", I, d);
+  if (M_host <= 0) return 0;
+  imp_tok_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul,
+                                                       pe_mode, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int special_fill(const float* special, const int* seg, float* tok, int d, int B, cudaStream_t st) {
+  special_fill_kernel<<<row_grid(B), TPB, 0, st>>>(special, seg, tok, d, B);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const float* w2, const int* row_slide, float* dUV, float* db1,
+                float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int M_host, const int* M_dev, cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  int g = row_grid(M_host); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
+  imp_tok_bwd_kernel<<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, db1, dw2, db2, dbin, I, d, imp_mul, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int special_grad(const float* dtok, const int* seg, float* dspecial, int d, int B, cudaStream_t st) {
+  special_grad_kernel<<<(d + 255) / 256, 256, 0, st>>>(dtok, seg, dspecial, d, B);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int res_ln_fwd(const float* res, const int* ridx, const float* add, const float* bias, const float* gamma, const float* beta, float* y,
+               float* xhat, float* rstd, int d, float eps, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
+  PATHS_REQUIRE(d <= 256, "layer norm width above 256 is not supported (d=%d)", d);
+  if (M_host + M_extra <= 0) return 0;
+  res_ln_fwd_kernel<<<row_grid(M_host + M_extra), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, M_host, M_dev, M_extra);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rstd, const float* gamma, float* dx, const int* didx, int accum,
+           float* dgamma, float* dbeta, float* dbias, int d, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
+  if (M_host + M_extra <= 0) return 0;
+  int g = row_grid(M_host + M_extra); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
+  ln_bwd_kernel<<<g, TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, M_host, M_dev, M_extra);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
+  if (M_host + M_extra <= 0) return 0;
+  relu_bwd_kernel<<<4 * kNumSMs, 256, 0, st>>>(dH, H, (size_t)ld, M_host, M_dev, M_extra);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
+  if (M_host + M_extra <= 0) return 0;
+  zero_rows_kernel<<<4 * kNumSMs, 256, 0, st>>>(X, (size_t)ld, M_host, M_dev, M_extra);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int scatter_add_rows(const float* src, const int* idx, float* dst, int d, int B, cudaStream_t st) {
+  scatter_add_rows_kernel<<<row_grid(B), TPB, 0, st>>>(src, idx, dst, d, B);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int head_fwd(const float* z, const float* Fprev, const float* Wc, const float* bc, float* F, float* logits, int d, int nl, int B, cudaStream_t st) {
+  PATHS_REQUIRE(d <= 256 && nl <= 32, "head: d <= 256 and at most 32 logits supported");
+  head_fwd_kernel<<<row_grid(B), TPB, 0, st>>>(z, Fprev, Wc, bc, F, logits, d, nl, B);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int head_bwd(const float* dlogits, const float* dF_in, const float* Wc, float* dF, int d, int nl, int B, cudaStream_t st) {
+  head_bwd_kernel<<<row_grid(B), TPB, 0, st>>>(dlogits, dF_in, Wc, dF, d, nl, B);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* hazards, float* loss_per, float* loss, float* dlogits, int nl,
+                 int B, int task, float scale, cudaStream_t st) {
+  loss_kernel<<<(B + 127) / 128, 128, 0, st>>>(logits, ybin, cens, hazards, loss_per, dlogits, nl, B, task, 0.4f, 1e-7f, scale);
+  PATHS_LAUNCH_CK();
+  loss_reduce_kernel<<<1, 256, 0, st>>>(loss_per, loss, B, scale);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+
+}  // namespace paths
+
+// ---- level-0 features from the collated, zero-padded batch["fts"] [B, N, D] (dataset.py:217) into packed rows --------
+namespace paths {
+namespace {
+__global__ void __launch_bounds__(256) pack_padded_kernel(const float* __restrict__ fts, int N, const int* __restrict__ seg,
+                                                          const int* __restrict__ row_slide, float* __restrict__ X, int D,
+                                                          int M_host, const int* M_dev) {
+  const int M = M_dev ? *M_dev : M_host;
+  const int lane = threadIdx.x & 31;
+  for (int m = blockIdx.x * 8 + (threadIdx.x >> 5); m < M; m += gridDim.x * 8) {
+    const int s = row_slide[m], i = m - seg[s];
+    const float4* src = reinterpret_cast<const float4*>(fts + ((size_t)s * N + i) * D);
+    float4* dst = reinterpret_cast<float4*>(X + (size_t)m * D);
+    for (int c = lane; c < D / 4; c += 32) dst[c] = __ldg(src + c);
+  }
+}
+}  // namespace
+int pack_padded_rows(const float* fts, int N, const int* seg, const int* row_slide, float* X, int D, int M_host, const int* M_dev,
+                     cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  int g = (M_host + 7) / 8; if (g > 8 * kNumSMs) g = 8 * kNumSMs;
+  pack_padded_kernel<<<g, 256, 0, st>>>(fts, N, seg, row_slide, X, D, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+}  // namespace paths
+
+// ---- occupancy bitmap of a [cells, D] grid (replaces the per-step `fts[x, y].sum() != 0` probe, slide.py:324) -----
+namespace paths {
+namespace {
+__global__ void __launch_bounds__(256) occupancy_kernel(const float* __restrict__ grid, int cells, int D, unsigned int* __restrict__ bits,
+                                                        int* __restrict__ count) {
+  const int lane = threadIdx.x & 31;
+  int local = 0;
+  for (int c = blockIdx.x * 8 + (threadIdx.x >> 5); c < cells; c += gridDim.x * 8) {
+    const float4* r = reinterpret_cast<const float4*>(grid + (size_t)c * D);
+    bool nz = false;
+    for (int i = lane; i < D / 4; i += 32) { const float4 v = __ldg(r + i); nz |= (v.x != 0.f) | (v.y != 0.f) | (v.z != 0.f) | (v.w != 0.f); }
+    const bool any = __any_sync(0xffffffffu, nz);
+    if (lane == 0 && any) { atomicOr(bits + (c >> 5), 1u << (c & 31)); ++local; }
+  }
+  if (lane == 0 && local) atomicAdd(count, local);
+}
+}  // namespace
+}  // namespace paths
+
+extern "C" int paths_build_occupancy(const float* grid, int cells, int D, uint32_t* bits, int32_t* count, void* stream) {
+  using namespace paths;
+  PATHS_REQUIRE(D % 4 == 0, "occupancy: D must be a multiple of 4");
+  if (cells <= 0) return 0;
+  int g = (cells + 7) / 8; if (g > 8 * kNumSMs) g = 8 * kNumSMs;
+  occupancy_kernel<<<g, 256, 0, static_cast<cudaStream_t>(stream)>>>(grid, cells, D, bits, count);
+  PATHS_LAUNCH_CK();
+  return 0;
+}

@@ -1,0 +1,73 @@
+// Host launchers of the row-wise kernels (rowops.cu), the varlen attention (attention.cu) and the
+// select/expand kernels (select.cu).  All pointers are device pointers; M_dev, when non-null, overrides M_host
+// as the live row count (M_host is then the capacity used to size the grid).
+#pragma once
+#include "common.cuh"
+
+namespace paths {
+
+int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, const int* slide_ids, const int* row_slide,
+                const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st);
+int pack_padded_rows(const float* fts, int N, const int* seg, const int* row_slide, float* X, int D, int M_host, const int* M_dev,
+                     cudaStream_t st);
+int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, int D, int C, int M_host, const int* M_dev, cudaStream_t st);
+int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, int D, int C, int M_host, const int* M_dev, cudaStream_t st);
+int lstm_point2_bwd(const float* dY, const float* dHc, const float* Pt, const float* G, float* dP, float* dG, int D, int C, int M_host,
+                    const int* M_dev, cudaStream_t st);
+int lstm_point1_bwd(const float* dCn, const float* dCc, const float* G, const float* Cprev, const int* parent, float* dG, float* dCrow,
+                    int D, int C, int M_host, const int* M_dev, cudaStream_t st);
+int parent_sum(const int* child_of, const float* dHrow, const float* dCrow, float* dHc, float* dCc, int D, int C, int M_host,
+               const int* M_dev, cudaStream_t st);
+int imp_tok_fwd(float* UV, const float* b1, const float* w2, const float* b2, const float* bin, const float* div, const int* row_slide,
+                const int* row_xy, const int* seg, float* alpha, float* tok, int I, int d, int imp_mul, int pe_mode, int M_host,
+                const int* M_dev, cudaStream_t st);
+int special_fill(const float* special, const int* seg, float* tok, int d, int B, cudaStream_t st);
+int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const float* w2, const int* row_slide, float* dUV, float* db1,
+                float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int M_host, const int* M_dev, cudaStream_t st);
+int special_grad(const float* dtok, const int* seg, float* dspecial, int d, int B, cudaStream_t st);
+int res_ln_fwd(const float* res, const int* ridx, const float* add, const float* bias, const float* gamma, const float* beta, float* y,
+               float* xhat, float* rstd, int d, float eps, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
+int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rstd, const float* gamma, float* dx, const int* didx, int accum,
+           float* dgamma, float* dbeta, float* dbias, int d, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
+int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
+int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
+int scatter_add_rows(const float* src, const int* idx, float* dst, int d, int B, cudaStream_t st);
+int head_fwd(const float* z, const float* Fprev, const float* Wc, const float* bc, float* F, float* logits, int d, int nl, int B, cudaStream_t st);
+int head_bwd(const float* dlogits, const float* dF_in, const float* Wc, float* dF, int d, int nl, int B, cudaStream_t st);
+int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* hazards, float* loss_per, float* loss, float* dlogits, int nl,
+                 int B, int task, float scale, cudaStream_t st);
+
+// attention.cu -- varlen softmax self-attention over packed token rows.  qkv is [ntok, 3d] (q | k | v), heads of width dh.
+// Slide s owns token rows [seg[s]+s, seg[s+1]+s+1).  nq_mode 0: every token is a query; 1: only token 0 of each slide
+// (the last decoder layer is read at the special token only, aggregator.py:75); outputs are then compact [B, d].
+int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st);
+int attn_bwd(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
+             int heads, int B, int max_T, int nq_mode, cudaStream_t st);
+
+// select.cu -- per-slide top-K by importance, 4-child expansion, bounds + occupancy filter, order-preserving compaction
+// (data_utils/slide.py:294-352).
+struct SelectArgs {
+  // level l (input)
+  const float* alpha; const int* seg; const int* row_xy; const int* count; int B; int cap;
+  int keep;                       // K (-1 = keep all)
+  int kcap;                       // per-slide bound on kept rows (host): K, or the per-slide row bound when K = -1
+  // pyramid store, level l+1
+  const int* gw; const int* gh; const unsigned long long* occ_off; const unsigned int* occ; const int* nonbg; int level; int L;
+  const int* slide_ids;
+  // level l outputs
+  int* sel;                       // [B * kcap] kept rows (global), importance-descending; -1 padded
+  int* sel_count;                 // [B]
+  int* child_of;                  // [cap * 4]
+  // level l+1 outputs
+  int* n_count; int* n_seg; int* n_row_slide; int* n_row_xy; int* n_row_parent; int* n_parent_local; int n_cap;
+  int* n_ntok;
+  int* overflow;                  // [2]: flag, rows needed
+  // scratch
+  int* slide_cnt;                 // [B] children per slide (after filter / fallback)
+  int* slide_fb;                  // [B] fallback flag
+};
+int select_expand(const SelectArgs& a, cudaStream_t st);
+int level0_rows(const int* gw, const int* gh, int L, const int* slide_ids, int B, int cap, int* count, int* ntok, int* seg, int* row_slide,
+                int* row_xy, int* row_parent, int* parent_local, int* overflow, cudaStream_t st);
+
+}  // namespace paths

@@ -1,0 +1,218 @@
+"""Binds a RecursiveModel's parameters to level engines and exposes the two reference-facing operations:
+the whole hierarchical step (utils.inference_end2end) with autograd, and one level on a padded PatchBatch
+(RecursiveModel.forward)."""
+from __future__ import annotations
+
+import os
+import warnings
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import _lib as L
+from .engine import Engine, ParamLayout, PyramidStore, make_dims, pe_div_table
+
+PRECISIONS = {"fp32": 0, "bf16x3": 1, "bf16": 2}
+
+
+def default_precision() -> int:
+    return PRECISIONS[os.environ.get("PATHS_B200_PRECISION", "fp32")]
+
+
+class _StepFn(torch.autograd.Function):
+    """Autograd node of one whole hierarchical step.  Gradients of the parameters are accumulated by the engine
+    directly into the flat gradient buffer the parameters' .grad are views of (no per-parameter copies)."""
+
+    @staticmethod
+    def forward(ctx, anchor, rt, eng, slide_ids, fts_padded, ybin, cens, scale):
+        eng.begin(slide_ids, fts_padded)
+        nl = eng.dims.L
+        for l in range(nl):
+            eng.level_forward(l)
+            if l < nl - 1:
+                eng.select(l)
+        eng.loss(ybin, cens, scale)
+        ctx.rt, ctx.eng = rt, eng
+        hz = eng.buffer(0, "HAZARDS").view(eng.B, eng.dims.nl).clone()
+        loss = eng.buffer(0, "LOSS").view(()).clone()
+        ctx.save_for_backward(hz)
+        return hz, loss
+
+    @staticmethod
+    def backward(ctx, g_hz, g_loss):
+        rt, eng = ctx.rt, ctx.eng
+        (hz,) = ctx.saved_tensors
+        dlog = eng.buffer(eng.dims.L - 1, "DLOGITS").view(eng.B, eng.dims.nl)
+        if g_loss is not None:
+            dlog.mul_(g_loss)
+        else:
+            dlog.zero_()
+        if g_hz is not None and rt.track_hazard_grad:
+            dlog.add_(g_hz * hz * (1 - hz) if eng.dims.task == 0 else g_hz)
+        rt.layout.prepare_grads()
+        eng.backward(False)
+        rt.layout.attach_grads()
+        return (None,) * 8
+
+
+class ModelRuntime:
+    def __init__(self, model, precision: Optional[int] = None):
+        self.model = model
+        self.precision = default_precision() if precision is None else precision
+        self.dims = make_dims(model.model_config, model.train_config, self.precision)
+        first = next(model.parameters())
+        if not first.is_cuda:
+            raise RuntimeError("paths_b200: move the model to a CUDA device first (model.to('cuda')); there is no CPU path")
+        self.device = first.device
+        self.layout = ParamLayout(model, self.dims)
+        self.div = pe_div_table(self.dims, self.device)
+        self.anchor = torch.zeros((), device=self.device, requires_grad=True)
+        self.engines: Dict[tuple, Engine] = {}
+        self.track_hazard_grad = False
+        self.strict_overflow = os.environ.get("PATHS_B200_STRICT_OVERFLOW", "0") == "1"
+        self._pending: Optional[Engine] = None
+        self._warned_dropout = False
+        self.global_batch: Optional[int] = None        # set by the data-parallel wrapper: loss = sum / global batch
+
+    # ------------------------------------------------------------------------------------------------------------
+    def set_precision(self, precision) -> None:
+        self.precision = PRECISIONS[precision] if isinstance(precision, str) else int(precision)
+        self.dims.precision = self.precision
+        for e in self.engines.values():
+            e.set_precision(self.precision)
+
+    def _dims_for(self, top_k: Sequence[int]) -> L.Dims:
+        d = L.Dims.from_buffer_copy(self.dims)
+        for i in range(L.MAX_LEVELS):
+            d.K[i] = int(top_k[i]) if i < len(top_k) else -1
+        d.precision = self.precision
+        return d
+
+    def engine_for(self, B: int, caps: Sequence[int], maxseg: Sequence[int], top_k: Sequence[int], tag: str = "step") -> Engine:
+        key = (tag, B, tuple(int(k) for k in top_k))
+        eng = self.engines.get(key)
+        if eng is None or not eng.fits(B, caps, maxseg):
+            if eng is not None:
+                caps = [max(a, b) for a, b in zip(caps, eng.caps)]
+                maxseg = [max(a, b) for a, b in zip(maxseg, eng.maxseg)]
+                del self.engines[key]
+                del eng
+                torch.cuda.empty_cache()
+            eng = Engine(self._dims_for(top_k), B, caps, maxseg, self.device)
+            eng.bind_params(self.layout, self.div)
+            self.engines[key] = eng
+        return eng
+
+    def _check_pending(self) -> None:
+        if self._pending is not None:
+            eng, self._pending = self._pending, None
+            over, need = eng.overflowed()
+            if over:
+                raise RuntimeError(
+                    f"paths_b200: the previous step overflowed a level's row capacity (needed {need} rows): a slide hit the "
+                    "no-child fallback of data_utils/slide.py:336-352.  Its loss was poisoned; rerun with "
+                    "PATHS_B200_STRICT_OVERFLOW=1 to size buffers for the fallback.")
+
+    # ------------------------------------------------------------------------------------------------------------
+    def end2end(self, batch: Dict, keep_patches: Sequence[int], use_batch_fts: bool = True):
+        """utils.inference_end2end (utils.py:228-279) on the device.  `batch` is the collated dict of
+        data_utils/dataset.py:229-243 whose "slide" entries are paths_b200 PreprocessedSlide objects."""
+        self._check_pending()
+        model = self.model
+        if model.training and model.model_config.dropout > 0 and not self._warned_dropout:
+            warnings.warn("paths_b200: dropout is not applied by the CUDA path yet (treated as 0.0)")
+            self._warned_dropout = True
+        slides = batch["slide"]
+        B = len(slides)
+        store: PyramidStore = slides[0].store
+        ids = [s.store_index for s in slides]
+        top_k = list(keep_patches)
+        worst = False
+        while True:
+            caps, maxseg = store.capacities(ids, top_k, worst_case=worst)
+            eng = self.engine_for(B, caps, maxseg, top_k)
+            if getattr(eng, "_store", (None,))[0] is not store or store.tables()[1] is not eng._store[2]:
+                eng.bind_store(store)
+            dev = self.device
+            slide_ids = torch.tensor(ids, dtype=torch.int32).to(dev, non_blocking=True)
+            fts = batch.get("fts") if use_batch_fts else None
+            if fts is not None:
+                fts = fts.to(dev, dtype=torch.float32, non_blocking=True).contiguous()
+            task = self.dims.task
+            if task == 0:
+                ybin = torch.as_tensor(batch["survival_bin"]).to(dev, dtype=torch.int32, non_blocking=True)
+                cens = torch.as_tensor(batch["censored"]).to(dev, dtype=torch.int32, non_blocking=True)
+            else:
+                ybin = torch.as_tensor(batch["subtype"]).to(dev, dtype=torch.int32, non_blocking=True)
+                cens = None
+            scale = 1.0 / float(self.global_batch if self.global_batch else B)
+            if torch.is_grad_enabled():
+                hz, loss = _StepFn.apply(self.anchor, self, eng, slide_ids, fts, ybin, cens, scale)
+            else:
+                hz, loss = _StepFn.forward(_NoCtx(), self.anchor, self, eng, slide_ids, fts, ybin, cens, scale)
+            if self.strict_overflow:
+                over, _ = eng.overflowed()
+                if over and not worst:
+                    worst = True
+                    continue
+            else:
+                self._pending = eng
+            self.last_engine = eng
+            return hz, loss
+
+    # ------------------------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def level_api(self, depth: int, data) -> Dict[str, torch.Tensor]:
+        """RecursiveModel.forward(depth, PatchBatch) (model/interface.py:96-99 -> model/paths.py:66-146): packs the padded
+        batch, runs one engine level, scatters the outputs back to the reference's padded layout."""
+        dm = self.dims
+        B, N = data.batch_size, data.max_patches
+        D, Cc, d = dm.D, dm.C, dm.d
+        num = data.num_ims.to(self.device)
+        valid = data.valid_inds.to(self.device)
+        M = int(num.sum().item())
+        caps = [1] * dm.L
+        maxseg = [1] * dm.L
+        caps[depth] = M
+        maxseg[depth] = N
+        if depth > 0:
+            caps[depth - 1] = M
+            maxseg[depth - 1] = N
+        eng = self.engine_for(B, caps, maxseg, [int(dm.K[i]) for i in range(dm.L - 1)], tag=f"level{depth}")
+        seg = torch.zeros(B + 1, dtype=torch.int32, device=self.device)
+        seg[1:] = torch.cumsum(num, 0).to(torch.int32)
+        ar = torch.arange(B, dtype=torch.int32, device=self.device)
+        eng.buffer(depth, "COUNT").fill_(M)
+        eng.buffer(depth, "NTOK").fill_(M + B)
+        eng.buffer(depth, "SEG").copy_(seg)
+        eng.buffer(depth, "TSEG").copy_(seg[:B] + ar)
+        row_slide = ar[:, None].expand(B, N)[valid]
+        eng.buffer(depth, "ROW_SLIDE")[:M] = row_slide
+        locs = torch.div(data.locs.to(self.device), self.model.model_config.patch_size, rounding_mode="floor")
+        eng.buffer(depth, "ROW_XY").view(-1, 2)[:M] = locs[valid].to(torch.int32)
+        eng.buffer(depth, "X").view(-1, D)[:M] = data.fts.to(self.device, torch.float32)[valid]
+        if depth > 0:
+            eng.buffer(depth, "ROW_PARENT")[:M] = torch.arange(M, dtype=torch.int32, device=self.device)
+            st = data.ctx_patch.to(self.device, torch.float32)[:, :, -1][valid]
+            eng.buffer(depth - 1, "H").view(-1, D)[:M] = st[:, :D]
+            eng.buffer(depth - 1, "CN").view(-1, Cc)[:M] = st[:, D:]
+            if data.ctx_depth > 0:
+                eng.buffer(depth - 1, "F").view(B, d).copy_(data.ctx_slide.to(self.device, torch.float32)[:, -1])
+            else:
+                eng.buffer(depth - 1, "F").zero_()
+        else:
+            eng.buffer(depth, "ROW_PARENT")[:M] = -1
+        eng.level_forward(depth)
+        out_imp = torch.zeros(B, N, device=self.device)
+        out_imp[valid] = eng.buffer(depth, "ALPHA")[:M]
+        ctx_patch = torch.zeros(B, N, D + Cc, device=self.device)
+        ctx_patch[valid] = torch.cat((eng.buffer(depth, "H").view(-1, D)[:M], eng.buffer(depth, "CN").view(-1, Cc)[:M]), dim=1)
+        return {"logits": eng.buffer(depth, "LOGITS").view(B, dm.nl).clone(),
+                "ctx_slide": eng.buffer(depth, "F").view(B, d).clone(),
+                "ctx_patch": ctx_patch, "importance": out_imp}
+
+
+class _NoCtx:
+    """Stand-in for the autograd ctx when grad is disabled (torch.no_grad inference)."""
+    def save_for_backward(self, *a):
+        pass

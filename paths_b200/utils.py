@@ -1,0 +1,26 @@
+"""Reference-facing entry points of the hot path (reference utils.py): `inference_end2end` and helpers."""
+from typing import Dict, Sequence
+
+import torch
+
+device = torch.device("cuda") if torch.cuda.is_available() else torch.device("cpu")
+
+
+def todevice(x, dev):
+    """utils.py:334-341."""
+    if hasattr(x, "to"):
+        return x.to(dev)
+    if isinstance(x, (list, tuple)):
+        return [todevice(i, dev) for i in x]
+    return x
+
+
+def inference_end2end(num_levels: int, keep_patches: Sequence[int], model, base_power: float, batch: Dict, task: str):
+    """Drop-in for the reference's utils.inference_end2end (utils.py:228-279): runs all `num_levels` magnification levels
+    of the PATHS model on the collated batch -- LSTM step, importance, top-K selection, child expansion, aggregation --
+    and returns (hazards, loss) for task "survival" or (logits, loss) for "subtype_classification".  `loss` carries an
+    autograd node: loss.backward() fills the .grad of the model's parameters.  Nothing is computed on the CPU."""
+    assert num_levels == model.train_config.num_levels, "num_levels must match the model's configuration"
+    assert task == model.train_config.task
+    keep = [keep_patches] * (num_levels - 1) if isinstance(keep_patches, int) else list(keep_patches)
+    return model.runtime().end2end(batch, keep)
