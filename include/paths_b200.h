@@ -105,6 +105,9 @@ void paths_engine_destroy(paths_engine_t* e);
 int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grads, int64_t n_floats, const int64_t* h_offsets,
                              const float* div);
 int paths_engine_bind_store(paths_engine_t* e, const paths_store_t* h_store);
+/* Re-split the bound weights into the bf16 (hi, lo) planes the tcgen05 path reads by TMA.  paths_engine_begin does this
+ * itself; call it before paths_engine_level_forward when levels are driven one by one after a weight update. */
+int paths_engine_refresh_weights(paths_engine_t* e, void* stream);
 
 /* Level-0 row tables for the batch (slide.py:258-271: every cell of grid 0, x-major) and their feature gather.
  * slide_ids[B]: index of each batch slot into the store (device int32). */
@@ -136,6 +139,12 @@ int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, siz
 int paths_engine_set_precision(paths_engine_t* e, int precision);
 /* number of kernel launches issued by this engine since creation (for bench.py's gpu_launches) */
 int64_t paths_engine_launch_count(paths_engine_t* e);
+
+/* Per-kernel device timing for the roofline report: while enabled, the engine brackets the tagged kernels with CUDA events
+ * on the launch stream; profile_read sums (and clears) the elapsed milliseconds and launch count of one tag. */
+enum paths_prof_tag { PATHS_PROF_GATES_FWD = 0, PATHS_PROF_GATES_DW, PATHS_PROF_GATES_DH, PATHS_PROF__COUNT };
+int paths_engine_profile(paths_engine_t* e, int on);
+int paths_engine_profile_read(paths_engine_t* e, int tag, double* total_ms, int64_t* launches);
 
 /* Occupancy bitmap of one [W*H, D] grid: bit c set iff any of the D floats of cell c is non-zero; *count += popcount. */
 int paths_build_occupancy(const float* grid, int cells, int D, uint32_t* bits, int32_t* count, void* stream);

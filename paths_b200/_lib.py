@@ -49,10 +49,10 @@ _lib = None
 
 # every symbol include/paths_b200.h declares (tests check that the library exports all of them)
 SYMBOLS = ["paths_last_error", "paths_abi_version", "paths_engine_workspace_bytes", "paths_engine_create",
-           "paths_engine_destroy", "paths_engine_bind_params", "paths_engine_bind_store", "paths_engine_begin",
+           "paths_engine_destroy", "paths_engine_bind_params", "paths_engine_bind_store", "paths_engine_refresh_weights", "paths_engine_begin",
            "paths_engine_begin_padded", "paths_engine_level_forward", "paths_engine_select", "paths_engine_loss",
            "paths_engine_level_backward", "paths_engine_forward", "paths_engine_backward", "paths_engine_buffer",
-           "paths_engine_set_precision", "paths_engine_launch_count", "paths_build_occupancy", "paths_gemm_nt",
+           "paths_engine_set_precision", "paths_engine_launch_count", "paths_engine_profile", "paths_engine_profile_read", "paths_build_occupancy", "paths_gemm_nt",
            "paths_gemm_tn"]
 
 
@@ -75,6 +75,7 @@ def lib() -> C.CDLL:
     L.paths_engine_destroy.restype = None
     L.paths_engine_bind_params.argtypes = [vp, vp, vp, i64, C.POINTER(C.c_int64), vp]
     L.paths_engine_bind_store.argtypes = [vp, C.POINTER(Store)]
+    L.paths_engine_refresh_weights.argtypes = [vp, vp]
     L.paths_engine_begin.argtypes = [vp, vp, vp]
     L.paths_engine_begin_padded.argtypes = [vp, vp, vp, i32, vp]
     L.paths_engine_level_forward.argtypes = [vp, i32, vp]
@@ -87,6 +88,8 @@ def lib() -> C.CDLL:
     L.paths_engine_set_precision.argtypes = [vp, i32]
     L.paths_engine_launch_count.argtypes = [vp]
     L.paths_engine_launch_count.restype = i64
+    L.paths_engine_profile.argtypes = [vp, i32]
+    L.paths_engine_profile_read.argtypes = [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     L.paths_build_occupancy.argtypes = [vp, i32, i32, vp, vp, vp]
     L.paths_gemm_nt.argtypes = [i32, vp, i32, vp, i32, i32, vp, i32, vp, i32, i32, i32, i32, vp]
     L.paths_gemm_tn.argtypes = [i32, vp, i32, vp, i32, vp, i32, i32, i32, i32, vp]

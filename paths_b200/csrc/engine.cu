@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <new>
+#include <vector>
 
 #include "../../include/paths_b200.h"
 #include "common.cuh"
@@ -29,12 +30,20 @@ int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, f
                const int* M_dev, int N, int K, int flags, cudaStream_t st);
 int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
                cudaStream_t st);
-bool gemm_tc_supported_nt(const RowSrc& A, int ldb, int b_kn, int ldc, int N, int K);
+bool gemm_tc_supported_nt(const RowSrc& A, const float* B, int ldb, int b_kn, int ldc, int N, int K);
 bool gemm_tc_supported_tn(int ldp, const RowSrc& Q, int ldc, int NI, int NJ);
+size_t packed_bytes(int R, int Cc);
+int register_packed(const float* src, int R, int Cc, int ld, void* dst);
+void unregister_packed(const float* src);
+int build_pack_jobs(const float* const* srcs, int n, void* jobs_dev, int* n_jobs, cudaStream_t st);
+int run_pack_jobs(const void* jobs_dev, int n_jobs, cudaStream_t st);
+size_t pack_job_bytes();
+void set_tc_scratch(void* a, size_t a_bytes, void* b, size_t b_bytes);
+size_t tc_scratch_bytes(int rows, int cols);
 
 int gemm_nt(int prec, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
             const int* M_dev, int N, int K, int flags, cudaStream_t st) {
-  if (prec != PREC_FP32_SIMT && gemm_tc_supported_nt(A, ldb, b_kn, ldc, N, K))
+  if (prec != PREC_FP32_SIMT && gemm_tc_supported_nt(A, B, ldb, b_kn, ldc, N, K))
     return gemm_nt_tc(prec == PREC_BF16X3_TC ? 3 : 1, A, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
   return gemm_nt_simt(A, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
 }
@@ -102,6 +111,14 @@ struct paths_engine {
   int64_t launches;
   size_t ws_bytes;
   char* ws_base;
+  // bf16 (hi, lo) planes of every weight matrix the tensor-core path contracts against
+  char* tc_scratch[2]; size_t tc_scratch_each;
+  char* packed_arena; size_t packed_arena_bytes;
+  void* pack_jobs; int n_pack_jobs;
+  std::vector<const float*> packed_srcs;
+  // optional per-kernel timing (CUDA events on the launch stream) for bench.py's roofline line
+  bool prof_on;
+  std::vector<cudaEvent_t> prof_ev[PATHS_PROF__COUNT];     // start/stop pairs
 };
 
 namespace {
@@ -150,6 +167,23 @@ size_t carve(paths_engine* e, char* base) {
   e->dF = b.take<float>((size_t)B * d); e->dz = b.take<float>((size_t)B * d); e->dy3s = b.take<float>((size_t)B * d);
   e->hazards = b.take<float>((size_t)B * dm.nl); e->loss = b.take<float>(1); e->loss_per = b.take<float>(B);
   e->overflow = b.take<int>(2); e->slide_cnt = b.take<int>(B); e->slide_fb = b.take<int>(B);
+  {
+    size_t pb = packed_bytes(3 * C + D, 2 * D) + packed_bytes(D, C);
+    const size_t per_level = packed_bytes(I + d, D) + (size_t)dm.layers * (packed_bytes(3 * d, d) + packed_bytes(d, d) +
+                                                                              packed_bytes(F, d) + packed_bytes(d, F));
+    pb += per_level * dm.L;
+    e->packed_arena_bytes = pb;
+    e->packed_arena = b.take<char>(pb);
+    e->pack_jobs = b.take<char>((size_t)(2 + dm.L * (1 + 4 * dm.layers)) * 64);
+    int cols = 2 * D;
+    if (3 * C + D > cols) cols = 3 * C + D;
+    if (F > cols) cols = F;
+    if (3 * d > cols) cols = 3 * d;
+    if (I + d > cols) cols = I + d;
+    e->tc_scratch_each = tc_scratch_bytes(e->maxtok, cols);
+    e->tc_scratch[0] = b.take<char>(e->tc_scratch_each);
+    e->tc_scratch[1] = b.take<char>(e->tc_scratch_each);
+  }
   return (b.off + 255) & ~size_t(255);
 }
 
@@ -199,6 +233,16 @@ void bind(Params& P, const float* base, const int64_t* off, const paths_dims_t& 
   }
 }
 
+struct ProfScope {
+  paths_engine* e; int tag; cudaStream_t st; bool on;
+  ProfScope(paths_engine* e_, int tag_, cudaStream_t st_) : e(e_), tag(tag_), st(st_), on(e_->prof_on) {
+    if (on) { cudaEvent_t a; cudaEventCreate(&a); cudaEventRecord(a, st); e->prof_ev[tag].push_back(a); }
+  }
+  ~ProfScope() {
+    if (on) { cudaEvent_t b; cudaEventCreate(&b); cudaEventRecord(b, st); e->prof_ev[tag].push_back(b); }
+  }
+};
+
 #define RUN(call)            \
   do {                       \
     int _r = (call);         \
@@ -210,6 +254,7 @@ inline float* W_(const float* p) { return const_cast<float*>(p); }   // gradient
 
 int level_forward(paths_engine* e, int l, cudaStream_t st) {
   const paths_dims_t& dm = e->dm;
+  set_tc_scratch(e->tc_scratch[0], e->tc_scratch_each, e->tc_scratch[1], e->tc_scratch_each);
   const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F, prec = dm.precision;
   Level& v = e->lv[l];
   const LevelP& p = e->P.level[l];
@@ -220,7 +265,10 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
   // ---- LSTM cell step for every patch (interface.py:49-56); [x || h_parent] is gathered inside the GEMM loader
   const bool has_parent = l > 0;
   RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
-  RUN(gemm_nt(prec, Axh, e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, has_parent ? 2 * D : D, 0, st));
+  {
+    ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
+    RUN(gemm_nt(prec, Axh, e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, has_parent ? 2 * D : D, 0, st));
+  }
   RUN(lstm_point1_fwd(v.G, has_parent ? e->lv[l - 1].Cn : nullptr, has_parent ? v.row_parent : nullptr, v.Cn, D, C, M, Md, st));
   RUN(gemm_nt(prec, row_src(v.Cn, C, C), e->P.Wmo, C, 0, v.Pt, D, e->P.bmo, M, Md, D, C, 0, st));
   RUN(lstm_point2_fwd(v.Pt, v.G, v.X, v.H, v.Y, D, C, M, Md, st));
@@ -259,6 +307,7 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
 
 int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   const paths_dims_t& dm = e->dm;
+  set_tc_scratch(e->tc_scratch[0], e->tc_scratch_each, e->tc_scratch[1], e->tc_scratch_each);
   const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F, prec = dm.precision;
   Level& v = e->lv[l];
   const LevelP& p = e->P.level[l];
@@ -336,10 +385,15 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   const bool has_parent = l > 0;
   RUN(lstm_point1_bwd(e->dCn, has_children ? e->dCc : nullptr, v.G, has_parent ? e->lv[l - 1].Cn : nullptr,
                       has_parent ? v.row_parent : nullptr, e->dG, has_parent ? v.dCrow : nullptr, D, C, M, Md, st));
-  if (has_parent)
+  if (has_parent) {
+    ProfScope ps(e, PATHS_PROF_GATES_DH, st);
     RUN(gemm_nt(prec, row_src(e->dG, ldg, ldg), e->P.Wg + D, 2 * D, 1, v.dHrow, D, nullptr, M, Md, D, ldg, 0, st));
+  }
   RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
-  RUN(gemm_tn(prec, e->dG, ldg, Axh, W_(e->Gr.Wg), 2 * D, M, Md, ldg, has_parent ? 2 * D : D, st));
+  {
+    ProfScope ps(e, PATHS_PROF_GATES_DW, st);
+    RUN(gemm_tn(prec, e->dG, ldg, Axh, W_(e->Gr.Wg), 2 * D, M, Md, ldg, has_parent ? 2 * D : D, st));
+  }
   RUN(colsum_accum(e->dG, ldg, W_(e->Gr.bg), M, Md, ldg, st));
   return 0;
 }
@@ -370,6 +424,7 @@ int do_begin(paths_engine* e, const int32_t* slide_ids, const float* fts_padded,
   PATHS_REQUIRE(e->have_store, "begin: no pyramid store bound");
   e->slide_ids = slide_ids;
   Level& v = e->lv[0];
+  if (e->dm.precision != PREC_FP32_SIMT && e->have_params) { RUN(run_pack_jobs(e->pack_jobs, e->n_pack_jobs, st)); }
   PATHS_CK(cudaMemsetAsync(e->overflow, 0, 2 * sizeof(int), st));
   RUN(level0_rows(e->store.gw, e->store.gh, e->dm.L, slide_ids, e->B, v.cap, v.count, v.ntok, v.seg, v.row_slide, v.row_xy,
                   v.row_parent, v.parent_local, e->overflow, st));
@@ -398,8 +453,7 @@ int paths_abi_version(void) { return PATHS_ABI_VERSION; }
 
 size_t paths_engine_workspace_bytes(const paths_dims_t* dims, int B, const int32_t* h_caps, const int32_t* h_maxseg) {
   if (check_dims(dims, B, h_caps, h_maxseg)) return 0;
-  paths_engine tmp;
-  memset(&tmp, 0, sizeof(tmp));
+  paths_engine tmp = paths_engine();
   tmp.dm = *dims; tmp.B = B;
   fill_level_meta(&tmp, h_caps, h_maxseg);
   return carve(&tmp, nullptr);
@@ -414,9 +468,8 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
     set_error("no CUDA device: paths_b200 has no CPU fallback");
     return -3;
   }
-  paths_engine* e = new (std::nothrow) paths_engine;
+  paths_engine* e = new (std::nothrow) paths_engine();
   PATHS_REQUIRE(e, "out of host memory");
-  memset(e, 0, sizeof(*e));
   e->dm = *dims; e->B = B;
   fill_level_meta(e, h_caps, h_maxseg);
   const size_t need = carve(e, nullptr);
@@ -431,7 +484,19 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
   return 0;
 }
 
-void paths_engine_destroy(paths_engine_t* e) { delete e; }
+void paths_engine_destroy(paths_engine_t* e) {
+  if (!e) return;
+  for (const float* src : e->packed_srcs) unregister_packed(src);
+  delete e;
+}
+
+int paths_engine_refresh_weights(paths_engine_t* e, void* stream) {
+  PATHS_REQUIRE(e && e->have_params, "refresh_weights: engine has no parameters bound");
+  if (e->dm.precision == PREC_FP32_SIMT) return 0;
+  if (int r = run_pack_jobs(e->pack_jobs, e->n_pack_jobs, static_cast<cudaStream_t>(stream))) return r;
+  e->launches++;
+  return 0;
+}
 
 int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grads, int64_t n_floats, const int64_t* h_offsets,
                              const float* div) {
@@ -440,6 +505,36 @@ int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grad
   if (grads) bind(e->Gr, grads, h_offsets, e->dm);
   e->grads_base = grads;
   e->grads_floats = (size_t)n_floats;
+  {
+    // (re-)register every contracted weight with the tensor-core path
+    for (const float* src : e->packed_srcs) unregister_packed(src);
+    e->packed_srcs.clear();
+    const paths_dims_t& dm = e->dm;
+    const int D = dm.D, Cm = dm.C, d = dm.d, I = dm.I, F = dm.F;
+    char* cur = e->packed_arena;
+    auto reg = [&](const float* src, int R, int Cc, int ld) -> int {
+      if (int r = register_packed(src, R, Cc, ld, cur)) return r;
+      cur += packed_bytes(R, Cc);
+      e->packed_srcs.push_back(src);
+      return 0;
+    };
+    int rc = 0;
+    rc = rc ? rc : reg(e->P.Wg, 3 * Cm + D, 2 * D, 2 * D);
+    rc = rc ? rc : reg(e->P.Wmo, D, Cm, Cm);
+    for (int l = 0; l < dm.L && !rc; ++l) {
+      rc = rc ? rc : reg(e->P.level[l].Wuv, I + d, D, D);
+      for (int j = 0; j < dm.layers && !rc; ++j) {
+        const LayerP& y = e->P.level[l].layer[j];
+        rc = rc ? rc : reg(y.Wqkv, 3 * d, d, d);
+        rc = rc ? rc : reg(y.Wo, d, d, d);
+        rc = rc ? rc : reg(y.W1, F, d, d);
+        rc = rc ? rc : reg(y.W2, d, F, F);
+      }
+    }
+    if (rc) return rc;
+    PATHS_REQUIRE((size_t)(cur - e->packed_arena) <= e->packed_arena_bytes, "packed-weight arena overrun");
+    if (int r = build_pack_jobs(e->packed_srcs.data(), (int)e->packed_srcs.size(), e->pack_jobs, &e->n_pack_jobs, 0)) return r;
+  }
   e->div = div;
   e->have_params = true;
   return 0;
@@ -560,13 +655,69 @@ int paths_engine_set_precision(paths_engine_t* e, int precision) {
 
 int64_t paths_engine_launch_count(paths_engine_t* e) { return e ? e->launches : 0; }
 
+int paths_engine_profile(paths_engine_t* e, int on) {
+  PATHS_REQUIRE(e, "null engine");
+  e->prof_on = on != 0;
+  return 0;
+}
+
+int paths_engine_profile_read(paths_engine_t* e, int tag, double* total_ms, int64_t* launches) {
+  PATHS_REQUIRE(e && total_ms && launches && tag >= 0 && tag < PATHS_PROF__COUNT, "bad argument");
+  std::vector<cudaEvent_t>& v = e->prof_ev[tag];
+  double tot = 0.0;
+  for (size_t i = 0; i + 1 < v.size(); i += 2) {
+    float ms = 0.f;
+    PATHS_CK(cudaEventSynchronize(v[i + 1]));
+    PATHS_CK(cudaEventElapsedTime(&ms, v[i], v[i + 1]));
+    tot += ms;
+  }
+  *total_ms = tot;
+  *launches = (int64_t)(v.size() / 2);
+  for (cudaEvent_t ev : v) cudaEventDestroy(ev);
+  v.clear();
+  return 0;
+}
+
 int paths_gemm_nt(int precision, const float* A, int lda, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias,
                   int M, int N, int K, int flags, void* stream) {
-  return gemm_nt(precision, row_src(A, lda, K), B, ldb, b_kn, C, ldc, bias, M, nullptr, N, K, flags, static_cast<cudaStream_t>(stream));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *tmp = nullptr, *jobs = nullptr, *scr = nullptr;
+  if (precision != PREC_FP32_SIMT) {          // stand-alone use: temporary packed weight + activation scratch
+    const int R = b_kn ? K : N, Cc = b_kn ? N : K;
+    PATHS_CK(cudaMalloc(&tmp, packed_bytes(R, Cc)));
+    PATHS_CK(cudaMalloc(&jobs, 64));
+    PATHS_CK(cudaMalloc(&scr, tc_scratch_bytes(M, K)));
+    set_tc_scratch(scr, tc_scratch_bytes(M, K), nullptr, 0);
+    if (int r = register_packed(B, R, Cc, ldb, tmp)) return r;
+    int nj = 0;
+    if (int r = build_pack_jobs(&B, 1, jobs, &nj, st)) return r;
+    if (int r = run_pack_jobs(jobs, nj, st)) return r;
+  }
+  int rc = gemm_nt(precision, row_src(A, lda, K), B, ldb, b_kn, C, ldc, bias, M, nullptr, N, K, flags, st);
+  if (tmp) {
+    cudaStreamSynchronize(st);
+    unregister_packed(B);
+    cudaFree(tmp); cudaFree(jobs); cudaFree(scr);
+    set_tc_scratch(nullptr, 0, nullptr, 0);
+  }
+  return rc;
 }
 
 int paths_gemm_tn(int precision, const float* P, int ldp, const float* Q, int ldq, float* C, int ldc, int M, int NI, int NJ, void* stream) {
-  return gemm_tn(precision, P, ldp, row_src(Q, ldq, NJ), C, ldc, M, nullptr, NI, NJ, static_cast<cudaStream_t>(stream));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *sa = nullptr, *sb = nullptr;
+  if (precision != PREC_FP32_SIMT) {
+    PATHS_CK(cudaMalloc(&sa, tc_scratch_bytes(M, NI)));
+    PATHS_CK(cudaMalloc(&sb, tc_scratch_bytes(M, NJ)));
+    set_tc_scratch(sa, tc_scratch_bytes(M, NI), sb, tc_scratch_bytes(M, NJ));
+  }
+  int rc = gemm_tn(precision, P, ldp, row_src(Q, ldq, NJ), C, ldc, M, nullptr, NI, NJ, st);
+  if (sa) {
+    cudaStreamSynchronize(st);
+    cudaFree(sa); cudaFree(sb);
+    set_tc_scratch(nullptr, 0, nullptr, 0);
+  }
+  return rc;
 }
 
 }  // extern "C"

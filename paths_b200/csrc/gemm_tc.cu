@@ -1,12 +1,580 @@
-// placeholder until the tcgen05 engine lands: reports "unsupported" so every contraction takes the fp32 SIMT path
+// tcgen05 / TMEM / TMA contractions for sm_100a.
+//
+//   gemm_nt_tc : C[M,N] (+)= act(A . B^T + bias)     A = fp32 activations (RowSrc: gathered / concatenated rows),
+//                                                     B = weights, pre-split into bf16 (hi, lo) planes and fed by TMA
+//   gemm_tn_tc : C[NI,NJ] += P^T . Q                  both operands fp32 activations (weight gradients)
+//
+// Precision: operands are split as x = hi + lo with hi = bf16(x), lo = bf16(x - hi).  `passes == 3` issues
+// hi*hi + hi*lo + lo*hi into the same fp32 TMEM accumulator (error ~2^-17 per product: the fp32-parity mode);
+// `passes == 1` issues hi*hi only (plain bf16: the fast mode).  Activations stay fp32 in HBM (the canonical storage
+// the parity oracle is compared against); a coalesced split kernel turns the rows a contraction needs -- gathered and
+// concatenated through RowSrc ([x || h_parent], token gathers) -- into (hi, lo) planes right before the contraction.
+//
+// A coalesced split kernel writes the planes (performing the gather / concat); the contraction kernel is then a pure
+// TMA -> tcgen05 pipeline: CTA = 10 warps: 1 TMA warp, 1 MMA warp (one elected thread issues tcgen05.mma), 8 epilogue warps.
+// One 128 x BN fp32 accumulator tile in TMEM per CTA; smem ring of `NS` stages, 64-deep (128-byte, SWIZZLE_128B) K-blocks.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
+
 namespace paths {
-bool gemm_tc_supported_nt(const RowSrc&, int, int, int, int, int) { return false; }
-bool gemm_tc_supported_tn(int, const RowSrc&, int, int, int) { return false; }
-int gemm_nt_tc(int, const RowSrc&, const float*, int, int, float*, int, const float*, int, const int*, int, int, int, cudaStream_t) {
-  set_error("tcgen05 path not built"); return -1;
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;                    // bf16 elements per k-block = one 128-byte swizzle row
+constexpr int TMA_WARP = 8, MMA_WARP = 9;
+constexpr int NTHREADS = 10 * 32;
+
+// ---------------------------------------------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
-int gemm_tn_tc(int, const float*, int, const RowSrc&, float*, int, int, const int*, int, int, cudaStream_t) {
-  set_error("tcgen05 path not built"); return -1;
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+// Bounded spin: a protocol bug traps (launch failure) instead of hanging the device.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 26)) __trap();
+  }
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem] (+)= A[smem] . B[smem]   (kind::f16 covers bf16 inputs with fp32 accumulation)
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------- descriptors
+// Shared-memory matrix descriptor (sm_100 UMMA): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) | version=1 [46,48) |
+// layout type [61,64) with SWIZZLE_128B = 2.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// Instruction descriptor: D=f32 [4,6)=1, A=bf16 [7,10)=1, B=bf16 [10,13)=1, a_major [15], b_major [16] (1 = MN-major),
+// N>>3 [17,23), M>>4 [24,29).
+__host__ __device__ constexpr uint32_t umma_idesc(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
+}
+
+// Tile layouts in shared memory (bf16, 128-byte rows, 8-row / 1024-byte swizzle atoms):
+//  K-major  tile [R rows x 64 k]   : byte(r, k)  = (r/8)*1024 + (r%8)*128 + (((k/8) ^ (r%8)) * 16) + (k%8)*2
+//  MN-major tile [64 k x R cols]   : byte(k, mn) = (mn/64)*8192 + (k/8)*1024 + (k%8)*128 + ((((mn%64)/8) ^ (k%8)) * 16) + (mn%8)*2
+// Both are what a SWIZZLE_128B TMA box {64 elements, rows} produces, so TMA-written and producer-written tiles agree.
+__device__ __forceinline__ uint32_t sw128_off(int row, int elem /* 0..63 */) {
+  return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((elem >> 3) ^ (row & 7))) << 4) + (elem & 7) * 2);
+}
+
+__device__ __forceinline__ void split_store(uint8_t* hi_plane, uint8_t* lo_plane, uint32_t off, float4 v, bool want_lo) {
+  __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+  uint2 hv;
+  hv.x = *reinterpret_cast<uint32_t*>(&h0); hv.y = *reinterpret_cast<uint32_t*>(&h1);
+  *reinterpret_cast<uint2*>(hi_plane + off) = hv;
+  if (want_lo) {
+    const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+    __nv_bfloat162 l0 = __floats2bfloat162_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2bfloat162_rn(v.z - f1.x, v.w - f1.y);
+    uint2 lv;
+    lv.x = *reinterpret_cast<uint32_t*>(&l0); lv.y = *reinterpret_cast<uint32_t*>(&l1);
+    *reinterpret_cast<uint2*>(lo_plane + off) = lv;
+  }
+}
+
+template <int BN, int NP>
+struct Cfg {
+  static constexpr int A_PLANE = BM * BK * 2;
+  static constexpr int B_PLANE = BN * BK * 2;
+  static constexpr int STAGE = NP * (A_PLANE + B_PLANE);
+  static constexpr int NS = (200 * 1024) / STAGE >= 4 ? 4 : (200 * 1024) / STAGE;
+  static constexpr int SMEM = NS * STAGE + 1024;
+  static_assert(NS >= 2, "need at least two stages");
+};
+
+// Epilogue shared by both kernels: thread (warp w, lane) owns accumulator row (w%4)*32+lane and the column half w/4.
+template <int BN, typename F>
+__device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int warp, int lane, F&& emit) {
+  const int q = warp & 3, half = warp >> 2;
+  constexpr int COLS = BN / 2;
+#pragma unroll 1
+  for (int c0 = 0; c0 < COLS; c0 += 32) {
+    uint32_t r[32];
+    const int col = half * COLS + c0;
+    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)col, r);
+    emit(q * 32 + lane, col, r);
+  }
+}
+
+// =================================================================================================== split kernel
+// fp32 rows (gathered / concatenated through RowSrc) -> bf16 planes stacked as [2 * plane_rows, ldp] (hi rows first).
+// Rows [M, round_up(M, 64)) are zero-filled so a reduction over rows (TN) may run whole 64-row blocks.
+__global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host, const int* __restrict__ M_dev, int K,
+                                                           __nv_bfloat16* __restrict__ planes, int plane_rows, int ldp, int want_lo) {
+  const int M = M_dev ? *M_dev : M_host;
+  int Mpad = (M + 63) & ~63;
+  if (Mpad > plane_rows) Mpad = plane_rows;
+  const int lane = threadIdx.x & 31;
+  for (int m = blockIdx.x * 8 + (threadIdx.x >> 5); m < Mpad; m += gridDim.x * 8) {
+    uint8_t* hi = reinterpret_cast<uint8_t*>(planes + (size_t)m * ldp);
+    uint8_t* lo = reinterpret_cast<uint8_t*>(planes + ((size_t)plane_rows + m) * ldp);
+    for (int k = lane * 4; k < K; k += 128) {
+      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (m < M) {
+        const float* p = rowsrc_ptr(A, m, k);
+        if (p) x = __ldg(reinterpret_cast<const float4*>(p));
+      }
+      split_store(hi, lo, (uint32_t)k * 2, x, want_lo != 0);
+    }
+  }
+}
+
+// =================================================================================================== TMA-fed UMMA kernel
+// D[128 x BN] (+)= sum over reduction blocks of A_tile . B_tile^T, both operands arriving by TMA as 64x64 bf16 boxes of
+// (hi, lo) planes.  Operand orientation:
+//   X_MN == false (K-major):  plane is [rows = output index, cols = reduction index]   (activations in NT, weights [N,K])
+//   X_MN == true  (MN-major): plane is [rows = reduction index, cols = output index]   (weights [K,N] in dX, both in TN)
+// The reduction length may live on the device (TN: number of packed rows); so may the output row count (NT).
+struct Operand { int row0, col0, plane_rows; };
+
+template <int BN, int NP, bool A_MN, bool B_MN, bool ATOMIC>
+__global__ void __launch_bounds__(NTHREADS, 1)
+gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Operand oa, Operand ob,
+                float* __restrict__ C, int ldc, const float* __restrict__ bias, int OI_host, const int* __restrict__ OI_dev, int OJ,
+                int R_host, const int* __restrict__ R_dev, int flags) {
+  using cfg = Cfg<BN, NP>;
+  constexpr int NS = cfg::NS;
+  const int OI = OI_dev ? *OI_dev : OI_host;
+  const int R = R_dev ? *R_dev : R_host;
+  const int i0 = blockIdx.y * BM, j0 = blockIdx.x * BN;
+  if (i0 >= OI) return;
+  const int nkb_total = (R + BK - 1) / BK;
+  const int per = (nkb_total + gridDim.z - 1) / gridDim.z;
+  const int kb_begin = blockIdx.z * per, kb_end = min(nkb_total, kb_begin + per);
+  if (kb_begin >= kb_end) return;
+  const int nkb = kb_end - kb_begin;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t full_bar[NS], empty_bar[NS], acc_bar;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NS; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&acc_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == MMA_WARP) tmem_alloc(&tmem_slot, BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == TMA_WARP) {
+    if (lane == 0) {
+      for (int it = 0; it < nkb; ++it) {
+        const int kb = kb_begin + it;
+        const int s = it % NS;
+        const uint32_t ph = (it / NS) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        mbar_arrive_expect_tx(&full_bar[s], NP * (cfg::A_PLANE + cfg::B_PLANE));
+        uint8_t* a_base = smem + (size_t)s * cfg::STAGE;
+        uint8_t* b_base = a_base + NP * cfg::A_PLANE;
+#pragma unroll
+        for (int pl = 0; pl < NP; ++pl) {
+#pragma unroll
+          for (int bx = 0; bx < BM / 64; ++bx) {
+            uint8_t* dst = a_base + pl * cfg::A_PLANE + bx * 8192;
+            if (!A_MN) tma_load_2d(dst, &tmA, oa.col0 + kb * BK, pl * oa.plane_rows + oa.row0 + i0 + bx * 64, &full_bar[s]);
+            else       tma_load_2d(dst, &tmA, oa.col0 + i0 + bx * 64, pl * oa.plane_rows + oa.row0 + kb * BK, &full_bar[s]);
+          }
+#pragma unroll
+          for (int bx = 0; bx < BN / 64; ++bx) {
+            uint8_t* dst = b_base + pl * cfg::B_PLANE + bx * 8192;
+            if (!B_MN) tma_load_2d(dst, &tmB, ob.col0 + kb * BK, pl * ob.plane_rows + ob.row0 + j0 + bx * 64, &full_bar[s]);
+            else       tma_load_2d(dst, &tmB, ob.col0 + j0 + bx * 64, pl * ob.plane_rows + ob.row0 + kb * BK, &full_bar[s]);
+          }
+        }
+      }
+    }
+  } else if (warp == MMA_WARP) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      for (int it = 0; it < nkb; ++it) {
+        const int s = it % NS;
+        const uint32_t ph = (it / NS) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * cfg::STAGE);
+        const uint32_t b_addr = a_addr + NP * cfg::A_PLANE;
+#pragma unroll
+        for (int ks = 0; ks < BK / 16; ++ks) {
+          const uint64_t a_hi = A_MN ? umma_desc(a_addr + ks * 2048, 8192, 1024) : umma_desc(a_addr + ks * 32, 16, 1024);
+          const uint64_t b_hi = B_MN ? umma_desc(b_addr + ks * 2048, 8192, 1024) : umma_desc(b_addr + ks * 32, 16, 1024);
+          const uint32_t acc0 = (it | ks) ? 1u : 0u;
+          if (NP == 2) {
+            const uint64_t a_lo = A_MN ? umma_desc(a_addr + cfg::A_PLANE + ks * 2048, 8192, 1024)
+                                       : umma_desc(a_addr + cfg::A_PLANE + ks * 32, 16, 1024);
+            const uint64_t b_lo = B_MN ? umma_desc(b_addr + cfg::B_PLANE + ks * 2048, 8192, 1024)
+                                       : umma_desc(b_addr + cfg::B_PLANE + ks * 32, 16, 1024);
+            umma_bf16(tmem_base, a_lo, b_hi, idesc, acc0);
+            umma_bf16(tmem_base, a_hi, b_lo, idesc, 1u);
+            umma_bf16(tmem_base, a_hi, b_hi, idesc, 1u);
+          } else {
+            umma_bf16(tmem_base, a_hi, b_hi, idesc, acc0);
+          }
+        }
+        umma_commit(&empty_bar[s]);
+      }
+      umma_commit(&acc_bar);
+    }
+  } else {
+    // ------------------------------------------------ epilogue warps: TMEM -> registers -> global
+    mbar_wait(&acc_bar, 0);
+    tc_fence_after();
+    const bool vec = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+    epilogue_rows<BN>(tmem_base, warp, lane, [&](int row, int col, uint32_t (&r)[32]) {
+      const int i = i0 + row;
+      if (i >= OI) return;
+      float* cp = C + (size_t)i * ldc + j0 + col;
+      if (ATOMIC) {
+#pragma unroll
+        for (int e = 0; e < 32; ++e)
+          if (j0 + col + e < OJ) atomicAdd(cp + e, __uint_as_float(r[e]));
+        return;
+      }
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const int n = j0 + col + j;
+        if (n >= OJ) break;
+        float o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float x = __uint_as_float(r[j + e]);
+          if (bias && n + e < OJ) x += bias[n + e];
+          if (flags & GEMM_RELU) x = fmaxf(x, 0.f);
+          o[e] = x;
+        }
+        if (vec && n + 3 < OJ) {
+          float4 w = make_float4(o[0], o[1], o[2], o[3]);
+          if (flags & GEMM_ACCUM) { const float4 c = *reinterpret_cast<const float4*>(cp + j); w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w; }
+          *reinterpret_cast<float4*>(cp + j) = w;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (n + e < OJ) cp[j + e] = (flags & GEMM_ACCUM) ? cp[j + e] + o[e] : o[e];
+        }
+      }
+    });
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == MMA_WARP) tmem_dealloc(tmem_base, BN);
+}
+
+// ---------------------------------------------------------------------------------------------- packed weights
+// fp32 [R, Cc] (leading dim ld) -> bf16 planes stacked as [2R, ldp]: rows [0,R) = hi, [R,2R) = lo.
+struct PackJob { const float* src; __nv_bfloat16* dst; int R, Cc, ld, ldp; };
+
+__global__ void __launch_bounds__(256) pack_weights_kernel(const PackJob* __restrict__ jobs) {
+  const PackJob jb = jobs[blockIdx.y];
+  const size_t total = (size_t)jb.R * jb.ldp;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(e / jb.ldp), c = (int)(e % jb.ldp);
+    const float x = c < jb.Cc ? jb.src[(size_t)r * jb.ld + c] : 0.f;
+    const __nv_bfloat16 h = __float2bfloat16_rn(x);
+    jb.dst[e] = h;
+    jb.dst[total + e] = __float2bfloat16_rn(x - __bfloat162float(h));
+  }
+}
+
+struct Packed {
+  const float* src; int R, Cc, ld, ldp;
+  __nv_bfloat16* dst;
+  CUtensorMap map;
+};
+
+std::mutex g_mu;
+std::vector<Packed> g_packed;
+
+typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                             const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                             CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeFn g_encode = nullptr;
+
+int get_encode() {
+  if (g_encode) return 0;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  PATHS_CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  PATHS_REQUIRE(fn != nullptr && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available from this driver");
+  g_encode = reinterpret_cast<EncodeFn>(fn);
+  return 0;
+}
+
+int make_map(Packed& p) {
+  if (int r = get_encode()) return r;
+  cuuint64_t gdim[2] = {(cuuint64_t)p.ldp, (cuuint64_t)(2 * p.R)};
+  cuuint64_t gstr[1] = {(cuuint64_t)p.ldp * 2};
+  cuuint32_t box[2] = {64, 64};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult rc = g_encode(&p.map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p.dst, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PATHS_REQUIRE(rc == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) for a [%d x %d] weight", (int)rc, 2 * p.R, p.ldp);
+  return 0;
+}
+
+const Packed* find_packed(const float* B, int ldb, int* row0, int* col0) {
+  for (const Packed& p : g_packed) {
+    if (p.ld != ldb) continue;
+    const ptrdiff_t off = B - p.src;
+    if (off < 0 || off >= (ptrdiff_t)p.R * p.ld) continue;
+    *row0 = (int)(off / p.ld); *col0 = (int)(off % p.ld);
+    return &p;
+  }
+  return nullptr;
+}
+
+template <typename Kern>
+int set_smem(Kern kern, int bytes) {
+  PATHS_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  return 0;
+}
+
+// activation planes: scratch provided by the engine (or by the stand-alone entry points)
+struct Scratch { void* p[2]; size_t bytes[2]; } g_scratch = {{nullptr, nullptr}, {0, 0}};
+
+struct MapKey { const void* ptr; int rows, cols, ldp; };
+struct MapEnt { MapKey k; CUtensorMap map; };
+std::vector<MapEnt> g_maps;          // tiny cache: scratch pointers and shapes repeat every step
+
+int encode_map(CUtensorMap* out, const void* ptr, int rows, int cols, int ldp) {
+  if (int r = get_encode()) return r;
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)ldp * 2};
+  cuuint32_t box[2] = {64, 64};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult rc = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PATHS_REQUIRE(rc == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) for a [%d x %d] plane (ld %d)", (int)rc, rows, cols, ldp);
+  return 0;
+}
+
+int cached_map(const CUtensorMap** out, const void* ptr, int rows, int cols, int ldp) {
+  for (MapEnt& e : g_maps)
+    if (e.k.ptr == ptr && e.k.rows == rows && e.k.cols == cols && e.k.ldp == ldp) { *out = &e.map; return 0; }
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps.reserve(4200);
+  MapEnt e;
+  e.k = MapKey{ptr, rows, cols, ldp};
+  if (int r = encode_map(&e.map, ptr, rows, cols, ldp)) return r;
+  g_maps.push_back(e);
+  *out = &g_maps.back().map;
+  return 0;
+}
+
+inline int pad_rows(int M) { return ((M + 63) / 64) * 64 + 64; }
+
+// splits A (fp32, RowSrc) into scratch `which`; returns the tensor map and operand record
+int split_to_scratch(int which, const RowSrc& A, int M_host, const int* M_dev, int K, bool want_lo, const CUtensorMap** map, Operand* op,
+                     cudaStream_t st) {
+  const int rows = pad_rows(M_host), ldp = (K + 7) / 8 * 8;
+  const size_t need = (size_t)2 * rows * ldp * sizeof(__nv_bfloat16);
+  PATHS_REQUIRE(g_scratch.p[which] && need <= g_scratch.bytes[which], "tensor-core scratch %d too small: need %zu bytes, have %zu", which,
+                need, g_scratch.bytes[which]);
+  __nv_bfloat16* planes = reinterpret_cast<__nv_bfloat16*>(g_scratch.p[which]);
+  int g = (rows + 7) / 8; if (g > 16 * kNumSMs) g = 16 * kNumSMs;
+  split_planes_kernel<<<g, 256, 0, st>>>(A, M_host, M_dev, K, planes, rows, ldp, want_lo ? 1 : 0);
+  PATHS_LAUNCH_CK();
+  if (int r = cached_map(map, planes, 2 * rows, K, ldp)) return r;
+  op->row0 = 0; op->col0 = 0; op->plane_rows = rows;
+  return 0;
+}
+
+template <int BN, int NP, bool A_MN, bool B_MN, bool ATOMIC>
+int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand ob, float* C, int ldc, const float* bias, int OI_host,
+               const int* OI_dev, int OJ, int R_host, const int* R_dev, int flags, int splits, cudaStream_t st) {
+  auto kern = gemm_tma_kernel<BN, NP, A_MN, B_MN, ATOMIC>;
+  static bool configured = false;
+  if (!configured) { if (int r = set_smem(kern, Cfg<BN, NP>::SMEM)) return r; configured = true; }
+  dim3 grid((OJ + BN - 1) / BN, (OI_host + BM - 1) / BM, splits);
+  kern<<<grid, NTHREADS, Cfg<BN, NP>::SMEM, st>>>(*ma, *mb, oa, ob, C, ldc, bias, OI_host, OI_dev, OJ, R_host, R_dev, flags);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+
+}  // namespace
+
+// ---- registry API (engine.cu registers every weight matrix it contracts against) -----------------------------------
+size_t packed_bytes(int R, int Cc) { return (size_t)2 * R * ((Cc + 7) / 8 * 8) * sizeof(__nv_bfloat16) + 256; }
+
+int register_packed(const float* src, int R, int Cc, int ld, void* dst) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (auto it = g_packed.begin(); it != g_packed.end();)
+    it = (it->src == src) ? g_packed.erase(it) : it + 1;
+  Packed p;
+  p.src = src; p.R = R; p.Cc = Cc; p.ld = ld; p.ldp = (Cc + 7) / 8 * 8;
+  p.dst = reinterpret_cast<__nv_bfloat16*>((reinterpret_cast<uintptr_t>(dst) + 255) & ~uintptr_t(255));
+  if (int r = make_map(p)) return r;
+  g_packed.push_back(p);
+  return 0;
+}
+
+void unregister_packed(const float* src) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (auto it = g_packed.begin(); it != g_packed.end();)
+    it = (it->src == src) ? g_packed.erase(it) : it + 1;
+}
+
+// Builds the device job table for the given registered weights (once, at bind time) ...
+int build_pack_jobs(const float* const* srcs, int n, void* jobs_dev, int* n_jobs, cudaStream_t st) {
+  std::vector<PackJob> jobs;
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int i = 0; i < n; ++i)
+      for (const Packed& p : g_packed)
+        if (p.src == srcs[i]) { jobs.push_back(PackJob{p.src, p.dst, p.R, p.Cc, p.ld, p.ldp}); break; }
+  }
+  *n_jobs = (int)jobs.size();
+  if (jobs.empty()) return 0;
+  PATHS_CK(cudaMemcpyAsync(jobs_dev, jobs.data(), jobs.size() * sizeof(PackJob), cudaMemcpyHostToDevice, st));
+  PATHS_CK(cudaStreamSynchronize(st));
+  return 0;
+}
+// ... and re-splits them into bf16 (hi, lo) planes: one launch per step (the weights change with every optimizer step).
+int run_pack_jobs(const void* jobs_dev, int n_jobs, cudaStream_t st) {
+  if (n_jobs <= 0) return 0;
+  pack_weights_kernel<<<dim3(32, (unsigned)n_jobs), 256, 0, st>>>(reinterpret_cast<const PackJob*>(jobs_dev));
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+size_t pack_job_bytes() { return sizeof(PackJob); }
+
+bool gemm_tc_supported_nt(const RowSrc& A, const float* B, int ldb, int b_kn, int ldc, int N, int K) {
+  if (K % 8 != 0 || A.k0 % 4 != 0 || A.ld0 % 4 != 0 || (A.p1 && A.ld1 % 4 != 0)) return false;
+  if ((reinterpret_cast<uintptr_t>(A.p0) & 15) || (A.p1 && (reinterpret_cast<uintptr_t>(A.p1) & 15))) return false;
+  std::lock_guard<std::mutex> lk(g_mu);
+  int r0, c0;
+  return find_packed(B, ldb, &r0, &c0) != nullptr;
+}
+bool gemm_tc_supported_tn(int ldp, const RowSrc& Q, int ldc, int NI, int NJ) {
+  if (ldp % 4 != 0 || NI % 8 != 0 || NJ % 8 != 0) return false;
+  if (Q.k0 % 4 != 0 || Q.ld0 % 4 != 0 || (Q.p1 && Q.ld1 % 4 != 0)) return false;
+  if ((reinterpret_cast<uintptr_t>(Q.p0) & 15) || (Q.p1 && (reinterpret_cast<uintptr_t>(Q.p1) & 15))) return false;
+  return NI >= 8 && NJ >= 8;
+}
+
+void set_tc_scratch(void* a, size_t a_bytes, void* b, size_t b_bytes) {
+  g_scratch.p[0] = a; g_scratch.bytes[0] = a_bytes; g_scratch.p[1] = b; g_scratch.bytes[1] = b_bytes;
+}
+size_t tc_scratch_bytes(int rows, int cols) { return (size_t)2 * pad_rows(rows) * ((cols + 7) / 8 * 8) * sizeof(__nv_bfloat16) + 256; }
+
+int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
+               const int* M_dev, int N, int K, int flags, cudaStream_t st) {
+  if (M_host <= 0 || N <= 0) return 0;
+  const Packed* pk; int r0, c0;
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    pk = find_packed(B, ldb, &r0, &c0);
+  }
+  PATHS_REQUIRE(pk, "gemm_nt_tc: weight matrix was not registered for the tensor-core path");
+  const CUtensorMap* ma; Operand oa;
+  if (int r = split_to_scratch(0, A, M_host, M_dev, K, passes == 3, &ma, &oa, st)) return r;
+  Operand ob; ob.row0 = r0; ob.col0 = c0; ob.plane_rows = pk->R;
+  const bool big = N > 128;
+#define NT_CASE(BN_, NP_, MN_) \
+  return launch_tma<BN_, NP_, false, MN_, false>(ma, &pk->map, oa, ob, C, ldc, bias, M_host, M_dev, N, K, nullptr, flags, 1, st)
+  if (passes == 3) {
+    if (big) { if (b_kn) NT_CASE(256, 2, true); else NT_CASE(256, 2, false); }
+    else     { if (b_kn) NT_CASE(128, 2, true); else NT_CASE(128, 2, false); }
+  } else {
+    if (big) { if (b_kn) NT_CASE(256, 1, true); else NT_CASE(256, 1, false); }
+    else     { if (b_kn) NT_CASE(128, 1, true); else NT_CASE(128, 1, false); }
+  }
+#undef NT_CASE
+  return 0;
+}
+
+int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
+               cudaStream_t st) {
+  if (M_host <= 0 || NI <= 0 || NJ <= 0) return 0;
+  const CUtensorMap *ma, *mb; Operand oa, ob;
+  if (int r = split_to_scratch(0, row_src(P, ldp, NI), M_host, M_dev, NI, passes == 3, &ma, &oa, st)) return r;
+  if (int r = split_to_scratch(1, Q, M_host, M_dev, NJ, passes == 3, &mb, &ob, st)) return r;
+  const bool big = NJ > 128;
+  const int BN = big ? 256 : 128;
+  const int tiles = ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
+  int splits = (2 * kNumSMs + tiles - 1) / tiles;
+  const int max_splits = (M_host + 4 * BK - 1) / (4 * BK);
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+#define TN_CASE(BN_, NP_) \
+  return launch_tma<BN_, NP_, true, true, true>(ma, mb, oa, ob, C, ldc, nullptr, NI, nullptr, NJ, M_host, M_dev, 0, splits, st)
+  if (passes == 3) { if (big) TN_CASE(256, 2); else TN_CASE(128, 2); }
+  else             { if (big) TN_CASE(256, 1); else TN_CASE(128, 1); }
+#undef TN_CASE
+  return 0;
+}
+
 }  // namespace paths

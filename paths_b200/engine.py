@@ -282,6 +282,9 @@ class Engine:
             L.check(self.lib.paths_engine_begin_padded(self.handle, slide_ids.data_ptr(), fts_padded.data_ptr(),
                                                        int(fts_padded.shape[1]), _stream()), "engine_begin_padded")
 
+    def refresh_weights(self) -> None:
+        L.check(self.lib.paths_engine_refresh_weights(self.handle, _stream()), "refresh_weights")
+
     def level_forward(self, level: int) -> None:
         L.check(self.lib.paths_engine_level_forward(self.handle, level, _stream()), "level_forward")
 
@@ -307,6 +310,14 @@ class Engine:
     def set_precision(self, precision: int) -> None:
         L.check(self.lib.paths_engine_set_precision(self.handle, precision), "set_precision")
         self.dims.precision = precision
+
+    def profile(self, on: bool) -> None:
+        L.check(self.lib.paths_engine_profile(self.handle, int(on)), "profile")
+
+    def profile_read(self, tag: int):
+        ms, n = C.c_double(), C.c_int64()
+        L.check(self.lib.paths_engine_profile_read(self.handle, tag, C.byref(ms), C.byref(n)), "profile_read")
+        return ms.value, n.value
 
     def launch_count(self) -> int:
         return int(self.lib.paths_engine_launch_count(self.handle))

@@ -202,6 +202,7 @@ class ModelRuntime:
                 eng.buffer(depth - 1, "F").zero_()
         else:
             eng.buffer(depth, "ROW_PARENT")[:M] = -1
+        eng.refresh_weights()
         eng.level_forward(depth)
         out_imp = torch.zeros(B, N, device=self.device)
         out_imp[valid] = eng.buffer(depth, "ALPHA")[:M]
