@@ -219,12 +219,17 @@ def main():
         if profile:
             eng.profile(True)
         l0 = eng.launch_count()
+        cuprof = profile and os.environ.get("PATHS_BENCH_CUPROF") == "1"    # ncu --profile-from-start off
+        if cuprof:
+            torch.cuda.cudart().cudaProfilerStart()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for _ in range(steps):
             fn()
         b.record()
         torch.cuda.synchronize()
+        if cuprof:
+            torch.cuda.cudart().cudaProfilerStop()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()

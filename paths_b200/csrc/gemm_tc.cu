@@ -200,59 +200,69 @@ template <int BN, int NP, bool A_MN, bool B_MN, bool ATOMIC>
 __global__ void __launch_bounds__(NTHREADS, 1)
 gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Operand oa, Operand ob,
                 float* __restrict__ C, int ldc, const float* __restrict__ bias, int OI_host, const int* __restrict__ OI_dev, int OJ,
-                int R_host, const int* __restrict__ R_dev, int flags) {
+                int R_host, const int* __restrict__ R_dev, int flags, int splits) {
+  // Persistent: one CTA per SM walks work units u = blockIdx.x, += gridDim.x; unit = (row tile, column tile, reduction split)
+  // with column tiles fastest so CTAs that run together share A rows in L2.  Two TMEM accumulators: the epilogue of unit n
+  // drains one while the MMA warp fills the other.
   using cfg = Cfg<BN, NP>;
   constexpr int NS = cfg::NS;
   const int OI = OI_dev ? *OI_dev : OI_host;
   const int R = R_dev ? *R_dev : R_host;
-  const int i0 = blockIdx.y * BM, j0 = blockIdx.x * BN;
-  if (i0 >= OI) return;
+  const int tiles_i = (OI + BM - 1) / BM, tiles_j = (OJ + BN - 1) / BN;
   const int nkb_total = (R + BK - 1) / BK;
-  const int per = (nkb_total + gridDim.z - 1) / gridDim.z;
-  const int kb_begin = blockIdx.z * per, kb_end = min(nkb_total, kb_begin + per);
-  if (kb_begin >= kb_end) return;
-  const int nkb = kb_end - kb_begin;
+  const int per = (nkb_total + splits - 1) / splits;
+  const int units = tiles_i * tiles_j * splits;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  __shared__ uint64_t full_bar[NS], empty_bar[NS], acc_bar;
+  __shared__ uint64_t full_bar[NS], empty_bar[NS], acc_full[2], acc_empty[2];
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    mbar_init(&acc_bar, 1);
+    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], NTHREADS / 32 - 2); }
     fence_barrier_init();
   }
-  if (warp == MMA_WARP) tmem_alloc(&tmem_slot, BN);
+  if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 2 * BN);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
+  auto unit_range = [&](int u, int& i0, int& j0, int& kb_begin, int& kb_end) {
+    const int z = u % splits, t = u / splits;
+    j0 = (t % tiles_j) * BN; i0 = (t / tiles_j) * BM;
+    kb_begin = z * per; kb_end = min(nkb_total, kb_begin + per);
+  };
+
   if (warp == TMA_WARP) {
     if (lane == 0) {
-      for (int it = 0; it < nkb; ++it) {
-        const int kb = kb_begin + it;
-        const int s = it % NS;
-        const uint32_t ph = (it / NS) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1);
-        mbar_arrive_expect_tx(&full_bar[s], NP * (cfg::A_PLANE + cfg::B_PLANE));
-        uint8_t* a_base = smem + (size_t)s * cfg::STAGE;
-        uint8_t* b_base = a_base + NP * cfg::A_PLANE;
+      uint32_t it = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        int i0, j0, kb_begin, kb_end;
+        unit_range(u, i0, j0, kb_begin, kb_end);
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+          const int s = it % NS;
+          const uint32_t ph = (it / NS) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          mbar_arrive_expect_tx(&full_bar[s], NP * (cfg::A_PLANE + cfg::B_PLANE));
+          uint8_t* a_base = smem + (size_t)s * cfg::STAGE;
+          uint8_t* b_base = a_base + NP * cfg::A_PLANE;
 #pragma unroll
-        for (int pl = 0; pl < NP; ++pl) {
+          for (int pl = 0; pl < NP; ++pl) {
 #pragma unroll
-          for (int bx = 0; bx < BM / 64; ++bx) {
-            uint8_t* dst = a_base + pl * cfg::A_PLANE + bx * 8192;
-            if (!A_MN) tma_load_2d(dst, &tmA, oa.col0 + kb * BK, pl * oa.plane_rows + oa.row0 + i0 + bx * 64, &full_bar[s]);
-            else       tma_load_2d(dst, &tmA, oa.col0 + i0 + bx * 64, pl * oa.plane_rows + oa.row0 + kb * BK, &full_bar[s]);
-          }
+            for (int bx = 0; bx < BM / 64; ++bx) {
+              uint8_t* dst = a_base + pl * cfg::A_PLANE + bx * 8192;
+              if (!A_MN) tma_load_2d(dst, &tmA, oa.col0 + kb * BK, pl * oa.plane_rows + oa.row0 + i0 + bx * 64, &full_bar[s]);
+              else       tma_load_2d(dst, &tmA, oa.col0 + i0 + bx * 64, pl * oa.plane_rows + oa.row0 + kb * BK, &full_bar[s]);
+            }
 #pragma unroll
-          for (int bx = 0; bx < BN / 64; ++bx) {
-            uint8_t* dst = b_base + pl * cfg::B_PLANE + bx * 8192;
-            if (!B_MN) tma_load_2d(dst, &tmB, ob.col0 + kb * BK, pl * ob.plane_rows + ob.row0 + j0 + bx * 64, &full_bar[s]);
-            else       tma_load_2d(dst, &tmB, ob.col0 + j0 + bx * 64, pl * ob.plane_rows + ob.row0 + kb * BK, &full_bar[s]);
+            for (int bx = 0; bx < BN / 64; ++bx) {
+              uint8_t* dst = b_base + pl * cfg::B_PLANE + bx * 8192;
+              if (!B_MN) tma_load_2d(dst, &tmB, ob.col0 + kb * BK, pl * ob.plane_rows + ob.row0 + j0 + bx * 64, &full_bar[s]);
+              else       tma_load_2d(dst, &tmB, ob.col0 + j0 + bx * 64, pl * ob.plane_rows + ob.row0 + kb * BK, &full_bar[s]);
+            }
           }
         }
       }
@@ -260,76 +270,98 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp == MMA_WARP) {
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
-      for (int it = 0; it < nkb; ++it) {
-        const int s = it % NS;
-        const uint32_t ph = (it / NS) & 1;
-        mbar_wait(&full_bar[s], ph);
+      uint32_t it = 0, tcount = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        int i0, j0, kb_begin, kb_end;
+        unit_range(u, i0, j0, kb_begin, kb_end);
+        if (kb_begin >= kb_end) continue;
+        const uint32_t buf = tcount & 1, aph = (tcount >> 1) & 1;
+        mbar_wait(&acc_empty[buf], aph ^ 1);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + (size_t)s * cfg::STAGE);
-        const uint32_t b_addr = a_addr + NP * cfg::A_PLANE;
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+          const int s = it % NS;
+          const uint32_t ph = (it / NS) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + (size_t)s * cfg::STAGE);
+          const uint32_t b_addr = a_addr + NP * cfg::A_PLANE;
 #pragma unroll
-        for (int ks = 0; ks < BK / 16; ++ks) {
-          const uint64_t a_hi = A_MN ? umma_desc(a_addr + ks * 2048, 8192, 1024) : umma_desc(a_addr + ks * 32, 16, 1024);
-          const uint64_t b_hi = B_MN ? umma_desc(b_addr + ks * 2048, 8192, 1024) : umma_desc(b_addr + ks * 32, 16, 1024);
-          const uint32_t acc0 = (it | ks) ? 1u : 0u;
-          if (NP == 2) {
-            const uint64_t a_lo = A_MN ? umma_desc(a_addr + cfg::A_PLANE + ks * 2048, 8192, 1024)
-                                       : umma_desc(a_addr + cfg::A_PLANE + ks * 32, 16, 1024);
-            const uint64_t b_lo = B_MN ? umma_desc(b_addr + cfg::B_PLANE + ks * 2048, 8192, 1024)
-                                       : umma_desc(b_addr + cfg::B_PLANE + ks * 32, 16, 1024);
-            umma_bf16(tmem_base, a_lo, b_hi, idesc, acc0);
-            umma_bf16(tmem_base, a_hi, b_lo, idesc, 1u);
-            umma_bf16(tmem_base, a_hi, b_hi, idesc, 1u);
-          } else {
-            umma_bf16(tmem_base, a_hi, b_hi, idesc, acc0);
+          for (int ks = 0; ks < BK / 16; ++ks) {
+            const uint64_t a_hi = A_MN ? umma_desc(a_addr + ks * 2048, 8192, 1024) : umma_desc(a_addr + ks * 32, 16, 1024);
+            const uint64_t b_hi = B_MN ? umma_desc(b_addr + ks * 2048, 8192, 1024) : umma_desc(b_addr + ks * 32, 16, 1024);
+            const uint32_t acc0 = (kb > kb_begin || ks) ? 1u : 0u;
+            if (NP == 2) {
+              const uint64_t a_lo = A_MN ? umma_desc(a_addr + cfg::A_PLANE + ks * 2048, 8192, 1024)
+                                         : umma_desc(a_addr + cfg::A_PLANE + ks * 32, 16, 1024);
+              const uint64_t b_lo = B_MN ? umma_desc(b_addr + cfg::B_PLANE + ks * 2048, 8192, 1024)
+                                         : umma_desc(b_addr + cfg::B_PLANE + ks * 32, 16, 1024);
+              umma_bf16(d_tmem, a_lo, b_hi, idesc, acc0);
+              umma_bf16(d_tmem, a_hi, b_lo, idesc, 1u);
+              umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
+            } else {
+              umma_bf16(d_tmem, a_hi, b_hi, idesc, acc0);
+            }
           }
+          umma_commit(&empty_bar[s]);
         }
-        umma_commit(&empty_bar[s]);
+        umma_commit(&acc_full[buf]);
+        ++tcount;
       }
-      umma_commit(&acc_bar);
     }
   } else {
     // ------------------------------------------------ epilogue warps: TMEM -> registers -> global
-    mbar_wait(&acc_bar, 0);
-    tc_fence_after();
     const bool vec = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
-    epilogue_rows<BN>(tmem_base, warp, lane, [&](int row, int col, uint32_t (&r)[32]) {
-      const int i = i0 + row;
-      if (i >= OI) return;
-      float* cp = C + (size_t)i * ldc + j0 + col;
-      if (ATOMIC) {
+    uint32_t tcount = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x) {
+      int i0, j0, kb_begin, kb_end;
+      unit_range(u, i0, j0, kb_begin, kb_end);
+      if (kb_begin >= kb_end) continue;
+      const uint32_t buf = tcount & 1, aph = (tcount >> 1) & 1;
+      mbar_wait(&acc_full[buf], aph);
+      tc_fence_after();
+      epilogue_rows<BN>(tmem_base + buf * BN, warp, lane, [&](int row, int col, uint32_t (&r)[32]) {
+        const int i = i0 + row;
+        if (i >= OI) return;
+        float* cp = C + (size_t)i * ldc + j0 + col;
+        if (ATOMIC) {
 #pragma unroll
-        for (int e = 0; e < 32; ++e)
-          if (j0 + col + e < OJ) atomicAdd(cp + e, __uint_as_float(r[e]));
-        return;
-      }
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        const int n = j0 + col + j;
-        if (n >= OJ) break;
-        float o[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          float x = __uint_as_float(r[j + e]);
-          if (bias && n + e < OJ) x += bias[n + e];
-          if (flags & GEMM_RELU) x = fmaxf(x, 0.f);
-          o[e] = x;
+          for (int e = 0; e < 32; ++e)
+            if (j0 + col + e < OJ) atomicAdd(cp + e, __uint_as_float(r[e]));
+          return;
         }
-        if (vec && n + 3 < OJ) {
-          float4 w = make_float4(o[0], o[1], o[2], o[3]);
-          if (flags & GEMM_ACCUM) { const float4 c = *reinterpret_cast<const float4*>(cp + j); w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w; }
-          *reinterpret_cast<float4*>(cp + j) = w;
-        } else {
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (n + e < OJ) cp[j + e] = (flags & GEMM_ACCUM) ? cp[j + e] + o[e] : o[e];
+        for (int j = 0; j < 32; j += 4) {
+          const int n = j0 + col + j;
+          if (n >= OJ) break;
+          float o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float x = __uint_as_float(r[j + e]);
+            if (bias && n + e < OJ) x += bias[n + e];
+            if (flags & GEMM_RELU) x = fmaxf(x, 0.f);
+            o[e] = x;
+          }
+          if (vec && n + 3 < OJ) {
+            float4 w = make_float4(o[0], o[1], o[2], o[3]);
+            if (flags & GEMM_ACCUM) { const float4 c = *reinterpret_cast<const float4*>(cp + j); w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w; }
+            *reinterpret_cast<float4*>(cp + j) = w;
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (n + e < OJ) cp[j + e] = (flags & GEMM_ACCUM) ? cp[j + e] + o[e] : o[e];
+          }
         }
-      }
-    });
+      });
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      ++tcount;
+    }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == MMA_WARP) tmem_dealloc(tmem_base, BN);
+  if (warp == MMA_WARP) tmem_dealloc(tmem_base, 2 * BN);
 }
 
 // ---------------------------------------------------------------------------------------------- packed weights
@@ -458,8 +490,9 @@ int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand
   auto kern = gemm_tma_kernel<BN, NP, A_MN, B_MN, ATOMIC>;
   static bool configured = false;
   if (!configured) { if (int r = set_smem(kern, Cfg<BN, NP>::SMEM)) return r; configured = true; }
-  dim3 grid((OJ + BN - 1) / BN, (OI_host + BM - 1) / BM, splits);
-  kern<<<grid, NTHREADS, Cfg<BN, NP>::SMEM, st>>>(*ma, *mb, oa, ob, C, ldc, bias, OI_host, OI_dev, OJ, R_host, R_dev, flags);
+  long units = (long)((OJ + BN - 1) / BN) * ((OI_host + BM - 1) / BM) * splits;
+  const int grid = units < kNumSMs ? (int)units : kNumSMs;
+  kern<<<grid, NTHREADS, Cfg<BN, NP>::SMEM, st>>>(*ma, *mb, oa, ob, C, ldc, bias, OI_host, OI_dev, OJ, R_host, R_dev, flags, splits);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -505,7 +538,7 @@ int build_pack_jobs(const float* const* srcs, int n, void* jobs_dev, int* n_jobs
 // ... and re-splits them into bf16 (hi, lo) planes: one launch per step (the weights change with every optimizer step).
 int run_pack_jobs(const void* jobs_dev, int n_jobs, cudaStream_t st) {
   if (n_jobs <= 0) return 0;
-  pack_weights_kernel<<<dim3(32, (unsigned)n_jobs), 256, 0, st>>>(reinterpret_cast<const PackJob*>(jobs_dev));
+  pack_weights_kernel<<<dim3(296, (unsigned)n_jobs), 256, 0, st>>>(reinterpret_cast<const PackJob*>(jobs_dev));
   PATHS_LAUNCH_CK();
   return 0;
 }

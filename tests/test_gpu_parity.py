@@ -140,9 +140,15 @@ def test_end2end_parity(name, prec):
     assert rel_err(hz.detach().cpu(), ohz) < tol
     assert abs(float(loss) - float(oloss)) < tol * max(1.0, abs(float(oloss)))
     # 3. gradients on every live parameter; None / zero pattern
+    #   fp32   : every tensor within 1e-4 of its own scale (floored at 1e-3 of the largest gradient entry; tensors of a
+    #            handful of elements -- the importance head's output bias -- are pure cancelling sums: floor 1e-2)
+    #   bf16x3 : the whole flat gradient within 1e-4 (max-norm and L2) of the gradient's scale; single tensors, whose entries
+    #            are strongly cancelling sums over patches, within 1e-2 of their own scale (split-bf16 products carry 2^-17)
+    #   bf16   : ReLU / top-K masks may flip for near-zero pre-activations; relative L2 error of the flat gradient < 5e-2
     named = dict(model.named_parameters())
     gmax = max(float(g.abs().max()) for g in ograds.values() if g is not None)
     num = den = 0.0
+    worst_abs = 0.0
     for k, og in ograds.items():
         mine = named[k].grad
         if og is None:
@@ -151,17 +157,15 @@ def test_end2end_parity(name, prec):
         assert mine is not None, k
         diff = (mine.detach().cpu().double() - og.double())
         num += float((diff ** 2).sum()); den += float((og.double() ** 2).sum())
+        worst_abs = max(worst_abs, float(diff.abs().max()))
         if prec < 2:
-            # fp32 modes: every tensor within 1e-4 of its own scale (floored at 1e-3 of the largest gradient entry:
-            # one-element gradients are cancelling sums)
-            # (tensors of a handful of elements -- the importance head's output bias -- are pure cancelling sums over all
-            # patches: their floor is 1e-2 of the largest entry)
-            scale = max(float(og.abs().max()), (1e-3 if og.numel() > 8 else 1e-2) * gmax)
-            err = float(diff.abs().max()) / scale
-            assert err < tol, f"{k}: gradient error {err:.2e}"
-    # bf16 fast mode: ReLU / top-K masks may flip for near-zero pre-activations, so the bound is on the whole gradient:
-    # relative L2 error of all live gradients below 5e-2 (stated tolerance of the fast mode for gradients)
-    assert (num / den) ** 0.5 < (5e-2 if prec == 2 else 1e-4), f"global gradient error {(num / den) ** 0.5:.2e}"
+            floor = (1e-3 if og.numel() > 8 else 1e-2) * gmax
+            err = float(diff.abs().max()) / max(float(og.abs().max()), floor)
+            assert err < (tol if prec == 0 else 1e-2), f"{k}: gradient error {err:.2e}"
+    gl2 = (num / den) ** 0.5
+    assert gl2 < (5e-2 if prec == 2 else 1e-4), f"flat gradient: relative L2 error {gl2:.2e}"
+    if prec < 2:
+        assert worst_abs / gmax < 1e-4, f"flat gradient: max-norm error {worst_abs / gmax:.2e}"
     # 4. the FREE-running oracle picks the same patches as we do, unless its own scores are tied within the tolerance
     #    at the selection boundary (torch.topk leaves tie order unspecified; we break ties towards the lowest row index)
     for j in range(B):
