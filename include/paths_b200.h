@@ -27,7 +27,7 @@ extern "C" {
 
 #define PATHS_MAX_LEVELS 8
 #define PATHS_MAX_LAYERS 4
-#define PATHS_ABI_VERSION 1
+#define PATHS_ABI_VERSION 2
 
 /* model_config + the train_config fields the hot path reads (config.py:19-79). */
 typedef struct paths_dims {
@@ -43,18 +43,23 @@ typedef struct paths_dims {
   int32_t K[PATHS_MAX_LEVELS];  /* top_k_patches[l] for l < L-1; -1 keeps all (slide.py:294) */
   int32_t imp_mul;        /* importance_mode == "mul" */
   int32_t pe_mode;        /* 1 = "1d", 2 = "2d" */
-  int32_t residual;       /* slide_ctx_mode == "residual" (1) or "none" (0) */
+  int32_t residual;       /* slide_ctx_mode: 0 "none", 1 "residual" (paths.py:130-131), 2 "concat" (paths.py:134-137) */
   int32_t task;           /* 0 survival NLL (utils.py:283), 1 cross-entropy (utils.py:277) */
   int32_t precision;      /* 0 fp32 SIMT, 1 tcgen05 bf16x3 (fp32-parity), 2 tcgen05 bf16 (fast) */
+  int32_t lstm;           /* 1: shared LSTM cell (interface.py:10-58); 0: per-level RNN MLP hctx_mlp (paths.py:46-54,101-109) */
+  int32_t hier_ctx;       /* hierarchical_ctx (only read when lstm == 0; config.py:106 forces it on with the LSTM) */
 } paths_dims_t;
 
 /* Offsets (in floats) of every live parameter inside the flat parameter / gradient buffers.  The stacked matrices
  * must be contiguous: Wg = [forget_gate; remember_gate; remember_map; out_select_gate].weight ([3C+D, 2D]),
- * bg likewise, Wuv = [importance_mlp.0.weight; global_agg.proj_in.weight] ([I+d, D]).  State-dict names: SURVEY §8b. */
+ * bg likewise, Wuv = [importance_mlp.0.weight; global_agg.proj_in.weight] ([I+d, D]).  State-dict names: SURVEY §8b.
+ * With slide_ctx_mode "concat" the classifier of level l is [nl, (l+1)*d]. */
 enum paths_lstm_param { PATHS_P_WG = 0, PATHS_P_BG, PATHS_P_WMO, PATHS_P_BMO, PATHS_P_LSTM_COUNT };
 enum paths_level_param {
   PATHS_P_WUV = 0, PATHS_P_B1, PATHS_P_W2, PATHS_P_B2, PATHS_P_BIN, PATHS_P_SPECIAL, PATHS_P_NFW, PATHS_P_NFB,
-  PATHS_P_WC, PATHS_P_BC, PATHS_P_LEVEL_HEAD_COUNT
+  PATHS_P_WC, PATHS_P_BC,
+  PATHS_P_WH0, PATHS_P_BH0, PATHS_P_WH2, PATHS_P_BH2,   /* hctx_mlp.{0,2} of the RNN variant (offset -1 when lstm == 1) */
+  PATHS_P_LEVEL_HEAD_COUNT
 };
 enum paths_layer_param {
   PATHS_P_WQKV = 0, PATHS_P_BQKV, PATHS_P_WO, PATHS_P_BO, PATHS_P_BCROSS, PATHS_P_FW1, PATHS_P_FB1, PATHS_P_FW2,
@@ -145,6 +150,14 @@ int64_t paths_engine_launch_count(paths_engine_t* e);
 enum paths_prof_tag { PATHS_PROF_GATES_FWD = 0, PATHS_PROF_GATES_DW, PATHS_PROF_GATES_DH, PATHS_PROF__COUNT };
 int paths_engine_profile(paths_engine_t* e, int on);
 int paths_engine_profile_read(paths_engine_t* e, int tag, double* total_ms, int64_t* launches);
+
+/* Fused AdamW step over the flat parameter buffer -- torch.optim.AdamW as used by train.py:49,66.  params/exp_avg/exp_avg_sq
+ * hold n_total floats, grads n_live; elements [n_live, n_total) (parameters whose gradient is identically zero: the dead
+ * encoder / cross-attention weights) only receive the decoupled weight decay.  h_skip: n_skip host pairs [start, end) of
+ * elements left untouched (parameters whose .grad the reference leaves at None).  step counts from 1. */
+int paths_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_live, int64_t n_total,
+                     const int64_t* h_skip, int n_skip, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                     void* stream);
 
 /* Occupancy bitmap of one [W*H, D] grid: bit c set iff any of the D floats of cell c is non-zero; *count += popcount. */
 int paths_build_occupancy(const float* grid, int cells, int D, uint32_t* bits, int32_t* count, void* stream);

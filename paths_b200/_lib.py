@@ -14,14 +14,14 @@ LIB_PATH = os.path.join(HERE, "libpaths_b200.so")
 MAX_LEVELS = 8
 MAX_LAYERS = 4
 P_LSTM_COUNT = 4
-P_LEVEL_HEAD_COUNT = 10
+P_LEVEL_HEAD_COUNT = 14
 P_LAYER_COUNT = 15
 LEVEL_STRIDE = P_LEVEL_HEAD_COUNT + MAX_LAYERS * P_LAYER_COUNT
 NUM_OFFSETS = P_LSTM_COUNT + MAX_LEVELS * LEVEL_STRIDE
 
 # enum paths_lstm_param / paths_level_param / paths_layer_param
 P_WG, P_BG, P_WMO, P_BMO = range(4)
-(P_WUV, P_B1, P_W2, P_B2, P_BIN, P_SPECIAL, P_NFW, P_NFB, P_WC, P_BC) = range(10)
+(P_WUV, P_B1, P_W2, P_B2, P_BIN, P_SPECIAL, P_NFW, P_NFB, P_WC, P_BC, P_WH0, P_BH0, P_WH2, P_BH2) = range(14)
 (P_WQKV, P_BQKV, P_WO, P_BO, P_BCROSS, P_FW1, P_FB1, P_FW2, P_FB2, P_N1W, P_N1B, P_N2W, P_N2B, P_N3W, P_N3B) = range(15)
 
 # enum paths_buffer
@@ -37,7 +37,7 @@ class Dims(C.Structure):
     _fields_ = [("D", C.c_int32), ("C", C.c_int32), ("d", C.c_int32), ("heads", C.c_int32), ("layers", C.c_int32),
                 ("I", C.c_int32), ("F", C.c_int32), ("nl", C.c_int32), ("L", C.c_int32), ("K", C.c_int32 * MAX_LEVELS),
                 ("imp_mul", C.c_int32), ("pe_mode", C.c_int32), ("residual", C.c_int32), ("task", C.c_int32),
-                ("precision", C.c_int32)]
+                ("precision", C.c_int32), ("lstm", C.c_int32), ("hier_ctx", C.c_int32)]
 
 
 class Store(C.Structure):
@@ -53,7 +53,7 @@ SYMBOLS = ["paths_last_error", "paths_abi_version", "paths_engine_workspace_byte
            "paths_engine_begin_padded", "paths_engine_level_forward", "paths_engine_select", "paths_engine_loss",
            "paths_engine_level_backward", "paths_engine_forward", "paths_engine_backward", "paths_engine_buffer",
            "paths_engine_set_precision", "paths_engine_launch_count", "paths_engine_profile", "paths_engine_profile_read", "paths_build_occupancy", "paths_gemm_nt",
-           "paths_gemm_tn"]
+           "paths_gemm_tn", "paths_adamw_step"]
 
 
 def lib() -> C.CDLL:
@@ -93,6 +93,7 @@ def lib() -> C.CDLL:
     L.paths_build_occupancy.argtypes = [vp, i32, i32, vp, vp, vp]
     L.paths_gemm_nt.argtypes = [i32, vp, i32, vp, i32, i32, vp, i32, vp, i32, i32, i32, i32, vp]
     L.paths_gemm_tn.argtypes = [i32, vp, i32, vp, i32, vp, i32, i32, i32, i32, vp]
+    L.paths_adamw_step.argtypes = [vp, vp, vp, vp, i64, i64, C.POINTER(C.c_int64), i32, f32, f32, f32, f32, f32, i32, vp]
     _lib = L
     return L
 

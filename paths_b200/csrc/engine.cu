@@ -74,10 +74,11 @@ struct Level {
   float *X, *G, *Cn, *Pt, *H, *Y, *UV, *alpha, *tok;
   LayerBuf layer[PATHS_MAX_LAYERS];
   float *xhf, *rsf, *z, *F, *logits, *dlogits, *dHrow, *dCrow;
+  float *dFc;                        // slide_ctx_mode "concat": d loss / d F_l written by the last level's head backward
 };
 
 struct LayerP { const float *Wqkv, *bqkv, *Wo, *bo, *bcross, *W1, *b1, *W2, *b2, *n1w, *n1b, *n2w, *n2b, *n3w, *n3b; };
-struct LevelP { const float *Wuv, *b1, *w2, *b2, *bin, *special, *nfw, *nfb, *Wc, *bc; LayerP layer[PATHS_MAX_LAYERS]; };
+struct LevelP { const float *Wuv, *b1, *w2, *b2, *bin, *special, *nfw, *nfb, *Wc, *bc, *Wh0, *bh0, *Wh2, *bh2; LayerP layer[PATHS_MAX_LAYERS]; };
 struct Params { const float *Wg, *bg, *Wmo, *bmo; LevelP level[PATHS_MAX_LEVELS]; };
 
 __global__ void tseg_kernel(const int* __restrict__ seg, int* __restrict__ tseg, int B) {
@@ -139,7 +140,7 @@ size_t carve(paths_engine* e, char* base) {
     v.parent_local = b.take<int>(cap);
     v.sel = b.take<int>((size_t)B * (v.kcap > 0 ? v.kcap : 1)); v.sel_count = b.take<int>(B);
     v.child_of = b.take<int>(4 * cap);
-    v.X = b.take<float>(cap * D); v.G = b.take<float>(cap * (3 * C + D)); v.Cn = b.take<float>(cap * C);
+    v.X = b.take<float>(cap * D); v.G = b.take<float>(dm.lstm ? cap * (3 * C + D) : 4); v.Cn = b.take<float>(cap * C);
     v.Pt = b.take<float>(cap * D); v.H = b.take<float>(cap * D); v.Y = b.take<float>(cap * D);
     v.UV = b.take<float>(cap * (I + d)); v.alpha = b.take<float>(cap); v.tok = b.take<float>(tokcap * d);
     for (int j = 0; j < dm.layers; ++j) {
@@ -155,11 +156,12 @@ size_t carve(paths_engine* e, char* base) {
     v.xhf = b.take<float>((size_t)B * d); v.rsf = b.take<float>(B); v.z = b.take<float>((size_t)B * d);
     v.F = b.take<float>((size_t)B * d); v.logits = b.take<float>((size_t)B * dm.nl); v.dlogits = b.take<float>((size_t)B * dm.nl);
     v.dHrow = b.take<float>(cap * D); v.dCrow = b.take<float>(cap * C);
+    v.dFc = b.take<float>((size_t)B * d);
   }
   e->maxcap = maxcap; e->maxtok = maxcap + B;
   const size_t mc = maxcap, mt = (size_t)maxcap + B;
   e->A1 = b.take<float>(mt * d); e->Fo = b.take<float>(mt * d);
-  e->dY = b.take<float>(mc * D); e->dP = b.take<float>(mc * D); e->dG = b.take<float>(mc * (3 * C + D));
+  e->dY = b.take<float>(mc * D); e->dP = b.take<float>(mc * D); e->dG = b.take<float>(dm.lstm ? mc * (3 * C + D) : 4);
   e->dCn = b.take<float>(mc * C); e->dHc = b.take<float>(mc * D); e->dCc = b.take<float>(mc * C);
   e->dUV = b.take<float>(mc * (I + d));
   e->ga = b.take<float>(mt * d); e->gb = b.take<float>(mt * d); e->gO = b.take<float>(mt * d); e->gt = b.take<float>(mt * d);
@@ -168,13 +170,13 @@ size_t carve(paths_engine* e, char* base) {
   e->hazards = b.take<float>((size_t)B * dm.nl); e->loss = b.take<float>(1); e->loss_per = b.take<float>(B);
   e->overflow = b.take<int>(2); e->slide_cnt = b.take<int>(B); e->slide_fb = b.take<int>(B);
   {
-    size_t pb = packed_bytes(3 * C + D, 2 * D) + packed_bytes(D, C);
-    const size_t per_level = packed_bytes(I + d, D) + (size_t)dm.layers * (packed_bytes(3 * d, d) + packed_bytes(d, d) +
-                                                                              packed_bytes(F, d) + packed_bytes(d, F));
+    size_t pb = dm.lstm ? packed_bytes(3 * C + D, 2 * D) + packed_bytes(D, C) : 0;
+    const size_t per_level = packed_bytes(I + d, D) + (dm.lstm ? 0 : packed_bytes(C, D) + packed_bytes(D, C)) +
+                             (size_t)dm.layers * (packed_bytes(3 * d, d) + packed_bytes(d, d) + packed_bytes(F, d) + packed_bytes(d, F));
     pb += per_level * dm.L;
     e->packed_arena_bytes = pb;
     e->packed_arena = b.take<char>(pb);
-    e->pack_jobs = b.take<char>((size_t)(2 + dm.L * (1 + 4 * dm.layers)) * 64);
+    e->pack_jobs = b.take<char>((size_t)(2 + dm.L * (3 + 4 * dm.layers)) * 64);
     int cols = 2 * D;
     if (3 * C + D > cols) cols = 3 * C + D;
     if (F > cols) cols = F;
@@ -196,6 +198,9 @@ int check_dims(const paths_dims_t* dm, int B, const int32_t* caps, const int32_t
   PATHS_REQUIRE(dm->d % dm->heads == 0 && dm->d / dm->heads <= 64, "head_dim must be <= 64");
   PATHS_REQUIRE(dm->d <= 256 && dm->I <= 256 && dm->nl <= 32, "trans_dim / importance hidden dim above 256 unsupported");
   PATHS_REQUIRE(dm->pe_mode == 1 || dm->pe_mode == 2, "pos_encoding_mode must be 1d or 2d");
+  PATHS_REQUIRE(dm->residual >= 0 && dm->residual <= 2, "slide_ctx_mode must be none (0), residual (1) or concat (2)");
+  PATHS_REQUIRE(dm->lstm == 1 || dm->lstm == 0, "lstm must be 0 or 1");
+  PATHS_REQUIRE(dm->lstm == 0 || dm->hier_ctx == 1, "the LSTM requires hierarchical_ctx (config.py:106)");
   PATHS_REQUIRE(B >= 1, "empty batch");
   for (int l = 0; l < dm->L; ++l) {
     PATHS_REQUIRE(caps[l] >= 1 && maxseg[l] >= 1, "level %d: capacity must be positive", l);
@@ -222,6 +227,7 @@ void bind(Params& P, const float* base, const int64_t* off, const paths_dims_t& 
     q.Wuv = at(o[PATHS_P_WUV]); q.b1 = at(o[PATHS_P_B1]); q.w2 = at(o[PATHS_P_W2]); q.b2 = at(o[PATHS_P_B2]);
     q.bin = at(o[PATHS_P_BIN]); q.special = at(o[PATHS_P_SPECIAL]); q.nfw = at(o[PATHS_P_NFW]); q.nfb = at(o[PATHS_P_NFB]);
     q.Wc = at(o[PATHS_P_WC]); q.bc = at(o[PATHS_P_BC]);
+    q.Wh0 = at(o[PATHS_P_WH0]); q.bh0 = at(o[PATHS_P_BH0]); q.Wh2 = at(o[PATHS_P_WH2]); q.bh2 = at(o[PATHS_P_BH2]);
     for (int j = 0; j < dm.layers; ++j) {
       const int64_t* p = o + PATHS_P_LEVEL_HEAD_COUNT + (size_t)j * PATHS_P_LAYER_COUNT;
       LayerP& y = q.layer[j];
@@ -262,21 +268,37 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
   const int* Md = v.count;
   const int ldg = 3 * C + D;
 
-  // ---- LSTM cell step for every patch (interface.py:49-56); [x || h_parent] is gathered inside the GEMM loader
   const bool has_parent = l > 0;
-  RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
-  {
-    ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
-    RUN(gemm_nt(prec, Axh, e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, has_parent ? 2 * D : D, 0, st));
-  }
-  RUN(lstm_point1_fwd(v.G, has_parent ? e->lv[l - 1].Cn : nullptr, has_parent ? v.row_parent : nullptr, v.Cn, D, C, M, Md, st));
-  RUN(gemm_nt(prec, row_src(v.Cn, C, C), e->P.Wmo, C, 0, v.Pt, D, e->P.bmo, M, Md, D, C, 0, st));
-  RUN(lstm_point2_fwd(v.Pt, v.G, v.X, v.H, v.Y, D, C, M, Md, st));
+  if (dm.lstm) {
+    // ---- LSTM cell step for every patch (interface.py:49-56); [x || h_parent] is gathered inside the GEMM loader
+    RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
+    {
+      ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
+      RUN(gemm_nt(prec, Axh, e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, has_parent ? 2 * D : D, 0, st));
+    }
+    RUN(lstm_point1_fwd(v.G, has_parent ? e->lv[l - 1].Cn : nullptr, has_parent ? v.row_parent : nullptr, v.Cn, D, C, M, Md, st));
+    RUN(gemm_nt(prec, row_src(v.Cn, C, C), e->P.Wmo, C, 0, v.Pt, D, e->P.bmo, M, Md, D, C, 0, st));
+    RUN(lstm_point2_fwd(v.Pt, v.G, v.X, v.H, v.Y, D, C, M, Md, st));
 
-  // ---- importance + token projection share one contraction over Y (paths.py:95-98, aggregator.py:48)
-  RUN(gemm_nt(prec, row_src(v.Y, D, D), p.Wuv, D, 0, v.UV, I + d, nullptr, M, Md, I + d, D, 0, st));
-  RUN(imp_tok_fwd(v.UV, p.b1, p.w2, p.b2, p.bin, e->div, v.row_slide, v.row_xy, v.seg, v.alpha, v.tok, I, d, dm.imp_mul,
-                  dm.pe_mode, M, Md, st));
+    // ---- importance + token projection share one contraction over Y (paths.py:95-98, aggregator.py:48)
+    RUN(gemm_nt(prec, row_src(v.Y, D, D), p.Wuv, D, 0, v.UV, I + d, nullptr, M, Md, I + d, D, 0, st));
+    RUN(imp_tok_fwd(v.UV, p.b1, p.w2, p.b2, p.bin, e->div, v.row_slide, v.row_xy, v.seg, v.alpha, v.tok, I, d, dm.imp_mul,
+                    dm.pe_mode, 0, M, Md, st));
+  } else {
+    // ---- RNN variant (paths.py:95-109): alpha from X; Z = alpha X + MLP_h(Z_parent); tokens from Z.  Z lives in v.H.
+    RUN(gemm_nt(prec, row_src(v.X, D, D), p.Wuv, D, 0, v.UV, I + d, nullptr, M, Md, I, D, 0, st));
+    RUN(imp_tok_fwd(v.UV, p.b1, p.w2, p.b2, p.bin, e->div, v.row_slide, v.row_xy, v.seg, v.alpha, v.tok, I, d, dm.imp_mul,
+                    dm.pe_mode, 1, M, Md, st));
+    const bool hctx = has_parent && dm.hier_ctx;
+    if (hctx) {
+      RUN(gemm_nt(prec, row_src(e->lv[l - 1].H, D, D, v.row_parent), p.Wh0, D, 0, v.Cn, C, p.bh0, M, Md, C, D, GEMM_RELU, st));
+      RUN(gemm_nt(prec, row_src(v.Cn, C, C), p.Wh2, C, 0, v.Pt, D, p.bh2, M, Md, D, C, 0, st));
+    }
+    RUN(rnn_z_fwd(v.X, v.alpha, hctx ? v.Pt : nullptr, v.H, D, dm.imp_mul, M, Md, st));
+    RUN(gemm_nt(prec, row_src(v.H, D, D), p.Wuv + (size_t)I * D, D, 0, v.UV + I, I + d, nullptr, M, Md, d, D, 0, st));
+    RUN(imp_tok_fwd(v.UV, p.b1, p.w2, p.b2, p.bin, e->div, v.row_slide, v.row_xy, v.seg, v.alpha, v.tok, I, d, dm.imp_mul,
+                    dm.pe_mode, 2, M, Md, st));
+  }
   RUN(special_fill(p.special, v.seg, v.tok, d, B, st));
 
   // ---- transformer aggregator: decoder layers over packed tokens, last layer evaluated at the special token only
@@ -301,7 +323,14 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
   }
   RUN(res_ln_fwd(t_in, nullptr, nullptr, nullptr, p.nfw, p.nfb, v.z, v.xhf, v.rsf, d, 1e-5f, B, nullptr, 0, st));
   // ---- residual slide context + classifier (paths.py:130-139)
-  RUN(head_fwd(v.z, (dm.residual && l > 0) ? e->lv[l - 1].F : nullptr, p.Wc, p.bc, v.F, v.logits, d, dm.nl, B, st));
+  if (dm.residual == 2) {
+    RUN(head_fwd(v.z, nullptr, nullptr, nullptr, v.F, nullptr, d, 0, B, st));          // F_l = z_l
+    FList fl; fl.n = l + 1;
+    for (int j = 0; j <= l; ++j) fl.f[j] = e->lv[j].F;
+    RUN(head_concat_fwd(fl, p.Wc, p.bc, v.logits, d, dm.nl, B, st));
+  } else {
+    RUN(head_fwd(v.z, (dm.residual == 1 && l > 0) ? e->lv[l - 1].F : nullptr, p.Wc, p.bc, v.F, v.logits, d, dm.nl, B, st));
+  }
   return 0;
 }
 
@@ -320,12 +349,27 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   const bool last_level = l == dm.L - 1;
 
   // ---- head: dF = dF(l+1) + dlogits.Wc
-  const float* dF_in = (dm.residual && !last_level) ? e->dF : nullptr;
   const float* dlog = use_dlogits ? v.dlogits : nullptr;
-  RUN(head_bwd(dlog, dF_in, p.Wc, e->dF, d, dm.nl, B, st));
-  if (dlog) {
-    RUN(gemm_tn(prec, dlog, dm.nl, row_src(v.F, d, d), W_(g.Wc), d, B, nullptr, dm.nl, d, st));
-    RUN(colsum_accum(dlog, dm.nl, W_(g.bc), B, nullptr, dm.nl, st));
+  if (dm.residual == 2) {
+    // concat: the classifier of the level whose logits reach the loss sees every F_j, j <= l (paths.py:134-137)
+    if (dlog) {
+      GList gl; gl.n = l + 1;
+      for (int j = 0; j <= l; ++j) gl.g[j] = e->lv[j].dFc;
+      RUN(head_concat_bwd(dlog, p.Wc, gl, d, dm.nl, B, st));
+      for (int j = 0; j <= l; ++j)
+        RUN(gemm_tn(prec, dlog, dm.nl, row_src(e->lv[j].F, d, d), W_(g.Wc) + (size_t)j * d, (l + 1) * d, B, nullptr, dm.nl, d, st));
+      RUN(colsum_accum(dlog, dm.nl, W_(g.bc), B, nullptr, dm.nl, st));
+    } else if (last_level) {
+      RUN(zero_rows(v.dFc, d, B, nullptr, 0, st));
+    }
+    RUN(head_bwd(nullptr, v.dFc, p.Wc, e->dF, d, dm.nl, B, st));
+  } else {
+    const float* dF_in = (dm.residual == 1 && !last_level) ? e->dF : nullptr;
+    RUN(head_bwd(dlog, dF_in, p.Wc, e->dF, d, dm.nl, B, st));
+    if (dlog) {
+      RUN(gemm_tn(prec, dlog, dm.nl, row_src(v.F, d, d), W_(g.Wc), d, B, nullptr, dm.nl, d, st));
+      RUN(colsum_accum(dlog, dm.nl, W_(g.bc), B, nullptr, dm.nl, st));
+    }
   }
   // ---- final LayerNorm at the special tokens
   RUN(ln_bwd(e->dF, nullptr, v.xhf, v.rsf, p.nfw, e->dy3s, nullptr, 0, W_(g.nfw), W_(g.nfb), nullptr, d, B, nullptr, 0, st));
@@ -370,11 +414,34 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   const float* dtok = dy3;
   // ---- special token, importance / projection
   RUN(special_grad(dtok, v.seg, W_(g.special), d, B, st));
-  RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, e->dUV, W_(g.b1), W_(g.w2), W_(g.b2), W_(g.bin), I, d, dm.imp_mul, M, Md, st));
+  const bool has_children = !last_level;
+  const bool has_parent = l > 0;
+  if (!dm.lstm) {
+    // ---- RNN variant: tok = Z.W_in^T + b_in + PE;  Z = alpha X + hctx;  hctx = Wh2 relu(Wh0 Z_parent + bh0) + bh2
+    const bool hctx = has_parent && dm.hier_ctx;
+    RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, e->dUV, W_(g.b1), W_(g.w2), W_(g.b2), W_(g.bin), I, d, dm.imp_mul, 2, M, Md, st));
+    RUN(gemm_nt(prec, row_src(e->dUV + I, I + d, d), p.Wuv + (size_t)I * D, D, 1, e->dY, D, nullptr, M, Md, D, d, 0, st));   // dZ
+    RUN(gemm_tn(prec, e->dUV + I, I + d, row_src(v.H, D, D), W_(g.Wuv) + (size_t)I * D, D, M, Md, d, D, st));
+    if (has_children && dm.hier_ctx)
+      RUN(parent_sum(v.child_of, e->lv[l + 1].dHrow, nullptr, e->dHc, nullptr, D, 0, M, Md, st));
+    RUN(rnn_alpha_bwd(e->dY, (has_children && dm.hier_ctx) ? e->dHc : nullptr, v.X, v.UV, v.alpha, p.w2, e->dUV, W_(g.b1), W_(g.w2),
+                      W_(g.b2), D, I, d, dm.imp_mul, M, Md, st));
+    RUN(gemm_tn(prec, e->dUV, I + d, row_src(v.X, D, D), W_(g.Wuv), D, M, Md, I, D, st));
+    if (hctx) {
+      RUN(gemm_tn(prec, e->dY, D, row_src(v.Cn, C, C), W_(g.Wh2), C, M, Md, D, C, st));
+      RUN(colsum_accum(e->dY, D, W_(g.bh2), M, Md, D, st));
+      RUN(gemm_nt(prec, row_src(e->dY, D, D), p.Wh2, C, 1, e->dCn, C, nullptr, M, Md, C, D, 0, st));
+      RUN(relu_bwd(e->dCn, v.Cn, C, M, Md, 0, st));
+      RUN(gemm_tn(prec, e->dCn, C, row_src(e->lv[l - 1].H, D, D, v.row_parent), W_(g.Wh0), D, M, Md, C, D, st));
+      RUN(colsum_accum(e->dCn, C, W_(g.bh0), M, Md, C, st));
+      RUN(gemm_nt(prec, row_src(e->dCn, C, C), p.Wh0, D, 1, v.dHrow, D, nullptr, M, Md, D, C, 0, st));
+    }
+    return 0;
+  }
+  RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, e->dUV, W_(g.b1), W_(g.w2), W_(g.b2), W_(g.bin), I, d, dm.imp_mul, 0, M, Md, st));
   RUN(gemm_nt(prec, row_src(e->dUV, I + d, I + d), p.Wuv, D, 1, e->dY, D, nullptr, M, Md, D, I + d, 0, st));
   RUN(gemm_tn(prec, e->dUV, I + d, row_src(v.Y, D, D), W_(g.Wuv), D, M, Md, I + d, D, st));
   // ---- state gradients arriving from the children of this level's selected rows
-  const bool has_children = !last_level;
   if (has_children)
     RUN(parent_sum(v.child_of, e->lv[l + 1].dHrow, e->lv[l + 1].dCrow, e->dHc, e->dCc, D, C, M, Md, st));
   // ---- LSTM cell
@@ -382,7 +449,6 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   RUN(gemm_nt(prec, row_src(e->dP, D, D), e->P.Wmo, C, 1, e->dCn, C, nullptr, M, Md, C, D, 0, st));
   RUN(gemm_tn(prec, e->dP, D, row_src(v.Cn, C, C), W_(e->Gr.Wmo), C, M, Md, D, C, st));
   RUN(colsum_accum(e->dP, D, W_(e->Gr.bmo), M, Md, D, st));
-  const bool has_parent = l > 0;
   RUN(lstm_point1_bwd(e->dCn, has_children ? e->dCc : nullptr, v.G, has_parent ? e->lv[l - 1].Cn : nullptr,
                       has_parent ? v.row_parent : nullptr, e->dG, has_parent ? v.dCrow : nullptr, D, C, M, Md, st));
   if (has_parent) {
@@ -519,10 +585,18 @@ int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grad
       return 0;
     };
     int rc = 0;
-    rc = rc ? rc : reg(e->P.Wg, 3 * Cm + D, 2 * D, 2 * D);
-    rc = rc ? rc : reg(e->P.Wmo, D, Cm, Cm);
+    if (dm.lstm) {
+      PATHS_REQUIRE(e->P.Wg && e->P.Wmo, "bind_params: LSTM weights missing");
+      rc = rc ? rc : reg(e->P.Wg, 3 * Cm + D, 2 * D, 2 * D);
+      rc = rc ? rc : reg(e->P.Wmo, D, Cm, Cm);
+    }
     for (int l = 0; l < dm.L && !rc; ++l) {
       rc = rc ? rc : reg(e->P.level[l].Wuv, I + d, D, D);
+      if (!dm.lstm && l > 0 && dm.hier_ctx) {
+        PATHS_REQUIRE(e->P.level[l].Wh0 && e->P.level[l].Wh2, "bind_params: hctx_mlp weights of level %d missing", l);
+        rc = rc ? rc : reg(e->P.level[l].Wh0, Cm, D, D);
+        rc = rc ? rc : reg(e->P.level[l].Wh2, D, Cm, Cm);
+      }
       for (int j = 0; j < dm.layers && !rc; ++j) {
         const LayerP& y = e->P.level[l].layer[j];
         rc = rc ? rc : reg(y.Wqkv, 3 * d, d, d);

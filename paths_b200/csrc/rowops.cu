@@ -161,24 +161,29 @@ __global__ void __launch_bounds__(TPB) imp_tok_fwd_kernel(float* __restrict__ UV
                                                           const int* __restrict__ row_slide, const int* __restrict__ row_xy,
                                                           const int* __restrict__ seg, float* __restrict__ alpha,
                                                           float* __restrict__ tok, int I, int d, int imp_mul, int pe_mode,
-                                                          int M_host, const int* M_dev) {
+                                                          int mode, int M_host, const int* M_dev) {
+  // mode 0: importance + token (LSTM path); 1: importance only; 2: token only, unscaled (RNN variant: V = Z.W_in^T)
   const int M = row_count(M_host, M_dev);
   const int ld = I + d;
   ROW_LOOP(m, M) {
     float* uv = UV + (size_t)m * ld;
-    float s = 0.f;
-    for (int j = lane; j < I; j += 32) {
-      const float u = fmaxf(uv[j] + b1[j], 0.f);
-      uv[j] = u;
-      s += u * w2[j];
+    float a = 1.f;
+    if (mode != 2) {
+      float s = 0.f;
+      for (int j = lane; j < I; j += 32) {
+        const float u = fmaxf(uv[j] + b1[j], 0.f);
+        uv[j] = u;
+        s += u * w2[j];
+      }
+      s = warp_sum(s) + b2[0];
+      a = sigmoidf_(s);
+      if (lane == 0) alpha[m] = a;
+      if (mode == 1) continue;
     }
-    s = warp_sum(s) + b2[0];
-    const float a = sigmoidf_(s);
-    if (lane == 0) alpha[m] = a;
     const int sl = row_slide[m];
     const int x = row_xy[2 * m], y = row_xy[2 * m + 1], i = m - seg[sl];
     float* t = tok + (size_t)(m + sl + 1) * d;
-    const float sc = imp_mul ? a : 1.f;
+    const float sc = (imp_mul && mode == 0) ? a : 1.f;
     for (int c = lane; c < d; c += 32) t[c] = sc * uv[I + c] + bin[c] + pos_enc(pe_mode, div, d, c, x, y, i);
   }
 }
@@ -197,10 +202,12 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restric
                                                           const float* __restrict__ alpha, const float* __restrict__ w2,
                                                           const int* __restrict__ row_slide, float* __restrict__ dUV,
                                                           float* __restrict__ db1, float* __restrict__ dw2, float* __restrict__ db2,
-                                                          float* __restrict__ dbin, int I, int d, int imp_mul, int M_host,
-                                                          const int* M_dev) {
+                                                          float* __restrict__ dbin, int I, int d, int imp_mul, int mode,
+                                                          int M_host, const int* M_dev) {
+  // mode 0: full backward of imp_tok_fwd; 2: token part only (dV = dtok, dbin), the importance head is handled elsewhere
   const int M = row_count(M_host, M_dev);
   const int ld = I + d;
+  if (mode == 2) imp_mul = 0;
   float a_b1[8], a_w2[8], a_bin[8], a_b2 = 0.f;
 #pragma unroll
   for (int q = 0; q < 8; ++q) a_b1[q] = a_w2[q] = a_bin[q] = 0.f;
@@ -223,6 +230,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restric
     float ds = 0.f;
     if (imp_mul) { da = warp_sum(da); ds = da * a * (1.f - a); }
     a_b2 += ds;
+    if (mode == 2) continue;
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
       const int j = lane + 32 * q;
@@ -249,14 +257,116 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restric
     float s0 = 0.f, s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int ww = 0; ww < WPB; ++ww) { s0 += red[ww][0][c]; s1 += red[ww][1][c]; s2 += red[ww][2][c]; }
-    if (c < I) { if (s0 != 0.f) atomicAdd(db1 + c, s0); if (s1 != 0.f) atomicAdd(dw2 + c, s1); }
+    if (c < I && mode != 2) { if (s0 != 0.f) atomicAdd(db1 + c, s0); if (s1 != 0.f) atomicAdd(dw2 + c, s1); }
     if (c < d && s2 != 0.f) atomicAdd(dbin + c, s2);
+  }
+  if (threadIdx.x == 0 && mode != 2) {
+    float s = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < WPB; ++ww) s += red_b2[ww];
+    if (s != 0.f) atomicAdd(db2, s);
+  }
+}
+
+// ---- RNN variant (lstm = false, paths.py:96-109): Z = alpha * X + hctx ------------------------------------------------
+__global__ void __launch_bounds__(TPB) rnn_z_fwd_kernel(const float* __restrict__ X, const float* __restrict__ alpha,
+                                                        const float* __restrict__ hctx, float* __restrict__ Z, int D, int imp_mul,
+                                                        int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  ROW_LOOP(m, M) {
+    const float a = imp_mul ? alpha[m] : 1.f;
+    for (int c = lane; c < D; c += 32) {
+      float z = a * X[(size_t)m * D + c];
+      if (hctx) z += hctx[(size_t)m * D + c];
+      Z[(size_t)m * D + c] = z;
+    }
+  }
+}
+
+// dZ (+= dZc from the children); d alpha = <dZ, X>; backward of the importance head -> dUV[:, :I], db1, dw2, db2
+__global__ void __launch_bounds__(TPB) rnn_alpha_bwd_kernel(float* __restrict__ dZ, const float* __restrict__ dZc,
+                                                            const float* __restrict__ X, const float* __restrict__ UV,
+                                                            const float* __restrict__ alpha, const float* __restrict__ w2,
+                                                            float* __restrict__ dUV, float* __restrict__ db1, float* __restrict__ dw2,
+                                                            float* __restrict__ db2, int D, int I, int d, int imp_mul, int M_host,
+                                                            const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ld = I + d;
+  float a_b1[8], a_w2[8], a_b2 = 0.f;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) a_b1[q] = a_w2[q] = 0.f;
+  ROW_LOOP(m, M) {
+    float da = 0.f;
+    for (int c = lane; c < D; c += 32) {
+      float g = dZ[(size_t)m * D + c];
+      if (dZc) { g += dZc[(size_t)m * D + c]; dZ[(size_t)m * D + c] = g; }
+      da += g * X[(size_t)m * D + c];
+    }
+    const float a = alpha[m];
+    float ds = 0.f;
+    if (imp_mul) { da = warp_sum(da); ds = da * a * (1.f - a); }
+    a_b2 += ds;
+    const float* uv = UV + (size_t)m * ld;
+    float* duv = dUV + (size_t)m * ld;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int j = lane + 32 * q;
+      if (j < I) {
+        const float u = uv[j];
+        a_w2[q] += ds * u;
+        const float du = (u > 0.f) ? ds * w2[j] : 0.f;
+        a_b1[q] += du;
+        duv[j] = du;
+      }
+    }
+  }
+  __shared__ float red[WPB][2][256];
+  const int w = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) { red[w][0][lane + 32 * q] = a_b1[q]; red[w][1][lane + 32 * q] = a_w2[q]; }
+  __shared__ float red_b2[WPB];
+  if (lane == 0) red_b2[w] = a_b2;
+  __syncthreads();
+  for (int c = threadIdx.x; c < I; c += TPB) {
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < WPB; ++ww) { s0 += red[ww][0][c]; s1 += red[ww][1][c]; }
+    if (s0 != 0.f) atomicAdd(db1 + c, s0);
+    if (s1 != 0.f) atomicAdd(dw2 + c, s1);
   }
   if (threadIdx.x == 0) {
     float s = 0.f;
 #pragma unroll
     for (int ww = 0; ww < WPB; ++ww) s += red_b2[ww];
     if (s != 0.f) atomicAdd(db2, s);
+  }
+}
+
+// ---- slide_ctx_mode "concat" (paths.py:134-137): logits = Wc . [F_0 | ... | F_l] + bc ------------------------------------
+__global__ void __launch_bounds__(TPB) head_concat_fwd_kernel(FList fl, const float* __restrict__ Wc, const float* __restrict__ bc,
+                                                              float* __restrict__ logits, int d, int nl, int B) {
+  const int ldw = fl.n * d;
+  ROW_LOOP(s, B) {
+    for (int k = 0; k < nl; ++k) {
+      float acc = 0.f;
+      for (int j = 0; j < fl.n; ++j)
+        for (int c = lane; c < d; c += 32) acc += fl.f[j][(size_t)s * d + c] * Wc[(size_t)k * ldw + j * d + c];
+      acc = warp_sum(acc);
+      if (lane == 0) logits[(size_t)s * nl + k] = acc + bc[k];
+    }
+  }
+}
+// dF_j = dlogits . Wc[:, j*d:(j+1)*d] for every level j <= l
+__global__ void __launch_bounds__(TPB) head_concat_bwd_kernel(const float* __restrict__ dlogits, const float* __restrict__ Wc, GList gl,
+                                                              int d, int nl, int B) {
+  const int ldw = gl.n * d;
+  ROW_LOOP(s, B) {
+    for (int j = 0; j < gl.n; ++j)
+      for (int c = lane; c < d; c += 32) {
+        float g = 0.f;
+        for (int k = 0; k < nl; ++k) g += dlogits[(size_t)s * nl + k] * Wc[(size_t)k * ldw + j * d + c];
+        gl.g[j][(size_t)s * d + c] = g;
+      }
   }
 }
 
@@ -537,12 +647,12 @@ int parent_sum(const int* child_of, const float* dHrow, const float* dCrow, floa
   return 0;
 }
 int imp_tok_fwd(float* UV, const float* b1, const float* w2, const float* b2, const float* bin, const float* div, const int* row_slide,
-                const int* row_xy, const int* seg, float* alpha, float* tok, int I, int d, int imp_mul, int pe_mode, int M_host,
+                const int* row_xy, const int* seg, float* alpha, float* tok, int I, int d, int imp_mul, int pe_mode, int mode, int M_host,
                 const int* M_dev, cudaStream_t st) {
   PATHS_REQUIRE(I <= 256 && d <= 256, "imp_tok: hidden dims above 256 are not supported (I=%d, d=%d)", I, d);
   if (M_host <= 0) return 0;
   imp_tok_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul,
-                                                       pe_mode, M_host, M_dev);
+                                                       pe_mode, mode, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -552,10 +662,35 @@ int special_fill(const float* special, const int* seg, float* tok, int d, int B,
   return 0;
 }
 int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const float* w2, const int* row_slide, float* dUV, float* db1,
-                float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int M_host, const int* M_dev, cudaStream_t st) {
+                float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int mode, int M_host, const int* M_dev, cudaStream_t st) {
   if (M_host <= 0) return 0;
   int g = row_grid(M_host); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
-  imp_tok_bwd_kernel<<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, db1, dw2, db2, dbin, I, d, imp_mul, M_host, M_dev);
+  imp_tok_bwd_kernel<<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, db1, dw2, db2, dbin, I, d, imp_mul, mode, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int rnn_z_fwd(const float* X, const float* alpha, const float* hctx, float* Z, int D, int imp_mul, int M_host, const int* M_dev,
+              cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  rnn_z_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(X, alpha, hctx, Z, D, imp_mul, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int rnn_alpha_bwd(float* dZ, const float* dZc, const float* X, const float* UV, const float* alpha, const float* w2, float* dUV, float* db1,
+                  float* dw2, float* db2, int D, int I, int d, int imp_mul, int M_host, const int* M_dev, cudaStream_t st) {
+  if (M_host <= 0) return 0;
+  int g = row_grid(M_host); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
+  rnn_alpha_bwd_kernel<<<g, TPB, 0, st>>>(dZ, dZc, X, UV, alpha, w2, dUV, db1, dw2, db2, D, I, d, imp_mul, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int head_concat_fwd(const FList& fl, const float* Wc, const float* bc, float* logits, int d, int nl, int B, cudaStream_t st) {
+  head_concat_fwd_kernel<<<row_grid(B), TPB, 0, st>>>(fl, Wc, bc, logits, d, nl, B);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int head_concat_bwd(const float* dlogits, const float* Wc, const GList& gl, int d, int nl, int B, cudaStream_t st) {
+  head_concat_bwd_kernel<<<row_grid(B), TPB, 0, st>>>(dlogits, Wc, gl, d, nl, B);
   PATHS_LAUNCH_CK();
   return 0;
 }

@@ -19,11 +19,20 @@ int lstm_point1_bwd(const float* dCn, const float* dCc, const float* G, const fl
 int parent_sum(const int* child_of, const float* dHrow, const float* dCrow, float* dHc, float* dCc, int D, int C, int M_host,
                const int* M_dev, cudaStream_t st);
 int imp_tok_fwd(float* UV, const float* b1, const float* w2, const float* b2, const float* bin, const float* div, const int* row_slide,
-                const int* row_xy, const int* seg, float* alpha, float* tok, int I, int d, int imp_mul, int pe_mode, int M_host,
+                const int* row_xy, const int* seg, float* alpha, float* tok, int I, int d, int imp_mul, int pe_mode, int mode, int M_host,
                 const int* M_dev, cudaStream_t st);
 int special_fill(const float* special, const int* seg, float* tok, int d, int B, cudaStream_t st);
 int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const float* w2, const int* row_slide, float* dUV, float* db1,
-                float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int M_host, const int* M_dev, cudaStream_t st);
+                float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int mode, int M_host, const int* M_dev, cudaStream_t st);
+// RNN variant (lstm = false, paths.py:96-109) and slide_ctx_mode "concat" (paths.py:134-137)
+struct FList { const float* f[8]; int n; };
+struct GList { float* g[8]; int n; };
+int rnn_z_fwd(const float* X, const float* alpha, const float* hctx, float* Z, int D, int imp_mul, int M_host, const int* M_dev,
+              cudaStream_t st);
+int rnn_alpha_bwd(float* dZ, const float* dZc, const float* X, const float* UV, const float* alpha, const float* w2, float* dUV, float* db1,
+                  float* dw2, float* db2, int D, int I, int d, int imp_mul, int M_host, const int* M_dev, cudaStream_t st);
+int head_concat_fwd(const FList& fl, const float* Wc, const float* bc, float* logits, int d, int nl, int B, cudaStream_t st);
+int head_concat_bwd(const float* dlogits, const float* Wc, const GList& gl, int d, int nl, int B, cudaStream_t st);
 int special_grad(const float* dtok, const int* seg, float* dspecial, int d, int B, cudaStream_t st);
 int res_ln_fwd(const float* res, const int* ridx, const float* add, const float* bias, const float* gamma, const float* beta, float* y,
                float* xhat, float* rstd, int d, float eps, int M_host, const int* M_dev, int M_extra, cudaStream_t st);

@@ -20,10 +20,8 @@ def _stream() -> int:
 def make_dims(model_config, train_config, precision: int = 0) -> L.Dims:
     """paths_dims_t from the reference's PATHSProcessorConfig / Config objects (config.py:19-79)."""
     mc, tc = model_config, train_config
-    if not mc.lstm:
-        raise NotImplementedError("paths_b200: the RNN variant (lstm=false, model/paths.py:46-54,101-109) is not accelerated yet")
-    if mc.slide_ctx_mode == "concat":
-        raise NotImplementedError("paths_b200: slide_ctx_mode='concat' (model/paths.py:134-137) is not accelerated yet")
+    if mc.slide_ctx_mode not in ("residual", "concat", "none"):
+        raise ValueError(f"unknown slide_ctx_mode {mc.slide_ctx_mode!r}")
     d = L.Dims()
     d.D, d.C, d.d, d.heads, d.layers = mc.patch_embed_dim, mc.hierarchical_ctx_mlp_hidden_dim, mc.trans_dim, mc.trans_heads, mc.trans_layers
     d.I, d.F = mc.importance_mlp_hidden_dim, 4 * mc.trans_dim
@@ -34,7 +32,9 @@ def make_dims(model_config, train_config, precision: int = 0) -> L.Dims:
         d.K[i] = int(ks[i]) if i < len(ks) else -1
     d.imp_mul = 1 if mc.importance_mode == "mul" else 0
     d.pe_mode = 2 if mc.pos_encoding_mode == "2d" else 1
-    d.residual = 1 if mc.slide_ctx_mode == "residual" else 0
+    d.residual = {"none": 0, "residual": 1, "concat": 2}[mc.slide_ctx_mode]
+    d.lstm = 1 if mc.lstm else 0
+    d.hier_ctx = 1 if mc.hierarchical_ctx else 0
     d.task = 0 if tc.task == "survival" else 1
     d.precision = precision
     return d
@@ -61,10 +61,11 @@ class ParamLayout:
         sd_names: List[Tuple[int, List[str]]] = []
         g = "lstm.{}.0.{}"
         gates = ["forget_gate", "remember_gate", "remember_map", "out_select_gate"]
-        sd_names.append((L.P_WG, [g.format(n, "weight") for n in gates]))
-        sd_names.append((L.P_BG, [g.format(n, "bias") for n in gates]))
-        sd_names.append((L.P_WMO, ["lstm.mem_to_out.0.weight"]))
-        sd_names.append((L.P_BMO, ["lstm.mem_to_out.0.bias"]))
+        if dims.lstm:
+            sd_names.append((L.P_WG, [g.format(n, "weight") for n in gates]))
+            sd_names.append((L.P_BG, [g.format(n, "bias") for n in gates]))
+            sd_names.append((L.P_WMO, ["lstm.mem_to_out.0.weight"]))
+            sd_names.append((L.P_BMO, ["lstm.mem_to_out.0.bias"]))
         for l in range(dims.L):
             base = L.P_LSTM_COUNT + l * L.LEVEL_STRIDE
             p = f"procs.{l}."
@@ -77,6 +78,9 @@ class ParamLayout:
                 (base + L.P_NFB, [a + "transformer.decoder.norm.bias"]), (base + L.P_WC, [p + "classification_layer.weight"]),
                 (base + L.P_BC, [p + "classification_layer.bias"]),
             ]
+            if not dims.lstm and dims.hier_ctx and l > 0:      # RNN variant; procs.0.hctx_mlp is never evaluated (paths.py:102)
+                sd_names += [(base + L.P_WH0, [p + "hctx_mlp.0.weight"]), (base + L.P_BH0, [p + "hctx_mlp.0.bias"]),
+                             (base + L.P_WH2, [p + "hctx_mlp.2.weight"]), (base + L.P_BH2, [p + "hctx_mlp.2.bias"])]
             for j in range(dims.layers):
                 q = a + f"transformer.decoder.layers.{j}."
                 lb = base + L.P_LEVEL_HEAD_COUNT + j * L.P_LAYER_COUNT
@@ -106,24 +110,32 @@ class ParamLayout:
         self.dead = [(n, prm) for n, prm in named.items() if n not in self.live]
         dev = self.entries[0][1].device
         self.device = dev
-        self.flat = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        # tail of the flat buffer: parameters the hot path never reads (the encoder / cross-attention weights of
+        # nn.Transformer).  They have no gradient storage; the fused AdamW only weight-decays them.
+        self.dead_entries: List[Tuple[str, torch.nn.Parameter, int, int]] = []
+        for n, prm in self.dead:
+            self.dead_entries.append((n, prm, off, prm.numel()))
+            off += prm.numel()
+        self.total_all = (off + 63) // 64 * 64
+        self.flat = torch.zeros(self.total_all, dtype=torch.float32, device=dev)
         self.gflat = torch.zeros(self.total, dtype=torch.float32, device=dev)
         self.views: Dict[str, torch.Tensor] = {}
         self.gviews: Dict[str, torch.Tensor] = {}
         with torch.no_grad():
-            for n, prm, o, k in self.entries:
+            for n, prm, o, k in self.entries + self.dead_entries:
                 v = self.flat[o:o + k].view(prm.shape)
                 v.copy_(prm.data)
                 prm.data = v
                 self.views[n] = v
-                self.gviews[n] = self.gflat[o:o + k].view(prm.shape)
+                if o < self.total:
+                    self.gviews[n] = self.gflat[o:o + k].view(prm.shape)
         # parameters whose gradient the reference leaves at None: classifiers of levels 0..L-2 (utils.py:263 only the
         # last level's logits reach the loss)
         self.none_grad = {f"procs.{l}.classification_layer.{w}" for l in range(dims.L - 1) for w in ("weight", "bias")}
 
     def valid(self) -> bool:
         """False if some parameter was re-allocated (e.g. model.to(other_device)); the layout must then be rebuilt."""
-        return all(prm.data_ptr() == self.views[n].data_ptr() for n, prm, _, _ in self.entries)
+        return all(prm.data_ptr() == self.views[n].data_ptr() for n, prm, _, _ in self.entries + self.dead_entries)
 
     def prepare_grads(self) -> None:
         """Make gflat the accumulation target of every live parameter's .grad (autograd semantics: grad += new)."""
@@ -145,8 +157,8 @@ class ParamLayout:
             if prm.requires_grad:
                 prm.grad = self.gviews[n]
         for n, prm in self.dead:                       # the reference produces exact zeros for the dead encoder / cross-attn
-            if prm.requires_grad and prm.grad is None:
-                prm.grad = torch.zeros_like(prm)
+            if prm.requires_grad and prm.grad is None and ".transformer." in n:
+                prm.grad = torch.zeros_like(prm)       # (never-evaluated modules such as procs.0.hctx_mlp keep grad = None)
 
 
 # ------------------------------------------------------------------------------------------------------------------

@@ -191,13 +191,21 @@ class ModelRuntime:
         locs = torch.div(data.locs.to(self.device), self.model.model_config.patch_size, rounding_mode="floor")
         eng.buffer(depth, "ROW_XY").view(-1, 2)[:M] = locs[valid].to(torch.int32)
         eng.buffer(depth, "X").view(-1, D)[:M] = data.fts.to(self.device, torch.float32)[valid]
+        lstm = bool(dm.lstm)
         if depth > 0:
             eng.buffer(depth, "ROW_PARENT")[:M] = torch.arange(M, dtype=torch.int32, device=self.device)
-            st = data.ctx_patch.to(self.device, torch.float32)[:, :, -1][valid]
-            eng.buffer(depth - 1, "H").view(-1, D)[:M] = st[:, :D]
-            eng.buffer(depth - 1, "CN").view(-1, Cc)[:M] = st[:, D:]
-            if data.ctx_depth > 0:
-                eng.buffer(depth - 1, "F").view(B, d).copy_(data.ctx_slide.to(self.device, torch.float32)[:, -1])
+            if data.ctx_patch.shape[2] > 0:
+                st = data.ctx_patch.to(self.device, torch.float32)[:, :, -1][valid]
+                eng.buffer(depth - 1, "H").view(-1, D)[:M] = st[:, :D]
+                if lstm:
+                    eng.buffer(depth - 1, "CN").view(-1, Cc)[:M] = st[:, D:]
+            cs = data.ctx_slide.to(self.device, torch.float32)
+            if dm.residual == 2:                       # concat reads the whole slide-context history (paths.py:135)
+                assert data.ctx_depth == depth, "slide_ctx_mode='concat' needs one slide context per previous level"
+                for j in range(depth):
+                    eng.buffer(j, "F").view(B, d).copy_(cs[:, j])
+            elif data.ctx_depth > 0:
+                eng.buffer(depth - 1, "F").view(B, d).copy_(cs[:, -1])
             else:
                 eng.buffer(depth - 1, "F").zero_()
         else:
@@ -206,8 +214,11 @@ class ModelRuntime:
         eng.level_forward(depth)
         out_imp = torch.zeros(B, N, device=self.device)
         out_imp[valid] = eng.buffer(depth, "ALPHA")[:M]
-        ctx_patch = torch.zeros(B, N, D + Cc, device=self.device)
-        ctx_patch[valid] = torch.cat((eng.buffer(depth, "H").view(-1, D)[:M], eng.buffer(depth, "CN").view(-1, Cc)[:M]), dim=1)
+        ctx_patch = torch.zeros(B, N, D + Cc if lstm else D, device=self.device)
+        if lstm:
+            ctx_patch[valid] = torch.cat((eng.buffer(depth, "H").view(-1, D)[:M], eng.buffer(depth, "CN").view(-1, Cc)[:M]), dim=1)
+        else:
+            ctx_patch[valid] = eng.buffer(depth, "H").view(-1, D)[:M]
         return {"logits": eng.buffer(depth, "LOGITS").view(B, dm.nl).clone(),
                 "ctx_slide": eng.buffer(depth, "F").view(B, d).clone(),
                 "ctx_patch": ctx_patch, "importance": out_imp}

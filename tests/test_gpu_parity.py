@@ -85,7 +85,7 @@ def _level_rows(eng, l, B):
 
 
 @pytest.mark.parametrize("prec", [0, 1, 2])
-@pytest.mark.parametrize("name", ["small_full", "small_edge", "cfg1_sample", "brca_b4"])
+@pytest.mark.parametrize("name", ["small_full", "small_edge", "cfg1_sample", "brca_b4", "small_rnn", "small_concat1d"])
 def test_end2end_parity(name, prec):
     fx, ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss = _run_product(name, prec)
     eng = rt.last_engine
@@ -117,7 +117,8 @@ def test_end2end_parity(name, prec):
             sl = slice(seg[j], seg[j] + n)
             assert torch.equal(xy[sl] * ocfg.patch_size, rec.locs[j, :n]), f"level {l} slide {j}: child locations differ"
             assert rel_err(alpha[sl], rec.importance[j, :n]) < tol, f"level {l} slide {j}: importance"
-            assert rel_err(torch.cat((H[sl], Cn[sl]), 1), rec.ctx_patch[j, :n]) < tol, f"level {l} slide {j}: LSTM state"
+            state = torch.cat((H[sl], Cn[sl]), 1) if ocfg.lstm else H[sl]          # RNN variant: patch state = Z
+            assert rel_err(state, rec.ctx_patch[j, :n]) < tol, f"level {l} slide {j}: patch state"
         assert rel_err(eng.buffer(l, "LOGITS").view(B, -1).cpu(), rec.logits) < tol, f"level {l}: logits"
         assert rel_err(eng.buffer(l, "F").view(B, -1).cpu(), rec.ctx_slide) < tol, f"level {l}: slide context"
         if l < L - 1:
@@ -182,7 +183,7 @@ def test_end2end_parity(name, prec):
             break
 
 
-@pytest.mark.parametrize("name", ["small_full", "cfg1_sample"])
+@pytest.mark.parametrize("name", ["small_full", "cfg1_sample", "small_rnn", "small_concat1d"])
 def test_level_api_matches_oracle(name):
     """RecursiveModel.forward(depth, PatchBatch) on the oracle's own padded batches (reference API, padded layout)."""
     from paths_b200.data_utils.patch_batch import PatchBatch
