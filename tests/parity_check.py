@@ -1,0 +1,119 @@
+"""The parity checker shared by the GPU tests: one finished step of the CUDA path against the CPU oracle.
+Values are compared with TEACHER-FORCED indices (ours fed to the oracle) so a near-tie in importance cannot cascade;
+indices are checked as a valid top-K of the oracle's scores; the free-running oracle must pick the same patches unless its
+own scores tie within the tolerance."""
+import torch
+
+from oracle import paths_oracle as po
+from tests.common import rel_err
+
+TOL = {0: 1e-4, 1: 1e-4, 2: 2e-2}
+
+
+def _level_rows(eng, l, B):
+    M = int(eng.buffer(l, "COUNT").item())
+    seg = eng.buffer(l, "SEG")[:B + 1].tolist()
+    return M, seg
+
+
+def check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, prec, check_grads=True):
+    """Compares one finished product step (hz, loss, engine buffers, parameter .grad) with the CPU oracle."""
+    eng = rt.last_engine
+    tol = TOL[prec]
+    B, L = len(slides), cfg.num_levels
+    assert not eng.overflowed()[0]
+
+    # 1. free-running oracle: our selection must be a valid top-K of the oracle's scores
+    _, _, free = po.end2end(sd, ocfg, [s.grids for s in slides], ybin, cens, record=True)
+    forced = []
+    for l in range(L - 1):
+        M, seg = _level_rows(eng, l, B)
+        kcap = eng.buffer(l, "SEL").numel() // B
+        sel = eng.buffer(l, "SEL").view(B, kcap).cpu()
+        cnt = eng.buffer(l, "SEL_COUNT")[:B].cpu()
+        forced.append([(sel[j, :int(cnt[j])] - seg[j]).long() for j in range(B)])
+    # 2. teacher-forced oracle (our indices) for value comparisons
+    ohz, oloss, ograds, recs = po.grads(sd, ocfg, [s.grids for s in slides], ybin, cens, forced_keep=forced)
+    for l in range(L):
+        M, seg = _level_rows(eng, l, B)
+        rec = recs[l]
+        assert seg[1:] == torch.cumsum(rec.num_ims, 0).tolist(), f"level {l}: bag sizes differ"
+        xy = eng.buffer(l, "ROW_XY").view(-1, 2)[:M].cpu().long()
+        alpha = eng.buffer(l, "ALPHA")[:M].cpu()
+        H = eng.buffer(l, "H").view(-1, ocfg.patch_embed_dim)[:M].cpu()
+        Cn = eng.buffer(l, "CN").view(-1, ocfg.hierarchical_ctx_mlp_hidden_dim)[:M].cpu()
+        for j in range(B):
+            n = int(rec.num_ims[j])
+            sl = slice(seg[j], seg[j] + n)
+            assert torch.equal(xy[sl] * ocfg.patch_size, rec.locs[j, :n]), f"level {l} slide {j}: child locations differ"
+            assert rel_err(alpha[sl], rec.importance[j, :n]) < tol, f"level {l} slide {j}: importance"
+            state = torch.cat((H[sl], Cn[sl]), 1) if ocfg.lstm else H[sl]          # RNN variant: patch state = Z
+            assert rel_err(state, rec.ctx_patch[j, :n]) < tol, f"level {l} slide {j}: patch state"
+        assert rel_err(eng.buffer(l, "LOGITS").view(B, -1).cpu(), rec.logits) < tol, f"level {l}: logits"
+        assert rel_err(eng.buffer(l, "F").view(B, -1).cpu(), rec.ctx_slide) < tol, f"level {l}: slide context"
+        if l < L - 1:
+            # selection validity against the FREE-running oracle is only meaningful while the trajectories coincide;
+            # check against the teacher-forced record (same inputs as ours at this level)
+            for j in range(B):
+                n = int(rec.num_ims[j])
+                sc = rec.importance[j, :n]
+                mine = forced[l][j]
+                k = len(mine)
+                if k < n:
+                    kth = torch.sort(sc, descending=True).values[k - 1]
+                    must = set(torch.nonzero(sc > kth + tol).flatten().tolist())
+                    may = set(torch.nonzero(sc >= kth - tol).flatten().tolist())
+                    assert must <= set(mine.tolist()) <= may, f"level {l} slide {j}: not a valid top-{k}"
+                    s_m = sc[mine]
+                    assert bool((s_m[:-1] >= s_m[1:] - tol).all()), "selection must be importance-descending"
+                else:
+                    assert sorted(mine.tolist()) == list(range(n))
+    assert rel_err(hz.detach().cpu(), ohz) < tol
+    assert abs(float(loss) - float(oloss)) < tol * max(1.0, abs(float(oloss)))
+    if not check_grads:
+        return recs
+    # 3. gradients on every live parameter; None / zero pattern
+    #   fp32   : every tensor within 1e-4 of its own scale (floored at 1e-3 of the largest gradient entry; tensors of a
+    #            handful of elements -- the importance head's output bias -- are pure cancelling sums: floor 1e-2)
+    #   bf16x3 : the whole flat gradient within 1e-4 (max-norm and L2) of the gradient's scale; single tensors, whose entries
+    #            are strongly cancelling sums over patches, within 1e-2 of their own scale (split-bf16 products carry 2^-17)
+    #   bf16   : ReLU / top-K masks may flip for near-zero pre-activations; relative L2 error of the flat gradient < 5e-2
+    named = dict(model.named_parameters())
+    gmax = max(float(g.abs().max()) for g in ograds.values() if g is not None)
+    num = den = 0.0
+    worst_abs = 0.0
+    for k, og in ograds.items():
+        mine = named[k].grad
+        if og is None:
+            assert mine is None or float(mine.abs().max()) == 0.0, f"{k}: reference leaves this gradient empty"
+            continue
+        assert mine is not None, k
+        diff = (mine.detach().cpu().double() - og.double())
+        num += float((diff ** 2).sum()); den += float((og.double() ** 2).sum())
+        worst_abs = max(worst_abs, float(diff.abs().max()))
+        if prec < 2:
+            floor = (1e-3 if og.numel() > 8 else 1e-2) * gmax
+            err = float(diff.abs().max()) / max(float(og.abs().max()), floor)
+            assert err < (tol if prec == 0 else 1e-2), f"{k}: gradient error {err:.2e}"
+    gl2 = (num / den) ** 0.5
+    assert gl2 < (5e-2 if prec == 2 else 1e-4), f"flat gradient: relative L2 error {gl2:.2e}"
+    if prec < 2:
+        assert worst_abs / gmax < 1e-4, f"flat gradient: max-norm error {worst_abs / gmax:.2e}"
+    # 4. the FREE-running oracle picks the same patches as we do, unless its own scores are tied within the tolerance
+    #    at the selection boundary (torch.topk leaves tie order unspecified; we break ties towards the lowest row index)
+    for j in range(B):
+        for l in range(1, L):
+            nf, nt = int(free[l].num_ims[j]), int(recs[l].num_ims[j])
+            if nf == nt and torch.equal(free[l].locs[j, :nf], recs[l].locs[j, :nt]):
+                continue
+            n = int(free[l - 1].num_ims[j])
+            sc = torch.sort(free[l - 1].importance[j, :n], descending=True).values
+            k = ocfg.top_k_patches[l - 1]
+            assert k >= 0, f"slide {j} level {l}: selections differ although every row was kept in its original order"
+            kk = min(k, n)                                   # rows kept; children follow the importance-descending order
+            gaps = sc[:-1] - sc[1:]
+            near_tie = bool((gaps[:kk - 1] <= tol).any()) or (kk < n and bool(gaps[kk - 1] <= tol))
+            assert near_tie, f"slide {j} level {l}: selected indices differ from the oracle without a near-tie"
+            break
+
+
