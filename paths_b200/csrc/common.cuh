@@ -1,5 +1,6 @@
 // Shared device/host helpers for the PATHS B200 kernels (sm_100a only).
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -55,6 +56,40 @@ __device__ __forceinline__ const float* rowsrc_ptr(const RowSrc& s, int m, int k
   return r < 0 ? nullptr : s.p1 + (size_t)r * s.ld1 + (k - s.k0);
 }
 
+// Tensor-core operand storage of an activation: bf16 planes stacked as [2 * rows, ldp] -- rows [0, rows) hold hi = bf16(x),
+// rows [rows, 2 rows) hold lo = bf16(x - hi).  Written by the kernel that produces the activation (or by split_rows) and read
+// by TMA as 64x64 SWIZZLE_128B boxes.  `rows` is the padded capacity: live rows are followed by zero rows up to the next
+// multiple of 64 so a reduction over rows (weight gradients) may run whole 64-row blocks.
+struct Planes { __nv_bfloat16* p; int rows; int ldp; };
+inline int planes_pad_rows(int M) { return ((M + 63) / 64) * 64 + 64; }
+inline size_t planes_bytes(int M_cap, int K) { return (size_t)2 * planes_pad_rows(M_cap) * ((K + 7) / 8 * 8) * sizeof(__nv_bfloat16) + 256; }
+inline Planes planes_at(void* mem, int M_cap, int K) {
+  Planes pl;
+  pl.p = reinterpret_cast<__nv_bfloat16*>((reinterpret_cast<uintptr_t>(mem) + 255) & ~uintptr_t(255));
+  pl.rows = planes_pad_rows(M_cap); pl.ldp = (K + 7) / 8 * 8;
+  return pl;
+}
+inline Planes no_planes() { Planes pl; pl.p = nullptr; pl.rows = 0; pl.ldp = 0; return pl; }
+
+__device__ __forceinline__ void planes_store4(const Planes& pl, int m, int k, float4 v, bool want_lo) {
+  __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+  uint2 hv;
+  hv.x = *reinterpret_cast<uint32_t*>(&h0); hv.y = *reinterpret_cast<uint32_t*>(&h1);
+  *reinterpret_cast<uint2*>(pl.p + (size_t)m * pl.ldp + k) = hv;
+  if (want_lo) {
+    const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+    __nv_bfloat162 l0 = __floats2bfloat162_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2bfloat162_rn(v.z - f1.x, v.w - f1.y);
+    uint2 lv;
+    lv.x = *reinterpret_cast<uint32_t*>(&l0); lv.y = *reinterpret_cast<uint32_t*>(&l1);
+    *reinterpret_cast<uint2*>(pl.p + ((size_t)pl.rows + m) * pl.ldp + k) = lv;
+  }
+}
+// number of rows a producer must cover: live rows plus the zero rows up to the next multiple of 64
+__device__ __forceinline__ int planes_rows_to_write(const Planes& pl, int M) {
+  int Mpad = (M + 63) & ~63;
+  return Mpad > pl.rows ? pl.rows : Mpad;
+}
+
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -87,6 +122,12 @@ int gemm_nt(int prec, const RowSrc& A, const float* B, int ldb, int b_kn, float*
 // Accumulates with fp32 atomics (split over m); C must be initialised (zeroed grads).
 int gemm_tn(int prec, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev,
             int NI, int NJ, cudaStream_t st);
+
+// An activation as the contraction wrappers see it: fp32 rows (f, ld) for the SIMT mode and/or bf16 planes for the tensor-core
+// modes; col0 selects a column window of either.  A null `pl.p` in a tensor-core mode means "split f on the fly".
+struct Act { const float* f; int ld; Planes pl; int col0; };
+inline Act act(const float* f, int ld, const Planes& pl, int col0 = 0) { Act a; a.f = f; a.ld = ld; a.pl = pl; a.col0 = col0; return a; }
+inline Act act_f(const float* f, int ld) { return act(f, ld, no_planes(), 0); }
 
 // out[n] += sum_m X[m, n]
 int colsum_accum(const float* X, int ld, float* out, int M_host, const int* M_dev, int N, cudaStream_t st);

@@ -32,6 +32,11 @@ int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, i
                cudaStream_t st);
 bool gemm_tc_supported_nt(const RowSrc& A, const float* B, int ldb, int b_kn, int ldc, int N, int K);
 bool gemm_tc_supported_tn(int ldp, const RowSrc& Q, int ldc, int NI, int NJ);
+int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
+                 const int* M_dev, int N, int K, int flags, cudaStream_t st);
+int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q_col0, float* C, int ldc, int M_host, const int* M_dev, int NI,
+                 int NJ, cudaStream_t st);
+int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Planes& dst, int col0, bool want_lo, cudaStream_t st);
 size_t packed_bytes(int R, int Cc);
 int register_packed(const float* src, int R, int Cc, int ld, void* dst);
 void unregister_packed(const float* src);
@@ -52,6 +57,22 @@ int gemm_tn(int prec, const float* P, int ldp, const RowSrc& Q, float* C, int ld
   if (prec != PREC_FP32_SIMT && gemm_tc_supported_tn(ldp, Q, ldc, NI, NJ))
     return gemm_tn_tc(prec == PREC_BF16X3_TC ? 3 : 1, P, ldp, Q, C, ldc, M_host, M_dev, NI, NJ, st);
   return gemm_tn_simt(P, ldp, Q, C, ldc, M_host, M_dev, NI, NJ, st);
+}
+
+// Contractions on activations that may already exist as tensor-core planes (written by their producer kernel).
+int gemm_nt_act(int prec, const Act& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host, const int* M_dev,
+                int N, int K, int flags, cudaStream_t st) {
+  if (prec != PREC_FP32_SIMT && A.pl.p)
+    return gemm_nt_tc_p(prec == PREC_BF16X3_TC ? 3 : 1, A.pl, A.col0, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
+  PATHS_REQUIRE(A.f, "gemm_nt: activation has neither fp32 rows nor planes");
+  return gemm_nt(prec, row_src(A.f + A.col0, A.ld, K), B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
+}
+int gemm_tn_act(int prec, const Act& P, const Act& Q, const RowSrc* Qsrc, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
+                cudaStream_t st) {
+  if (prec != PREC_FP32_SIMT && P.pl.p && Q.pl.p)
+    return gemm_tn_tc_p(prec == PREC_BF16X3_TC ? 3 : 1, P.pl, P.col0, Q.pl, Q.col0, C, ldc, M_host, M_dev, NI, NJ, st);
+  PATHS_REQUIRE(P.f && (Q.f || Qsrc), "gemm_tn: activation has neither fp32 rows nor planes");
+  return gemm_tn(prec, P.f + P.col0, P.ld, Qsrc ? *Qsrc : row_src(Q.f + Q.col0, Q.ld, NJ), C, ldc, M_host, M_dev, NI, NJ, st);
 }
 
 namespace {
@@ -75,6 +96,7 @@ struct Level {
   LayerBuf layer[PATHS_MAX_LAYERS];
   float *xhf, *rsf, *z, *F, *logits, *dlogits, *dHrow, *dCrow;
   float *dFc;                        // slide_ctx_mode "concat": d loss / d F_l written by the last level's head backward
+  Planes AxhP, CnP, YP;              // tensor-core operand planes written by the producers: [x || h_parent], c', Y
 };
 
 struct LayerP { const float *Wqkv, *bqkv, *Wo, *bo, *bcross, *W1, *b1, *W2, *b2, *n1w, *n1b, *n2w, *n2b, *n3w, *n3b; };
@@ -101,6 +123,7 @@ struct paths_engine {
   float *dY, *dP, *dG, *dCn, *dHc, *dCc, *dUV;          // backward, row-shaped
   float *ga, *gb, *gO, *gt, *dqkv, *dHf, *Dvec;         // backward, token-shaped
   float *dF, *dz, *dy3s;                                 // [B, d]
+  Planes dGP, dPP, dUVP;                                 // gradient planes written by the pointwise backward kernels
   float *hazards, *loss, *loss_per;
   int *overflow, *slide_cnt, *slide_fb;
   const int* slide_ids;
@@ -157,6 +180,14 @@ size_t carve(paths_engine* e, char* base) {
     v.F = b.take<float>((size_t)B * d); v.logits = b.take<float>((size_t)B * dm.nl); v.dlogits = b.take<float>((size_t)B * dm.nl);
     v.dHrow = b.take<float>(cap * D); v.dCrow = b.take<float>(cap * C);
     v.dFc = b.take<float>((size_t)B * d);
+    if (dm.lstm) {
+      v.AxhP = planes_at(b.take<char>(planes_bytes(v.cap, 2 * D)), v.cap, 2 * D);
+      v.CnP = planes_at(b.take<char>(planes_bytes(v.cap, C)), v.cap, C);
+      v.YP = planes_at(b.take<char>(planes_bytes(v.cap, D)), v.cap, D);
+      if (!base) { v.AxhP.p = nullptr; v.CnP.p = nullptr; v.YP.p = nullptr; }
+    } else {
+      v.AxhP = v.CnP = v.YP = no_planes();
+    }
   }
   e->maxcap = maxcap; e->maxtok = maxcap + B;
   const size_t mc = maxcap, mt = (size_t)maxcap + B;
@@ -164,6 +195,13 @@ size_t carve(paths_engine* e, char* base) {
   e->dY = b.take<float>(mc * D); e->dP = b.take<float>(mc * D); e->dG = b.take<float>(dm.lstm ? mc * (3 * C + D) : 4);
   e->dCn = b.take<float>(mc * C); e->dHc = b.take<float>(mc * D); e->dCc = b.take<float>(mc * C);
   e->dUV = b.take<float>(mc * (I + d));
+  if (dm.lstm) {
+    e->dGP = planes_at(b.take<char>(planes_bytes(maxcap, 3 * C + D)), maxcap, 3 * C + D);
+    e->dPP = planes_at(b.take<char>(planes_bytes(maxcap, D)), maxcap, D);
+    e->dUVP = planes_at(b.take<char>(planes_bytes(maxcap, I + d)), maxcap, I + d);
+  } else {
+    e->dGP = e->dPP = e->dUVP = no_planes();
+  }
   e->ga = b.take<float>(mt * d); e->gb = b.take<float>(mt * d); e->gO = b.take<float>(mt * d); e->gt = b.take<float>(mt * d);
   e->dqkv = b.take<float>(mt * 3 * d); e->dHf = b.take<float>(mt * F); e->Dvec = b.take<float>(mt * dm.heads);
   e->dF = b.take<float>((size_t)B * d); e->dz = b.take<float>((size_t)B * d); e->dy3s = b.take<float>((size_t)B * d);
@@ -239,6 +277,11 @@ void bind(Params& P, const float* base, const int64_t* off, const paths_dims_t& 
   }
 }
 
+// Producer-written operand planes need every contraction extent of the LSTM block to satisfy the TMA/UMMA alignment rules.
+inline bool planes_mode(const paths_dims_t& dm) {
+  return dm.precision != PREC_FP32_SIMT && dm.lstm && dm.D % 8 == 0 && dm.C % 8 == 0 && (dm.I + dm.d) % 8 == 0;
+}
+
 struct ProfScope {
   paths_engine* e; int tag; cudaStream_t st; bool on;
   ProfScope(paths_engine* e_, int tag_, cudaStream_t st_) : e(e_), tag(tag_), st(st_), on(e_->prof_on) {
@@ -270,18 +313,26 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
 
   const bool has_parent = l > 0;
   if (dm.lstm) {
-    // ---- LSTM cell step for every patch (interface.py:49-56); [x || h_parent] is gathered inside the GEMM loader
+    // ---- LSTM cell step for every patch (interface.py:49-56).  In the tensor-core modes every contraction operand of this
+    // block lives as bf16 planes written by its producer: [x || h_parent] by one split pass that also performs the parent
+    // gather (kept for the weight gradient), c' and Y by the gate kernels.
+    const bool pl = planes_mode(dm);
+    const int lo = prec == PREC_BF16X3_TC ? 1 : 0;
+    const int Kx = has_parent ? 2 * D : D;
     RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
+    if (pl) RUN(split_rows(Axh, M, Md, Kx, v.AxhP, 0, lo != 0, st));
     {
       ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
-      RUN(gemm_nt(prec, Axh, e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, has_parent ? 2 * D : D, 0, st));
+      if (pl) RUN(gemm_nt_act(prec, act(nullptr, 0, v.AxhP), e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, Kx, 0, st));
+      else RUN(gemm_nt(prec, Axh, e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, Kx, 0, st));
     }
-    RUN(lstm_point1_fwd(v.G, has_parent ? e->lv[l - 1].Cn : nullptr, has_parent ? v.row_parent : nullptr, v.Cn, D, C, M, Md, st));
-    RUN(gemm_nt(prec, row_src(v.Cn, C, C), e->P.Wmo, C, 0, v.Pt, D, e->P.bmo, M, Md, D, C, 0, st));
-    RUN(lstm_point2_fwd(v.Pt, v.G, v.X, v.H, v.Y, D, C, M, Md, st));
+    RUN(lstm_point1_fwd(v.G, has_parent ? e->lv[l - 1].Cn : nullptr, has_parent ? v.row_parent : nullptr, v.Cn, pl ? v.CnP : no_planes(), lo,
+                        D, C, M, Md, st));
+    RUN(gemm_nt_act(prec, act(v.Cn, C, pl ? v.CnP : no_planes()), e->P.Wmo, C, 0, v.Pt, D, e->P.bmo, M, Md, D, C, 0, st));
+    RUN(lstm_point2_fwd(v.Pt, v.G, v.X, v.H, pl ? nullptr : v.Y, pl ? v.YP : no_planes(), lo, D, C, M, Md, st));
 
     // ---- importance + token projection share one contraction over Y (paths.py:95-98, aggregator.py:48)
-    RUN(gemm_nt(prec, row_src(v.Y, D, D), p.Wuv, D, 0, v.UV, I + d, nullptr, M, Md, I + d, D, 0, st));
+    RUN(gemm_nt_act(prec, act(v.Y, D, pl ? v.YP : no_planes()), p.Wuv, D, 0, v.UV, I + d, nullptr, M, Md, I + d, D, 0, st));
     RUN(imp_tok_fwd(v.UV, p.b1, p.w2, p.b2, p.bin, e->div, v.row_slide, v.row_xy, v.seg, v.alpha, v.tok, I, d, dm.imp_mul,
                     dm.pe_mode, 0, M, Md, st));
   } else {
@@ -419,7 +470,8 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   if (!dm.lstm) {
     // ---- RNN variant: tok = Z.W_in^T + b_in + PE;  Z = alpha X + hctx;  hctx = Wh2 relu(Wh0 Z_parent + bh0) + bh2
     const bool hctx = has_parent && dm.hier_ctx;
-    RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, e->dUV, W_(g.b1), W_(g.w2), W_(g.b2), W_(g.bin), I, d, dm.imp_mul, 2, M, Md, st));
+    RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, e->dUV, no_planes(), 0, W_(g.b1), W_(g.w2), W_(g.b2), W_(g.bin), I, d, dm.imp_mul, 2,
+                    M, Md, st));
     RUN(gemm_nt(prec, row_src(e->dUV + I, I + d, d), p.Wuv + (size_t)I * D, D, 1, e->dY, D, nullptr, M, Md, D, d, 0, st));   // dZ
     RUN(gemm_tn(prec, e->dUV + I, I + d, row_src(v.H, D, D), W_(g.Wuv) + (size_t)I * D, D, M, Md, d, D, st));
     if (has_children && dm.hier_ctx)
@@ -438,29 +490,36 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
     }
     return 0;
   }
-  RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, e->dUV, W_(g.b1), W_(g.w2), W_(g.b2), W_(g.bin), I, d, dm.imp_mul, 0, M, Md, st));
-  RUN(gemm_nt(prec, row_src(e->dUV, I + d, I + d), p.Wuv, D, 1, e->dY, D, nullptr, M, Md, D, I + d, 0, st));
-  RUN(gemm_tn(prec, e->dUV, I + d, row_src(v.Y, D, D), W_(g.Wuv), D, M, Md, I + d, D, st));
+  const bool pl = planes_mode(dm);
+  const int lo = prec == PREC_BF16X3_TC ? 1 : 0;
+  const Planes none = no_planes();
+  RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, pl ? nullptr : e->dUV, pl ? e->dUVP : none, lo, W_(g.b1), W_(g.w2), W_(g.b2),
+                  W_(g.bin), I, d, dm.imp_mul, 0, M, Md, st));
+  const Act aUV = act(e->dUV, I + d, pl ? e->dUVP : none), aY = act(v.Y, D, pl ? v.YP : none);
+  RUN(gemm_nt_act(prec, aUV, p.Wuv, D, 1, e->dY, D, nullptr, M, Md, D, I + d, 0, st));
+  RUN(gemm_tn_act(prec, aUV, aY, nullptr, W_(g.Wuv), D, M, Md, I + d, D, st));
   // ---- state gradients arriving from the children of this level's selected rows
   if (has_children)
     RUN(parent_sum(v.child_of, e->lv[l + 1].dHrow, e->lv[l + 1].dCrow, e->dHc, e->dCc, D, C, M, Md, st));
-  // ---- LSTM cell
-  RUN(lstm_point2_bwd(e->dY, has_children ? e->dHc : nullptr, v.Pt, v.G, e->dP, e->dG, D, C, M, Md, st));
-  RUN(gemm_nt(prec, row_src(e->dP, D, D), e->P.Wmo, C, 1, e->dCn, C, nullptr, M, Md, C, D, 0, st));
-  RUN(gemm_tn(prec, e->dP, D, row_src(v.Cn, C, C), W_(e->Gr.Wmo), C, M, Md, D, C, st));
-  RUN(colsum_accum(e->dP, D, W_(e->Gr.bmo), M, Md, D, st));
+  // ---- LSTM cell (the pointwise kernels also accumulate the bias gradients of mem_to_out and of the four gates)
+  RUN(lstm_point2_bwd(e->dY, has_children ? e->dHc : nullptr, v.Pt, v.G, pl ? nullptr : e->dP, pl ? e->dPP : none, pl ? nullptr : e->dG,
+                      pl ? e->dGP : none, W_(e->Gr.bmo), W_(e->Gr.bg) + 3 * C, lo, D, C, M, Md, st));
+  const Act aP = act(e->dP, D, pl ? e->dPP : none), aCn = act(v.Cn, C, pl ? v.CnP : none);
+  RUN(gemm_nt_act(prec, aP, e->P.Wmo, C, 1, e->dCn, C, nullptr, M, Md, C, D, 0, st));
+  RUN(gemm_tn_act(prec, aP, aCn, nullptr, W_(e->Gr.Wmo), C, M, Md, D, C, st));
   RUN(lstm_point1_bwd(e->dCn, has_children ? e->dCc : nullptr, v.G, has_parent ? e->lv[l - 1].Cn : nullptr,
-                      has_parent ? v.row_parent : nullptr, e->dG, has_parent ? v.dCrow : nullptr, D, C, M, Md, st));
+                      has_parent ? v.row_parent : nullptr, pl ? nullptr : e->dG, pl ? e->dGP : none, has_parent ? v.dCrow : nullptr,
+                      W_(e->Gr.bg), lo, D, C, M, Md, st));
+  const Act aG = act(e->dG, ldg, pl ? e->dGP : none);
   if (has_parent) {
     ProfScope ps(e, PATHS_PROF_GATES_DH, st);
-    RUN(gemm_nt(prec, row_src(e->dG, ldg, ldg), e->P.Wg + D, 2 * D, 1, v.dHrow, D, nullptr, M, Md, D, ldg, 0, st));
+    RUN(gemm_nt_act(prec, aG, e->P.Wg + D, 2 * D, 1, v.dHrow, D, nullptr, M, Md, D, ldg, 0, st));
   }
   RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
   {
     ProfScope ps(e, PATHS_PROF_GATES_DW, st);
-    RUN(gemm_tn(prec, e->dG, ldg, Axh, W_(e->Gr.Wg), 2 * D, M, Md, ldg, has_parent ? 2 * D : D, st));
+    RUN(gemm_tn_act(prec, aG, act(nullptr, 0, pl ? v.AxhP : none), &Axh, W_(e->Gr.Wg), 2 * D, M, Md, ldg, has_parent ? 2 * D : D, st));
   }
-  RUN(colsum_accum(e->dG, ldg, W_(e->Gr.bg), M, Md, ldg, st));
   return 0;
 }
 

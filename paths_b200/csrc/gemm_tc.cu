@@ -127,20 +127,6 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int elem /* 0..63 */) {
   return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((elem >> 3) ^ (row & 7))) << 4) + (elem & 7) * 2);
 }
 
-__device__ __forceinline__ void split_store(uint8_t* hi_plane, uint8_t* lo_plane, uint32_t off, float4 v, bool want_lo) {
-  __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
-  uint2 hv;
-  hv.x = *reinterpret_cast<uint32_t*>(&h0); hv.y = *reinterpret_cast<uint32_t*>(&h1);
-  *reinterpret_cast<uint2*>(hi_plane + off) = hv;
-  if (want_lo) {
-    const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
-    __nv_bfloat162 l0 = __floats2bfloat162_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2bfloat162_rn(v.z - f1.x, v.w - f1.y);
-    uint2 lv;
-    lv.x = *reinterpret_cast<uint32_t*>(&l0); lv.y = *reinterpret_cast<uint32_t*>(&l1);
-    *reinterpret_cast<uint2*>(lo_plane + off) = lv;
-  }
-}
-
 template <int BN, int NP>
 struct Cfg {
   static constexpr int A_PLANE = BM * BK * 2;
@@ -168,22 +154,19 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int warp, int 
 // =================================================================================================== split kernel
 // fp32 rows (gathered / concatenated through RowSrc) -> bf16 planes stacked as [2 * plane_rows, ldp] (hi rows first).
 // Rows [M, round_up(M, 64)) are zero-filled so a reduction over rows (TN) may run whole 64-row blocks.
-__global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host, const int* __restrict__ M_dev, int K,
-                                                           __nv_bfloat16* __restrict__ planes, int plane_rows, int ldp, int want_lo) {
+__global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host, const int* __restrict__ M_dev, int K, Planes dst, int col0,
+                                                           int want_lo) {
   const int M = M_dev ? *M_dev : M_host;
-  int Mpad = (M + 63) & ~63;
-  if (Mpad > plane_rows) Mpad = plane_rows;
+  const int Mpad = planes_rows_to_write(dst, M);
   const int lane = threadIdx.x & 31;
   for (int m = blockIdx.x * 8 + (threadIdx.x >> 5); m < Mpad; m += gridDim.x * 8) {
-    uint8_t* hi = reinterpret_cast<uint8_t*>(planes + (size_t)m * ldp);
-    uint8_t* lo = reinterpret_cast<uint8_t*>(planes + ((size_t)plane_rows + m) * ldp);
     for (int k = lane * 4; k < K; k += 128) {
       float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
       if (m < M) {
         const float* p = rowsrc_ptr(A, m, k);
         if (p) x = __ldg(reinterpret_cast<const float4*>(p));
       }
-      split_store(hi, lo, (uint32_t)k * 2, x, want_lo != 0);
+      planes_store4(dst, m, col0 + k, x, want_lo != 0);
     }
   }
 }
@@ -433,6 +416,9 @@ int set_smem(Kern kern, int bytes) {
   return 0;
 }
 
+}  // namespace
+int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Planes& dst, int col0, bool want_lo, cudaStream_t st);
+namespace {
 // activation planes: scratch provided by the engine (or by the stand-alone entry points)
 struct Scratch { void* p[2]; size_t bytes[2]; } g_scratch = {{nullptr, nullptr}, {0, 0}};
 
@@ -466,22 +452,13 @@ int cached_map(const CUtensorMap** out, const void* ptr, int rows, int cols, int
   return 0;
 }
 
-inline int pad_rows(int M) { return ((M + 63) / 64) * 64 + 64; }
-
-// splits A (fp32, RowSrc) into scratch `which`; returns the tensor map and operand record
-int split_to_scratch(int which, const RowSrc& A, int M_host, const int* M_dev, int K, bool want_lo, const CUtensorMap** map, Operand* op,
-                     cudaStream_t st) {
-  const int rows = pad_rows(M_host), ldp = (K + 7) / 8 * 8;
-  const size_t need = (size_t)2 * rows * ldp * sizeof(__nv_bfloat16);
+// splits A (fp32, RowSrc) into scratch `which`; returns the planes record
+int split_to_scratch(int which, const RowSrc& A, int M_host, const int* M_dev, int K, bool want_lo, Planes* out, cudaStream_t st) {
+  const size_t need = planes_bytes(M_host, K);
   PATHS_REQUIRE(g_scratch.p[which] && need <= g_scratch.bytes[which], "tensor-core scratch %d too small: need %zu bytes, have %zu", which,
                 need, g_scratch.bytes[which]);
-  __nv_bfloat16* planes = reinterpret_cast<__nv_bfloat16*>(g_scratch.p[which]);
-  int g = (rows + 7) / 8; if (g > 16 * kNumSMs) g = 16 * kNumSMs;
-  split_planes_kernel<<<g, 256, 0, st>>>(A, M_host, M_dev, K, planes, rows, ldp, want_lo ? 1 : 0);
-  PATHS_LAUNCH_CK();
-  if (int r = cached_map(map, planes, 2 * rows, K, ldp)) return r;
-  op->row0 = 0; op->col0 = 0; op->plane_rows = rows;
-  return 0;
+  *out = planes_at(g_scratch.p[which], M_host, K);
+  return split_rows(A, M_host, M_dev, K, *out, 0, want_lo, st);
 }
 
 template <int BN, int NP, bool A_MN, bool B_MN, bool ATOMIC>
@@ -561,10 +538,21 @@ bool gemm_tc_supported_tn(int ldp, const RowSrc& Q, int ldc, int NI, int NJ) {
 void set_tc_scratch(void* a, size_t a_bytes, void* b, size_t b_bytes) {
   g_scratch.p[0] = a; g_scratch.bytes[0] = a_bytes; g_scratch.p[1] = b; g_scratch.bytes[1] = b_bytes;
 }
-size_t tc_scratch_bytes(int rows, int cols) { return (size_t)2 * pad_rows(rows) * ((cols + 7) / 8 * 8) * sizeof(__nv_bfloat16) + 256; }
+size_t tc_scratch_bytes(int rows, int cols) { return planes_bytes(rows, cols) + 256; }
 
-int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
-               const int* M_dev, int N, int K, int flags, cudaStream_t st) {
+int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Planes& dst, int col0, bool want_lo, cudaStream_t st) {
+  PATHS_REQUIRE(dst.p && K % 4 == 0 && col0 % 4 == 0 && col0 + K <= dst.ldp, "split_rows: bad destination window (col0 %d, K %d, ldp %d)", col0,
+                K, dst.ldp);
+  if (M_host <= 0) return 0;
+  int g = (planes_pad_rows(M_host) + 7) / 8; if (g > 16 * kNumSMs) g = 16 * kNumSMs;
+  split_planes_kernel<<<g, 256, 0, st>>>(A, M_host, M_dev, K, dst, col0, want_lo ? 1 : 0);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+
+// C[M,N] (+)= act(A . B^T + bias), A given as planes (columns [a_col0, a_col0 + K))
+int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
+                 const int* M_dev, int N, int K, int flags, cudaStream_t st) {
   if (M_host <= 0 || N <= 0) return 0;
   const Packed* pk; int r0, c0;
   {
@@ -572,8 +560,10 @@ int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, f
     pk = find_packed(B, ldb, &r0, &c0);
   }
   PATHS_REQUIRE(pk, "gemm_nt_tc: weight matrix was not registered for the tensor-core path");
-  const CUtensorMap* ma; Operand oa;
-  if (int r = split_to_scratch(0, A, M_host, M_dev, K, passes == 3, &ma, &oa, st)) return r;
+  PATHS_REQUIRE(A.p && a_col0 % 8 == 0 && M_host <= A.rows, "gemm_nt_tc: bad activation planes");
+  const CUtensorMap* ma;
+  if (int r = cached_map(&ma, A.p, 2 * A.rows, a_col0 + K, A.ldp)) return r;
+  Operand oa; oa.row0 = 0; oa.col0 = a_col0; oa.plane_rows = A.rows;
   Operand ob; ob.row0 = r0; ob.col0 = c0; ob.plane_rows = pk->R;
   const bool big = N > 128;
 #define NT_CASE(BN_, NP_, MN_) \
@@ -589,12 +579,25 @@ int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, f
   return 0;
 }
 
-int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
-               cudaStream_t st) {
+int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
+               const int* M_dev, int N, int K, int flags, cudaStream_t st) {
+  if (M_host <= 0 || N <= 0) return 0;
+  Planes pa;
+  if (int r = split_to_scratch(0, A, M_host, M_dev, K, passes == 3, &pa, st)) return r;
+  return gemm_nt_tc_p(passes, pa, 0, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
+}
+
+// C[NI,NJ] += P^T . Q, both operands as planes (column windows p_col0 / q_col0)
+int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q_col0, float* C, int ldc, int M_host, const int* M_dev, int NI,
+                 int NJ, cudaStream_t st) {
   if (M_host <= 0 || NI <= 0 || NJ <= 0) return 0;
-  const CUtensorMap *ma, *mb; Operand oa, ob;
-  if (int r = split_to_scratch(0, row_src(P, ldp, NI), M_host, M_dev, NI, passes == 3, &ma, &oa, st)) return r;
-  if (int r = split_to_scratch(1, Q, M_host, M_dev, NJ, passes == 3, &mb, &ob, st)) return r;
+  PATHS_REQUIRE(P.p && Q.p && p_col0 % 8 == 0 && q_col0 % 8 == 0 && M_host <= P.rows && M_host <= Q.rows, "gemm_tn_tc: bad activation planes");
+  const CUtensorMap *ma, *mb;
+  if (int r = cached_map(&ma, P.p, 2 * P.rows, p_col0 + NI, P.ldp)) return r;
+  if (int r = cached_map(&mb, Q.p, 2 * Q.rows, q_col0 + NJ, Q.ldp)) return r;
+  Operand oa, ob;
+  oa.row0 = 0; oa.col0 = p_col0; oa.plane_rows = P.rows;
+  ob.row0 = 0; ob.col0 = q_col0; ob.plane_rows = Q.rows;
   const bool big = NJ > 128;
   const int BN = big ? 256 : 128;
   const int tiles = ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
@@ -608,6 +611,15 @@ int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, i
   else             { if (big) TN_CASE(256, 1); else TN_CASE(128, 1); }
 #undef TN_CASE
   return 0;
+}
+
+int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
+               cudaStream_t st) {
+  if (M_host <= 0 || NI <= 0 || NJ <= 0) return 0;
+  Planes pp, pq;
+  if (int r = split_to_scratch(0, row_src(P, ldp, NI), M_host, M_dev, NI, passes == 3, &pp, st)) return r;
+  if (int r = split_to_scratch(1, Q, M_host, M_dev, NJ, passes == 3, &pq, st)) return r;
+  return gemm_tn_tc_p(passes, pp, 0, pq, 0, C, ldc, M_host, M_dev, NI, NJ, st);
 }
 
 }  // namespace paths

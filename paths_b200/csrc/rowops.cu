@@ -36,82 +36,166 @@ __global__ void __launch_bounds__(TPB) gather_rows_kernel(const float* const* __
 
 // ---------------------------------------------------------------------------------------------------------
 // LSTM cell, model/interface.py:49-56.  G holds the pre-activations [f | r | m | o] (+bias) of one row.
+// Every kernel below can emit its outputs as fp32 rows (SIMT mode / pointwise consumers) and/or as bf16 (hi, lo) planes
+// (the operand format of the tensor-core contractions), so no separate split pass over the activations is needed.
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+
 __global__ void __launch_bounds__(TPB) lstm_point1_fwd_kernel(float* __restrict__ G, const float* __restrict__ Cprev,
-                                                              const int* __restrict__ parent, float* __restrict__ Cn,
+                                                              const int* __restrict__ parent, float* __restrict__ Cn, Planes CnP, int want_lo,
                                                               int D, int C, int M_host, const int* M_dev) {
   const int M = row_count(M_host, M_dev);
   const int ldg = 3 * C + D;
-  ROW_LOOP(m, M) {
+  const int Mw = CnP.p ? planes_rows_to_write(CnP, M) : M;
+  ROW_LOOP(m, Mw) {
+    if (m >= M) {                                            // zero rows behind the live ones (planes only)
+      for (int c4 = lane; c4 < C / 4; c4 += 32) planes_store4(CnP, m, 4 * c4, make_float4(0.f, 0.f, 0.f, 0.f), want_lo);
+      continue;
+    }
     float* g = G + (size_t)m * ldg;
     const int p = parent ? parent[m] : -1;
     const float* cp = (Cprev && p >= 0) ? Cprev + (size_t)p * C : nullptr;
-    for (int c = lane; c < C; c += 32) {
-      const float f = sigmoidf_(g[c]), r = sigmoidf_(g[C + c]), mm = tanhf(g[2 * C + c]);
-      g[c] = f; g[C + c] = r; g[2 * C + c] = mm;
-      const float cprev = cp ? cp[c] : 0.f;
-      Cn[(size_t)m * C + c] = cprev * f + r * mm;
+    for (int c4 = lane; c4 < C / 4; c4 += 32) {
+      const int c = 4 * c4;
+      float4 f = ld4(g + c), r = ld4(g + C + c), mm = ld4(g + 2 * C + c);
+      const float4 cprev = cp ? ld4(cp + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      f.x = sigmoidf_(f.x); f.y = sigmoidf_(f.y); f.z = sigmoidf_(f.z); f.w = sigmoidf_(f.w);
+      r.x = sigmoidf_(r.x); r.y = sigmoidf_(r.y); r.z = sigmoidf_(r.z); r.w = sigmoidf_(r.w);
+      mm.x = tanhf(mm.x); mm.y = tanhf(mm.y); mm.z = tanhf(mm.z); mm.w = tanhf(mm.w);
+      st4(g + c, f); st4(g + C + c, r); st4(g + 2 * C + c, mm);
+      const float4 cn = make_float4(cprev.x * f.x + r.x * mm.x, cprev.y * f.y + r.y * mm.y, cprev.z * f.z + r.z * mm.z,
+                                    cprev.w * f.w + r.w * mm.w);
+      st4(Cn + (size_t)m * C + c, cn);
+      if (CnP.p) planes_store4(CnP, m, c, cn, want_lo);
     }
-    for (int j = lane; j < D; j += 32) g[3 * C + j] = sigmoidf_(g[3 * C + j]);
+    for (int j4 = lane; j4 < D / 4; j4 += 32) {
+      float4 o = ld4(g + 3 * C + 4 * j4);
+      o.x = sigmoidf_(o.x); o.y = sigmoidf_(o.y); o.z = sigmoidf_(o.z); o.w = sigmoidf_(o.w);
+      st4(g + 3 * C + 4 * j4, o);
+    }
   }
 }
 
 // t = tanh(P), h' = o * t, Y = X + h'                       (interface.py:56, paths.py:89)
 __global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(float* __restrict__ Pt, const float* __restrict__ G,
                                                               const float* __restrict__ X, float* __restrict__ H,
-                                                              float* __restrict__ Y, int D, int C, int M_host, const int* M_dev) {
-  const int M = row_count(M_host, M_dev);
-  const int ldg = 3 * C + D;
-  ROW_LOOP(m, M) {
-    for (int j = lane; j < D; j += 32) {
-      const float t = tanhf(Pt[(size_t)m * D + j]);
-      Pt[(size_t)m * D + j] = t;
-      const float h = G[(size_t)m * ldg + 3 * C + j] * t;
-      H[(size_t)m * D + j] = h;
-      Y[(size_t)m * D + j] = X[(size_t)m * D + j] + h;
-    }
-  }
-}
-
-// dH = dY + dHc;  do = dH*t, dP = dH*o*(1-t^2), dGo = do*o*(1-o)
-__global__ void __launch_bounds__(TPB) lstm_point2_bwd_kernel(const float* __restrict__ dY, const float* __restrict__ dHc,
-                                                              const float* __restrict__ Pt, const float* __restrict__ G,
-                                                              float* __restrict__ dP, float* __restrict__ dG, int D, int C,
-                                                              int M_host, const int* M_dev) {
-  const int M = row_count(M_host, M_dev);
-  const int ldg = 3 * C + D;
-  ROW_LOOP(m, M) {
-    for (int j = lane; j < D; j += 32) {
-      float dh = dY ? dY[(size_t)m * D + j] : 0.f;
-      if (dHc) dh += dHc[(size_t)m * D + j];
-      const float t = Pt[(size_t)m * D + j], o = G[(size_t)m * ldg + 3 * C + j];
-      dP[(size_t)m * D + j] = dh * o * (1.f - t * t);
-      dG[(size_t)m * ldg + 3 * C + j] = dh * t * o * (1.f - o);
-    }
-  }
-}
-
-// dc' = dCn + dCc;  df, dr, dm -> dG[:, :3C];  dCrow = dc' * f (gradient w.r.t. the inherited c of this row)
-__global__ void __launch_bounds__(TPB) lstm_point1_bwd_kernel(const float* __restrict__ dCn, const float* __restrict__ dCc,
-                                                              const float* __restrict__ G, const float* __restrict__ Cprev,
-                                                              const int* __restrict__ parent, float* __restrict__ dG,
-                                                              float* __restrict__ dCrow, int D, int C, int M_host,
+                                                              float* __restrict__ Y, Planes YP, int want_lo, int D, int C, int M_host,
                                                               const int* M_dev) {
   const int M = row_count(M_host, M_dev);
   const int ldg = 3 * C + D;
-  ROW_LOOP(m, M) {
-    const float* g = G + (size_t)m * ldg;
-    float* dg = dG + (size_t)m * ldg;
-    const int p = parent ? parent[m] : -1;
-    const float* cp = (Cprev && p >= 0) ? Cprev + (size_t)p * C : nullptr;
-    for (int c = lane; c < C; c += 32) {
-      float dc = dCn[(size_t)m * C + c];
-      if (dCc) dc += dCc[(size_t)m * C + c];
-      const float f = g[c], r = g[C + c], mm = g[2 * C + c];
-      const float cprev = cp ? cp[c] : 0.f;
-      dg[c] = dc * cprev * f * (1.f - f);
-      dg[C + c] = dc * mm * r * (1.f - r);
-      dg[2 * C + c] = dc * r * (1.f - mm * mm);
-      if (dCrow) dCrow[(size_t)m * C + c] = dc * f;
+  const int Mw = YP.p ? planes_rows_to_write(YP, M) : M;
+  ROW_LOOP(m, Mw) {
+    for (int j4 = lane; j4 < D / 4; j4 += 32) {
+      const int j = 4 * j4;
+      if (m >= M) { planes_store4(YP, m, j, make_float4(0.f, 0.f, 0.f, 0.f), want_lo); continue; }
+      float4 t = ld4(Pt + (size_t)m * D + j);
+      t.x = tanhf(t.x); t.y = tanhf(t.y); t.z = tanhf(t.z); t.w = tanhf(t.w);
+      st4(Pt + (size_t)m * D + j, t);
+      const float4 o = ld4(G + (size_t)m * ldg + 3 * C + j), x = ld4(X + (size_t)m * D + j);
+      const float4 h = make_float4(o.x * t.x, o.y * t.y, o.z * t.z, o.w * t.w);
+      st4(H + (size_t)m * D + j, h);
+      const float4 y = make_float4(x.x + h.x, x.y + h.y, x.z + h.z, x.w + h.w);
+      if (Y) st4(Y + (size_t)m * D + j, y);
+      if (YP.p) planes_store4(YP, m, j, y, want_lo);
+    }
+  }
+}
+
+// dH = dY + dHc;  dP = dH*o*(1-t^2), dGo = dH*t*o*(1-o);  column sums of both (the bias gradients of mem_to_out and of the
+// output gate) are accumulated on the way.  Threads own float4 column groups, blocks stride over rows.
+constexpr int CG = 4;                                     // float4 column groups per thread: D <= 4 * 4 * 256
+__global__ void __launch_bounds__(256) lstm_point2_bwd_kernel(const float* __restrict__ dY, const float* __restrict__ dHc,
+                                                              const float* __restrict__ Pt, const float* __restrict__ G,
+                                                              float* __restrict__ dP, Planes dPP, float* __restrict__ dG, Planes dGP,
+                                                              float* __restrict__ db_mo, float* __restrict__ db_o, int want_lo, int D, int C,
+                                                              int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ldg = 3 * C + D;
+  const int Mw = dPP.p ? planes_rows_to_write(dPP, M) : M;
+  float4 aP[CG], aG[CG];
+#pragma unroll
+  for (int q = 0; q < CG; ++q) aP[q] = aG[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int m = blockIdx.x; m < Mw; m += gridDim.x) {
+#pragma unroll
+    for (int q = 0; q < CG; ++q) {
+      const int j = 4 * (threadIdx.x + 256 * q);
+      if (j >= D) break;
+      float4 vp = make_float4(0.f, 0.f, 0.f, 0.f), vg = vp;
+      if (m < M) {
+        float4 dh = dY ? ld4(dY + (size_t)m * D + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (dHc) { const float4 e = ld4(dHc + (size_t)m * D + j); dh.x += e.x; dh.y += e.y; dh.z += e.z; dh.w += e.w; }
+        const float4 t = ld4(Pt + (size_t)m * D + j), o = ld4(G + (size_t)m * ldg + 3 * C + j);
+        vp = make_float4(dh.x * o.x * (1.f - t.x * t.x), dh.y * o.y * (1.f - t.y * t.y), dh.z * o.z * (1.f - t.z * t.z),
+                         dh.w * o.w * (1.f - t.w * t.w));
+        vg = make_float4(dh.x * t.x * o.x * (1.f - o.x), dh.y * t.y * o.y * (1.f - o.y), dh.z * t.z * o.z * (1.f - o.z),
+                         dh.w * t.w * o.w * (1.f - o.w));
+        aP[q].x += vp.x; aP[q].y += vp.y; aP[q].z += vp.z; aP[q].w += vp.w;
+        aG[q].x += vg.x; aG[q].y += vg.y; aG[q].z += vg.z; aG[q].w += vg.w;
+        if (dP) st4(dP + (size_t)m * D + j, vp);
+        if (dG) st4(dG + (size_t)m * ldg + 3 * C + j, vg);
+      }
+      if (dPP.p) planes_store4(dPP, m, j, vp, want_lo);
+      if (dGP.p) planes_store4(dGP, m, 3 * C + j, vg, want_lo);
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < CG; ++q) {
+    const int j = 4 * (threadIdx.x + 256 * q);
+    if (j >= D) break;
+    atomicAdd(db_mo + j, aP[q].x); atomicAdd(db_mo + j + 1, aP[q].y); atomicAdd(db_mo + j + 2, aP[q].z); atomicAdd(db_mo + j + 3, aP[q].w);
+    atomicAdd(db_o + j, aG[q].x); atomicAdd(db_o + j + 1, aG[q].y); atomicAdd(db_o + j + 2, aG[q].z); atomicAdd(db_o + j + 3, aG[q].w);
+  }
+}
+
+// dc' = dCn + dCc;  df, dr, dm -> dG[:, :3C] (+ their column sums -> gate bias gradients);  dCrow = dc' * f (gradient w.r.t. the
+// inherited c of this row).  A block covers 256 / (C/4) rows at a time; thread = (row slot, float4 column group).
+__global__ void __launch_bounds__(256) lstm_point1_bwd_kernel(const float* __restrict__ dCn, const float* __restrict__ dCc,
+                                                              const float* __restrict__ G, const float* __restrict__ Cprev,
+                                                              const int* __restrict__ parent, float* __restrict__ dG, Planes dGP,
+                                                              float* __restrict__ dCrow, float* __restrict__ db_g, int want_lo, int D, int C,
+                                                              int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ldg = 3 * C + D;
+  const int G4 = C / 4, R = 256 / G4;
+  const int c4 = threadIdx.x % G4, sub = threadIdx.x / G4;
+  const int c = 4 * c4;
+  const int Mw = dGP.p ? planes_rows_to_write(dGP, M) : M;
+  float4 af = make_float4(0.f, 0.f, 0.f, 0.f), ar = af, am = af;
+  if (sub < R) {
+    for (int m = blockIdx.x * R + sub; m < Mw; m += gridDim.x * R) {
+      float4 df = make_float4(0.f, 0.f, 0.f, 0.f), dr = df, dm = df;
+      if (m < M) {
+        const float* g = G + (size_t)m * ldg;
+        const int p = parent ? parent[m] : -1;
+        float4 dc = ld4(dCn + (size_t)m * C + c);
+        if (dCc) { const float4 e = ld4(dCc + (size_t)m * C + c); dc.x += e.x; dc.y += e.y; dc.z += e.z; dc.w += e.w; }
+        const float4 f = ld4(g + c), r = ld4(g + C + c), mm = ld4(g + 2 * C + c);
+        const float4 cprev = (Cprev && p >= 0) ? ld4(Cprev + (size_t)p * C + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        df = make_float4(dc.x * cprev.x * f.x * (1.f - f.x), dc.y * cprev.y * f.y * (1.f - f.y), dc.z * cprev.z * f.z * (1.f - f.z),
+                         dc.w * cprev.w * f.w * (1.f - f.w));
+        dr = make_float4(dc.x * mm.x * r.x * (1.f - r.x), dc.y * mm.y * r.y * (1.f - r.y), dc.z * mm.z * r.z * (1.f - r.z),
+                         dc.w * mm.w * r.w * (1.f - r.w));
+        dm = make_float4(dc.x * r.x * (1.f - mm.x * mm.x), dc.y * r.y * (1.f - mm.y * mm.y), dc.z * r.z * (1.f - mm.z * mm.z),
+                         dc.w * r.w * (1.f - mm.w * mm.w));
+        af.x += df.x; af.y += df.y; af.z += df.z; af.w += df.w;
+        ar.x += dr.x; ar.y += dr.y; ar.z += dr.z; ar.w += dr.w;
+        am.x += dm.x; am.y += dm.y; am.z += dm.z; am.w += dm.w;
+        if (dG) { float* dg = dG + (size_t)m * ldg; st4(dg + c, df); st4(dg + C + c, dr); st4(dg + 2 * C + c, dm); }
+        if (dCrow) st4(dCrow + (size_t)m * C + c, make_float4(dc.x * f.x, dc.y * f.y, dc.z * f.z, dc.w * f.w));
+      }
+      if (dGP.p) { planes_store4(dGP, m, c, df, want_lo); planes_store4(dGP, m, C + c, dr, want_lo); planes_store4(dGP, m, 2 * C + c, dm, want_lo); }
+    }
+  }
+  __shared__ float4 red[3][256];
+  red[0][threadIdx.x] = af; red[1][threadIdx.x] = ar; red[2][threadIdx.x] = am;
+  __syncthreads();
+  if (sub == 0) {
+#pragma unroll
+    for (int gsel = 0; gsel < 3; ++gsel) {
+      float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = 0; r < R; ++r) { const float4 v = red[gsel][r * G4 + c4]; s4.x += v.x; s4.y += v.y; s4.z += v.z; s4.w += v.w; }
+      float* o = db_g + gsel * C + c;
+      atomicAdd(o, s4.x); atomicAdd(o + 1, s4.y); atomicAdd(o + 2, s4.z); atomicAdd(o + 3, s4.w);
     }
   }
 }
@@ -200,10 +284,10 @@ __global__ void __launch_bounds__(TPB) special_fill_kernel(const float* __restri
 // keeps private partial sums for its columns across the rows its warp visits (d, I <= 256).
 __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restrict__ dtok, const float* __restrict__ UV,
                                                           const float* __restrict__ alpha, const float* __restrict__ w2,
-                                                          const int* __restrict__ row_slide, float* __restrict__ dUV,
-                                                          float* __restrict__ db1, float* __restrict__ dw2, float* __restrict__ db2,
-                                                          float* __restrict__ dbin, int I, int d, int imp_mul, int mode,
-                                                          int M_host, const int* M_dev) {
+                                                          const int* __restrict__ row_slide, float* __restrict__ dUV, Planes dUVP,
+                                                          int want_lo, float* __restrict__ db1, float* __restrict__ dw2,
+                                                          float* __restrict__ db2, float* __restrict__ dbin, int I, int d, int imp_mul,
+                                                          int mode, int M_host, const int* M_dev) {
   // mode 0: full backward of imp_tok_fwd; 2: token part only (dV = dtok, dbin), the importance head is handled elsewhere
   const int M = row_count(M_host, M_dev);
   const int ld = I + d;
@@ -211,10 +295,22 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restric
   float a_b1[8], a_w2[8], a_bin[8], a_b2 = 0.f;
 #pragma unroll
   for (int q = 0; q < 8; ++q) a_b1[q] = a_w2[q] = a_bin[q] = 0.f;
-  ROW_LOOP(m, M) {
+  const int Mw = dUVP.p ? planes_rows_to_write(dUVP, M) : M;
+  auto put = [&](int m, int col, float v) {
+    if (dUV) dUV[(size_t)m * ld + col] = v;
+    if (dUVP.p) {
+      const __nv_bfloat16 h = __float2bfloat16_rn(v);
+      dUVP.p[(size_t)m * dUVP.ldp + col] = h;
+      if (want_lo) dUVP.p[((size_t)dUVP.rows + m) * dUVP.ldp + col] = __float2bfloat16_rn(v - __bfloat162float(h));
+    }
+  };
+  ROW_LOOP(m, Mw) {
+    if (m >= M) {
+      for (int col = lane; col < ld; col += 32) put(m, col, 0.f);
+      continue;
+    }
     const float* uv = UV + (size_t)m * ld;
     const float* dt = dtok + (size_t)(m + row_slide[m] + 1) * d;
-    float* duv = dUV + (size_t)m * ld;
     const float a = alpha[m];
     float da = 0.f;
 #pragma unroll
@@ -224,7 +320,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restric
         const float g = dt[c];
         a_bin[q] += g;
         da += g * uv[I + c];
-        duv[I + c] = imp_mul ? a * g : g;
+        put(m, I + c, imp_mul ? a * g : g);
       }
     }
     float ds = 0.f;
@@ -239,7 +335,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restric
         a_w2[q] += ds * u;
         const float du = (u > 0.f) ? ds * w2[j] : 0.f;
         a_b1[q] += du;
-        duv[j] = du;
+        put(m, j, du);
       }
     }
   }
@@ -613,29 +709,37 @@ int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, c
   PATHS_LAUNCH_CK();
   return 0;
 }
-int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, const Planes& CnP, int want_lo, int D, int C, int M_host,
+                    const int* M_dev, cudaStream_t st) {
+  PATHS_REQUIRE(D % 4 == 0 && C % 4 == 0, "lstm: D and C must be multiples of 4");
   if (M_host <= 0) return 0;
-  lstm_point1_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(G, Cprev, parent, Cn, D, C, M_host, M_dev);
+  lstm_point1_fwd_kernel<<<row_grid(M_host + 64), TPB, 0, st>>>(G, Cprev, parent, Cn, CnP, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
-int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
-  if (M_host <= 0) return 0;
-  lstm_point2_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(Pt, G, X, H, Y, D, C, M_host, M_dev);
-  PATHS_LAUNCH_CK();
-  return 0;
-}
-int lstm_point2_bwd(const float* dY, const float* dHc, const float* Pt, const float* G, float* dP, float* dG, int D, int C, int M_host,
+int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
                     const int* M_dev, cudaStream_t st) {
   if (M_host <= 0) return 0;
-  lstm_point2_bwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(dY, dHc, Pt, G, dP, dG, D, C, M_host, M_dev);
+  lstm_point2_fwd_kernel<<<row_grid(M_host + 64), TPB, 0, st>>>(Pt, G, X, H, Y, YP, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
-int lstm_point1_bwd(const float* dCn, const float* dCc, const float* G, const float* Cprev, const int* parent, float* dG, float* dCrow,
-                    int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+int lstm_point2_bwd(const float* dY, const float* dHc, const float* Pt, const float* G, float* dP, const Planes& dPP, float* dG,
+                    const Planes& dGP, float* db_mo, float* db_o, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+  PATHS_REQUIRE(D <= 4 * CG * 256, "lstm backward: patch_embed_dim above %d unsupported", 4 * CG * 256);
   if (M_host <= 0) return 0;
-  lstm_point1_bwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(dCn, dCc, G, Cprev, parent, dG, dCrow, D, C, M_host, M_dev);
+  int g = M_host + 64; if (g > 3 * kNumSMs) g = 3 * kNumSMs;
+  lstm_point2_bwd_kernel<<<g, 256, 0, st>>>(dY, dHc, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int lstm_point1_bwd(const float* dCn, const float* dCc, const float* G, const float* Cprev, const int* parent, float* dG, const Planes& dGP,
+                    float* dCrow, float* db_g, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+  PATHS_REQUIRE(C / 4 <= 256, "lstm backward: hierarchical_ctx_mlp_hidden_dim above 1024 unsupported");
+  if (M_host <= 0) return 0;
+  const int R = 256 / (C / 4);
+  int g = (M_host + 64 + R - 1) / R; if (g > 3 * kNumSMs) g = 3 * kNumSMs;
+  lstm_point1_bwd_kernel<<<g, 256, 0, st>>>(dCn, dCc, G, Cprev, parent, dG, dGP, dCrow, db_g, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -661,11 +765,13 @@ int special_fill(const float* special, const int* seg, float* tok, int d, int B,
   PATHS_LAUNCH_CK();
   return 0;
 }
-int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const float* w2, const int* row_slide, float* dUV, float* db1,
-                float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int mode, int M_host, const int* M_dev, cudaStream_t st) {
+int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const float* w2, const int* row_slide, float* dUV, const Planes& dUVP,
+                int want_lo, float* db1, float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int mode, int M_host, const int* M_dev,
+                cudaStream_t st) {
   if (M_host <= 0) return 0;
-  int g = row_grid(M_host); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
-  imp_tok_bwd_kernel<<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, db1, dw2, db2, dbin, I, d, imp_mul, mode, M_host, M_dev);
+  int g = row_grid(M_host + 64); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
+  imp_tok_bwd_kernel<<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, mode, M_host,
+                                        M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }

@@ -10,20 +10,25 @@ int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, c
                 const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st);
 int pack_padded_rows(const float* fts, int N, const int* seg, const int* row_slide, float* X, int D, int M_host, const int* M_dev,
                      cudaStream_t st);
-int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, int D, int C, int M_host, const int* M_dev, cudaStream_t st);
-int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, int D, int C, int M_host, const int* M_dev, cudaStream_t st);
-int lstm_point2_bwd(const float* dY, const float* dHc, const float* Pt, const float* G, float* dP, float* dG, int D, int C, int M_host,
+// Outputs come as fp32 rows (pointer may be null) and/or bf16 (hi, lo) planes (Planes.p may be null); want_lo = 0 skips the
+// lo plane (single-pass bf16 mode).  The backward kernels also accumulate the bias gradients (column sums) they pass over.
+int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, const Planes& CnP, int want_lo, int D, int C, int M_host,
                     const int* M_dev, cudaStream_t st);
-int lstm_point1_bwd(const float* dCn, const float* dCc, const float* G, const float* Cprev, const int* parent, float* dG, float* dCrow,
-                    int D, int C, int M_host, const int* M_dev, cudaStream_t st);
+int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
+                    const int* M_dev, cudaStream_t st);
+int lstm_point2_bwd(const float* dY, const float* dHc, const float* Pt, const float* G, float* dP, const Planes& dPP, float* dG,
+                    const Planes& dGP, float* db_mo, float* db_o, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st);
+int lstm_point1_bwd(const float* dCn, const float* dCc, const float* G, const float* Cprev, const int* parent, float* dG, const Planes& dGP,
+                    float* dCrow, float* db_g, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st);
 int parent_sum(const int* child_of, const float* dHrow, const float* dCrow, float* dHc, float* dCc, int D, int C, int M_host,
                const int* M_dev, cudaStream_t st);
 int imp_tok_fwd(float* UV, const float* b1, const float* w2, const float* b2, const float* bin, const float* div, const int* row_slide,
                 const int* row_xy, const int* seg, float* alpha, float* tok, int I, int d, int imp_mul, int pe_mode, int mode, int M_host,
                 const int* M_dev, cudaStream_t st);
 int special_fill(const float* special, const int* seg, float* tok, int d, int B, cudaStream_t st);
-int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const float* w2, const int* row_slide, float* dUV, float* db1,
-                float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int mode, int M_host, const int* M_dev, cudaStream_t st);
+int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const float* w2, const int* row_slide, float* dUV, const Planes& dUVP,
+                int want_lo, float* db1, float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int mode, int M_host, const int* M_dev,
+                cudaStream_t st);
 // RNN variant (lstm = false, paths.py:96-109) and slide_ctx_mode "concat" (paths.py:134-137)
 struct FList { const float* f[8]; int n; };
 struct GList { float* g[8]; int n; };
