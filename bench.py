@@ -94,8 +94,9 @@ def cpu_oracle_rate(n_slides, steps, warmup, threads=None):
     from oracle import paths_oracle as po
     from paths_b200 import synth
     from paths_b200.config import Config
-    if threads:
-        torch.set_num_threads(threads)
+    if threads is None:                      # torchrun exports OMP_NUM_THREADS=1: use every core this process may run on
+        threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    torch.set_num_threads(max(1, threads))
     cfg = Config.from_dict(BRCA_CONFIG)
     torch.manual_seed(cfg.seed)
     model = cfg.get_model()

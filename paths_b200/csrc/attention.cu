@@ -22,9 +22,10 @@ __device__ __forceinline__ Seg seg_of(const int* seg, int s) { Seg r; r.t0 = seg
 // out[q, h*dh + c] = sum_j softmax_j(scale * q.k_j) v_j[c];  lse[q, h] = logsumexp_j(scale * q.k_j)
 __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
                                                            float* __restrict__ out, float* __restrict__ lse, int d, int heads,
-                                                           int nq_mode) {
+                                                           int nq_mode, int skip_T) {
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
+  if (sg.T <= skip_T) return;                        // short bags belong to the *_small kernels
   const int nq = nq_mode ? 1 : sg.T;
   const int q0 = blockIdx.x * QB;
   if (q0 >= nq) return;
@@ -97,9 +98,10 @@ __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restri
 __global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
                                                               const float* __restrict__ out, const float* __restrict__ lse,
                                                               const float* __restrict__ dout, float* __restrict__ dqkv,
-                                                              float* __restrict__ Dvec, int d, int heads, int nq_mode) {
+                                                              float* __restrict__ Dvec, int d, int heads, int nq_mode, int skip_T) {
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
+  if (sg.T <= skip_T) return;
   const int nq = nq_mode ? 1 : sg.T;
   const int q0 = blockIdx.x * QB;
   if (q0 >= nq) return;
@@ -171,9 +173,10 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __res
 __global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
                                                                const float* __restrict__ lse, const float* __restrict__ dout,
                                                                const float* __restrict__ Dvec, float* __restrict__ dqkv, int d,
-                                                               int heads, int nq_mode) {
+                                                               int heads, int nq_mode, int skip_T) {
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
+  if (sg.T <= skip_T) return;
   const int nq = nq_mode ? 1 : sg.T;
   const int j0 = blockIdx.x * QB;
   if (j0 >= sg.T) return;
@@ -249,26 +252,502 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __re
   }
 }
 
+// ====================================================================================================================
+// Short-bag kernels (head_dim 32, T <= 32*NKC <= 128 tokens per slide: every level of the BRCA-shaped workload).  One CTA
+// per (head, slide) keeps the head's Q (pre-scaled), K, V (and dO in the backward) in shared memory as [T][33] rows --
+// stride 33 makes the row-major ([j][lane]), the transposed ([lane + 32m][c]) and the broadcast access all conflict-free --
+// and each warp works on blocks of SQ queries (or keys) with the whole score row in registers: SQ x NKC accumulators per
+// lane instead of one shuffle per multiply.  Slides longer than 32*NKC tokens are left to the tiled kernels above.
+constexpr int SQ = 8;            // queries (keys in the key-major phase) per warp pass
+constexpr int SW = 4;            // warps per CTA
+constexpr int SP = 33;           // padded row stride (floats)
+
+template <int NKC>
+__global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+                                                                 float* __restrict__ out, float* __restrict__ lse, int d, int heads,
+                                                                 int nq_mode) {
+  constexpr int TP = 32 * NKC;
+  const int h = blockIdx.x, s = blockIdx.y;
+  const Seg sg = seg_of(seg, s);
+  const int T = sg.T;
+  if (T > TP) return;
+  const int nq = nq_mode ? 1 : T;
+  extern __shared__ float sm[];
+  float* Qs = sm;                       // [TP][SP]
+  float* Ks = Qs + TP * SP;
+  float* Vs = Ks + TP * SP;
+  float* Pw = Vs + TP * SP;             // [SW][SQ][TP]
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const float scale = rsqrtf(32.f);
+  const int ld = 3 * d;
+  {
+    // every load of the head's Q/K/V slice is issued before the first shared-memory store: (row, 16-byte quad) items, 8 per row
+    constexpr int NIT = TP * 8 / (SW * 32);
+    float4 q4[NIT], k4[NIT], v4[NIT];
+#pragma unroll
+    for (int k = 0; k < NIT; ++k) {
+      const int item = threadIdx.x + k * SW * 32, j = item >> 3, c4 = (item & 7) * 4;
+      q4[k] = k4[k] = v4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (j < T) {
+        const float* rp = qkv + (size_t)(sg.t0 + j) * ld + h * 32 + c4;
+        if (j < nq) q4[k] = __ldg(reinterpret_cast<const float4*>(rp));
+        k4[k] = __ldg(reinterpret_cast<const float4*>(rp + d));
+        v4[k] = __ldg(reinterpret_cast<const float4*>(rp + 2 * d));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < NIT; ++k) {
+      const int item = threadIdx.x + k * SW * 32, j = item >> 3, c4 = (item & 7) * 4;
+      float* qd = Qs + j * SP + c4; float* kd = Ks + j * SP + c4; float* vd = Vs + j * SP + c4;
+      qd[0] = q4[k].x * scale; qd[1] = q4[k].y * scale; qd[2] = q4[k].z * scale; qd[3] = q4[k].w * scale;
+      kd[0] = k4[k].x; kd[1] = k4[k].y; kd[2] = k4[k].z; kd[3] = k4[k].w;
+      vd[0] = v4[k].x; vd[1] = v4[k].y; vd[2] = v4[k].z; vd[3] = v4[k].w;
+    }
+  }
+  __syncthreads();
+  float* P = Pw + w * SQ * TP;
+  for (int i0 = w * SQ; i0 < nq; i0 += SW * SQ) {
+    float sc[SQ][NKC];
+#pragma unroll
+    for (int i = 0; i < SQ; ++i)
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) sc[i][m] = 0.f;
+#pragma unroll 4
+    for (int c = 0; c < 32; ++c) {
+      float kv[NKC];
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) kv[m] = Ks[(lane + 32 * m) * SP + c];
+#pragma unroll
+      for (int i = 0; i < SQ; ++i) {
+        const float qv = Qs[(i0 + i) * SP + c];        // rows past nq are zero (inside TP because i0 + SQ <= TP)
+#pragma unroll
+        for (int m = 0; m < NKC; ++m) sc[i][m] = fmaf(qv, kv[m], sc[i][m]);
+      }
+    }
+    float linv[SQ], lsev[SQ];
+#pragma unroll
+    for (int i = 0; i < SQ; ++i) {
+      float mx = -INFINITY;
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) {
+        if (lane + 32 * m >= T) sc[i][m] = -INFINITY;
+        mx = fmaxf(mx, sc[i][m]);
+      }
+      mx = warp_max(mx);
+      float sum = 0.f;
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) {
+        const float p = expf(sc[i][m] - mx);            // exp(-inf) = 0 at masked keys
+        P[i * TP + lane + 32 * m] = p;
+        sum += p;
+      }
+      sum = warp_sum(sum);
+      linv[i] = 1.f / sum; lsev[i] = mx + logf(sum);
+    }
+    __syncwarp();
+    float o[SQ];
+#pragma unroll
+    for (int i = 0; i < SQ; ++i) o[i] = 0.f;
+    const int T4 = (T + 3) & ~3;
+    for (int j = 0; j < T4; j += 4) {
+      const float v0 = Vs[j * SP + lane], v1 = Vs[(j + 1) * SP + lane], v2 = Vs[(j + 2) * SP + lane], v3 = Vs[(j + 3) * SP + lane];
+#pragma unroll
+      for (int i = 0; i < SQ; ++i) {
+        const float4 p = *reinterpret_cast<const float4*>(P + i * TP + j);
+        o[i] = fmaf(p.x, v0, fmaf(p.y, v1, fmaf(p.z, v2, fmaf(p.w, v3, o[i]))));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < SQ; ++i) {
+      const int q = i0 + i;
+      if (q < nq) {
+        const size_t orow = nq_mode ? (size_t)s : (size_t)(sg.t0 + q);
+        out[orow * d + h * 32 + lane] = o[i] * linv[i];
+        if (lane == 0) lse[orow * heads + h] = lsev[i];
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// Backward of the short-bag attention: phase A is query-major (dq), phase B key-major (dk, dv); both recompute the
+// probabilities from the saved log-sum-exp, so nothing is accumulated across warps and no atomics are needed.
+template <int NKC>
+__global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+                                                                 const float* __restrict__ out, const float* __restrict__ lse,
+                                                                 const float* __restrict__ dout, float* __restrict__ dqkv, int d,
+                                                                 int heads, int nq_mode) {
+  constexpr int TP = 32 * NKC;
+  const int h = blockIdx.x, s = blockIdx.y;
+  const Seg sg = seg_of(seg, s);
+  const int T = sg.T;
+  if (T > TP) return;
+  const int nq = nq_mode ? 1 : T;
+  extern __shared__ float sm[];
+  float* Qs = sm;                       // [TP][SP], pre-scaled
+  float* Ks = Qs + TP * SP;
+  float* Vs = Ks + TP * SP;
+  float* Gs = Vs + TP * SP;             // dO
+  float* Ls = Gs + TP * SP;             // [TP] log-sum-exp per query
+  float* Ds = Ls + TP;                  // [TP] dO . O per query
+  float* Pw = Ds + TP;                  // [SW][2][SQ][TP]
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const float scale = rsqrtf(32.f);
+  const int ld = 3 * d;
+  {
+    constexpr int NIT = TP * 8 / (SW * 32);
+    float4 a4[NIT], b4[NIT], c4r[NIT];
+#pragma unroll
+    for (int k = 0; k < NIT; ++k) {                     // K, V
+      const int item = threadIdx.x + k * SW * 32, j = item >> 3, c4 = (item & 7) * 4;
+      a4[k] = b4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (j < T) {
+        const float* rp = qkv + (size_t)(sg.t0 + j) * ld + h * 32 + c4;
+        a4[k] = __ldg(reinterpret_cast<const float4*>(rp + d));
+        b4[k] = __ldg(reinterpret_cast<const float4*>(rp + 2 * d));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < NIT; ++k) {
+      const int item = threadIdx.x + k * SW * 32, j = item >> 3, c4 = (item & 7) * 4;
+      float* kd = Ks + j * SP + c4; float* vd = Vs + j * SP + c4;
+      kd[0] = a4[k].x; kd[1] = a4[k].y; kd[2] = a4[k].z; kd[3] = a4[k].w;
+      vd[0] = b4[k].x; vd[1] = b4[k].y; vd[2] = b4[k].z; vd[3] = b4[k].w;
+    }
+#pragma unroll
+    for (int k = 0; k < NIT; ++k) {                     // Q, dO, O (-> D), lse
+      const int item = threadIdx.x + k * SW * 32, j = item >> 3, c4 = (item & 7) * 4;
+      a4[k] = b4[k] = c4r[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (j < nq) {
+        const size_t orow = nq_mode ? (size_t)s : (size_t)(sg.t0 + j);
+        a4[k] = __ldg(reinterpret_cast<const float4*>(qkv + (size_t)(sg.t0 + j) * ld + h * 32 + c4));
+        b4[k] = __ldg(reinterpret_cast<const float4*>(dout + orow * d + h * 32 + c4));
+        c4r[k] = __ldg(reinterpret_cast<const float4*>(out + orow * d + h * 32 + c4));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < NIT; ++k) {
+      const int item = threadIdx.x + k * SW * 32, j = item >> 3, c4 = (item & 7) * 4;
+      float* qd = Qs + j * SP + c4; float* gd = Gs + j * SP + c4;
+      qd[0] = a4[k].x * scale; qd[1] = a4[k].y * scale; qd[2] = a4[k].z * scale; qd[3] = a4[k].w * scale;
+      gd[0] = b4[k].x; gd[1] = b4[k].y; gd[2] = b4[k].z; gd[3] = b4[k].w;
+      float dd = b4[k].x * c4r[k].x + b4[k].y * c4r[k].y + b4[k].z * c4r[k].z + b4[k].w * c4r[k].w;
+      dd += __shfl_xor_sync(0xffffffffu, dd, 1);
+      dd += __shfl_xor_sync(0xffffffffu, dd, 2);
+      dd += __shfl_xor_sync(0xffffffffu, dd, 4);
+      if ((item & 7) == 0) {
+        Ds[j] = dd;
+        Ls[j] = (j < nq) ? lse[(nq_mode ? (size_t)s : (size_t)(sg.t0 + j)) * heads + h] : 0.f;
+      }
+    }
+  }
+  __syncthreads();
+  float* P = Pw + w * 2 * SQ * TP;      // probabilities (phase B)
+  float* S = P + SQ * TP;               // dS
+  // ---- phase A: dq_i = scale * sum_j dS_ij k_j,  dS_ij = p_ij (dO_i . v_j - D_i)
+  for (int i0 = w * SQ; i0 < nq; i0 += SW * SQ) {
+    float sc[SQ][NKC], dp[SQ][NKC];
+#pragma unroll
+    for (int i = 0; i < SQ; ++i)
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) { sc[i][m] = 0.f; dp[i][m] = 0.f; }
+#pragma unroll 2
+    for (int c = 0; c < 32; ++c) {
+      float kv[NKC], vv[NKC];
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) { kv[m] = Ks[(lane + 32 * m) * SP + c]; vv[m] = Vs[(lane + 32 * m) * SP + c]; }
+#pragma unroll
+      for (int i = 0; i < SQ; ++i) {
+        const float qv = Qs[(i0 + i) * SP + c], gv = Gs[(i0 + i) * SP + c];
+#pragma unroll
+        for (int m = 0; m < NKC; ++m) { sc[i][m] = fmaf(qv, kv[m], sc[i][m]); dp[i][m] = fmaf(gv, vv[m], dp[i][m]); }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < SQ; ++i) {
+      const float L = Ls[i0 + i], Dq = Ds[i0 + i];
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) {
+        const float p = (lane + 32 * m < T) ? expf(sc[i][m] - L) : 0.f;
+        S[i * TP + lane + 32 * m] = p * (dp[i][m] - Dq);
+      }
+    }
+    __syncwarp();
+    float a[SQ];
+#pragma unroll
+    for (int i = 0; i < SQ; ++i) a[i] = 0.f;
+    const int T4 = (T + 3) & ~3;
+    for (int j = 0; j < T4; j += 4) {
+      const float k0 = Ks[j * SP + lane], k1 = Ks[(j + 1) * SP + lane], k2 = Ks[(j + 2) * SP + lane], k3 = Ks[(j + 3) * SP + lane];
+#pragma unroll
+      for (int i = 0; i < SQ; ++i) {
+        const float4 ds = *reinterpret_cast<const float4*>(S + i * TP + j);
+        a[i] = fmaf(ds.x, k0, fmaf(ds.y, k1, fmaf(ds.z, k2, fmaf(ds.w, k3, a[i]))));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < SQ; ++i)
+      if (i0 + i < nq) dqkv[(size_t)(sg.t0 + i0 + i) * ld + h * 32 + lane] = a[i] * scale;
+    __syncwarp();
+  }
+  // ---- phase B: dv_j = sum_i p_ij dO_i,  dk_j = sum_i dS_ij (scale q_i); lanes run over the queries
+  const int nqc = (nq + 31) >> 5;
+  for (int j0 = w * SQ; j0 < T; j0 += SW * SQ) {
+    float sc[SQ][NKC], dp[SQ][NKC];
+#pragma unroll
+    for (int i = 0; i < SQ; ++i)
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) { sc[i][m] = 0.f; dp[i][m] = 0.f; }
+#pragma unroll 2
+    for (int c = 0; c < 32; ++c) {
+      float qv[NKC], gv[NKC];
+#pragma unroll
+      for (int m = 0; m < NKC; ++m) {
+        qv[m] = 0.f; gv[m] = 0.f;
+        if (m < nqc) { qv[m] = Qs[(lane + 32 * m) * SP + c]; gv[m] = Gs[(lane + 32 * m) * SP + c]; }
+      }
+#pragma unroll
+      for (int i = 0; i < SQ; ++i) {
+        const float kv = Ks[(j0 + i) * SP + c], vv = Vs[(j0 + i) * SP + c];
+#pragma unroll
+        for (int m = 0; m < NKC; ++m) { sc[i][m] = fmaf(kv, qv[m], sc[i][m]); dp[i][m] = fmaf(vv, gv[m], dp[i][m]); }
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < NKC; ++m) {
+      const int qi = lane + 32 * m;
+      const float L = Ls[qi], Dq = Ds[qi];
+#pragma unroll
+      for (int i = 0; i < SQ; ++i) {
+        const float p = (qi < nq) ? expf(sc[i][m] - L) : 0.f;
+        P[i * TP + qi] = p;
+        S[i * TP + qi] = p * (dp[i][m] - Dq);
+      }
+    }
+    __syncwarp();
+    float dk[SQ], dv[SQ];
+#pragma unroll
+    for (int i = 0; i < SQ; ++i) { dk[i] = 0.f; dv[i] = 0.f; }
+    const int n4 = (nq + 3) & ~3;
+    for (int q = 0; q < n4; q += 4) {
+      const float g0 = Gs[q * SP + lane], g1 = Gs[(q + 1) * SP + lane], g2 = Gs[(q + 2) * SP + lane], g3 = Gs[(q + 3) * SP + lane];
+      const float q0 = Qs[q * SP + lane], q1 = Qs[(q + 1) * SP + lane], q2 = Qs[(q + 2) * SP + lane], q3 = Qs[(q + 3) * SP + lane];
+#pragma unroll
+      for (int i = 0; i < SQ; ++i) {
+        const float4 p = *reinterpret_cast<const float4*>(P + i * TP + q);
+        const float4 ds = *reinterpret_cast<const float4*>(S + i * TP + q);
+        dv[i] = fmaf(p.x, g0, fmaf(p.y, g1, fmaf(p.z, g2, fmaf(p.w, g3, dv[i]))));
+        dk[i] = fmaf(ds.x, q0, fmaf(ds.y, q1, fmaf(ds.z, q2, fmaf(ds.w, q3, dk[i]))));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < SQ; ++i) {
+      if (j0 + i < T) {
+        float* rp = dqkv + (size_t)(sg.t0 + j0 + i) * ld + h * 32 + lane;
+        rp[d] = dk[i]; rp[2 * d] = dv[i];
+      }
+    }
+    __syncwarp();
+  }
+}
+
+}  // namespace
+
+
+namespace {
+// ====================================================================================================================
+// Single-query attention (nq_mode 1: the last decoder layer is read at the special token only, aggregator.py:75), head_dim 32.
+// One warp per (slide, head), any bag length: lanes run over the keys of a 32-key chunk for the scores (each lane reads its
+// key row), then over the head dims for the value sum (coalesced rows, probabilities by shuffle); online softmax over chunks.
+__global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+                                                           float* __restrict__ out, float* __restrict__ lse, int d, int heads, int B) {
+  const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (wid >= B * heads) return;
+  const int s = wid / heads, h = wid % heads;
+  const Seg sg = seg_of(seg, s);
+  const int ld = 3 * d;
+  const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
+  const float qv = base[lane] * rsqrtf(32.f);
+  float m = -INFINITY, l = 0.f, o = 0.f;
+  for (int j0 = 0; j0 < sg.T; j0 += 32) {
+    const int j = j0 + lane;
+    float4 k4[8];
+    if (j < sg.T) {
+      const float4* kr = reinterpret_cast<const float4*>(base + (size_t)j * ld + d);
+#pragma unroll
+      for (int c = 0; c < 8; ++c) k4[c] = __ldg(kr + c);
+    } else {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) k4[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float sc = 0.f;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {                        // shuffles are executed by every lane
+      sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c), k4[c].x, sc);
+      sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 1), k4[c].y, sc);
+      sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 2), k4[c].z, sc);
+      sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 3), k4[c].w, sc);
+    }
+    if (j >= sg.T) sc = -INFINITY;
+    const float mn = fmaxf(m, warp_max(sc));
+    const float p = (j < sg.T) ? expf(sc - mn) : 0.f;
+    const float corr = expf(m - mn);
+    l = l * corr + warp_sum(p);
+    o *= corr;
+    const int jmax = min(32, sg.T - j0);
+#pragma unroll 8
+    for (int jj = 0; jj < 32; ++jj) {                    // fixed trip count: the value-row loads of a chunk are all in flight
+      const float vv = (jj < jmax) ? __ldg(base + (size_t)(j0 + jj) * ld + 2 * d + lane) : 0.f;
+      o = fmaf(__shfl_sync(0xffffffffu, p, jj), vv, o);
+    }
+    m = mn;
+  }
+  out[(size_t)s * d + h * 32 + lane] = o / l;
+  if (lane == 0) lse[(size_t)s * heads + h] = m + logf(l);
+}
+
+// Backward of the single-query attention; writes the q, k and v parts of every dqkv row of the slide (q part is zero
+// except at the special token), so the caller needs no zero-fill.
+__global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+                                                           const float* __restrict__ out, const float* __restrict__ lse,
+                                                           const float* __restrict__ dout, float* __restrict__ dqkv, int d, int heads,
+                                                           int B) {
+  const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (wid >= B * heads) return;
+  const int s = wid / heads, h = wid % heads;
+  const Seg sg = seg_of(seg, s);
+  const int ld = 3 * d;
+  const float scale = rsqrtf(32.f);
+  const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
+  float* dbase = dqkv + (size_t)sg.t0 * ld + h * 32;
+  const float qv = base[lane] * scale;
+  const float g = dout[(size_t)s * d + h * 32 + lane];
+  const float Dq = warp_sum(g * out[(size_t)s * d + h * 32 + lane]);
+  const float L = lse[(size_t)s * heads + h];
+  float dq = 0.f;
+  for (int j0 = 0; j0 < sg.T; j0 += 32) {
+    const int j = j0 + lane;
+    float sc = 0.f, dp = 0.f;
+    float4 k4[8], v4[8];
+    if (j < sg.T) {
+      const float4* kr = reinterpret_cast<const float4*>(base + (size_t)j * ld + d);
+      const float4* vr = reinterpret_cast<const float4*>(base + (size_t)j * ld + 2 * d);
+#pragma unroll
+      for (int c = 0; c < 8; ++c) { k4[c] = __ldg(kr + c); v4[c] = __ldg(vr + c); }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) { k4[c] = make_float4(0.f, 0.f, 0.f, 0.f); v4[c] = k4[c]; }
+    }
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c), k4[c].x, sc);     dp = fmaf(__shfl_sync(0xffffffffu, g, 4 * c), v4[c].x, dp);
+      sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 1), k4[c].y, sc); dp = fmaf(__shfl_sync(0xffffffffu, g, 4 * c + 1), v4[c].y, dp);
+      sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 2), k4[c].z, sc); dp = fmaf(__shfl_sync(0xffffffffu, g, 4 * c + 2), v4[c].z, dp);
+      sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 3), k4[c].w, sc); dp = fmaf(__shfl_sync(0xffffffffu, g, 4 * c + 3), v4[c].w, dp);
+    }
+    const float p = (j < sg.T) ? expf(sc - L) : 0.f;
+    const float ds = p * (dp - Dq);
+    const int jmax = min(32, sg.T - j0);
+#pragma unroll 8
+    for (int jj = 0; jj < 32; ++jj) {
+      const float pj = __shfl_sync(0xffffffffu, p, jj), dsj = __shfl_sync(0xffffffffu, ds, jj);
+      if (jj < jmax) {
+        const size_t r = (size_t)(j0 + jj) * ld;
+        dq = fmaf(dsj, __ldg(base + r + d + lane), dq);
+        if (j0 + jj > 0) dbase[r + lane] = 0.f;
+        dbase[r + d + lane] = dsj * qv;
+        dbase[r + 2 * d + lane] = pj * g;
+      }
+    }
+  }
+  dbase[lane] = dq * scale;
+}
+}  // namespace
+
+namespace {
+constexpr int SMALL_MAX_T = 128;
+inline size_t small_fwd_smem(int nkc) { return (size_t)(3 * 32 * nkc * SP + SW * SQ * 32 * nkc) * sizeof(float); }
+inline size_t small_bwd_smem(int nkc) { return (size_t)(4 * 32 * nkc * SP + 2 * 32 * nkc + SW * 2 * SQ * 32 * nkc) * sizeof(float); }
+
+template <int NKC>
+int launch_fwd_small(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int nq_mode, cudaStream_t st) {
+  static bool cfg = false;
+  const int bytes = (int)small_fwd_smem(NKC);
+  if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_fwd_small_kernel<NKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
+  attn_fwd_small_kernel<NKC><<<dim3(heads, B), SW * 32, bytes, st>>>(qkv, seg, out, lse, d, heads, nq_mode);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+template <int NKC>
+int launch_bwd_small(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, int d, int heads,
+                     int B, int nq_mode, cudaStream_t st) {
+  static bool cfg = false;
+  const int bytes = (int)small_bwd_smem(NKC);
+  if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_bwd_small_kernel<NKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
+  attn_bwd_small_kernel<NKC><<<dim3(heads, B), SW * 32, bytes, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
 }  // namespace
 
 int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st) {
   PATHS_REQUIRE(d % heads == 0 && d / heads <= MAXDH, "attention: head_dim %d unsupported (max %d)", d / heads, MAXDH);
   if (B <= 0) return 0;
+  int skip_T = 0;
+  if (d / heads == 32 && nq_mode) {
+    attn_fwd_nq1_kernel<<<(B * heads + 3) / 4, 128, 0, st>>>(qkv, seg, out, lse, d, heads, B);
+    PATHS_LAUNCH_CK();
+    return 0;
+  }
+  if (d / heads == 32) {                       // short bags: whole-head-in-shared-memory kernels
+    const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
+    int r = 0;
+    switch (nkc) {
+      case 1: r = launch_fwd_small<1>(qkv, seg, out, lse, d, heads, B, nq_mode, st); break;
+      case 2: r = launch_fwd_small<2>(qkv, seg, out, lse, d, heads, B, nq_mode, st); break;
+      case 3: r = launch_fwd_small<3>(qkv, seg, out, lse, d, heads, B, nq_mode, st); break;
+      default: r = launch_fwd_small<4>(qkv, seg, out, lse, d, heads, B, nq_mode, st); break;
+    }
+    if (r) return r;
+    if (max_T <= SMALL_MAX_T) return 0;
+    skip_T = SMALL_MAX_T;
+  }
   dim3 grid(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
-  attn_fwd_kernel<<<grid, AW * 32, 0, st>>>(qkv, seg, out, lse, d, heads, nq_mode);
+  attn_fwd_kernel<<<grid, AW * 32, 0, st>>>(qkv, seg, out, lse, d, heads, nq_mode, skip_T);
   PATHS_LAUNCH_CK();
   return 0;
 }
 
-// dqkv must be zero-initialised by the caller when nq_mode == 1 (dq rows of non-query tokens are not written).
+// dqkv must be zero-initialised by the caller when nq_mode == 1 and attn_bwd_writes_all(d, heads) is false (the dq rows of
+// non-query tokens are then not written).
+bool attn_bwd_writes_all(int d, int heads) { return d / heads == 32; }
 int attn_bwd(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
              int heads, int B, int max_T, int nq_mode, cudaStream_t st) {
   if (B <= 0) return 0;
+  int skip_T = 0;
+  if (d / heads == 32 && nq_mode) {
+    attn_bwd_nq1_kernel<<<(B * heads + 3) / 4, 128, 0, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, B);
+    PATHS_LAUNCH_CK();
+    return 0;
+  }
+  if (d / heads == 32) {
+    const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
+    int r = 0;
+    switch (nkc) {
+      case 1: r = launch_bwd_small<1>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st); break;
+      case 2: r = launch_bwd_small<2>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st); break;
+      case 3: r = launch_bwd_small<3>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st); break;
+      default: r = launch_bwd_small<4>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st); break;
+    }
+    if (r) return r;
+    if (max_T <= SMALL_MAX_T) return 0;
+    skip_T = SMALL_MAX_T;
+  }
   dim3 gq(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
-  attn_bwd_dq_kernel<<<gq, AW * 32, 0, st>>>(qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, nq_mode);
+  attn_bwd_dq_kernel<<<gq, AW * 32, 0, st>>>(qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, nq_mode, skip_T);
   PATHS_LAUNCH_CK();
   dim3 gk((max_T + QB - 1) / QB, heads, B);
-  attn_bwd_dkv_kernel<<<gk, AW * 32, 0, st>>>(qkv, seg, lse, dout, Dvec, dqkv, d, heads, nq_mode);
+  attn_bwd_dkv_kernel<<<gk, AW * 32, 0, st>>>(qkv, seg, lse, dout, Dvec, dqkv, d, heads, nq_mode, skip_T);
   PATHS_LAUNCH_CK();
   return 0;
 }

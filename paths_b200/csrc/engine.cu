@@ -45,6 +45,8 @@ int run_pack_jobs(const void* jobs_dev, int n_jobs, cudaStream_t st);
 size_t pack_job_bytes();
 void set_tc_scratch(void* a, size_t a_bytes, void* b, size_t b_bytes);
 size_t tc_scratch_bytes(int rows, int cols);
+size_t tn_workspace_bytes(int NI, int NJ, int M_host);
+void set_tn_workspace(void* p, size_t bytes);
 
 int gemm_nt(int prec, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
             const int* M_dev, int N, int K, int flags, cudaStream_t st) {
@@ -137,6 +139,7 @@ struct paths_engine {
   char* ws_base;
   // bf16 (hi, lo) planes of every weight matrix the tensor-core path contracts against
   char* tc_scratch[2]; size_t tc_scratch_each;
+  char* tn_ws; size_t tn_ws_bytes;                       // stream-K partial tiles of the weight-gradient contractions
   char* packed_arena; size_t packed_arena_bytes;
   void* pack_jobs; int n_pack_jobs;
   std::vector<const float*> packed_srcs;
@@ -223,6 +226,14 @@ size_t carve(paths_engine* e, char* base) {
     e->tc_scratch_each = tc_scratch_bytes(e->maxtok, cols);
     e->tc_scratch[0] = b.take<char>(e->tc_scratch_each);
     e->tc_scratch[1] = b.take<char>(e->tc_scratch_each);
+    const int tn_shapes[][2] = {{3 * C + D, 2 * D}, {D, C}, {C, D}, {I + d, D}, {I, D}, {d, D}, {3 * d, d}, {d, d}, {F, d}, {d, F}};
+    size_t tnb = 0;
+    for (const auto& sh : tn_shapes) {
+      const size_t need = tn_workspace_bytes(sh[0], sh[1], e->maxtok);
+      if (need > tnb) tnb = need;
+    }
+    e->tn_ws_bytes = tnb;
+    e->tn_ws = b.take<char>(tnb);
   }
   return (b.off + 255) & ~size_t(255);
 }
@@ -388,6 +399,7 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
 int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   const paths_dims_t& dm = e->dm;
   set_tc_scratch(e->tc_scratch[0], e->tc_scratch_each, e->tc_scratch[1], e->tc_scratch_each);
+  set_tn_workspace(e->tn_ws, e->tn_ws_bytes);
   const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F, prec = dm.precision;
   Level& v = e->lv[l];
   const LevelP& p = e->P.level[l];
@@ -447,7 +459,7 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
     RUN(ln_bwd(e->gb, nullptr, y.xh1, y.rs1, w.n1w, e->ga, nullptr, 0, W_(gw.n1w), W_(gw.n1b), W_(gw.bo), d, R, Rd, 0, st));  // ga = da
     RUN(gemm_nt(prec, row_src(e->ga, d, d), w.Wo, d, 1, e->gO, d, nullptr, R, Rd, d, d, 0, st));
     RUN(gemm_tn(prec, e->ga, d, row_src(y.O, d, d), W_(gw.Wo), d, R, Rd, d, d, st));
-    if (last) RUN(zero_rows(e->dqkv, 3 * d, Mt, Mtd, 0, st));
+    if (last && !attn_bwd_writes_all(d, dm.heads)) RUN(zero_rows(e->dqkv, 3 * d, Mt, Mtd, 0, st));
     RUN(attn_bwd(y.qkv, v.seg, y.O, y.lse, e->gO, e->dqkv, e->Dvec, d, dm.heads, B, v.maxseg + 1, last ? 1 : 0, st));
     RUN(gemm_tn(prec, e->dqkv, 3 * d, row_src(t_in, d, d), W_(gw.Wqkv), d, Mt, Mtd, 3 * d, d, st));
     RUN(colsum_accum(e->dqkv, 3 * d, W_(gw.bqkv), Mt, Mtd, 3 * d, st));
@@ -838,17 +850,20 @@ int paths_gemm_nt(int precision, const float* A, int lda, const float* B, int ld
 
 int paths_gemm_tn(int precision, const float* P, int ldp, const float* Q, int ldq, float* C, int ldc, int M, int NI, int NJ, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  void *sa = nullptr, *sb = nullptr;
+  void *sa = nullptr, *sb = nullptr, *sw = nullptr;
   if (precision != PREC_FP32_SIMT) {
     PATHS_CK(cudaMalloc(&sa, tc_scratch_bytes(M, NI)));
     PATHS_CK(cudaMalloc(&sb, tc_scratch_bytes(M, NJ)));
+    PATHS_CK(cudaMalloc(&sw, tn_workspace_bytes(NI, NJ, M)));
     set_tc_scratch(sa, tc_scratch_bytes(M, NI), sb, tc_scratch_bytes(M, NJ));
+    set_tn_workspace(sw, tn_workspace_bytes(NI, NJ, M));
   }
   int rc = gemm_tn(precision, P, ldp, row_src(Q, ldq, NJ), C, ldc, M, nullptr, NI, NJ, st);
   if (sa) {
     cudaStreamSynchronize(st);
-    cudaFree(sa); cudaFree(sb);
+    cudaFree(sa); cudaFree(sb); cudaFree(sw);
     set_tc_scratch(nullptr, 0, nullptr, 0);
+    set_tn_workspace(nullptr, 0);
   }
   return rc;
 }

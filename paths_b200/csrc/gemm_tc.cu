@@ -27,8 +27,9 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;                    // bf16 elements per k-block = one 128-byte swizzle row
-constexpr int TMA_WARP = 8, MMA_WARP = 9;
-constexpr int NTHREADS = 10 * 32;
+constexpr int EPI_WARPS = 8, TMA_WARP = 8, MMA_WARP = 9;
+constexpr int LOADER_WARP0 = 10, LOADER_WARPS = 8;           // only present when an operand is converted in-kernel
+constexpr int NTHREADS_TMA = 10 * 32, NTHREADS_CVT = (10 + LOADER_WARPS) * 32;
 
 // ---------------------------------------------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -133,7 +134,9 @@ struct Cfg {
   static constexpr int B_PLANE = BN * BK * 2;
   static constexpr int STAGE = NP * (A_PLANE + B_PLANE);
   static constexpr int NS = (200 * 1024) / STAGE >= 4 ? 4 : (200 * 1024) / STAGE;
-  static constexpr int SMEM = NS * STAGE + 1024;
+  static constexpr int EPI_STAGE = 8 * 4096;                 // per-epilogue-warp 32 x 32 fp32 transpose buffers
+  static constexpr int SMEM = NS * STAGE + EPI_STAGE + 1024;
+  static_assert(SMEM <= 227 * 1024 + 1024 - 2048, "shared memory budget");
   static_assert(NS >= 2, "need at least two stages");
 };
 
@@ -179,22 +182,82 @@ __global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host,
 // The reduction length may live on the device (TN: number of packed rows); so may the output row count (NT).
 struct Operand { int row0, col0, plane_rows; };
 
-template <int BN, int NP, bool A_MN, bool B_MN, bool ATOMIC>
-__global__ void __launch_bounds__(NTHREADS, 1)
+// In-kernel operand conversion: the loader warps read an fp32 operand tile straight from its RowSrc (gather / concat
+// included), split it into bf16 (hi, lo) and store it in the SWIZZLE_128B layout a TMA box would have produced -- no separate
+// split pass, no bf16 copy in HBM.  K-major tile: [W rows (output index) x 64 k]; MN-major tile: [64 k x W cols (output index)].
+// Work item = one 16-byte bf16 chunk (8 elements = two float4 loads); W * 8 items per tile, 4 per thread per batch.
+template <int W, bool MN, int NP>
+__device__ __forceinline__ void load_convert(const RowSrc& S, uint8_t* dst, int plane_bytes, int o0, int o_lim, int r0, int r_lim, int ltid) {
+  constexpr int NLT = LOADER_WARPS * 32;
+  constexpr int PER = W * 8 / NLT;
+  static_assert(PER % 4 == 0 || PER < 4, "loader batches");
+  constexpr int BATCH = PER < 4 ? PER : 4;
+#pragma unroll 1
+  for (int b0 = 0; b0 < PER; b0 += BATCH) {
+    float4 x[BATCH][2];
+    uint32_t off[BATCH];
+#pragma unroll
+    for (int n = 0; n < BATCH; ++n) {
+      const int item = ltid + (b0 + n) * NLT;
+      int o, k;
+      if (!MN) {
+        const int r = item >> 3, ch = item & 7;
+        o = o0 + r; k = r0 + ch * 8;
+        off[n] = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((ch ^ (r & 7)) << 4));
+      } else {
+        const int kr = item / (W / 8), ch = item % (W / 8);
+        o = o0 + ch * 8; k = r0 + kr;
+        off[n] = (uint32_t)((ch >> 3) * 8192 + (kr >> 3) * 1024 + (kr & 7) * 128 + (((ch & 7) ^ (kr & 7)) << 4));
+      }
+      const float* p = (o < o_lim && k < r_lim) ? (MN ? rowsrc_ptr(S, k, o) : rowsrc_ptr(S, o, k)) : nullptr;
+      x[n][0] = x[n][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (p) { x[n][0] = __ldg(reinterpret_cast<const float4*>(p)); x[n][1] = __ldg(reinterpret_cast<const float4*>(p) + 1); }
+    }
+#pragma unroll
+    for (int n = 0; n < BATCH; ++n) {
+      const float v[8] = {x[n][0].x, x[n][0].y, x[n][0].z, x[n][0].w, x[n][1].x, x[n][1].y, x[n][1].z, x[n][1].w};
+      uint32_t hi[4], lo[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+        const float2 hf = __bfloat1622float2(h);
+        const __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * e] - hf.x, v[2 * e + 1] - hf.y);
+        hi[e] = *reinterpret_cast<const uint32_t*>(&h); lo[e] = *reinterpret_cast<const uint32_t*>(&l);
+      }
+      *reinterpret_cast<uint4*>(dst + off[n]) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      if (NP == 2) *reinterpret_cast<uint4*>(dst + plane_bytes + off[n]) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+  }
+}
+
+// SK (stream-K, used by the weight-gradient contractions whose reduction runs over the packed rows): the linearised
+// (output tile, k-block) space is cut into gridDim.x equal contiguous ranges, one per CTA, so every SM gets the same number of
+// k-blocks whatever the tile count; each (CTA, tile) segment leaves a partial 128 x BN tile in a workspace slot
+// [blockIdx.x * segmax + ordinal] (row-major) and tn_reduce_kernel adds the slots of a tile in
+// CTA order into C: deterministic, no atomics.
+// A_CVT / B_CVT: the operand comes as fp32 rows (RowSrc sa / sb) and is converted by the loader warps instead of arriving as
+// TMA boxes of pre-split planes.
+template <int BN, int NP, bool A_MN, bool B_MN, bool SK, bool A_CVT, bool B_CVT>
+__global__ void __launch_bounds__((A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA, 1)
 gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Operand oa, Operand ob,
-                float* __restrict__ C, int ldc, const float* __restrict__ bias, int OI_host, const int* __restrict__ OI_dev, int OJ,
-                int R_host, const int* __restrict__ R_dev, int flags, int splits) {
+                const RowSrc sa, const RowSrc sb, float* __restrict__ C, int ldc, const float* __restrict__ bias, int OI_host, const int* __restrict__ OI_dev, int OJ,
+                int R_host, const int* __restrict__ R_dev, int flags, int segmax) {
   // Persistent: one CTA per SM walks work units u = blockIdx.x, += gridDim.x; unit = (row tile, column tile, reduction split)
   // with column tiles fastest so CTAs that run together share A rows in L2.  Two TMEM accumulators: the epilogue of unit n
   // drains one while the MMA warp fills the other.
   using cfg = Cfg<BN, NP>;
   constexpr int NS = cfg::NS;
+  constexpr uint32_t TMA_BYTES = (A_CVT ? 0 : NP * cfg::A_PLANE) + (B_CVT ? 0 : NP * cfg::B_PLANE);
+  constexpr uint32_t FULL_COUNT = (TMA_BYTES ? 1 : 0) + ((A_CVT || B_CVT) ? LOADER_WARPS : 0);
   const int OI = OI_dev ? *OI_dev : OI_host;
   const int R = R_dev ? *R_dev : R_host;
   const int tiles_i = (OI + BM - 1) / BM, tiles_j = (OJ + BN - 1) / BN;
   const int nkb_total = (R + BK - 1) / BK;
-  const int per = (nkb_total + splits - 1) / splits;
-  const int units = tiles_i * tiles_j * splits;
+  const int units = tiles_i * tiles_j;
+  const long long sk_total = (long long)units * nkb_total;
+  const long long sk_q = (sk_total + gridDim.x - 1) / gridDim.x;
+  const long long sk_lo = (long long)blockIdx.x * sk_q;
+  const long long sk_hi = sk_lo + sk_q < sk_total ? sk_lo + sk_q : sk_total;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -203,8 +266,8 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < NS; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], NTHREADS / 32 - 2); }
+    for (int s = 0; s < NS; ++s) { mbar_init(&full_bar[s], FULL_COUNT); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 2 * BN);
@@ -213,35 +276,68 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
-  auto unit_range = [&](int u, int& i0, int& j0, int& kb_begin, int& kb_end) {
-    const int z = u % splits, t = u / splits;
+  // n-th work unit of this CTA: (output tile origin, k-block range); false when the CTA has no more work
+  auto get_unit = [&](int n, int& i0, int& j0, int& kb_begin, int& kb_end) -> bool {
+    int t;
+    if (SK) {
+      if (nkb_total == 0) return false;
+      t = (int)(sk_lo / nkb_total) + n;
+      const long long t_lo = (long long)t * nkb_total;
+      const long long b = sk_lo > t_lo ? sk_lo : t_lo;
+      const long long e = sk_hi < t_lo + nkb_total ? sk_hi : t_lo + nkb_total;
+      if (b >= e) return false;
+      kb_begin = (int)(b - t_lo); kb_end = (int)(e - t_lo);
+    } else {
+      t = blockIdx.x + n * gridDim.x;
+      if (t >= units || nkb_total == 0) return false;
+      kb_begin = 0; kb_end = nkb_total;
+    }
     j0 = (t % tiles_j) * BN; i0 = (t / tiles_j) * BM;
-    kb_begin = z * per; kb_end = min(nkb_total, kb_begin + per);
+    return true;
   };
 
-  if (warp == TMA_WARP) {
-    if (lane == 0) {
+  if (warp >= LOADER_WARP0) {
+    if (A_CVT || B_CVT) {
+      const int ltid = threadIdx.x - LOADER_WARP0 * 32;
       uint32_t it = 0;
-      for (int u = blockIdx.x; u < units; u += gridDim.x) {
-        int i0, j0, kb_begin, kb_end;
-        unit_range(u, i0, j0, kb_begin, kb_end);
+      int i0, j0, kb_begin, kb_end;
+      for (int n = 0; get_unit(n, i0, j0, kb_begin, kb_end); ++n) {
         for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const int s = it % NS;
           const uint32_t ph = (it / NS) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full_bar[s], NP * (cfg::A_PLANE + cfg::B_PLANE));
+          uint8_t* a_base = smem + (size_t)s * cfg::STAGE;
+          uint8_t* b_base = a_base + NP * cfg::A_PLANE;
+          if (A_CVT) load_convert<BM, A_MN, NP>(sa, a_base, cfg::A_PLANE, i0, OI, kb * BK, R, ltid);
+          if (B_CVT) load_convert<BN, B_MN, NP>(sb, b_base, cfg::B_PLANE, j0, OJ, kb * BK, R, ltid);
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&full_bar[s]);
+        }
+      }
+    }
+  } else if (warp == TMA_WARP) {
+    if (lane == 0 && TMA_BYTES != 0) {
+      uint32_t it = 0;
+      int i0, j0, kb_begin, kb_end;
+      for (int n = 0; get_unit(n, i0, j0, kb_begin, kb_end); ++n) {
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+          const int s = it % NS;
+          const uint32_t ph = (it / NS) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          mbar_arrive_expect_tx(&full_bar[s], TMA_BYTES);
           uint8_t* a_base = smem + (size_t)s * cfg::STAGE;
           uint8_t* b_base = a_base + NP * cfg::A_PLANE;
 #pragma unroll
           for (int pl = 0; pl < NP; ++pl) {
 #pragma unroll
-            for (int bx = 0; bx < BM / 64; ++bx) {
+            for (int bx = 0; bx < (A_CVT ? 0 : BM / 64); ++bx) {
               uint8_t* dst = a_base + pl * cfg::A_PLANE + bx * 8192;
               if (!A_MN) tma_load_2d(dst, &tmA, oa.col0 + kb * BK, pl * oa.plane_rows + oa.row0 + i0 + bx * 64, &full_bar[s]);
               else       tma_load_2d(dst, &tmA, oa.col0 + i0 + bx * 64, pl * oa.plane_rows + oa.row0 + kb * BK, &full_bar[s]);
             }
 #pragma unroll
-            for (int bx = 0; bx < BN / 64; ++bx) {
+            for (int bx = 0; bx < (B_CVT ? 0 : BN / 64); ++bx) {
               uint8_t* dst = b_base + pl * cfg::B_PLANE + bx * 8192;
               if (!B_MN) tma_load_2d(dst, &tmB, ob.col0 + kb * BK, pl * ob.plane_rows + ob.row0 + j0 + bx * 64, &full_bar[s]);
               else       tma_load_2d(dst, &tmB, ob.col0 + j0 + bx * 64, pl * ob.plane_rows + ob.row0 + kb * BK, &full_bar[s]);
@@ -254,10 +350,8 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       uint32_t it = 0, tcount = 0;
-      for (int u = blockIdx.x; u < units; u += gridDim.x) {
-        int i0, j0, kb_begin, kb_end;
-        unit_range(u, i0, j0, kb_begin, kb_end);
-        if (kb_begin >= kb_end) continue;
+      int i0, j0, kb_begin, kb_end;
+      for (int n = 0; get_unit(n, i0, j0, kb_begin, kb_end); ++n) {
         const uint32_t buf = tcount & 1, aph = (tcount >> 1) & 1;
         mbar_wait(&acc_empty[buf], aph ^ 1);
         tc_fence_after();
@@ -293,49 +387,65 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else {
-    // ------------------------------------------------ epilogue warps: TMEM -> registers -> global
-    const bool vec = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+    // ------------------------------------------------ epilogue warps: TMEM -> registers -> shared (transpose) -> global
+    // tcgen05.ld hands lane r the 32 columns of accumulator row r; stored as they come, one instruction would touch 32
+    // different 128-byte lines.  Each warp therefore transposes its 32 x 32 chunk through a private 4 KB XOR-swizzled buffer
+    // (16-byte slot q of row r lives at slot q ^ (r & 7): conflict-free both ways) and writes rows out 8 lanes x 16 B = one
+    // full line per row, 4 rows per instruction.
+    float* stg = reinterpret_cast<float*>(smem + (size_t)NS * cfg::STAGE) + warp * 1024;
+    const int q = warp & 3, half = warp >> 2;
+    const int orow = lane >> 3, oq = lane & 7;               // output mapping: row within a group of 4, 16-byte slot
     uint32_t tcount = 0;
-    for (int u = blockIdx.x; u < units; u += gridDim.x) {
-      int i0, j0, kb_begin, kb_end;
-      unit_range(u, i0, j0, kb_begin, kb_end);
-      if (kb_begin >= kb_end) continue;
+    int i0, j0, kb_begin, kb_end;
+    for (int n = 0; get_unit(n, i0, j0, kb_begin, kb_end); ++n) {
       const uint32_t buf = tcount & 1, aph = (tcount >> 1) & 1;
       mbar_wait(&acc_full[buf], aph);
       tc_fence_after();
-      epilogue_rows<BN>(tmem_base + buf * BN, warp, lane, [&](int row, int col, uint32_t (&r)[32]) {
-        const int i = i0 + row;
-        if (i >= OI) return;
-        float* cp = C + (size_t)i * ldc + j0 + col;
-        if (ATOMIC) {
+      float* Cb; int ldo, oi_lim, oj_lim, ci0, cj0;
+      if (SK) {                                              // partial tile -> workspace slot, row-major [BM][BN]
+        Cb = C + ((size_t)blockIdx.x * segmax + n) * (BM * BN); ldo = BN; oi_lim = BM; oj_lim = BN; ci0 = 0; cj0 = 0;
+      } else {
+        Cb = C; ldo = ldc; oi_lim = OI; oj_lim = OJ; ci0 = i0; cj0 = j0;
+      }
+      const bool vec = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN / 2; c0 += 32) {
+        uint32_t r[32];
+        const int col = half * (BN / 2) + c0;
+        tmem_ld32(tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)col, r);
 #pragma unroll
-          for (int e = 0; e < 32; ++e)
-            if (j0 + col + e < OJ) atomicAdd(cp + e, __uint_as_float(r[e]));
-          return;
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        __syncwarp();
+        const int nn = cj0 + col + oq * 4;                   // first of this lane's 4 output columns
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!SK && bias) {
+          if (nn + 3 < oj_lim) bv = make_float4(bias[nn], bias[nn + 1], bias[nn + 2], bias[nn + 3]);
+          else { if (nn < oj_lim) bv.x = bias[nn]; if (nn + 1 < oj_lim) bv.y = bias[nn + 1]; if (nn + 2 < oj_lim) bv.z = bias[nn + 2]; }
         }
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const int n = j0 + col + j;
-          if (n >= OJ) break;
-          float o[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            float x = __uint_as_float(r[j + e]);
-            if (bias && n + e < OJ) x += bias[n + e];
-            if (flags & GEMM_RELU) x = fmaxf(x, 0.f);
-            o[e] = x;
+        for (int r4 = 0; r4 < 32; r4 += 4) {
+          const int row = r4 + orow;
+          float4 w = *reinterpret_cast<const float4*>(stg + row * 32 + ((oq ^ (row & 7)) << 2));
+          const int i = ci0 + q * 32 + row;
+          if (i >= oi_lim || nn >= oj_lim) continue;
+          float* cp = Cb + (size_t)i * ldo + nn;
+          if (!SK) {
+            w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
+            if (flags & GEMM_RELU) { w.x = fmaxf(w.x, 0.f); w.y = fmaxf(w.y, 0.f); w.z = fmaxf(w.z, 0.f); w.w = fmaxf(w.w, 0.f); }
           }
-          if (vec && n + 3 < OJ) {
-            float4 w = make_float4(o[0], o[1], o[2], o[3]);
-            if (flags & GEMM_ACCUM) { const float4 c = *reinterpret_cast<const float4*>(cp + j); w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w; }
-            *reinterpret_cast<float4*>(cp + j) = w;
+          if (vec && nn + 3 < oj_lim) {
+            if (!SK && (flags & GEMM_ACCUM)) { const float4 c = *reinterpret_cast<const float4*>(cp); w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w; }
+            *reinterpret_cast<float4*>(cp) = w;
           } else {
+            const float o[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-              if (n + e < OJ) cp[j + e] = (flags & GEMM_ACCUM) ? cp[j + e] + o[e] : o[e];
+              if (nn + e < oj_lim) cp[e] = (!SK && (flags & GEMM_ACCUM)) ? cp[e] + o[e] : o[e];
           }
         }
-      });
+        __syncwarp();
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
@@ -461,18 +571,69 @@ int split_to_scratch(int which, const RowSrc& A, int M_host, const int* M_dev, i
   return split_rows(A, M_host, M_dev, K, *out, 0, want_lo, st);
 }
 
-template <int BN, int NP, bool A_MN, bool B_MN, bool ATOMIC>
-int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand ob, float* C, int ldc, const float* bias, int OI_host,
-               const int* OI_dev, int OJ, int R_host, const int* R_dev, int flags, int splits, cudaStream_t st) {
-  auto kern = gemm_tma_kernel<BN, NP, A_MN, B_MN, ATOMIC>;
+template <int BN, int NP, bool A_MN, bool B_MN, bool SK, bool A_CVT, bool B_CVT>
+int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand ob, const RowSrc& sa, const RowSrc& sb, float* C, int ldc,
+               const float* bias, int OI_host, const int* OI_dev, int OJ, int R_host, const int* R_dev, int flags, int grid_sk, int segmax,
+               cudaStream_t st) {
+  auto kern = gemm_tma_kernel<BN, NP, A_MN, B_MN, SK, A_CVT, B_CVT>;
   static bool configured = false;
   if (!configured) { if (int r = set_smem(kern, Cfg<BN, NP>::SMEM)) return r; configured = true; }
-  long units = (long)((OJ + BN - 1) / BN) * ((OI_host + BM - 1) / BM) * splits;
-  const int grid = units < kNumSMs ? (int)units : kNumSMs;
-  kern<<<grid, NTHREADS, Cfg<BN, NP>::SMEM, st>>>(*ma, *mb, oa, ob, C, ldc, bias, OI_host, OI_dev, OJ, R_host, R_dev, flags, splits);
+  static const CUtensorMap dummy = {};                       // stands in for the map of an operand converted in-kernel
+  long units = (long)((OJ + BN - 1) / BN) * ((OI_host + BM - 1) / BM);
+  const int grid = SK ? grid_sk : (units < kNumSMs ? (int)units : kNumSMs);
+  kern<<<grid, (A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA, Cfg<BN, NP>::SMEM, st>>>(
+      A_CVT ? dummy : *ma, B_CVT ? dummy : *mb, oa, ob, sa, sb, C, ldc, bias, OI_host, OI_dev, OJ, R_host, R_dev, flags, segmax);
   PATHS_LAUNCH_CK();
   return 0;
 }
+
+// C[tile] += sum over the stream-K segments of the tile, in a fixed order (deterministic).  A block owns 256 / PG consecutive
+// float4 outputs of one tile; PG thread groups each sum every PG-th segment and are combined through shared memory.
+template <int BN, int PG>
+__global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict__ ws, float* __restrict__ C, int ldc, int NI, int NJ,
+                                                        int R_host, const int* __restrict__ R_dev, int G, int segmax) {
+  constexpr int OUT = 256 / PG;
+  const int R = R_dev ? *R_dev : R_host;
+  const int nkb = (R + BK - 1) / BK;
+  if (nkb == 0) return;
+  const int tiles_j = (NJ + BN - 1) / BN;
+  const int t = blockIdx.x;
+  const int units = ((NI + BM - 1) / BM) * tiles_j;
+  const long long total = (long long)units * nkb, q = (total + G - 1) / G;
+  const long long t_lo = (long long)t * nkb;
+  const int c_first = (int)(t_lo / q), c_last = (int)((t_lo + nkb - 1) / q);
+  const int o = threadIdx.x % OUT, g = threadIdx.x / OUT;
+  const int elem = blockIdx.y * OUT + o;                 // float4 index inside the tile, row-major
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int c = c_first + g; c <= c_last; c += PG) {
+    const int ord = t - (int)(((long long)c * q) / nkb);
+    const float4 v = __ldcs(ws + ((size_t)c * segmax + ord) * (BM * BN / 4) + elem);
+    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  }
+  if (PG > 1) {
+    __shared__ float4 red[PG][OUT];
+    red[g][o] = acc;
+    __syncthreads();
+    if (g != 0) return;
+#pragma unroll
+    for (int k = 1; k < PG; ++k) { const float4 v = red[k][o]; acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
+  }
+  const int row = elem / (BN / 4), c4 = elem % (BN / 4);
+  const int i = (t / tiles_j) * BM + row, j = (t % tiles_j) * BN + c4 * 4;
+  if (i >= NI || j >= NJ) return;
+  float* cp = C + (size_t)i * ldc + j;
+  const bool vec = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+  if (vec && j + 3 < NJ) {
+    float4 w = *reinterpret_cast<float4*>(cp);
+    w.x += acc.x; w.y += acc.y; w.z += acc.z; w.w += acc.w;
+    *reinterpret_cast<float4*>(cp) = w;
+  } else {
+    const float av[4] = {acc.x, acc.y, acc.z, acc.w};
+    for (int k = 0; k < 4 && j + k < NJ; ++k) cp[k] += av[k];
+  }
+}
+
+struct TnWs { void* p; size_t bytes; } g_tn_ws = {nullptr, 0};
 
 }  // namespace
 
@@ -550,9 +711,9 @@ int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Plane
   return 0;
 }
 
-// C[M,N] (+)= act(A . B^T + bias), A given as planes (columns [a_col0, a_col0 + K))
-int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
-                 const int* M_dev, int N, int K, int flags, cudaStream_t st) {
+// C[M,N] (+)= act(A . B^T + bias); A either as planes (columns [a_col0, a_col0 + K)) or as fp32 rows converted in-kernel
+static int nt_impl(int passes, const Planes* A, int a_col0, const RowSrc* Asrc, const float* B, int ldb, int b_kn, float* C, int ldc,
+                   const float* bias, int M_host, const int* M_dev, int N, int K, int flags, cudaStream_t st) {
   if (M_host <= 0 || N <= 0) return 0;
   const Packed* pk; int r0, c0;
   {
@@ -560,14 +721,23 @@ int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ld
     pk = find_packed(B, ldb, &r0, &c0);
   }
   PATHS_REQUIRE(pk, "gemm_nt_tc: weight matrix was not registered for the tensor-core path");
-  PATHS_REQUIRE(A.p && a_col0 % 8 == 0 && M_host <= A.rows, "gemm_nt_tc: bad activation planes");
-  const CUtensorMap* ma;
-  if (int r = cached_map(&ma, A.p, 2 * A.rows, a_col0 + K, A.ldp)) return r;
-  Operand oa; oa.row0 = 0; oa.col0 = a_col0; oa.plane_rows = A.rows;
+  const CUtensorMap* ma = nullptr;
+  Operand oa; oa.row0 = 0; oa.col0 = a_col0; oa.plane_rows = 0;
+  RowSrc none = row_src(nullptr, 0, 0);
+  if (A) {
+    PATHS_REQUIRE(A->p && a_col0 % 8 == 0 && M_host <= A->rows, "gemm_nt_tc: bad activation planes");
+    if (int r = cached_map(&ma, A->p, 2 * A->rows, a_col0 + K, A->ldp)) return r;
+    oa.plane_rows = A->rows;
+  }
   Operand ob; ob.row0 = r0; ob.col0 = c0; ob.plane_rows = pk->R;
   const bool big = N > 128;
-#define NT_CASE(BN_, NP_, MN_) \
-  return launch_tma<BN_, NP_, false, MN_, false>(ma, &pk->map, oa, ob, C, ldc, bias, M_host, M_dev, N, K, nullptr, flags, 1, st)
+#define NT_CASE(BN_, NP_, MN_)                                                                                                         \
+  do {                                                                                                                                 \
+    if (A) return launch_tma<BN_, NP_, false, MN_, false, false, false>(ma, &pk->map, oa, ob, none, none, C, ldc, bias, M_host, M_dev, \
+                                                                        N, K, nullptr, flags, 0, 0, st);                             \
+    return launch_tma<BN_, NP_, false, MN_, false, true, false>(nullptr, &pk->map, oa, ob, *Asrc, none, C, ldc, bias, M_host, M_dev, N, \
+                                                                K, nullptr, flags, 0, 0, st);                                        \
+  } while (0)
   if (passes == 3) {
     if (big) { if (b_kn) NT_CASE(256, 2, true); else NT_CASE(256, 2, false); }
     else     { if (b_kn) NT_CASE(128, 2, true); else NT_CASE(128, 2, false); }
@@ -579,45 +749,103 @@ int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ld
   return 0;
 }
 
+int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
+                 const int* M_dev, int N, int K, int flags, cudaStream_t st) {
+  return nt_impl(passes, &A, a_col0, nullptr, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
+}
+
+// fp32 rows qualify for the in-kernel conversion when every 8-element chunk lies inside one 16-byte-aligned source row
+static bool cvt_ok(const RowSrc& A) {
+  if (A.k0 % 8 != 0 || A.ld0 % 4 != 0 || (A.p1 && A.ld1 % 4 != 0)) return false;
+  return !(reinterpret_cast<uintptr_t>(A.p0) & 15) && !(A.p1 && (reinterpret_cast<uintptr_t>(A.p1) & 15));
+}
+
 int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
                const int* M_dev, int N, int K, int flags, cudaStream_t st) {
   if (M_host <= 0 || N <= 0) return 0;
+  if (cvt_ok(A)) return nt_impl(passes, nullptr, 0, &A, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
   Planes pa;
   if (int r = split_to_scratch(0, A, M_host, M_dev, K, passes == 3, &pa, st)) return r;
   return gemm_nt_tc_p(passes, pa, 0, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
 }
 
-// C[NI,NJ] += P^T . Q, both operands as planes (column windows p_col0 / q_col0)
-int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q_col0, float* C, int ldc, int M_host, const int* M_dev, int NI,
-                 int NJ, cudaStream_t st) {
+// Stream-K plan of a weight-gradient contraction: CTAs and workspace slots per CTA.
+static void tn_plan(int NI, int NJ, int M_host, int* G, int* segmax) {
+  const int BN = NJ > 128 ? 256 : 128;
+  const int tiles = ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
+  const long total = (long)tiles * ((M_host + BK - 1) / BK);
+  long g = total / 4;                            // at least ~4 k-blocks per CTA
+  if (g > kNumSMs) g = kNumSMs;
+  if (g < 1) g = 1;
+  *G = (int)g;
+  *segmax = (tiles + *G - 1) / *G + 2;
+}
+size_t tn_workspace_bytes(int NI, int NJ, int M_host) {
+  int G, segmax;
+  tn_plan(NI, NJ, M_host, &G, &segmax);
+  return (size_t)G * segmax * BM * (NJ > 128 ? 256 : 128) * sizeof(float);
+}
+void set_tn_workspace(void* p, size_t bytes) { g_tn_ws.p = p; g_tn_ws.bytes = bytes; }
+
+// C[NI,NJ] += P^T . Q; operands as planes (column windows p_col0 / q_col0) or as fp32 rows converted in-kernel
+static int tn_impl(int passes, const Planes* P, int p_col0, const Planes* Q, int q_col0, const RowSrc* Ps, const RowSrc* Qs, float* C, int ldc,
+                   int M_host, const int* M_dev, int NI, int NJ, cudaStream_t st) {
   if (M_host <= 0 || NI <= 0 || NJ <= 0) return 0;
-  PATHS_REQUIRE(P.p && Q.p && p_col0 % 8 == 0 && q_col0 % 8 == 0 && M_host <= P.rows && M_host <= Q.rows, "gemm_tn_tc: bad activation planes");
-  const CUtensorMap *ma, *mb;
-  if (int r = cached_map(&ma, P.p, 2 * P.rows, p_col0 + NI, P.ldp)) return r;
-  if (int r = cached_map(&mb, Q.p, 2 * Q.rows, q_col0 + NJ, Q.ldp)) return r;
+  const CUtensorMap *ma = nullptr, *mb = nullptr;
   Operand oa, ob;
-  oa.row0 = 0; oa.col0 = p_col0; oa.plane_rows = P.rows;
-  ob.row0 = 0; ob.col0 = q_col0; ob.plane_rows = Q.rows;
+  oa.row0 = 0; oa.col0 = p_col0; oa.plane_rows = 0;
+  ob.row0 = 0; ob.col0 = q_col0; ob.plane_rows = 0;
+  RowSrc none = row_src(nullptr, 0, 0);
+  if (P) {
+    PATHS_REQUIRE(P->p && Q && Q->p && p_col0 % 8 == 0 && q_col0 % 8 == 0 && M_host <= P->rows && M_host <= Q->rows,
+                  "gemm_tn_tc: bad activation planes");
+    if (int r = cached_map(&ma, P->p, 2 * P->rows, p_col0 + NI, P->ldp)) return r;
+    if (int r = cached_map(&mb, Q->p, 2 * Q->rows, q_col0 + NJ, Q->ldp)) return r;
+    oa.plane_rows = P->rows; ob.plane_rows = Q->rows;
+  }
   const bool big = NJ > 128;
   const int BN = big ? 256 : 128;
   const int tiles = ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
-  int splits = (2 * kNumSMs + tiles - 1) / tiles;
-  const int max_splits = (M_host + 4 * BK - 1) / (4 * BK);
-  if (splits > max_splits) splits = max_splits;
-  if (splits < 1) splits = 1;
-#define TN_CASE(BN_, NP_) \
-  return launch_tma<BN_, NP_, true, true, true>(ma, mb, oa, ob, C, ldc, nullptr, NI, nullptr, NJ, M_host, M_dev, 0, splits, st)
+  int G, segmax;
+  tn_plan(NI, NJ, M_host, &G, &segmax);
+  const size_t need = (size_t)G * segmax * BM * BN * sizeof(float);
+  PATHS_REQUIRE(g_tn_ws.p && need <= g_tn_ws.bytes, "gemm_tn_tc: stream-K workspace too small: need %zu bytes, have %zu", need, g_tn_ws.bytes);
+  float* ws = static_cast<float*>(g_tn_ws.p);
+#define TN_CASE(BN_, NP_)                                                                                                              \
+  do {                                                                                                                                 \
+    int r;                                                                                                                             \
+    if (P) r = launch_tma<BN_, NP_, true, true, true, false, false>(ma, mb, oa, ob, none, none, ws, 0, nullptr, NI, nullptr, NJ, M_host, \
+                                                                    M_dev, 0, G, segmax, st);                                        \
+    else r = launch_tma<BN_, NP_, true, true, true, true, true>(nullptr, nullptr, oa, ob, *Ps, *Qs, ws, 0, nullptr, NI, nullptr, NJ,   \
+                                                                M_host, M_dev, 0, G, segmax, st);                                    \
+    if (r) return r;                                                                                                                   \
+    if (4 * tiles >= G)                                                                                                                \
+      tn_reduce_kernel<BN_, 1><<<dim3(tiles, BM * BN_ / 4 / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(ws), C, ldc, NI, NJ,  \
+                                                                               M_host, M_dev, G, segmax);                             \
+    else                                                                                                                               \
+      tn_reduce_kernel<BN_, 8><<<dim3(tiles, BM * BN_ / 4 / 32), 256, 0, st>>>(reinterpret_cast<const float4*>(ws), C, ldc, NI, NJ,   \
+                                                                              M_host, M_dev, G, segmax);                              \
+    PATHS_LAUNCH_CK();                                                                                                                 \
+    return 0;                                                                                                                          \
+  } while (0)
   if (passes == 3) { if (big) TN_CASE(256, 2); else TN_CASE(128, 2); }
   else             { if (big) TN_CASE(256, 1); else TN_CASE(128, 1); }
 #undef TN_CASE
   return 0;
 }
 
+int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q_col0, float* C, int ldc, int M_host, const int* M_dev, int NI,
+                 int NJ, cudaStream_t st) {
+  return tn_impl(passes, &P, p_col0, &Q, q_col0, nullptr, nullptr, C, ldc, M_host, M_dev, NI, NJ, st);
+}
+
 int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
                cudaStream_t st) {
   if (M_host <= 0 || NI <= 0 || NJ <= 0) return 0;
+  const RowSrc Ps = row_src(P, ldp, NI);
+  if (cvt_ok(Ps) && cvt_ok(Q)) return tn_impl(passes, nullptr, 0, nullptr, 0, &Ps, &Q, C, ldc, M_host, M_dev, NI, NJ, st);
   Planes pp, pq;
-  if (int r = split_to_scratch(0, row_src(P, ldp, NI), M_host, M_dev, NI, passes == 3, &pp, st)) return r;
+  if (int r = split_to_scratch(0, Ps, M_host, M_dev, NI, passes == 3, &pp, st)) return r;
   if (int r = split_to_scratch(1, Q, M_host, M_dev, NJ, passes == 3, &pq, st)) return r;
   return gemm_tn_tc_p(passes, pp, 0, pq, 0, C, ldc, M_host, M_dev, NI, NJ, st);
 }

@@ -55,6 +55,7 @@ int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* h
 // Slide s owns token rows [seg[s]+s, seg[s+1]+s+1).  nq_mode 0: every token is a query; 1: only token 0 of each slide
 // (the last decoder layer is read at the special token only, aggregator.py:75); outputs are then compact [B, d].
 int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st);
+bool attn_bwd_writes_all(int d, int heads);
 int attn_bwd(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
              int heads, int B, int max_T, int nq_mode, cudaStream_t st);
 
