@@ -186,47 +186,47 @@ struct Operand { int row0, col0, plane_rows; };
 // included), split it into bf16 (hi, lo) and store it in the SWIZZLE_128B layout a TMA box would have produced -- no separate
 // split pass, no bf16 copy in HBM.  K-major tile: [W rows (output index) x 64 k]; MN-major tile: [64 k x W cols (output index)].
 // Work item = one 16-byte bf16 chunk (8 elements = two float4 loads); W * 8 items per tile, 4 per thread per batch.
-template <int W, bool MN, int NP>
-__device__ __forceinline__ void load_convert(const RowSrc& S, uint8_t* dst, int plane_bytes, int o0, int o_lim, int r0, int r_lim, int ltid) {
+constexpr int LB = 4;                                       // items per thread per batch
+struct CvtRegs { float4 x[LB][2]; uint32_t off[LB]; };
+
+// issue the global loads of batch `bi` (items bi*LB .. bi*LB+LB-1 of this thread) of a W-wide tile
+template <int W, bool MN>
+__device__ __forceinline__ void cvt_issue(const RowSrc& S, int bi, int o0, int o_lim, int r0, int r_lim, int ltid, CvtRegs& g) {
   constexpr int NLT = LOADER_WARPS * 32;
-  constexpr int PER = W * 8 / NLT;
-  static_assert(PER % 4 == 0 || PER < 4, "loader batches");
-  constexpr int BATCH = PER < 4 ? PER : 4;
-#pragma unroll 1
-  for (int b0 = 0; b0 < PER; b0 += BATCH) {
-    float4 x[BATCH][2];
-    uint32_t off[BATCH];
 #pragma unroll
-    for (int n = 0; n < BATCH; ++n) {
-      const int item = ltid + (b0 + n) * NLT;
-      int o, k;
-      if (!MN) {
-        const int r = item >> 3, ch = item & 7;
-        o = o0 + r; k = r0 + ch * 8;
-        off[n] = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((ch ^ (r & 7)) << 4));
-      } else {
-        const int kr = item / (W / 8), ch = item % (W / 8);
-        o = o0 + ch * 8; k = r0 + kr;
-        off[n] = (uint32_t)((ch >> 3) * 8192 + (kr >> 3) * 1024 + (kr & 7) * 128 + (((ch & 7) ^ (kr & 7)) << 4));
-      }
-      const float* p = (o < o_lim && k < r_lim) ? (MN ? rowsrc_ptr(S, k, o) : rowsrc_ptr(S, o, k)) : nullptr;
-      x[n][0] = x[n][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (p) { x[n][0] = __ldg(reinterpret_cast<const float4*>(p)); x[n][1] = __ldg(reinterpret_cast<const float4*>(p) + 1); }
+  for (int n = 0; n < LB; ++n) {
+    const int item = ltid + (bi * LB + n) * NLT;
+    int o, k;
+    if (!MN) {
+      const int r = item >> 3, ch = item & 7;
+      o = o0 + r; k = r0 + ch * 8;
+      g.off[n] = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((ch ^ (r & 7)) << 4));
+    } else {
+      const int kr = item / (W / 8), ch = item % (W / 8);
+      o = o0 + ch * 8; k = r0 + kr;
+      g.off[n] = (uint32_t)((ch >> 3) * 8192 + (kr >> 3) * 1024 + (kr & 7) * 128 + (((ch & 7) ^ (kr & 7)) << 4));
     }
+    const float* p = (o < o_lim && k < r_lim) ? (MN ? rowsrc_ptr(S, k, o) : rowsrc_ptr(S, o, k)) : nullptr;
+    g.x[n][0] = g.x[n][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p) { g.x[n][0] = __ldg(reinterpret_cast<const float4*>(p)); g.x[n][1] = __ldg(reinterpret_cast<const float4*>(p) + 1); }
+  }
+}
+// split the loaded batch into (hi, lo) and store it into the swizzled operand tile
+template <int NP>
+__device__ __forceinline__ void cvt_store(const CvtRegs& g, uint8_t* dst, int plane_bytes) {
 #pragma unroll
-    for (int n = 0; n < BATCH; ++n) {
-      const float v[8] = {x[n][0].x, x[n][0].y, x[n][0].z, x[n][0].w, x[n][1].x, x[n][1].y, x[n][1].z, x[n][1].w};
-      uint32_t hi[4], lo[4];
+  for (int n = 0; n < LB; ++n) {
+    const float v[8] = {g.x[n][0].x, g.x[n][0].y, g.x[n][0].z, g.x[n][0].w, g.x[n][1].x, g.x[n][1].y, g.x[n][1].z, g.x[n][1].w};
+    uint32_t hi[4], lo[4];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
-        const float2 hf = __bfloat1622float2(h);
-        const __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * e] - hf.x, v[2 * e + 1] - hf.y);
-        hi[e] = *reinterpret_cast<const uint32_t*>(&h); lo[e] = *reinterpret_cast<const uint32_t*>(&l);
-      }
-      *reinterpret_cast<uint4*>(dst + off[n]) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-      if (NP == 2) *reinterpret_cast<uint4*>(dst + plane_bytes + off[n]) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    for (int e = 0; e < 4; ++e) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+      const float2 hf = __bfloat1622float2(h);
+      const __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * e] - hf.x, v[2 * e + 1] - hf.y);
+      hi[e] = *reinterpret_cast<const uint32_t*>(&h); lo[e] = *reinterpret_cast<const uint32_t*>(&l);
     }
+    *reinterpret_cast<uint4*>(dst + g.off[n]) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    if (NP == 2) *reinterpret_cast<uint4*>(dst + plane_bytes + g.off[n]) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
   }
 }
 
@@ -298,22 +298,49 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
   if (warp >= LOADER_WARP0) {
     if (A_CVT || B_CVT) {
+      // Software-pipelined by one batch: the loads of batch b+1 are in flight while batch b is converted and stored, so the
+      // loader never sits idle behind a DRAM round trip.  A batch = LB 16-byte chunks per thread of one operand of one k-block.
+      constexpr int NLT = LOADER_WARPS * 32;
+      constexpr int NA = A_CVT ? (BM * 8 / NLT) / LB : 0, NB = B_CVT ? (BN * 8 / NLT) / LB : 0, NSUB = NA + NB;
+      static_assert((BM * 8 / NLT) % LB == 0 && (BN * 8 / NLT) % LB == 0, "loader batch size");
       const int ltid = threadIdx.x - LOADER_WARP0 * 32;
-      uint32_t it = 0;
-      int i0, j0, kb_begin, kb_end;
-      for (int n = 0; get_unit(n, i0, j0, kb_begin, kb_end); ++n) {
-        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
-          const int s = it % NS;
-          const uint32_t ph = (it / NS) & 1;
-          mbar_wait(&empty_bar[s], ph ^ 1);
-          uint8_t* a_base = smem + (size_t)s * cfg::STAGE;
-          uint8_t* b_base = a_base + NP * cfg::A_PLANE;
-          if (A_CVT) load_convert<BM, A_MN, NP>(sa, a_base, cfg::A_PLANE, i0, OI, kb * BK, R, ltid);
-          if (B_CVT) load_convert<BN, B_MN, NP>(sb, b_base, cfg::B_PLANE, j0, OJ, kb * BK, R, ltid);
+      struct Pos { int n, i0, j0, kb, kb_end, sub; uint32_t it; bool ok; };
+      Pos cur; cur.n = 0; cur.sub = 0; cur.it = 0;
+      { int kb0; cur.ok = get_unit(0, cur.i0, cur.j0, kb0, cur.kb_end); cur.kb = kb0; }
+      auto advance = [&](Pos p) -> Pos {
+        if (++p.sub < NSUB) return p;
+        p.sub = 0; ++p.it;
+        if (++p.kb < p.kb_end) return p;
+        ++p.n;
+        int kb0; p.ok = get_unit(p.n, p.i0, p.j0, kb0, p.kb_end); p.kb = kb0;
+        return p;
+      };
+      auto issue = [&](const Pos& p, CvtRegs& g) {
+        if (A_CVT && p.sub < NA) cvt_issue<BM, A_MN>(sa, p.sub, p.i0, OI, p.kb * BK, R, ltid, g);
+        else if (B_CVT) cvt_issue<BN, B_MN>(sb, p.sub - NA, p.j0, OJ, p.kb * BK, R, ltid, g);
+      };
+      auto retire = [&](const Pos& p, const CvtRegs& g) {
+        const int s = p.it % NS;
+        if (p.sub == 0) mbar_wait(&empty_bar[s], ((p.it / NS) & 1) ^ 1);
+        uint8_t* a_base = smem + (size_t)s * cfg::STAGE;
+        if (A_CVT && p.sub < NA) cvt_store<NP>(g, a_base, cfg::A_PLANE);
+        else cvt_store<NP>(g, a_base + NP * cfg::A_PLANE, cfg::B_PLANE);
+        if (p.sub == NSUB - 1) {
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) mbar_arrive(&full_bar[s]);
         }
+      };
+      CvtRegs g0, g1;
+      if (cur.ok) issue(cur, g0);
+      while (cur.ok) {
+        Pos nxt = advance(cur);
+        if (nxt.ok) issue(nxt, g1);
+        retire(cur, g0);
+        if (!nxt.ok) break;
+        cur = advance(nxt);
+        if (cur.ok) issue(cur, g0);
+        retire(nxt, g1);
       }
     }
   } else if (warp == TMA_WARP) {
