@@ -251,6 +251,11 @@ def main():
     gate_ms, gate_n = eng.profile_read(0)
     dw_ms, dw_n = eng.profile_read(1)
     eng.profile_read(2)
+    # in-situ region times (CUDA events on the stream each region runs on; decoder regions overlap the LSTM chain)
+    regions = {}
+    for tag, name in [(3, "lstm_fwd"), (4, "decoder_fwd"), (5, "select_gather"), (6, "decoder_bwd"), (7, "lstm_bwd")]:
+        r_ms, _ = eng.profile_read(tag)
+        regions[name] = r_ms / args.steps
     value = B * world * args.steps / (ms / 1e3)
 
     # ---- roofline of the dominant kernel: the LSTM gate contraction G = [x || h_parent] . Wg^T  (tcgen05, TMEM accumulators)
@@ -269,7 +274,8 @@ def main():
                 "peak_source": pk_src + ", bf16 dense sustained", "kernel_ms_per_step": gate_ms / args.steps,
                 "kernel_share_of_step": gate_ms / ms, "algorithmic_flops_per_step": flops_per_step,
                 "mma_passes": passes, "tensor_issue_frac": (achieved * passes / peak) if passes and peak else None,
-                "dW_kernel_tflops": (flops_per_step * args.steps / (dw_ms / 1e3) / 1e12) if dw_ms > 0 else None}
+                "dW_kernel_tflops": (flops_per_step * args.steps / (dw_ms / 1e3) / 1e12) if dw_ms > 0 else None,
+                "region_ms_per_step": regions}
 
     # ---- end-to-end through the reference-facing API with host buffers
     e2e = None

@@ -147,7 +147,10 @@ int64_t paths_engine_launch_count(paths_engine_t* e);
 
 /* Per-kernel device timing for the roofline report: while enabled, the engine brackets the tagged kernels with CUDA events
  * on the launch stream; profile_read sums (and clears) the elapsed milliseconds and launch count of one tag. */
-enum paths_prof_tag { PATHS_PROF_GATES_FWD = 0, PATHS_PROF_GATES_DW, PATHS_PROF_GATES_DH, PATHS_PROF__COUNT };
+enum paths_prof_tag { PATHS_PROF_GATES_FWD = 0, PATHS_PROF_GATES_DW, PATHS_PROF_GATES_DH,
+                      /* whole regions of a step (each includes every kernel launched inside it) */
+                      PATHS_PROF_LSTM_FWD, PATHS_PROF_DEC_FWD, PATHS_PROF_SELECT, PATHS_PROF_DEC_BWD, PATHS_PROF_LSTM_BWD,
+                      PATHS_PROF__COUNT };
 int paths_engine_profile(paths_engine_t* e, int on);
 int paths_engine_profile_read(paths_engine_t* e, int tag, double* total_ms, int64_t* launches);
 
@@ -161,6 +164,17 @@ int paths_adamw_step(float* params, const float* grads, float* exp_avg, float* e
 
 /* Occupancy bitmap of one [W*H, D] grid: bit c set iff any of the D floats of cell c is non-zero; *count += popcount. */
 int paths_build_occupancy(const float* grid, int cells, int D, uint32_t* bits, int32_t* count, void* stream);
+
+/* Importance heat-map compositing (replaces the numpy block of heatmap_visualise.py:142-178).  locs_yx: [n_patches, 2] int32
+ * (y, x) patch origins in the pixel space of their own level, patches of level d at rows [level_off[d], level_off[d+1]);
+ * importance: [n_patches] float32.  Every patch fills its (patch_size >> d)-sized square of an [L, H, W] canvas in level-0
+ * pixel space with importance + 1e-4 (later patches overwrite earlier ones), finer levels are folded into coarser ones with
+ * weight 0.5 wherever they are non-zero, zeros of the result become the smallest positive value.  out: [H, W] float64,
+ * alpha: [H, W] float32 (0.5 where covered, else 0).  workspace: paths_heatmap_workspace_bytes(L, H, W) device bytes. */
+size_t paths_heatmap_workspace_bytes(int L, int H, int W);
+int paths_heatmap_composite(const int32_t* locs_yx, const float* importance, const int32_t* level_off, int32_t n_patches, int L,
+                            int patch_size, int H, int W, void* workspace, size_t workspace_bytes, double* out, float* alpha,
+                            void* stream);
 
 /* Stand-alone dense contractions (tests; the engine uses the same kernels).
  * C[M,N] (+)= act(A[M,K] . B^T + bias) with B [N,K] (b_kn = 0) or [K,N] (b_kn = 1); flags: 1 relu, 2 accumulate. */

@@ -53,7 +53,7 @@ SYMBOLS = ["paths_last_error", "paths_abi_version", "paths_engine_workspace_byte
            "paths_engine_begin_padded", "paths_engine_level_forward", "paths_engine_select", "paths_engine_loss",
            "paths_engine_level_backward", "paths_engine_forward", "paths_engine_backward", "paths_engine_buffer",
            "paths_engine_set_precision", "paths_engine_launch_count", "paths_engine_profile", "paths_engine_profile_read", "paths_build_occupancy", "paths_gemm_nt",
-           "paths_gemm_tn", "paths_adamw_step"]
+           "paths_gemm_tn", "paths_adamw_step", "paths_heatmap_workspace_bytes", "paths_heatmap_composite"]
 
 
 def lib() -> C.CDLL:
@@ -94,6 +94,9 @@ def lib() -> C.CDLL:
     L.paths_gemm_nt.argtypes = [i32, vp, i32, vp, i32, i32, vp, i32, vp, i32, i32, i32, i32, vp]
     L.paths_gemm_tn.argtypes = [i32, vp, i32, vp, i32, vp, i32, i32, i32, i32, vp]
     L.paths_adamw_step.argtypes = [vp, vp, vp, vp, i64, i64, C.POINTER(C.c_int64), i32, f32, f32, f32, f32, f32, i32, vp]
+    L.paths_heatmap_workspace_bytes.restype = sz
+    L.paths_heatmap_workspace_bytes.argtypes = [i32, i32, i32]
+    L.paths_heatmap_composite.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, vp, sz, vp, vp, vp]
     _lib = L
     return L
 

@@ -99,6 +99,12 @@ struct Level {
   float *xhf, *rsf, *z, *F, *logits, *dlogits, *dHrow, *dCrow;
   float *dFc;                        // slide_ctx_mode "concat": d loss / d F_l written by the last level's head backward
   Planes AxhP, CnP, YP;              // tensor-core operand planes written by the producers: [x || h_parent], c', Y
+  // decoder scratch, one set per level so the levels' aggregators can run concurrently on their own streams
+  float *A1, *Fo;                                        // forward temporaries [tokens, d]
+  float *ga, *gb, *gO, *gt, *dqkv, *dHf, *Dvec;          // backward, token-shaped
+  float *dFl, *dy3s;                                     // [B, d]: d loss / d F_l, gradient entering the last decoder layer
+  const float* dtok;                                     // gradient w.r.t. the level's tokens (points into ga / gt)
+  char* tn_ws; size_t tn_ws_bytes;                       // stream-K workspace of this level's decoder weight gradients
 };
 
 struct LayerP { const float *Wqkv, *bqkv, *Wo, *bo, *bcross, *W1, *b1, *W2, *b2, *n1w, *n1b, *n2w, *n2b, *n3w, *n3b; };
@@ -121,10 +127,12 @@ struct paths_engine {
   Level lv[PATHS_MAX_LEVELS];
   // shared scratch
   int maxcap, maxtok;
-  float *A1, *Fo;                                       // forward temporaries [maxtok, d]
-  float *dY, *dP, *dG, *dCn, *dHc, *dCc, *dUV;          // backward, row-shaped
-  float *ga, *gb, *gO, *gt, *dqkv, *dHf, *Dvec;         // backward, token-shaped
-  float *dF, *dz, *dy3s;                                 // [B, d]
+  float *dY, *dP, *dG, *dCn, *dHc, *dCc, *dUV;          // backward, row-shaped (LSTM block: main stream only)
+  // the aggregator (decoder) of a level depends only on that level's tokens, and nothing downstream but the slide vector
+  // depends on it: each level's decoder runs on its own stream, overlapping the LSTM / select chain of the deeper levels
+  cudaStream_t side[PATHS_MAX_LEVELS];
+  cudaEvent_t ev_tok[PATHS_MAX_LEVELS], ev_z[PATHS_MAX_LEVELS], ev_head[PATHS_MAX_LEVELS], ev_dtok[PATHS_MAX_LEVELS];
+  bool have_streams;
   Planes dGP, dPP, dUVP;                                 // gradient planes written by the pointwise backward kernels
   float *hazards, *loss, *loss_per;
   int *overflow, *slide_cnt, *slide_fb;
@@ -183,6 +191,20 @@ size_t carve(paths_engine* e, char* base) {
     v.F = b.take<float>((size_t)B * d); v.logits = b.take<float>((size_t)B * dm.nl); v.dlogits = b.take<float>((size_t)B * dm.nl);
     v.dHrow = b.take<float>(cap * D); v.dCrow = b.take<float>(cap * C);
     v.dFc = b.take<float>((size_t)B * d);
+    v.A1 = b.take<float>(tokcap * d); v.Fo = b.take<float>(tokcap * d);
+    v.ga = b.take<float>(tokcap * d); v.gb = b.take<float>(tokcap * d); v.gO = b.take<float>(tokcap * d); v.gt = b.take<float>(tokcap * d);
+    v.dqkv = b.take<float>(tokcap * 3 * d); v.dHf = b.take<float>(tokcap * F); v.Dvec = b.take<float>(tokcap * dm.heads);
+    v.dFl = b.take<float>((size_t)B * d); v.dy3s = b.take<float>((size_t)B * d);
+    {
+      const int dec_shapes[][2] = {{3 * d, d}, {d, d}, {F, d}, {d, F}};
+      size_t tnb = 0;
+      for (const auto& sh : dec_shapes) {
+        const size_t need = tn_workspace_bytes(sh[0], sh[1], (int)tokcap);
+        if (need > tnb) tnb = need;
+      }
+      v.tn_ws_bytes = tnb;
+      v.tn_ws = b.take<char>(tnb);
+    }
     if (dm.lstm) {
       v.AxhP = planes_at(b.take<char>(planes_bytes(v.cap, 2 * D)), v.cap, 2 * D);
       v.CnP = planes_at(b.take<char>(planes_bytes(v.cap, C)), v.cap, C);
@@ -194,7 +216,6 @@ size_t carve(paths_engine* e, char* base) {
   }
   e->maxcap = maxcap; e->maxtok = maxcap + B;
   const size_t mc = maxcap, mt = (size_t)maxcap + B;
-  e->A1 = b.take<float>(mt * d); e->Fo = b.take<float>(mt * d);
   e->dY = b.take<float>(mc * D); e->dP = b.take<float>(mc * D); e->dG = b.take<float>(dm.lstm ? mc * (3 * C + D) : 4);
   e->dCn = b.take<float>(mc * C); e->dHc = b.take<float>(mc * D); e->dCc = b.take<float>(mc * C);
   e->dUV = b.take<float>(mc * (I + d));
@@ -205,9 +226,6 @@ size_t carve(paths_engine* e, char* base) {
   } else {
     e->dGP = e->dPP = e->dUVP = no_planes();
   }
-  e->ga = b.take<float>(mt * d); e->gb = b.take<float>(mt * d); e->gO = b.take<float>(mt * d); e->gt = b.take<float>(mt * d);
-  e->dqkv = b.take<float>(mt * 3 * d); e->dHf = b.take<float>(mt * F); e->Dvec = b.take<float>(mt * dm.heads);
-  e->dF = b.take<float>((size_t)B * d); e->dz = b.take<float>((size_t)B * d); e->dy3s = b.take<float>((size_t)B * d);
   e->hazards = b.take<float>((size_t)B * dm.nl); e->loss = b.take<float>(1); e->loss_per = b.take<float>(B);
   e->overflow = b.take<int>(2); e->slide_cnt = b.take<int>(B); e->slide_fb = b.take<int>(B);
   {
@@ -298,9 +316,10 @@ struct ProfScope {
   ProfScope(paths_engine* e_, int tag_, cudaStream_t st_) : e(e_), tag(tag_), st(st_), on(e_->prof_on) {
     if (on) { cudaEvent_t a; cudaEventCreate(&a); cudaEventRecord(a, st); e->prof_ev[tag].push_back(a); }
   }
-  ~ProfScope() {
-    if (on) { cudaEvent_t b; cudaEventCreate(&b); cudaEventRecord(b, st); e->prof_ev[tag].push_back(b); }
+  void end() {
+    if (on) { cudaEvent_t b; cudaEventCreate(&b); cudaEventRecord(b, st); e->prof_ev[tag].push_back(b); on = false; }
   }
+  ~ProfScope() { end(); }
 };
 
 #define RUN(call)            \
@@ -312,9 +331,11 @@ struct ProfScope {
 
 inline float* W_(const float* p) { return const_cast<float*>(p); }   // gradient views share the Params struct
 
-int level_forward(paths_engine* e, int l, cudaStream_t st) {
+// ---- forward of one level, part 1: patch contextualiser (LSTM / RNN step), importance, tokens
+int lstm_forward(paths_engine* e, int l, cudaStream_t st) {
   const paths_dims_t& dm = e->dm;
   set_tc_scratch(e->tc_scratch[0], e->tc_scratch_each, e->tc_scratch[1], e->tc_scratch_each);
+  ProfScope ps_blk(e, PATHS_PROF_LSTM_FWD, st);
   const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F, prec = dm.precision;
   Level& v = e->lv[l];
   const LevelP& p = e->P.level[l];
@@ -362,8 +383,17 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
                     dm.pe_mode, 2, M, Md, st));
   }
   RUN(special_fill(p.special, v.seg, v.tok, d, B, st));
+  return 0;
+}
 
-  // ---- transformer aggregator: decoder layers over packed tokens, last layer evaluated at the special token only
+// ---- part 2: transformer aggregator -- decoder layers over packed tokens, last layer evaluated at the special token only.
+// Reads only this level's tokens and writes only this level's buffers (safe on a per-level stream).
+int decoder_forward(paths_engine* e, int l, cudaStream_t st) {
+  const paths_dims_t& dm = e->dm;
+  const int B = e->B, d = dm.d, F = dm.F, prec = dm.precision;
+  Level& v = e->lv[l];
+  const LevelP& p = e->P.level[l];
+  ProfScope ps_dec(e, PATHS_PROF_DEC_FWD, st);
   const int Mt = v.ncap_tok;
   const int* Mtd = v.ntok;
   const float* t_in = v.tok;
@@ -375,16 +405,24 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
     const int* Rd = last ? nullptr : Mtd;
     RUN(gemm_nt(prec, row_src(t_in, d, d), w.Wqkv, d, 0, y.qkv, 3 * d, w.bqkv, Mt, Mtd, 3 * d, d, 0, st));
     RUN(attn_fwd(y.qkv, v.seg, y.O, y.lse, d, dm.heads, B, v.maxseg + 1, last ? 1 : 0, st));
-    RUN(gemm_nt(prec, row_src(y.O, d, d), w.Wo, d, 0, e->A1, d, nullptr, R, Rd, d, d, 0, st));
-    RUN(res_ln_fwd(t_in, last ? v.tseg : nullptr, e->A1, w.bo, w.n1w, w.n1b, y.y1, y.xh1, y.rs1, d, 1e-5f, last ? B : Mt, Rd, 0, st));
+    RUN(gemm_nt(prec, row_src(y.O, d, d), w.Wo, d, 0, v.A1, d, nullptr, R, Rd, d, d, 0, st));
+    RUN(res_ln_fwd(t_in, last ? v.tseg : nullptr, v.A1, w.bo, w.n1w, w.n1b, y.y1, y.xh1, y.rs1, d, 1e-5f, last ? B : Mt, Rd, 0, st));
     RUN(res_ln_fwd(y.y1, nullptr, nullptr, w.bcross, w.n2w, w.n2b, y.y2, y.xh2, y.rs2, d, 1e-5f, last ? B : Mt, Rd, 0, st));
     RUN(gemm_nt(prec, row_src(y.y2, d, d), w.W1, d, 0, y.Hf, F, w.b1, R, Rd, F, d, GEMM_RELU, st));
-    RUN(gemm_nt(prec, row_src(y.Hf, F, F), w.W2, F, 0, e->Fo, d, nullptr, R, Rd, d, F, 0, st));
-    RUN(res_ln_fwd(y.y2, nullptr, e->Fo, w.b2, w.n3w, w.n3b, y.y3, y.xh3, y.rs3, d, 1e-5f, last ? B : Mt, Rd, 0, st));
+    RUN(gemm_nt(prec, row_src(y.Hf, F, F), w.W2, F, 0, v.Fo, d, nullptr, R, Rd, d, F, 0, st));
+    RUN(res_ln_fwd(y.y2, nullptr, v.Fo, w.b2, w.n3w, w.n3b, y.y3, y.xh3, y.rs3, d, 1e-5f, last ? B : Mt, Rd, 0, st));
     t_in = y.y3;
   }
   RUN(res_ln_fwd(t_in, nullptr, nullptr, nullptr, p.nfw, p.nfb, v.z, v.xhf, v.rsf, d, 1e-5f, B, nullptr, 0, st));
-  // ---- residual slide context + classifier (paths.py:130-139)
+  return 0;
+}
+
+// ---- part 3: residual slide context + classifier (paths.py:130-139); needs F of the previous level
+int head_forward(paths_engine* e, int l, cudaStream_t st) {
+  const paths_dims_t& dm = e->dm;
+  const int B = e->B, d = dm.d;
+  Level& v = e->lv[l];
+  const LevelP& p = e->P.level[l];
   if (dm.residual == 2) {
     RUN(head_fwd(v.z, nullptr, nullptr, nullptr, v.F, nullptr, d, 0, B, st));          // F_l = z_l
     FList fl; fl.n = l + 1;
@@ -396,22 +434,20 @@ int level_forward(paths_engine* e, int l, cudaStream_t st) {
   return 0;
 }
 
-int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
+int level_forward(paths_engine* e, int l, cudaStream_t st) {
+  if (int r = lstm_forward(e, l, st)) return r;
+  if (int r = decoder_forward(e, l, st)) return r;
+  return head_forward(e, l, st);
+}
+
+// ---- backward of one level, part 1: classifier + residual slide context -> dFl (needs dFl of level l+1)
+int head_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   const paths_dims_t& dm = e->dm;
-  set_tc_scratch(e->tc_scratch[0], e->tc_scratch_each, e->tc_scratch[1], e->tc_scratch_each);
-  set_tn_workspace(e->tn_ws, e->tn_ws_bytes);
-  const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F, prec = dm.precision;
+  const int B = e->B, d = dm.d, prec = dm.precision;
   Level& v = e->lv[l];
   const LevelP& p = e->P.level[l];
   const LevelP& g = e->Gr.level[l];
-  const int M = v.cap;
-  const int* Md = v.count;
-  const int Mt = v.ncap_tok;
-  const int* Mtd = v.ntok;
-  const int ldg = 3 * C + D;
   const bool last_level = l == dm.L - 1;
-
-  // ---- head: dF = dF(l+1) + dlogits.Wc
   const float* dlog = use_dlogits ? v.dlogits : nullptr;
   if (dm.residual == 2) {
     // concat: the classifier of the level whose logits reach the loss sees every F_j, j <= l (paths.py:134-137)
@@ -425,19 +461,34 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
     } else if (last_level) {
       RUN(zero_rows(v.dFc, d, B, nullptr, 0, st));
     }
-    RUN(head_bwd(nullptr, v.dFc, p.Wc, e->dF, d, dm.nl, B, st));
+    RUN(head_bwd(nullptr, v.dFc, p.Wc, v.dFl, d, dm.nl, B, st));
   } else {
-    const float* dF_in = (dm.residual == 1 && !last_level) ? e->dF : nullptr;
-    RUN(head_bwd(dlog, dF_in, p.Wc, e->dF, d, dm.nl, B, st));
+    const float* dF_in = (dm.residual == 1 && !last_level) ? e->lv[l + 1].dFl : nullptr;
+    RUN(head_bwd(dlog, dF_in, p.Wc, v.dFl, d, dm.nl, B, st));
     if (dlog) {
       RUN(gemm_tn(prec, dlog, dm.nl, row_src(v.F, d, d), W_(g.Wc), d, B, nullptr, dm.nl, d, st));
       RUN(colsum_accum(dlog, dm.nl, W_(g.bc), B, nullptr, dm.nl, st));
     }
   }
-  // ---- final LayerNorm at the special tokens
-  RUN(ln_bwd(e->dF, nullptr, v.xhf, v.rsf, p.nfw, e->dy3s, nullptr, 0, W_(g.nfw), W_(g.nfb), nullptr, d, B, nullptr, 0, st));
+  return 0;
+}
 
-  const float* dy3 = e->dy3s;
+// ---- part 2: aggregator backward, dFl -> gradient of the level's tokens (v.dtok) and of the level's decoder parameters.
+// Touches only this level's buffers, scratch and parameter gradients (safe on a per-level stream).
+int decoder_backward(paths_engine* e, int l, cudaStream_t st) {
+  const paths_dims_t& dm = e->dm;
+  set_tn_workspace(e->lv[l].tn_ws, e->lv[l].tn_ws_bytes);
+  const int B = e->B, d = dm.d, F = dm.F, prec = dm.precision;
+  Level& v = e->lv[l];
+  const LevelP& p = e->P.level[l];
+  const LevelP& g = e->Gr.level[l];
+  const int Mt = v.ncap_tok;
+  const int* Mtd = v.ntok;
+  ProfScope ps_dec(e, PATHS_PROF_DEC_BWD, st);
+  // ---- final LayerNorm at the special tokens
+  RUN(ln_bwd(v.dFl, nullptr, v.xhf, v.rsf, p.nfw, v.dy3s, nullptr, 0, W_(g.nfw), W_(g.nfb), nullptr, d, B, nullptr, 0, st));
+
+  const float* dy3 = v.dy3s;
   for (int j = dm.layers - 1; j >= 0; --j) {
     const LayerP& w = p.layer[j];
     const LayerP& gw = g.layer[j];
@@ -447,36 +498,52 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
     const int* Rd = last ? nullptr : Mtd;
     const float* t_in = j == 0 ? v.tok : v.layer[j - 1].y3;
     // LN3 -> ga = d(y2 + ffn); db2
-    RUN(ln_bwd(dy3, nullptr, y.xh3, y.rs3, w.n3w, e->ga, nullptr, 0, W_(gw.n3w), W_(gw.n3b), W_(gw.b2), d, R, Rd, 0, st));
-    RUN(gemm_nt(prec, row_src(e->ga, d, d), w.W2, F, 1, e->dHf, F, nullptr, R, Rd, F, d, 0, st));
-    RUN(gemm_tn(prec, e->ga, d, row_src(y.Hf, F, F), W_(gw.W2), F, R, Rd, d, F, st));
-    RUN(relu_bwd(e->dHf, y.Hf, F, R, Rd, 0, st));
-    RUN(gemm_tn(prec, e->dHf, F, row_src(y.y2, d, d), W_(gw.W1), d, R, Rd, F, d, st));
-    RUN(colsum_accum(e->dHf, F, W_(gw.b1), R, Rd, F, st));
-    RUN(gemm_nt(prec, row_src(e->dHf, F, F), w.W1, d, 1, e->ga, d, nullptr, R, Rd, d, F, GEMM_ACCUM, st));     // ga = dy2
+    RUN(ln_bwd(dy3, nullptr, y.xh3, y.rs3, w.n3w, v.ga, nullptr, 0, W_(gw.n3w), W_(gw.n3b), W_(gw.b2), d, R, Rd, 0, st));
+    RUN(gemm_nt(prec, row_src(v.ga, d, d), w.W2, F, 1, v.dHf, F, nullptr, R, Rd, F, d, 0, st));
+    RUN(gemm_tn(prec, v.ga, d, row_src(y.Hf, F, F), W_(gw.W2), F, R, Rd, d, F, st));
+    RUN(relu_bwd(v.dHf, y.Hf, F, R, Rd, 0, W_(gw.b1), st));
+    RUN(gemm_tn(prec, v.dHf, F, row_src(y.y2, d, d), W_(gw.W1), d, R, Rd, F, d, st));
+    RUN(gemm_nt(prec, row_src(v.dHf, F, F), w.W1, d, 1, v.ga, d, nullptr, R, Rd, d, F, GEMM_ACCUM, st));     // ga = dy2
     // LN2 (cross-attention over an empty memory contributes only its output bias), then LN1
-    RUN(ln_bwd(e->ga, nullptr, y.xh2, y.rs2, w.n2w, e->gb, nullptr, 0, W_(gw.n2w), W_(gw.n2b), W_(gw.bcross), d, R, Rd, 0, st));
-    RUN(ln_bwd(e->gb, nullptr, y.xh1, y.rs1, w.n1w, e->ga, nullptr, 0, W_(gw.n1w), W_(gw.n1b), W_(gw.bo), d, R, Rd, 0, st));  // ga = da
-    RUN(gemm_nt(prec, row_src(e->ga, d, d), w.Wo, d, 1, e->gO, d, nullptr, R, Rd, d, d, 0, st));
-    RUN(gemm_tn(prec, e->ga, d, row_src(y.O, d, d), W_(gw.Wo), d, R, Rd, d, d, st));
-    if (last && !attn_bwd_writes_all(d, dm.heads)) RUN(zero_rows(e->dqkv, 3 * d, Mt, Mtd, 0, st));
-    RUN(attn_bwd(y.qkv, v.seg, y.O, y.lse, e->gO, e->dqkv, e->Dvec, d, dm.heads, B, v.maxseg + 1, last ? 1 : 0, st));
-    RUN(gemm_tn(prec, e->dqkv, 3 * d, row_src(t_in, d, d), W_(gw.Wqkv), d, Mt, Mtd, 3 * d, d, st));
-    RUN(colsum_accum(e->dqkv, 3 * d, W_(gw.bqkv), Mt, Mtd, 3 * d, st));
+    RUN(ln_bwd(v.ga, nullptr, y.xh2, y.rs2, w.n2w, v.gb, nullptr, 0, W_(gw.n2w), W_(gw.n2b), W_(gw.bcross), d, R, Rd, 0, st));
+    RUN(ln_bwd(v.gb, nullptr, y.xh1, y.rs1, w.n1w, v.ga, nullptr, 0, W_(gw.n1w), W_(gw.n1b), W_(gw.bo), d, R, Rd, 0, st));  // ga = da
+    RUN(gemm_nt(prec, row_src(v.ga, d, d), w.Wo, d, 1, v.gO, d, nullptr, R, Rd, d, d, 0, st));
+    RUN(gemm_tn(prec, v.ga, d, row_src(y.O, d, d), W_(gw.Wo), d, R, Rd, d, d, st));
+    if (last && !attn_bwd_writes_all(d, dm.heads)) RUN(zero_rows(v.dqkv, 3 * d, Mt, Mtd, 0, st));
+    RUN(attn_bwd(y.qkv, v.seg, y.O, y.lse, v.gO, v.dqkv, v.Dvec, d, dm.heads, B, v.maxseg + 1, last ? 1 : 0, st));
+    RUN(gemm_tn(prec, v.dqkv, 3 * d, row_src(t_in, d, d), W_(gw.Wqkv), d, Mt, Mtd, 3 * d, d, st));
+    RUN(colsum_accum(v.dqkv, 3 * d, W_(gw.bqkv), Mt, Mtd, 3 * d, st));
     if (last) {
-      RUN(gemm_nt(prec, row_src(e->dqkv, 3 * d, 3 * d), w.Wqkv, d, 1, e->gt, d, nullptr, Mt, Mtd, d, 3 * d, 0, st));
-      RUN(scatter_add_rows(e->ga, v.tseg, e->gt, d, B, st));
-      dy3 = e->gt;
+      RUN(gemm_nt(prec, row_src(v.dqkv, 3 * d, 3 * d), w.Wqkv, d, 1, v.gt, d, nullptr, Mt, Mtd, d, 3 * d, 0, st));
+      RUN(scatter_add_rows(v.ga, v.tseg, v.gt, d, B, st));
+      dy3 = v.gt;
     } else {
       // ga holds da (the residual branch); add the attention branch, then hand the buffer over as the next layer's dy3
-      RUN(gemm_nt(prec, row_src(e->dqkv, 3 * d, 3 * d), w.Wqkv, d, 1, e->ga, d, nullptr, Mt, Mtd, d, 3 * d, GEMM_ACCUM, st));
-      float* tmp = e->ga; e->ga = e->gt; e->gt = tmp;
-      dy3 = e->gt;
+      RUN(gemm_nt(prec, row_src(v.dqkv, 3 * d, 3 * d), w.Wqkv, d, 1, v.ga, d, nullptr, Mt, Mtd, d, 3 * d, GEMM_ACCUM, st));
+      float* tmp = v.ga; v.ga = v.gt; v.gt = tmp;
+      dy3 = v.gt;
     }
   }
-  const float* dtok = dy3;
-  // ---- special token, importance / projection
-  RUN(special_grad(dtok, v.seg, W_(g.special), d, B, st));
+  v.dtok = dy3;
+  RUN(special_grad(v.dtok, v.seg, W_(g.special), d, B, st));
+  return 0;
+}
+
+// ---- part 3: importance / projection, LSTM (or RNN) step, gradients handed to the parent rows
+int lstm_backward(paths_engine* e, int l, cudaStream_t st) {
+  const paths_dims_t& dm = e->dm;
+  set_tc_scratch(e->tc_scratch[0], e->tc_scratch_each, e->tc_scratch[1], e->tc_scratch_each);
+  set_tn_workspace(e->tn_ws, e->tn_ws_bytes);
+  const int D = dm.D, C = dm.C, d = dm.d, I = dm.I, prec = dm.precision;
+  Level& v = e->lv[l];
+  const LevelP& p = e->P.level[l];
+  const LevelP& g = e->Gr.level[l];
+  const int M = v.cap;
+  const int* Md = v.count;
+  const int ldg = 3 * C + D;
+  const bool last_level = l == dm.L - 1;
+  ProfScope ps_blk(e, PATHS_PROF_LSTM_BWD, st);
+  const float* dtok = v.dtok;
   const bool has_children = !last_level;
   const bool has_parent = l > 0;
   if (!dm.lstm) {
@@ -495,7 +562,7 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
       RUN(gemm_tn(prec, e->dY, D, row_src(v.Cn, C, C), W_(g.Wh2), C, M, Md, D, C, st));
       RUN(colsum_accum(e->dY, D, W_(g.bh2), M, Md, D, st));
       RUN(gemm_nt(prec, row_src(e->dY, D, D), p.Wh2, C, 1, e->dCn, C, nullptr, M, Md, C, D, 0, st));
-      RUN(relu_bwd(e->dCn, v.Cn, C, M, Md, 0, st));
+      RUN(relu_bwd(e->dCn, v.Cn, C, M, Md, 0, nullptr, st));
       RUN(gemm_tn(prec, e->dCn, C, row_src(e->lv[l - 1].H, D, D, v.row_parent), W_(g.Wh0), D, M, Md, C, D, st));
       RUN(colsum_accum(e->dCn, C, W_(g.bh0), M, Md, C, st));
       RUN(gemm_nt(prec, row_src(e->dCn, C, C), p.Wh0, D, 1, v.dHrow, D, nullptr, M, Md, D, C, 0, st));
@@ -535,12 +602,19 @@ int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   return 0;
 }
 
+int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
+  if (int r = head_backward(e, l, use_dlogits, st)) return r;
+  if (int r = decoder_backward(e, l, st)) return r;
+  return lstm_backward(e, l, st);
+}
+
 int do_select(paths_engine* e, int l, cudaStream_t st) {
   const paths_dims_t& dm = e->dm;
   PATHS_REQUIRE(l >= 0 && l < dm.L - 1, "select: level %d has no successor", l);
   PATHS_REQUIRE(e->have_store, "select: no pyramid store bound");
   Level& v = e->lv[l];
   Level& n = e->lv[l + 1];
+  ProfScope ps_sel(e, PATHS_PROF_SELECT, st);
   SelectArgs a;
   a.alpha = v.alpha; a.seg = v.seg; a.row_xy = v.row_xy; a.count = v.count; a.B = e->B; a.cap = v.cap;
   a.keep = dm.K[l]; a.kcap = v.kcap;
@@ -617,6 +691,19 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
   }
   carve(e, static_cast<char*>(workspace));
   e->ws_base = static_cast<char*>(workspace); e->ws_bytes = need;
+  e->have_streams = true;
+  for (int l = 0; l < e->dm.L && e->have_streams; ++l) {
+    bool ok = cudaStreamCreateWithFlags(&e->side[l], cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_tok[l], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_z[l], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_head[l], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_dtok[l], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+      set_error("could not create the per-level streams / events: %s", cudaGetErrorString(cudaGetLastError()));
+      delete e;
+      return -1;
+    }
+  }
   *out = e;
   return 0;
 }
@@ -624,6 +711,12 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
 void paths_engine_destroy(paths_engine_t* e) {
   if (!e) return;
   for (const float* src : e->packed_srcs) unregister_packed(src);
+  if (e->have_streams)
+    for (int l = 0; l < e->dm.L; ++l) {
+      cudaStreamSynchronize(e->side[l]);
+      cudaStreamDestroy(e->side[l]);
+      cudaEventDestroy(e->ev_tok[l]); cudaEventDestroy(e->ev_z[l]); cudaEventDestroy(e->ev_head[l]); cudaEventDestroy(e->ev_dtok[l]);
+    }
   delete e;
 }
 
@@ -724,15 +817,40 @@ int paths_engine_level_backward(paths_engine_t* e, int level, int use_dlogits, v
   return level_backward(e, level, use_dlogits, static_cast<cudaStream_t>(stream));
 }
 
+// The whole-step entry points run each level's aggregator on its own stream: select(l) needs only the importances, so the
+// LSTM / select chain of the deeper levels (main stream) overlaps the decoders of the shallower ones; the slide-vector chain
+// (heads) joins them at the end.  Backward mirrors it: head chain first, the L decoder backwards concurrently, then the LSTM
+// chain from the deepest level up, each level waiting only for its own token gradient.
+static bool use_side_streams(const paths_engine* e) {
+  return e->have_streams && planes_mode(e->dm) && e->dm.d % 8 == 0 && e->dm.F % 8 == 0;
+}
+
 int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int32_t* ybin, const int32_t* censored, float scale,
                          int with_loss, void* stream) {
   PATHS_REQUIRE(e && e->have_params, "forward: engine has no parameters bound");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int L = e->dm.L;
   if (int r = do_begin(e, slide_ids, nullptr, 0, st)) return r;
-  for (int l = 0; l < e->dm.L; ++l) {
-    if (int r = level_forward(e, l, st)) return r;
-    if (l < e->dm.L - 1)
-      if (int r = do_select(e, l, st)) return r;
+  if (!use_side_streams(e)) {
+    for (int l = 0; l < L; ++l) {
+      if (int r = level_forward(e, l, st)) return r;
+      if (l < L - 1)
+        if (int r = do_select(e, l, st)) return r;
+    }
+  } else {
+    for (int l = 0; l < L; ++l) {
+      if (int r = lstm_forward(e, l, st)) return r;
+      PATHS_CK(cudaEventRecord(e->ev_tok[l], st));
+      PATHS_CK(cudaStreamWaitEvent(e->side[l], e->ev_tok[l], 0));
+      if (int r = decoder_forward(e, l, e->side[l])) return r;
+      PATHS_CK(cudaEventRecord(e->ev_z[l], e->side[l]));
+      if (l < L - 1)
+        if (int r = do_select(e, l, st)) return r;
+    }
+    for (int l = 0; l < L; ++l) {
+      PATHS_CK(cudaStreamWaitEvent(st, e->ev_z[l], 0));
+      if (int r = head_forward(e, l, st)) return r;
+    }
   }
   if (with_loss) return do_loss(e, ybin, censored, scale, st);
   return 0;
@@ -741,9 +859,24 @@ int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int3
 int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream) {
   PATHS_REQUIRE(e && e->have_params && e->grads_base, "backward: no gradient buffer bound");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int L = e->dm.L;
   if (zero_grads) PATHS_CK(cudaMemsetAsync(e->grads_base, 0, e->grads_floats * sizeof(float), st));
-  for (int l = e->dm.L - 1; l >= 0; --l)
-    if (int r = level_backward(e, l, l == e->dm.L - 1, st)) return r;
+  if (!use_side_streams(e)) {
+    for (int l = L - 1; l >= 0; --l)
+      if (int r = level_backward(e, l, l == L - 1, st)) return r;
+    return 0;
+  }
+  for (int l = L - 1; l >= 0; --l) {
+    if (int r = head_backward(e, l, l == L - 1, st)) return r;
+    PATHS_CK(cudaEventRecord(e->ev_head[l], st));
+    PATHS_CK(cudaStreamWaitEvent(e->side[l], e->ev_head[l], 0));
+    if (int r = decoder_backward(e, l, e->side[l])) return r;
+    PATHS_CK(cudaEventRecord(e->ev_dtok[l], e->side[l]));
+  }
+  for (int l = L - 1; l >= 0; --l) {
+    PATHS_CK(cudaStreamWaitEvent(st, e->ev_dtok[l], 0));
+    if (int r = lstm_backward(e, l, st)) return r;
+  }
   return 0;
 }
 
@@ -783,7 +916,7 @@ int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, siz
     case PATHS_BUF_LOSS: p = e->loss; n = f; break;
     case PATHS_BUF_LOSS_PER: p = e->loss_per; n = B * f; break;
     case PATHS_BUF_OVERFLOW: p = e->overflow; n = 2 * i4; break;
-    case PATHS_BUF_DF_IN: p = e->dF; n = B * dm.d * f; break;
+    case PATHS_BUF_DF_IN: p = v.dFl; n = B * dm.d * f; break;
     case PATHS_BUF_DHROW: p = v.dHrow; n = cap * dm.D * f; break;
     case PATHS_BUF_DCROW: p = v.dCrow; n = cap * dm.C * f; break;
     default: set_error("unknown buffer id %d", which); return -2;

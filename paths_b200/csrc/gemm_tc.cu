@@ -186,6 +186,24 @@ struct Operand { int row0, col0, plane_rows; };
 // included), split it into bf16 (hi, lo) and store it in the SWIZZLE_128B layout a TMA box would have produced -- no separate
 // split pass, no bf16 copy in HBM.  K-major tile: [W rows (output index) x 64 k]; MN-major tile: [64 k x W cols (output index)].
 // Work item = one 16-byte bf16 chunk (8 elements = two float4 loads); W * 8 items per tile, 4 per thread per batch.
+// Stream-K partition shared by the contraction kernel and tn_reduce_kernel.  k1 >= 0 (more CTAs than tiles): CTA t < tiles
+// owns k-blocks [0, k1) of tile t; the other G - tiles CTAs split the tails [k1, nkb) of all tiles (tile-major, q k-blocks
+// each; tl = nkb - k1, total = tiles * tl).  k1 < 0: plain tile-major stream-K over all G CTAs.
+struct SkPlan { int k1, tl; long long q, total; };
+__host__ __device__ __forceinline__ SkPlan sk_plan(int tiles, int nkb, int G) {
+  SkPlan p;
+  if (G > tiles) {
+    p.k1 = (int)(((long long)nkb * tiles) / G);
+    p.tl = nkb - p.k1;
+    p.total = (long long)tiles * p.tl;
+    p.q = (p.total + (G - tiles) - 1) / (G - tiles);
+    if (p.q < 1) p.q = 1;
+  } else {
+    p.k1 = -1; p.tl = nkb; p.total = (long long)tiles * nkb; p.q = (p.total + G - 1) / G;
+  }
+  return p;
+}
+
 constexpr int LB = 4;                                       // items per thread per batch
 struct CvtRegs { float4 x[LB][2]; uint32_t off[LB]; };
 
@@ -281,12 +299,31 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     int t;
     if (SK) {
       if (nkb_total == 0) return false;
-      t = (int)(sk_lo / nkb_total) + n;
-      const long long t_lo = (long long)t * nkb_total;
-      const long long b = sk_lo > t_lo ? sk_lo : t_lo;
-      const long long e = sk_hi < t_lo + nkb_total ? sk_hi : t_lo + nkb_total;
-      if (b >= e) return false;
-      kb_begin = (int)(b - t_lo); kb_end = (int)(e - t_lo);
+      const SkPlan pl = sk_plan(units, nkb_total, (int)gridDim.x);
+      if (pl.k1 >= 0) {
+        // more CTAs than tiles: CTA t < tiles sweeps k-blocks [0, k1) of tile t in lock step with the others (all of them read
+        // the same reduction rows at the same time: operands stay L2-resident); the remaining CTAs stream over the tails
+        if ((int)blockIdx.x < units) {
+          if (n > 0 || pl.k1 == 0) return false;
+          t = blockIdx.x; kb_begin = 0; kb_end = pl.k1;
+        } else {
+          const long long lo = (long long)(blockIdx.x - units) * pl.q, hi0 = lo + pl.q;
+          const long long hi = hi0 < pl.total ? hi0 : pl.total;
+          t = (int)(lo / pl.tl) + n;
+          const long long t_lo = (long long)t * pl.tl;
+          const long long b = lo > t_lo ? lo : t_lo;
+          const long long e = hi < t_lo + pl.tl ? hi : t_lo + pl.tl;
+          if (b >= e) return false;
+          kb_begin = pl.k1 + (int)(b - t_lo); kb_end = pl.k1 + (int)(e - t_lo);
+        }
+      } else {
+        t = (int)(sk_lo / nkb_total) + n;
+        const long long t_lo = (long long)t * nkb_total;
+        const long long b = sk_lo > t_lo ? sk_lo : t_lo;
+        const long long e = sk_hi < t_lo + nkb_total ? sk_hi : t_lo + nkb_total;
+        if (b >= e) return false;
+        kb_begin = (int)(b - t_lo); kb_end = (int)(e - t_lo);
+      }
     } else {
       t = blockIdx.x + n * gridDim.x;
       if (t >= units || nkb_total == 0) return false;
@@ -626,15 +663,23 @@ __global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict
   const int tiles_j = (NJ + BN - 1) / BN;
   const int t = blockIdx.x;
   const int units = ((NI + BM - 1) / BM) * tiles_j;
-  const long long total = (long long)units * nkb, q = (total + G - 1) / G;
-  const long long t_lo = (long long)t * nkb;
-  const int c_first = (int)(t_lo / q), c_last = (int)((t_lo + nkb - 1) / q);
+  const SkPlan pl = sk_plan(units, nkb, G);
   const int o = threadIdx.x % OUT, g = threadIdx.x / OUT;
   const int elem = blockIdx.y * OUT + o;                 // float4 index inside the tile, row-major
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int c = c_first + g; c <= c_last; c += PG) {
-    const int ord = t - (int)(((long long)c * q) / nkb);
-    const float4 v = __ldcs(ws + ((size_t)c * segmax + ord) * (BM * BN / 4) + elem);
+  // contributions in a fixed order: (lock-step CTA t, if any), then the streaming CTAs that touched the tile
+  const int c_base = pl.k1 >= 0 ? units : 0;
+  const long long t_lo = (long long)t * pl.tl;
+  const int c_first = pl.tl > 0 ? (int)(t_lo / pl.q) : 0, c_last = pl.tl > 0 ? (int)((t_lo + pl.tl - 1) / pl.q) : -1;
+  const int extra = pl.k1 > 0 ? 1 : 0;
+  for (int k = g; k < extra + (c_last - c_first + 1); k += PG) {
+    size_t slot;
+    if (k < extra) slot = (size_t)t * segmax;
+    else {
+      const int c = c_first + (k - extra);
+      slot = (size_t)(c_base + c) * segmax + (t - (int)(((long long)c * pl.q) / pl.tl));
+    }
+    const float4 v = __ldcs(ws + slot * (BM * BN / 4) + elem);
     acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
   }
   if (PG > 1) {
@@ -806,6 +851,10 @@ static void tn_plan(int NI, int NJ, int M_host, int* G, int* segmax) {
   if (g < 1) g = 1;
   *G = (int)g;
   *segmax = (tiles + *G - 1) / *G + 2;
+  if (*G > tiles) {                              // tail CTAs of the lock-step plan touch ceil(tiles / (G - tiles)) + 1 tiles at most
+    const int s2 = (tiles + (*G - tiles) - 1) / (*G - tiles) + 2;
+    if (s2 > *segmax) *segmax = s2;
+  }
 }
 size_t tn_workspace_bytes(int NI, int NJ, int M_host) {
   int G, segmax;

@@ -81,7 +81,7 @@ size_t paths_heatmap_workspace_bytes(int L, int H, int W) { return (size_t)L * H
 int paths_heatmap_composite(const int32_t* locs_yx, const float* importance, const int32_t* level_off, int32_t n_patches, int L,
                             int patch_size, int H, int W, void* workspace, size_t workspace_bytes, double* out, float* alpha,
                             void* stream) {
-  PATHS_REQUIRE(locs_yx && importance && level_off && workspace && out && alpha, "heatmap: null argument");
+  PATHS_REQUIRE(level_off && workspace && out && alpha && (n_patches == 0 || (locs_yx && importance)), "heatmap: null argument");
   PATHS_REQUIRE(L >= 1 && L <= 30 && H > 0 && W > 0 && patch_size > 0, "heatmap: bad shape (L=%d H=%d W=%d P=%d)", L, H, W, patch_size);
   PATHS_REQUIRE(workspace_bytes >= paths_heatmap_workspace_bytes(L, H, W), "heatmap: workspace too small");
   cudaStream_t st = static_cast<cudaStream_t>(stream);

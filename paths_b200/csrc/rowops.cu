@@ -466,13 +466,32 @@ __global__ void __launch_bounds__(TPB) head_concat_bwd_kernel(const float* __res
   }
 }
 
+// dspecial[c] += sum_b dtok[special token of slide b, c]: one block, warp w takes slides w, w+8, ... (independent loads), the
+// eight partial rows are combined in a fixed order (deterministic).
 __global__ void __launch_bounds__(256) special_grad_kernel(const float* __restrict__ dtok, const int* __restrict__ seg,
                                                            float* __restrict__ dspecial, int d, int B) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= d) return;
-  float s = 0.f;
-  for (int b = 0; b < B; ++b) s += dtok[(size_t)(seg[b] + b) * d + c];
-  atomicAdd(dspecial + c, s);
+  __shared__ float part[8][256];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  float acc[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) acc[q] = 0.f;
+#pragma unroll 4
+  for (int b = w; b < B; b += 8) {
+    const float* r = dtok + (size_t)(seg[b] + b) * d;
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      if (lane + 32 * q < d) acc[q] += r[lane + 32 * q];
+  }
+#pragma unroll
+  for (int q = 0; q < 8; ++q) part[w][lane + 32 * q] = acc[q];
+  __syncthreads();
+  const int c = threadIdx.x;
+  if (c < d) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += part[k][c];
+    dspecial[c] += s;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -575,10 +594,37 @@ __global__ void __launch_bounds__(TPB) ln_bwd_kernel(const float* __restrict__ d
 }
 
 // relu backward in place: dH *= (H > 0)
-__global__ void relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, size_t ld, int M_host, const int* M_dev, int M_extra) {
-  const size_t n = (size_t)(row_count(M_host, M_dev) + M_extra) * ld;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    if (!(H[i] > 0.f)) dH[i] = 0.f;
+// dH *= (H > 0); optionally dbias[c] += sum_m dH[m, c] in the same pass (the bias gradient of the layer that fed the ReLU).
+// ld % 4 == 0; a thread keeps one float4 column group and walks rows, so the column sums need one shared-memory combine
+// and one atomic per column per block.
+__global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, int ld, int M_host,
+                                                       const int* M_dev, int M_extra, float* __restrict__ dbias) {
+  const int M = row_count(M_host, M_dev) + M_extra;
+  const int ngrp = ld >> 2;                               // float4 groups per row
+  const int rpb = 256 / ngrp > 0 ? 256 / ngrp : 1;        // rows per block iteration (ld <= 1024)
+  const int g = threadIdx.x % ngrp, rsub = threadIdx.x / ngrp;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (rsub < rpb) {
+#pragma unroll 4
+    for (int m = blockIdx.x * rpb + rsub; m < M; m += gridDim.x * rpb) {
+      float4* dp = reinterpret_cast<float4*>(dH + (size_t)m * ld) + g;
+      const float4 h = __ldg(reinterpret_cast<const float4*>(H + (size_t)m * ld) + g);
+      float4 v = *dp;
+      v.x = h.x > 0.f ? v.x : 0.f; v.y = h.y > 0.f ? v.y : 0.f; v.z = h.z > 0.f ? v.z : 0.f; v.w = h.w > 0.f ? v.w : 0.f;
+      *dp = v;
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+  }
+  if (!dbias) return;
+  __shared__ float4 part[256];
+  part[threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.x < ngrp) {
+    float4 t = part[threadIdx.x];
+    for (int k = 1; k < rpb; ++k) { const float4 u = part[k * ngrp + threadIdx.x]; t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+    float* o = dbias + 4 * threadIdx.x;
+    atomicAdd(o, t.x); atomicAdd(o + 1, t.y); atomicAdd(o + 2, t.z); atomicAdd(o + 3, t.w);
+  }
 }
 
 __global__ void zero_rows_kernel(float* __restrict__ X, size_t ld, int M_host, const int* M_dev, int M_extra) {
@@ -801,7 +847,8 @@ int head_concat_bwd(const float* dlogits, const float* Wc, const GList& gl, int 
   return 0;
 }
 int special_grad(const float* dtok, const int* seg, float* dspecial, int d, int B, cudaStream_t st) {
-  special_grad_kernel<<<(d + 255) / 256, 256, 0, st>>>(dtok, seg, dspecial, d, B);
+  PATHS_REQUIRE(d <= 256, "special_grad: trans_dim above 256 is not supported (d=%d)", d);
+  special_grad_kernel<<<1, 256, 0, st>>>(dtok, seg, dspecial, d, B);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -821,9 +868,13 @@ int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rs
   PATHS_LAUNCH_CK();
   return 0;
 }
-int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
+int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, float* dbias, cudaStream_t st) {
   if (M_host + M_extra <= 0) return 0;
-  relu_bwd_kernel<<<4 * kNumSMs, 256, 0, st>>>(dH, H, (size_t)ld, M_host, M_dev, M_extra);
+  PATHS_REQUIRE(ld % 4 == 0 && ld <= 1024, "relu_bwd: row width %d unsupported (multiple of 4, <= 1024)", ld);
+  const int rpb = 256 / (ld / 4) > 0 ? 256 / (ld / 4) : 1;
+  int g = (M_host + M_extra + rpb - 1) / rpb;
+  if (g > 2 * kNumSMs) g = 2 * kNumSMs;
+  relu_bwd_kernel<<<g, 256, 0, st>>>(dH, H, ld, M_host, M_dev, M_extra, dbias);
   PATHS_LAUNCH_CK();
   return 0;
 }

@@ -43,7 +43,7 @@ int res_ln_fwd(const float* res, const int* ridx, const float* add, const float*
                float* xhat, float* rstd, int d, float eps, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
 int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rstd, const float* gamma, float* dx, const int* didx, int accum,
            float* dgamma, float* dbeta, float* dbias, int d, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
-int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
+int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, float* dbias, cudaStream_t st);
 int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
 int scatter_add_rows(const float* src, const int* idx, float* dst, int d, int B, cudaStream_t st);
 int head_fwd(const float* z, const float* Fprev, const float* Wc, const float* bc, float* F, float* logits, int d, int nl, int B, cudaStream_t st);
