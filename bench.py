@@ -145,6 +145,7 @@ def main():
     ap.add_argument("--slides-per-gpu", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fast-mode", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -286,6 +287,19 @@ def main():
                "d2h_bytes_per_step": 4, "ms_per_step": e_ms / args.steps,
                "api": "paths_b200.utils.inference_end2end(collated host batch) + loss.backward() + loss.item()"}
 
+    # ---- the stated-tolerance fast mode (single-pass bf16 operands, 1e-2), same workload, reported beside the headline
+    fast = None
+    if args.precision == "bf16x3" and not args.no_fast_mode:
+        rt.set_precision("bf16")
+        f_ms, _, _ = timed(step_resident, args.steps, 3, profile=True)
+        fg_ms, _ = eng.profile_read(0)
+        for tag in range(1, 8):
+            eng.profile_read(tag)
+        f_ach = flops_per_step * args.steps / (fg_ms / 1e3) / 1e12 if fg_ms > 0 else 0.0
+        fast = {"dtype": "bf16 (single pass, stated tolerance 1e-2)", "value": B * world * args.steps / (f_ms / 1e3), "unit": "slides/s",
+                "ms_per_step": f_ms / args.steps, "gate_kernel_tflops": f_ach, "gate_kernel_frac_of_peak": f_ach / peak if peak else None}
+        rt.set_precision(args.precision)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         rate, spp, cores = cpu_oracle_rate(16, 2, 1)
@@ -301,9 +315,14 @@ def main():
             "config": {"workload": WORKLOAD, "slides_per_gpu": B, "global_batch": B * world, "levels": Lv, "top_k": 20,
                        "packed_rows_per_step_per_gpu": rows, "rows_per_level": counts, "parallelism": f"dp{world}",
                        "l2": "per-step working set (activations ~3 GB, pyramids 16 GB) far exceeds the 126 MB L2"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "fast_mode": fast, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line))
+    if os.environ.get("PATHS_B200_PROF_DUMP"):               # developer aid: per-call-site timings are written at engine destruction
+        torch.cuda.synchronize()
+        rt.engines.clear(); rt.last_engine = None; rt._pending = None
+        del eng
+        import gc; gc.collect()
     if world > 1:
         dist.destroy_process_group()
 

@@ -3,6 +3,7 @@
 // (utils.py:228-279 inference_end2end + loss.backward()).  All row counts live on the device: nothing here
 // synchronises with the host, so a whole step is one uninterrupted stream of launches.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -131,6 +132,8 @@ struct paths_engine {
   // the aggregator (decoder) of a level depends only on that level's tokens, and nothing downstream but the slide vector
   // depends on it: each level's decoder runs on its own stream, overlapping the LSTM / select chain of the deeper levels
   cudaStream_t side[PATHS_MAX_LEVELS];
+  cudaStream_t mainp;                                    // engine-owned high-priority stream of the LSTM / select chain
+  cudaEvent_t ev_in, ev_out;                             // fork from / join into the caller's stream
   cudaEvent_t ev_tok[PATHS_MAX_LEVELS], ev_z[PATHS_MAX_LEVELS], ev_head[PATHS_MAX_LEVELS], ev_dtok[PATHS_MAX_LEVELS];
   bool have_streams;
   Planes dGP, dPP, dUVP;                                 // gradient planes written by the pointwise backward kernels
@@ -154,6 +157,8 @@ struct paths_engine {
   // optional per-kernel timing (CUDA events on the launch stream) for bench.py's roofline line
   bool prof_on;
   std::vector<cudaEvent_t> prof_ev[PATHS_PROF__COUNT];     // start/stop pairs
+  struct Site { int line; const char* what; cudaEvent_t a, b; };
+  bool site_on; std::vector<Site> sites; int site_skip;
 };
 
 namespace {
@@ -322,11 +327,24 @@ struct ProfScope {
   ~ProfScope() { end(); }
 };
 
-#define RUN(call)            \
-  do {                       \
-    int _r = (call);         \
-    if (_r) return _r;       \
-    e->launches++;           \
+// Developer aid: with PATHS_B200_PROF_DUMP=<file> every RUN() call site is bracketed by CUDA events on its stream and the
+// per-call-site totals (warm, in-situ) are written to <file> when the engine is destroyed.  Use with PATHS_B200_NO_STREAMS=1.
+struct SiteScope {
+  paths_engine* e; int line; const char* what; cudaStream_t st; cudaEvent_t a;
+  SiteScope(paths_engine* e_, int line_, const char* what_, cudaStream_t st_) : e(e_), line(line_), what(what_), st(st_), a(nullptr) {
+    if (e->site_on) { cudaEventCreate(&a); cudaEventRecord(a, st); }
+  }
+  ~SiteScope() {
+    if (a) { cudaEvent_t b; cudaEventCreate(&b); cudaEventRecord(b, st); e->sites.push_back(paths_engine::Site{line, what, a, b}); }
+  }
+};
+
+#define RUN(call)                          \
+  do {                                     \
+    SiteScope _ss(e, __LINE__, #call, st); \
+    int _r = (call);                       \
+    if (_r) return _r;                     \
+    e->launches++;                         \
   } while (0)
 
 inline float* W_(const float* p) { return const_cast<float*>(p); }   // gradient views share the Params struct
@@ -691,9 +709,26 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
   }
   carve(e, static_cast<char*>(workspace));
   e->ws_base = static_cast<char*>(workspace); e->ws_bytes = need;
+  e->site_on = getenv("PATHS_B200_PROF_DUMP") != nullptr;
   e->have_streams = true;
+  // priorities: the chain every level waits on runs highest; among the decoders the deeper level goes first (its token
+  // gradient is the first one the backward chain needs)
+  int prio_least = 0, prio_greatest = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+  {
+    bool ok = cudaStreamCreateWithPriority(&e->mainp, cudaStreamNonBlocking, prio_greatest) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_in, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_out, cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+      set_error("could not create the engine streams / events: %s", cudaGetErrorString(cudaGetLastError()));
+      delete e;
+      return -1;
+    }
+  }
   for (int l = 0; l < e->dm.L && e->have_streams; ++l) {
-    bool ok = cudaStreamCreateWithFlags(&e->side[l], cudaStreamNonBlocking) == cudaSuccess;
+    int prio = prio_greatest + 1 + (e->dm.L - 1 - l);
+    if (prio > prio_least) prio = prio_least;
+    bool ok = cudaStreamCreateWithPriority(&e->side[l], cudaStreamNonBlocking, prio) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&e->ev_tok[l], cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&e->ev_z[l], cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&e->ev_head[l], cudaEventDisableTiming) == cudaSuccess;
@@ -710,7 +745,27 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
 
 void paths_engine_destroy(paths_engine_t* e) {
   if (!e) return;
+  if (e->site_on && !e->sites.empty()) {
+    cudaDeviceSynchronize();
+    struct Acc { double ms; int n; const char* what; };
+    std::vector<Acc> acc(4096, Acc{0.0, 0, nullptr});
+    for (const paths_engine::Site& s : e->sites) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess && s.line < 4096) { acc[s.line].ms += ms; acc[s.line].n++; acc[s.line].what = s.what; }
+      cudaEventDestroy(s.a); cudaEventDestroy(s.b);
+    }
+    if (FILE* f = fopen(getenv("PATHS_B200_PROF_DUMP"), "w")) {
+      for (int i = 0; i < 4096; ++i)
+        if (acc[i].n) fprintf(f, "%d\t%.4f\t%d\t%.80s\n", i, acc[i].ms, acc[i].n, acc[i].what);
+      fclose(f);
+    }
+  }
   for (const float* src : e->packed_srcs) unregister_packed(src);
+  if (e->have_streams) {
+    cudaStreamSynchronize(e->mainp);
+    cudaStreamDestroy(e->mainp);
+    cudaEventDestroy(e->ev_in); cudaEventDestroy(e->ev_out);
+  }
   if (e->have_streams)
     for (int l = 0; l < e->dm.L; ++l) {
       cudaStreamSynchronize(e->side[l]);
@@ -822,16 +877,24 @@ int paths_engine_level_backward(paths_engine_t* e, int level, int use_dlogits, v
 // (heads) joins them at the end.  Backward mirrors it: head chain first, the L decoder backwards concurrently, then the LSTM
 // chain from the deepest level up, each level waiting only for its own token gradient.
 static bool use_side_streams(const paths_engine* e) {
-  return e->have_streams && planes_mode(e->dm) && e->dm.d % 8 == 0 && e->dm.F % 8 == 0;
+  static const bool off = getenv("PATHS_B200_NO_STREAMS") != nullptr;
+  return !off && e->have_streams && planes_mode(e->dm) && e->dm.d % 8 == 0 && e->dm.F % 8 == 0;
 }
 
 int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int32_t* ybin, const int32_t* censored, float scale,
                          int with_loss, void* stream) {
   PATHS_REQUIRE(e && e->have_params, "forward: engine has no parameters bound");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaStream_t caller = static_cast<cudaStream_t>(stream);
+  cudaStream_t st = caller;
   const int L = e->dm.L;
+  const bool conc = use_side_streams(e);
+  if (conc) {                                            // fork: the step runs on the engine's own streams
+    PATHS_CK(cudaEventRecord(e->ev_in, caller));
+    PATHS_CK(cudaStreamWaitEvent(e->mainp, e->ev_in, 0));
+    st = e->mainp;
+  }
   if (int r = do_begin(e, slide_ids, nullptr, 0, st)) return r;
-  if (!use_side_streams(e)) {
+  if (!conc) {
     for (int l = 0; l < L; ++l) {
       if (int r = level_forward(e, l, st)) return r;
       if (l < L - 1)
@@ -852,20 +915,29 @@ int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int3
       if (int r = head_forward(e, l, st)) return r;
     }
   }
-  if (with_loss) return do_loss(e, ybin, censored, scale, st);
+  if (with_loss)
+    if (int r = do_loss(e, ybin, censored, scale, st)) return r;
+  if (conc) {                                            // join
+    PATHS_CK(cudaEventRecord(e->ev_out, st));
+    PATHS_CK(cudaStreamWaitEvent(caller, e->ev_out, 0));
+  }
   return 0;
 }
 
 int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream) {
   PATHS_REQUIRE(e && e->have_params && e->grads_base, "backward: no gradient buffer bound");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaStream_t caller = static_cast<cudaStream_t>(stream);
   const int L = e->dm.L;
-  if (zero_grads) PATHS_CK(cudaMemsetAsync(e->grads_base, 0, e->grads_floats * sizeof(float), st));
   if (!use_side_streams(e)) {
+    if (zero_grads) PATHS_CK(cudaMemsetAsync(e->grads_base, 0, e->grads_floats * sizeof(float), caller));
     for (int l = L - 1; l >= 0; --l)
-      if (int r = level_backward(e, l, l == L - 1, st)) return r;
+      if (int r = level_backward(e, l, l == L - 1, caller)) return r;
     return 0;
   }
+  PATHS_CK(cudaEventRecord(e->ev_in, caller));
+  PATHS_CK(cudaStreamWaitEvent(e->mainp, e->ev_in, 0));
+  cudaStream_t st = e->mainp;
+  if (zero_grads) PATHS_CK(cudaMemsetAsync(e->grads_base, 0, e->grads_floats * sizeof(float), st));
   for (int l = L - 1; l >= 0; --l) {
     if (int r = head_backward(e, l, l == L - 1, st)) return r;
     PATHS_CK(cudaEventRecord(e->ev_head[l], st));
@@ -877,6 +949,8 @@ int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream) {
     PATHS_CK(cudaStreamWaitEvent(st, e->ev_dtok[l], 0));
     if (int r = lstm_backward(e, l, st)) return r;
   }
+  PATHS_CK(cudaEventRecord(e->ev_out, st));
+  PATHS_CK(cudaStreamWaitEvent(caller, e->ev_out, 0));
   return 0;
 }
 

@@ -466,31 +466,26 @@ __global__ void __launch_bounds__(TPB) head_concat_bwd_kernel(const float* __res
   }
 }
 
-// dspecial[c] += sum_b dtok[special token of slide b, c]: one block, warp w takes slides w, w+8, ... (independent loads), the
-// eight partial rows are combined in a fixed order (deterministic).
+// dspecial[c] += sum_b dtok[special token of slide b, c]: a block sums 8 slides (one per warp) through shared memory and adds
+// its 8-row partial with one atomic per column.
 __global__ void __launch_bounds__(256) special_grad_kernel(const float* __restrict__ dtok, const int* __restrict__ seg,
                                                            float* __restrict__ dspecial, int d, int B) {
   __shared__ float part[8][256];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  float acc[8];
+  const int b = blockIdx.x * 8 + w;
+  const float* r = b < B ? dtok + (size_t)(seg[b] + b) * d : nullptr;
 #pragma unroll
-  for (int q = 0; q < 8; ++q) acc[q] = 0.f;
-#pragma unroll 4
-  for (int b = w; b < B; b += 8) {
-    const float* r = dtok + (size_t)(seg[b] + b) * d;
-#pragma unroll
-    for (int q = 0; q < 8; ++q)
-      if (lane + 32 * q < d) acc[q] += r[lane + 32 * q];
+  for (int q = 0; q < 8; ++q) {
+    const int c = lane + 32 * q;
+    part[w][c] = (r && c < d) ? r[c] : 0.f;
   }
-#pragma unroll
-  for (int q = 0; q < 8; ++q) part[w][lane + 32 * q] = acc[q];
   __syncthreads();
   const int c = threadIdx.x;
   if (c < d) {
     float s = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) s += part[k][c];
-    dspecial[c] += s;
+    atomicAdd(dspecial + c, s);
   }
 }
 
@@ -848,7 +843,7 @@ int head_concat_bwd(const float* dlogits, const float* Wc, const GList& gl, int 
 }
 int special_grad(const float* dtok, const int* seg, float* dspecial, int d, int B, cudaStream_t st) {
   PATHS_REQUIRE(d <= 256, "special_grad: trans_dim above 256 is not supported (d=%d)", d);
-  special_grad_kernel<<<1, 256, 0, st>>>(dtok, seg, dspecial, d, B);
+  special_grad_kernel<<<(B + 7) / 8, 256, 0, st>>>(dtok, seg, dspecial, d, B);
   PATHS_LAUNCH_CK();
   return 0;
 }

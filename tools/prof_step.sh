@@ -4,7 +4,7 @@
 set -x
 FULL="$1"; shift
 export PATHS_BENCH_CUPROF=1
-B="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e $*"
+B="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-fast-mode $*"
 $B > gpurun_out/plain.log 2>&1 && \
 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches.csv $B > gpurun_out/ncu1.log 2>&1
 echo "launch-list rc=$?"
