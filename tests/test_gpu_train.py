@@ -85,3 +85,20 @@ def test_dp_step_equals_autograd_step():
         else:
             # weight gradients accumulate with fp32 atomics: order may differ between runs
             assert rel_err(p.grad, want[n]) < 1e-5, n
+
+
+def test_device_prefetcher_same_results_as_host_batches():
+    """Batches staged one step ahead by DevicePrefetcher give bit-identical hazards/loss to host batches handed over directly."""
+    from paths_b200.data_utils.prefetch import DevicePrefetcher
+    from paths_b200.utils import inference_end2end
+    cfg, model, batch = _setup("brca_b4")
+    with torch.no_grad():
+        hz0, loss0 = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+    n = 0
+    for b in DevicePrefetcher((batch for _ in range(3)), "cuda"):
+        assert b["fts"].is_cuda and not batch["fts"].is_cuda            # the host batch itself is left untouched
+        hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
+        loss.backward()
+        assert torch.equal(hz.detach(), hz0) and torch.equal(loss.detach(), loss0)
+        n += 1
+    assert n == 3
