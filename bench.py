@@ -142,7 +142,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=os.environ.get("PATHS_B200_PRECISION", "bf16x3"), choices=["fp32", "bf16x3", "bf16"])
-    ap.add_argument("--slides-per-gpu", type=int, default=256)
+    ap.add_argument("--slides-per-gpu", type=int, default=512)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fast-mode", action="store_true")
@@ -216,6 +216,8 @@ def main():
             losses.append(float(loss.item()))
         return losses
 
+    host_ms = [0.0]
+
     def timed(fn, steps, warmup, profile=False, multi=False):
         if multi:
             fn(warmup)
@@ -235,11 +237,13 @@ def main():
             torch.cuda.cudart().cudaProfilerStart()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
+        h0 = time.perf_counter()
         if multi:
             fn(steps)
         else:
             for _ in range(steps):
                 fn()
+        host_ms[0] = (time.perf_counter() - h0) * 1e3 / steps      # host time to enqueue one step (no device sync inside)
         b.record()
         torch.cuda.synchronize()
         if cuprof:
@@ -258,6 +262,7 @@ def main():
         return ms, eng.launch_count() - l0 + (steps if world > 1 else 0), clocks
 
     ms, launches, clocks = timed(step_resident, args.steps, args.warmup, profile=True)
+    host_enqueue_ms = host_ms[0]
     over, need = eng.overflowed()
     assert not over, f"row capacity overflow ({need})"
     counts = eng.counts()
@@ -328,7 +333,7 @@ def main():
             "config": {"workload": WORKLOAD, "slides_per_gpu": B, "global_batch": B * world, "levels": Lv, "top_k": 20,
                        "packed_rows_per_step_per_gpu": rows, "rows_per_level": counts, "parallelism": f"dp{world}",
                        "l2": "per-step working set (activations ~3 GB, pyramids 16 GB) far exceeds the 126 MB L2"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "fast_mode": fast, "gpu_launches": launches, "clocks": clocks,
+            "host_enqueue_ms_per_step": host_enqueue_ms, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "fast_mode": fast, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line))
     if os.environ.get("PATHS_B200_PROF_DUMP"):               # developer aid: per-call-site timings are written at engine destruction

@@ -27,7 +27,7 @@ extern "C" {
 
 #define PATHS_MAX_LEVELS 8
 #define PATHS_MAX_LAYERS 4
-#define PATHS_ABI_VERSION 2
+#define PATHS_ABI_VERSION 3
 
 /* model_config + the train_config fields the hot path reads (config.py:19-79). */
 typedef struct paths_dims {
@@ -137,6 +137,10 @@ int paths_engine_level_backward(paths_engine_t* e, int level, int use_dlogits, v
 /* Whole step: begin, L x (level_forward, select), loss.  utils.inference_end2end (utils.py:228-279). */
 int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int32_t* ybin, const int32_t* censored, float scale,
                          int with_loss, void* stream);
+/* The same step on a collated batch whose level-0 features arrive as the reference's padded `fts` tensor [B, N, D]
+ * (data_utils/dataset.py:229-243; device memory) instead of being gathered from the resident pyramid store. */
+int paths_engine_forward_padded(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, const int32_t* ybin,
+                                const int32_t* censored, float scale, int with_loss, void* stream);
 /* loss.backward() of train.py:65: levels L-1..0.  zero_grads: clear the grad buffer first. */
 int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream);
 

@@ -3,6 +3,8 @@
 // 128 MMA-FLOP per exp, i.e. the op is SFU/latency-bound, not tensor-bound, and at T <= 4K+1 tokens it is <1 % of the
 // level's FLOPs, so it stays on the SIMT pipes: one warp per query, lanes over keys (scores) / head dims (outputs),
 // K/V tiles of 32 keys staged in shared memory, online softmax.  Long bags (20 k tokens) tile over keys the same way.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "rowops.cuh"
 
@@ -16,11 +18,18 @@ constexpr int QB = QW * AW;      // queries per block
 constexpr int KT = 32;           // keys per tile
 constexpr int MAXDH = 64;
 
-struct Seg { int t0, T; };
-__device__ __forceinline__ Seg seg_of(const int* seg, int s) { Seg r; r.t0 = seg[s] + s; r.T = seg[s + 1] - seg[s] + 1; return r; }
+// Virtual slide sv of a grouped launch = (group g = sv / B, slide s = sv % B): its tokens are rows roff[g] + seg[g][s] + s ...
+// of the concatenated qkv buffer, its compact (single-query) output row is oroff[g] + s.
+struct Seg { int t0, T, os; };
+__device__ __forceinline__ Seg seg_of(const SegGrp& sg, int sv) {
+  const int g = sv / sg.B, s = sv - g * sg.B;
+  const int* seg = pick(sg.seg, g);
+  Seg r; r.t0 = pick(sg.roff, g) + seg[s] + s; r.T = seg[s + 1] - seg[s] + 1; r.os = pick(sg.oroff, g) + s;
+  return r;
+}
 
 // out[q, h*dh + c] = sum_j softmax_j(scale * q.k_j) v_j[c];  lse[q, h] = logsumexp_j(scale * q.k_j)
-__global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+__global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                            float* __restrict__ out, float* __restrict__ lse, int d, int heads,
                                                            int nq_mode, int skip_T) {
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
@@ -86,7 +95,7 @@ __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restri
   for (int i = 0; i < QW; ++i) {
     const int q = q0 + w * QW + i;
     if (q >= nq) continue;
-    const size_t orow = nq_mode ? (size_t)s : (size_t)(sg.t0 + q);
+    const size_t orow = nq_mode ? (size_t)sg.os : (size_t)(sg.t0 + q);
     const float inv = 1.f / l[i];
     if (lane < dh) out[orow * d + h * dh + lane] = oa[i] * inv;
     if (lane + 32 < dh) out[orow * d + h * dh + lane + 32] = ob[i] * inv;
@@ -95,7 +104,7 @@ __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restri
 }
 
 // dq (and Dvec[q, h] = dout . out) for every query: dS_j = p_j (dout.v_j - D), dq = scale * sum_j dS_j k_j
-__global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+__global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                               const float* __restrict__ out, const float* __restrict__ lse,
                                                               const float* __restrict__ dout, float* __restrict__ dqkv,
                                                               float* __restrict__ Dvec, int d, int heads, int nq_mode, int skip_T) {
@@ -117,7 +126,7 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __res
     qa[i] = qb[i] = ga[i] = gb[i] = 0.f; Dq[i] = 0.f; L[i] = 0.f; da[i] = db[i] = 0.f;
     if (q < nq) {
       const float* qp = qkv + (size_t)(sg.t0 + q) * ld + h * dh;
-      const size_t orow = nq_mode ? (size_t)s : (size_t)(sg.t0 + q);
+      const size_t orow = nq_mode ? (size_t)sg.os : (size_t)(sg.t0 + q);
       float dd = 0.f;
       if (lane < dh) { qa[i] = qp[lane] * scale; ga[i] = dout[orow * d + h * dh + lane]; dd += ga[i] * out[orow * d + h * dh + lane]; }
       if (lane + 32 < dh) { qb[i] = qp[lane + 32] * scale; gb[i] = dout[orow * d + h * dh + lane + 32]; dd += gb[i] * out[orow * d + h * dh + lane + 32]; }
@@ -170,7 +179,7 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __res
 }
 
 // dk_j = sum_i dS_ij (scale q_i), dv_j = sum_i p_ij dout_i : one warp per key, lanes over queries, query tiles in smem.
-__global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+__global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                                const float* __restrict__ lse, const float* __restrict__ dout,
                                                                const float* __restrict__ Dvec, float* __restrict__ dqkv, int d,
                                                                int heads, int nq_mode, int skip_T) {
@@ -202,7 +211,7 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __re
       const int i = e / dh, c = e % dh;
       float qv = 0.f, gv = 0.f;
       if (i0 + i < nq) {
-        const size_t orow = nq_mode ? (size_t)s : (size_t)(sg.t0 + i0 + i);
+        const size_t orow = nq_mode ? (size_t)sg.os : (size_t)(sg.t0 + i0 + i);
         qv = qkv[(size_t)(sg.t0 + i0 + i) * ld + h * dh + c] * scale;
         gv = dout[orow * d + h * dh + c];
       }
@@ -212,7 +221,7 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __re
       const int i = threadIdx.x;
       float lv = 0.f, dv = 0.f;
       if (i0 + i < nq) {
-        const size_t orow = nq_mode ? (size_t)s : (size_t)(sg.t0 + i0 + i);
+        const size_t orow = nq_mode ? (size_t)sg.os : (size_t)(sg.t0 + i0 + i);
         lv = lse[orow * heads + h]; dv = Dvec[orow * heads + h];
       }
       Ls[i] = lv; Ds[i] = dv;
@@ -263,7 +272,7 @@ constexpr int SW = 4;            // warps per CTA
 constexpr int SP = 33;           // padded row stride (floats)
 
 template <int NKC>
-__global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+__global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                                  float* __restrict__ out, float* __restrict__ lse, int d, int heads,
                                                                  int nq_mode) {
   constexpr int TP = 32 * NKC;
@@ -361,7 +370,7 @@ __global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __
     for (int i = 0; i < SQ; ++i) {
       const int q = i0 + i;
       if (q < nq) {
-        const size_t orow = nq_mode ? (size_t)s : (size_t)(sg.t0 + q);
+        const size_t orow = nq_mode ? (size_t)sg.os : (size_t)(sg.t0 + q);
         out[orow * d + h * 32 + lane] = o[i] * linv[i];
         if (lane == 0) lse[orow * heads + h] = lsev[i];
       }
@@ -373,7 +382,7 @@ __global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __
 // Backward of the short-bag attention: phase A is query-major (dq), phase B key-major (dk, dv); both recompute the
 // probabilities from the saved log-sum-exp, so nothing is accumulated across warps and no atomics are needed.
 template <int NKC>
-__global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+__global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                                  const float* __restrict__ out, const float* __restrict__ lse,
                                                                  const float* __restrict__ dout, float* __restrict__ dqkv, int d,
                                                                  int heads, int nq_mode) {
@@ -419,7 +428,7 @@ __global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __
       const int item = threadIdx.x + k * SW * 32, j = item >> 3, c4 = (item & 7) * 4;
       a4[k] = b4[k] = c4r[k] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (j < nq) {
-        const size_t orow = nq_mode ? (size_t)s : (size_t)(sg.t0 + j);
+        const size_t orow = nq_mode ? (size_t)sg.os : (size_t)(sg.t0 + j);
         a4[k] = __ldg(reinterpret_cast<const float4*>(qkv + (size_t)(sg.t0 + j) * ld + h * 32 + c4));
         b4[k] = __ldg(reinterpret_cast<const float4*>(dout + orow * d + h * 32 + c4));
         c4r[k] = __ldg(reinterpret_cast<const float4*>(out + orow * d + h * 32 + c4));
@@ -437,7 +446,7 @@ __global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __
       dd += __shfl_xor_sync(0xffffffffu, dd, 4);
       if ((item & 7) == 0) {
         Ds[j] = dd;
-        Ls[j] = (j < nq) ? lse[(nq_mode ? (size_t)s : (size_t)(sg.t0 + j)) * heads + h] : 0.f;
+        Ls[j] = (j < nq) ? lse[(nq_mode ? (size_t)sg.os : (size_t)(sg.t0 + j)) * heads + h] : 0.f;
       }
     }
   }
@@ -556,10 +565,215 @@ __global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __
 
 namespace {
 // ====================================================================================================================
+// Row-per-thread-pair kernels (head_dim 32, bags of at most NT tokens: every level of the BRCA-shaped workload).  One CTA per
+// (head, slide) stages the head's K and V rows in shared memory as float4 rows; the two lanes of a pair own query i and one
+// 16-wide half of the head each: pre-scaled query half, running max / sum and 16 output accumulators live in registers, the
+// pair's partial dot products meet through one shuffle.  Every K / V access is a 16-byte load of a row all pairs of the warp
+// read at the same time (two distinct addresses per warp: broadcast, no bank conflicts), and the score row never touches
+// memory.  Keys are consumed four at a time so the online-softmax rescale is paid once per four keys.
+__device__ __forceinline__ float dot4(const float4& a, const float4& b, float acc) {
+  return fmaf(a.x, b.x, fmaf(a.y, b.y, fmaf(a.z, b.z, fmaf(a.w, b.w, acc))));
+}
+__device__ __forceinline__ void axpy4(float s, const float4& x, float4& y) {
+  y.x = fmaf(s, x.x, y.x); y.y = fmaf(s, x.y, y.y); y.z = fmaf(s, x.z, y.z); y.w = fmaf(s, x.w, y.w);
+}
+__device__ __forceinline__ float pair_sum(float v) { return v + __shfl_xor_sync(0xffffffffu, v, 1); }
+
+template <int NT>
+__global__ void __launch_bounds__(2 * NT) attn_fwd_tq_kernel(const float* __restrict__ qkv, const SegGrp seg, float* __restrict__ out,
+                                                             float* __restrict__ lse, int d, int heads) {
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.y);
+  const int T = sg.T;
+  if (T > NT) return;                                    // longer bags belong to the tiled kernels
+  extern __shared__ float4 sm4[];
+  float4* K4 = sm4;                                      // [NT + 3][8]  (3 zero rows of slack for the 4-key blocks)
+  float4* V4 = sm4 + (NT + 3) * 8;
+  const int ld = 3 * d;
+  const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
+  for (int idx = threadIdx.x; idx < (NT + 3) * 8; idx += 2 * NT) {
+    const int j = idx >> 3, c = idx & 7;
+    float4 kv = make_float4(0.f, 0.f, 0.f, 0.f), vv = kv;
+    if (j < T) {
+      kv = __ldg(reinterpret_cast<const float4*>(base + (size_t)j * ld + d) + c);
+      vv = __ldg(reinterpret_cast<const float4*>(base + (size_t)j * ld + 2 * d) + c);
+    }
+    K4[idx] = kv; V4[idx] = vv;
+  }
+  const int i = threadIdx.x >> 1, hf = (threadIdx.x & 1) * 4;    // query row, first float4 of this lane's half
+  const bool live = i < T;                                        // both lanes of a pair agree; dead pairs still shuffle
+  float4 q[4];
+  {
+    const float scale = rsqrtf(32.f);
+    const float4* qp = reinterpret_cast<const float4*>(base + (size_t)(live ? i : 0) * ld) + hf;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      q[c] = __ldg(qp + c);
+      q[c].x *= scale; q[c].y *= scale; q[c].z *= scale; q[c].w *= scale;
+    }
+  }
+  __syncthreads();
+  float4 o[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) o[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float m = -INFINITY, l = 0.f;
+  for (int j0 = 0; j0 < T; j0 += 4) {
+    float sc[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const float4* kr = K4 + (j0 + u) * 8 + hf;
+      const float a = dot4(q[0], kr[0], 0.f) + dot4(q[1], kr[1], 0.f), b = dot4(q[2], kr[2], 0.f) + dot4(q[3], kr[3], 0.f);
+      sc[u] = pair_sum(a + b);
+      if (j0 + u >= T) sc[u] = -INFINITY;
+    }
+    const float mn = fmaxf(fmaxf(m, fmaxf(sc[0], sc[1])), fmaxf(sc[2], sc[3]));
+    const float corr = expf(m - mn);                     // exp(-inf) = 0 on the first block
+    float p[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) p[u] = expf(sc[u] - mn);
+    l = l * corr + ((p[0] + p[1]) + (p[2] + p[3]));
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      o[c].x *= corr; o[c].y *= corr; o[c].z *= corr; o[c].w *= corr;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) axpy4(p[u], V4[(j0 + u) * 8 + hf + c], o[c]);
+    }
+    m = mn;
+  }
+  if (!live) return;
+  const float inv = 1.f / l;
+  float4* op = reinterpret_cast<float4*>(out + (size_t)(sg.t0 + i) * d + h * 32) + hf;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) op[c] = make_float4(o[c].x * inv, o[c].y * inv, o[c].z * inv, o[c].w * inv);
+  if (hf == 0) lse[(size_t)(sg.t0 + i) * heads + h] = m + logf(l);
+}
+
+// Backward, same layout.  Phase A (pair = query i): dS_ij = p_ij (dO_i . v_j - D_i), dq_i = scale * sum_j dS_ij k_j.
+// Phase B (pair = key j): dv_j = sum_i p_ij dO_i, dk_j = sum_i dS_ij (scale q_i).  Probabilities are recomputed from the saved
+// log-sum-exp in both phases; nothing is accumulated across pairs, so no atomics and a fixed summation order.
+template <int NT>
+__global__ void __launch_bounds__(2 * NT, NT == 96 ? 3 : NT == 128 ? 2 : NT == 64 ? 4 : 8) attn_bwd_tq_kernel(const float* __restrict__ qkv, const SegGrp seg, const float* __restrict__ out,
+                                                             const float* __restrict__ lse, const float* __restrict__ dout,
+                                                             float* __restrict__ dqkv, int d, int heads) {
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.y);
+  const int T = sg.T;
+  if (T > NT) return;
+  extern __shared__ float4 sm4[];
+  float4* Q4 = sm4;                                      // [NT][8] pre-scaled queries
+  float4* K4 = Q4 + NT * 8;
+  float4* V4 = K4 + NT * 8;
+  float4* G4 = V4 + NT * 8;                              // dO
+  float* Ls = reinterpret_cast<float*>(G4 + NT * 8);     // [NT] log-sum-exp per query
+  float* Ds = Ls + NT;                                   // [NT] dO . O per query
+  const int ld = 3 * d;
+  const float scale = rsqrtf(32.f);
+  const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
+  for (int idx = threadIdx.x; idx < NT * 8; idx += 2 * NT) {
+    const int j = idx >> 3, c = idx & 7;
+    float4 qv = make_float4(0.f, 0.f, 0.f, 0.f), kv = qv, vv = qv, gv = qv;
+    if (j < T) {
+      const float4* rp = reinterpret_cast<const float4*>(base + (size_t)j * ld) + c;
+      qv = __ldg(rp); kv = __ldg(rp + d / 4); vv = __ldg(rp + d / 2);
+      gv = __ldg(reinterpret_cast<const float4*>(dout + (size_t)(sg.t0 + j) * d + h * 32) + c);
+      qv.x *= scale; qv.y *= scale; qv.z *= scale; qv.w *= scale;
+    }
+    Q4[idx] = qv; K4[idx] = kv; V4[idx] = vv; G4[idx] = gv;
+  }
+  const int i = threadIdx.x >> 1, hf = (threadIdx.x & 1) * 4;
+  const bool live = i < T;
+  float L = 0.f, Dq = 0.f;
+  {
+    float part = 0.f;
+    if (live) {
+      const float4* op = reinterpret_cast<const float4*>(out + (size_t)(sg.t0 + i) * d + h * 32) + hf;
+      const float4* gp = reinterpret_cast<const float4*>(dout + (size_t)(sg.t0 + i) * d + h * 32) + hf;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) part = dot4(__ldg(op + c), __ldg(gp + c), part);
+      L = lse[(size_t)(sg.t0 + i) * heads + h];
+    }
+    Dq = pair_sum(part);
+    if (hf == 0) { Ls[i] = L; Ds[i] = Dq; }
+  }
+  __syncthreads();
+  {
+    // ---- phase A: this pair's query row
+    float4 q[4], g[4], dq[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { q[c] = Q4[(live ? i : 0) * 8 + hf + c]; g[c] = G4[(live ? i : 0) * 8 + hf + c]; dq[c] = make_float4(0.f, 0.f, 0.f, 0.f); }
+    for (int j = 0; j < T; ++j) {
+      float4 k[4];
+      float sa = 0.f, sb = 0.f, da = 0.f, db = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) k[c] = K4[j * 8 + hf + c];
+      sa = dot4(q[0], k[0], dot4(q[1], k[1], 0.f)); sb = dot4(q[2], k[2], dot4(q[3], k[3], 0.f));
+      da = dot4(g[0], V4[j * 8 + hf], dot4(g[1], V4[j * 8 + hf + 1], 0.f)); db = dot4(g[2], V4[j * 8 + hf + 2], dot4(g[3], V4[j * 8 + hf + 3], 0.f));
+      const float sc = pair_sum(sa + sb), dp = pair_sum(da + db);
+      const float ds = expf(sc - L) * (dp - Dq);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) axpy4(ds, k[c], dq[c]);
+    }
+    if (live) {
+      float4* dqp = reinterpret_cast<float4*>(dqkv + (size_t)(sg.t0 + i) * ld + h * 32) + hf;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) dqp[c] = make_float4(dq[c].x * scale, dq[c].y * scale, dq[c].z * scale, dq[c].w * scale);
+    }
+  }
+  {
+    // ---- phase B: this pair's key row
+    float4 k[4], v[4], dk[4], dv[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      k[c] = K4[(live ? i : 0) * 8 + hf + c]; v[c] = V4[(live ? i : 0) * 8 + hf + c];
+      dk[c] = make_float4(0.f, 0.f, 0.f, 0.f); dv[c] = dk[c];
+    }
+    for (int qi = 0; qi < T; ++qi) {
+      float4 a[4], b[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) { a[c] = Q4[qi * 8 + hf + c]; b[c] = G4[qi * 8 + hf + c]; }
+      const float sa = dot4(k[0], a[0], dot4(k[1], a[1], 0.f)), sb = dot4(k[2], a[2], dot4(k[3], a[3], 0.f));
+      const float da = dot4(v[0], b[0], dot4(v[1], b[1], 0.f)), db = dot4(v[2], b[2], dot4(v[3], b[3], 0.f));
+      const float sc = pair_sum(sa + sb), dp = pair_sum(da + db);
+      const float p = expf(sc - Ls[qi]);
+      const float ds = p * (dp - Ds[qi]);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) { axpy4(ds, a[c], dk[c]); axpy4(p, b[c], dv[c]); }
+    }
+    if (live) {
+      float4* rp = reinterpret_cast<float4*>(dqkv + (size_t)(sg.t0 + i) * ld + h * 32) + hf;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) { rp[d / 4 + c] = dk[c]; rp[d / 2 + c] = dv[c]; }
+    }
+  }
+}
+
+template <int NT>
+int launch_fwd_tq(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int B, cudaStream_t st) {
+  static bool cfg = false;
+  const int bytes = 2 * (NT + 3) * 8 * (int)sizeof(float4);
+  if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_fwd_tq_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
+  attn_fwd_tq_kernel<NT><<<dim3(heads, B), 2 * NT, bytes, st>>>(qkv, seg, out, lse, d, heads);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+template <int NT>
+int launch_bwd_tq(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d, int heads,
+                  int B, cudaStream_t st) {
+  static bool cfg = false;
+  const int bytes = 4 * NT * 8 * (int)sizeof(float4) + 2 * NT * (int)sizeof(float);
+  if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_bwd_tq_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
+  attn_bwd_tq_kernel<NT><<<dim3(heads, B), 2 * NT, bytes, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+}  // namespace
+
+namespace {
+// ====================================================================================================================
 // Single-query attention (nq_mode 1: the last decoder layer is read at the special token only, aggregator.py:75), head_dim 32.
 // One warp per (slide, head), any bag length: lanes run over the keys of a 32-key chunk for the scores (each lane reads its
 // key row), then over the head dims for the value sum (coalesced rows, probabilities by shuffle); online softmax over chunks.
-__global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+__global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                            float* __restrict__ out, float* __restrict__ lse, int d, int heads, int B) {
   const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (wid >= B * heads) return;
@@ -602,13 +816,13 @@ __global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restri
     }
     m = mn;
   }
-  out[(size_t)s * d + h * 32 + lane] = o / l;
-  if (lane == 0) lse[(size_t)s * heads + h] = m + logf(l);
+  out[(size_t)sg.os * d + h * 32 + lane] = o / l;
+  if (lane == 0) lse[(size_t)sg.os * heads + h] = m + logf(l);
 }
 
 // Backward of the single-query attention; writes the q, k and v parts of every dqkv row of the slide (q part is zero
 // except at the special token), so the caller needs no zero-fill.
-__global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restrict__ qkv, const int* __restrict__ seg,
+__global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                            const float* __restrict__ out, const float* __restrict__ lse,
                                                            const float* __restrict__ dout, float* __restrict__ dqkv, int d, int heads,
                                                            int B) {
@@ -621,9 +835,9 @@ __global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restri
   const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
   float* dbase = dqkv + (size_t)sg.t0 * ld + h * 32;
   const float qv = base[lane] * scale;
-  const float g = dout[(size_t)s * d + h * 32 + lane];
-  const float Dq = warp_sum(g * out[(size_t)s * d + h * 32 + lane]);
-  const float L = lse[(size_t)s * heads + h];
+  const float g = dout[(size_t)sg.os * d + h * 32 + lane];
+  const float Dq = warp_sum(g * out[(size_t)sg.os * d + h * 32 + lane]);
+  const float L = lse[(size_t)sg.os * heads + h];
   float dq = 0.f;
   for (int j0 = 0; j0 < sg.T; j0 += 32) {
     const int j = j0 + lane;
@@ -670,7 +884,7 @@ inline size_t small_fwd_smem(int nkc) { return (size_t)(3 * 32 * nkc * SP + SW *
 inline size_t small_bwd_smem(int nkc) { return (size_t)(4 * 32 * nkc * SP + 2 * 32 * nkc + SW * 2 * SQ * 32 * nkc) * sizeof(float); }
 
 template <int NKC>
-int launch_fwd_small(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int nq_mode, cudaStream_t st) {
+int launch_fwd_small(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int B, int nq_mode, cudaStream_t st) {
   static bool cfg = false;
   const int bytes = (int)small_fwd_smem(NKC);
   if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_fwd_small_kernel<NKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
@@ -679,7 +893,7 @@ int launch_fwd_small(const float* qkv, const int* seg, float* out, float* lse, i
   return 0;
 }
 template <int NKC>
-int launch_bwd_small(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, int d, int heads,
+int launch_bwd_small(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d, int heads,
                      int B, int nq_mode, cudaStream_t st) {
   static bool cfg = false;
   const int bytes = (int)small_bwd_smem(NKC);
@@ -691,7 +905,11 @@ int launch_bwd_small(const float* qkv, const int* seg, const float* out, const f
 }  // namespace
 
 int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st) {
+  return attn_fwd_grp(qkv, seg_single(seg, B), out, lse, d, heads, max_T, nq_mode, st);
+}
+int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st) {
   PATHS_REQUIRE(d % heads == 0 && d / heads <= MAXDH, "attention: head_dim %d unsupported (max %d)", d / heads, MAXDH);
+  const int B = seg.n * seg.B;                       // virtual slides
   if (B <= 0) return 0;
   int skip_T = 0;
   if (d / heads == 32 && nq_mode) {
@@ -699,7 +917,20 @@ int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, in
     PATHS_LAUNCH_CK();
     return 0;
   }
-  if (d / heads == 32) {                       // short bags: whole-head-in-shared-memory kernels
+  static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;   // experimental pair-per-row kernels (not faster: off)
+  if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode) {
+    const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
+    int r = 0;
+    switch (nkc) {
+      case 1: r = launch_fwd_tq<32>(qkv, seg, out, lse, d, heads, B, st); break;
+      case 2: r = launch_fwd_tq<64>(qkv, seg, out, lse, d, heads, B, st); break;
+      case 3: r = launch_fwd_tq<96>(qkv, seg, out, lse, d, heads, B, st); break;
+      default: r = launch_fwd_tq<128>(qkv, seg, out, lse, d, heads, B, st); break;
+    }
+    if (r) return r;
+    if (max_T <= SMALL_MAX_T) return 0;
+    skip_T = SMALL_MAX_T;
+  } else if (d / heads == 32) {                // whole-head-in-shared-memory kernels
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
     switch (nkc) {
@@ -723,6 +954,11 @@ int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, in
 bool attn_bwd_writes_all(int d, int heads) { return d / heads == 32; }
 int attn_bwd(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
              int heads, int B, int max_T, int nq_mode, cudaStream_t st) {
+  return attn_bwd_grp(qkv, seg_single(seg, B), out, lse, dout, dqkv, Dvec, d, heads, max_T, nq_mode, st);
+}
+int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
+                 int heads, int max_T, int nq_mode, cudaStream_t st) {
+  const int B = seg.n * seg.B;
   if (B <= 0) return 0;
   int skip_T = 0;
   if (d / heads == 32 && nq_mode) {
@@ -730,7 +966,20 @@ int attn_bwd(const float* qkv, const int* seg, const float* out, const float* ls
     PATHS_LAUNCH_CK();
     return 0;
   }
-  if (d / heads == 32) {
+  static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;
+  if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode) {
+    const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
+    int r = 0;
+    switch (nkc) {
+      case 1: r = launch_bwd_tq<32>(qkv, seg, out, lse, dout, dqkv, d, heads, B, st); break;
+      case 2: r = launch_bwd_tq<64>(qkv, seg, out, lse, dout, dqkv, d, heads, B, st); break;
+      case 3: r = launch_bwd_tq<96>(qkv, seg, out, lse, dout, dqkv, d, heads, B, st); break;
+      default: r = launch_bwd_tq<128>(qkv, seg, out, lse, dout, dqkv, d, heads, B, st); break;
+    }
+    if (r) return r;
+    if (max_T <= SMALL_MAX_T) return 0;
+    skip_T = SMALL_MAX_T;
+  } else if (d / heads == 32) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
     switch (nkc) {

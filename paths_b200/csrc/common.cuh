@@ -103,6 +103,59 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// ---- row groups --------------------------------------------------------------------------------------------------------
+// The aggregators (decoders) of the L magnification levels are independent problems with the same shapes but their own weights
+// and their own row counts.  Their token-shaped buffers are laid out back to back in one allocation (level l owns rows
+// [roff[l], roff[l] + capacity_l), roff a multiple of 128) so that ONE launch can serve every level: a kernel receives the
+// buffer's base pointer plus a Grp describing which row regions are live, and per-group parameter pointers (PtrL / MutL).
+constexpr int kMaxGroups = 8;        // == PATHS_MAX_LEVELS
+struct Grp {
+  int n;                             // number of groups
+  int roff[kMaxGroups];              // first row of each group in the concatenated buffer
+  int hcnt[kMaxGroups];              // host-side row count (capacity when cnt[g] != nullptr)
+  const int* cnt[kMaxGroups];        // live row count on the device, or nullptr => hcnt
+};
+struct PtrL { const float* p[kMaxGroups]; };
+struct MutL { float* p[kMaxGroups]; };
+struct IdxL { const int* p[kMaxGroups]; };
+// Select entry g of a per-group table held in kernel parameters with compile-time indices only: a dynamically indexed
+// parameter array would be copied to local memory by every thread at kernel entry.
+template <typename T>
+__host__ __device__ __forceinline__ T pick(const T (&a)[kMaxGroups], int g) {
+  T r = a[0];
+#pragma unroll
+  for (int k = 1; k < kMaxGroups; ++k) r = (g == k) ? a[k] : r;
+  return r;
+}
+__host__ __device__ __forceinline__ int grp_count(const Grp& g, int i) {
+#ifdef __CUDA_ARCH__
+  const int* c = pick(g.cnt, i);
+  return c ? *c : pick(g.hcnt, i);
+#else
+  return g.hcnt[i];
+#endif
+}
+inline Grp grp_single(int M_host, const int* M_dev, int roff = 0) {
+  Grp g; g.n = 1;
+  for (int i = 0; i < kMaxGroups; ++i) { g.roff[i] = 0; g.hcnt[i] = 0; g.cnt[i] = nullptr; }
+  g.roff[0] = roff; g.hcnt[0] = M_host; g.cnt[0] = M_dev;
+  return g;
+}
+inline int grp_max_rows(const Grp& g) { int m = 0; for (int i = 0; i < g.n; ++i) if (g.hcnt[i] > m) m = g.hcnt[i]; return m; }
+inline PtrL ptrl1(const float* p) { PtrL l; for (int i = 0; i < kMaxGroups; ++i) l.p[i] = nullptr; l.p[0] = p; return l; }
+inline MutL mutl1(float* p) { MutL l; for (int i = 0; i < kMaxGroups; ++i) l.p[i] = nullptr; l.p[0] = p; return l; }
+inline IdxL idxl1(const int* p) { IdxL l; for (int i = 0; i < kMaxGroups; ++i) l.p[i] = nullptr; l.p[0] = p; return l; }
+
+// Grouped contraction: group g reads/writes rows of the concatenated activation buffers per `rows`, contracts against the
+// g-th member of a stacked packed weight (wlev[g] = index inside the stack), adds bias[g]; the weight-gradient form (TN)
+// reduces over the group's rows into cout[g].
+struct GemmGrp {
+  Grp rows;
+  int wlev[kMaxGroups];
+  const float* bias[kMaxGroups];
+  float* cout[kMaxGroups];
+};
+
 enum GemmFlags { GEMM_RELU = 1, GEMM_ACCUM = 2 };
 
 // Precision modes of the dense contractions.

@@ -38,15 +38,19 @@ int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ld
 int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q_col0, float* C, int ldc, int M_host, const int* M_dev, int NI,
                  int NJ, cudaStream_t st);
 int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Planes& dst, int col0, bool want_lo, cudaStream_t st);
+bool gemm_tc_supported_nt_grp(const RowSrc& A, const float* B, int ldb, int N, int K);
+int gemm_nt_tc_grp(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const GemmGrp& gg, int N, int K, int flags,
+                   cudaStream_t st);
+int gemm_tn_tc_grp(int passes, const float* P, int ldp, const RowSrc& Q, int ldc, const GemmGrp& gg, int NI, int NJ, cudaStream_t st);
 size_t packed_bytes(int R, int Cc);
-int register_packed(const float* src, int R, int Cc, int ld, void* dst);
+int register_packed(const float* src, int R, int Cc, int ld, void* dst, int nstack);
 void unregister_packed(const float* src);
 int build_pack_jobs(const float* const* srcs, int n, void* jobs_dev, int* n_jobs, cudaStream_t st);
 int run_pack_jobs(const void* jobs_dev, int n_jobs, cudaStream_t st);
 size_t pack_job_bytes();
 void set_tc_scratch(void* a, size_t a_bytes, void* b, size_t b_bytes);
 size_t tc_scratch_bytes(int rows, int cols);
-size_t tn_workspace_bytes(int NI, int NJ, int M_host);
+size_t tn_workspace_bytes(int NI, int NJ, int M_host, int ngroups);
 void set_tn_workspace(void* p, size_t bytes);
 
 int gemm_nt(int prec, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
@@ -100,12 +104,15 @@ struct Level {
   float *xhf, *rsf, *z, *F, *logits, *dlogits, *dHrow, *dCrow;
   float *dFc;                        // slide_ctx_mode "concat": d loss / d F_l written by the last level's head backward
   Planes AxhP, CnP, YP;              // tensor-core operand planes written by the producers: [x || h_parent], c', Y
-  // decoder scratch, one set per level so the levels' aggregators can run concurrently on their own streams
+  // decoder buffers.  Every token-shaped ([tokens, *]) and slide-shaped ([B, *]) decoder buffer of the L levels is ONE allocation
+  // with the levels back to back (level l at rows tok_off[l] resp. l * B): lv[0]'s pointer is the base of the concatenated
+  // buffer, lv[l]'s the level's slice, so the same kernels serve one level or, in a single grouped launch, any set of levels.
+  int tok_off;                                           // first token row of this level in the concatenated buffers
   float *A1, *Fo;                                        // forward temporaries [tokens, d]
+  float *A1b, *Fob;                                      // ... and their [B, d] counterparts (last layer: special-token rows only)
   float *ga, *gb, *gO, *gt, *dqkv, *dHf, *Dvec;          // backward, token-shaped
+  float *gab, *gbb, *gOb, *dHfb;                         // backward, slide-shaped (last layer)
   float *dFl, *dy3s;                                     // [B, d]: d loss / d F_l, gradient entering the last decoder layer
-  const float* dtok;                                     // gradient w.r.t. the level's tokens (points into ga / gt)
-  char* tn_ws; size_t tn_ws_bytes;                       // stream-K workspace of this level's decoder weight gradients
 };
 
 struct LayerP { const float *Wqkv, *bqkv, *Wo, *bo, *bcross, *W1, *b1, *W2, *b2, *n1w, *n1b, *n2w, *n2b, *n3w, *n3b; };
@@ -151,6 +158,13 @@ struct paths_engine {
   // bf16 (hi, lo) planes of every weight matrix the tensor-core path contracts against
   char* tc_scratch[2]; size_t tc_scratch_each;
   char* tn_ws; size_t tn_ws_bytes;                       // stream-K partial tiles of the weight-gradient contractions
+  char* dec_tn_ws[PATHS_MAX_LEVELS]; size_t dec_tn_ws_bytes;   // ... of the decoder sets (one per concurrently running set)
+  const float* dtok_base;                                // gradient w.r.t. the tokens, concatenated (one of lv[0].ga / lv[0].gt)
+  bool stacked;                                          // decoder weights are packed as per-kind stacks over the levels
+  // level sets of the whole-step entry points: each set's aggregators run as one grouped pass on the set's own stream
+  int n_fsets, n_bsets;
+  int fset_n[PATHS_MAX_LEVELS], fset_lv[PATHS_MAX_LEVELS][PATHS_MAX_LEVELS];
+  int bset_n[PATHS_MAX_LEVELS], bset_lv[PATHS_MAX_LEVELS][PATHS_MAX_LEVELS];
   char* packed_arena; size_t packed_arena_bytes;
   void* pack_jobs; int n_pack_jobs;
   std::vector<const float*> packed_srcs;
@@ -168,11 +182,61 @@ size_t carve(paths_engine* e, char* base) {
   const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F;
   Bump b{base, 0};
   int maxcap = 0;
+  size_t Ttot = 0;
   for (int l = 0; l < dm.L; ++l) {
     Level& v = e->lv[l];
-    const size_t cap = v.cap, tokcap = (size_t)v.cap + B;
-    v.ncap_tok = (int)tokcap;
+    v.ncap_tok = v.cap + B;
+    v.tok_off = (int)Ttot;
+    Ttot += (size_t)v.ncap_tok;
     if (v.cap > maxcap) maxcap = v.cap;
+  }
+  // concatenated decoder buffers: one allocation of [Ttot, cols] (token-shaped) or [L * B, cols] (slide-shaped), sliced per level
+  auto cat_tok = [&](size_t cols, float* Level::*m) {
+    float* base_p = b.take<float>(Ttot * cols);
+    for (int l = 0; l < dm.L; ++l) e->lv[l].*m = base_p ? base_p + (size_t)e->lv[l].tok_off * cols : nullptr;
+  };
+  auto cat_b = [&](size_t cols, float* Level::*m) {
+    float* base_p = b.take<float>((size_t)dm.L * B * cols);
+    for (int l = 0; l < dm.L; ++l) e->lv[l].*m = base_p ? base_p + (size_t)l * B * cols : nullptr;
+  };
+  auto cat_layer = [&](int j, bool tokens, size_t cols, float* LayerBuf::*m) {
+    const size_t rows = tokens ? Ttot : (size_t)dm.L * B;
+    float* base_p = b.take<float>(rows * cols);
+    for (int l = 0; l < dm.L; ++l)
+      e->lv[l].layer[j].*m = base_p ? base_p + (tokens ? (size_t)e->lv[l].tok_off : (size_t)l * B) * cols : nullptr;
+  };
+  cat_tok(d, &Level::tok);
+  for (int j = 0; j < dm.layers; ++j) {
+    const bool tk = j != dm.layers - 1;                 // the last layer is evaluated at the special tokens only: [B, *] rows
+    cat_layer(j, true, 3 * d, &LayerBuf::qkv);
+    cat_layer(j, tk, d, &LayerBuf::O); cat_layer(j, tk, dm.heads, &LayerBuf::lse);
+    cat_layer(j, tk, d, &LayerBuf::y1); cat_layer(j, tk, d, &LayerBuf::xh1); cat_layer(j, tk, 1, &LayerBuf::rs1);
+    cat_layer(j, tk, d, &LayerBuf::y2); cat_layer(j, tk, d, &LayerBuf::xh2); cat_layer(j, tk, 1, &LayerBuf::rs2);
+    cat_layer(j, tk, F, &LayerBuf::Hf);
+    cat_layer(j, tk, d, &LayerBuf::y3); cat_layer(j, tk, d, &LayerBuf::xh3); cat_layer(j, tk, 1, &LayerBuf::rs3);
+  }
+  cat_b(d, &Level::xhf); cat_b(1, &Level::rsf); cat_b(d, &Level::z);
+  cat_tok(d, &Level::A1); cat_tok(d, &Level::Fo); cat_b(d, &Level::A1b); cat_b(d, &Level::Fob);
+  cat_tok(d, &Level::ga); cat_tok(d, &Level::gb); cat_tok(d, &Level::gO); cat_tok(d, &Level::gt);
+  cat_tok(3 * d, &Level::dqkv); cat_tok(F, &Level::dHf); cat_tok(dm.heads, &Level::Dvec);
+  cat_b(d, &Level::gab); cat_b(d, &Level::gbb); cat_b(d, &Level::gOb); cat_b(F, &Level::dHfb);
+  cat_b(d, &Level::dFl); cat_b(d, &Level::dy3s);
+  {
+    const int dec_shapes[][2] = {{3 * d, d}, {d, d}, {F, d}, {d, F}};
+    size_t tnb = 0;
+    int tokmax = 1;
+    for (int l = 0; l < dm.L; ++l) if (e->lv[l].ncap_tok > tokmax) tokmax = e->lv[l].ncap_tok;
+    for (const auto& sh : dec_shapes)
+      for (int ng = 1; ng <= dm.L; ++ng) {
+        const size_t need = tn_workspace_bytes(sh[0], sh[1], tokmax, ng);
+        if (need > tnb) tnb = need;
+      }
+    e->dec_tn_ws_bytes = tnb;
+    for (int l = 0; l < dm.L; ++l) e->dec_tn_ws[l] = b.take<char>(tnb);
+  }
+  for (int l = 0; l < dm.L; ++l) {
+    Level& v = e->lv[l];
+    const size_t cap = v.cap;
     v.count = b.take<int>(1); v.ntok = b.take<int>(1);
     v.seg = b.take<int>(B + 1); v.tseg = b.take<int>(B);
     v.row_slide = b.take<int>(cap); v.row_xy = b.take<int>(2 * cap); v.row_parent = b.take<int>(cap);
@@ -181,35 +245,10 @@ size_t carve(paths_engine* e, char* base) {
     v.child_of = b.take<int>(4 * cap);
     v.X = b.take<float>(cap * D); v.G = b.take<float>(dm.lstm ? cap * (3 * C + D) : 4); v.Cn = b.take<float>(cap * C);
     v.Pt = b.take<float>(cap * D); v.H = b.take<float>(cap * D); v.Y = b.take<float>(cap * D);
-    v.UV = b.take<float>(cap * (I + d)); v.alpha = b.take<float>(cap); v.tok = b.take<float>(tokcap * d);
-    for (int j = 0; j < dm.layers; ++j) {
-      LayerBuf& y = v.layer[j];
-      const size_t rows = (j == dm.layers - 1) ? (size_t)B : tokcap;
-      y.qkv = b.take<float>(tokcap * 3 * d);
-      y.O = b.take<float>(rows * d); y.lse = b.take<float>(rows * dm.heads);
-      y.y1 = b.take<float>(rows * d); y.xh1 = b.take<float>(rows * d); y.rs1 = b.take<float>(rows);
-      y.y2 = b.take<float>(rows * d); y.xh2 = b.take<float>(rows * d); y.rs2 = b.take<float>(rows);
-      y.Hf = b.take<float>(rows * F);
-      y.y3 = b.take<float>(rows * d); y.xh3 = b.take<float>(rows * d); y.rs3 = b.take<float>(rows);
-    }
-    v.xhf = b.take<float>((size_t)B * d); v.rsf = b.take<float>(B); v.z = b.take<float>((size_t)B * d);
+    v.UV = b.take<float>(cap * (I + d)); v.alpha = b.take<float>(cap);
     v.F = b.take<float>((size_t)B * d); v.logits = b.take<float>((size_t)B * dm.nl); v.dlogits = b.take<float>((size_t)B * dm.nl);
     v.dHrow = b.take<float>(cap * D); v.dCrow = b.take<float>(cap * C);
     v.dFc = b.take<float>((size_t)B * d);
-    v.A1 = b.take<float>(tokcap * d); v.Fo = b.take<float>(tokcap * d);
-    v.ga = b.take<float>(tokcap * d); v.gb = b.take<float>(tokcap * d); v.gO = b.take<float>(tokcap * d); v.gt = b.take<float>(tokcap * d);
-    v.dqkv = b.take<float>(tokcap * 3 * d); v.dHf = b.take<float>(tokcap * F); v.Dvec = b.take<float>(tokcap * dm.heads);
-    v.dFl = b.take<float>((size_t)B * d); v.dy3s = b.take<float>((size_t)B * d);
-    {
-      const int dec_shapes[][2] = {{3 * d, d}, {d, d}, {F, d}, {d, F}};
-      size_t tnb = 0;
-      for (const auto& sh : dec_shapes) {
-        const size_t need = tn_workspace_bytes(sh[0], sh[1], (int)tokcap);
-        if (need > tnb) tnb = need;
-      }
-      v.tn_ws_bytes = tnb;
-      v.tn_ws = b.take<char>(tnb);
-    }
     if (dm.lstm) {
       v.AxhP = planes_at(b.take<char>(planes_bytes(v.cap, 2 * D)), v.cap, 2 * D);
       v.CnP = planes_at(b.take<char>(planes_bytes(v.cap, C)), v.cap, C);
@@ -252,7 +291,7 @@ size_t carve(paths_engine* e, char* base) {
     const int tn_shapes[][2] = {{3 * C + D, 2 * D}, {D, C}, {C, D}, {I + d, D}, {I, D}, {d, D}, {3 * d, d}, {d, d}, {F, d}, {d, F}};
     size_t tnb = 0;
     for (const auto& sh : tn_shapes) {
-      const size_t need = tn_workspace_bytes(sh[0], sh[1], e->maxtok);
+      const size_t need = tn_workspace_bytes(sh[0], sh[1], e->maxtok, 1);
       if (need > tnb) tnb = need;
     }
     e->tn_ws_bytes = tnb;
@@ -404,34 +443,122 @@ int lstm_forward(paths_engine* e, int l, cudaStream_t st) {
   return 0;
 }
 
+// ---- level sets ---------------------------------------------------------------------------------------------------------
+// The aggregators of different levels are independent problems of identical shapes: a DecSet names the levels one pass of
+// decoder_forward / decoder_backward serves, every kernel of the pass being ONE grouped launch over the levels' row regions of
+// the concatenated buffers (common.cuh: Grp).  A set of one level reproduces the per-level behaviour (level API, fallbacks).
+struct DecSet {
+  int n; int lv[PATHS_MAX_LEVELS];
+  Grp gt, gb;                          // token-shaped / slide-shaped row groups
+  SegGrp sg;                           // slide segments for the attention kernels
+  GIdx tsegI, segI;                    // special-token rows (tseg) and segment offsets, relative to the level's token region
+  int max_T;
+};
+
+DecSet make_set(const paths_engine* e, const int* lvls, int n) {
+  DecSet S;
+  S.n = n; S.max_T = 1;
+  S.gt.n = S.gb.n = n; S.sg.n = n; S.sg.B = e->B;
+  for (int g = 0; g < kMaxGroups; ++g) {
+    S.gt.roff[g] = S.gb.roff[g] = 0; S.gt.hcnt[g] = S.gb.hcnt[g] = 0; S.gt.cnt[g] = S.gb.cnt[g] = nullptr;
+    S.sg.seg[g] = nullptr; S.sg.roff[g] = S.sg.oroff[g] = 0;
+    S.tsegI.idx.p[g] = S.segI.idx.p[g] = nullptr; S.tsegI.roff[g] = S.segI.roff[g] = 0;
+    S.lv[g] = 0;
+  }
+  for (int g = 0; g < n; ++g) {
+    const int l = lvls[g];
+    const Level& v = e->lv[l];
+    S.lv[g] = l;
+    S.gt.roff[g] = v.tok_off; S.gt.hcnt[g] = v.ncap_tok; S.gt.cnt[g] = v.ntok;
+    S.gb.roff[g] = l * e->B; S.gb.hcnt[g] = e->B; S.gb.cnt[g] = nullptr;
+    S.sg.seg[g] = v.seg; S.sg.roff[g] = v.tok_off; S.sg.oroff[g] = l * e->B;
+    S.tsegI.idx.p[g] = v.tseg; S.tsegI.roff[g] = v.tok_off;
+    S.segI.idx.p[g] = v.seg; S.segI.roff[g] = v.tok_off;
+    if (v.maxseg + 1 > S.max_T) S.max_T = v.maxseg + 1;
+  }
+  return S;
+}
+
+template <typename Fn> PtrL PL(const DecSet& S, Fn f) { PtrL r; for (int g = 0; g < kMaxGroups; ++g) r.p[g] = g < S.n ? f(S.lv[g]) : nullptr; return r; }
+template <typename Fn> MutL ML(const DecSet& S, Fn f) { MutL r; for (int g = 0; g < kMaxGroups; ++g) r.p[g] = g < S.n ? const_cast<float*>(f(S.lv[g])) : nullptr; return r; }
+inline PtrL PL0() { return ptrl1(nullptr); }
+inline MutL ML0() { return mutl1(nullptr); }
+inline GIdx noidx() { return gidx1(nullptr); }
+
+// C rows of every group (+)= act(A rows . W_level^T + bias_level): grouped tensor-core launch when the weights are stacked,
+// per-level contractions otherwise (fp32 SIMT mode, odd dimensions).  A and C are bases of concatenated buffers.
+template <typename WF>
+int gemm_nt_set(paths_engine* e, const DecSet& S, const Grp& rows, const float* A, int lda, WF W, int ldb, int b_kn, float* C, int ldc,
+                const PtrL& bias, int N, int K, int flags, cudaStream_t st) {
+  const int prec = e->dm.precision;
+  if (prec != PREC_FP32_SIMT && e->stacked && gemm_tc_supported_nt_grp(row_src(A, lda, K), W(0), ldb, N, K)) {
+    GemmGrp gg;
+    gg.rows = rows;
+    for (int g = 0; g < kMaxGroups; ++g) { gg.wlev[g] = g < S.n ? S.lv[g] : 0; gg.bias[g] = bias.p[g]; gg.cout[g] = nullptr; }
+    return gemm_nt_tc_grp(prec == PREC_BF16X3_TC ? 3 : 1, row_src(A, lda, K), W(0), ldb, b_kn, C, ldc, gg, N, K, flags, st);
+  }
+  for (int g = 0; g < S.n; ++g) {
+    const size_t r0 = rows.roff[g];
+    if (int r = gemm_nt(prec, row_src(A + r0 * lda, lda, K), W(S.lv[g]), ldb, b_kn, C + r0 * ldc, ldc, bias.p[g], rows.hcnt[g], rows.cnt[g], N, K,
+                        flags, st))
+      return r;
+  }
+  return 0;
+}
+// dW_level[NI, NJ] += P rows^T . Q rows over every group's rows
+template <typename GF>
+int gemm_tn_set(paths_engine* e, const DecSet& S, const Grp& rows, const float* P, int ldp, const float* Q, int ldq, GF dW, int ldc, int NI, int NJ,
+                cudaStream_t st) {
+  const int prec = e->dm.precision;
+  if (prec != PREC_FP32_SIMT && gemm_tc_supported_tn(ldp, row_src(Q, ldq, NJ), ldc, NI, NJ) && ldp % 8 == 0 && ldq % 8 == 0) {
+    GemmGrp gg;
+    gg.rows = rows;
+    for (int g = 0; g < kMaxGroups; ++g) { gg.wlev[g] = 0; gg.bias[g] = nullptr; gg.cout[g] = g < S.n ? const_cast<float*>(dW(S.lv[g])) : nullptr; }
+    return gemm_tn_tc_grp(prec == PREC_BF16X3_TC ? 3 : 1, P, ldp, row_src(Q, ldq, NJ), ldc, gg, NI, NJ, st);
+  }
+  for (int g = 0; g < S.n; ++g) {
+    const size_t r0 = rows.roff[g];
+    if (int r = gemm_tn(prec, P + r0 * ldp, ldp, row_src(Q + r0 * ldq, ldq, NJ), const_cast<float*>(dW(S.lv[g])), ldc, rows.hcnt[g], rows.cnt[g], NI, NJ,
+                        st))
+      return r;
+  }
+  return 0;
+}
+
 // ---- part 2: transformer aggregator -- decoder layers over packed tokens, last layer evaluated at the special token only.
-// Reads only this level's tokens and writes only this level's buffers (safe on a per-level stream).
-int decoder_forward(paths_engine* e, int l, cudaStream_t st) {
+// Reads only the set's tokens and writes only the set's rows of the decoder buffers (safe on the set's own stream).
+int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
   const paths_dims_t& dm = e->dm;
-  const int B = e->B, d = dm.d, F = dm.F, prec = dm.precision;
-  Level& v = e->lv[l];
-  const LevelP& p = e->P.level[l];
+  const int d = dm.d, F = dm.F;
+  Level& v0 = e->lv[0];                                  // base pointers of the concatenated buffers
+  const LevelP* P = e->P.level;
   ProfScope ps_dec(e, PATHS_PROF_DEC_FWD, st);
-  const int Mt = v.ncap_tok;
-  const int* Mtd = v.ntok;
-  const float* t_in = v.tok;
+  const float* t_in = v0.tok;
   for (int j = 0; j < dm.layers; ++j) {
-    const LayerP& w = p.layer[j];
-    LayerBuf& y = v.layer[j];
+    LayerBuf& y = v0.layer[j];
     const bool last = j == dm.layers - 1;
-    const int R = last ? B : Mt;
-    const int* Rd = last ? nullptr : Mtd;
-    RUN(gemm_nt(prec, row_src(t_in, d, d), w.Wqkv, d, 0, y.qkv, 3 * d, w.bqkv, Mt, Mtd, 3 * d, d, 0, st));
-    RUN(attn_fwd(y.qkv, v.seg, y.O, y.lse, d, dm.heads, B, v.maxseg + 1, last ? 1 : 0, st));
-    RUN(gemm_nt(prec, row_src(y.O, d, d), w.Wo, d, 0, v.A1, d, nullptr, R, Rd, d, d, 0, st));
-    RUN(res_ln_fwd(t_in, last ? v.tseg : nullptr, v.A1, w.bo, w.n1w, w.n1b, y.y1, y.xh1, y.rs1, d, 1e-5f, last ? B : Mt, Rd, 0, st));
-    RUN(res_ln_fwd(y.y1, nullptr, nullptr, w.bcross, w.n2w, w.n2b, y.y2, y.xh2, y.rs2, d, 1e-5f, last ? B : Mt, Rd, 0, st));
-    RUN(gemm_nt(prec, row_src(y.y2, d, d), w.W1, d, 0, y.Hf, F, w.b1, R, Rd, F, d, GEMM_RELU, st));
-    RUN(gemm_nt(prec, row_src(y.Hf, F, F), w.W2, F, 0, v.Fo, d, nullptr, R, Rd, d, F, 0, st));
-    RUN(res_ln_fwd(y.y2, nullptr, v.Fo, w.b2, w.n3w, w.n3b, y.y3, y.xh3, y.rs3, d, 1e-5f, last ? B : Mt, Rd, 0, st));
+    const Grp& gr = last ? S.gb : S.gt;
+    float* A1 = last ? v0.A1b : v0.A1;
+    float* Fo = last ? v0.Fob : v0.Fo;
+    RUN(gemm_nt_set(e, S, S.gt, t_in, d, [&](int l) { return P[l].layer[j].Wqkv; }, d, 0, y.qkv, 3 * d,
+                    PL(S, [&](int l) { return P[l].layer[j].bqkv; }), 3 * d, d, 0, st));
+    RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st));
+    RUN(gemm_nt_set(e, S, gr, y.O, d, [&](int l) { return P[l].layer[j].Wo; }, d, 0, A1, d, PL0(), d, d, 0, st));
+    RUN(res_ln_fwd_grp(t_in, last ? S.tsegI : noidx(), A1, PL(S, [&](int l) { return P[l].layer[j].bo; }),
+                       PL(S, [&](int l) { return P[l].layer[j].n1w; }), PL(S, [&](int l) { return P[l].layer[j].n1b; }), y.y1, y.xh1, y.rs1, d,
+                       1e-5f, gr, st));
+    RUN(res_ln_fwd_grp(y.y1, noidx(), nullptr, PL(S, [&](int l) { return P[l].layer[j].bcross; }),
+                       PL(S, [&](int l) { return P[l].layer[j].n2w; }), PL(S, [&](int l) { return P[l].layer[j].n2b; }), y.y2, y.xh2, y.rs2, d,
+                       1e-5f, gr, st));
+    RUN(gemm_nt_set(e, S, gr, y.y2, d, [&](int l) { return P[l].layer[j].W1; }, d, 0, y.Hf, F, PL(S, [&](int l) { return P[l].layer[j].b1; }), F,
+                    d, GEMM_RELU, st));
+    RUN(gemm_nt_set(e, S, gr, y.Hf, F, [&](int l) { return P[l].layer[j].W2; }, F, 0, Fo, d, PL0(), d, F, 0, st));
+    RUN(res_ln_fwd_grp(y.y2, noidx(), Fo, PL(S, [&](int l) { return P[l].layer[j].b2; }), PL(S, [&](int l) { return P[l].layer[j].n3w; }),
+                       PL(S, [&](int l) { return P[l].layer[j].n3b; }), y.y3, y.xh3, y.rs3, d, 1e-5f, gr, st));
     t_in = y.y3;
   }
-  RUN(res_ln_fwd(t_in, nullptr, nullptr, nullptr, p.nfw, p.nfb, v.z, v.xhf, v.rsf, d, 1e-5f, B, nullptr, 0, st));
+  RUN(res_ln_fwd_grp(t_in, noidx(), nullptr, PL0(), PL(S, [&](int l) { return P[l].nfw; }), PL(S, [&](int l) { return P[l].nfb; }), v0.z, v0.xhf,
+                     v0.rsf, d, 1e-5f, S.gb, st));
   return 0;
 }
 
@@ -454,7 +581,7 @@ int head_forward(paths_engine* e, int l, cudaStream_t st) {
 
 int level_forward(paths_engine* e, int l, cudaStream_t st) {
   if (int r = lstm_forward(e, l, st)) return r;
-  if (int r = decoder_forward(e, l, st)) return r;
+  if (int r = decoder_forward(e, make_set(e, &l, 1), st)) return r;
   return head_forward(e, l, st);
 }
 
@@ -491,59 +618,67 @@ int head_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   return 0;
 }
 
-// ---- part 2: aggregator backward, dFl -> gradient of the level's tokens (v.dtok) and of the level's decoder parameters.
-// Touches only this level's buffers, scratch and parameter gradients (safe on a per-level stream).
-int decoder_backward(paths_engine* e, int l, cudaStream_t st) {
+// ---- part 2: aggregator backward of a level set, dFl -> gradient of the tokens (e->dtok_base) and of the decoder parameters.
+// Touches only the set's rows of the decoder buffers, the set's workspace and parameter gradients (safe on the set's own stream).
+int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t st) {
   const paths_dims_t& dm = e->dm;
-  set_tn_workspace(e->lv[l].tn_ws, e->lv[l].tn_ws_bytes);
-  const int B = e->B, d = dm.d, F = dm.F, prec = dm.precision;
-  Level& v = e->lv[l];
-  const LevelP& p = e->P.level[l];
-  const LevelP& g = e->Gr.level[l];
-  const int Mt = v.ncap_tok;
-  const int* Mtd = v.ntok;
+  set_tn_workspace(e->dec_tn_ws[ws_slot], e->dec_tn_ws_bytes);
+  const int B = e->B, d = dm.d, F = dm.F;
+  Level& v0 = e->lv[0];
+  const LevelP* P = e->P.level;
+  const LevelP* G = e->Gr.level;
   ProfScope ps_dec(e, PATHS_PROF_DEC_BWD, st);
   // ---- final LayerNorm at the special tokens
-  RUN(ln_bwd(v.dFl, nullptr, v.xhf, v.rsf, p.nfw, v.dy3s, nullptr, 0, W_(g.nfw), W_(g.nfb), nullptr, d, B, nullptr, 0, st));
+  RUN(ln_bwd_grp(v0.dFl, nullptr, v0.xhf, v0.rsf, PL(S, [&](int l) { return P[l].nfw; }), v0.dy3s, noidx(), 0,
+                 ML(S, [&](int l) { return G[l].nfw; }), ML(S, [&](int l) { return G[l].nfb; }), ML0(), d, S.gb, st));
 
-  const float* dy3 = v.dy3s;
+  const float* dy3 = v0.dy3s;
+  float* ga = v0.ga; float* gtk = v0.gt;                 // token-shaped ping-pong pair
   for (int j = dm.layers - 1; j >= 0; --j) {
-    const LayerP& w = p.layer[j];
-    const LayerP& gw = g.layer[j];
-    LayerBuf& y = v.layer[j];
+    LayerBuf& y = v0.layer[j];
     const bool last = j == dm.layers - 1;
-    const int R = last ? B : Mt;
-    const int* Rd = last ? nullptr : Mtd;
-    const float* t_in = j == 0 ? v.tok : v.layer[j - 1].y3;
-    // LN3 -> ga = d(y2 + ffn); db2
-    RUN(ln_bwd(dy3, nullptr, y.xh3, y.rs3, w.n3w, v.ga, nullptr, 0, W_(gw.n3w), W_(gw.n3b), W_(gw.b2), d, R, Rd, 0, st));
-    RUN(gemm_nt(prec, row_src(v.ga, d, d), w.W2, F, 1, v.dHf, F, nullptr, R, Rd, F, d, 0, st));
-    RUN(gemm_tn(prec, v.ga, d, row_src(y.Hf, F, F), W_(gw.W2), F, R, Rd, d, F, st));
-    RUN(relu_bwd(v.dHf, y.Hf, F, R, Rd, 0, W_(gw.b1), st));
-    RUN(gemm_tn(prec, v.dHf, F, row_src(y.y2, d, d), W_(gw.W1), d, R, Rd, F, d, st));
-    RUN(gemm_nt(prec, row_src(v.dHf, F, F), w.W1, d, 1, v.ga, d, nullptr, R, Rd, d, F, GEMM_ACCUM, st));     // ga = dy2
+    const Grp& gr = last ? S.gb : S.gt;
+    float* gA = last ? v0.gab : ga;
+    float* gB = last ? v0.gbb : v0.gb;
+    float* gO = last ? v0.gOb : v0.gO;
+    float* dHf = last ? v0.dHfb : v0.dHf;
+    const float* t_in = j == 0 ? v0.tok : v0.layer[j - 1].y3;
+    auto Wl = [&](int l) -> const LayerP& { return P[l].layer[j]; };
+    auto Gl = [&](int l) -> const LayerP& { return G[l].layer[j]; };
+    // LN3 -> gA = d(y2 + ffn); db2
+    RUN(ln_bwd_grp(dy3, nullptr, y.xh3, y.rs3, PL(S, [&](int l) { return Wl(l).n3w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n3w; }),
+                   ML(S, [&](int l) { return Gl(l).n3b; }), ML(S, [&](int l) { return Gl(l).b2; }), d, gr, st));
+    RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).W2; }, F, 1, dHf, F, PL0(), F, d, 0, st));
+    RUN(gemm_tn_set(e, S, gr, gA, d, y.Hf, F, [&](int l) { return Gl(l).W2; }, F, d, F, st));
+    RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st));
+    RUN(gemm_tn_set(e, S, gr, dHf, F, y.y2, d, [&](int l) { return Gl(l).W1; }, d, F, d, st));
+    RUN(gemm_nt_set(e, S, gr, dHf, F, [&](int l) { return Wl(l).W1; }, d, 1, gA, d, PL0(), d, F, GEMM_ACCUM, st));     // gA = dy2
     // LN2 (cross-attention over an empty memory contributes only its output bias), then LN1
-    RUN(ln_bwd(v.ga, nullptr, y.xh2, y.rs2, w.n2w, v.gb, nullptr, 0, W_(gw.n2w), W_(gw.n2b), W_(gw.bcross), d, R, Rd, 0, st));
-    RUN(ln_bwd(v.gb, nullptr, y.xh1, y.rs1, w.n1w, v.ga, nullptr, 0, W_(gw.n1w), W_(gw.n1b), W_(gw.bo), d, R, Rd, 0, st));  // ga = da
-    RUN(gemm_nt(prec, row_src(v.ga, d, d), w.Wo, d, 1, v.gO, d, nullptr, R, Rd, d, d, 0, st));
-    RUN(gemm_tn(prec, v.ga, d, row_src(y.O, d, d), W_(gw.Wo), d, R, Rd, d, d, st));
-    if (last && !attn_bwd_writes_all(d, dm.heads)) RUN(zero_rows(v.dqkv, 3 * d, Mt, Mtd, 0, st));
-    RUN(attn_bwd(y.qkv, v.seg, y.O, y.lse, v.gO, v.dqkv, v.Dvec, d, dm.heads, B, v.maxseg + 1, last ? 1 : 0, st));
-    RUN(gemm_tn(prec, v.dqkv, 3 * d, row_src(t_in, d, d), W_(gw.Wqkv), d, Mt, Mtd, 3 * d, d, st));
-    RUN(colsum_accum(v.dqkv, 3 * d, W_(gw.bqkv), Mt, Mtd, 3 * d, st));
+    RUN(ln_bwd_grp(gA, nullptr, y.xh2, y.rs2, PL(S, [&](int l) { return Wl(l).n2w; }), gB, noidx(), 0, ML(S, [&](int l) { return Gl(l).n2w; }),
+                   ML(S, [&](int l) { return Gl(l).n2b; }), ML(S, [&](int l) { return Gl(l).bcross; }), d, gr, st));
+    RUN(ln_bwd_grp(gB, nullptr, y.xh1, y.rs1, PL(S, [&](int l) { return Wl(l).n1w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n1w; }),
+                   ML(S, [&](int l) { return Gl(l).n1b; }), ML(S, [&](int l) { return Gl(l).bo; }), d, gr, st));      // gA = da
+    RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).Wo; }, d, 1, gO, d, PL0(), d, d, 0, st));
+    RUN(gemm_tn_set(e, S, gr, gA, d, y.O, d, [&](int l) { return Gl(l).Wo; }, d, d, d, st));
+    if (last && !attn_bwd_writes_all(d, dm.heads))
+      for (int g = 0; g < S.n; ++g)
+        RUN(zero_rows(v0.dqkv + (size_t)S.gt.roff[g] * 3 * d, 3 * d, S.gt.hcnt[g], S.gt.cnt[g], 0, st));
+    RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st));
+    RUN(gemm_tn_set(e, S, S.gt, v0.dqkv, 3 * d, t_in, d, [&](int l) { return Gl(l).Wqkv; }, d, 3 * d, d, st));
+    RUN(colsum_accum_grp(v0.dqkv, 3 * d, ML(S, [&](int l) { return Gl(l).bqkv; }), S.gt, 3 * d, st));
     if (last) {
-      RUN(gemm_nt(prec, row_src(v.dqkv, 3 * d, 3 * d), w.Wqkv, d, 1, v.gt, d, nullptr, Mt, Mtd, d, 3 * d, 0, st));
-      RUN(scatter_add_rows(v.ga, v.tseg, v.gt, d, B, st));
-      dy3 = v.gt;
+      RUN(gemm_nt_set(e, S, S.gt, v0.dqkv, 3 * d, [&](int l) { return Wl(l).Wqkv; }, d, 1, gtk, d, PL0(), d, 3 * d, 0, st));
+      RUN(scatter_add_rows_grp(gA, S.tsegI, gtk, d, S.gb, st));
+      dy3 = gtk;
     } else {
       // ga holds da (the residual branch); add the attention branch, then hand the buffer over as the next layer's dy3
-      RUN(gemm_nt(prec, row_src(v.dqkv, 3 * d, 3 * d), w.Wqkv, d, 1, v.ga, d, nullptr, Mt, Mtd, d, 3 * d, GEMM_ACCUM, st));
-      float* tmp = v.ga; v.ga = v.gt; v.gt = tmp;
-      dy3 = v.gt;
+      RUN(gemm_nt_set(e, S, S.gt, v0.dqkv, 3 * d, [&](int l) { return Wl(l).Wqkv; }, d, 1, ga, d, PL0(), d, 3 * d, GEMM_ACCUM, st));
+      float* tmp = ga; ga = gtk; gtk = tmp;
+      dy3 = gtk;
     }
   }
-  v.dtok = dy3;
-  RUN(special_grad(v.dtok, v.seg, W_(g.special), d, B, st));
+  e->dtok_base = dy3;
+  RUN(special_grad_grp(dy3, S.segI, ML(S, [&](int l) { return G[l].special; }), d, B, S.n, st));
   return 0;
 }
 
@@ -561,7 +696,7 @@ int lstm_backward(paths_engine* e, int l, cudaStream_t st) {
   const int ldg = 3 * C + D;
   const bool last_level = l == dm.L - 1;
   ProfScope ps_blk(e, PATHS_PROF_LSTM_BWD, st);
-  const float* dtok = v.dtok;
+  const float* dtok = e->dtok_base + (size_t)v.tok_off * d;
   const bool has_children = !last_level;
   const bool has_parent = l > 0;
   if (!dm.lstm) {
@@ -622,7 +757,7 @@ int lstm_backward(paths_engine* e, int l, cudaStream_t st) {
 
 int level_backward(paths_engine* e, int l, int use_dlogits, cudaStream_t st) {
   if (int r = head_backward(e, l, use_dlogits, st)) return r;
-  if (int r = decoder_backward(e, l, st)) return r;
+  if (int r = decoder_backward(e, make_set(e, &l, 1), l, st)) return r;
   return lstm_backward(e, l, st);
 }
 
@@ -710,6 +845,41 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
   carve(e, static_cast<char*>(workspace));
   e->ws_base = static_cast<char*>(workspace); e->ws_bytes = need;
   e->site_on = getenv("PATHS_B200_PROF_DUMP") != nullptr;
+  {
+    // "012,34": comma-separated sets of level digits (PATHS_B200_DEC_SETS_FWD / _BWD); a forward set starts once the tokens of
+    // its deepest level exist, backward sets are launched last-to-first.
+    auto parse = [&](const char* spec, int* n_sets, int* set_n, int (*set_lv)[PATHS_MAX_LEVELS]) {
+      const int L = e->dm.L;
+      bool seen[PATHS_MAX_LEVELS] = {false};
+      int ns = 0;
+      bool ok = spec != nullptr && *spec != 0;
+      if (ok) {
+        set_n[0] = 0;
+        for (const char* c = spec; *c && ok; ++c) {
+          if (*c == ',') { if (set_n[ns] == 0) ok = false; else if (++ns >= PATHS_MAX_LEVELS) ok = false; else set_n[ns] = 0; continue; }
+          const int l = *c - '0';
+          if (l < 0 || l >= L || seen[l]) { ok = false; break; }
+          seen[l] = true;
+          set_lv[ns][set_n[ns]++] = l;
+        }
+        if (ok && set_n[ns] == 0) ok = false;
+        for (int l = 0; l < L && ok; ++l) ok = seen[l];
+        if (ok) ++ns;
+      }
+      if (!ok) {
+        // default: levels 0..L-2 as one grouped pass (it overlaps the deepest level's LSTM step), the deepest level on its own
+        // (forward: its tokens come last; backward: its token gradient is what the LSTM chain waits for first)
+        if (L == 1) { ns = 1; set_n[0] = 1; set_lv[0][0] = 0; }
+        else {
+          ns = 2; set_n[0] = L - 1; set_n[1] = 1; set_lv[1][0] = L - 1;
+          for (int l = 0; l < L - 1; ++l) set_lv[0][l] = l;
+        }
+      }
+      *n_sets = ns;
+    };
+    parse(getenv("PATHS_B200_DEC_SETS_FWD"), &e->n_fsets, e->fset_n, e->fset_lv);
+    parse(getenv("PATHS_B200_DEC_SETS_BWD"), &e->n_bsets, e->bset_n, e->bset_lv);
+  }
   e->have_streams = true;
   // priorities: the chain every level waits on runs highest; among the decoders the deeper level goes first (its token
   // gradient is the first one the backward chain needs)
@@ -798,11 +968,25 @@ int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grad
     const int D = dm.D, Cm = dm.C, d = dm.d, I = dm.I, F = dm.F;
     char* cur = e->packed_arena;
     auto reg = [&](const float* src, int R, int Cc, int ld) -> int {
-      if (int r = register_packed(src, R, Cc, ld, cur)) return r;
+      if (int r = register_packed(src, R, Cc, ld, cur, 1)) return r;
       cur += packed_bytes(R, Cc);
       e->packed_srcs.push_back(src);
       return 0;
     };
+    // the same weight of every level, packed back to back (member l at 2R plane rows from member l-1): the head's tensor map
+    // spans the stack, so a grouped contraction reaches level l's weight by a row offset
+    auto reg_stack = [&](const float* const* srcs, int n, int R, int Cc, int ld) -> int {
+      const size_t member = (size_t)2 * R * ((Cc + 7) / 8 * 8) * sizeof(__nv_bfloat16);
+      char* base_al = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(cur) + 255) & ~uintptr_t(255));
+      for (int l = 0; l < n; ++l) {
+        PATHS_REQUIRE(srcs[l], "bind_params: decoder weight of level %d missing", l);
+        if (int r = register_packed(srcs[l], R, Cc, ld, base_al + (size_t)l * member, l == 0 ? n : 1)) return r;
+        e->packed_srcs.push_back(srcs[l]);
+      }
+      cur = base_al + (size_t)n * member;
+      return 0;
+    };
+    e->stacked = d % 8 == 0 && F % 8 == 0;                 // member stride stays 256-byte aligned, every extent TMA-legal
     int rc = 0;
     if (dm.lstm) {
       PATHS_REQUIRE(e->P.Wg && e->P.Wmo, "bind_params: LSTM weights missing");
@@ -816,13 +1000,24 @@ int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grad
         rc = rc ? rc : reg(e->P.level[l].Wh0, Cm, D, D);
         rc = rc ? rc : reg(e->P.level[l].Wh2, D, Cm, Cm);
       }
-      for (int j = 0; j < dm.layers && !rc; ++j) {
+      for (int j = 0; j < dm.layers && !rc && !e->stacked; ++j) {
         const LayerP& y = e->P.level[l].layer[j];
         rc = rc ? rc : reg(y.Wqkv, 3 * d, d, d);
         rc = rc ? rc : reg(y.Wo, d, d, d);
         rc = rc ? rc : reg(y.W1, F, d, d);
         rc = rc ? rc : reg(y.W2, d, F, F);
       }
+    }
+    for (int j = 0; j < dm.layers && !rc && e->stacked; ++j) {
+      const float* w[4][PATHS_MAX_LEVELS];
+      for (int l = 0; l < dm.L; ++l) {
+        const LayerP& y = e->P.level[l].layer[j];
+        w[0][l] = y.Wqkv; w[1][l] = y.Wo; w[2][l] = y.W1; w[3][l] = y.W2;
+      }
+      rc = rc ? rc : reg_stack(w[0], dm.L, 3 * d, d, d);
+      rc = rc ? rc : reg_stack(w[1], dm.L, d, d, d);
+      rc = rc ? rc : reg_stack(w[2], dm.L, F, d, d);
+      rc = rc ? rc : reg_stack(w[3], dm.L, d, F, F);
     }
     if (rc) return rc;
     PATHS_REQUIRE((size_t)(cur - e->packed_arena) <= e->packed_arena_bytes, "packed-weight arena overrun");
@@ -881,8 +1076,22 @@ static bool use_side_streams(const paths_engine* e) {
   return !off && e->have_streams && planes_mode(e->dm) && e->dm.d % 8 == 0 && e->dm.F % 8 == 0;
 }
 
+static int forward_impl(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, const int32_t* ybin,
+                        const int32_t* censored, float scale, int with_loss, void* stream);
+
 int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int32_t* ybin, const int32_t* censored, float scale,
                          int with_loss, void* stream) {
+  return forward_impl(e, slide_ids, nullptr, 0, ybin, censored, scale, with_loss, stream);
+}
+
+int paths_engine_forward_padded(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, const int32_t* ybin,
+                                const int32_t* censored, float scale, int with_loss, void* stream) {
+  PATHS_REQUIRE(fts_padded && N >= 1, "forward_padded: null feature batch");
+  return forward_impl(e, slide_ids, fts_padded, N, ybin, censored, scale, with_loss, stream);
+}
+
+static int forward_impl(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, const int32_t* ybin,
+                        const int32_t* censored, float scale, int with_loss, void* stream) {
   PATHS_REQUIRE(e && e->have_params, "forward: engine has no parameters bound");
   cudaStream_t caller = static_cast<cudaStream_t>(stream);
   cudaStream_t st = caller;
@@ -893,7 +1102,7 @@ int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int3
     PATHS_CK(cudaStreamWaitEvent(e->mainp, e->ev_in, 0));
     st = e->mainp;
   }
-  if (int r = do_begin(e, slide_ids, nullptr, 0, st)) return r;
+  if (int r = do_begin(e, slide_ids, fts_padded, N, st)) return r;
   if (!conc) {
     for (int l = 0; l < L; ++l) {
       if (int r = level_forward(e, l, st)) return r;
@@ -904,16 +1113,20 @@ int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int3
     for (int l = 0; l < L; ++l) {
       if (int r = lstm_forward(e, l, st)) return r;
       PATHS_CK(cudaEventRecord(e->ev_tok[l], st));
-      PATHS_CK(cudaStreamWaitEvent(e->side[l], e->ev_tok[l], 0));
-      if (int r = decoder_forward(e, l, e->side[l])) return r;
-      PATHS_CK(cudaEventRecord(e->ev_z[l], e->side[l]));
+      for (int si = 0; si < e->n_fsets; ++si) {            // a set starts when the tokens of its deepest level exist
+        int deepest = 0;
+        for (int k = 0; k < e->fset_n[si]; ++k) deepest = e->fset_lv[si][k] > deepest ? e->fset_lv[si][k] : deepest;
+        if (deepest != l) continue;
+        PATHS_CK(cudaStreamWaitEvent(e->side[si], e->ev_tok[l], 0));
+        if (int r = decoder_forward(e, make_set(e, e->fset_lv[si], e->fset_n[si]), e->side[si])) return r;
+        PATHS_CK(cudaEventRecord(e->ev_z[si], e->side[si]));
+      }
       if (l < L - 1)
         if (int r = do_select(e, l, st)) return r;
     }
-    for (int l = 0; l < L; ++l) {
-      PATHS_CK(cudaStreamWaitEvent(st, e->ev_z[l], 0));
+    for (int si = 0; si < e->n_fsets; ++si) PATHS_CK(cudaStreamWaitEvent(st, e->ev_z[si], 0));
+    for (int l = 0; l < L; ++l)
       if (int r = head_forward(e, l, st)) return r;
-    }
   }
   if (with_loss)
     if (int r = do_loss(e, ybin, censored, scale, st)) return r;
@@ -938,15 +1151,18 @@ int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream) {
   PATHS_CK(cudaStreamWaitEvent(e->mainp, e->ev_in, 0));
   cudaStream_t st = e->mainp;
   if (zero_grads) PATHS_CK(cudaMemsetAsync(e->grads_base, 0, e->grads_floats * sizeof(float), st));
-  for (int l = L - 1; l >= 0; --l) {
+  for (int l = L - 1; l >= 0; --l)
     if (int r = head_backward(e, l, l == L - 1, st)) return r;
-    PATHS_CK(cudaEventRecord(e->ev_head[l], st));
-    PATHS_CK(cudaStreamWaitEvent(e->side[l], e->ev_head[l], 0));
-    if (int r = decoder_backward(e, l, e->side[l])) return r;
-    PATHS_CK(cudaEventRecord(e->ev_dtok[l], e->side[l]));
+  PATHS_CK(cudaEventRecord(e->ev_head[0], st));
+  int set_of[PATHS_MAX_LEVELS] = {0};
+  for (int si = e->n_bsets - 1; si >= 0; --si) {           // sets holding the deeper levels first: the LSTM chain needs them first
+    PATHS_CK(cudaStreamWaitEvent(e->side[si], e->ev_head[0], 0));
+    if (int r = decoder_backward(e, make_set(e, e->bset_lv[si], e->bset_n[si]), si, e->side[si])) return r;
+    PATHS_CK(cudaEventRecord(e->ev_dtok[si], e->side[si]));
+    for (int k = 0; k < e->bset_n[si]; ++k) set_of[e->bset_lv[si][k]] = si;
   }
   for (int l = L - 1; l >= 0; --l) {
-    PATHS_CK(cudaStreamWaitEvent(st, e->ev_dtok[l], 0));
+    PATHS_CK(cudaStreamWaitEvent(st, e->ev_dtok[set_of[l]], 0));
     if (int r = lstm_backward(e, l, st)) return r;
   }
   PATHS_CK(cudaEventRecord(e->ev_out, st));
@@ -1040,7 +1256,7 @@ int paths_gemm_nt(int precision, const float* A, int lda, const float* B, int ld
     PATHS_CK(cudaMalloc(&jobs, 64));
     PATHS_CK(cudaMalloc(&scr, tc_scratch_bytes(M, K)));
     set_tc_scratch(scr, tc_scratch_bytes(M, K), nullptr, 0);
-    if (int r = register_packed(B, R, Cc, ldb, tmp)) return r;
+    if (int r = register_packed(B, R, Cc, ldb, tmp, 1)) return r;
     int nj = 0;
     if (int r = build_pack_jobs(&B, 1, jobs, &nj, st)) return r;
     if (int r = run_pack_jobs(jobs, nj, st)) return r;
@@ -1061,9 +1277,9 @@ int paths_gemm_tn(int precision, const float* P, int ldp, const float* Q, int ld
   if (precision != PREC_FP32_SIMT) {
     PATHS_CK(cudaMalloc(&sa, tc_scratch_bytes(M, NI)));
     PATHS_CK(cudaMalloc(&sb, tc_scratch_bytes(M, NJ)));
-    PATHS_CK(cudaMalloc(&sw, tn_workspace_bytes(NI, NJ, M)));
+    PATHS_CK(cudaMalloc(&sw, tn_workspace_bytes(NI, NJ, M, 1)));
     set_tc_scratch(sa, tc_scratch_bytes(M, NI), sb, tc_scratch_bytes(M, NJ));
-    set_tn_workspace(sw, tn_workspace_bytes(NI, NJ, M));
+    set_tn_workspace(sw, tn_workspace_bytes(NI, NJ, M, 1));
   }
   int rc = gemm_tn(precision, P, ldp, row_src(Q, ldq, NJ), C, ldc, M, nullptr, NI, NJ, st);
   if (sa) {

@@ -219,9 +219,10 @@ __global__ void __launch_bounds__(NT) gemm_tn_kernel(const float* __restrict__ P
 
 // out[n] += sum_m X[m, n].  Vector path (N % 4 == 0, ld % 4 == 0, N <= 1024): a thread keeps one float4 column group and
 // walks rows (independent loads, unrolled), one shared-memory combine and one atomic per column per block.
-__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, int ld, float* __restrict__ out,
-                                                     int M_host, const int* __restrict__ M_dev, int N) {
-  const int M = M_dev ? *M_dev : M_host;
+__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, int ld, MutL outl, Grp grp, int N) {
+  const int M = grp_count(grp, blockIdx.y);                // blockIdx.y = row group of the concatenated buffer
+  X += (size_t)pick(grp.roff, blockIdx.y) * ld;
+  float* out = pick(outl.p, blockIdx.y);
   const int ngrp = N >> 2;
   const int rpb = 256 / ngrp > 0 ? 256 / ngrp : 1;
   const int g = threadIdx.x % ngrp, rsub = threadIdx.x / ngrp;
@@ -294,14 +295,25 @@ int gemm_tn_simt(const float* P, int ldp, const RowSrc& Q, float* C, int ldc, in
   return 0;
 }
 
+static bool colsum_vec_ok(const float* X, int ld, int N) {
+  return N % 4 == 0 && ld % 4 == 0 && N <= 1024 && N >= 8 && (reinterpret_cast<uintptr_t>(X) & 15) == 0;
+}
+int colsum_accum_grp(const float* X, int ld, const MutL& out, const Grp& grp, int N, cudaStream_t st) {
+  const int cap = grp_max_rows(grp);
+  if (cap <= 0 || N <= 0) return 0;
+  PATHS_REQUIRE(colsum_vec_ok(X, ld, N), "colsum_accum_grp: width %d / leading dim %d unsupported", N, ld);
+  const int rpb = 256 / (N / 4) > 0 ? 256 / (N / 4) : 1;
+  int g = (cap + 8 * rpb - 1) / (8 * rpb);                // few blocks: the final same-address atomics serialise in L2
+  if (g > 96) g = 96;
+  if (g < 1) g = 1;
+  colsum_kernel<<<dim3(g, grp.n), 256, 0, st>>>(X, ld, out, grp, N);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
 int colsum_accum(const float* X, int ld, float* out, int M_host, const int* M_dev, int N, cudaStream_t st) {
   if (M_host <= 0 || N <= 0) return 0;
-  if (N % 4 == 0 && ld % 4 == 0 && N <= 1024 && N >= 8 && (reinterpret_cast<uintptr_t>(X) & 15) == 0) {
-    const int rpb = 256 / (N / 4) > 0 ? 256 / (N / 4) : 1;
-    int g = (M_host + 8 * rpb - 1) / (8 * rpb);           // few blocks: the final same-address atomics serialise in L2
-    if (g > 96) g = 96;
-    if (g < 1) g = 1;
-    colsum_kernel<<<g, 256, 0, st>>>(X, ld, out, M_host, M_dev, N);
+  if (colsum_vec_ok(X, ld, N)) {
+    return colsum_accum_grp(X, ld, mutl1(out), grp_single(M_host, M_dev), N, st);
   } else {
     int splits = (M_host + 255) / 256;
     if (splits > 64) splits = 64;

@@ -190,6 +190,8 @@ struct Operand { int row0, col0, plane_rows; };
 // owns k-blocks [0, k1) of tile t; the other G - tiles CTAs split the tails [k1, nkb) of all tiles (tile-major, q k-blocks
 // each; tl = nkb - k1, total = tiles * tl).  k1 < 0: plain tile-major stream-K over all G CTAs.
 struct SkPlan { int k1, tl; long long q, total; };
+// One work unit of the contraction kernel: output tile origin, k-block range, row group, A-row limit, reduction row window.
+struct Unit { int i0, j0, kb_begin, kb_end, g; };
 __host__ __device__ __forceinline__ SkPlan sk_plan(int tiles, int nkb, int G) {
   SkPlan p;
   if (G > tiles) {
@@ -258,8 +260,8 @@ __device__ __forceinline__ void cvt_store(const CvtRegs& g, uint8_t* dst, int pl
 template <int BN, int NP, bool A_MN, bool B_MN, bool SK, bool A_CVT, bool B_CVT>
 __global__ void __launch_bounds__((A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA, 1)
 gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Operand oa, Operand ob,
-                const RowSrc sa, const RowSrc sb, float* __restrict__ C, int ldc, const float* __restrict__ bias, int OI_host, const int* __restrict__ OI_dev, int OJ,
-                int R_host, const int* __restrict__ R_dev, int flags, int segmax) {
+                const RowSrc sa, const RowSrc sb, float* __restrict__ C, int ldc, const GemmGrp gg, int b_grp_rows, int OI_host, int OJ,
+                int R_host, int flags, int segmax) {
   // Persistent: one CTA per SM walks work units u = blockIdx.x, += gridDim.x; unit = (row tile, column tile, reduction split)
   // with column tiles fastest so CTAs that run together share A rows in L2.  Two TMEM accumulators: the epilogue of unit n
   // drains one while the MMA warp fills the other.
@@ -267,15 +269,24 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   constexpr int NS = cfg::NS;
   constexpr uint32_t TMA_BYTES = (A_CVT ? 0 : NP * cfg::A_PLANE) + (B_CVT ? 0 : NP * cfg::B_PLANE);
   constexpr uint32_t FULL_COUNT = (TMA_BYTES ? 1 : 0) + ((A_CVT || B_CVT) ? LOADER_WARPS : 0);
-  const int OI = OI_dev ? *OI_dev : OI_host;
-  const int R = R_dev ? *R_dev : R_host;
-  const int tiles_i = (OI + BM - 1) / BM, tiles_j = (OJ + BN - 1) / BN;
-  const int nkb_total = (R + BK - 1) / BK;
-  const int units = tiles_i * tiles_j;
-  const long long sk_total = (long long)units * nkb_total;
-  const long long sk_q = (sk_total + gridDim.x - 1) / gridDim.x;
-  const long long sk_lo = (long long)blockIdx.x * sk_q;
-  const long long sk_hi = sk_lo + sk_q < sk_total ? sk_lo + sk_q : sk_total;
+  // Row groups (common.cuh): the NT form walks the live 128-row tiles of every group of the concatenated activation buffer
+  // (weights / bias of the tile's group); the TN form (SK) produces one [OI_host x OJ] output per group, reducing over the
+  // group's rows -- every output tile gets the k-block count of the longest group, shorter groups read zeros past their end.
+  __shared__ int g_cnt[kMaxGroups], g_cum[kMaxGroups + 1], g_max, g_roff[kMaxGroups], g_wlev[kMaxGroups];
+  __shared__ const float* g_bias[kMaxGroups];
+  if (threadIdx.x == 0) {
+    int cum = 0, mx = 0;
+    g_cum[0] = 0;
+#pragma unroll
+    for (int g = 0; g < kMaxGroups; ++g) {                 // compile-time indices into the parameter struct (see pick())
+      const int c = g < gg.rows.n ? (gg.rows.cnt[g] ? *gg.rows.cnt[g] : gg.rows.hcnt[g]) : 0;
+      g_cnt[g] = c; g_roff[g] = gg.rows.roff[g]; g_wlev[g] = gg.wlev[g]; g_bias[g] = gg.bias[g];
+      cum += (c + BM - 1) / BM;
+      g_cum[g + 1] = cum;
+      mx = c > mx ? c : mx;
+    }
+    g_max = mx;
+  }
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -293,10 +304,18 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  const int tiles_i = SK ? (OI_host + BM - 1) / BM : g_cum[kMaxGroups], tiles_j = (OJ + BN - 1) / BN;
+  const int nkb_total = ((SK ? g_max : R_host) + BK - 1) / BK;
+  const int units = SK ? gg.rows.n * tiles_i * tiles_j : tiles_i * tiles_j;
+  const long long sk_total = (long long)units * nkb_total;
+  const long long sk_q = (sk_total + gridDim.x - 1) / gridDim.x;
+  const long long sk_lo = (long long)blockIdx.x * sk_q;
+  const long long sk_hi = sk_lo + sk_q < sk_total ? sk_lo + sk_q : sk_total;
 
   // n-th work unit of this CTA: (output tile origin, k-block range); false when the CTA has no more work
-  auto get_unit = [&](int n, int& i0, int& j0, int& kb_begin, int& kb_end) -> bool {
+  auto get_unit = [&](int n, Unit& u) -> bool {
     int t;
+    int& kb_begin = u.kb_begin; int& kb_end = u.kb_end;
     if (SK) {
       if (nkb_total == 0) return false;
       const SkPlan pl = sk_plan(units, nkb_total, (int)gridDim.x);
@@ -329,9 +348,23 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (t >= units || nkb_total == 0) return false;
       kb_begin = 0; kb_end = nkb_total;
     }
-    j0 = (t % tiles_j) * BN; i0 = (t / tiles_j) * BM;
+    if (SK) {
+      const int tpg = tiles_i * tiles_j, tt = t % tpg;
+      u.g = t / tpg;
+      u.j0 = (tt % tiles_j) * BN; u.i0 = (tt / tiles_j) * BM;
+    } else {
+      const int r = t / tiles_j;
+      int g = 0;
+      for (int k = 1; k < gg.rows.n; ++k) g = r >= g_cum[k] ? k : g;
+      u.g = g;
+      u.j0 = (t % tiles_j) * BN; u.i0 = g_roff[g] + (r - g_cum[g]) * BM;
+    }
     return true;
   };
+  // A-row limit of a unit's group / reduction row window (NT: the K extent; TN: the group's rows)
+  auto a_olim = [&](const Unit& u) -> int { return SK ? OI_host : g_roff[u.g] + g_cnt[u.g]; };
+  auto r_base = [&](const Unit& u) -> int { return SK ? g_roff[u.g] : 0; };
+  auto r_lim = [&](const Unit& u) -> int { return SK ? g_roff[u.g] + g_cnt[u.g] : R_host; };
 
   if (warp >= LOADER_WARP0) {
     if (A_CVT || B_CVT) {
@@ -341,20 +374,20 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       constexpr int NA = A_CVT ? (BM * 8 / NLT) / LB : 0, NB = B_CVT ? (BN * 8 / NLT) / LB : 0, NSUB = NA + NB;
       static_assert((BM * 8 / NLT) % LB == 0 && (BN * 8 / NLT) % LB == 0, "loader batch size");
       const int ltid = threadIdx.x - LOADER_WARP0 * 32;
-      struct Pos { int n, i0, j0, kb, kb_end, sub; uint32_t it; bool ok; };
+      struct Pos { int n, kb, sub; Unit u; uint32_t it; bool ok; };
       Pos cur; cur.n = 0; cur.sub = 0; cur.it = 0;
-      { int kb0; cur.ok = get_unit(0, cur.i0, cur.j0, kb0, cur.kb_end); cur.kb = kb0; }
+      cur.ok = get_unit(0, cur.u); cur.kb = cur.u.kb_begin;
       auto advance = [&](Pos p) -> Pos {
         if (++p.sub < NSUB) return p;
         p.sub = 0; ++p.it;
-        if (++p.kb < p.kb_end) return p;
+        if (++p.kb < p.u.kb_end) return p;
         ++p.n;
-        int kb0; p.ok = get_unit(p.n, p.i0, p.j0, kb0, p.kb_end); p.kb = kb0;
+        p.ok = get_unit(p.n, p.u); p.kb = p.u.kb_begin;
         return p;
       };
       auto issue = [&](const Pos& p, CvtRegs& g) {
-        if (A_CVT && p.sub < NA) cvt_issue<BM, A_MN>(sa, p.sub, p.i0, OI, p.kb * BK, R, ltid, g);
-        else if (B_CVT) cvt_issue<BN, B_MN>(sb, p.sub - NA, p.j0, OJ, p.kb * BK, R, ltid, g);
+        if (A_CVT && p.sub < NA) cvt_issue<BM, A_MN>(sa, p.sub, p.u.i0, a_olim(p.u), r_base(p.u) + p.kb * BK, r_lim(p.u), ltid, g);
+        else if (B_CVT) cvt_issue<BN, B_MN>(sb, p.sub - NA, p.u.j0, OJ, r_base(p.u) + p.kb * BK, r_lim(p.u), ltid, g);
       };
       auto retire = [&](const Pos& p, const CvtRegs& g) {
         const int s = p.it % NS;
@@ -383,9 +416,12 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp == TMA_WARP) {
     if (lane == 0 && TMA_BYTES != 0) {
       uint32_t it = 0;
-      int i0, j0, kb_begin, kb_end;
-      for (int n = 0; get_unit(n, i0, j0, kb_begin, kb_end); ++n) {
-        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+      Unit u;
+      for (int n = 0; get_unit(n, u); ++n) {
+        const int i0 = u.i0, j0 = u.j0;
+        const int b_row0 = ob.row0 + (SK ? 0 : g_wlev[u.g] * b_grp_rows);   // the group's member of a stacked packed weight
+        const int rb = r_base(u);
+        for (int kb = u.kb_begin; kb < u.kb_end; ++kb, ++it) {
           const int s = it % NS;
           const uint32_t ph = (it / NS) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
@@ -398,13 +434,13 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             for (int bx = 0; bx < (A_CVT ? 0 : BM / 64); ++bx) {
               uint8_t* dst = a_base + pl * cfg::A_PLANE + bx * 8192;
               if (!A_MN) tma_load_2d(dst, &tmA, oa.col0 + kb * BK, pl * oa.plane_rows + oa.row0 + i0 + bx * 64, &full_bar[s]);
-              else       tma_load_2d(dst, &tmA, oa.col0 + i0 + bx * 64, pl * oa.plane_rows + oa.row0 + kb * BK, &full_bar[s]);
+              else       tma_load_2d(dst, &tmA, oa.col0 + i0 + bx * 64, pl * oa.plane_rows + oa.row0 + rb + kb * BK, &full_bar[s]);
             }
 #pragma unroll
             for (int bx = 0; bx < (B_CVT ? 0 : BN / 64); ++bx) {
               uint8_t* dst = b_base + pl * cfg::B_PLANE + bx * 8192;
-              if (!B_MN) tma_load_2d(dst, &tmB, ob.col0 + kb * BK, pl * ob.plane_rows + ob.row0 + j0 + bx * 64, &full_bar[s]);
-              else       tma_load_2d(dst, &tmB, ob.col0 + j0 + bx * 64, pl * ob.plane_rows + ob.row0 + kb * BK, &full_bar[s]);
+              if (!B_MN) tma_load_2d(dst, &tmB, ob.col0 + kb * BK, pl * ob.plane_rows + b_row0 + j0 + bx * 64, &full_bar[s]);
+              else       tma_load_2d(dst, &tmB, ob.col0 + j0 + bx * 64, pl * ob.plane_rows + b_row0 + rb + kb * BK, &full_bar[s]);
             }
           }
         }
@@ -414,8 +450,9 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       uint32_t it = 0, tcount = 0;
-      int i0, j0, kb_begin, kb_end;
-      for (int n = 0; get_unit(n, i0, j0, kb_begin, kb_end); ++n) {
+      Unit u;
+      for (int n = 0; get_unit(n, u); ++n) {
+        const int kb_begin = u.kb_begin, kb_end = u.kb_end;
         const uint32_t buf = tcount & 1, aph = (tcount >> 1) & 1;
         mbar_wait(&acc_empty[buf], aph ^ 1);
         tc_fence_after();
@@ -460,8 +497,10 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int q = warp & 3, half = warp >> 2;
     const int orow = lane >> 3, oq = lane & 7;               // output mapping: row within a group of 4, 16-byte slot
     uint32_t tcount = 0;
-    int i0, j0, kb_begin, kb_end;
-    for (int n = 0; get_unit(n, i0, j0, kb_begin, kb_end); ++n) {
+    Unit u;
+    for (int n = 0; get_unit(n, u); ++n) {
+      const int i0 = u.i0, j0 = u.j0;
+      const float* bias = SK ? nullptr : g_bias[u.g];
       const uint32_t buf = tcount & 1, aph = (tcount >> 1) & 1;
       mbar_wait(&acc_full[buf], aph);
       tc_fence_after();
@@ -469,7 +508,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (SK) {                                              // partial tile -> workspace slot, row-major [BM][BN]
         Cb = C + ((size_t)blockIdx.x * segmax + n) * (BM * BN); ldo = BN; oi_lim = BM; oj_lim = BN; ci0 = 0; cj0 = 0;
       } else {
-        Cb = C; ldo = ldc; oi_lim = OI; oj_lim = OJ; ci0 = i0; cj0 = j0;
+        Cb = C; ldo = ldc; oi_lim = a_olim(u); oj_lim = OJ; ci0 = i0; cj0 = j0;
       }
       const bool vec = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
 #pragma unroll 1
@@ -539,7 +578,8 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const PackJob* __rest
 
 struct Packed {
   const float* src; int R, Cc, ld, ldp;
-  __nv_bfloat16* dst;
+  int nstack;                          // > 1: head of a stack of same-shaped matrices packed back to back (2R rows apart); the
+  __nv_bfloat16* dst;                  //      map then spans the whole stack so a grouped contraction can address member g
   CUtensorMap map;
 };
 
@@ -563,7 +603,7 @@ int get_encode() {
 
 int make_map(Packed& p) {
   if (int r = get_encode()) return r;
-  cuuint64_t gdim[2] = {(cuuint64_t)p.ldp, (cuuint64_t)(2 * p.R)};
+  cuuint64_t gdim[2] = {(cuuint64_t)p.ldp, (cuuint64_t)(2 * p.R) * (cuuint64_t)(p.nstack > 1 ? p.nstack : 1)};
   cuuint64_t gstr[1] = {(cuuint64_t)p.ldp * 2};
   cuuint32_t box[2] = {64, 64};
   cuuint32_t estr[2] = {1, 1};
@@ -637,16 +677,18 @@ int split_to_scratch(int which, const RowSrc& A, int M_host, const int* M_dev, i
 
 template <int BN, int NP, bool A_MN, bool B_MN, bool SK, bool A_CVT, bool B_CVT>
 int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand ob, const RowSrc& sa, const RowSrc& sb, float* C, int ldc,
-               const float* bias, int OI_host, const int* OI_dev, int OJ, int R_host, const int* R_dev, int flags, int grid_sk, int segmax,
-               cudaStream_t st) {
+               const GemmGrp& gg, int b_grp_rows, int OI_host, int OJ, int R_host, int flags, int grid_sk, int segmax, cudaStream_t st) {
   auto kern = gemm_tma_kernel<BN, NP, A_MN, B_MN, SK, A_CVT, B_CVT>;
   static bool configured = false;
   if (!configured) { if (int r = set_smem(kern, Cfg<BN, NP>::SMEM)) return r; configured = true; }
   static const CUtensorMap dummy = {};                       // stands in for the map of an operand converted in-kernel
-  long units = (long)((OJ + BN - 1) / BN) * ((OI_host + BM - 1) / BM);
+  long row_tiles = 0;                                         // by capacity: the live tile count is only known on the device
+  for (int g = 0; g < gg.rows.n; ++g) row_tiles += (gg.rows.hcnt[g] + BM - 1) / BM;
+  long units = (long)((OJ + BN - 1) / BN) * row_tiles;
+  if (units < 1) units = 1;
   const int grid = SK ? grid_sk : (units < kNumSMs ? (int)units : kNumSMs);
   kern<<<grid, (A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA, Cfg<BN, NP>::SMEM, st>>>(
-      A_CVT ? dummy : *ma, B_CVT ? dummy : *mb, oa, ob, sa, sb, C, ldc, bias, OI_host, OI_dev, OJ, R_host, R_dev, flags, segmax);
+      A_CVT ? dummy : *ma, B_CVT ? dummy : *mb, oa, ob, sa, sb, C, ldc, gg, b_grp_rows, OI_host, OJ, R_host, flags, segmax);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -654,15 +696,23 @@ int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand
 // C[tile] += sum over the stream-K segments of the tile, in a fixed order (deterministic).  A block owns 256 / PG consecutive
 // float4 outputs of one tile; PG thread groups each sum every PG-th segment and are combined through shared memory.
 template <int BN, int PG>
-__global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict__ ws, float* __restrict__ C, int ldc, int NI, int NJ,
-                                                        int R_host, const int* __restrict__ R_dev, int G, int segmax) {
+__global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict__ ws, const GemmGrp gg, int ldc, int NI, int NJ, int G,
+                                                        int segmax) {
   constexpr int OUT = 256 / PG;
-  const int R = R_dev ? *R_dev : R_host;
+  int R = 0;
+#pragma unroll
+  for (int g = 0; g < kMaxGroups; ++g) {
+    const int c = g < gg.rows.n ? (gg.rows.cnt[g] ? *gg.rows.cnt[g] : gg.rows.hcnt[g]) : 0;
+    R = c > R ? c : R;
+  }
   const int nkb = (R + BK - 1) / BK;
   if (nkb == 0) return;
   const int tiles_j = (NJ + BN - 1) / BN;
   const int t = blockIdx.x;
-  const int units = ((NI + BM - 1) / BM) * tiles_j;
+  const int tpg = ((NI + BM - 1) / BM) * tiles_j;            // output tiles per group
+  const int units = gg.rows.n * tpg;
+  float* __restrict__ C = pick(gg.cout, t / tpg);
+  const int tt = t % tpg;
   const SkPlan pl = sk_plan(units, nkb, G);
   const int o = threadIdx.x % OUT, g = threadIdx.x / OUT;
   const int elem = blockIdx.y * OUT + o;                 // float4 index inside the tile, row-major
@@ -691,7 +741,7 @@ __global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict
     for (int k = 1; k < PG; ++k) { const float4 v = red[k][o]; acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
   }
   const int row = elem / (BN / 4), c4 = elem % (BN / 4);
-  const int i = (t / tiles_j) * BM + row, j = (t % tiles_j) * BN + c4 * 4;
+  const int i = (tt / tiles_j) * BM + row, j = (tt % tiles_j) * BN + c4 * 4;
   if (i >= NI || j >= NJ) return;
   float* cp = C + (size_t)i * ldc + j;
   const bool vec = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
@@ -712,12 +762,12 @@ struct TnWs { void* p; size_t bytes; } g_tn_ws = {nullptr, 0};
 // ---- registry API (engine.cu registers every weight matrix it contracts against) -----------------------------------
 size_t packed_bytes(int R, int Cc) { return (size_t)2 * R * ((Cc + 7) / 8 * 8) * sizeof(__nv_bfloat16) + 256; }
 
-int register_packed(const float* src, int R, int Cc, int ld, void* dst) {
+int register_packed(const float* src, int R, int Cc, int ld, void* dst, int nstack) {
   std::lock_guard<std::mutex> lk(g_mu);
   for (auto it = g_packed.begin(); it != g_packed.end();)
     it = (it->src == src) ? g_packed.erase(it) : it + 1;
   Packed p;
-  p.src = src; p.R = R; p.Cc = Cc; p.ld = ld; p.ldp = (Cc + 7) / 8 * 8;
+  p.src = src; p.R = R; p.Cc = Cc; p.ld = ld; p.ldp = (Cc + 7) / 8 * 8; p.nstack = nstack;
   p.dst = reinterpret_cast<__nv_bfloat16*>((reinterpret_cast<uintptr_t>(dst) + 255) & ~uintptr_t(255));
   if (int r = make_map(p)) return r;
   g_packed.push_back(p);
@@ -785,8 +835,15 @@ int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Plane
 
 // C[M,N] (+)= act(A . B^T + bias); A either as planes (columns [a_col0, a_col0 + K)) or as fp32 rows converted in-kernel
 static int nt_impl(int passes, const Planes* A, int a_col0, const RowSrc* Asrc, const float* B, int ldb, int b_kn, float* C, int ldc,
-                   const float* bias, int M_host, const int* M_dev, int N, int K, int flags, cudaStream_t st) {
+                   const float* bias, int M_host, const int* M_dev, int N, int K, int flags, cudaStream_t st, const GemmGrp* grp = nullptr) {
   if (M_host <= 0 || N <= 0) return 0;
+  GemmGrp gg;
+  if (grp) gg = *grp;
+  else {
+    gg.rows = grp_single(M_host, M_dev);
+    for (int i = 0; i < kMaxGroups; ++i) { gg.wlev[i] = 0; gg.bias[i] = nullptr; gg.cout[i] = nullptr; }
+    gg.bias[0] = bias;
+  }
   const Packed* pk; int r0, c0;
   {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -802,13 +859,18 @@ static int nt_impl(int passes, const Planes* A, int a_col0, const RowSrc* Asrc, 
     oa.plane_rows = A->rows;
   }
   Operand ob; ob.row0 = r0; ob.col0 = c0; ob.plane_rows = pk->R;
+  const int bgr = 2 * pk->R;                                   // rows between the members of a stacked packed weight
+  if (grp)
+    for (int g = 0; g < gg.rows.n; ++g)
+      PATHS_REQUIRE(gg.wlev[g] >= 0 && gg.wlev[g] < (pk->nstack > 1 ? pk->nstack : 1), "gemm_nt_tc: group %d addresses member %d of a %d-stack",
+                    g, gg.wlev[g], pk->nstack);
   const bool big = N > 128;
 #define NT_CASE(BN_, NP_, MN_)                                                                                                         \
   do {                                                                                                                                 \
-    if (A) return launch_tma<BN_, NP_, false, MN_, false, false, false>(ma, &pk->map, oa, ob, none, none, C, ldc, bias, M_host, M_dev, \
-                                                                        N, K, nullptr, flags, 0, 0, st);                             \
-    return launch_tma<BN_, NP_, false, MN_, false, true, false>(nullptr, &pk->map, oa, ob, *Asrc, none, C, ldc, bias, M_host, M_dev, N, \
-                                                                K, nullptr, flags, 0, 0, st);                                        \
+    if (A) return launch_tma<BN_, NP_, false, MN_, false, false, false>(ma, &pk->map, oa, ob, none, none, C, ldc, gg, bgr, M_host,     \
+                                                                        N, K, flags, 0, 0, st);                                      \
+    return launch_tma<BN_, NP_, false, MN_, false, true, false>(nullptr, &pk->map, oa, ob, *Asrc, none, C, ldc, gg, bgr, M_host, N,    \
+                                                                K, flags, 0, 0, st);                                                 \
   } while (0)
   if (passes == 3) {
     if (big) { if (b_kn) NT_CASE(256, 2, true); else NT_CASE(256, 2, false); }
@@ -842,9 +904,9 @@ int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, f
 }
 
 // Stream-K plan of a weight-gradient contraction: CTAs and workspace slots per CTA.
-static void tn_plan(int NI, int NJ, int M_host, int* G, int* segmax) {
+static void tn_plan(int NI, int NJ, int M_host, int ngroups, int* G, int* segmax) {
   const int BN = NJ > 128 ? 256 : 128;
-  const int tiles = ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
+  const int tiles = ngroups * ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
   const long total = (long)tiles * ((M_host + BK - 1) / BK);
   long g = total / 4;                            // at least ~4 k-blocks per CTA
   if (g > kNumSMs) g = kNumSMs;
@@ -856,17 +918,25 @@ static void tn_plan(int NI, int NJ, int M_host, int* G, int* segmax) {
     if (s2 > *segmax) *segmax = s2;
   }
 }
-size_t tn_workspace_bytes(int NI, int NJ, int M_host) {
+size_t tn_workspace_bytes(int NI, int NJ, int M_host, int ngroups) {
   int G, segmax;
-  tn_plan(NI, NJ, M_host, &G, &segmax);
+  tn_plan(NI, NJ, M_host, ngroups, &G, &segmax);
   return (size_t)G * segmax * BM * (NJ > 128 ? 256 : 128) * sizeof(float);
 }
 void set_tn_workspace(void* p, size_t bytes) { g_tn_ws.p = p; g_tn_ws.bytes = bytes; }
 
 // C[NI,NJ] += P^T . Q; operands as planes (column windows p_col0 / q_col0) or as fp32 rows converted in-kernel
 static int tn_impl(int passes, const Planes* P, int p_col0, const Planes* Q, int q_col0, const RowSrc* Ps, const RowSrc* Qs, float* C, int ldc,
-                   int M_host, const int* M_dev, int NI, int NJ, cudaStream_t st) {
+                   int M_host, const int* M_dev, int NI, int NJ, cudaStream_t st, const GemmGrp* grp = nullptr) {
   if (M_host <= 0 || NI <= 0 || NJ <= 0) return 0;
+  GemmGrp gg;
+  if (grp) gg = *grp;
+  else {
+    gg.rows = grp_single(M_host, M_dev);
+    for (int i = 0; i < kMaxGroups; ++i) { gg.wlev[i] = 0; gg.bias[i] = nullptr; gg.cout[i] = nullptr; }
+    gg.cout[0] = C;
+  }
+  const int ng = gg.rows.n;
   const CUtensorMap *ma = nullptr, *mb = nullptr;
   Operand oa, ob;
   oa.row0 = 0; oa.col0 = p_col0; oa.plane_rows = 0;
@@ -881,26 +951,26 @@ static int tn_impl(int passes, const Planes* P, int p_col0, const Planes* Q, int
   }
   const bool big = NJ > 128;
   const int BN = big ? 256 : 128;
-  const int tiles = ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
+  const int tiles = ng * ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
   int G, segmax;
-  tn_plan(NI, NJ, M_host, &G, &segmax);
+  tn_plan(NI, NJ, M_host, ng, &G, &segmax);
   const size_t need = (size_t)G * segmax * BM * BN * sizeof(float);
   PATHS_REQUIRE(g_tn_ws.p && need <= g_tn_ws.bytes, "gemm_tn_tc: stream-K workspace too small: need %zu bytes, have %zu", need, g_tn_ws.bytes);
   float* ws = static_cast<float*>(g_tn_ws.p);
 #define TN_CASE(BN_, NP_)                                                                                                              \
   do {                                                                                                                                 \
     int r;                                                                                                                             \
-    if (P) r = launch_tma<BN_, NP_, true, true, true, false, false>(ma, mb, oa, ob, none, none, ws, 0, nullptr, NI, nullptr, NJ, M_host, \
-                                                                    M_dev, 0, G, segmax, st);                                        \
-    else r = launch_tma<BN_, NP_, true, true, true, true, true>(nullptr, nullptr, oa, ob, *Ps, *Qs, ws, 0, nullptr, NI, nullptr, NJ,   \
-                                                                M_host, M_dev, 0, G, segmax, st);                                    \
+    if (P) r = launch_tma<BN_, NP_, true, true, true, false, false>(ma, mb, oa, ob, none, none, ws, 0, gg, 0, NI, NJ, M_host, 0, G,    \
+                                                                    segmax, st);                                                     \
+    else r = launch_tma<BN_, NP_, true, true, true, true, true>(nullptr, nullptr, oa, ob, *Ps, *Qs, ws, 0, gg, 0, NI, NJ, M_host, 0,  \
+                                                                G, segmax, st);                                                      \
     if (r) return r;                                                                                                                   \
     if (4 * tiles >= G)                                                                                                                \
-      tn_reduce_kernel<BN_, 1><<<dim3(tiles, BM * BN_ / 4 / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(ws), C, ldc, NI, NJ,  \
-                                                                               M_host, M_dev, G, segmax);                             \
+      tn_reduce_kernel<BN_, 1><<<dim3(tiles, BM * BN_ / 4 / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(ws), gg, ldc, NI, NJ, \
+                                                                               G, segmax);                                            \
     else                                                                                                                               \
-      tn_reduce_kernel<BN_, 8><<<dim3(tiles, BM * BN_ / 4 / 32), 256, 0, st>>>(reinterpret_cast<const float4*>(ws), C, ldc, NI, NJ,   \
-                                                                              M_host, M_dev, G, segmax);                              \
+      tn_reduce_kernel<BN_, 8><<<dim3(tiles, BM * BN_ / 4 / 32), 256, 0, st>>>(reinterpret_cast<const float4*>(ws), gg, ldc, NI, NJ,  \
+                                                                              G, segmax);                                             \
     PATHS_LAUNCH_CK();                                                                                                                 \
     return 0;                                                                                                                          \
   } while (0)
@@ -913,6 +983,30 @@ static int tn_impl(int passes, const Planes* P, int p_col0, const Planes* Q, int
 int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q_col0, float* C, int ldc, int M_host, const int* M_dev, int NI,
                  int NJ, cudaStream_t st) {
   return tn_impl(passes, &P, p_col0, &Q, q_col0, nullptr, nullptr, C, ldc, M_host, M_dev, NI, NJ, st);
+}
+
+// ---- grouped forms: one launch for the same contraction of several row groups (levels) of concatenated activation buffers.
+// A / P / Q are addressed with GLOBAL rows of the concatenated buffer; B is the first member of a stacked packed weight.
+bool gemm_tc_supported_nt_grp(const RowSrc& A, const float* B, int ldb, int N, int K) {
+  if (!cvt_ok(A) || K % 8 != 0) return false;
+  std::lock_guard<std::mutex> lk(g_mu);
+  int r0, c0;
+  const Packed* pk = find_packed(B, ldb, &r0, &c0);
+  return pk != nullptr;
+}
+int gemm_nt_tc_grp(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const GemmGrp& gg, int N, int K, int flags,
+                   cudaStream_t st) {
+  const int cap = grp_max_rows(gg.rows);
+  if (cap <= 0 || N <= 0) return 0;
+  PATHS_REQUIRE(cvt_ok(A), "gemm_nt_tc_grp: activation rows must be 16-byte aligned");
+  return nt_impl(passes, nullptr, 0, &A, B, ldb, b_kn, C, ldc, nullptr, cap, nullptr, N, K, flags, st, &gg);
+}
+int gemm_tn_tc_grp(int passes, const float* P, int ldp, const RowSrc& Q, int ldc, const GemmGrp& gg, int NI, int NJ, cudaStream_t st) {
+  const int cap = grp_max_rows(gg.rows);
+  if (cap <= 0 || NI <= 0 || NJ <= 0) return 0;
+  const RowSrc Ps = row_src(P, ldp, NI);
+  PATHS_REQUIRE(cvt_ok(Ps) && cvt_ok(Q), "gemm_tn_tc_grp: activation rows must be 16-byte aligned");
+  return tn_impl(passes, nullptr, 0, nullptr, 0, &Ps, &Q, nullptr, ldc, cap, nullptr, NI, NJ, st, &gg);
 }
 
 int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,

@@ -468,12 +468,13 @@ __global__ void __launch_bounds__(TPB) head_concat_bwd_kernel(const float* __res
 
 // dspecial[c] += sum_b dtok[special token of slide b, c]: a block sums 8 slides (one per warp) through shared memory and adds
 // its 8-row partial with one atomic per column.
-__global__ void __launch_bounds__(256) special_grad_kernel(const float* __restrict__ dtok, const int* __restrict__ seg,
-                                                           float* __restrict__ dspecial, int d, int B) {
+__global__ void __launch_bounds__(256) special_grad_kernel(const float* __restrict__ dtok, GIdx sg, MutL dsp, int d, int B) {
   __shared__ float part[8][256];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int b = blockIdx.x * 8 + w;
-  const float* r = b < B ? dtok + (size_t)(seg[b] + b) * d : nullptr;
+  const int* seg = pick(sg.idx.p, blockIdx.y);
+  float* dspecial = pick(dsp.p, blockIdx.y);
+  const float* r = b < B ? dtok + (size_t)(pick(sg.roff, blockIdx.y) + seg[b] + b) * d : nullptr;
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
     const int c = lane + 32 * q;
@@ -491,12 +492,20 @@ __global__ void __launch_bounds__(256) special_grad_kernel(const float* __restri
 
 // ---------------------------------------------------------------------------------------------------------
 // y = LayerNorm(res[ridx] + add + bias) (post-norm residual block of nn.TransformerDecoderLayer), saving xhat and rstd.
-__global__ void __launch_bounds__(TPB) res_ln_fwd_kernel(const float* __restrict__ res, const int* __restrict__ ridx,
-                                                         const float* __restrict__ add, const float* __restrict__ bias,
-                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                         float* __restrict__ y, float* __restrict__ xhat, float* __restrict__ rstd,
-                                                         int d, float eps, int M_host, const int* M_dev, int M_extra) {
-  const int M = row_count(M_host, M_dev) + M_extra;
+// Grouped (common.cuh): blockIdx.y is the row group; buffers are concatenated (rows grp.roff[g] + m), parameters per group.
+// With a row index list, res rows are ri.roff[g] + ridx[m] of the (token-shaped) res buffer.
+__global__ void __launch_bounds__(TPB) res_ln_fwd_kernel(const float* __restrict__ res, GIdx ri, const float* __restrict__ add, PtrL biasl,
+                                                         PtrL gammal, PtrL betal, float* __restrict__ y, float* __restrict__ xhat,
+                                                         float* __restrict__ rstd, int d, float eps, Grp grp) {
+  const int gi = blockIdx.y;
+  const int M = grp_count(grp, gi);
+  const size_t r0 = pick(grp.roff, gi);
+  const int* ridx = pick(ri.idx.p, gi);
+  if (res) res += (size_t)(ridx ? pick(ri.roff, gi) : r0) * d;
+  if (add) add += r0 * d;
+  y += r0 * d; xhat += r0 * d; rstd += r0;
+  const float* __restrict__ bias = pick(biasl.p, gi); const float* __restrict__ gamma = pick(gammal.p, gi);
+  const float* __restrict__ beta = pick(betal.p, gi);
   ROW_LOOP(m, M) {
     const float* r = res ? res + (size_t)(ridx ? ridx[m] : m) * d : nullptr;
     float v[8];
@@ -534,11 +543,18 @@ __global__ void __launch_bounds__(TPB) res_ln_fwd_kernel(const float* __restrict
 // dx = rstd * (g - mean(g) - xhat*mean(g*xhat)), g = dy*gamma.  dx is written (or accumulated) to dx[didx[m]];
 // dgamma/dbeta and (optionally) colsum(dx) -> dbias are accumulated.
 __global__ void __launch_bounds__(TPB) ln_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ dy2,
-                                                     const float* __restrict__ xhat, const float* __restrict__ rstd,
-                                                     const float* __restrict__ gamma, float* __restrict__ dx, const int* __restrict__ didx,
-                                                     int accum, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                     float* __restrict__ dbias, int d, int M_host, const int* M_dev, int M_extra) {
-  const int M = row_count(M_host, M_dev) + M_extra;
+                                                     const float* __restrict__ xhat, const float* __restrict__ rstd, PtrL gammal,
+                                                     float* __restrict__ dx, GIdx di, int accum, MutL dgammal, MutL dbetal, MutL dbiasl,
+                                                     int d, Grp grp) {
+  const int gi = blockIdx.y;
+  const int M = grp_count(grp, gi);
+  const size_t r0 = pick(grp.roff, gi);
+  const int* didx = pick(di.idx.p, gi);
+  dy += r0 * d; if (dy2) dy2 += r0 * d;
+  xhat += r0 * d; rstd += r0;
+  dx += (size_t)(didx ? pick(di.roff, gi) : r0) * d;
+  const float* __restrict__ gamma = pick(gammal.p, gi);
+  float* dgamma = pick(dgammal.p, gi); float* dbeta = pick(dbetal.p, gi); float* dbias = pick(dbiasl.p, gi);
   float a_g[8], a_b[8], a_x[8];
 #pragma unroll
   for (int q = 0; q < 8; ++q) a_g[q] = a_b[q] = a_x[q] = 0.f;
@@ -592,9 +608,10 @@ __global__ void __launch_bounds__(TPB) ln_bwd_kernel(const float* __restrict__ d
 // dH *= (H > 0); optionally dbias[c] += sum_m dH[m, c] in the same pass (the bias gradient of the layer that fed the ReLU).
 // ld % 4 == 0; a thread keeps one float4 column group and walks rows, so the column sums need one shared-memory combine
 // and one atomic per column per block.
-__global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, int ld, int M_host,
-                                                       const int* M_dev, int M_extra, float* __restrict__ dbias) {
-  const int M = row_count(M_host, M_dev) + M_extra;
+__global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, int ld, Grp grp, MutL dbiasl) {
+  const int M = grp_count(grp, blockIdx.y);
+  dH += (size_t)pick(grp.roff, blockIdx.y) * ld; H += (size_t)pick(grp.roff, blockIdx.y) * ld;
+  float* dbias = pick(dbiasl.p, blockIdx.y);
   const int ngrp = ld >> 2;                               // float4 groups per row
   const int rpb = 256 / ngrp > 0 ? 256 / ngrp : 1;        // rows per block iteration (ld <= 1024)
   const int g = threadIdx.x % ngrp, rsub = threadIdx.x / ngrp;
@@ -628,8 +645,11 @@ __global__ void zero_rows_kernel(float* __restrict__ X, size_t ld, int M_host, c
 }
 
 // dst[idx[m], :] += src[m, :]   (m < B rows; idx unique)
-__global__ void __launch_bounds__(TPB) scatter_add_rows_kernel(const float* __restrict__ src, const int* __restrict__ idx,
-                                                               float* __restrict__ dst, int d, int B) {
+__global__ void __launch_bounds__(TPB) scatter_add_rows_kernel(const float* __restrict__ src, GIdx di, float* __restrict__ dst, int d, Grp grp) {
+  const int B = grp_count(grp, blockIdx.y);
+  src += (size_t)pick(grp.roff, blockIdx.y) * d;
+  dst += (size_t)pick(di.roff, blockIdx.y) * d;
+  const int* idx = pick(di.idx.p, blockIdx.y);
   ROW_LOOP(m, B) {
     float* o = dst + (size_t)idx[m] * d;
     for (int c = lane; c < d; c += 32) o[c] += src[(size_t)m * d + c];
@@ -841,37 +861,63 @@ int head_concat_bwd(const float* dlogits, const float* Wc, const GList& gl, int 
   PATHS_LAUNCH_CK();
   return 0;
 }
-int special_grad(const float* dtok, const int* seg, float* dspecial, int d, int B, cudaStream_t st) {
+int special_grad_grp(const float* dtok, const GIdx& seg, const MutL& dspecial, int d, int B, int ngroups, cudaStream_t st) {
   PATHS_REQUIRE(d <= 256, "special_grad: trans_dim above 256 is not supported (d=%d)", d);
-  special_grad_kernel<<<(B + 7) / 8, 256, 0, st>>>(dtok, seg, dspecial, d, B);
+  special_grad_kernel<<<dim3((B + 7) / 8, ngroups), 256, 0, st>>>(dtok, seg, dspecial, d, B);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int special_grad(const float* dtok, const int* seg, float* dspecial, int d, int B, cudaStream_t st) {
+  return special_grad_grp(dtok, gidx1(seg), mutl1(dspecial), d, B, 1, st);
+}
+int res_ln_fwd_grp(const float* res, const GIdx& ridx, const float* add, const PtrL& bias, const PtrL& gamma, const PtrL& beta, float* y,
+                   float* xhat, float* rstd, int d, float eps, const Grp& grp, cudaStream_t st) {
+  PATHS_REQUIRE(d <= 256, "layer norm width above 256 is not supported (d=%d)", d);
+  const int cap = grp_max_rows(grp);
+  if (cap <= 0) return 0;
+  int g = row_grid(cap);
+  if (grp.n > 1 && g > 2 * kNumSMs) g = 2 * kNumSMs;
+  res_ln_fwd_kernel<<<dim3(g, grp.n), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int res_ln_fwd(const float* res, const int* ridx, const float* add, const float* bias, const float* gamma, const float* beta, float* y,
                float* xhat, float* rstd, int d, float eps, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
-  PATHS_REQUIRE(d <= 256, "layer norm width above 256 is not supported (d=%d)", d);
-  if (M_host + M_extra <= 0) return 0;
-  res_ln_fwd_kernel<<<row_grid(M_host + M_extra), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, M_host, M_dev, M_extra);
+  PATHS_REQUIRE(M_extra == 0, "res_ln_fwd: M_extra is no longer supported");
+  return res_ln_fwd_grp(res, gidx1(ridx), add, ptrl1(bias), ptrl1(gamma), ptrl1(beta), y, xhat, rstd, d, eps, grp_single(M_host, M_dev), st);
+}
+int ln_bwd_grp(const float* dy, const float* dy2, const float* xhat, const float* rstd, const PtrL& gamma, float* dx, const GIdx& didx, int accum,
+               const MutL& dgamma, const MutL& dbeta, const MutL& dbias, int d, const Grp& grp, cudaStream_t st) {
+  const int cap = grp_max_rows(grp);
+  if (cap <= 0) return 0;
+  int g = row_grid(cap);
+  const int lim = grp.n > 1 ? kNumSMs : 2 * kNumSMs;
+  if (g > lim) g = lim;
+  ln_bwd_kernel<<<dim3(g, grp.n), TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rstd, const float* gamma, float* dx, const int* didx, int accum,
            float* dgamma, float* dbeta, float* dbias, int d, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
-  if (M_host + M_extra <= 0) return 0;
-  int g = row_grid(M_host + M_extra); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
-  ln_bwd_kernel<<<g, TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, M_host, M_dev, M_extra);
+  PATHS_REQUIRE(M_extra == 0, "ln_bwd: M_extra is no longer supported");
+  return ln_bwd_grp(dy, dy2, xhat, rstd, ptrl1(gamma), dx, gidx1(didx), accum, mutl1(dgamma), mutl1(dbeta), mutl1(dbias), d,
+                    grp_single(M_host, M_dev), st);
+}
+int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st) {
+  const int cap = grp_max_rows(grp);
+  if (cap <= 0) return 0;
+  PATHS_REQUIRE(ld % 4 == 0 && ld <= 1024, "relu_bwd: row width %d unsupported (multiple of 4, <= 1024)", ld);
+  const int rpb = 256 / (ld / 4) > 0 ? 256 / (ld / 4) : 1;
+  int g = (cap + rpb - 1) / rpb;
+  const int lim = grp.n > 1 ? kNumSMs : 2 * kNumSMs;
+  if (g > lim) g = lim;
+  relu_bwd_kernel<<<dim3(g, grp.n), 256, 0, st>>>(dH, H, ld, grp, dbias);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, float* dbias, cudaStream_t st) {
-  if (M_host + M_extra <= 0) return 0;
-  PATHS_REQUIRE(ld % 4 == 0 && ld <= 1024, "relu_bwd: row width %d unsupported (multiple of 4, <= 1024)", ld);
-  const int rpb = 256 / (ld / 4) > 0 ? 256 / (ld / 4) : 1;
-  int g = (M_host + M_extra + rpb - 1) / rpb;
-  if (g > 2 * kNumSMs) g = 2 * kNumSMs;
-  relu_bwd_kernel<<<g, 256, 0, st>>>(dH, H, ld, M_host, M_dev, M_extra, dbias);
-  PATHS_LAUNCH_CK();
-  return 0;
+  PATHS_REQUIRE(M_extra == 0, "relu_bwd: M_extra is no longer supported");
+  return relu_bwd_grp(dH, H, ld, grp_single(M_host, M_dev), mutl1(dbias), st);
 }
 int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
   if (M_host + M_extra <= 0) return 0;
@@ -879,10 +925,15 @@ int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaS
   PATHS_LAUNCH_CK();
   return 0;
 }
-int scatter_add_rows(const float* src, const int* idx, float* dst, int d, int B, cudaStream_t st) {
-  scatter_add_rows_kernel<<<row_grid(B), TPB, 0, st>>>(src, idx, dst, d, B);
+int scatter_add_rows_grp(const float* src, const GIdx& idx, float* dst, int d, const Grp& grp, cudaStream_t st) {
+  const int cap = grp_max_rows(grp);
+  if (cap <= 0) return 0;
+  scatter_add_rows_kernel<<<dim3(row_grid(cap), grp.n), TPB, 0, st>>>(src, idx, dst, d, grp);
   PATHS_LAUNCH_CK();
   return 0;
+}
+int scatter_add_rows(const float* src, const int* idx, float* dst, int d, int B, cudaStream_t st) {
+  return scatter_add_rows_grp(src, gidx1(idx), dst, d, grp_single(B, nullptr), st);
 }
 int head_fwd(const float* z, const float* Fprev, const float* Wc, const float* bc, float* F, float* logits, int d, int nl, int B, cudaStream_t st) {
   PATHS_REQUIRE(d <= 256 && nl <= 32, "head: d <= 256 and at most 32 logits supported");

@@ -6,6 +6,15 @@
 
 namespace paths {
 
+// Per-group row index lists into a concatenated buffer: group g's entry idx.p[g][m] is relative to row roff[g] of that buffer.
+struct GIdx { IdxL idx; int roff[kMaxGroups]; };
+inline GIdx gidx1(const int* idx, int roff = 0) {
+  GIdx g; g.idx = idxl1(idx);
+  for (int i = 0; i < kMaxGroups; ++i) g.roff[i] = 0;
+  g.roff[0] = roff;
+  return g;
+}
+
 int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, const int* slide_ids, const int* row_slide,
                 const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st);
 int pack_padded_rows(const float* fts, int N, const int* seg, const int* row_slide, float* X, int D, int M_host, const int* M_dev,
@@ -39,6 +48,15 @@ int rnn_alpha_bwd(float* dZ, const float* dZc, const float* X, const float* UV, 
 int head_concat_fwd(const FList& fl, const float* Wc, const float* bc, float* logits, int d, int nl, int B, cudaStream_t st);
 int head_concat_bwd(const float* dlogits, const float* Wc, const GList& gl, int d, int nl, int B, cudaStream_t st);
 int special_grad(const float* dtok, const int* seg, float* dspecial, int d, int B, cudaStream_t st);
+// grouped forms (common.cuh: Grp): buffers are concatenated over the groups, parameters come per group
+int res_ln_fwd_grp(const float* res, const GIdx& ridx, const float* add, const PtrL& bias, const PtrL& gamma, const PtrL& beta, float* y,
+                   float* xhat, float* rstd, int d, float eps, const Grp& grp, cudaStream_t st);
+int ln_bwd_grp(const float* dy, const float* dy2, const float* xhat, const float* rstd, const PtrL& gamma, float* dx, const GIdx& didx, int accum,
+               const MutL& dgamma, const MutL& dbeta, const MutL& dbias, int d, const Grp& grp, cudaStream_t st);
+int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st);
+int scatter_add_rows_grp(const float* src, const GIdx& idx, float* dst, int d, const Grp& grp, cudaStream_t st);
+int special_grad_grp(const float* dtok, const GIdx& seg, const MutL& dspecial, int d, int B, int ngroups, cudaStream_t st);
+int colsum_accum_grp(const float* X, int ld, const MutL& out, const Grp& grp, int N, cudaStream_t st);
 int res_ln_fwd(const float* res, const int* ridx, const float* add, const float* bias, const float* gamma, const float* beta, float* y,
                float* xhat, float* rstd, int d, float eps, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
 int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rstd, const float* gamma, float* dx, const int* didx, int accum,
@@ -54,6 +72,16 @@ int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* h
 // attention.cu -- varlen softmax self-attention over packed token rows.  qkv is [ntok, 3d] (q | k | v), heads of width dh.
 // Slide s owns token rows [seg[s]+s, seg[s+1]+s+1).  nq_mode 0: every token is a query; 1: only token 0 of each slide
 // (the last decoder layer is read at the special token only, aggregator.py:75); outputs are then compact [B, d].
+struct SegGrp { int n, B; const int* seg[kMaxGroups]; int roff[kMaxGroups]; int oroff[kMaxGroups]; };
+inline SegGrp seg_single(const int* seg, int B) {
+  SegGrp g; g.n = 1; g.B = B;
+  for (int i = 0; i < kMaxGroups; ++i) { g.seg[i] = nullptr; g.roff[i] = 0; g.oroff[i] = 0; }
+  g.seg[0] = seg;
+  return g;
+}
+int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st);
+int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
+                 int heads, int max_T, int nq_mode, cudaStream_t st);
 int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st);
 bool attn_bwd_writes_all(int d, int heads);
 int attn_bwd(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,

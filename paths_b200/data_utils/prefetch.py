@@ -32,7 +32,9 @@ class DevicePrefetcher:
             return None
         out = dict(batch)
         with torch.cuda.stream(self.copy_stream):
-            for k in self.keys:
+            # small (pageable) label tensors first: a pageable copy blocks the host until it has run, and behind the feature
+            # copy that would be the whole 84 MB transfer
+            for k in sorted(self.keys, key=lambda k: k == "fts"):
                 v = batch.get(k)
                 if torch.is_tensor(v) and not v.is_cuda:
                     if k == "fts" and not v.is_pinned():

@@ -132,10 +132,15 @@ class ParamLayout:
         # parameters whose gradient the reference leaves at None: classifiers of levels 0..L-2 (utils.py:263 only the
         # last level's logits reach the loss)
         self.none_grad = {f"procs.{l}.classification_layer.{w}" for l in range(dims.L - 1) for w in ("weight", "bias")}
+        self._dead_zero: Dict[str, torch.Tensor] = {}
 
     def valid(self) -> bool:
         """False if some parameter was re-allocated (e.g. model.to(other_device)); the layout must then be rebuilt."""
-        return all(prm.data_ptr() == self.views[n].data_ptr() for n, prm, _, _ in self.entries + self.dead_entries)
+        # every parameter is re-allocated together by the operations that invalidate the layout (.to(), .float(), load with
+        # assign=True): probing the first, middle and last tensor keeps this off the per-step critical path
+        ents = self.entries
+        probe = (ents[0], ents[len(ents) // 2], ents[-1]) + ((self.dead_entries[-1],) if self.dead_entries else ())
+        return all(prm.data_ptr() == self.views[n].data_ptr() for n, prm, _, _ in probe)
 
     def prepare_grads(self) -> None:
         """Make gflat the accumulation target of every live parameter's .grad (autograd semantics: grad += new)."""
@@ -158,7 +163,10 @@ class ParamLayout:
                 prm.grad = self.gviews[n]
         for n, prm in self.dead:                       # the reference produces exact zeros for the dead encoder / cross-attn
             if prm.requires_grad and prm.grad is None and ".transformer." in n:
-                prm.grad = torch.zeros_like(prm)       # (never-evaluated modules such as procs.0.hctx_mlp keep grad = None)
+                z = self._dead_zero.get(n)             # (never-evaluated modules such as procs.0.hctx_mlp keep grad = None)
+                if z is None:
+                    z = self._dead_zero[n] = torch.zeros_like(prm)     # never written by the engine: allocated once
+                prm.grad = z
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -168,6 +176,7 @@ class PyramidStore:
     step then only names slides by index."""
 
     def __init__(self, num_levels: int, dim: int, device):
+        self._cap_cache = {}
         self.L, self.D, self.device = num_levels, dim, torch.device(device)
         self.grids: List[List[torch.Tensor]] = []
         self.bits: List[torch.Tensor] = []
@@ -216,6 +225,10 @@ class PyramidStore:
     def capacities(self, slide_ids: Sequence[int], top_k: Sequence[int], worst_case: bool = False) -> Tuple[List[int], List[int]]:
         """Row capacity and largest bag per level for a batch (bounds of slide.py:294-331: at most 4 children per kept
         row and never more than the grid has cells).  worst_case sizes for the no-child fallback (slide.py:336-352)."""
+        key = (tuple(slide_ids), tuple(top_k), bool(worst_case))      # the same batches recur every epoch
+        hit = self._cap_cache.get(key)
+        if hit is not None:
+            return list(hit[0]), list(hit[1])
         caps, maxseg = [0] * self.L, [1] * self.L
         for sid in slide_ids:
             n = self.shapes[sid][0][0] * self.shapes[sid][0][1]
@@ -227,6 +240,9 @@ class PyramidStore:
                     n = cells if worst_case else min(4 * kept, cells)
                 caps[l] += n
                 maxseg[l] = max(maxseg[l], n)
+        if len(self._cap_cache) > 4096:
+            self._cap_cache.clear()
+        self._cap_cache[key] = (tuple(caps), tuple(maxseg))
         return caps, maxseg
 
 
@@ -311,10 +327,17 @@ class Engine:
         L.check(self.lib.paths_engine_level_backward(self.handle, level, int(use_dlogits), _stream()), "level_backward")
 
     def forward(self, slide_ids: torch.Tensor, ybin: Optional[torch.Tensor], cens: Optional[torch.Tensor], scale: float,
-                with_loss: bool = True) -> None:
-        L.check(self.lib.paths_engine_forward(self.handle, slide_ids.data_ptr(), ybin.data_ptr() if ybin is not None else None,
-                                              cens.data_ptr() if cens is not None else None, scale, int(with_loss), _stream()),
-                "engine_forward")
+                with_loss: bool = True, fts_padded: Optional[torch.Tensor] = None) -> None:
+        yb = ybin.data_ptr() if ybin is not None else None
+        cs = cens.data_ptr() if cens is not None else None
+        if fts_padded is None:
+            L.check(self.lib.paths_engine_forward(self.handle, slide_ids.data_ptr(), yb, cs, scale, int(with_loss), _stream()),
+                    "engine_forward")
+        else:
+            assert fts_padded.is_cuda and fts_padded.dtype == torch.float32 and fts_padded.is_contiguous()
+            L.check(self.lib.paths_engine_forward_padded(self.handle, slide_ids.data_ptr(), fts_padded.data_ptr(),
+                                                         int(fts_padded.shape[1]), yb, cs, scale, int(with_loss), _stream()),
+                    "engine_forward_padded")
 
     def backward(self, zero_grads: bool = False) -> None:
         L.check(self.lib.paths_engine_backward(self.handle, int(zero_grads), _stream()), "engine_backward")

@@ -16,7 +16,7 @@ PRECISIONS = {"fp32": 0, "bf16x3": 1, "bf16": 2}
 
 
 def default_precision() -> int:
-    return PRECISIONS[os.environ.get("PATHS_B200_PRECISION", "fp32")]
+    return PRECISIONS[os.environ.get("PATHS_B200_PRECISION", "bf16x3")]
 
 
 class _StepFn(torch.autograd.Function):
@@ -25,13 +25,7 @@ class _StepFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, anchor, rt, eng, slide_ids, fts_padded, ybin, cens, scale):
-        eng.begin(slide_ids, fts_padded)
-        nl = eng.dims.L
-        for l in range(nl):
-            eng.level_forward(l)
-            if l < nl - 1:
-                eng.select(l)
-        eng.loss(ybin, cens, scale)
+        eng.forward(slide_ids, ybin, cens, scale, True, fts_padded)       # whole step: chain + grouped aggregators on the engine's streams
         ctx.rt, ctx.eng = rt, eng
         hz = eng.buffer(0, "HAZARDS").view(eng.B, eng.dims.nl).clone()
         loss = eng.buffer(0, "LOSS").view(()).clone()
@@ -72,6 +66,7 @@ class ModelRuntime:
         self.strict_overflow = os.environ.get("PATHS_B200_STRICT_OVERFLOW", "0") == "1"
         self._pending: Optional[Engine] = None
         self._warned_dropout = False
+        self._ids_cache: Dict[tuple, torch.Tensor] = {}
         self.global_batch: Optional[int] = None        # set by the data-parallel wrapper: loss = sum / global batch
 
     # ------------------------------------------------------------------------------------------------------------
@@ -134,7 +129,12 @@ class ModelRuntime:
             if getattr(eng, "_store", (None,))[0] is not store or store.tables()[1] is not eng._store[2]:
                 eng.bind_store(store)
             dev = self.device
-            slide_ids = torch.tensor(ids, dtype=torch.int32).to(dev, non_blocking=True)
+            key = tuple(ids)
+            slide_ids = self._ids_cache.get(key)               # the same batches recur every epoch: no per-step host -> device copy
+            if slide_ids is None:
+                if len(self._ids_cache) > 4096:
+                    self._ids_cache.clear()
+                slide_ids = self._ids_cache[key] = torch.tensor(ids, dtype=torch.int32).to(dev)
             fts = batch.get("fts") if use_batch_fts else None
             if fts is not None:
                 fts = fts.to(dev, dtype=torch.float32, non_blocking=True).contiguous()
