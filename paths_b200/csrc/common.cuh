@@ -156,7 +156,9 @@ struct GemmGrp {
   float* cout[kMaxGroups];
 };
 
-enum GemmFlags { GEMM_RELU = 1, GEMM_ACCUM = 2 };
+// GEMM_GATES: the output is the LSTM gate pre-activation block [f | r | m | o] (widths C, C, C, D; C = flags >> 8): the
+// epilogue applies sigmoid / sigmoid / tanh / sigmoid by column range, so the gates reach HBM already activated.
+enum GemmFlags { GEMM_RELU = 1, GEMM_ACCUM = 2, GEMM_GATES = 4 };
 
 // Precision modes of the dense contractions.
 //   0: fp32 SIMT FFMA (exact fp32 semantics, the parity anchor)

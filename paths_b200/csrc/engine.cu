@@ -412,11 +412,12 @@ int lstm_forward(paths_engine* e, int l, cudaStream_t st) {
     if (pl) RUN(split_rows(Axh, M, Md, Kx, v.AxhP, 0, lo != 0, st));
     {
       ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
-      if (pl) RUN(gemm_nt_act(prec, act(nullptr, 0, v.AxhP), e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, Kx, 0, st));
+      // tensor-core path: the epilogue applies the gate non-linearities, G reaches HBM activated (written once)
+      if (pl) RUN(gemm_nt_act(prec, act(nullptr, 0, v.AxhP), e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, Kx, GEMM_GATES | (C << 8), st));
       else RUN(gemm_nt(prec, Axh, e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, Kx, 0, st));
     }
     RUN(lstm_point1_fwd(v.G, has_parent ? e->lv[l - 1].Cn : nullptr, has_parent ? v.row_parent : nullptr, v.Cn, pl ? v.CnP : no_planes(), lo,
-                        D, C, M, Md, st));
+                        pl ? 1 : 0, D, C, M, Md, st));
     RUN(gemm_nt_act(prec, act(v.Cn, C, pl ? v.CnP : no_planes()), e->P.Wmo, C, 0, v.Pt, D, e->P.bmo, M, Md, D, C, 0, st));
     RUN(lstm_point2_fwd(v.Pt, v.G, v.X, v.H, pl ? nullptr : v.Y, pl ? v.YP : no_planes(), lo, D, C, M, Md, st));
 

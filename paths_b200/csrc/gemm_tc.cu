@@ -536,6 +536,11 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           if (!SK) {
             w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
             if (flags & GEMM_RELU) { w.x = fmaxf(w.x, 0.f); w.y = fmaxf(w.y, 0.f); w.z = fmaxf(w.z, 0.f); w.w = fmaxf(w.w, 0.f); }
+            if (flags & GEMM_GATES) {                        // column ranges are multiples of 4: one branch per float4
+              const int gc = flags >> 8;
+              if (nn >= 2 * gc && nn < 3 * gc) { w.x = tanhf(w.x); w.y = tanhf(w.y); w.z = tanhf(w.z); w.w = tanhf(w.w); }
+              else { w.x = sigmoidf_(w.x); w.y = sigmoidf_(w.y); w.z = sigmoidf_(w.z); w.w = sigmoidf_(w.w); }
+            }
           }
           if (vec && nn + 3 < oj_lim) {
             if (!SK && (flags & GEMM_ACCUM)) { const float4 c = *reinterpret_cast<const float4*>(cp); w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w; }

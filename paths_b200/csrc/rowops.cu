@@ -43,7 +43,7 @@ __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<floa
 
 __global__ void __launch_bounds__(TPB) lstm_point1_fwd_kernel(float* __restrict__ G, const float* __restrict__ Cprev,
                                                               const int* __restrict__ parent, float* __restrict__ Cn, Planes CnP, int want_lo,
-                                                              int D, int C, int M_host, const int* M_dev) {
+                                                              int activated, int D, int C, int M_host, const int* M_dev) {
   const int M = row_count(M_host, M_dev);
   const int ldg = 3 * C + D;
   const int Mw = CnP.p ? planes_rows_to_write(CnP, M) : M;
@@ -59,20 +59,23 @@ __global__ void __launch_bounds__(TPB) lstm_point1_fwd_kernel(float* __restrict_
       const int c = 4 * c4;
       float4 f = ld4(g + c), r = ld4(g + C + c), mm = ld4(g + 2 * C + c);
       const float4 cprev = cp ? ld4(cp + c) : make_float4(0.f, 0.f, 0.f, 0.f);
-      f.x = sigmoidf_(f.x); f.y = sigmoidf_(f.y); f.z = sigmoidf_(f.z); f.w = sigmoidf_(f.w);
-      r.x = sigmoidf_(r.x); r.y = sigmoidf_(r.y); r.z = sigmoidf_(r.z); r.w = sigmoidf_(r.w);
-      mm.x = tanhf(mm.x); mm.y = tanhf(mm.y); mm.z = tanhf(mm.z); mm.w = tanhf(mm.w);
-      st4(g + c, f); st4(g + C + c, r); st4(g + 2 * C + c, mm);
+      if (!activated) {                                      // (the tensor-core gate contraction activates in its epilogue)
+        f.x = sigmoidf_(f.x); f.y = sigmoidf_(f.y); f.z = sigmoidf_(f.z); f.w = sigmoidf_(f.w);
+        r.x = sigmoidf_(r.x); r.y = sigmoidf_(r.y); r.z = sigmoidf_(r.z); r.w = sigmoidf_(r.w);
+        mm.x = tanhf(mm.x); mm.y = tanhf(mm.y); mm.z = tanhf(mm.z); mm.w = tanhf(mm.w);
+        st4(g + c, f); st4(g + C + c, r); st4(g + 2 * C + c, mm);
+      }
       const float4 cn = make_float4(cprev.x * f.x + r.x * mm.x, cprev.y * f.y + r.y * mm.y, cprev.z * f.z + r.z * mm.z,
                                     cprev.w * f.w + r.w * mm.w);
       st4(Cn + (size_t)m * C + c, cn);
       if (CnP.p) planes_store4(CnP, m, c, cn, want_lo);
     }
-    for (int j4 = lane; j4 < D / 4; j4 += 32) {
-      float4 o = ld4(g + 3 * C + 4 * j4);
-      o.x = sigmoidf_(o.x); o.y = sigmoidf_(o.y); o.z = sigmoidf_(o.z); o.w = sigmoidf_(o.w);
-      st4(g + 3 * C + 4 * j4, o);
-    }
+    if (!activated)
+      for (int j4 = lane; j4 < D / 4; j4 += 32) {
+        float4 o = ld4(g + 3 * C + 4 * j4);
+        o.x = sigmoidf_(o.x); o.y = sigmoidf_(o.y); o.z = sigmoidf_(o.z); o.w = sigmoidf_(o.w);
+        st4(g + 3 * C + 4 * j4, o);
+      }
   }
 }
 
@@ -770,11 +773,12 @@ int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, c
   PATHS_LAUNCH_CK();
   return 0;
 }
-int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, const Planes& CnP, int want_lo, int D, int C, int M_host,
+int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, const Planes& CnP, int want_lo, int activated, int D, int C,
+                    int M_host,
                     const int* M_dev, cudaStream_t st) {
   PATHS_REQUIRE(D % 4 == 0 && C % 4 == 0, "lstm: D and C must be multiples of 4");
   if (M_host <= 0) return 0;
-  lstm_point1_fwd_kernel<<<row_grid(M_host + 64), TPB, 0, st>>>(G, Cprev, parent, Cn, CnP, want_lo, D, C, M_host, M_dev);
+  lstm_point1_fwd_kernel<<<row_grid(M_host + 64), TPB, 0, st>>>(G, Cprev, parent, Cn, CnP, want_lo, activated, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }

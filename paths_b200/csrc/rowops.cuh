@@ -21,7 +21,8 @@ int pack_padded_rows(const float* fts, int N, const int* seg, const int* row_sli
                      cudaStream_t st);
 // Outputs come as fp32 rows (pointer may be null) and/or bf16 (hi, lo) planes (Planes.p may be null); want_lo = 0 skips the
 // lo plane (single-pass bf16 mode).  The backward kernels also accumulate the bias gradients (column sums) they pass over.
-int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, const Planes& CnP, int want_lo, int D, int C, int M_host,
+int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, const Planes& CnP, int want_lo, int activated, int D, int C,
+                    int M_host,
                     const int* M_dev, cudaStream_t st);
 int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
                     const int* M_dev, cudaStream_t st);
