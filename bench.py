@@ -131,11 +131,24 @@ def run_reference(args):
         "e2e": {"value": rate, "unit": "slides/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    print(json.dumps(line), file=_OUT, flush=True)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+# The JSON line is the only thing that may reach stdout: libraries that print there (NCCL's version banner under torchrun)
+# are sent to stderr for the duration of the run.
+_OUT = sys.stdout
+
+
+def _claim_stdout():
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -335,7 +348,7 @@ def main():
                        "l2": "per-step working set (activations ~3 GB, pyramids 16 GB) far exceeds the 126 MB L2"},
             "host_enqueue_ms_per_step": host_enqueue_ms, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "fast_mode": fast, "gpu_launches": launches, "clocks": clocks,
         }
-        print(json.dumps(line))
+        print(json.dumps(line), file=_OUT, flush=True)
     if os.environ.get("PATHS_B200_PROF_DUMP"):               # developer aid: per-call-site timings are written at engine destruction
         torch.cuda.synchronize()
         rt.engines.clear(); rt.last_engine = None; rt._pending = None

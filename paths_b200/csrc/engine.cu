@@ -42,6 +42,10 @@ bool gemm_tc_supported_nt_grp(const RowSrc& A, const float* B, int ldb, int N, i
 int gemm_nt_tc_grp(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const GemmGrp& gg, int N, int K, int flags,
                    cudaStream_t st);
 int gemm_tn_tc_grp(int passes, const float* P, int ldp, const RowSrc& Q, int ldc, const GemmGrp& gg, int NI, int NJ, cudaStream_t st);
+int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp& grp, bool want_lo, cudaStream_t st);
+int gemm_nt_tc_grp_p(int passes, const Planes& A, const float* B, int ldb, int b_kn, float* C, int ldc, const GemmGrp& gg, int N, int K, int flags,
+                     cudaStream_t st);
+int gemm_tn_tc_grp_p(int passes, const Planes& P, const Planes& Q, int ldc, const GemmGrp& gg, int NI, int NJ, cudaStream_t st);
 size_t packed_bytes(int R, int Cc);
 int register_packed(const float* src, int R, int Cc, int ld, void* dst, int nstack);
 void unregister_packed(const float* src);
@@ -161,6 +165,8 @@ struct paths_engine {
   char* dec_tn_ws[PATHS_MAX_LEVELS]; size_t dec_tn_ws_bytes;   // ... of the decoder sets (one per concurrently running set)
   const float* dtok_base;                                // gradient w.r.t. the tokens, concatenated (one of lv[0].ga / lv[0].gt)
   bool stacked;                                          // decoder weights are packed as per-kind stacks over the levels
+  int S, Bs;                                             // row stride between the levels' regions: token-shaped / slide-shaped buffers
+  Planes dplD[2], dplF[2], dpl3;                         // decoder operand planes (bf16 hi, lo) of width d, F, 3d over all L * S rows
   // level sets of the whole-step entry points: each set's aggregators run as one grouped pass on the set's own stream
   int n_fsets, n_bsets;
   int fset_n[PATHS_MAX_LEVELS], fset_lv[PATHS_MAX_LEVELS][PATHS_MAX_LEVELS];
@@ -182,28 +188,33 @@ size_t carve(paths_engine* e, char* base) {
   const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F;
   Bump b{base, 0};
   int maxcap = 0;
-  size_t Ttot = 0;
+  // uniform region stride (a multiple of 64 rows): a level's region can be zero-filled up to the longest level's row count
+  // without touching its neighbour (what the grouped weight-gradient contraction on TMA-fed planes needs)
+  int S = 64;
   for (int l = 0; l < dm.L; ++l) {
     Level& v = e->lv[l];
     v.ncap_tok = v.cap + B;
-    v.tok_off = (int)Ttot;
-    Ttot += (size_t)v.ncap_tok;
+    if (((v.ncap_tok + 63) & ~63) > S) S = (v.ncap_tok + 63) & ~63;
     if (v.cap > maxcap) maxcap = v.cap;
   }
+  const int Bs = (B + 63) & ~63;
+  e->S = S; e->Bs = Bs;
+  for (int l = 0; l < dm.L; ++l) e->lv[l].tok_off = l * S;
+  const size_t Ttot = (size_t)dm.L * S;
   // concatenated decoder buffers: one allocation of [Ttot, cols] (token-shaped) or [L * B, cols] (slide-shaped), sliced per level
   auto cat_tok = [&](size_t cols, float* Level::*m) {
     float* base_p = b.take<float>(Ttot * cols);
     for (int l = 0; l < dm.L; ++l) e->lv[l].*m = base_p ? base_p + (size_t)e->lv[l].tok_off * cols : nullptr;
   };
   auto cat_b = [&](size_t cols, float* Level::*m) {
-    float* base_p = b.take<float>((size_t)dm.L * B * cols);
-    for (int l = 0; l < dm.L; ++l) e->lv[l].*m = base_p ? base_p + (size_t)l * B * cols : nullptr;
+    float* base_p = b.take<float>((size_t)dm.L * Bs * cols);
+    for (int l = 0; l < dm.L; ++l) e->lv[l].*m = base_p ? base_p + (size_t)l * Bs * cols : nullptr;
   };
   auto cat_layer = [&](int j, bool tokens, size_t cols, float* LayerBuf::*m) {
-    const size_t rows = tokens ? Ttot : (size_t)dm.L * B;
+    const size_t rows = tokens ? Ttot : (size_t)dm.L * Bs;
     float* base_p = b.take<float>(rows * cols);
     for (int l = 0; l < dm.L; ++l)
-      e->lv[l].layer[j].*m = base_p ? base_p + (tokens ? (size_t)e->lv[l].tok_off : (size_t)l * B) * cols : nullptr;
+      e->lv[l].layer[j].*m = base_p ? base_p + (tokens ? (size_t)e->lv[l].tok_off : (size_t)l * Bs) * cols : nullptr;
   };
   cat_tok(d, &Level::tok);
   for (int j = 0; j < dm.layers; ++j) {
@@ -221,6 +232,17 @@ size_t carve(paths_engine* e, char* base) {
   cat_tok(3 * d, &Level::dqkv); cat_tok(F, &Level::dHf); cat_tok(dm.heads, &Level::Dvec);
   cat_b(d, &Level::gab); cat_b(d, &Level::gbb); cat_b(d, &Level::gOb); cat_b(F, &Level::dHfb);
   cat_b(d, &Level::dFl); cat_b(d, &Level::dy3s);
+  {
+    auto mk = [&](int cols) {
+      Planes pl = planes_at(b.take<char>(planes_bytes((int)Ttot, cols)), (int)Ttot, cols);
+      if (!base) pl.p = nullptr;
+      return pl;
+    };
+    const bool want = d % 8 == 0 && F % 8 == 0;
+    e->dplD[0] = want ? mk(d) : no_planes(); e->dplD[1] = want ? mk(d) : no_planes();
+    e->dplF[0] = want ? mk(F) : no_planes(); e->dplF[1] = want ? mk(F) : no_planes();
+    e->dpl3 = want ? mk(3 * d) : no_planes();
+  }
   {
     const int dec_shapes[][2] = {{3 * d, d}, {d, d}, {F, d}, {d, F}};
     size_t tnb = 0;
@@ -471,8 +493,8 @@ DecSet make_set(const paths_engine* e, const int* lvls, int n) {
     const Level& v = e->lv[l];
     S.lv[g] = l;
     S.gt.roff[g] = v.tok_off; S.gt.hcnt[g] = v.ncap_tok; S.gt.cnt[g] = v.ntok;
-    S.gb.roff[g] = l * e->B; S.gb.hcnt[g] = e->B; S.gb.cnt[g] = nullptr;
-    S.sg.seg[g] = v.seg; S.sg.roff[g] = v.tok_off; S.sg.oroff[g] = l * e->B;
+    S.gb.roff[g] = l * e->Bs; S.gb.hcnt[g] = e->B; S.gb.cnt[g] = nullptr;
+    S.sg.seg[g] = v.seg; S.sg.roff[g] = v.tok_off; S.sg.oroff[g] = l * e->Bs;
     S.tsegI.idx.p[g] = v.tseg; S.tsegI.roff[g] = v.tok_off;
     S.segI.idx.p[g] = v.seg; S.segI.roff[g] = v.tok_off;
     if (v.maxseg + 1 > S.max_T) S.max_T = v.maxseg + 1;
@@ -488,10 +510,35 @@ inline GIdx noidx() { return gidx1(nullptr); }
 
 // C rows of every group (+)= act(A rows . W_level^T + bias_level): grouped tensor-core launch when the weights are stacked,
 // per-level contractions otherwise (fp32 SIMT mode, odd dimensions).  A and C are bases of concatenated buffers.
+// An operand of the grouped contractions as bf16 (hi, lo) planes in one of the engine's scratch plane buffers: split once
+// (one coalesced pass, which also zero-fills the rows the weight-gradient form reads past a short group), then fed by TMA to
+// every contraction that uses it -- the small-K aggregator contractions are latency-bound when their loader warps convert
+// fp32 rows themselves (one 32 KB batch in flight per SM), and TMA keeps the whole smem ring in flight.
+struct OpPl { Planes pl; bool ready; };
+inline OpPl oppl(const Planes& pl) { OpPl o; o.pl = pl; o.ready = false; return o; }
+inline bool dec_planes_on(const paths_engine* e) {
+  static const bool off = getenv("PATHS_B200_DEC_NO_PLANES") != nullptr;
+  return !off && e->dm.precision != PREC_FP32_SIMT && e->stacked && e->dplD[0].p != nullptr;
+}
+int ensure_split(paths_engine* e, const Grp& rows, const float* A, int lda, int K, OpPl* op, cudaStream_t st) {
+  if (op->ready) return 0;
+  if (int r = split_rows_grp(A, lda, K, op->pl, rows, e->dm.precision == PREC_BF16X3_TC, st)) return r;
+  e->launches++;
+  op->ready = true;
+  return 0;
+}
+
 template <typename WF>
 int gemm_nt_set(paths_engine* e, const DecSet& S, const Grp& rows, const float* A, int lda, WF W, int ldb, int b_kn, float* C, int ldc,
-                const PtrL& bias, int N, int K, int flags, cudaStream_t st) {
+                const PtrL& bias, int N, int K, int flags, cudaStream_t st, OpPl* ap = nullptr) {
   const int prec = e->dm.precision;
+  if (ap && dec_planes_on(e) && K % 8 == 0 && lda == K) {
+    GemmGrp gg;
+    gg.rows = rows;
+    for (int g = 0; g < kMaxGroups; ++g) { gg.wlev[g] = g < S.n ? S.lv[g] : 0; gg.bias[g] = bias.p[g]; gg.cout[g] = nullptr; }
+    if (int r = ensure_split(e, rows, A, lda, K, ap, st)) return r;
+    return gemm_nt_tc_grp_p(prec == PREC_BF16X3_TC ? 3 : 1, ap->pl, W(0), ldb, b_kn, C, ldc, gg, N, K, flags, st);
+  }
   if (prec != PREC_FP32_SIMT && e->stacked && gemm_tc_supported_nt_grp(row_src(A, lda, K), W(0), ldb, N, K)) {
     GemmGrp gg;
     gg.rows = rows;
@@ -509,8 +556,16 @@ int gemm_nt_set(paths_engine* e, const DecSet& S, const Grp& rows, const float* 
 // dW_level[NI, NJ] += P rows^T . Q rows over every group's rows
 template <typename GF>
 int gemm_tn_set(paths_engine* e, const DecSet& S, const Grp& rows, const float* P, int ldp, const float* Q, int ldq, GF dW, int ldc, int NI, int NJ,
-                cudaStream_t st) {
+                cudaStream_t st, OpPl* pp = nullptr, OpPl* qp = nullptr) {
   const int prec = e->dm.precision;
+  if (pp && qp && dec_planes_on(e) && NI % 8 == 0 && NJ % 8 == 0 && ldp == NI && ldq == NJ) {
+    GemmGrp gg;
+    gg.rows = rows;
+    for (int g = 0; g < kMaxGroups; ++g) { gg.wlev[g] = 0; gg.bias[g] = nullptr; gg.cout[g] = g < S.n ? const_cast<float*>(dW(S.lv[g])) : nullptr; }
+    if (int r = ensure_split(e, rows, P, ldp, NI, pp, st)) return r;
+    if (int r = ensure_split(e, rows, Q, ldq, NJ, qp, st)) return r;
+    return gemm_tn_tc_grp_p(prec == PREC_BF16X3_TC ? 3 : 1, pp->pl, qp->pl, ldc, gg, NI, NJ, st);
+  }
   if (prec != PREC_FP32_SIMT && gemm_tc_supported_tn(ldp, row_src(Q, ldq, NJ), ldc, NI, NJ) && ldp % 8 == 0 && ldq % 8 == 0) {
     GemmGrp gg;
     gg.rows = rows;
@@ -541,10 +596,11 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
     const Grp& gr = last ? S.gb : S.gt;
     float* A1 = last ? v0.A1b : v0.A1;
     float* Fo = last ? v0.Fob : v0.Fo;
+    OpPl pT = oppl(e->dplD[0]), pO = oppl(e->dplD[1]), pY2 = oppl(e->dplD[0]), pHf = oppl(e->dplF[0]);
     RUN(gemm_nt_set(e, S, S.gt, t_in, d, [&](int l) { return P[l].layer[j].Wqkv; }, d, 0, y.qkv, 3 * d,
-                    PL(S, [&](int l) { return P[l].layer[j].bqkv; }), 3 * d, d, 0, st));
+                    PL(S, [&](int l) { return P[l].layer[j].bqkv; }), 3 * d, d, 0, st, &pT));
     RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st));
-    RUN(gemm_nt_set(e, S, gr, y.O, d, [&](int l) { return P[l].layer[j].Wo; }, d, 0, A1, d, PL0(), d, d, 0, st));
+    RUN(gemm_nt_set(e, S, gr, y.O, d, [&](int l) { return P[l].layer[j].Wo; }, d, 0, A1, d, PL0(), d, d, 0, st, &pO));
     RUN(res_ln_fwd_grp(t_in, last ? S.tsegI : noidx(), A1, PL(S, [&](int l) { return P[l].layer[j].bo; }),
                        PL(S, [&](int l) { return P[l].layer[j].n1w; }), PL(S, [&](int l) { return P[l].layer[j].n1b; }), y.y1, y.xh1, y.rs1, d,
                        1e-5f, gr, st));
@@ -552,8 +608,8 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
                        PL(S, [&](int l) { return P[l].layer[j].n2w; }), PL(S, [&](int l) { return P[l].layer[j].n2b; }), y.y2, y.xh2, y.rs2, d,
                        1e-5f, gr, st));
     RUN(gemm_nt_set(e, S, gr, y.y2, d, [&](int l) { return P[l].layer[j].W1; }, d, 0, y.Hf, F, PL(S, [&](int l) { return P[l].layer[j].b1; }), F,
-                    d, GEMM_RELU, st));
-    RUN(gemm_nt_set(e, S, gr, y.Hf, F, [&](int l) { return P[l].layer[j].W2; }, F, 0, Fo, d, PL0(), d, F, 0, st));
+                    d, GEMM_RELU, st, &pY2));
+    RUN(gemm_nt_set(e, S, gr, y.Hf, F, [&](int l) { return P[l].layer[j].W2; }, F, 0, Fo, d, PL0(), d, F, 0, st, &pHf));
     RUN(res_ln_fwd_grp(y.y2, noidx(), Fo, PL(S, [&](int l) { return P[l].layer[j].b2; }), PL(S, [&](int l) { return P[l].layer[j].n3w; }),
                        PL(S, [&](int l) { return P[l].layer[j].n3b; }), y.y3, y.xh3, y.rs3, d, 1e-5f, gr, st));
     t_in = y.y3;
@@ -649,31 +705,35 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
     // LN3 -> gA = d(y2 + ffn); db2
     RUN(ln_bwd_grp(dy3, nullptr, y.xh3, y.rs3, PL(S, [&](int l) { return Wl(l).n3w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n3w; }),
                    ML(S, [&](int l) { return Gl(l).n3b; }), ML(S, [&](int l) { return Gl(l).b2; }), d, gr, st));
-    RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).W2; }, F, 1, dHf, F, PL0(), F, d, 0, st));
-    RUN(gemm_tn_set(e, S, gr, gA, d, y.Hf, F, [&](int l) { return Gl(l).W2; }, F, d, F, st));
+    // operand planes: each tensor is split once and feeds both the data-gradient and the weight-gradient contraction
+    OpPl pA = oppl(e->dplD[0]), pHf = oppl(e->dplF[0]), pdHf = oppl(e->dplF[1]), pY2 = oppl(e->dplD[1]);
+    RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).W2; }, F, 1, dHf, F, PL0(), F, d, 0, st, &pA));
+    RUN(gemm_tn_set(e, S, gr, gA, d, y.Hf, F, [&](int l) { return Gl(l).W2; }, F, d, F, st, &pA, &pHf));
     RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st));
-    RUN(gemm_tn_set(e, S, gr, dHf, F, y.y2, d, [&](int l) { return Gl(l).W1; }, d, F, d, st));
-    RUN(gemm_nt_set(e, S, gr, dHf, F, [&](int l) { return Wl(l).W1; }, d, 1, gA, d, PL0(), d, F, GEMM_ACCUM, st));     // gA = dy2
+    RUN(gemm_tn_set(e, S, gr, dHf, F, y.y2, d, [&](int l) { return Gl(l).W1; }, d, F, d, st, &pdHf, &pY2));
+    RUN(gemm_nt_set(e, S, gr, dHf, F, [&](int l) { return Wl(l).W1; }, d, 1, gA, d, PL0(), d, F, GEMM_ACCUM, st, &pdHf));     // gA = dy2
     // LN2 (cross-attention over an empty memory contributes only its output bias), then LN1
     RUN(ln_bwd_grp(gA, nullptr, y.xh2, y.rs2, PL(S, [&](int l) { return Wl(l).n2w; }), gB, noidx(), 0, ML(S, [&](int l) { return Gl(l).n2w; }),
                    ML(S, [&](int l) { return Gl(l).n2b; }), ML(S, [&](int l) { return Gl(l).bcross; }), d, gr, st));
     RUN(ln_bwd_grp(gB, nullptr, y.xh1, y.rs1, PL(S, [&](int l) { return Wl(l).n1w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n1w; }),
                    ML(S, [&](int l) { return Gl(l).n1b; }), ML(S, [&](int l) { return Gl(l).bo; }), d, gr, st));      // gA = da
-    RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).Wo; }, d, 1, gO, d, PL0(), d, d, 0, st));
-    RUN(gemm_tn_set(e, S, gr, gA, d, y.O, d, [&](int l) { return Gl(l).Wo; }, d, d, d, st));
+    OpPl pA2 = oppl(e->dplD[0]), pO = oppl(e->dplD[1]);
+    RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).Wo; }, d, 1, gO, d, PL0(), d, d, 0, st, &pA2));
+    RUN(gemm_tn_set(e, S, gr, gA, d, y.O, d, [&](int l) { return Gl(l).Wo; }, d, d, d, st, &pA2, &pO));
     if (last && !attn_bwd_writes_all(d, dm.heads))
       for (int g = 0; g < S.n; ++g)
         RUN(zero_rows(v0.dqkv + (size_t)S.gt.roff[g] * 3 * d, 3 * d, S.gt.hcnt[g], S.gt.cnt[g], 0, st));
     RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st));
-    RUN(gemm_tn_set(e, S, S.gt, v0.dqkv, 3 * d, t_in, d, [&](int l) { return Gl(l).Wqkv; }, d, 3 * d, d, st));
+    OpPl p3 = oppl(e->dpl3), pT = oppl(e->dplD[0]);
+    RUN(gemm_tn_set(e, S, S.gt, v0.dqkv, 3 * d, t_in, d, [&](int l) { return Gl(l).Wqkv; }, d, 3 * d, d, st, &p3, &pT));
     RUN(colsum_accum_grp(v0.dqkv, 3 * d, ML(S, [&](int l) { return Gl(l).bqkv; }), S.gt, 3 * d, st));
     if (last) {
-      RUN(gemm_nt_set(e, S, S.gt, v0.dqkv, 3 * d, [&](int l) { return Wl(l).Wqkv; }, d, 1, gtk, d, PL0(), d, 3 * d, 0, st));
+      RUN(gemm_nt_set(e, S, S.gt, v0.dqkv, 3 * d, [&](int l) { return Wl(l).Wqkv; }, d, 1, gtk, d, PL0(), d, 3 * d, 0, st, &p3));
       RUN(scatter_add_rows_grp(gA, S.tsegI, gtk, d, S.gb, st));
       dy3 = gtk;
     } else {
       // ga holds da (the residual branch); add the attention branch, then hand the buffer over as the next layer's dy3
-      RUN(gemm_nt_set(e, S, S.gt, v0.dqkv, 3 * d, [&](int l) { return Wl(l).Wqkv; }, d, 1, ga, d, PL0(), d, 3 * d, GEMM_ACCUM, st));
+      RUN(gemm_nt_set(e, S, S.gt, v0.dqkv, 3 * d, [&](int l) { return Wl(l).Wqkv; }, d, 1, ga, d, PL0(), d, 3 * d, GEMM_ACCUM, st, &p3));
       float* tmp = ga; ga = gtk; gtk = tmp;
       dy3 = gtk;
     }

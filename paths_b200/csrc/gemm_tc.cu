@@ -174,6 +174,32 @@ __global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host,
   }
 }
 
+// Grouped form (common.cuh: Grp): rows are global rows of a concatenated buffer, blockIdx.y is the row group.  Every group's
+// region is zero-filled from its live count up to round_up(max live count over the launch's groups, 64): the weight-gradient
+// contraction gives every output tile the k-block count of the longest group, so the shorter groups must read zeros there
+// (the engine spaces the regions by at least that much).
+__global__ void __launch_bounds__(256) split_planes_grp_kernel(const float* __restrict__ A, int lda, int K, Planes dst, Grp grp, int want_lo) {
+  const int gi = blockIdx.y;
+  const int M = grp_count(grp, gi);
+  int mx = 0;
+#pragma unroll
+  for (int g = 0; g < kMaxGroups; ++g) {
+    const int c = g < grp.n ? (grp.cnt[g] ? *grp.cnt[g] : grp.hcnt[g]) : 0;
+    mx = c > mx ? c : mx;
+  }
+  const int Mfill = (mx + 63) & ~63;
+  const int r0 = pick(grp.roff, gi);
+  const int lane = threadIdx.x & 31;
+  for (int m = blockIdx.x * 8 + (threadIdx.x >> 5); m < Mfill; m += gridDim.x * 8) {
+    const float* row = A + (size_t)(r0 + m) * lda;
+    for (int k = lane * 4; k < K; k += 128) {
+      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (m < M) x = __ldg(reinterpret_cast<const float4*>(row + k));
+      planes_store4(dst, r0 + m, k, x, want_lo != 0);
+    }
+  }
+}
+
 // =================================================================================================== TMA-fed UMMA kernel
 // D[128 x BN] (+)= sum over reduction blocks of A_tile . B_tile^T, both operands arriving by TMA as 64x64 bf16 boxes of
 // (hi, lo) planes.  Operand orientation:
@@ -988,6 +1014,31 @@ static int tn_impl(int passes, const Planes* P, int p_col0, const Planes* Q, int
 int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q_col0, float* C, int ldc, int M_host, const int* M_dev, int NI,
                  int NJ, cudaStream_t st) {
   return tn_impl(passes, &P, p_col0, &Q, q_col0, nullptr, nullptr, C, ldc, M_host, M_dev, NI, NJ, st);
+}
+
+int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp& grp, bool want_lo, cudaStream_t st) {
+  PATHS_REQUIRE(dst.p && K % 4 == 0 && K <= dst.ldp && lda % 4 == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0,
+                "split_rows_grp: bad operands (K %d, ldp %d, lda %d)", K, dst.ldp, lda);
+  const int cap = grp_max_rows(grp);
+  if (cap <= 0) return 0;
+  int g = (cap + 64 + 7) / 8;
+  const int lim = grp.n > 1 ? 4 * kNumSMs : 16 * kNumSMs;
+  if (g > lim) g = lim;
+  split_planes_grp_kernel<<<dim3(g, grp.n), 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+// grouped contractions on pre-split operand planes (rows of the planes = global rows of the concatenated buffers)
+int gemm_nt_tc_grp_p(int passes, const Planes& A, const float* B, int ldb, int b_kn, float* C, int ldc, const GemmGrp& gg, int N, int K, int flags,
+                     cudaStream_t st) {
+  const int cap = grp_max_rows(gg.rows);
+  if (cap <= 0 || N <= 0) return 0;
+  return nt_impl(passes, &A, 0, nullptr, B, ldb, b_kn, C, ldc, nullptr, cap, nullptr, N, K, flags, st, &gg);
+}
+int gemm_tn_tc_grp_p(int passes, const Planes& P, const Planes& Q, int ldc, const GemmGrp& gg, int NI, int NJ, cudaStream_t st) {
+  const int cap = grp_max_rows(gg.rows);
+  if (cap <= 0 || NI <= 0 || NJ <= 0) return 0;
+  return tn_impl(passes, &P, 0, &Q, 0, nullptr, nullptr, nullptr, ldc, cap, nullptr, NI, NJ, st, &gg);
 }
 
 // ---- grouped forms: one launch for the same contraction of several row groups (levels) of concatenated activation buffers.
