@@ -42,7 +42,7 @@ bool gemm_tc_supported_nt_grp(const RowSrc& A, const float* B, int ldb, int N, i
 int gemm_nt_tc_grp(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, float* C, int ldc, const GemmGrp& gg, int N, int K, int flags,
                    cudaStream_t st);
 int gemm_tn_tc_grp(int passes, const float* P, int ldp, const RowSrc& Q, int ldc, const GemmGrp& gg, int NI, int NJ, cudaStream_t st);
-int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp& grp, bool want_lo, cudaStream_t st);
+int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp& grp, bool want_lo, const MutL* colsum, cudaStream_t st);
 int gemm_nt_tc_grp_p(int passes, const Planes& A, const float* B, int ldb, int b_kn, float* C, int ldc, const GemmGrp& gg, int N, int K, int flags,
                      cudaStream_t st);
 int gemm_tn_tc_grp_p(int passes, const Planes& P, const Planes& Q, int ldc, const GemmGrp& gg, int NI, int NJ, cudaStream_t st);
@@ -165,6 +165,7 @@ struct paths_engine {
   char* dec_tn_ws[PATHS_MAX_LEVELS]; size_t dec_tn_ws_bytes;   // ... of the decoder sets (one per concurrently running set)
   const float* dtok_base;                                // gradient w.r.t. the tokens, concatenated (one of lv[0].ga / lv[0].gt)
   bool stacked;                                          // decoder weights are packed as per-kind stacks over the levels
+  bool dec_planes;                                       // aggregator contractions on pre-split planes (PATHS_B200_DEC_NO_PLANES unsets)
   int S, Bs;                                             // row stride between the levels' regions: token-shaped / slide-shaped buffers
   Planes dplD[2], dplF[2], dpl3;                         // decoder operand planes (bf16 hi, lo) of width d, F, 3d over all L * S rows
   // level sets of the whole-step entry points: each set's aggregators run as one grouped pass on the set's own stream
@@ -517,13 +518,11 @@ inline GIdx noidx() { return gidx1(nullptr); }
 struct OpPl { Planes pl; bool ready; };
 inline OpPl oppl(const Planes& pl) { OpPl o; o.pl = pl; o.ready = false; return o; }
 inline bool dec_planes_on(const paths_engine* e) {
-  static const bool off = getenv("PATHS_B200_DEC_NO_PLANES") != nullptr;
-  return !off && e->dm.precision != PREC_FP32_SIMT && e->stacked && e->dplD[0].p != nullptr;
+  return e->dec_planes && e->dm.precision != PREC_FP32_SIMT && e->stacked && e->dplD[0].p != nullptr;
 }
-int ensure_split(paths_engine* e, const Grp& rows, const float* A, int lda, int K, OpPl* op, cudaStream_t st) {
+int ensure_split(paths_engine* e, const Grp& rows, const float* A, int lda, int K, OpPl* op, cudaStream_t st, const MutL* colsum = nullptr) {
   if (op->ready) return 0;
-  if (int r = split_rows_grp(A, lda, K, op->pl, rows, e->dm.precision == PREC_BF16X3_TC, st)) return r;
-  e->launches++;
+  if (int r = split_rows_grp(A, lda, K, op->pl, rows, e->dm.precision == PREC_BF16X3_TC, colsum, st)) return r;
   op->ready = true;
   return 0;
 }
@@ -536,6 +535,7 @@ int gemm_nt_set(paths_engine* e, const DecSet& S, const Grp& rows, const float* 
     GemmGrp gg;
     gg.rows = rows;
     for (int g = 0; g < kMaxGroups; ++g) { gg.wlev[g] = g < S.n ? S.lv[g] : 0; gg.bias[g] = bias.p[g]; gg.cout[g] = nullptr; }
+    if (!ap->ready) e->launches++;
     if (int r = ensure_split(e, rows, A, lda, K, ap, st)) return r;
     return gemm_nt_tc_grp_p(prec == PREC_BF16X3_TC ? 3 : 1, ap->pl, W(0), ldb, b_kn, C, ldc, gg, N, K, flags, st);
   }
@@ -562,6 +562,7 @@ int gemm_tn_set(paths_engine* e, const DecSet& S, const Grp& rows, const float* 
     GemmGrp gg;
     gg.rows = rows;
     for (int g = 0; g < kMaxGroups; ++g) { gg.wlev[g] = 0; gg.bias[g] = nullptr; gg.cout[g] = g < S.n ? const_cast<float*>(dW(S.lv[g])) : nullptr; }
+    e->launches += (pp->ready ? 0 : 1) + (qp->ready ? 0 : 1);
     if (int r = ensure_split(e, rows, P, ldp, NI, pp, st)) return r;
     if (int r = ensure_split(e, rows, Q, ldq, NJ, qp, st)) return r;
     return gemm_tn_tc_grp_p(prec == PREC_BF16X3_TC ? 3 : 1, pp->pl, qp->pl, ldc, gg, NI, NJ, st);
@@ -709,7 +710,12 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
     OpPl pA = oppl(e->dplD[0]), pHf = oppl(e->dplF[0]), pdHf = oppl(e->dplF[1]), pY2 = oppl(e->dplD[1]);
     RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).W2; }, F, 1, dHf, F, PL0(), F, d, 0, st, &pA));
     RUN(gemm_tn_set(e, S, gr, gA, d, y.Hf, F, [&](int l) { return Gl(l).W2; }, F, d, F, st, &pA, &pHf));
-    RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st));
+    if (dec_planes_on(e) && F % 8 == 0) {                  // masked gradient straight to operand planes (no fp32 write, no split pass)
+      RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st, &pdHf.pl, e->dm.precision == PREC_BF16X3_TC));
+      pdHf.ready = true;
+    } else {
+      RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st));
+    }
     RUN(gemm_tn_set(e, S, gr, dHf, F, y.y2, d, [&](int l) { return Gl(l).W1; }, d, F, d, st, &pdHf, &pY2));
     RUN(gemm_nt_set(e, S, gr, dHf, F, [&](int l) { return Wl(l).W1; }, d, 1, gA, d, PL0(), d, F, GEMM_ACCUM, st, &pdHf));     // gA = dy2
     // LN2 (cross-attention over an empty memory contributes only its output bias), then LN1
@@ -725,8 +731,11 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
         RUN(zero_rows(v0.dqkv + (size_t)S.gt.roff[g] * 3 * d, 3 * d, S.gt.hcnt[g], S.gt.cnt[g], 0, st));
     RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st));
     OpPl p3 = oppl(e->dpl3), pT = oppl(e->dplD[0]);
+    const MutL dbqkv = ML(S, [&](int l) { return Gl(l).bqkv; });
+    const bool fused_bias = dec_planes_on(e) && 3 * d <= 512 && d % 8 == 0;
+    if (fused_bias) RUN(ensure_split(e, S.gt, v0.dqkv, 3 * d, 3 * d, &p3, st, &dbqkv));      // split pass also sums the columns: d b_qkv
     RUN(gemm_tn_set(e, S, S.gt, v0.dqkv, 3 * d, t_in, d, [&](int l) { return Gl(l).Wqkv; }, d, 3 * d, d, st, &p3, &pT));
-    RUN(colsum_accum_grp(v0.dqkv, 3 * d, ML(S, [&](int l) { return Gl(l).bqkv; }), S.gt, 3 * d, st));
+    if (!fused_bias) RUN(colsum_accum_grp(v0.dqkv, 3 * d, dbqkv, S.gt, 3 * d, st));
     if (last) {
       RUN(gemm_nt_set(e, S, S.gt, v0.dqkv, 3 * d, [&](int l) { return Wl(l).Wqkv; }, d, 1, gtk, d, PL0(), d, 3 * d, 0, st, &p3));
       RUN(scatter_add_rows_grp(gA, S.tsegI, gtk, d, S.gb, st));
@@ -906,6 +915,7 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
   carve(e, static_cast<char*>(workspace));
   e->ws_base = static_cast<char*>(workspace); e->ws_bytes = need;
   e->site_on = getenv("PATHS_B200_PROF_DUMP") != nullptr;
+  e->dec_planes = getenv("PATHS_B200_DEC_NO_PLANES") == nullptr;
   {
     // "012,34": comma-separated sets of level digits (PATHS_B200_DEC_SETS_FWD / _BWD); a forward set starts once the tokens of
     // its deepest level exist, backward sets are launched last-to-first.

@@ -178,7 +178,10 @@ __global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host,
 // region is zero-filled from its live count up to round_up(max live count over the launch's groups, 64): the weight-gradient
 // contraction gives every output tile the k-block count of the longest group, so the shorter groups must read zeros there
 // (the engine spaces the regions by at least that much).
-__global__ void __launch_bounds__(256) split_planes_grp_kernel(const float* __restrict__ A, int lda, int K, Planes dst, Grp grp, int want_lo) {
+// With `csum` the pass also accumulates the column sums of the live rows into csum.p[group] (K <= 512): the bias gradient
+// that would otherwise need its own pass over the same tensor.
+__global__ void __launch_bounds__(256) split_planes_grp_kernel(const float* __restrict__ A, int lda, int K, Planes dst, Grp grp, int want_lo,
+                                                               MutL csum) {
   const int gi = blockIdx.y;
   const int M = grp_count(grp, gi);
   int mx = 0;
@@ -190,12 +193,42 @@ __global__ void __launch_bounds__(256) split_planes_grp_kernel(const float* __re
   const int Mfill = (mx + 63) & ~63;
   const int r0 = pick(grp.roff, gi);
   const int lane = threadIdx.x & 31;
+  float* cs = pick(csum.p, gi);
+  float4 acc[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int m = blockIdx.x * 8 + (threadIdx.x >> 5); m < Mfill; m += gridDim.x * 8) {
     const float* row = A + (size_t)(r0 + m) * lda;
-    for (int k = lane * 4; k < K; k += 128) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = lane * 4 + 128 * j;
+      if (k < K) {
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m < M) x = __ldg(reinterpret_cast<const float4*>(row + k));
+        planes_store4(dst, r0 + m, k, x, want_lo != 0);
+        acc[j].x += x.x; acc[j].y += x.y; acc[j].z += x.z; acc[j].w += x.w;
+      }
+    }
+    for (int k = lane * 4 + 512; k < K; k += 128) {        // wider rows (no column sums there)
       float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
       if (m < M) x = __ldg(reinterpret_cast<const float4*>(row + k));
       planes_store4(dst, r0 + m, k, x, want_lo != 0);
+    }
+  }
+  if (cs == nullptr) return;                               // block-uniform
+  __shared__ float4 part[8][128];
+  const int w = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) part[w][lane + 32 * j] = acc[j];
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int j = threadIdx.x >> 5, ln = threadIdx.x & 31;
+    const int k = ln * 4 + 128 * j;                          // column of part[*][threadIdx.x]
+    if (k < K) {
+      float4 t = part[0][threadIdx.x];
+#pragma unroll
+      for (int ww = 1; ww < 8; ++ww) { const float4 u = part[ww][threadIdx.x]; t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+      atomicAdd(cs + k, t.x); atomicAdd(cs + k + 1, t.y); atomicAdd(cs + k + 2, t.z); atomicAdd(cs + k + 3, t.w);
     }
   }
 }
@@ -1016,7 +1049,8 @@ int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q
   return tn_impl(passes, &P, p_col0, &Q, q_col0, nullptr, nullptr, C, ldc, M_host, M_dev, NI, NJ, st);
 }
 
-int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp& grp, bool want_lo, cudaStream_t st) {
+int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp& grp, bool want_lo, const MutL* colsum, cudaStream_t st) {
+  PATHS_REQUIRE(colsum == nullptr || K <= 512, "split_rows_grp: column sums need K <= 512 (K %d)", K);
   PATHS_REQUIRE(dst.p && K % 4 == 0 && K <= dst.ldp && lda % 4 == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0,
                 "split_rows_grp: bad operands (K %d, ldp %d, lda %d)", K, dst.ldp, lda);
   const int cap = grp_max_rows(grp);
@@ -1024,7 +1058,8 @@ int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp&
   int g = (cap + 64 + 7) / 8;
   const int lim = grp.n > 1 ? 4 * kNumSMs : 16 * kNumSMs;
   if (g > lim) g = lim;
-  split_planes_grp_kernel<<<dim3(g, grp.n), 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0);
+  if (colsum && g > kNumSMs) g = kNumSMs;                    // fewer blocks: fewer same-address atomics at the end
+  split_planes_grp_kernel<<<dim3(g, grp.n), 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, colsum ? *colsum : mutl1(nullptr));
   PATHS_LAUNCH_CK();
   return 0;
 }

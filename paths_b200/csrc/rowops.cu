@@ -611,23 +611,41 @@ __global__ void __launch_bounds__(TPB) ln_bwd_kernel(const float* __restrict__ d
 // dH *= (H > 0); optionally dbias[c] += sum_m dH[m, c] in the same pass (the bias gradient of the layer that fed the ReLU).
 // ld % 4 == 0; a thread keeps one float4 column group and walks rows, so the column sums need one shared-memory combine
 // and one atomic per column per block.
-__global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, int ld, Grp grp, MutL dbiasl) {
+// With `outp` the masked gradient is written as tensor-core operand planes (global rows of the concatenated buffer, zero rows
+// up to round_up(longest group, 64) like split_planes_grp_kernel) instead of back to dH: its only consumers are contractions.
+__global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, int ld, Grp grp, MutL dbiasl,
+                                                       Planes outp, int want_lo) {
   const int M = grp_count(grp, blockIdx.y);
-  dH += (size_t)pick(grp.roff, blockIdx.y) * ld; H += (size_t)pick(grp.roff, blockIdx.y) * ld;
+  const int r0 = pick(grp.roff, blockIdx.y);
+  dH += (size_t)r0 * ld; H += (size_t)r0 * ld;
   float* dbias = pick(dbiasl.p, blockIdx.y);
+  int Mfill = M;
+  if (outp.p) {
+    int mx = 0;
+#pragma unroll
+    for (int g = 0; g < kMaxGroups; ++g) {
+      const int c = g < grp.n ? (grp.cnt[g] ? *grp.cnt[g] : grp.hcnt[g]) : 0;
+      mx = c > mx ? c : mx;
+    }
+    Mfill = (mx + 63) & ~63;
+  }
   const int ngrp = ld >> 2;                               // float4 groups per row
   const int rpb = 256 / ngrp > 0 ? 256 / ngrp : 1;        // rows per block iteration (ld <= 1024)
   const int g = threadIdx.x % ngrp, rsub = threadIdx.x / ngrp;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   if (rsub < rpb) {
 #pragma unroll 4
-    for (int m = blockIdx.x * rpb + rsub; m < M; m += gridDim.x * rpb) {
-      float4* dp = reinterpret_cast<float4*>(dH + (size_t)m * ld) + g;
-      const float4 h = __ldg(reinterpret_cast<const float4*>(H + (size_t)m * ld) + g);
-      float4 v = *dp;
-      v.x = h.x > 0.f ? v.x : 0.f; v.y = h.y > 0.f ? v.y : 0.f; v.z = h.z > 0.f ? v.z : 0.f; v.w = h.w > 0.f ? v.w : 0.f;
-      *dp = v;
-      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    for (int m = blockIdx.x * rpb + rsub; m < Mfill; m += gridDim.x * rpb) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (m < M) {
+        float4* dp = reinterpret_cast<float4*>(dH + (size_t)m * ld) + g;
+        const float4 h = __ldg(reinterpret_cast<const float4*>(H + (size_t)m * ld) + g);
+        v = *dp;
+        v.x = h.x > 0.f ? v.x : 0.f; v.y = h.y > 0.f ? v.y : 0.f; v.z = h.z > 0.f ? v.z : 0.f; v.w = h.w > 0.f ? v.w : 0.f;
+        if (!outp.p) *dp = v;
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      if (outp.p) planes_store4(outp, r0 + m, 4 * g, v, want_lo != 0);
     }
   }
   if (!dbias) return;
@@ -907,7 +925,7 @@ int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rs
   return ln_bwd_grp(dy, dy2, xhat, rstd, ptrl1(gamma), dx, gidx1(didx), accum, mutl1(dgamma), mutl1(dbeta), mutl1(dbias), d,
                     grp_single(M_host, M_dev), st);
 }
-int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st) {
+int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st, const Planes* outp, int want_lo) {
   const int cap = grp_max_rows(grp);
   if (cap <= 0) return 0;
   PATHS_REQUIRE(ld % 4 == 0 && ld <= 1024, "relu_bwd: row width %d unsupported (multiple of 4, <= 1024)", ld);
@@ -915,13 +933,14 @@ int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& 
   int g = (cap + rpb - 1) / rpb;
   const int lim = grp.n > 1 ? kNumSMs : 2 * kNumSMs;
   if (g > lim) g = lim;
-  relu_bwd_kernel<<<dim3(g, grp.n), 256, 0, st>>>(dH, H, ld, grp, dbias);
+  PATHS_REQUIRE(outp == nullptr || (outp->p && ld <= outp->ldp), "relu_bwd: output planes narrower than the rows");
+  relu_bwd_kernel<<<dim3(g, grp.n), 256, 0, st>>>(dH, H, ld, grp, dbias, outp ? *outp : no_planes(), want_lo);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, float* dbias, cudaStream_t st) {
   PATHS_REQUIRE(M_extra == 0, "relu_bwd: M_extra is no longer supported");
-  return relu_bwd_grp(dH, H, ld, grp_single(M_host, M_dev), mutl1(dbias), st);
+  return relu_bwd_grp(dH, H, ld, grp_single(M_host, M_dev), mutl1(dbias), st, nullptr, 0);
 }
 int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
   if (M_host + M_extra <= 0) return 0;

@@ -54,7 +54,8 @@ int res_ln_fwd_grp(const float* res, const GIdx& ridx, const float* add, const P
                    float* xhat, float* rstd, int d, float eps, const Grp& grp, cudaStream_t st);
 int ln_bwd_grp(const float* dy, const float* dy2, const float* xhat, const float* rstd, const PtrL& gamma, float* dx, const GIdx& didx, int accum,
                const MutL& dgamma, const MutL& dbeta, const MutL& dbias, int d, const Grp& grp, cudaStream_t st);
-int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st);
+int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st, const Planes* outp = nullptr,
+                 int want_lo = 0);
 int scatter_add_rows_grp(const float* src, const GIdx& idx, float* dst, int d, const Grp& grp, cudaStream_t st);
 int special_grad_grp(const float* dtok, const GIdx& seg, const MutL& dspecial, int d, int B, int ngroups, cudaStream_t st);
 int colsum_accum_grp(const float* X, int ld, const MutL& out, const Grp& grp, int N, cudaStream_t st);

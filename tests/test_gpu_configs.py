@@ -9,7 +9,7 @@ import torch
 
 from oracle import paths_oracle as po
 from paths_b200 import synth
-from tests.common import BASE_CONFIG, product_model, product_batch, rel_err
+from tests.common import BASE_CONFIG, product_model, product_batch, rel_err, load_fixture, fixture_inputs, product_config
 from tests.parity_check import check_against_oracle
 
 pytestmark = pytest.mark.gpu
@@ -158,3 +158,37 @@ def test_cfg4_20k_patch_bag_properties():
     assert rel_err(alone[0]["alpha"][:n0], a) < 1e-6
     assert torch.equal(alone[1]["xy"], xy1)
     assert rel_err(alone["hz"][0], mixed["hz"][0]) < 1e-5
+
+
+@pytest.mark.parametrize("prec", [1, 2])
+def test_level_sets_and_operand_paths_agree(prec, monkeypatch):
+    """The aggregators of any grouping of the levels (one grouped pass, the default split, one pass per level) and both operand
+    paths of their contractions (pre-split planes over TMA / in-kernel conversion) compute the same step: hazards bit-identical
+    or within float re-association, gradients within 1e-5 of each other (they differ only in summation order)."""
+    from paths_b200.utils import inference_end2end
+    fx = load_fixture("brca_b4")
+    ocfg, sd, slides, ybin, cens = fixture_inputs(fx)
+    results = []
+    for env in ({}, {"PATHS_B200_DEC_SETS_FWD": "01234", "PATHS_B200_DEC_SETS_BWD": "01234"},
+                {"PATHS_B200_DEC_SETS_FWD": "0,1,2,3,4", "PATHS_B200_DEC_SETS_BWD": "0,1,2,3,4"},
+                {"PATHS_B200_DEC_SETS_FWD": "01,234", "PATHS_B200_DEC_SETS_BWD": "0,1234", "PATHS_B200_DEC_NO_PLANES": "1"},
+                {"PATHS_B200_DEC_NO_PLANES": "1"}):
+        for k in ("PATHS_B200_DEC_SETS_FWD", "PATHS_B200_DEC_SETS_BWD", "PATHS_B200_DEC_NO_PLANES"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)                        # read when the engine is created
+        cfg = product_config(fx)
+        model = product_model(cfg, sd)
+        model.runtime().set_precision(prec)
+        batch, _ = product_batch(cfg, model, slides)
+        hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+        loss.backward()
+        torch.cuda.synchronize()
+        results.append((hz.detach().clone(), {n: p.grad.detach().clone() for n, p in model.named_parameters() if p.grad is not None}))
+    hz0, g0 = results[0]
+    tol = 1e-5 if prec == 1 else 2e-3                       # bf16 mode: the two operand paths round at different points
+    for hz, g in results[1:]:
+        assert rel_err(hz, hz0) < tol
+        assert g.keys() == g0.keys()
+        for n in g0:
+            assert rel_err(g[n], g0[n]) < tol, n
