@@ -49,6 +49,7 @@ int gemm_tn_tc_grp_p(int passes, const Planes& P, const Planes& Q, int ldc, cons
 size_t packed_bytes(int R, int Cc);
 int register_packed(const float* src, int R, int Cc, int ld, void* dst, int nstack);
 void unregister_packed(const float* src);
+const void* packed_dst_of(const float* src);
 int build_pack_jobs(const float* const* srcs, int n, void* jobs_dev, int* n_jobs, cudaStream_t st);
 int run_pack_jobs(const void* jobs_dev, int n_jobs, cudaStream_t st);
 size_t pack_job_bytes();
@@ -882,6 +883,9 @@ int do_loss(paths_engine* e, const int32_t* ybin, const int32_t* cens, float sca
 // ---- C ABI ---------------------------------------------------------------------------------------------------
 extern "C" {
 
+static int register_weights(paths_engine_t* e);
+static int ensure_registry(paths_engine_t* e, cudaStream_t st);
+
 const char* paths_last_error(void) { return paths::g_err; }
 int paths_abi_version(void) { return PATHS_ABI_VERSION; }
 
@@ -1018,21 +1022,17 @@ void paths_engine_destroy(paths_engine_t* e) {
 
 int paths_engine_refresh_weights(paths_engine_t* e, void* stream) {
   PATHS_REQUIRE(e && e->have_params, "refresh_weights: engine has no parameters bound");
+  if (int r = ensure_registry(e, static_cast<cudaStream_t>(stream))) return r;
   if (e->dm.precision == PREC_FP32_SIMT) return 0;
   if (int r = run_pack_jobs(e->pack_jobs, e->n_pack_jobs, static_cast<cudaStream_t>(stream))) return r;
   e->launches++;
   return 0;
 }
 
-int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grads, int64_t n_floats, const int64_t* h_offsets,
-                             const float* div) {
-  PATHS_REQUIRE(e && params && h_offsets && div, "null argument");
-  bind(e->P, params, h_offsets, e->dm);
-  if (grads) bind(e->Gr, grads, h_offsets, e->dm);
-  e->grads_base = grads;
-  e->grads_floats = (size_t)n_floats;
+// (Re-)registers every contracted weight of the engine with the tensor-core path: the registry then resolves those weight
+// pointers to THIS engine's packed arena.
+static int register_weights(paths_engine_t* e) {
   {
-    // (re-)register every contracted weight with the tensor-core path
     for (const float* src : e->packed_srcs) unregister_packed(src);
     e->packed_srcs.clear();
     const paths_dims_t& dm = e->dm;
@@ -1092,8 +1092,35 @@ int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grad
     }
     if (rc) return rc;
     PATHS_REQUIRE((size_t)(cur - e->packed_arena) <= e->packed_arena_bytes, "packed-weight arena overrun");
-    if (int r = build_pack_jobs(e->packed_srcs.data(), (int)e->packed_srcs.size(), e->pack_jobs, &e->n_pack_jobs, 0)) return r;
   }
+  return 0;
+}
+
+// Several engines may be bound to the same parameters (the step engine, per-level engines of the level API, engines of other
+// batch sizes); the weight registry is keyed by the weight pointer, so the engine bound last owns it.  Every entry point that
+// launches contractions first makes sure the registry points into ITS arena -- re-registering and re-packing if another
+// engine took over (or was destroyed) in the meantime -- so an engine never contracts against another engine's stale copy.
+static int ensure_registry(paths_engine_t* e, cudaStream_t st) {
+  if (!e->have_params || e->packed_srcs.empty()) return 0;
+  const char* dst = static_cast<const char*>(packed_dst_of(e->packed_srcs[0]));
+  if (dst && dst >= e->packed_arena && dst < e->packed_arena + e->packed_arena_bytes) return 0;
+  if (int r = register_weights(e)) return r;
+  if (e->dm.precision != PREC_FP32_SIMT) {
+    if (int r = run_pack_jobs(e->pack_jobs, e->n_pack_jobs, st)) return r;
+    e->launches++;
+  }
+  return 0;
+}
+
+int paths_engine_bind_params(paths_engine_t* e, const float* params, float* grads, int64_t n_floats, const int64_t* h_offsets,
+                             const float* div) {
+  PATHS_REQUIRE(e && params && h_offsets && div, "null argument");
+  bind(e->P, params, h_offsets, e->dm);
+  if (grads) bind(e->Gr, grads, h_offsets, e->dm);
+  e->grads_base = grads;
+  e->grads_floats = (size_t)n_floats;
+  if (int r = register_weights(e)) return r;
+  if (int r = build_pack_jobs(e->packed_srcs.data(), (int)e->packed_srcs.size(), e->pack_jobs, &e->n_pack_jobs, 0)) return r;
   e->div = div;
   e->have_params = true;
   return 0;
@@ -1108,17 +1135,20 @@ int paths_engine_bind_store(paths_engine_t* e, const paths_store_t* h_store) {
 
 int paths_engine_begin(paths_engine_t* e, const int32_t* slide_ids, void* stream) {
   PATHS_REQUIRE(e, "null engine");
+  if (int r = ensure_registry(e, static_cast<cudaStream_t>(stream))) return r;
   return do_begin(e, slide_ids, nullptr, 0, static_cast<cudaStream_t>(stream));
 }
 
 int paths_engine_begin_padded(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, void* stream) {
   PATHS_REQUIRE(e && fts_padded, "null argument");
+  if (int r = ensure_registry(e, static_cast<cudaStream_t>(stream))) return r;
   return do_begin(e, slide_ids, fts_padded, N, static_cast<cudaStream_t>(stream));
 }
 
 int paths_engine_level_forward(paths_engine_t* e, int level, void* stream) {
   PATHS_REQUIRE(e && e->have_params, "level_forward: engine has no parameters bound");
   PATHS_REQUIRE(level >= 0 && level < e->dm.L, "level %d out of range", level);
+  if (int r = ensure_registry(e, static_cast<cudaStream_t>(stream))) return r;
   return level_forward(e, level, static_cast<cudaStream_t>(stream));
 }
 
@@ -1135,6 +1165,7 @@ int paths_engine_loss(paths_engine_t* e, const int32_t* ybin, const int32_t* cen
 int paths_engine_level_backward(paths_engine_t* e, int level, int use_dlogits, void* stream) {
   PATHS_REQUIRE(e && e->have_params && e->grads_base, "level_backward: no gradient buffer bound");
   PATHS_REQUIRE(level >= 0 && level < e->dm.L, "level %d out of range", level);
+  if (int r = ensure_registry(e, static_cast<cudaStream_t>(stream))) return r;
   return level_backward(e, level, use_dlogits, static_cast<cudaStream_t>(stream));
 }
 
@@ -1165,6 +1196,7 @@ static int forward_impl(paths_engine_t* e, const int32_t* slide_ids, const float
                         const int32_t* censored, float scale, int with_loss, void* stream) {
   PATHS_REQUIRE(e && e->have_params, "forward: engine has no parameters bound");
   cudaStream_t caller = static_cast<cudaStream_t>(stream);
+  if (int r = ensure_registry(e, caller)) return r;
   cudaStream_t st = caller;
   const int L = e->dm.L;
   const bool conc = use_side_streams(e);
@@ -1211,6 +1243,7 @@ static int forward_impl(paths_engine_t* e, const int32_t* slide_ids, const float
 int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream) {
   PATHS_REQUIRE(e && e->have_params && e->grads_base, "backward: no gradient buffer bound");
   cudaStream_t caller = static_cast<cudaStream_t>(stream);
+  if (int r = ensure_registry(e, caller)) return r;
   const int L = e->dm.L;
   if (!use_side_streams(e)) {
     if (zero_grads) PATHS_CK(cudaMemsetAsync(e->grads_base, 0, e->grads_floats * sizeof(float), caller));

@@ -838,6 +838,14 @@ int register_packed(const float* src, int R, int Cc, int ld, void* dst, int nsta
   return 0;
 }
 
+// where the registry currently keeps the packed copy of `src` (nullptr: not registered)
+const void* packed_dst_of(const float* src) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (const Packed& p : g_packed)
+    if (p.src == src) return p.dst;
+  return nullptr;
+}
+
 void unregister_packed(const float* src) {
   std::lock_guard<std::mutex> lk(g_mu);
   for (auto it = g_packed.begin(); it != g_packed.end();)

@@ -102,3 +102,29 @@ def test_device_prefetcher_same_results_as_host_batches():
         assert torch.equal(hz.detach(), hz0) and torch.equal(loss.detach(), loss0)
         n += 1
     assert n == 3
+
+
+def test_engines_sharing_parameters_never_use_stale_packed_weights():
+    """The step engine and a level-API engine are bound to the same parameters and share the packed-weight registry.  After
+    the level engine took the registry over and the weights changed, the step engine must re-pack and contract against its own
+    copy: its result equals that of a fresh model built from the updated weights."""
+    from paths_b200.data_utils.patch_batch import from_batch
+    from paths_b200.utils import inference_end2end
+    cfg, model, batch = _setup("brca_b4")
+    keys = ("fts", "locs", "parent_inds", "ctx_patch", "ctx_slide", "num_ims")
+    with torch.no_grad():
+        inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)          # step engine packs
+        model(0, from_batch({k: batch[k].clone() for k in keys}, "cuda"))                                       # level engine registers
+        for p in model.parameters():
+            p.mul_(0.9)
+        hz1, loss1 = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+        out_level = model(0, from_batch({k: batch[k].clone() for k in keys}, "cuda"))
+        sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+    fx = load_fixture("brca_b4")
+    fresh = product_model(product_config(fx), sd)
+    with torch.no_grad():
+        batch2, _ = product_batch(cfg, fresh, fixture_inputs(fx)[2])
+        hz2, loss2 = inference_end2end(cfg.num_levels, cfg.top_k_patches, fresh, cfg.base_power, batch2, cfg.task)
+        out_level2 = fresh(0, from_batch({k: batch2[k].clone() for k in keys}, "cuda"))
+    assert torch.equal(hz1, hz2) and torch.equal(loss1, loss2)
+    assert torch.equal(out_level["importance"], out_level2["importance"])
