@@ -116,6 +116,7 @@ struct Level {
   float *A1, *Fo;                                        // forward temporaries [tokens, d]
   float *A1b, *Fob;                                      // ... and their [B, d] counterparts (last layer: special-token rows only)
   float *ga, *gb, *gO, *gt, *dqkv, *dHf, *Dvec;          // backward, token-shaped
+  float* Dvecb;                                          // dO.O of the single-query (last) layer, slide-shaped
   float *gab, *gbb, *gOb, *dHfb;                         // backward, slide-shaped (last layer)
   float *dFl, *dy3s;                                     // [B, d]: d loss / d F_l, gradient entering the last decoder layer
 };
@@ -169,6 +170,8 @@ struct paths_engine {
   bool dec_planes;                                       // aggregator contractions on pre-split planes (PATHS_B200_DEC_NO_PLANES unsets)
   int S, Bs;                                             // row stride between the levels' regions: token-shaped / slide-shaped buffers
   Planes dplD[2], dplF[2], dpl3;                         // decoder operand planes (bf16 hi, lo) of width d, F, 3d over all L * S rows
+  Planes dplDb[2], dplFb[2];                             // ... and for the slide-shaped operands of the last layer (L * Bs rows): the two
+                                                         // row spaces overlap, and level sets run concurrently on different streams
   // level sets of the whole-step entry points: each set's aggregators run as one grouped pass on the set's own stream
   int n_fsets, n_bsets;
   int fset_n[PATHS_MAX_LEVELS], fset_lv[PATHS_MAX_LEVELS][PATHS_MAX_LEVELS];
@@ -232,6 +235,7 @@ size_t carve(paths_engine* e, char* base) {
   cat_tok(d, &Level::A1); cat_tok(d, &Level::Fo); cat_b(d, &Level::A1b); cat_b(d, &Level::Fob);
   cat_tok(d, &Level::ga); cat_tok(d, &Level::gb); cat_tok(d, &Level::gO); cat_tok(d, &Level::gt);
   cat_tok(3 * d, &Level::dqkv); cat_tok(F, &Level::dHf); cat_tok(dm.heads, &Level::Dvec);
+  cat_b(dm.heads, &Level::Dvecb);
   cat_b(d, &Level::gab); cat_b(d, &Level::gbb); cat_b(d, &Level::gOb); cat_b(F, &Level::dHfb);
   cat_b(d, &Level::dFl); cat_b(d, &Level::dy3s);
   {
@@ -244,6 +248,13 @@ size_t carve(paths_engine* e, char* base) {
     e->dplD[0] = want ? mk(d) : no_planes(); e->dplD[1] = want ? mk(d) : no_planes();
     e->dplF[0] = want ? mk(F) : no_planes(); e->dplF[1] = want ? mk(F) : no_planes();
     e->dpl3 = want ? mk(3 * d) : no_planes();
+    auto mkb = [&](int cols) {
+      Planes pl = planes_at(b.take<char>(planes_bytes(dm.L * Bs, cols)), dm.L * Bs, cols);
+      if (!base) pl.p = nullptr;
+      return pl;
+    };
+    e->dplDb[0] = want ? mkb(d) : no_planes(); e->dplDb[1] = want ? mkb(d) : no_planes();
+    e->dplFb[0] = want ? mkb(F) : no_planes(); e->dplFb[1] = want ? mkb(F) : no_planes();
   }
   {
     const int dec_shapes[][2] = {{3 * d, d}, {d, d}, {F, d}, {d, F}};
@@ -598,7 +609,9 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
     const Grp& gr = last ? S.gb : S.gt;
     float* A1 = last ? v0.A1b : v0.A1;
     float* Fo = last ? v0.Fob : v0.Fo;
-    OpPl pT = oppl(e->dplD[0]), pO = oppl(e->dplD[1]), pY2 = oppl(e->dplD[0]), pHf = oppl(e->dplF[0]);
+    // (the last layer's slide-shaped operands have their own plane buffers: their rows alias token rows of other levels)
+    OpPl pT = oppl(e->dplD[0]), pO = oppl(last ? e->dplDb[1] : e->dplD[1]), pY2 = oppl(last ? e->dplDb[0] : e->dplD[0]),
+         pHf = oppl(last ? e->dplFb[0] : e->dplF[0]);
     RUN(gemm_nt_set(e, S, S.gt, t_in, d, [&](int l) { return P[l].layer[j].Wqkv; }, d, 0, y.qkv, 3 * d,
                     PL(S, [&](int l) { return P[l].layer[j].bqkv; }), 3 * d, d, 0, st, &pT));
     RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st));
@@ -708,7 +721,8 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
     RUN(ln_bwd_grp(dy3, nullptr, y.xh3, y.rs3, PL(S, [&](int l) { return Wl(l).n3w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n3w; }),
                    ML(S, [&](int l) { return Gl(l).n3b; }), ML(S, [&](int l) { return Gl(l).b2; }), d, gr, st));
     // operand planes: each tensor is split once and feeds both the data-gradient and the weight-gradient contraction
-    OpPl pA = oppl(e->dplD[0]), pHf = oppl(e->dplF[0]), pdHf = oppl(e->dplF[1]), pY2 = oppl(e->dplD[1]);
+    OpPl pA = oppl(last ? e->dplDb[0] : e->dplD[0]), pHf = oppl(last ? e->dplFb[0] : e->dplF[0]),
+         pdHf = oppl(last ? e->dplFb[1] : e->dplF[1]), pY2 = oppl(last ? e->dplDb[1] : e->dplD[1]);
     RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).W2; }, F, 1, dHf, F, PL0(), F, d, 0, st, &pA));
     RUN(gemm_tn_set(e, S, gr, gA, d, y.Hf, F, [&](int l) { return Gl(l).W2; }, F, d, F, st, &pA, &pHf));
     if (dec_planes_on(e) && F % 8 == 0) {                  // masked gradient straight to operand planes (no fp32 write, no split pass)
@@ -724,13 +738,13 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
                    ML(S, [&](int l) { return Gl(l).n2b; }), ML(S, [&](int l) { return Gl(l).bcross; }), d, gr, st));
     RUN(ln_bwd_grp(gB, nullptr, y.xh1, y.rs1, PL(S, [&](int l) { return Wl(l).n1w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n1w; }),
                    ML(S, [&](int l) { return Gl(l).n1b; }), ML(S, [&](int l) { return Gl(l).bo; }), d, gr, st));      // gA = da
-    OpPl pA2 = oppl(e->dplD[0]), pO = oppl(e->dplD[1]);
+    OpPl pA2 = oppl(last ? e->dplDb[0] : e->dplD[0]), pO = oppl(last ? e->dplDb[1] : e->dplD[1]);
     RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).Wo; }, d, 1, gO, d, PL0(), d, d, 0, st, &pA2));
     RUN(gemm_tn_set(e, S, gr, gA, d, y.O, d, [&](int l) { return Gl(l).Wo; }, d, d, d, st, &pA2, &pO));
     if (last && !attn_bwd_writes_all(d, dm.heads))
       for (int g = 0; g < S.n; ++g)
         RUN(zero_rows(v0.dqkv + (size_t)S.gt.roff[g] * 3 * d, 3 * d, S.gt.hcnt[g], S.gt.cnt[g], 0, st));
-    RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st));
+    RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, last ? v0.Dvecb : v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st));
     OpPl p3 = oppl(e->dpl3), pT = oppl(e->dplD[0]);
     const MutL dbqkv = ML(S, [&](int l) { return Gl(l).bqkv; });
     const bool fused_bias = dec_planes_on(e) && 3 * d <= 512 && d % 8 == 0;

@@ -128,3 +128,23 @@ def test_engines_sharing_parameters_never_use_stale_packed_weights():
         out_level2 = fresh(0, from_batch({k: batch2[k].clone() for k in keys}, "cuda"))
     assert torch.equal(hz1, hz2) and torch.equal(loss1, loss2)
     assert torch.equal(out_level["importance"], out_level2["importance"])
+
+
+def test_step_is_reproducible():
+    """Level sets run concurrently on engine-owned streams: repeated steps on the same batch must give the same loss bit for
+    bit (forward has no atomics) and gradients equal up to the order of the fp32 atomics of the LayerNorm / bias sums."""
+    from paths_b200.utils import inference_end2end
+    cfg, model, batch = _setup("brca_b4")
+    ref_loss, ref_g = None, None
+    for it in range(8):
+        for p in model.parameters():
+            p.grad = None
+        hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+        loss.backward()
+        torch.cuda.synchronize()
+        g = model.runtime().layout.gflat.clone()
+        if ref_loss is None:
+            ref_loss, ref_g = loss.detach().clone(), g
+        else:
+            assert torch.equal(loss.detach(), ref_loss), it
+            assert rel_err(g, ref_g) < 1e-5, it
