@@ -227,9 +227,11 @@ def main():
             if world > 1:
                 dist.all_reduce(gflat)
             losses.append(float(loss.item()))
+        e2e_losses.extend(losses)
         return losses
 
     host_ms = [0.0]
+    e2e_losses = []
 
     def timed(fn, steps, warmup, profile=False, multi=False):
         if multi:
@@ -276,6 +278,7 @@ def main():
 
     ms, launches, clocks = timed(step_resident, args.steps, args.warmup, profile=True)
     host_enqueue_ms = host_ms[0]
+    loss_resident = float(eng.buffer(0, "LOSS").item())       # read after the timed region
     over, need = eng.overflowed()
     assert not over, f"row capacity overflow ({need})"
     counts = eng.counts()
@@ -337,6 +340,13 @@ def main():
         cpu = {"value": rate, "unit": "slides/s", "cores": cores, "kind": "port",
                "sample": "16 BRCA-shaped slides per step, fwd+bwd, 2 timed steps after 1 warm-up (oracle/paths_oracle.py, torch CPU)"}
 
+    # full-size consistency (no oracle at this size): the resident path (features gathered from the HBM store) and the
+    # end-to-end path (the same features arriving as the padded host batch) must compute the same loss, step after step
+    consistency = None
+    if e2e_losses:
+        consistency = {"loss_resident": loss_resident, "loss_e2e": e2e_losses[-1],
+                       "rel_diff": abs(e2e_losses[-1] - loss_resident) / max(abs(loss_resident), 1e-30),
+                       "e2e_step_spread": max(e2e_losses) - min(e2e_losses)}
     if rank == 0:
         rows = sum(counts)
         line = {
@@ -346,7 +356,7 @@ def main():
             "config": {"workload": WORKLOAD, "slides_per_gpu": B, "global_batch": B * world, "levels": Lv, "top_k": 20,
                        "packed_rows_per_step_per_gpu": rows, "rows_per_level": counts, "parallelism": f"dp{world}",
                        "l2": "per-step working set (activations ~3 GB, pyramids 16 GB) far exceeds the 126 MB L2"},
-            "host_enqueue_ms_per_step": host_enqueue_ms, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "fast_mode": fast, "gpu_launches": launches, "clocks": clocks,
+            "host_enqueue_ms_per_step": host_enqueue_ms, "consistency": consistency, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "fast_mode": fast, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line), file=_OUT, flush=True)
     if os.environ.get("PATHS_B200_PROF_DUMP"):               # developer aid: per-call-site timings are written at engine destruction
