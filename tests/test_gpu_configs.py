@@ -192,3 +192,16 @@ def test_level_sets_and_operand_paths_agree(prec, monkeypatch):
         assert g.keys() == g0.keys()
         for n in g0:
             assert rel_err(g[n], g0[n]) < tol, n
+
+
+def test_cfg3_training_parity_96_slides():
+    """BRCA-shaped survival training step (fwd+bwd) on 96 slides in the default tensor-core mode: large enough for the
+    slide-shaped regions (96 -> 128-row stride) to overlap several levels' token regions in the shared scratch buffers, with
+    the level sets running concurrently -- values and every live gradient against the oracle."""
+    cfg = _config()
+    sd = _weights(cfg)
+    slides = synth.make_brca_batch(range(96), cfg.num_levels, cfg.model_config.patch_embed_dim)
+    ybin, cens = _labels(slides)
+    model, rt, hz, loss = _run(cfg, sd, slides, 1, grad=True)
+    ocfg = po.OracleConfig.from_config(cfg)
+    check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, 1)
