@@ -155,7 +155,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=os.environ.get("PATHS_B200_PRECISION", "bf16x3"), choices=["fp32", "bf16x3", "bf16"])
-    ap.add_argument("--slides-per-gpu", type=int, default=512)
+    ap.add_argument("--slides-per-gpu", type=int, default=672)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fast-mode", action="store_true")
