@@ -172,6 +172,11 @@ struct paths_engine {
   Planes dplD[2], dplF[2], dpl3;                         // decoder operand planes (bf16 hi, lo) of width d, F, 3d over all L * S rows
   Planes dplDb[2], dplFb[2];                             // ... and for the slide-shaped operands of the last layer (L * Bs rows): the two
                                                          // row spaces overlap, and level sets run concurrently on different streams
+  // operand planes of the forward pass's saved activations (layer input, attention output, FFN input, FFN hidden), kept for the
+  // backward pass: its weight-gradient contractions read them as they are instead of splitting the fp32 tensors again
+  Planes svT[PATHS_MAX_LAYERS], svO[PATHS_MAX_LAYERS], svY2[PATHS_MAX_LAYERS], svHf[PATHS_MAX_LAYERS];
+  int sv_prec[PATHS_MAX_LEVELS];                         // precision the level's saved planes were written in (-1: none)
+  unsigned sv_set[PATHS_MAX_LEVELS];                     // levels of the forward set that wrote them (its zero-fill covers their longest)
   // level sets of the whole-step entry points: each set's aggregators run as one grouped pass on the set's own stream
   int n_fsets, n_bsets;
   int fset_n[PATHS_MAX_LEVELS], fset_lv[PATHS_MAX_LEVELS][PATHS_MAX_LEVELS];
@@ -255,6 +260,13 @@ size_t carve(paths_engine* e, char* base) {
     };
     e->dplDb[0] = want ? mkb(d) : no_planes(); e->dplDb[1] = want ? mkb(d) : no_planes();
     e->dplFb[0] = want ? mkb(F) : no_planes(); e->dplFb[1] = want ? mkb(F) : no_planes();
+    for (int j = 0; j < PATHS_MAX_LAYERS; ++j) {
+      const bool on = want && j < dm.layers, tk = j != dm.layers - 1;
+      e->svT[j] = on ? mk(d) : no_planes();
+      e->svO[j] = on ? (tk ? mk(d) : mkb(d)) : no_planes();
+      e->svY2[j] = on ? (tk ? mk(d) : mkb(d)) : no_planes();
+      e->svHf[j] = on ? (tk ? mk(F) : mkb(F)) : no_planes();
+    }
   }
   {
     const int dec_shapes[][2] = {{3 * d, d}, {d, d}, {F, d}, {d, F}};
@@ -602,6 +614,9 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
   Level& v0 = e->lv[0];                                  // base pointers of the concatenated buffers
   const LevelP* P = e->P.level;
   ProfScope ps_dec(e, PATHS_PROF_DEC_FWD, st);
+  unsigned set_mask = 0;
+  for (int g = 0; g < S.n; ++g) set_mask |= 1u << S.lv[g];
+  for (int g = 0; g < S.n; ++g) { e->sv_prec[S.lv[g]] = dec_planes_on(e) ? dm.precision : -1; e->sv_set[S.lv[g]] = set_mask; }
   const float* t_in = v0.tok;
   for (int j = 0; j < dm.layers; ++j) {
     LayerBuf& y = v0.layer[j];
@@ -610,8 +625,7 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
     float* A1 = last ? v0.A1b : v0.A1;
     float* Fo = last ? v0.Fob : v0.Fo;
     // (the last layer's slide-shaped operands have their own plane buffers: their rows alias token rows of other levels)
-    OpPl pT = oppl(e->dplD[0]), pO = oppl(last ? e->dplDb[1] : e->dplD[1]), pY2 = oppl(last ? e->dplDb[0] : e->dplD[0]),
-         pHf = oppl(last ? e->dplFb[0] : e->dplF[0]);
+    OpPl pT = oppl(e->svT[j]), pO = oppl(e->svO[j]), pY2 = oppl(e->svY2[j]), pHf = oppl(e->svHf[j]);
     RUN(gemm_nt_set(e, S, S.gt, t_in, d, [&](int l) { return P[l].layer[j].Wqkv; }, d, 0, y.qkv, 3 * d,
                     PL(S, [&](int l) { return P[l].layer[j].bqkv; }), 3 * d, d, 0, st, &pT));
     RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st));
@@ -700,6 +714,11 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
   const LevelP* P = e->P.level;
   const LevelP* G = e->Gr.level;
   ProfScope ps_dec(e, PATHS_PROF_DEC_BWD, st);
+  // the forward pass left its operand planes, zero-filled to the longest level of ITS set: usable when this set is inside it
+  bool saved = dec_planes_on(e);
+  unsigned set_mask = 0;
+  for (int g = 0; g < S.n; ++g) set_mask |= 1u << S.lv[g];
+  for (int g = 0; g < S.n; ++g) saved = saved && e->sv_prec[S.lv[g]] == dm.precision && (set_mask & ~e->sv_set[S.lv[g]]) == 0;
   // ---- final LayerNorm at the special tokens
   RUN(ln_bwd_grp(v0.dFl, nullptr, v0.xhf, v0.rsf, PL(S, [&](int l) { return P[l].nfw; }), v0.dy3s, noidx(), 0,
                  ML(S, [&](int l) { return G[l].nfw; }), ML(S, [&](int l) { return G[l].nfb; }), ML0(), d, S.gb, st));
@@ -721,8 +740,9 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
     RUN(ln_bwd_grp(dy3, nullptr, y.xh3, y.rs3, PL(S, [&](int l) { return Wl(l).n3w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n3w; }),
                    ML(S, [&](int l) { return Gl(l).n3b; }), ML(S, [&](int l) { return Gl(l).b2; }), d, gr, st));
     // operand planes: each tensor is split once and feeds both the data-gradient and the weight-gradient contraction
-    OpPl pA = oppl(last ? e->dplDb[0] : e->dplD[0]), pHf = oppl(last ? e->dplFb[0] : e->dplF[0]),
-         pdHf = oppl(last ? e->dplFb[1] : e->dplF[1]), pY2 = oppl(last ? e->dplDb[1] : e->dplD[1]);
+    OpPl pA = oppl(last ? e->dplDb[0] : e->dplD[0]), pHf = oppl(saved ? e->svHf[j] : last ? e->dplFb[0] : e->dplF[0]),
+         pdHf = oppl(last ? e->dplFb[1] : e->dplF[1]), pY2 = oppl(saved ? e->svY2[j] : last ? e->dplDb[1] : e->dplD[1]);
+    pHf.ready = pY2.ready = saved;
     RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).W2; }, F, 1, dHf, F, PL0(), F, d, 0, st, &pA));
     RUN(gemm_tn_set(e, S, gr, gA, d, y.Hf, F, [&](int l) { return Gl(l).W2; }, F, d, F, st, &pA, &pHf));
     if (dec_planes_on(e) && F % 8 == 0) {                  // masked gradient straight to operand planes (no fp32 write, no split pass)
@@ -738,14 +758,16 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
                    ML(S, [&](int l) { return Gl(l).n2b; }), ML(S, [&](int l) { return Gl(l).bcross; }), d, gr, st));
     RUN(ln_bwd_grp(gB, nullptr, y.xh1, y.rs1, PL(S, [&](int l) { return Wl(l).n1w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n1w; }),
                    ML(S, [&](int l) { return Gl(l).n1b; }), ML(S, [&](int l) { return Gl(l).bo; }), d, gr, st));      // gA = da
-    OpPl pA2 = oppl(last ? e->dplDb[0] : e->dplD[0]), pO = oppl(last ? e->dplDb[1] : e->dplD[1]);
+    OpPl pA2 = oppl(last ? e->dplDb[0] : e->dplD[0]), pO = oppl(saved ? e->svO[j] : last ? e->dplDb[1] : e->dplD[1]);
+    pO.ready = saved;
     RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).Wo; }, d, 1, gO, d, PL0(), d, d, 0, st, &pA2));
     RUN(gemm_tn_set(e, S, gr, gA, d, y.O, d, [&](int l) { return Gl(l).Wo; }, d, d, d, st, &pA2, &pO));
     if (last && !attn_bwd_writes_all(d, dm.heads))
       for (int g = 0; g < S.n; ++g)
         RUN(zero_rows(v0.dqkv + (size_t)S.gt.roff[g] * 3 * d, 3 * d, S.gt.hcnt[g], S.gt.cnt[g], 0, st));
     RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, last ? v0.Dvecb : v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st));
-    OpPl p3 = oppl(e->dpl3), pT = oppl(e->dplD[0]);
+    OpPl p3 = oppl(e->dpl3), pT = oppl(saved ? e->svT[j] : e->dplD[0]);
+    pT.ready = saved;
     const MutL dbqkv = ML(S, [&](int l) { return Gl(l).bqkv; });
     const bool fused_bias = dec_planes_on(e) && 3 * d <= 512 && d % 8 == 0;
     if (fused_bias) RUN(ensure_split(e, S.gt, v0.dqkv, 3 * d, 3 * d, &p3, st, &dbqkv));      // split pass also sums the columns: d b_qkv
@@ -934,6 +956,7 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
   e->ws_base = static_cast<char*>(workspace); e->ws_bytes = need;
   e->site_on = getenv("PATHS_B200_PROF_DUMP") != nullptr;
   e->dec_planes = getenv("PATHS_B200_DEC_NO_PLANES") == nullptr;
+  for (int l = 0; l < PATHS_MAX_LEVELS; ++l) { e->sv_prec[l] = -1; e->sv_set[l] = 0; }
   {
     // "012,34": comma-separated sets of level digits (PATHS_B200_DEC_SETS_FWD / _BWD); a forward set starts once the tokens of
     // its deepest level exist, backward sets are launched last-to-first.

@@ -172,6 +172,9 @@ def test_level_sets_and_operand_paths_agree(prec, monkeypatch):
     for env in ({}, {"PATHS_B200_DEC_SETS_FWD": "01234", "PATHS_B200_DEC_SETS_BWD": "01234"},
                 {"PATHS_B200_DEC_SETS_FWD": "0,1,2,3,4", "PATHS_B200_DEC_SETS_BWD": "0,1,2,3,4"},
                 {"PATHS_B200_DEC_SETS_FWD": "01,234", "PATHS_B200_DEC_SETS_BWD": "0,1234", "PATHS_B200_DEC_NO_PLANES": "1"},
+                # backward sets inside the forward sets reuse the forward pass's operand planes; sets that straddle them re-split
+                {"PATHS_B200_DEC_SETS_FWD": "01234", "PATHS_B200_DEC_SETS_BWD": "0,12,34"},
+                {"PATHS_B200_DEC_SETS_FWD": "01,234", "PATHS_B200_DEC_SETS_BWD": "0,1234"},
                 {"PATHS_B200_DEC_NO_PLANES": "1"}):
         for k in ("PATHS_B200_DEC_SETS_FWD", "PATHS_B200_DEC_SETS_BWD", "PATHS_B200_DEC_NO_PLANES"):
             monkeypatch.delenv(k, raising=False)
