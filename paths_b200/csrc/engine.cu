@@ -838,15 +838,15 @@ int lstm_backward(paths_engine* e, int l, cudaStream_t st) {
   RUN(gemm_nt_act(prec, aUV, p.Wuv, D, 1, e->dY, D, nullptr, M, Md, D, I + d, 0, st));
   RUN(gemm_tn_act(prec, aUV, aY, nullptr, W_(g.Wuv), D, M, Md, I + d, D, st));
   // ---- state gradients arriving from the children of this level's selected rows
-  if (has_children)
-    RUN(parent_sum(v.child_of, e->lv[l + 1].dHrow, e->lv[l + 1].dCrow, e->dHc, e->dCc, D, C, M, Md, st));
-  // ---- LSTM cell (the pointwise kernels also accumulate the bias gradients of mem_to_out and of the four gates)
-  RUN(lstm_point2_bwd(e->dY, has_children ? e->dHc : nullptr, v.Pt, v.G, pl ? nullptr : e->dP, pl ? e->dPP : none, pl ? nullptr : e->dG,
+  // ---- LSTM cell (the pointwise kernels sum the state gradients of a row's children (slide.py:318-329) as they read them, and
+  //      accumulate the bias gradients of mem_to_out and of the four gates)
+  const int* kids = has_children ? v.child_of : nullptr;
+  RUN(lstm_point2_bwd(e->dY, has_children ? e->lv[l + 1].dHrow : nullptr, kids, v.Pt, v.G, pl ? nullptr : e->dP, pl ? e->dPP : none, pl ? nullptr : e->dG,
                       pl ? e->dGP : none, W_(e->Gr.bmo), W_(e->Gr.bg) + 3 * C, lo, D, C, M, Md, st));
   const Act aP = act(e->dP, D, pl ? e->dPP : none), aCn = act(v.Cn, C, pl ? v.CnP : none);
   RUN(gemm_nt_act(prec, aP, e->P.Wmo, C, 1, e->dCn, C, nullptr, M, Md, C, D, 0, st));
   RUN(gemm_tn_act(prec, aP, aCn, nullptr, W_(e->Gr.Wmo), C, M, Md, D, C, st));
-  RUN(lstm_point1_bwd(e->dCn, has_children ? e->dCc : nullptr, v.G, has_parent ? e->lv[l - 1].Cn : nullptr,
+  RUN(lstm_point1_bwd(e->dCn, has_children ? e->lv[l + 1].dCrow : nullptr, kids, v.G, has_parent ? e->lv[l - 1].Cn : nullptr,
                       has_parent ? v.row_parent : nullptr, pl ? nullptr : e->dG, pl ? e->dGP : none, has_parent ? v.dCrow : nullptr,
                       W_(e->Gr.bg), lo, D, C, M, Md, st));
   const Act aG = act(e->dG, ldg, pl ? e->dGP : none);

@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(TPB) lstm_point1_fwd_kernel(float* __restrict_
 }
 
 // t = tanh(P), h' = o * t, Y = X + h'                       (interface.py:56, paths.py:89)
-__global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(float* __restrict__ Pt, const float* __restrict__ G,
+__global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(const float* __restrict__ Pt, const float* __restrict__ G,
                                                               const float* __restrict__ X, float* __restrict__ H,
                                                               float* __restrict__ Y, Planes YP, int want_lo, int D, int C, int M_host,
                                                               const int* M_dev) {
@@ -91,9 +91,8 @@ __global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(float* __restrict_
     for (int j4 = lane; j4 < D / 4; j4 += 32) {
       const int j = 4 * j4;
       if (m >= M) { planes_store4(YP, m, j, make_float4(0.f, 0.f, 0.f, 0.f), want_lo); continue; }
-      float4 t = ld4(Pt + (size_t)m * D + j);
+      float4 t = ld4(Pt + (size_t)m * D + j);                // P stays as it is: the backward kernel takes tanh again (4 KB/row less)
       t.x = tanhf(t.x); t.y = tanhf(t.y); t.z = tanhf(t.z); t.w = tanhf(t.w);
-      st4(Pt + (size_t)m * D + j, t);
       const float4 o = ld4(G + (size_t)m * ldg + 3 * C + j), x = ld4(X + (size_t)m * D + j);
       const float4 h = make_float4(o.x * t.x, o.y * t.y, o.z * t.z, o.w * t.w);
       st4(H + (size_t)m * D + j, h);
@@ -107,7 +106,10 @@ __global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(float* __restrict_
 // dH = dY + dHc;  dP = dH*o*(1-t^2), dGo = dH*t*o*(1-o);  column sums of both (the bias gradients of mem_to_out and of the
 // output gate) are accumulated on the way.  Threads own float4 column groups, blocks stride over rows.
 constexpr int CG = 4;                                     // float4 column groups per thread: D <= 4 * 4 * 256
+//   child_of != nullptr: dHc is the CHILD level's per-row gradient table and row m adds the rows child_of[4m .. 4m+3] (>= 0) in
+//   that order -- the child -> parent sum of parent_sum_kernel without the [M, D] round trip through HBM.
 __global__ void __launch_bounds__(256) lstm_point2_bwd_kernel(const float* __restrict__ dY, const float* __restrict__ dHc,
+                                                              const int* __restrict__ child_of,
                                                               const float* __restrict__ Pt, const float* __restrict__ G,
                                                               float* __restrict__ dP, Planes dPP, float* __restrict__ dG, Planes dGP,
                                                               float* __restrict__ db_mo, float* __restrict__ db_o, int want_lo, int D, int C,
@@ -119,6 +121,8 @@ __global__ void __launch_bounds__(256) lstm_point2_bwd_kernel(const float* __res
 #pragma unroll
   for (int q = 0; q < CG; ++q) aP[q] = aG[q] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int m = blockIdx.x; m < Mw; m += gridDim.x) {
+    int ch[4] = {-1, -1, -1, -1};
+    if (child_of && m < M) { const int4 c4 = __ldg(reinterpret_cast<const int4*>(child_of) + m); ch[0] = c4.x; ch[1] = c4.y; ch[2] = c4.z; ch[3] = c4.w; }
 #pragma unroll
     for (int q = 0; q < CG; ++q) {
       const int j = 4 * (threadIdx.x + 256 * q);
@@ -126,8 +130,16 @@ __global__ void __launch_bounds__(256) lstm_point2_bwd_kernel(const float* __res
       float4 vp = make_float4(0.f, 0.f, 0.f, 0.f), vg = vp;
       if (m < M) {
         float4 dh = dY ? ld4(dY + (size_t)m * D + j) : make_float4(0.f, 0.f, 0.f, 0.f);
-        if (dHc) { const float4 e = ld4(dHc + (size_t)m * D + j); dh.x += e.x; dh.y += e.y; dh.z += e.z; dh.w += e.w; }
-        const float4 t = ld4(Pt + (size_t)m * D + j), o = ld4(G + (size_t)m * ldg + 3 * C + j);
+        if (dHc && child_of) {
+          float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (ch[k] >= 0) { const float4 u = ld4(dHc + (size_t)ch[k] * D + j); e.x += u.x; e.y += u.y; e.z += u.z; e.w += u.w; }
+          dh.x += e.x; dh.y += e.y; dh.z += e.z; dh.w += e.w;
+        } else if (dHc) { const float4 e = ld4(dHc + (size_t)m * D + j); dh.x += e.x; dh.y += e.y; dh.z += e.z; dh.w += e.w; }
+        float4 t = ld4(Pt + (size_t)m * D + j);
+        t.x = tanhf(t.x); t.y = tanhf(t.y); t.z = tanhf(t.z); t.w = tanhf(t.w);
+        const float4 o = ld4(G + (size_t)m * ldg + 3 * C + j);
         vp = make_float4(dh.x * o.x * (1.f - t.x * t.x), dh.y * o.y * (1.f - t.y * t.y), dh.z * o.z * (1.f - t.z * t.z),
                          dh.w * o.w * (1.f - t.w * t.w));
         vg = make_float4(dh.x * t.x * o.x * (1.f - o.x), dh.y * t.y * o.y * (1.f - o.y), dh.z * t.z * o.z * (1.f - o.z),
@@ -153,6 +165,7 @@ __global__ void __launch_bounds__(256) lstm_point2_bwd_kernel(const float* __res
 // dc' = dCn + dCc;  df, dr, dm -> dG[:, :3C] (+ their column sums -> gate bias gradients);  dCrow = dc' * f (gradient w.r.t. the
 // inherited c of this row).  A block covers 256 / (C/4) rows at a time; thread = (row slot, float4 column group).
 __global__ void __launch_bounds__(256) lstm_point1_bwd_kernel(const float* __restrict__ dCn, const float* __restrict__ dCc,
+                                                              const int* __restrict__ child_of,
                                                               const float* __restrict__ G, const float* __restrict__ Cprev,
                                                               const int* __restrict__ parent, float* __restrict__ dG, Planes dGP,
                                                               float* __restrict__ dCrow, float* __restrict__ db_g, int want_lo, int D, int C,
@@ -171,7 +184,15 @@ __global__ void __launch_bounds__(256) lstm_point1_bwd_kernel(const float* __res
         const float* g = G + (size_t)m * ldg;
         const int p = parent ? parent[m] : -1;
         float4 dc = ld4(dCn + (size_t)m * C + c);
-        if (dCc) { const float4 e = ld4(dCc + (size_t)m * C + c); dc.x += e.x; dc.y += e.y; dc.z += e.z; dc.w += e.w; }
+        if (dCc && child_of) {                                  // children's rows of the child level's dCrow, summed in index order
+          const int4 ch = __ldg(reinterpret_cast<const int4*>(child_of) + m);
+          float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (ch.x >= 0) { const float4 u = ld4(dCc + (size_t)ch.x * C + c); e.x += u.x; e.y += u.y; e.z += u.z; e.w += u.w; }
+          if (ch.y >= 0) { const float4 u = ld4(dCc + (size_t)ch.y * C + c); e.x += u.x; e.y += u.y; e.z += u.z; e.w += u.w; }
+          if (ch.z >= 0) { const float4 u = ld4(dCc + (size_t)ch.z * C + c); e.x += u.x; e.y += u.y; e.z += u.z; e.w += u.w; }
+          if (ch.w >= 0) { const float4 u = ld4(dCc + (size_t)ch.w * C + c); e.x += u.x; e.y += u.y; e.z += u.z; e.w += u.w; }
+          dc.x += e.x; dc.y += e.y; dc.z += e.z; dc.w += e.w;
+        } else if (dCc) { const float4 e = ld4(dCc + (size_t)m * C + c); dc.x += e.x; dc.y += e.y; dc.z += e.z; dc.w += e.w; }
         const float4 f = ld4(g + c), r = ld4(g + C + c), mm = ld4(g + 2 * C + c);
         const float4 cprev = (Cprev && p >= 0) ? ld4(Cprev + (size_t)p * C + c) : make_float4(0.f, 0.f, 0.f, 0.f);
         df = make_float4(dc.x * cprev.x * f.x * (1.f - f.x), dc.y * cprev.y * f.y * (1.f - f.y), dc.z * cprev.z * f.z * (1.f - f.z),
@@ -800,29 +821,29 @@ int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, 
   PATHS_LAUNCH_CK();
   return 0;
 }
-int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
+int lstm_point2_fwd(const float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
                     const int* M_dev, cudaStream_t st) {
   if (M_host <= 0) return 0;
   lstm_point2_fwd_kernel<<<row_grid(M_host + 64), TPB, 0, st>>>(Pt, G, X, H, Y, YP, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
-int lstm_point2_bwd(const float* dY, const float* dHc, const float* Pt, const float* G, float* dP, const Planes& dPP, float* dG,
-                    const Planes& dGP, float* db_mo, float* db_o, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+int lstm_point2_bwd(const float* dY, const float* dHc, const int* child_of, const float* Pt, const float* G, float* dP, const Planes& dPP,
+                    float* dG, const Planes& dGP, float* db_mo, float* db_o, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
   PATHS_REQUIRE(D <= 4 * CG * 256, "lstm backward: patch_embed_dim above %d unsupported", 4 * CG * 256);
   if (M_host <= 0) return 0;
   int g = M_host + 64; if (g > 3 * kNumSMs) g = 3 * kNumSMs;
-  lstm_point2_bwd_kernel<<<g, 256, 0, st>>>(dY, dHc, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
+  lstm_point2_bwd_kernel<<<g, 256, 0, st>>>(dY, dHc, child_of, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
-int lstm_point1_bwd(const float* dCn, const float* dCc, const float* G, const float* Cprev, const int* parent, float* dG, const Planes& dGP,
-                    float* dCrow, float* db_g, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
+int lstm_point1_bwd(const float* dCn, const float* dCc, const int* child_of, const float* G, const float* Cprev, const int* parent, float* dG,
+                    const Planes& dGP, float* dCrow, float* db_g, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
   PATHS_REQUIRE(C / 4 <= 256, "lstm backward: hierarchical_ctx_mlp_hidden_dim above 1024 unsupported");
   if (M_host <= 0) return 0;
   const int R = 256 / (C / 4);
   int g = (M_host + 64 + R - 1) / R; if (g > 3 * kNumSMs) g = 3 * kNumSMs;
-  lstm_point1_bwd_kernel<<<g, 256, 0, st>>>(dCn, dCc, G, Cprev, parent, dG, dGP, dCrow, db_g, want_lo, D, C, M_host, M_dev);
+  lstm_point1_bwd_kernel<<<g, 256, 0, st>>>(dCn, dCc, child_of, G, Cprev, parent, dG, dGP, dCrow, db_g, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
