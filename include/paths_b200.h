@@ -27,7 +27,7 @@ extern "C" {
 
 #define PATHS_MAX_LEVELS 8
 #define PATHS_MAX_LAYERS 4
-#define PATHS_ABI_VERSION 3
+#define PATHS_ABI_VERSION 4
 
 /* model_config + the train_config fields the hot path reads (config.py:19-79). */
 typedef struct paths_dims {
@@ -92,6 +92,7 @@ enum paths_buffer {
   PATHS_BUF_TOK, PATHS_BUF_Z, PATHS_BUF_F, PATHS_BUF_LOGITS,
   PATHS_BUF_HAZARDS, PATHS_BUF_LOSS, PATHS_BUF_DLOGITS, PATHS_BUF_OVERFLOW, PATHS_BUF_DF_IN, PATHS_BUF_DHROW, PATHS_BUF_DCROW,
   PATHS_BUF_LOSS_PER,
+  PATHS_BUF_HF0,              /* FFN hidden activations of the level's first aggregator layer, [tokens, 4 * trans_dim] */
   PATHS_BUF__COUNT
 };
 
@@ -146,6 +147,12 @@ int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream);
 
 int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, size_t* bytes);
 int paths_engine_set_precision(paths_engine_t* e, int precision);
+/* nn.Transformer(dropout=p) in training mode (model/aggregator.py:25-33, train.py:131): the aggregators of the NEXT forward
+ * pass (whole step or single level) drop attention probabilities, the three sublayer outputs and the FFN hidden activations
+ * with probability p and rescale the survivors by 1/(1-p); the matching backward pass repeats the decisions.  Decisions come
+ * from a counter-based hash of (seed, level, layer, site, token row, column) -- torch's generator stream is not reproducible
+ * -- so the caller passes a fresh seed per step.  p = 0 (the default, and model.eval()) switches dropout off. */
+int paths_engine_set_dropout(paths_engine_t* e, float p, uint64_t seed);
 /* number of kernel launches issued by this engine since creation (for bench.py's gpu_launches) */
 int64_t paths_engine_launch_count(paths_engine_t* e);
 

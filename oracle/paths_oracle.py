@@ -25,6 +25,7 @@ import math
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
+import numpy as np
 import torch
 import torch.nn.functional as F
 
@@ -121,8 +122,74 @@ def pe_1d(length: int, dim: int, dtype=torch.float32, k: float = 10000.0) -> Ten
     return pe
 
 
-def _mha_self(sd: Dict[str, Tensor], p: str, t: Tensor, key_pad: Tensor, nhead: int) -> Tensor:
-    """Self-attention of nn.MultiheadAttention (batch_first) with a key padding mask; dropout = 0."""
+# ---- dropout with explicit masks ---------------------------------------------------------------------------------
+# nn.Transformer(dropout=p) in training mode (model/aggregator.py:25-33; train.py:131) draws its masks from torch's
+# generator, which no other implementation can reproduce.  WHERE the masks act and how survivors are rescaled is
+# pinned against torch itself (tests/golden/make_golden_dropout.py records the masks torch drew and
+# tests/test_oracle_golden.py replays them through `decoder_stack`); WHICH elements are dropped is a convention of
+# the CUDA path -- a counter-based hash (paths_b200/csrc/common.cuh: drop_keep) that `HashDropout` restates.
+DROP_ATTN, DROP_SA_OUT, DROP_CROSS_OUT, DROP_FFN_INNER, DROP_FFN_OUT = range(5)
+
+
+def _fmix64(x: np.ndarray) -> np.ndarray:
+    x = np.asarray(x, dtype=np.uint64).copy()
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint64(33); x *= np.uint64(0xff51afd7ed558ccd)
+        x ^= x >> np.uint64(33); x *= np.uint64(0xc4ceb9fe1a85ec53)
+        x ^= x >> np.uint64(33)
+    return x
+
+
+class HashDropout:
+    """mask(level, layer, site, rows, cols) -> float32 array of {0, 1/(1-p)}: element (row, col) is kept iff
+    fmix64(site_key ^ (row << 32 | col)) >> 32 >= p * 2**32; `rows` are level-local packed token rows."""
+
+    def __init__(self, p: float, seed: int):
+        self.p = float(np.float32(p))
+        self.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+        t = float(np.float32(p)) * 4294967296.0
+        self.thresh = 0 if t <= 0 else 4294967295 if t >= 4294967295.0 else int(t)
+        self.inv_keep = np.float32(1.0) / (np.float32(1.0) - np.float32(p))
+
+    def site_key(self, level: int, layer: int, site: int) -> np.uint64:
+        with np.errstate(over="ignore"):
+            mult = np.uint64(0x9E3779B97F4A7C15) * np.uint64((level * 8 + layer) * 8 + site + 1)
+        return _fmix64(np.uint64(self.seed) ^ mult)
+
+    def mask(self, level: int, layer: int, site: int, rows: np.ndarray, cols: np.ndarray) -> Tensor:
+        key = self.site_key(level, layer, site)
+        h = _fmix64(key ^ ((rows.astype(np.uint64) << np.uint64(32)) | cols.astype(np.uint64))) >> np.uint64(32)
+        return torch.from_numpy(np.where(h >= np.uint64(self.thresh), self.inv_keep, np.float32(0.0)).astype(np.float32))
+
+    def elem(self, level: int, layer: int, site: int, rows: Tensor, width: int) -> Tensor:
+        """[B, T, width] mask of a sublayer output; rows: [B, T] packed token rows."""
+        r = rows.numpy().astype(np.uint64)[:, :, None]
+        return self.mask(level, layer, site, r, np.arange(width, dtype=np.uint64)[None, None, :])
+
+    def attn(self, level: int, layer: int, rows: Tensor, nhead: int) -> Tensor:
+        """[B, nhead, T, T] mask of the attention probabilities (query row, head << 24 | key index)."""
+        B, T = rows.shape
+        r = rows.numpy().astype(np.uint64)[:, None, :, None]
+        col = (np.arange(nhead, dtype=np.uint64)[None, :, None, None] << np.uint64(24)) | np.arange(T, dtype=np.uint64)[None, None, None, :]
+        return self.mask(level, layer, DROP_ATTN, r, col)
+
+
+class RecordedDropout:
+    """Masks recorded from torch (tests/golden/make_golden_dropout.py), replayed by site."""
+
+    def __init__(self, masks: Dict[Tuple[int, int, int], Tensor]):
+        self.masks = masks
+
+    def elem(self, level, layer, site, rows, width):
+        return self.masks[(level, layer, site)]
+
+    def attn(self, level, layer, rows, nhead):
+        return self.masks[(level, layer, DROP_ATTN)]
+
+
+def _mha_self(sd: Dict[str, Tensor], p: str, t: Tensor, key_pad: Tensor, nhead: int, amask: Optional[Tensor] = None) -> Tensor:
+    """Self-attention of nn.MultiheadAttention (batch_first) with a key padding mask; `amask` ([B, h, T, T] of
+    {0, 1/(1-p)}) is the dropout applied to the softmax probabilities (F.scaled_dot_product_attention's dropout_p)."""
     B, T, d = t.shape
     dh = d // nhead
     qkv = t @ sd[p + ".in_proj_weight"].t() + sd[p + ".in_proj_bias"]
@@ -133,27 +200,43 @@ def _mha_self(sd: Dict[str, Tensor], p: str, t: Tensor, key_pad: Tensor, nhead: 
     s = (q @ k.transpose(-1, -2)) / math.sqrt(dh)
     s = s.masked_fill(key_pad[:, None, None, :], float("-inf"))
     a = torch.softmax(s, dim=-1)
+    if amask is not None:
+        a = a * amask.to(a.dtype)
     o = (a @ v).transpose(1, 2).reshape(B, T, d)
     return o @ sd[p + ".out_proj.weight"].t() + sd[p + ".out_proj.bias"]
 
 
 def decoder_stack(sd: Dict[str, Tensor], prefix: str, t: Tensor, key_pad: Tensor, nhead: int, layers: int,
-                  eps: float = 1e-5) -> Tensor:
+                  eps: float = 1e-5, drop=None, level: int = 0, rows: Optional[Tensor] = None) -> Tensor:
     """What nn.Transformer(d, nhead, layers, layers, 4d, batch_first=True) computes for an EMPTY
     encoder input (model/paths.py:116, model/aggregator.py:25-33,70-72): post-norm decoder layers
-    whose cross-attention over zero keys yields exactly `multihead_attn.out_proj.bias`."""
+    whose cross-attention over zero keys yields exactly `multihead_attn.out_proj.bias`.
+    Training-mode dropout (`drop`: HashDropout / RecordedDropout) acts where nn.TransformerDecoderLayer applies it:
+    attention probabilities, dropout1(self-attn block), dropout2(cross-attn block = its bias), the FFN's inner
+    dropout after the ReLU, dropout3(FFN block) -- each block INCLUDING its output bias."""
     d = t.shape[-1]
     for j in range(layers):
         p = f"{prefix}.decoder.layers.{j}"
         ln = lambda x, n: F.layer_norm(x, (d,), sd[f"{p}.{n}.weight"], sd[f"{p}.{n}.bias"], eps)
-        t = ln(t + _mha_self(sd, p + ".self_attn", t, key_pad, nhead), "norm1")
-        t = ln(t + sd[p + ".multihead_attn.out_proj.bias"], "norm2")
-        ff = _lin(sd, p + ".linear2", torch.relu(_lin(sd, p + ".linear1", t)))
-        t = ln(t + ff, "norm3")
+        if drop is None:
+            t = ln(t + _mha_self(sd, p + ".self_attn", t, key_pad, nhead), "norm1")
+            t = ln(t + sd[p + ".multihead_attn.out_proj.bias"], "norm2")
+            ff = _lin(sd, p + ".linear2", torch.relu(_lin(sd, p + ".linear1", t)))
+            t = ln(t + ff, "norm3")
+            continue
+        m = lambda site, width: drop.elem(level, j, site, rows, width).to(t.dtype)
+        sa = _mha_self(sd, p + ".self_attn", t, key_pad, nhead, drop.attn(level, j, rows, nhead))
+        t = ln(t + sa * m(DROP_SA_OUT, d), "norm1")
+        cross = sd[p + ".multihead_attn.out_proj.bias"].expand_as(t)
+        t = ln(t + cross * m(DROP_CROSS_OUT, d), "norm2")
+        h = torch.relu(_lin(sd, p + ".linear1", t))
+        h = h * m(DROP_FFN_INNER, h.shape[-1])
+        ff = _lin(sd, p + ".linear2", h)
+        t = ln(t + ff * m(DROP_FFN_OUT, d), "norm3")
     return F.layer_norm(t, (d,), sd[prefix + ".decoder.norm.weight"], sd[prefix + ".decoder.norm.bias"], eps)
 
 
-def aggregate(sd: Dict[str, Tensor], cfg: OracleConfig, depth: int, tokens: Tensor, num_ims: Tensor) -> Tensor:
+def aggregate(sd: Dict[str, Tensor], cfg: OracleConfig, depth: int, tokens: Tensor, num_ims: Tensor, drop=None) -> Tensor:
     """model/aggregator.py:58-76: prepend the special token, mask padding keys, read token 0."""
     B, N, d = tokens.shape
     p = f"procs.{depth}.global_agg"
@@ -161,11 +244,15 @@ def aggregate(sd: Dict[str, Tensor], cfg: OracleConfig, depth: int, tokens: Tens
     seq = torch.cat((special, tokens), dim=1)
     lengths = num_ims + 1
     key_pad = torch.arange(N + 1)[None] >= lengths[:, None]             # utils.py:97-103
-    out = decoder_stack(sd, p + ".transformer", seq, key_pad, cfg.trans_heads, cfg.trans_layers)
+    # packed token row of padded position (b, t): slide b's tokens follow those of slides < b, special token first
+    tseg = torch.cumsum(lengths, 0) - lengths
+    rows = tseg[:, None] + torch.arange(N + 1)[None]
+    out = decoder_stack(sd, p + ".transformer", seq, key_pad, cfg.trans_heads, cfg.trans_layers, drop=drop, level=depth,
+                        rows=rows)
     return out[:, 0]
 
 
-def level_forward(sd: Dict[str, Tensor], cfg: OracleConfig, depth: int, batch: Dict[str, Tensor]) -> Dict[str, Tensor]:
+def level_forward(sd: Dict[str, Tensor], cfg: OracleConfig, depth: int, batch: Dict[str, Tensor], drop=None) -> Dict[str, Tensor]:
     """model/paths.py:66-146 on a padded batch (keys as data_utils/patch_batch.py:20-27)."""
     fts, locs, num_ims = batch["fts"], batch["locs"], batch["num_ims"]
     ctx_slide, ctx_patch = batch["ctx_slide"], batch["ctx_patch"]
@@ -203,7 +290,7 @@ def level_forward(sd: Dict[str, Tensor], cfg: OracleConfig, depth: int, batch: D
         tok = tok + pe_2d(pl[:, :, 0].reshape(-1), pl[:, :, 1].reshape(-1), d, fts.dtype).view(B, N, d)
     else:
         tok = tok + pe_1d(N, d, fts.dtype)[None]
-    slide_ft = aggregate(sd, cfg, depth, tok, num_ims)                      # paths.py:127
+    slide_ft = aggregate(sd, cfg, depth, tok, num_ims, drop)                    # paths.py:127
     if cfg.slide_ctx_mode == "residual" and ctx_slide.shape[1] > 0:         # paths.py:130-131
         slide_ft = slide_ft + ctx_slide[:, -1]
     pc = f"procs.{depth}.classification_layer"
@@ -323,7 +410,7 @@ class LevelRecord:
 def end2end(sd: Dict[str, Tensor], cfg: OracleConfig, slides: Sequence[Sequence[Tensor]],
             survival_bin: Optional[Tensor] = None, censored: Optional[Tensor] = None,
             subtype: Optional[Tensor] = None, dtype=torch.float32, record: bool = False,
-            forced_keep: Optional[List[List[Tensor]]] = None):
+            forced_keep: Optional[List[List[Tensor]]] = None, drop=None):
     """utils.py:228-279.  `slides[j]` is the list of L grids of slide j.  Returns (hazards|logits, loss,
     records).  `forced_keep[l][j]`, when given, replaces the top-K indices (teacher forcing for tests)."""
     sd = {k: v.to(dtype) if v.is_floating_point() else v for k, v in sd.items()}
@@ -331,7 +418,7 @@ def end2end(sd: Dict[str, Tensor], cfg: OracleConfig, slides: Sequence[Sequence[
     recs: List[LevelRecord] = []
     out = None
     for i in range(cfg.num_levels):
-        out = level_forward(sd, cfg, i, batch)
+        out = level_forward(sd, cfg, i, batch, drop)
         rec = LevelRecord(batch["num_ims"].clone(), batch["locs"].clone(), out["logits"], out["ctx_slide"],
                           out["importance"], out["ctx_patch"]) if record else None
         if i != cfg.num_levels - 1:
@@ -365,11 +452,11 @@ def end2end(sd: Dict[str, Tensor], cfg: OracleConfig, slides: Sequence[Sequence[
 
 
 def grads(sd: Dict[str, Tensor], cfg: OracleConfig, slides, survival_bin, censored, dtype=torch.float32,
-          forced_keep=None):
+          forced_keep=None, drop=None):
     """loss.backward() of train.py:65 on leaf copies of the state dict; returns (hazards, loss, grad dict).
     Parameters that the loss does not reach get None (the reference leaves .grad = None)."""
     leaf = {k: v.detach().to(dtype).clone().requires_grad_(True) for k, v in sd.items() if v.is_floating_point()}
     hz, loss, recs = end2end(leaf, cfg, slides, survival_bin, censored, dtype=dtype, record=True,
-                             forced_keep=forced_keep)
+                             forced_keep=forced_keep, drop=drop)
     loss.backward()
     return hz.detach(), loss.detach(), {k: (v.grad if v.grad is not None else None) for k, v in leaf.items()}, recs

@@ -20,21 +20,23 @@ constexpr int MAXDH = 64;
 
 // Virtual slide sv of a grouped launch = (group g = sv / B, slide s = sv % B): its tokens are rows roff[g] + seg[g][s] + s ...
 // of the concatenated qkv buffer, its compact (single-query) output row is oroff[g] + s.
-struct Seg { int t0, T, os; };
+struct Seg { int t0, T, os, g, r0; };            // (+ row group and its first row: dropout hashes level-local token rows)
 __device__ __forceinline__ Seg seg_of(const SegGrp& sg, int sv) {
   const int g = sv / sg.B, s = sv - g * sg.B;
   const int* seg = pick(sg.seg, g);
-  Seg r; r.t0 = pick(sg.roff, g) + seg[s] + s; r.T = seg[s + 1] - seg[s] + 1; r.os = pick(sg.oroff, g) + s;
+  Seg r; r.r0 = pick(sg.roff, g); r.g = g; r.t0 = r.r0 + seg[s] + s; r.T = seg[s + 1] - seg[s] + 1; r.os = pick(sg.oroff, g) + s;
   return r;
 }
 
 // out[q, h*dh + c] = sum_j softmax_j(scale * q.k_j) v_j[c];  lse[q, h] = logsumexp_j(scale * q.k_j)
 __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                            float* __restrict__ out, float* __restrict__ lse, int d, int heads,
-                                                           int nq_mode, int skip_T) {
+                                                           int nq_mode, int skip_T, const Drop dr) {
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
   if (sg.T <= skip_T) return;                        // short bags belong to the *_small kernels
+  const uint64_t dkey = pick(dr.key, sg.g);          // dropout of the attention probabilities (dr.thresh != 0): the normaliser
+                                                     // sums every probability, the value sum only the kept ones / (1 - p)
   const int nq = nq_mode ? 1 : sg.T;
   const int q0 = blockIdx.x * QB;
   if (q0 >= nq) return;
@@ -81,9 +83,12 @@ __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restri
       const float corr = expf(m[i] - mn);
       l[i] = l[i] * corr + warp_sum(p);
       oa[i] *= corr; ob[i] *= corr;
+      float pd = p;
+      if (dr.thresh)
+        pd = drop_keep(dkey, (uint32_t)(sg.t0 - sg.r0 + q0 + w * QW + i), ((uint32_t)h << 24) | (uint32_t)(k0 + lane), dr.thresh) ? p * dr.inv_keep : 0.f;
       const int jmax = min(KT, sg.T - k0);
       for (int j = 0; j < jmax; ++j) {
-        const float pj = __shfl_sync(0xffffffffu, p, j);
+        const float pj = __shfl_sync(0xffffffffu, pd, j);
         oa[i] = fmaf(pj, Vs[j][lane], oa[i]);
         if (dh > 32) ob[i] = fmaf(pj, Vs[j][lane + 32], ob[i]);
       }
@@ -107,10 +112,12 @@ __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restri
 __global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                               const float* __restrict__ out, const float* __restrict__ lse,
                                                               const float* __restrict__ dout, float* __restrict__ dqkv,
-                                                              float* __restrict__ Dvec, int d, int heads, int nq_mode, int skip_T) {
+                                                              float* __restrict__ Dvec, int d, int heads, int nq_mode, int skip_T,
+                                                              const Drop dr) {
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
   if (sg.T <= skip_T) return;
+  const uint64_t dkey = pick(dr.key, sg.g);
   const int nq = nq_mode ? 1 : sg.T;
   const int q0 = blockIdx.x * QB;
   if (q0 >= nq) return;
@@ -158,6 +165,8 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __res
         dp = fmaf(gc, Vs[lane][c], dp);
       }
       const float p = valid ? expf(sc - L[i]) : 0.f;
+      if (dr.thresh)                                       // d(kept probability) = dout.v / (1 - p), dropped ones get none
+        dp = drop_keep(dkey, (uint32_t)(sg.t0 - sg.r0 + q0 + w * QW + i), ((uint32_t)h << 24) | (uint32_t)(k0 + lane), dr.thresh) ? dp * dr.inv_keep : 0.f;
       const float ds = p * (dp - Dq[i]);
       const int jmax = min(KT, sg.T - k0);
       for (int j = 0; j < jmax; ++j) {
@@ -182,10 +191,11 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __res
 __global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                                const float* __restrict__ lse, const float* __restrict__ dout,
                                                                const float* __restrict__ Dvec, float* __restrict__ dqkv, int d,
-                                                               int heads, int nq_mode, int skip_T) {
+                                                               int heads, int nq_mode, int skip_T, const Drop dr) {
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
   if (sg.T <= skip_T) return;
+  const uint64_t dkey = pick(dr.key, sg.g);
   const int nq = nq_mode ? 1 : sg.T;
   const int j0 = blockIdx.x * QB;
   if (j0 >= sg.T) return;
@@ -239,10 +249,16 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __re
         dp = fmaf(vc, Gs[lane][c], dp);
       }
       const float p = valid ? expf(sc - Ls[lane]) : 0.f;
+      float pm = p;
+      if (dr.thresh) {
+        const bool keep = drop_keep(dkey, (uint32_t)(sg.t0 - sg.r0 + i0 + lane), ((uint32_t)h << 24) | (uint32_t)(j0 + w * QW + i), dr.thresh);
+        pm = keep ? p * dr.inv_keep : 0.f;
+        dp = keep ? dp * dr.inv_keep : 0.f;
+      }
       const float ds = p * (dp - Ds[lane]);
       const int imax = min(KT, nq - i0);
       for (int ii = 0; ii < imax; ++ii) {
-        const float pi = __shfl_sync(0xffffffffu, p, ii);
+        const float pi = __shfl_sync(0xffffffffu, pm, ii);
         const float dsi = __shfl_sync(0xffffffffu, ds, ii);
         dva[i] = fmaf(pi, Gs[ii][lane], dva[i]);
         dka[i] = fmaf(dsi, Qs[ii][lane], dka[i]);
@@ -907,11 +923,20 @@ int launch_bwd_small(const float* qkv, const SegGrp& seg, const float* out, cons
 int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st) {
   return attn_fwd_grp(qkv, seg_single(seg, B), out, lse, d, heads, max_T, nq_mode, st);
 }
-int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st) {
+int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st,
+                 const Drop* drop) {
   PATHS_REQUIRE(d % heads == 0 && d / heads <= MAXDH, "attention: head_dim %d unsupported (max %d)", d / heads, MAXDH);
   const int B = seg.n * seg.B;                       // virtual slides
   if (B <= 0) return 0;
   int skip_T = 0;
+  const Drop dr = drop ? *drop : no_drop();
+  if (dr.thresh) {                                   // probability dropout: the tiled kernels serve every bag length
+    PATHS_REQUIRE(max_T < (1 << 24) && heads < 256, "attention dropout: bag of %d tokens / %d heads outside the hash's index range", max_T, heads);
+    dim3 grid(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
+    attn_fwd_kernel<<<grid, AW * 32, 0, st>>>(qkv, seg, out, lse, d, heads, nq_mode, 0, dr);
+    PATHS_LAUNCH_CK();
+    return 0;
+  }
   if (d / heads == 32 && nq_mode) {
     attn_fwd_nq1_kernel<<<(B * heads + 3) / 4, 128, 0, st>>>(qkv, seg, out, lse, d, heads, B);
     PATHS_LAUNCH_CK();
@@ -944,7 +969,7 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
     skip_T = SMALL_MAX_T;
   }
   dim3 grid(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
-  attn_fwd_kernel<<<grid, AW * 32, 0, st>>>(qkv, seg, out, lse, d, heads, nq_mode, skip_T);
+  attn_fwd_kernel<<<grid, AW * 32, 0, st>>>(qkv, seg, out, lse, d, heads, nq_mode, skip_T, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -957,10 +982,20 @@ int attn_bwd(const float* qkv, const int* seg, const float* out, const float* ls
   return attn_bwd_grp(qkv, seg_single(seg, B), out, lse, dout, dqkv, Dvec, d, heads, max_T, nq_mode, st);
 }
 int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
-                 int heads, int max_T, int nq_mode, cudaStream_t st) {
+                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop) {
   const int B = seg.n * seg.B;
   if (B <= 0) return 0;
   int skip_T = 0;
+  const Drop dr = drop ? *drop : no_drop();
+  if (dr.thresh) {                                   // (with nq_mode the caller zero-fills dqkv: only query rows get a dq)
+    dim3 gq(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
+    attn_bwd_dq_kernel<<<gq, AW * 32, 0, st>>>(qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, nq_mode, 0, dr);
+    PATHS_LAUNCH_CK();
+    dim3 gk((max_T + QB - 1) / QB, heads, B);
+    attn_bwd_dkv_kernel<<<gk, AW * 32, 0, st>>>(qkv, seg, lse, dout, Dvec, dqkv, d, heads, nq_mode, 0, dr);
+    PATHS_LAUNCH_CK();
+    return 0;
+  }
   if (d / heads == 32 && nq_mode) {
     attn_bwd_nq1_kernel<<<(B * heads + 3) / 4, 128, 0, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, B);
     PATHS_LAUNCH_CK();
@@ -993,10 +1028,10 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
     skip_T = SMALL_MAX_T;
   }
   dim3 gq(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
-  attn_bwd_dq_kernel<<<gq, AW * 32, 0, st>>>(qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, nq_mode, skip_T);
+  attn_bwd_dq_kernel<<<gq, AW * 32, 0, st>>>(qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, nq_mode, skip_T, dr);
   PATHS_LAUNCH_CK();
   dim3 gk((max_T + QB - 1) / QB, heads, B);
-  attn_bwd_dkv_kernel<<<gk, AW * 32, 0, st>>>(qkv, seg, lse, dout, Dvec, dqkv, d, heads, nq_mode, skip_T);
+  attn_bwd_dkv_kernel<<<gk, AW * 32, 0, st>>>(qkv, seg, lse, dout, Dvec, dqkv, d, heads, nq_mode, skip_T, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }

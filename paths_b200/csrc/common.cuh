@@ -156,6 +156,33 @@ struct GemmGrp {
   float* cout[kMaxGroups];
 };
 
+// ---- dropout (nn.Transformer(dropout=p) in training mode, model/aggregator.py:25-33) ------------------------------------
+// torch's generator stream cannot be reproduced, so keep/drop decisions come from a counter-based hash: an element is kept
+// iff fmix64(site_key ^ (row << 32 | col)) >> 32 >= p * 2^32, where site_key mixes the step's seed with (level, layer, site),
+// `row` is the token's packed row inside its level and `col` the feature column (attention probabilities: head << 24 | key).
+// Forward and backward recompute the same decision; oracle/paths_oracle.py restates the hash to build explicit masks.
+enum DropSite { DROP_ATTN = 0, DROP_SA_OUT = 1, DROP_CROSS_OUT = 2, DROP_FFN_INNER = 3, DROP_FFN_OUT = 4 };
+__host__ __device__ __forceinline__ uint64_t fmix64(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+  return x;
+}
+inline uint64_t drop_site_key(uint64_t seed, int level, int layer, int site) {
+  return fmix64(seed ^ (0x9E3779B97F4A7C15ULL * (uint64_t)((level * 8 + layer) * 8 + site + 1)));
+}
+__device__ __forceinline__ bool drop_keep(uint64_t key, uint32_t row, uint32_t col, uint32_t thresh) {
+  return (uint32_t)(fmix64(key ^ (((uint64_t)row << 32) | col)) >> 32) >= thresh;
+}
+struct Drop {
+  uint32_t thresh;                   // 0: dropout off
+  float inv_keep;                    // 1 / (1 - p)
+  uint64_t key[kMaxGroups];          // site key of each row group (level)
+};
+inline Drop no_drop() { Drop d; d.thresh = 0; d.inv_keep = 1.f; for (int i = 0; i < kMaxGroups; ++i) d.key[i] = 0; return d; }
+inline uint32_t drop_thresh(float p) {
+  const double t = (double)p * 4294967296.0;
+  return t <= 0.0 ? 0u : t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+}
+
 // GEMM_GATES: the output is the LSTM gate pre-activation block [f | r | m | o] (widths C, C, C, D; C = flags >> 8): the
 // epilogue applies sigmoid / sigmoid / tanh / sigmoid by column range, so the gates reach HBM already activated.
 enum GemmFlags { GEMM_RELU = 1, GEMM_ACCUM = 2, GEMM_GATES = 4 };

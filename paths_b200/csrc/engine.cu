@@ -177,6 +177,10 @@ struct paths_engine {
   Planes svT[PATHS_MAX_LAYERS], svO[PATHS_MAX_LAYERS], svY2[PATHS_MAX_LAYERS], svHf[PATHS_MAX_LAYERS];
   int sv_prec[PATHS_MAX_LEVELS];                         // precision the level's saved planes were written in (-1: none)
   unsigned sv_set[PATHS_MAX_LEVELS];                     // levels of the forward set that wrote them (its zero-fill covers their longest)
+  // dropout of the aggregators (paths_engine_set_dropout): probability and seed of the NEXT forward pass; each level's forward
+  // pass records what it used so that its backward pass repeats the same keep/drop decisions
+  float drop_p; uint64_t drop_seed;
+  float lv_drop_p[PATHS_MAX_LEVELS]; uint64_t lv_drop_seed[PATHS_MAX_LEVELS];
   // level sets of the whole-step entry points: each set's aggregators run as one grouped pass on the set's own stream
   int n_fsets, n_bsets;
   int fset_n[PATHS_MAX_LEVELS], fset_lv[PATHS_MAX_LEVELS][PATHS_MAX_LEVELS];
@@ -606,6 +610,16 @@ int gemm_tn_set(paths_engine* e, const DecSet& S, const Grp& rows, const float* 
   return 0;
 }
 
+// keep/drop parameters of one dropout site of layer j for every level of the set (seeds as recorded by the levels' forward)
+Drop set_drop(const paths_engine* e, const DecSet& S, int j, int site) {
+  Drop dr = no_drop();
+  const float p = e->lv_drop_p[S.lv[0]];
+  dr.thresh = drop_thresh(p);
+  dr.inv_keep = 1.f / (1.f - p);
+  for (int g = 0; g < S.n; ++g) dr.key[g] = drop_site_key(e->lv_drop_seed[S.lv[g]], S.lv[g], j, site);
+  return dr;
+}
+
 // ---- part 2: transformer aggregator -- decoder layers over packed tokens, last layer evaluated at the special token only.
 // Reads only the set's tokens and writes only the set's rows of the decoder buffers (safe on the set's own stream).
 int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
@@ -617,6 +631,8 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
   unsigned set_mask = 0;
   for (int g = 0; g < S.n; ++g) set_mask |= 1u << S.lv[g];
   for (int g = 0; g < S.n; ++g) { e->sv_prec[S.lv[g]] = dec_planes_on(e) ? dm.precision : -1; e->sv_set[S.lv[g]] = set_mask; }
+  for (int g = 0; g < S.n; ++g) { e->lv_drop_p[S.lv[g]] = e->drop_p; e->lv_drop_seed[S.lv[g]] = e->drop_seed; }
+  const bool drop = e->drop_p > 0.f;                     // training-mode dropout at the five sites of nn.TransformerDecoderLayer
   const float* t_in = v0.tok;
   for (int j = 0; j < dm.layers; ++j) {
     LayerBuf& y = v0.layer[j];
@@ -628,18 +644,29 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
     OpPl pT = oppl(e->svT[j]), pO = oppl(e->svO[j]), pY2 = oppl(e->svY2[j]), pHf = oppl(e->svHf[j]);
     RUN(gemm_nt_set(e, S, S.gt, t_in, d, [&](int l) { return P[l].layer[j].Wqkv; }, d, 0, y.qkv, 3 * d,
                     PL(S, [&](int l) { return P[l].layer[j].bqkv; }), 3 * d, d, 0, st, &pT));
-    RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st));
+    const GIdx hrow = last ? S.tsegI : noidx();          // slide-shaped rows hash as their special token's row
+    const PtrL bo = PL(S, [&](int l) { return P[l].layer[j].bo; }), bcross = PL(S, [&](int l) { return P[l].layer[j].bcross; }),
+               b2 = PL(S, [&](int l) { return P[l].layer[j].b2; });
+    Drop dA;
+    if (drop) dA = set_drop(e, S, j, DROP_ATTN);
+    RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr));
     RUN(gemm_nt_set(e, S, gr, y.O, d, [&](int l) { return P[l].layer[j].Wo; }, d, 0, A1, d, PL0(), d, d, 0, st, &pO));
-    RUN(res_ln_fwd_grp(t_in, last ? S.tsegI : noidx(), A1, PL(S, [&](int l) { return P[l].layer[j].bo; }),
+    // dropout1(W_o a + b_o), dropout2(b_cross) and dropout3(W_2 h + b_2) are applied to the branch INCLUDING its bias before
+    // the residual sum; the cross-attention branch (a bias only) is materialised in Fo, free until the FFN writes it
+    if (drop) RUN(dropout_fwd_grp(A1, A1, d, bo, gr, hrow, set_drop(e, S, j, DROP_SA_OUT), st));
+    RUN(res_ln_fwd_grp(t_in, last ? S.tsegI : noidx(), A1, drop ? PL0() : bo,
                        PL(S, [&](int l) { return P[l].layer[j].n1w; }), PL(S, [&](int l) { return P[l].layer[j].n1b; }), y.y1, y.xh1, y.rs1, d,
                        1e-5f, gr, st));
-    RUN(res_ln_fwd_grp(y.y1, noidx(), nullptr, PL(S, [&](int l) { return P[l].layer[j].bcross; }),
+    if (drop) RUN(dropout_fwd_grp(nullptr, Fo, d, bcross, gr, hrow, set_drop(e, S, j, DROP_CROSS_OUT), st));
+    RUN(res_ln_fwd_grp(y.y1, noidx(), drop ? Fo : nullptr, drop ? PL0() : bcross,
                        PL(S, [&](int l) { return P[l].layer[j].n2w; }), PL(S, [&](int l) { return P[l].layer[j].n2b; }), y.y2, y.xh2, y.rs2, d,
                        1e-5f, gr, st));
     RUN(gemm_nt_set(e, S, gr, y.y2, d, [&](int l) { return P[l].layer[j].W1; }, d, 0, y.Hf, F, PL(S, [&](int l) { return P[l].layer[j].b1; }), F,
                     d, GEMM_RELU, st, &pY2));
+    if (drop) RUN(dropout_fwd_grp(y.Hf, y.Hf, F, PL0(), gr, hrow, set_drop(e, S, j, DROP_FFN_INNER), st));
     RUN(gemm_nt_set(e, S, gr, y.Hf, F, [&](int l) { return P[l].layer[j].W2; }, F, 0, Fo, d, PL0(), d, F, 0, st, &pHf));
-    RUN(res_ln_fwd_grp(y.y2, noidx(), Fo, PL(S, [&](int l) { return P[l].layer[j].b2; }), PL(S, [&](int l) { return P[l].layer[j].n3w; }),
+    if (drop) RUN(dropout_fwd_grp(Fo, Fo, d, b2, gr, hrow, set_drop(e, S, j, DROP_FFN_OUT), st));
+    RUN(res_ln_fwd_grp(y.y2, noidx(), Fo, drop ? PL0() : b2, PL(S, [&](int l) { return P[l].layer[j].n3w; }),
                        PL(S, [&](int l) { return P[l].layer[j].n3b; }), y.y3, y.xh3, y.rs3, d, 1e-5f, gr, st));
     t_in = y.y3;
   }
@@ -736,36 +763,58 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
     const float* t_in = j == 0 ? v0.tok : v0.layer[j - 1].y3;
     auto Wl = [&](int l) -> const LayerP& { return P[l].layer[j]; };
     auto Gl = [&](int l) -> const LayerP& { return G[l].layer[j]; };
+    // With dropout the gradient of a branch is the masked, rescaled copy of the residual-sum gradient (and its column sums the
+    // gradient of the branch's bias): it is written to gB, which is free at both points where a copy is needed.
+    const bool drop = e->lv_drop_p[S.lv[0]] > 0.f;
+    for (int g = 1; g < S.n; ++g)
+      PATHS_REQUIRE((e->lv_drop_p[S.lv[g]] > 0.f) == drop && e->lv_drop_p[S.lv[g]] == e->lv_drop_p[S.lv[0]],
+                    "decoder backward: the levels of a set ran their forward passes with different dropout");
+    const GIdx hrow = last ? S.tsegI : noidx();
     // LN3 -> gA = d(y2 + ffn); db2
     RUN(ln_bwd_grp(dy3, nullptr, y.xh3, y.rs3, PL(S, [&](int l) { return Wl(l).n3w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n3w; }),
-                   ML(S, [&](int l) { return Gl(l).n3b; }), ML(S, [&](int l) { return Gl(l).b2; }), d, gr, st));
+                   ML(S, [&](int l) { return Gl(l).n3b; }), drop ? ML0() : ML(S, [&](int l) { return Gl(l).b2; }), d, gr, st));
+    const float* gF = gA;                                  // gradient of the FFN branch output
+    if (drop) {
+      RUN(dropout_bwd_grp(gA, gB, d, ML(S, [&](int l) { return Gl(l).b2; }), gr, hrow, set_drop(e, S, j, DROP_FFN_OUT), st));
+      gF = gB;
+    }
     // operand planes: each tensor is split once and feeds both the data-gradient and the weight-gradient contraction
     OpPl pA = oppl(last ? e->dplDb[0] : e->dplD[0]), pHf = oppl(saved ? e->svHf[j] : last ? e->dplFb[0] : e->dplF[0]),
          pdHf = oppl(last ? e->dplFb[1] : e->dplF[1]), pY2 = oppl(saved ? e->svY2[j] : last ? e->dplDb[1] : e->dplD[1]);
     pHf.ready = pY2.ready = saved;
-    RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).W2; }, F, 1, dHf, F, PL0(), F, d, 0, st, &pA));
-    RUN(gemm_tn_set(e, S, gr, gA, d, y.Hf, F, [&](int l) { return Gl(l).W2; }, F, d, F, st, &pA, &pHf));
+    RUN(gemm_nt_set(e, S, gr, gF, d, [&](int l) { return Wl(l).W2; }, F, 1, dHf, F, PL0(), F, d, 0, st, &pA));
+    RUN(gemm_tn_set(e, S, gr, gF, d, y.Hf, F, [&](int l) { return Gl(l).W2; }, F, d, F, st, &pA, &pHf));
+    const float inner_scale = drop ? 1.f / (1.f - e->lv_drop_p[S.lv[0]]) : 1.f;    // Hf was saved after the inner dropout
     if (dec_planes_on(e) && F % 8 == 0) {                  // masked gradient straight to operand planes (no fp32 write, no split pass)
-      RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st, &pdHf.pl, e->dm.precision == PREC_BF16X3_TC));
+      RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st, &pdHf.pl, e->dm.precision == PREC_BF16X3_TC, inner_scale));
       pdHf.ready = true;
     } else {
-      RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st));
+      RUN(relu_bwd_grp(dHf, y.Hf, F, gr, ML(S, [&](int l) { return Gl(l).b1; }), st, nullptr, 0, inner_scale));
     }
     RUN(gemm_tn_set(e, S, gr, dHf, F, y.y2, d, [&](int l) { return Gl(l).W1; }, d, F, d, st, &pdHf, &pY2));
     RUN(gemm_nt_set(e, S, gr, dHf, F, [&](int l) { return Wl(l).W1; }, d, 1, gA, d, PL0(), d, F, GEMM_ACCUM, st, &pdHf));     // gA = dy2
     // LN2 (cross-attention over an empty memory contributes only its output bias), then LN1
     RUN(ln_bwd_grp(gA, nullptr, y.xh2, y.rs2, PL(S, [&](int l) { return Wl(l).n2w; }), gB, noidx(), 0, ML(S, [&](int l) { return Gl(l).n2w; }),
-                   ML(S, [&](int l) { return Gl(l).n2b; }), ML(S, [&](int l) { return Gl(l).bcross; }), d, gr, st));
+                   ML(S, [&](int l) { return Gl(l).n2b; }), drop ? ML0() : ML(S, [&](int l) { return Gl(l).bcross; }), d, gr, st));
+    if (drop)                                              // the cross-attention branch is its bias alone: only d b_cross
+      RUN(dropout_bwd_grp(gB, nullptr, d, ML(S, [&](int l) { return Gl(l).bcross; }), gr, hrow, set_drop(e, S, j, DROP_CROSS_OUT), st));
     RUN(ln_bwd_grp(gB, nullptr, y.xh1, y.rs1, PL(S, [&](int l) { return Wl(l).n1w; }), gA, noidx(), 0, ML(S, [&](int l) { return Gl(l).n1w; }),
-                   ML(S, [&](int l) { return Gl(l).n1b; }), ML(S, [&](int l) { return Gl(l).bo; }), d, gr, st));      // gA = da
+                   ML(S, [&](int l) { return Gl(l).n1b; }), drop ? ML0() : ML(S, [&](int l) { return Gl(l).bo; }), d, gr, st));      // gA = da
+    const float* gS = gA;                                  // gradient of the self-attention branch output
+    if (drop) {
+      RUN(dropout_bwd_grp(gA, gB, d, ML(S, [&](int l) { return Gl(l).bo; }), gr, hrow, set_drop(e, S, j, DROP_SA_OUT), st));
+      gS = gB;
+    }
     OpPl pA2 = oppl(last ? e->dplDb[0] : e->dplD[0]), pO = oppl(saved ? e->svO[j] : last ? e->dplDb[1] : e->dplD[1]);
     pO.ready = saved;
-    RUN(gemm_nt_set(e, S, gr, gA, d, [&](int l) { return Wl(l).Wo; }, d, 1, gO, d, PL0(), d, d, 0, st, &pA2));
-    RUN(gemm_tn_set(e, S, gr, gA, d, y.O, d, [&](int l) { return Gl(l).Wo; }, d, d, d, st, &pA2, &pO));
-    if (last && !attn_bwd_writes_all(d, dm.heads))
+    RUN(gemm_nt_set(e, S, gr, gS, d, [&](int l) { return Wl(l).Wo; }, d, 1, gO, d, PL0(), d, d, 0, st, &pA2));
+    RUN(gemm_tn_set(e, S, gr, gS, d, y.O, d, [&](int l) { return Gl(l).Wo; }, d, d, d, st, &pA2, &pO));
+    if (last && (!attn_bwd_writes_all(d, dm.heads) || drop))
       for (int g = 0; g < S.n; ++g)
         RUN(zero_rows(v0.dqkv + (size_t)S.gt.roff[g] * 3 * d, 3 * d, S.gt.hcnt[g], S.gt.cnt[g], 0, st));
-    RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, last ? v0.Dvecb : v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st));
+    Drop dA;
+    if (drop) dA = set_drop(e, S, j, DROP_ATTN);
+    RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, last ? v0.Dvecb : v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr));
     OpPl p3 = oppl(e->dpl3), pT = oppl(saved ? e->svT[j] : e->dplD[0]);
     pT.ready = saved;
     const MutL dbqkv = ML(S, [&](int l) { return Gl(l).bqkv; });
@@ -956,7 +1005,8 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
   e->ws_base = static_cast<char*>(workspace); e->ws_bytes = need;
   e->site_on = getenv("PATHS_B200_PROF_DUMP") != nullptr;
   e->dec_planes = getenv("PATHS_B200_DEC_NO_PLANES") == nullptr;
-  for (int l = 0; l < PATHS_MAX_LEVELS; ++l) { e->sv_prec[l] = -1; e->sv_set[l] = 0; }
+  for (int l = 0; l < PATHS_MAX_LEVELS; ++l) { e->sv_prec[l] = -1; e->sv_set[l] = 0; e->lv_drop_p[l] = 0.f; e->lv_drop_seed[l] = 0; }
+  e->drop_p = 0.f; e->drop_seed = 0;
   {
     // "012,34": comma-separated sets of level digits (PATHS_B200_DEC_SETS_FWD / _BWD); a forward set starts once the tokens of
     // its deepest level exist, backward sets are launched last-to-first.
@@ -1350,9 +1400,16 @@ int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, siz
     case PATHS_BUF_DF_IN: p = v.dFl; n = B * dm.d * f; break;
     case PATHS_BUF_DHROW: p = v.dHrow; n = cap * dm.D * f; break;
     case PATHS_BUF_DCROW: p = v.dCrow; n = cap * dm.C * f; break;
+    case PATHS_BUF_HF0: p = v.layer[0].Hf; n = (dm.layers > 1 ? (size_t)v.ncap_tok : (size_t)B) * dm.F * f; break;
     default: set_error("unknown buffer id %d", which); return -2;
   }
   *ptr = p; *bytes = n;
+  return 0;
+}
+
+int paths_engine_set_dropout(paths_engine_t* e, float p, uint64_t seed) {
+  PATHS_REQUIRE(e && p >= 0.f && p < 1.f, "dropout probability must lie in [0, 1)");
+  e->drop_p = p; e->drop_seed = seed;
   return 0;
 }
 

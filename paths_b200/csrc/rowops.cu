@@ -635,7 +635,7 @@ __global__ void __launch_bounds__(TPB) ln_bwd_kernel(const float* __restrict__ d
 // With `outp` the masked gradient is written as tensor-core operand planes (global rows of the concatenated buffer, zero rows
 // up to round_up(longest group, 64) like split_planes_grp_kernel) instead of back to dH: its only consumers are contractions.
 __global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, int ld, Grp grp, MutL dbiasl,
-                                                       Planes outp, int want_lo) {
+                                                       Planes outp, int want_lo, float scale) {
   const int M = grp_count(grp, blockIdx.y);
   const int r0 = pick(grp.roff, blockIdx.y);
   dH += (size_t)r0 * ld; H += (size_t)r0 * ld;
@@ -662,11 +662,74 @@ __global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, c
         float4* dp = reinterpret_cast<float4*>(dH + (size_t)m * ld) + g;
         const float4 h = __ldg(reinterpret_cast<const float4*>(H + (size_t)m * ld) + g);
         v = *dp;
-        v.x = h.x > 0.f ? v.x : 0.f; v.y = h.y > 0.f ? v.y : 0.f; v.z = h.z > 0.f ? v.z : 0.f; v.w = h.w > 0.f ? v.w : 0.f;
+        // (scale != 1: H went through dropout after the relu -- its zeros cover both masks, the survivors carry 1 / (1 - p))
+        v.x = h.x > 0.f ? v.x * scale : 0.f; v.y = h.y > 0.f ? v.y * scale : 0.f; v.z = h.z > 0.f ? v.z * scale : 0.f;
+        v.w = h.w > 0.f ? v.w * scale : 0.f;
         if (!outp.p) *dp = v;
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       }
       if (outp.p) planes_store4(outp, r0 + m, 4 * g, v, want_lo != 0);
+    }
+  }
+  if (!dbias) return;
+  __shared__ float4 part[256];
+  part[threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.x < ngrp) {
+    float4 t = part[threadIdx.x];
+    for (int k = 1; k < rpb; ++k) { const float4 u = part[k * ngrp + threadIdx.x]; t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+    float* o = dbias + 4 * threadIdx.x;
+    atomicAdd(o, t.x); atomicAdd(o + 1, t.y); atomicAdd(o + 2, t.z); atomicAdd(o + 3, t.w);
+  }
+}
+
+__global__ void __launch_bounds__(256) dropout_fwd_kernel(const float* __restrict__ in, float* __restrict__ out, int cols, PtrL biasl,
+                                                          Grp grp, GIdx hrow, Drop dr) {
+  const int gi = blockIdx.y;
+  const int M = grp_count(grp, gi);
+  const size_t r0 = (size_t)pick(grp.roff, gi);
+  const float* bias = pick(biasl.p, gi);
+  const int* hr = pick(hrow.idx.p, gi);
+  const uint64_t key = pick(dr.key, gi);
+  const int n4 = cols >> 2;
+  const size_t total = (size_t)M * n4;
+  for (size_t e = (size_t)blockIdx.x * 256 + threadIdx.x; e < total; e += (size_t)gridDim.x * 256) {
+    const int m = (int)(e / n4), c = 4 * (int)(e % n4);
+    const uint32_t row = hr ? (uint32_t)hr[m] : (uint32_t)m;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (in) v = ld4(in + (r0 + m) * cols + c);
+    if (bias) { const float4 b = ld4(bias + c); v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w; }
+    v.x = drop_keep(key, row, c, dr.thresh) ? v.x * dr.inv_keep : 0.f;
+    v.y = drop_keep(key, row, c + 1, dr.thresh) ? v.y * dr.inv_keep : 0.f;
+    v.z = drop_keep(key, row, c + 2, dr.thresh) ? v.z * dr.inv_keep : 0.f;
+    v.w = drop_keep(key, row, c + 3, dr.thresh) ? v.w * dr.inv_keep : 0.f;
+    st4(out + (r0 + m) * cols + c, v);
+  }
+}
+
+__global__ void __launch_bounds__(256) dropout_bwd_kernel(const float* __restrict__ g, float* __restrict__ out, int cols, MutL dbiasl,
+                                                          Grp grp, GIdx hrow, Drop dr) {
+  const int gi = blockIdx.y;
+  const int M = grp_count(grp, gi);
+  const size_t r0 = (size_t)pick(grp.roff, gi);
+  float* dbias = pick(dbiasl.p, gi);
+  const int* hr = pick(hrow.idx.p, gi);
+  const uint64_t key = pick(dr.key, gi);
+  const int ngrp = cols >> 2;
+  const int rpb = 256 / ngrp > 0 ? 256 / ngrp : 1;
+  const int cg = threadIdx.x % ngrp, rsub = threadIdx.x / ngrp;
+  const int c = 4 * cg;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (rsub < rpb) {
+    for (int m = blockIdx.x * rpb + rsub; m < M; m += gridDim.x * rpb) {
+      const uint32_t row = hr ? (uint32_t)hr[m] : (uint32_t)m;
+      float4 v = ld4(g + (r0 + m) * cols + c);
+      v.x = drop_keep(key, row, c, dr.thresh) ? v.x * dr.inv_keep : 0.f;
+      v.y = drop_keep(key, row, c + 1, dr.thresh) ? v.y * dr.inv_keep : 0.f;
+      v.z = drop_keep(key, row, c + 2, dr.thresh) ? v.z * dr.inv_keep : 0.f;
+      v.w = drop_keep(key, row, c + 3, dr.thresh) ? v.w * dr.inv_keep : 0.f;
+      if (out) st4(out + (r0 + m) * cols + c, v);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
     }
   }
   if (!dbias) return;
@@ -946,7 +1009,8 @@ int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rs
   return ln_bwd_grp(dy, dy2, xhat, rstd, ptrl1(gamma), dx, gidx1(didx), accum, mutl1(dgamma), mutl1(dbeta), mutl1(dbias), d,
                     grp_single(M_host, M_dev), st);
 }
-int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st, const Planes* outp, int want_lo) {
+int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st, const Planes* outp, int want_lo,
+                 float scale) {
   const int cap = grp_max_rows(grp);
   if (cap <= 0) return 0;
   PATHS_REQUIRE(ld % 4 == 0 && ld <= 1024, "relu_bwd: row width %d unsupported (multiple of 4, <= 1024)", ld);
@@ -955,13 +1019,34 @@ int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& 
   const int lim = grp.n > 1 ? kNumSMs : 2 * kNumSMs;
   if (g > lim) g = lim;
   PATHS_REQUIRE(outp == nullptr || (outp->p && ld <= outp->ldp), "relu_bwd: output planes narrower than the rows");
-  relu_bwd_kernel<<<dim3(g, grp.n), 256, 0, st>>>(dH, H, ld, grp, dbias, outp ? *outp : no_planes(), want_lo);
+  relu_bwd_kernel<<<dim3(g, grp.n), 256, 0, st>>>(dH, H, ld, grp, dbias, outp ? *outp : no_planes(), want_lo, scale);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int dropout_fwd_grp(const float* in, float* out, int cols, const PtrL& bias, const Grp& grp, const GIdx& hrow, const Drop& dr, cudaStream_t st) {
+  PATHS_REQUIRE(cols % 4 == 0 && cols > 0, "dropout: row width %d is not a multiple of 4", cols);
+  const int cap = grp_max_rows(grp);
+  if (cap <= 0) return 0;
+  size_t g = ((size_t)cap * (cols >> 2) + 255) / 256;
+  if (g > (size_t)8 * kNumSMs) g = 8 * kNumSMs;
+  dropout_fwd_kernel<<<dim3((unsigned)g, grp.n), 256, 0, st>>>(in, out, cols, bias, grp, hrow, dr);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int dropout_bwd_grp(const float* g, float* out, int cols, const MutL& dbias, const Grp& grp, const GIdx& hrow, const Drop& dr, cudaStream_t st) {
+  PATHS_REQUIRE(cols % 4 == 0 && cols > 0 && cols <= 1024, "dropout backward: row width %d unsupported", cols);
+  const int cap = grp_max_rows(grp);
+  if (cap <= 0) return 0;
+  const int rpb = 256 / (cols >> 2) > 0 ? 256 / (cols >> 2) : 1;
+  int nb = (cap + rpb - 1) / rpb;
+  if (nb > 2 * kNumSMs) nb = 2 * kNumSMs;
+  dropout_bwd_kernel<<<dim3(nb, grp.n), 256, 0, st>>>(g, out, cols, dbias, grp, hrow, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, int M_extra, float* dbias, cudaStream_t st) {
   PATHS_REQUIRE(M_extra == 0, "relu_bwd: M_extra is no longer supported");
-  return relu_bwd_grp(dH, H, ld, grp_single(M_host, M_dev), mutl1(dbias), st, nullptr, 0);
+  return relu_bwd_grp(dH, H, ld, grp_single(M_host, M_dev), mutl1(dbias), st, nullptr, 0, 1.f);
 }
 int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
   if (M_host + M_extra <= 0) return 0;

@@ -56,10 +56,16 @@ int res_ln_fwd_grp(const float* res, const GIdx& ridx, const float* add, const P
 int ln_bwd_grp(const float* dy, const float* dy2, const float* xhat, const float* rstd, const PtrL& gamma, float* dx, const GIdx& didx, int accum,
                const MutL& dgamma, const MutL& dbeta, const MutL& dbias, int d, const Grp& grp, cudaStream_t st);
 int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& dbias, cudaStream_t st, const Planes* outp = nullptr,
-                 int want_lo = 0);
+                 int want_lo = 0, float scale = 1.f);
 int scatter_add_rows_grp(const float* src, const GIdx& idx, float* dst, int d, const Grp& grp, cudaStream_t st);
 int special_grad_grp(const float* dtok, const GIdx& seg, const MutL& dspecial, int d, int B, int ngroups, cudaStream_t st);
 int colsum_accum_grp(const float* X, int ld, const MutL& out, const Grp& grp, int N, cudaStream_t st);
+// Dropout of a sublayer output (common.cuh: Drop).  Rows are hashed by their level-local token row: the row itself, or
+// hrow.idx[g][m] for slide-shaped buffers (the special token's row).
+//   fwd: out[m, :] = keep ? ((in ? in[m, :] : 0) + bias_g) / (1 - p) : 0          (in == out allowed; cols % 4 == 0)
+//   bwd: out[m, :] = keep ? g[m, :] / (1 - p) : 0  (out may be null);  dbias_g += column sums of it   (cols <= 1024)
+int dropout_fwd_grp(const float* in, float* out, int cols, const PtrL& bias, const Grp& grp, const GIdx& hrow, const Drop& dr, cudaStream_t st);
+int dropout_bwd_grp(const float* g, float* out, int cols, const MutL& dbias, const Grp& grp, const GIdx& hrow, const Drop& dr, cudaStream_t st);
 int res_ln_fwd(const float* res, const int* ridx, const float* add, const float* bias, const float* gamma, const float* beta, float* y,
                float* xhat, float* rstd, int d, float eps, int M_host, const int* M_dev, int M_extra, cudaStream_t st);
 int ln_bwd(const float* dy, const float* dy2, const float* xhat, const float* rstd, const float* gamma, float* dx, const int* didx, int accum,
@@ -82,9 +88,11 @@ inline SegGrp seg_single(const int* seg, int B) {
   g.seg[0] = seg;
   return g;
 }
-int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st);
+// drop (optional): dropout of the attention probabilities, hashed on (level-local query row, head << 24 | key index)
+int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st,
+                 const Drop* drop = nullptr);
 int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
-                 int heads, int max_T, int nq_mode, cudaStream_t st);
+                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop = nullptr);
 int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st);
 bool attn_bwd_writes_all(int d, int heads);
 int attn_bwd(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,

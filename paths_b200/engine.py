@@ -346,6 +346,10 @@ class Engine:
         L.check(self.lib.paths_engine_set_precision(self.handle, precision), "set_precision")
         self.dims.precision = precision
 
+    def set_dropout(self, p: float, seed: int) -> None:
+        """Dropout of the aggregators for the next forward pass (and its backward pass); p = 0 switches it off."""
+        L.check(self.lib.paths_engine_set_dropout(self.handle, float(p), int(seed) & 0xFFFFFFFFFFFFFFFF), "set_dropout")
+
     def profile(self, on: bool) -> None:
         L.check(self.lib.paths_engine_profile(self.handle, int(on)), "profile")
 

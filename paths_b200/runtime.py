@@ -65,7 +65,7 @@ class ModelRuntime:
         self.track_hazard_grad = False
         self.strict_overflow = os.environ.get("PATHS_B200_STRICT_OVERFLOW", "0") == "1"
         self._pending: Optional[Engine] = None
-        self._warned_dropout = False
+        self.last_dropout = (0.0, 0)                    # (p, seed) of the latest forward pass (tests rebuild the masks from it)
         self._ids_cache: Dict[tuple, torch.Tensor] = {}
         self.global_batch: Optional[int] = None        # set by the data-parallel wrapper: loss = sum / global batch
 
@@ -98,6 +98,14 @@ class ModelRuntime:
             self.engines[key] = eng
         return eng
 
+    def _arm_dropout(self, eng: Engine) -> None:
+        """nn.Transformer's dropout is live in model.train() (train.py:131) and off in model.eval().  The keep/drop decisions
+        are hashed from a per-step seed drawn from torch's CPU generator, so torch.manual_seed makes runs repeatable."""
+        p = float(self.model.model_config.dropout) if self.model.training else 0.0
+        seed = int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item()) if p > 0 else 0
+        eng.set_dropout(p, seed)
+        self.last_dropout = (p, seed)
+
     def _check_pending(self) -> None:
         if self._pending is not None:
             eng, self._pending = self._pending, None
@@ -113,10 +121,6 @@ class ModelRuntime:
         """utils.inference_end2end (utils.py:228-279) on the device.  `batch` is the collated dict of
         data_utils/dataset.py:229-243 whose "slide" entries are paths_b200 PreprocessedSlide objects."""
         self._check_pending()
-        model = self.model
-        if model.training and model.model_config.dropout > 0 and not self._warned_dropout:
-            warnings.warn("paths_b200: dropout is not applied by the CUDA path yet (treated as 0.0)")
-            self._warned_dropout = True
         slides = batch["slide"]
         B = len(slides)
         store: PyramidStore = slides[0].store
@@ -146,6 +150,7 @@ class ModelRuntime:
                 ybin = torch.as_tensor(batch["subtype"]).to(dev, dtype=torch.int32, non_blocking=True)
                 cens = None
             scale = 1.0 / float(self.global_batch if self.global_batch else B)
+            self._arm_dropout(eng)
             if torch.is_grad_enabled():
                 hz, loss = _StepFn.apply(self.anchor, self, eng, slide_ids, fts, ybin, cens, scale)
             else:
@@ -211,6 +216,7 @@ class ModelRuntime:
         else:
             eng.buffer(depth, "ROW_PARENT")[:M] = -1
         eng.refresh_weights()
+        self._arm_dropout(eng)                          # model(depth, data) in train mode drops like the whole step does
         eng.level_forward(depth)
         out_imp = torch.zeros(B, N, device=self.device)
         out_imp[valid] = eng.buffer(depth, "ALPHA")[:M]

@@ -16,7 +16,7 @@ def _level_rows(eng, l, B):
     return M, seg
 
 
-def check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, prec, check_grads=True):
+def check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, prec, check_grads=True, drop=None):
     """Compares one finished product step (hz, loss, engine buffers, parameter .grad) with the CPU oracle."""
     eng = rt.last_engine
     tol = TOL[prec]
@@ -24,7 +24,7 @@ def check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss,
     assert not eng.overflowed()[0]
 
     # 1. free-running oracle: our selection must be a valid top-K of the oracle's scores
-    _, _, free = po.end2end(sd, ocfg, [s.grids for s in slides], ybin, cens, record=True)
+    _, _, free = po.end2end(sd, ocfg, [s.grids for s in slides], ybin, cens, record=True, drop=drop)
     forced = []
     for l in range(L - 1):
         M, seg = _level_rows(eng, l, B)
@@ -33,7 +33,7 @@ def check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss,
         cnt = eng.buffer(l, "SEL_COUNT")[:B].cpu()
         forced.append([(sel[j, :int(cnt[j])] - seg[j]).long() for j in range(B)])
     # 2. teacher-forced oracle (our indices) for value comparisons
-    ohz, oloss, ograds, recs = po.grads(sd, ocfg, [s.grids for s in slides], ybin, cens, forced_keep=forced)
+    ohz, oloss, ograds, recs = po.grads(sd, ocfg, [s.grids for s in slides], ybin, cens, forced_keep=forced, drop=drop)
     for l in range(L):
         M, seg = _level_rows(eng, l, B)
         rec = recs[l]
