@@ -287,13 +287,16 @@ constexpr int SQ = 8;            // queries (keys in the key-major phase) per wa
 constexpr int SW = 4;            // warps per CTA
 constexpr int SP = 33;           // padded row stride (floats)
 
-template <int NKC>
+// DROP: dropout of the probabilities (common.cuh: Drop) -- the normaliser sums every probability, the value sum the kept ones.
+template <int NKC, bool DROP>
 __global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                                  float* __restrict__ out, float* __restrict__ lse, int d, int heads,
-                                                                 int nq_mode) {
+                                                                 int nq_mode, const Drop dr) {
   constexpr int TP = 32 * NKC;
   const int h = blockIdx.x, s = blockIdx.y;
   const Seg sg = seg_of(seg, s);
+  const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
+  const uint32_t hrow0 = (uint32_t)(sg.t0 - sg.r0), hcol = (uint32_t)h << 24;
   const int T = sg.T;
   if (T > TP) return;
   const int nq = nq_mode ? 1 : T;
@@ -363,7 +366,8 @@ __global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __
 #pragma unroll
       for (int m = 0; m < NKC; ++m) {
         const float p = expf(sc[i][m] - mx);            // exp(-inf) = 0 at masked keys
-        P[i * TP + lane + 32 * m] = p;
+        if (DROP) P[i * TP + lane + 32 * m] = drop_keep(dkey, hrow0 + i0 + i, hcol | (uint32_t)(lane + 32 * m), dr.thresh) ? p * dr.inv_keep : 0.f;
+        else P[i * TP + lane + 32 * m] = p;
         sum += p;
       }
       sum = warp_sum(sum);
@@ -397,14 +401,16 @@ __global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __
 
 // Backward of the short-bag attention: phase A is query-major (dq), phase B key-major (dk, dv); both recompute the
 // probabilities from the saved log-sum-exp, so nothing is accumulated across warps and no atomics are needed.
-template <int NKC>
+template <int NKC, bool DROP>
 __global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                                  const float* __restrict__ out, const float* __restrict__ lse,
                                                                  const float* __restrict__ dout, float* __restrict__ dqkv, int d,
-                                                                 int heads, int nq_mode) {
+                                                                 int heads, int nq_mode, const Drop dr) {
   constexpr int TP = 32 * NKC;
   const int h = blockIdx.x, s = blockIdx.y;
   const Seg sg = seg_of(seg, s);
+  const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
+  const uint32_t hrow0 = (uint32_t)(sg.t0 - sg.r0), hcol = (uint32_t)h << 24;
   const int T = sg.T;
   if (T > TP) return;
   const int nq = nq_mode ? 1 : T;
@@ -494,7 +500,9 @@ __global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __
 #pragma unroll
       for (int m = 0; m < NKC; ++m) {
         const float p = (lane + 32 * m < T) ? expf(sc[i][m] - L) : 0.f;
-        S[i * TP + lane + 32 * m] = p * (dp[i][m] - Dq);
+        float dpm = dp[i][m];                             // d(kept probability) = dO.v / (1 - p); dropped ones get none
+        if (DROP) dpm = drop_keep(dkey, hrow0 + i0 + i, hcol | (uint32_t)(lane + 32 * m), dr.thresh) ? dpm * dr.inv_keep : 0.f;
+        S[i * TP + lane + 32 * m] = p * (dpm - Dq);
       }
     }
     __syncwarp();
@@ -545,8 +553,13 @@ __global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __
 #pragma unroll
       for (int i = 0; i < SQ; ++i) {
         const float p = (qi < nq) ? expf(sc[i][m] - L) : 0.f;
-        P[i * TP + qi] = p;
-        S[i * TP + qi] = p * (dp[i][m] - Dq);
+        float pm = p, dpm = dp[i][m];
+        if (DROP) {
+          const bool keep = drop_keep(dkey, hrow0 + qi, hcol | (uint32_t)(j0 + i), dr.thresh);
+          pm = keep ? p * dr.inv_keep : 0.f; dpm = keep ? dpm * dr.inv_keep : 0.f;
+        }
+        P[i * TP + qi] = pm;
+        S[i * TP + qi] = p * (dpm - Dq);
       }
     }
     __syncwarp();
@@ -899,24 +912,37 @@ constexpr int SMALL_MAX_T = 128;
 inline size_t small_fwd_smem(int nkc) { return (size_t)(3 * 32 * nkc * SP + SW * SQ * 32 * nkc) * sizeof(float); }
 inline size_t small_bwd_smem(int nkc) { return (size_t)(4 * 32 * nkc * SP + 2 * 32 * nkc + SW * 2 * SQ * 32 * nkc) * sizeof(float); }
 
-template <int NKC>
-int launch_fwd_small(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int B, int nq_mode, cudaStream_t st) {
+template <int NKC, bool DROP>
+int launch_fwd_small_d(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int B, int nq_mode, const Drop& dr,
+                       cudaStream_t st) {
   static bool cfg = false;
   const int bytes = (int)small_fwd_smem(NKC);
-  if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_fwd_small_kernel<NKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
-  attn_fwd_small_kernel<NKC><<<dim3(heads, B), SW * 32, bytes, st>>>(qkv, seg, out, lse, d, heads, nq_mode);
+  if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_fwd_small_kernel<NKC, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
+  attn_fwd_small_kernel<NKC, DROP><<<dim3(heads, B), SW * 32, bytes, st>>>(qkv, seg, out, lse, d, heads, nq_mode, dr);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+template <int NKC>
+int launch_fwd_small(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int B, int nq_mode, cudaStream_t st,
+                     const Drop& dr) {
+  return dr.thresh ? launch_fwd_small_d<NKC, true>(qkv, seg, out, lse, d, heads, B, nq_mode, dr, st)
+                   : launch_fwd_small_d<NKC, false>(qkv, seg, out, lse, d, heads, B, nq_mode, dr, st);
+}
+template <int NKC, bool DROP>
+int launch_bwd_small_d(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d, int heads,
+                       int B, int nq_mode, const Drop& dr, cudaStream_t st) {
+  static bool cfg = false;
+  const int bytes = (int)small_bwd_smem(NKC);
+  if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_bwd_small_kernel<NKC, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
+  attn_bwd_small_kernel<NKC, DROP><<<dim3(heads, B), SW * 32, bytes, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
 template <int NKC>
 int launch_bwd_small(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d, int heads,
-                     int B, int nq_mode, cudaStream_t st) {
-  static bool cfg = false;
-  const int bytes = (int)small_bwd_smem(NKC);
-  if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_bwd_small_kernel<NKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
-  attn_bwd_small_kernel<NKC><<<dim3(heads, B), SW * 32, bytes, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode);
-  PATHS_LAUNCH_CK();
-  return 0;
+                     int B, int nq_mode, cudaStream_t st, const Drop& dr) {
+  return dr.thresh ? launch_bwd_small_d<NKC, true>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, dr, st)
+                   : launch_bwd_small_d<NKC, false>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, dr, st);
 }
 }  // namespace
 
@@ -930,20 +956,15 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
   if (B <= 0) return 0;
   int skip_T = 0;
   const Drop dr = drop ? *drop : no_drop();
-  if (dr.thresh) {                                   // probability dropout: the tiled kernels serve every bag length
-    PATHS_REQUIRE(max_T < (1 << 24) && heads < 256, "attention dropout: bag of %d tokens / %d heads outside the hash's index range", max_T, heads);
-    dim3 grid(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
-    attn_fwd_kernel<<<grid, AW * 32, 0, st>>>(qkv, seg, out, lse, d, heads, nq_mode, 0, dr);
-    PATHS_LAUNCH_CK();
-    return 0;
-  }
-  if (d / heads == 32 && nq_mode) {
+  PATHS_REQUIRE(!dr.thresh || (max_T < (1 << 24) && heads < 256), "attention dropout: bag of %d tokens / %d heads outside the hash's index range",
+                max_T, heads);
+  if (d / heads == 32 && nq_mode && !dr.thresh) {    // (with dropout the short-bag / tiled kernels serve the single-query layer too)
     attn_fwd_nq1_kernel<<<(B * heads + 3) / 4, 128, 0, st>>>(qkv, seg, out, lse, d, heads, B);
     PATHS_LAUNCH_CK();
     return 0;
   }
   static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;   // experimental pair-per-row kernels (not faster: off)
-  if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode) {
+  if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
     switch (nkc) {
@@ -959,10 +980,10 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
     switch (nkc) {
-      case 1: r = launch_fwd_small<1>(qkv, seg, out, lse, d, heads, B, nq_mode, st); break;
-      case 2: r = launch_fwd_small<2>(qkv, seg, out, lse, d, heads, B, nq_mode, st); break;
-      case 3: r = launch_fwd_small<3>(qkv, seg, out, lse, d, heads, B, nq_mode, st); break;
-      default: r = launch_fwd_small<4>(qkv, seg, out, lse, d, heads, B, nq_mode, st); break;
+      case 1: r = launch_fwd_small<1>(qkv, seg, out, lse, d, heads, B, nq_mode, st, dr); break;
+      case 2: r = launch_fwd_small<2>(qkv, seg, out, lse, d, heads, B, nq_mode, st, dr); break;
+      case 3: r = launch_fwd_small<3>(qkv, seg, out, lse, d, heads, B, nq_mode, st, dr); break;
+      default: r = launch_fwd_small<4>(qkv, seg, out, lse, d, heads, B, nq_mode, st, dr); break;
     }
     if (r) return r;
     if (max_T <= SMALL_MAX_T) return 0;
@@ -987,22 +1008,13 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
   if (B <= 0) return 0;
   int skip_T = 0;
   const Drop dr = drop ? *drop : no_drop();
-  if (dr.thresh) {                                   // (with nq_mode the caller zero-fills dqkv: only query rows get a dq)
-    dim3 gq(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
-    attn_bwd_dq_kernel<<<gq, AW * 32, 0, st>>>(qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, nq_mode, 0, dr);
-    PATHS_LAUNCH_CK();
-    dim3 gk((max_T + QB - 1) / QB, heads, B);
-    attn_bwd_dkv_kernel<<<gk, AW * 32, 0, st>>>(qkv, seg, lse, dout, Dvec, dqkv, d, heads, nq_mode, 0, dr);
-    PATHS_LAUNCH_CK();
-    return 0;
-  }
-  if (d / heads == 32 && nq_mode) {
+  if (d / heads == 32 && nq_mode && !dr.thresh) {    // (with dropout and nq_mode the caller zero-fills dqkv: only query rows get a dq)
     attn_bwd_nq1_kernel<<<(B * heads + 3) / 4, 128, 0, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, B);
     PATHS_LAUNCH_CK();
     return 0;
   }
   static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;
-  if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode) {
+  if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
     switch (nkc) {
@@ -1018,10 +1030,10 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
     switch (nkc) {
-      case 1: r = launch_bwd_small<1>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st); break;
-      case 2: r = launch_bwd_small<2>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st); break;
-      case 3: r = launch_bwd_small<3>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st); break;
-      default: r = launch_bwd_small<4>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st); break;
+      case 1: r = launch_bwd_small<1>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st, dr); break;
+      case 2: r = launch_bwd_small<2>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st, dr); break;
+      case 3: r = launch_bwd_small<3>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st, dr); break;
+      default: r = launch_bwd_small<4>(qkv, seg, out, lse, dout, dqkv, d, heads, B, nq_mode, st, dr); break;
     }
     if (r) return r;
     if (max_T <= SMALL_MAX_T) return 0;

@@ -13,9 +13,11 @@ from tests.parity_check import check_against_oracle
 pytestmark = pytest.mark.gpu
 
 
-def _step(name, prec, p, train=True, seed=11, env=None):
+def _step(name, prec, p, train=True, seed=11, slide_specs=None):
     from paths_b200.utils import inference_end2end
     fx = load_fixture(name)
+    if slide_specs is not None:
+        fx = dict(fx, slide_specs=slide_specs)
     ocfg, sd, slides, ybin, cens = fixture_inputs(fx)
     cfg = product_config(fx, dropout=p)
     model = product_model(cfg, sd)
@@ -40,6 +42,16 @@ def test_dropout_step_matches_oracle_with_the_same_masks(name, p, prec):
     check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, prec, drop=po.HashDropout(p, seed))
 
 
+@pytest.mark.parametrize("prec", [0, 1])
+def test_dropout_long_bags(prec):
+    """Bags beyond 128 tokens (level 0 of a 17 x 12 grid; level 2 keeps every row) take the tiled attention kernels, the short
+    slide beside them the short-bag kernels of the same launch."""
+    ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss = _step("small_full", prec, 0.2, slide_specs=[(0, 17, 12), (1, 4, 3), (2, 9, 9)])
+    eng = rt.last_engine
+    assert int(eng.buffer(0, "SEG")[1]) > 128
+    check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, prec, drop=po.HashDropout(0.2, rt.last_dropout[1]))
+
+
 def test_dropout_is_live_in_train_mode_only_and_seeded_by_torch():
     base = _step("brca_b4", 1, 0.0)
     ev = _step("brca_b4", 1, 0.2, train=False)
@@ -52,7 +64,8 @@ def test_dropout_is_live_in_train_mode_only_and_seeded_by_torch():
     assert torch.equal(a[8], b[8]) and float(a[9]) == float(b[9])
     ga = {n: q.grad for n, q in a[6].named_parameters() if q.grad is not None}
     gb = {n: q.grad for n, q in b[6].named_parameters() if q.grad is not None}
-    assert all(rel_err(ga[n], gb[n]) < 1e-6 for n in ga)
+    worst = max((rel_err(ga[n], gb[n]), n) for n in ga)                   # same masks: only the order of atomic bias sums differs
+    assert worst[0] < 1e-5, worst
     assert rel_err(a[8], base[8]) > 1e-3 and rel_err(a[8], c[8]) > 1e-3  # dropout changes the step, and per seed
 
 
