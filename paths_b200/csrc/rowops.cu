@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(TPB) lstm_point1_fwd_kernel(float* __restrict_
 }
 
 // t = tanh(P), h' = o * t, Y = X + h'                       (interface.py:56, paths.py:89)
-__global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(const float* __restrict__ Pt, const float* __restrict__ G,
+__global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(float* __restrict__ Pt, const float* __restrict__ G,
                                                               const float* __restrict__ X, float* __restrict__ H,
                                                               float* __restrict__ Y, Planes YP, int want_lo, int D, int C, int M_host,
                                                               const int* M_dev) {
@@ -91,8 +91,9 @@ __global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(const float* __res
     for (int j4 = lane; j4 < D / 4; j4 += 32) {
       const int j = 4 * j4;
       if (m >= M) { planes_store4(YP, m, j, make_float4(0.f, 0.f, 0.f, 0.f), want_lo); continue; }
-      float4 t = ld4(Pt + (size_t)m * D + j);                // P stays as it is: the backward kernel takes tanh again (4 KB/row less)
+      float4 t = ld4(Pt + (size_t)m * D + j);
       t.x = tanhf(t.x); t.y = tanhf(t.y); t.z = tanhf(t.z); t.w = tanhf(t.w);
+      st4(Pt + (size_t)m * D + j, t);                        // (recomputing tanh in the backward kernel costs more than these 4 KB/row)
       const float4 o = ld4(G + (size_t)m * ldg + 3 * C + j), x = ld4(X + (size_t)m * D + j);
       const float4 h = make_float4(o.x * t.x, o.y * t.y, o.z * t.z, o.w * t.w);
       st4(H + (size_t)m * D + j, h);
@@ -108,6 +109,10 @@ __global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(const float* __res
 constexpr int CG = 4;                                     // float4 column groups per thread: D <= 4 * 4 * 256
 //   child_of != nullptr: dHc is the CHILD level's per-row gradient table and row m adds the rows child_of[4m .. 4m+3] (>= 0) in
 //   that order -- the child -> parent sum of parent_sum_kernel without the [M, D] round trip through HBM.
+// Two rows per block iteration, every load of both rows issued before the first use: the child rows hang off an index load, and
+// one row at a time leaves too few bytes in flight per SM to cover the two dependent latencies.
+constexpr int P2R = 2;
+template <int CGT>                                        // float4 column groups per thread actually in use: ceil(D / 1024)
 __global__ void __launch_bounds__(256) lstm_point2_bwd_kernel(const float* __restrict__ dY, const float* __restrict__ dHc,
                                                               const int* __restrict__ child_of,
                                                               const float* __restrict__ Pt, const float* __restrict__ G,
@@ -117,44 +122,70 @@ __global__ void __launch_bounds__(256) lstm_point2_bwd_kernel(const float* __res
   const int M = row_count(M_host, M_dev);
   const int ldg = 3 * C + D;
   const int Mw = dPP.p ? planes_rows_to_write(dPP, M) : M;
-  float4 aP[CG], aG[CG];
+  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 aP[CGT], aG[CGT];
 #pragma unroll
-  for (int q = 0; q < CG; ++q) aP[q] = aG[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int m = blockIdx.x; m < Mw; m += gridDim.x) {
-    int ch[4] = {-1, -1, -1, -1};
-    if (child_of && m < M) { const int4 c4 = __ldg(reinterpret_cast<const int4*>(child_of) + m); ch[0] = c4.x; ch[1] = c4.y; ch[2] = c4.z; ch[3] = c4.w; }
+  for (int q = 0; q < CGT; ++q) aP[q] = aG[q] = z4;
+  for (int m0 = blockIdx.x; m0 < Mw; m0 += P2R * gridDim.x) {
+    int4 ch[P2R];
 #pragma unroll
-    for (int q = 0; q < CG; ++q) {
+    for (int r = 0; r < P2R; ++r) {
+      const int m = m0 + r * gridDim.x;
+      ch[r] = make_int4(-1, -1, -1, -1);
+      if (child_of && m < M) ch[r] = __ldg(reinterpret_cast<const int4*>(child_of) + m);
+    }
+#pragma unroll
+    for (int q = 0; q < CGT; ++q) {
       const int j = 4 * (threadIdx.x + 256 * q);
       if (j >= D) break;
-      float4 vp = make_float4(0.f, 0.f, 0.f, 0.f), vg = vp;
-      if (m < M) {
-        float4 dh = dY ? ld4(dY + (size_t)m * D + j) : make_float4(0.f, 0.f, 0.f, 0.f);
-        if (dHc && child_of) {
-          float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 dh[P2R], t[P2R], o[P2R], e[P2R][4];
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (ch[k] >= 0) { const float4 u = ld4(dHc + (size_t)ch[k] * D + j); e.x += u.x; e.y += u.y; e.z += u.z; e.w += u.w; }
-          dh.x += e.x; dh.y += e.y; dh.z += e.z; dh.w += e.w;
-        } else if (dHc) { const float4 e = ld4(dHc + (size_t)m * D + j); dh.x += e.x; dh.y += e.y; dh.z += e.z; dh.w += e.w; }
-        float4 t = ld4(Pt + (size_t)m * D + j);
-        t.x = tanhf(t.x); t.y = tanhf(t.y); t.z = tanhf(t.z); t.w = tanhf(t.w);
-        const float4 o = ld4(G + (size_t)m * ldg + 3 * C + j);
-        vp = make_float4(dh.x * o.x * (1.f - t.x * t.x), dh.y * o.y * (1.f - t.y * t.y), dh.z * o.z * (1.f - t.z * t.z),
-                         dh.w * o.w * (1.f - t.w * t.w));
-        vg = make_float4(dh.x * t.x * o.x * (1.f - o.x), dh.y * t.y * o.y * (1.f - o.y), dh.z * t.z * o.z * (1.f - o.z),
-                         dh.w * t.w * o.w * (1.f - o.w));
-        aP[q].x += vp.x; aP[q].y += vp.y; aP[q].z += vp.z; aP[q].w += vp.w;
-        aG[q].x += vg.x; aG[q].y += vg.y; aG[q].z += vg.z; aG[q].w += vg.w;
-        if (dP) st4(dP + (size_t)m * D + j, vp);
-        if (dG) st4(dG + (size_t)m * ldg + 3 * C + j, vg);
+      for (int r = 0; r < P2R; ++r) {
+        const int m = m0 + r * gridDim.x;
+        dh[r] = t[r] = o[r] = z4;
+        e[r][0] = e[r][1] = e[r][2] = e[r][3] = z4;
+        if (m < M) {
+          if (dY) dh[r] = ld4(dY + (size_t)m * D + j);
+          t[r] = ld4(Pt + (size_t)m * D + j);
+          o[r] = ld4(G + (size_t)m * ldg + 3 * C + j);
+          if (dHc && child_of) {
+            if (ch[r].x >= 0) e[r][0] = ld4(dHc + (size_t)ch[r].x * D + j);
+            if (ch[r].y >= 0) e[r][1] = ld4(dHc + (size_t)ch[r].y * D + j);
+            if (ch[r].z >= 0) e[r][2] = ld4(dHc + (size_t)ch[r].z * D + j);
+            if (ch[r].w >= 0) e[r][3] = ld4(dHc + (size_t)ch[r].w * D + j);
+          } else if (dHc) {
+            e[r][0] = ld4(dHc + (size_t)m * D + j);
+          }
+        }
       }
-      if (dPP.p) planes_store4(dPP, m, j, vp, want_lo);
-      if (dGP.p) planes_store4(dGP, m, 3 * C + j, vg, want_lo);
+#pragma unroll
+      for (int r = 0; r < P2R; ++r) {
+        const int m = m0 + r * gridDim.x;
+        if (m >= Mw) continue;
+        float4 vp = z4, vg = z4;
+        if (m < M) {
+          float4 s4 = e[r][0];                                 // ((c0 + c1) + c2) + c3: the order of parent_sum_kernel
+          s4.x += e[r][1].x; s4.y += e[r][1].y; s4.z += e[r][1].z; s4.w += e[r][1].w;
+          s4.x += e[r][2].x; s4.y += e[r][2].y; s4.z += e[r][2].z; s4.w += e[r][2].w;
+          s4.x += e[r][3].x; s4.y += e[r][3].y; s4.z += e[r][3].z; s4.w += e[r][3].w;
+          const float4 d4 = make_float4(dh[r].x + s4.x, dh[r].y + s4.y, dh[r].z + s4.z, dh[r].w + s4.w);
+          const float4 tt = t[r], oo = o[r];
+          vp = make_float4(d4.x * oo.x * (1.f - tt.x * tt.x), d4.y * oo.y * (1.f - tt.y * tt.y), d4.z * oo.z * (1.f - tt.z * tt.z),
+                           d4.w * oo.w * (1.f - tt.w * tt.w));
+          vg = make_float4(d4.x * tt.x * oo.x * (1.f - oo.x), d4.y * tt.y * oo.y * (1.f - oo.y), d4.z * tt.z * oo.z * (1.f - oo.z),
+                           d4.w * tt.w * oo.w * (1.f - oo.w));
+          aP[q].x += vp.x; aP[q].y += vp.y; aP[q].z += vp.z; aP[q].w += vp.w;
+          aG[q].x += vg.x; aG[q].y += vg.y; aG[q].z += vg.z; aG[q].w += vg.w;
+          if (dP) st4(dP + (size_t)m * D + j, vp);
+          if (dG) st4(dG + (size_t)m * ldg + 3 * C + j, vg);
+        }
+        if (dPP.p) planes_store4(dPP, m, j, vp, want_lo);
+        if (dGP.p) planes_store4(dGP, m, 3 * C + j, vg, want_lo);
+      }
     }
   }
 #pragma unroll
-  for (int q = 0; q < CG; ++q) {
+  for (int q = 0; q < CGT; ++q) {
     const int j = 4 * (threadIdx.x + 256 * q);
     if (j >= D) break;
     atomicAdd(db_mo + j, aP[q].x); atomicAdd(db_mo + j + 1, aP[q].y); atomicAdd(db_mo + j + 2, aP[q].z); atomicAdd(db_mo + j + 3, aP[q].w);
@@ -884,7 +915,7 @@ int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, 
   PATHS_LAUNCH_CK();
   return 0;
 }
-int lstm_point2_fwd(const float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
+int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
                     const int* M_dev, cudaStream_t st) {
   if (M_host <= 0) return 0;
   lstm_point2_fwd_kernel<<<row_grid(M_host + 64), TPB, 0, st>>>(Pt, G, X, H, Y, YP, want_lo, D, C, M_host, M_dev);
@@ -895,8 +926,18 @@ int lstm_point2_bwd(const float* dY, const float* dHc, const int* child_of, cons
                     float* dG, const Planes& dGP, float* db_mo, float* db_o, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st) {
   PATHS_REQUIRE(D <= 4 * CG * 256, "lstm backward: patch_embed_dim above %d unsupported", 4 * CG * 256);
   if (M_host <= 0) return 0;
-  int g = M_host + 64; if (g > 3 * kNumSMs) g = 3 * kNumSMs;
-  lstm_point2_bwd_kernel<<<g, 256, 0, st>>>(dY, dHc, child_of, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
+  // one resident wave: the blocks stride over the rows and end with 2 D atomics each
+  static int occ[2] = {0, 0};
+  const int wide = D > 1024 ? 1 : 0;
+  if (!occ[wide]) {
+    if (wide) PATHS_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], lstm_point2_bwd_kernel<CG>, 256, 0));
+    else PATHS_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], lstm_point2_bwd_kernel<1>, 256, 0));
+    if (occ[wide] < 1) occ[wide] = 1;
+    if (occ[wide] > 4) occ[wide] = 4;
+  }
+  int g = (M_host + 64 + P2R - 1) / P2R; if (g > occ[wide] * kNumSMs) g = occ[wide] * kNumSMs;
+  if (wide) lstm_point2_bwd_kernel<CG><<<g, 256, 0, st>>>(dY, dHc, child_of, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
+  else lstm_point2_bwd_kernel<1><<<g, 256, 0, st>>>(dY, dHc, child_of, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }

@@ -24,7 +24,7 @@ int pack_padded_rows(const float* fts, int N, const int* seg, const int* row_sli
 int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, const Planes& CnP, int want_lo, int activated, int D, int C,
                     int M_host,
                     const int* M_dev, cudaStream_t st);
-int lstm_point2_fwd(const float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
+int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
                     const int* M_dev, cudaStream_t st);
 // child_of != nullptr: dHc / dCc are the CHILD level's per-row gradient tables and each row sums its children's rows itself
 int lstm_point2_bwd(const float* dY, const float* dHc, const int* child_of, const float* Pt, const float* G, float* dP, const Planes& dPP,
