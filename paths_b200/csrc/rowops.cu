@@ -419,6 +419,115 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restric
   }
 }
 
+// The same backward with 16-byte accesses (I, d multiples of 4, at most 256): a lane owns the float4 column groups lane + 32 q,
+// a warp works on two rows at a time with every load issued before the first use, and the grid is several blocks per SM -- the
+// scalar kernel above is bound by the latency of its per-row chain (slide index -> token row -> loads -> warp sum -> stores).
+constexpr int ITR = 2;                                    // rows per warp iteration
+template <int Q>                                           // float4 column groups per lane: ceil(max(I, d) / 128)
+__global__ void __launch_bounds__(TPB) imp_tok_bwd4_kernel(const float* __restrict__ dtok, const float* __restrict__ UV,
+                                                           const float* __restrict__ alpha, const float* __restrict__ w2,
+                                                           const int* __restrict__ row_slide, float* __restrict__ dUV, Planes dUVP,
+                                                           int want_lo, float* __restrict__ db1, float* __restrict__ dw2,
+                                                           float* __restrict__ db2, float* __restrict__ dbin, int I, int d, int imp_mul,
+                                                           int M_host, const int* M_dev) {
+  const int M = row_count(M_host, M_dev);
+  const int ld = I + d;
+  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 a_b1[Q], a_w2[Q], a_bin[Q];
+  float a_b2 = 0.f;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) a_b1[q] = a_w2[q] = a_bin[q] = z4;
+  const int Mw = dUVP.p ? planes_rows_to_write(dUVP, M) : M;
+  const int lane = threadIdx.x & 31;
+  const int wid = blockIdx.x * WPB + (threadIdx.x >> 5), nw = gridDim.x * WPB;
+  float4 w4[Q];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { const int j = 4 * lane + 128 * q; w4[q] = j < I ? ld4(w2 + j) : z4; }
+  auto put4 = [&](int m, int col, const float4& v) {
+    if (dUV) st4(dUV + (size_t)m * ld + col, v);
+    if (dUVP.p) planes_store4(dUVP, m, col, v, want_lo != 0);
+  };
+  for (int m0 = wid; m0 < Mw; m0 += ITR * nw) {
+    float4 g4[ITR][Q], v4[ITR][Q], u4[ITR][Q];
+    float a[ITR];
+#pragma unroll
+    for (int r = 0; r < ITR; ++r) {
+      const int m = m0 + r * nw;
+      a[r] = 0.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) g4[r][q] = v4[r][q] = u4[r][q] = z4;
+      if (m < M) {
+        const float* uv = UV + (size_t)m * ld;
+        const float* dt = dtok + (size_t)(m + row_slide[m] + 1) * d;
+        a[r] = alpha[m];
+#pragma unroll
+        for (int q = 0; q < Q; ++q) {
+          const int c = 4 * lane + 128 * q;
+          if (c < d) { g4[r][q] = ld4(dt + c); v4[r][q] = ld4(uv + I + c); }
+          if (c < I) u4[r][q] = ld4(uv + c);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < ITR; ++r) {
+      const int m = m0 + r * nw;
+      if (m >= Mw) continue;                                 // warp-uniform
+      if (m >= M) {
+#pragma unroll
+        for (int q = 0; q < Q; ++q) { const int c = 4 * lane + 128 * q; if (c < I) put4(m, c, z4); if (c < d) put4(m, I + c, z4); }
+        continue;
+      }
+      float da = 0.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int c = 4 * lane + 128 * q;
+        if (c < d) {
+          const float4 g = g4[r][q], v = v4[r][q];
+          a_bin[q].x += g.x; a_bin[q].y += g.y; a_bin[q].z += g.z; a_bin[q].w += g.w;
+          da += g.x * v.x + g.y * v.y + g.z * v.z + g.w * v.w;
+          put4(m, I + c, imp_mul ? make_float4(a[r] * g.x, a[r] * g.y, a[r] * g.z, a[r] * g.w) : g);
+        }
+      }
+      float ds = 0.f;
+      if (imp_mul) { da = warp_sum(da); ds = da * a[r] * (1.f - a[r]); }
+      a_b2 += ds;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int j = 4 * lane + 128 * q;
+        if (j < I) {
+          const float4 u = u4[r][q];
+          a_w2[q].x += ds * u.x; a_w2[q].y += ds * u.y; a_w2[q].z += ds * u.z; a_w2[q].w += ds * u.w;
+          const float4 du = make_float4(u.x > 0.f ? ds * w4[q].x : 0.f, u.y > 0.f ? ds * w4[q].y : 0.f, u.z > 0.f ? ds * w4[q].z : 0.f,
+                                        u.w > 0.f ? ds * w4[q].w : 0.f);
+          a_b1[q].x += du.x; a_b1[q].y += du.y; a_b1[q].z += du.z; a_b1[q].w += du.w;
+          put4(m, j, du);
+        }
+      }
+    }
+  }
+  __shared__ float4 red[WPB][3][32 * Q];
+  const int w = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { red[w][0][lane + 32 * q] = a_b1[q]; red[w][1][lane + 32 * q] = a_w2[q]; red[w][2][lane + 32 * q] = a_bin[q]; }
+  __shared__ float red_b2[WPB];
+  if (lane == 0) red_b2[w] = a_b2;
+  __syncthreads();
+  for (int e = threadIdx.x; e < 3 * 32 * Q; e += TPB) {
+    const int k = e / (32 * Q), c4 = e % (32 * Q), c = 4 * c4;
+    float4 t = red[0][k][c4];
+#pragma unroll
+    for (int ww = 1; ww < WPB; ++ww) { const float4 u = red[ww][k][c4]; t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+    float* o = k == 0 ? db1 : k == 1 ? dw2 : dbin;
+    if (c < (k == 2 ? d : I)) { atomicAdd(o + c, t.x); atomicAdd(o + c + 1, t.y); atomicAdd(o + c + 2, t.z); atomicAdd(o + c + 3, t.w); }
+  }
+  if (threadIdx.x == 0) {
+    float sb = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < WPB; ++ww) sb += red_b2[ww];
+    if (sb != 0.f) atomicAdd(db2, sb);
+  }
+}
+
 // ---- RNN variant (lstm = false, paths.py:96-109): Z = alpha * X + hctx ------------------------------------------------
 __global__ void __launch_bounds__(TPB) rnn_z_fwd_kernel(const float* __restrict__ X, const float* __restrict__ alpha,
                                                         const float* __restrict__ hctx, float* __restrict__ Z, int D, int imp_mul,
@@ -977,7 +1086,25 @@ int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const fl
                 int want_lo, float* db1, float* dw2, float* db2, float* dbin, int I, int d, int imp_mul, int mode, int M_host, const int* M_dev,
                 cudaStream_t st) {
   if (M_host <= 0) return 0;
-  int g = row_grid(M_host + 64); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
+  int g = row_grid(M_host + 64);
+  const bool vec = mode == 0 && I % 4 == 0 && d % 4 == 0 && I <= 256 && d <= 256 && ((reinterpret_cast<uintptr_t>(dtok) | reinterpret_cast<uintptr_t>(UV) |
+                   reinterpret_cast<uintptr_t>(w2) | reinterpret_cast<uintptr_t>(dUV)) & 15) == 0 && (!dUVP.p || dUVP.ldp % 4 == 0);
+  if (vec) {
+    const int wide = (I > 128 || d > 128) ? 1 : 0;
+    static int occ[2] = {0, 0};
+    if (!occ[wide]) {
+      if (wide) PATHS_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], imp_tok_bwd4_kernel<2>, TPB, 0));
+      else PATHS_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], imp_tok_bwd4_kernel<1>, TPB, 0));
+      if (occ[wide] < 1) occ[wide] = 1;
+    }
+    g = (M_host + 64 + WPB * ITR - 1) / (WPB * ITR);
+    if (g > occ[wide] * kNumSMs) g = occ[wide] * kNumSMs;     // one resident wave: each block ends with up to 3 * 256 atomics
+    if (wide) imp_tok_bwd4_kernel<2><<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, M_host, M_dev);
+    else imp_tok_bwd4_kernel<1><<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, M_host, M_dev);
+    PATHS_LAUNCH_CK();
+    return 0;
+  }
+  if (g > 2 * kNumSMs) g = 2 * kNumSMs;
   imp_tok_bwd_kernel<<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, mode, M_host,
                                         M_dev);
   PATHS_LAUNCH_CK();
