@@ -289,9 +289,8 @@ constexpr int SP = 33;           // padded row stride (floats)
 
 // DROP: dropout of the probabilities (common.cuh: Drop) -- the normaliser sums every probability, the value sum the kept ones.
 template <int NKC, bool DROP>
-__global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
-                                                                 float* __restrict__ out, float* __restrict__ lse, int d, int heads,
-                                                                 int nq_mode, const Drop dr) {
+__device__ __forceinline__ void attn_fwd_small_body(const float* __restrict__ qkv, const SegGrp& seg, float* __restrict__ out,
+                                                    float* __restrict__ lse, int d, int heads, int nq_mode, const Drop& dr) {
   constexpr int TP = 32 * NKC;
   const int h = blockIdx.x, s = blockIdx.y;
   const Seg sg = seg_of(seg, s);
@@ -399,13 +398,25 @@ __global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __
   }
 }
 
+// The launch is compiled for the longest bag (32 * NKC tokens); a CTA whose own bag is shorter runs the body compiled for its
+// length class: the score rows of a 57-token bag then span 64 key slots instead of 96 (a third less FMA work in the score phases).
+template <int NKC, bool DROP>
+__global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
+                                                                 float* __restrict__ out, float* __restrict__ lse, int d, int heads,
+                                                                 int nq_mode, const Drop dr) {
+  const int T = seg_of(seg, blockIdx.y).T;
+  if (NKC >= 2 && T <= 32) attn_fwd_small_body<1, DROP>(qkv, seg, out, lse, d, heads, nq_mode, dr);
+  else if (NKC >= 3 && T <= 64) attn_fwd_small_body<2, DROP>(qkv, seg, out, lse, d, heads, nq_mode, dr);
+  else if (NKC >= 4 && T <= 96) attn_fwd_small_body<3, DROP>(qkv, seg, out, lse, d, heads, nq_mode, dr);
+  else attn_fwd_small_body<NKC, DROP>(qkv, seg, out, lse, d, heads, nq_mode, dr);
+}
+
 // Backward of the short-bag attention: phase A is query-major (dq), phase B key-major (dk, dv); both recompute the
 // probabilities from the saved log-sum-exp, so nothing is accumulated across warps and no atomics are needed.
 template <int NKC, bool DROP>
-__global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
-                                                                 const float* __restrict__ out, const float* __restrict__ lse,
-                                                                 const float* __restrict__ dout, float* __restrict__ dqkv, int d,
-                                                                 int heads, int nq_mode, const Drop dr) {
+__device__ __forceinline__ void attn_bwd_small_body(const float* __restrict__ qkv, const SegGrp& seg, const float* __restrict__ out,
+                                                    const float* __restrict__ lse, const float* __restrict__ dout,
+                                                    float* __restrict__ dqkv, int d, int heads, int nq_mode, const Drop& dr) {
   constexpr int TP = 32 * NKC;
   const int h = blockIdx.x, s = blockIdx.y;
   const Seg sg = seg_of(seg, s);
@@ -587,6 +598,18 @@ __global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __
     }
     __syncwarp();
   }
+}
+
+template <int NKC, bool DROP>
+__global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
+                                                                 const float* __restrict__ out, const float* __restrict__ lse,
+                                                                 const float* __restrict__ dout, float* __restrict__ dqkv, int d,
+                                                                 int heads, int nq_mode, const Drop dr) {
+  const int T = seg_of(seg, blockIdx.y).T;
+  if (NKC >= 2 && T <= 32) attn_bwd_small_body<1, DROP>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
+  else if (NKC >= 3 && T <= 64) attn_bwd_small_body<2, DROP>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
+  else if (NKC >= 4 && T <= 96) attn_bwd_small_body<3, DROP>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
+  else attn_bwd_small_body<NKC, DROP>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
 }
 
 }  // namespace
