@@ -220,13 +220,15 @@ def main():
         if world > 1:
             dist.all_reduce(gflat)
 
+    from paths_b200.optim import FlatAdamW
+    opt = FlatAdamW(model, lr=cfg.lr) if hasattr(cfg, "lr") else FlatAdamW(model)
+
     def run_e2e(steps):
         # the reference's train-loop body (train.py:58-65) over host batches; the loader wrapper stages batch i+1 into HBM
         # (pinned host -> device, on a copy stream) while step i runs.  Every step copies its own inputs and reads its loss.
         losses = []
         for b in DevicePrefetcher((batch for _ in range(steps)), dev):
-            for p in model.parameters():
-                p.grad = None
+            opt.zero_grad()                                    # train.py:59
             hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
             loss.backward()
             if world > 1:

@@ -4,13 +4,16 @@ The reference moves each collated batch to the GPU inside the step (`PatchBatch.
 utils.py:236; train.py:58-60 iterates the DataLoader directly), so the level-0 feature copy (84 MB for 256 BRCA-shaped
 slides) sits on the critical path of every step.  `DevicePrefetcher` wraps the same iterable of collated batches and
 issues the copy of batch i+1 on a dedicated copy stream while step i computes; `utils.inference_end2end` accepts the
-yielded batch unchanged (its `.to(device)` calls are no-ops on tensors that already live there).
+yielded batch unchanged (its `.to(device)` calls are no-ops on tensors that already live there).  Fetching the next batch
+from the loader and enqueuing its copies happens on a helper thread: when the consumer comes back from reading its loss the
+GPU is idle, and every host millisecond before the next step's first launch is a millisecond of idle GPU.
 
     for batch in DevicePrefetcher(train_loader, device):       # instead of: for batch in train_loader
         hazards, loss = utils.inference_end2end(..., batch, config.task)
 """
 from __future__ import annotations
 
+from concurrent.futures import ThreadPoolExecutor
 from typing import Dict, Iterable, Iterator, Optional
 
 import torch
@@ -24,13 +27,19 @@ class DevicePrefetcher:
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("paths_b200: DevicePrefetcher stages batches into CUDA memory; there is no CPU path")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.keys = tuple(keys)
         self.copy_stream = torch.cuda.Stream(self.device)
+
+    def _fetch_and_stage(self, it):
+        return self._stage(next(it, None))
 
     def _stage(self, batch: Optional[Dict]):
         if batch is None:
             return None
         out = dict(batch)
+        torch.cuda.set_device(self.device)                     # (helper thread: the current device is per thread)
         with torch.cuda.stream(self.copy_stream):
             # small (pageable) label tensors first: a pageable copy blocks the host until it has run, and behind the feature
             # copy that would be the whole 84 MB transfer
@@ -46,17 +55,24 @@ class DevicePrefetcher:
 
     def __iter__(self) -> Iterator[Dict]:
         it = iter(self.loader)
-        staged = self._stage(next(it, None))
-        while staged is not None:
-            batch, ev = staged
-            cur = torch.cuda.current_stream(self.device)
-            cur.wait_event(ev)                                 # the consumer's stream orders after the copy, no host sync
-            for k in self.keys:
-                v = batch.get(k)
-                if torch.is_tensor(v) and v.is_cuda:
-                    v.record_stream(cur)
-            staged = self._stage(next(it, None))               # copy of the next batch overlaps this step's kernels
-            yield batch
+        pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix="paths_b200_prefetch")
+        try:
+            pending = pool.submit(self._fetch_and_stage, it)
+            while True:
+                staged = pending.result()                      # (an exception of the loader or of a copy surfaces here)
+                if staged is None:
+                    break
+                batch, ev = staged
+                cur = torch.cuda.current_stream(self.device)
+                cur.wait_event(ev)                             # the consumer's stream orders after the copy, no host sync
+                for k in self.keys:
+                    v = batch.get(k)
+                    if torch.is_tensor(v) and v.is_cuda:
+                        v.record_stream(cur)
+                pending = pool.submit(self._fetch_and_stage, it)   # next batch: fetched and copied while this step runs
+                yield batch
+        finally:
+            pool.shutdown(wait=True, cancel_futures=True)
 
     def __len__(self):
         return len(self.loader)

@@ -24,6 +24,16 @@ class FlatAdamW(torch.optim.Optimizer):
         self.exp_avg = torch.zeros(lay.total_all, dtype=torch.float32, device=lay.device)
         self.exp_avg_sq = torch.zeros(lay.total_all, dtype=torch.float32, device=lay.device)
         self.t = 0
+        self._params = [q for g in self.param_groups for q in g["params"]]
+
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        """`opt.zero_grad()` of train.py:59.  The gradients live in one flat buffer: dropping the views costs a plain loop over a
+        cached list (no module-tree walk, no per-tensor kernels); the buffer itself is cleared by the next backward pass."""
+        if set_to_none:
+            for q in self._params:
+                q.grad = None
+            return
+        super().zero_grad(set_to_none=False)
 
     def _skip_ranges(self, lay):
         rng = []

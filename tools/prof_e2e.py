@@ -18,6 +18,8 @@ cfg = Config.from_dict(BRCA_CONFIG)
 torch.manual_seed(cfg.seed)
 model = cfg.get_model().to(dev); model.train()
 rt = model.runtime(); rt.set_precision("bf16x3")
+from paths_b200.optim import FlatAdamW
+opt = FlatAdamW(model)
 D, Lv = cfg.model_config.patch_embed_dim, cfg.num_levels
 store = PyramidStore(Lv, D, dev)
 items = []
@@ -32,8 +34,7 @@ batch["fts"] = batch["fts"].pin_memory()
 
 def run(steps):
     for b in DevicePrefetcher((batch for _ in range(steps)), dev):
-        for p in model.parameters():
-            p.grad = None
+        opt.zero_grad()
         hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
         loss.backward()
         loss.item()
