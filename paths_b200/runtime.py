@@ -8,6 +8,7 @@ import warnings
 from typing import Dict, List, Optional, Sequence
 
 import torch
+import torch.distributed
 
 from . import _lib as L
 from .engine import Engine, ParamLayout, PyramidStore, make_dims, pe_div_table
@@ -103,6 +104,9 @@ class ModelRuntime:
         are hashed from a per-step seed drawn from torch's CPU generator, so torch.manual_seed makes runs repeatable."""
         p = float(self.model.model_config.dropout) if self.model.training else 0.0
         seed = int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item()) if p > 0 else 0
+        if p > 0 and torch.distributed.is_available() and torch.distributed.is_initialized():
+            # data-parallel ranks seeded alike must not drop the same (row, column) positions of their shards
+            seed = (seed + torch.distributed.get_rank() * 0x9E3779B97F4A7C15) & 0x3FFFFFFFFFFFFFFF
         eng.set_dropout(p, seed)
         self.last_dropout = (p, seed)
 
