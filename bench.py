@@ -89,6 +89,9 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+CPU_SAMPLE_SLIDES, CPU_SAMPLE_STEPS = 32, 30      # the reference's own batch size (larger oracle batches run slower per slide)
+
+
 def cpu_oracle_rate(n_slides, steps, warmup, threads=None):
     """slides/s of the CPU oracle (fwd+bwd) on a bounded sample of the same workload."""
     from oracle import paths_oracle as po
@@ -119,7 +122,7 @@ def run_reference(args):
     if rank != 0:
         return
     n = 32                                   # the reference's own batch_size (models/brca_paths_0/config.json:6)
-    steps = max(1, min(args.steps, 5)); warm = max(1, min(args.warmup, 1))
+    steps = max(1, min(args.steps, 200)); warm = max(0, min(args.warmup, 50))     # ~0.3 s per step: the driver's K and W as given
     rate, spp, cores = cpu_oracle_rate(n, steps, warm)
     line = {
         "metric": "slides_per_sec_fwd_bwd", "value": rate, "unit": "slides/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
@@ -343,9 +346,9 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        rate, spp, cores = cpu_oracle_rate(16, 2, 1)
+        rate, spp, cores = cpu_oracle_rate(CPU_SAMPLE_SLIDES, CPU_SAMPLE_STEPS, 1)          # ~10 s of host work
         cpu = {"value": rate, "unit": "slides/s", "cores": cores, "kind": "port",
-               "sample": "16 BRCA-shaped slides per step, fwd+bwd, 2 timed steps after 1 warm-up (oracle/paths_oracle.py, torch CPU)"}
+               "sample": f"{CPU_SAMPLE_SLIDES} BRCA-shaped slides per step, fwd+bwd, {CPU_SAMPLE_STEPS} timed steps after 1 warm-up (oracle/paths_oracle.py, torch CPU)"}
 
     # full-size consistency (no oracle at this size): the resident path (features gathered from the HBM store) and the
     # end-to-end path (the same features arriving as the padded host batch) must compute the same loss, step after step
