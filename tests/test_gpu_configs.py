@@ -208,3 +208,17 @@ def test_cfg3_training_parity_96_slides():
     model, rt, hz, loss = _run(cfg, sd, slides, 1, grad=True)
     ocfg = po.OracleConfig.from_config(cfg)
     check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, 1)
+
+
+@pytest.mark.parametrize("prec", [0, 1])
+def test_wide_model_dimensions(prec):
+    """Dimensions beyond the shipped configs': patch_embed_dim 1280 (> 1024: the LSTM backward kernel's multi-column-group
+    form), trans_dim 192 with 4 heads of 48 (> 128: two float4 column groups per lane in the importance/token backward,
+    the generic-head-width attention kernels), importance hidden 160, fwd+bwd against the oracle."""
+    cfg = _config(num_levels=3, top_k_patches=[6, 6], patch_embed_dim=1280, trans_dim=192, importance_mlp_hidden_dim=160,
+                  hierarchical_ctx_mlp_hidden_dim=192)
+    sd = _weights(cfg)
+    slides = synth.make_brca_batch(range(5), 3, cfg.model_config.patch_embed_dim, wrange=(3, 6), hrange=(2, 5))
+    ybin, cens = _labels(slides)
+    model, rt, hz, loss = _run(cfg, sd, slides, prec)
+    check_against_oracle(po.OracleConfig.from_config(cfg), sd, slides, ybin, cens, cfg, model, rt, hz, loss, prec)
