@@ -148,3 +148,30 @@ def test_step_is_reproducible():
         else:
             assert torch.equal(loss.detach(), ref_loss), it
             assert rel_err(g, ref_g) < 1e-5, it
+
+
+def test_device_prefetcher_early_exit_and_loader_errors():
+    """The helper thread of DevicePrefetcher: leaving the loop early shuts it down, an exception of the wrapped loader
+    surfaces in the consuming loop, device placement and values are those of the host batches."""
+    from paths_b200.data_utils.prefetch import DevicePrefetcher
+
+    def mk(i):
+        return {"fts": torch.full((2, 3, 4), float(i)), "survival_bin": torch.tensor([i, i + 1]), "censored": torch.tensor([0, 1]),
+                "slide": ["a", "b"]}
+
+    it = iter(DevicePrefetcher((mk(i) for i in range(5)), "cuda"))
+    b0 = next(it)
+    assert b0["fts"].is_cuda and b0["survival_bin"].is_cuda and b0["slide"] == ["a", "b"]
+    assert float(b0["fts"].sum()) == 0.0
+    b1 = next(it)
+    assert float(b1["fts"].mean()) == 1.0
+    it.close()                                                  # early exit: the worker is joined, nothing hangs
+
+    def bad():
+        yield mk(0)
+        raise ValueError("loader failed")
+
+    with pytest.raises(ValueError, match="loader failed"):
+        for _ in DevicePrefetcher(bad(), torch.device("cuda", 0)):
+            pass
+    assert [float(b["fts"].mean()) for b in DevicePrefetcher((mk(i) for i in range(4)), "cuda")] == [0.0, 1.0, 2.0, 3.0]
