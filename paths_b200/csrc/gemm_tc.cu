@@ -180,6 +180,9 @@ __global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host,
 // (the engine spaces the regions by at least that much).
 // With `csum` the pass also accumulates the column sums of the live rows into csum.p[group] (K <= 512): the bias gradient
 // that would otherwise need its own pass over the same tensor.
+// J = float4 column groups per lane in use (ceil(min(K, 512) / 128)), R = rows per warp iteration: a 128-column row is ONE
+// 16-byte load per lane, so several rows are loaded before the first is stored to keep enough bytes in flight per SM.
+template <int J, int R>
 __global__ void __launch_bounds__(256) split_planes_grp_kernel(const float* __restrict__ A, int lda, int K, Planes dst, Grp grp, int want_lo,
                                                                MutL csum) {
   const int gi = blockIdx.y;
@@ -194,32 +197,51 @@ __global__ void __launch_bounds__(256) split_planes_grp_kernel(const float* __re
   const int r0 = pick(grp.roff, gi);
   const int lane = threadIdx.x & 31;
   float* cs = pick(csum.p, gi);
-  float4 acc[4];
+  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 acc[J];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int m = blockIdx.x * 8 + (threadIdx.x >> 5); m < Mfill; m += gridDim.x * 8) {
-    const float* row = A + (size_t)(r0 + m) * lda;
+  for (int j = 0; j < J; ++j) acc[j] = z4;
+  const int stride = gridDim.x * 8;
+  for (int m0 = blockIdx.x * 8 + (threadIdx.x >> 5); m0 < Mfill; m0 += R * stride) {
+    float4 x[R][J];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int k = lane * 4 + 128 * j;
-      if (k < K) {
-        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (m < M) x = __ldg(reinterpret_cast<const float4*>(row + k));
-        planes_store4(dst, r0 + m, k, x, want_lo != 0);
-        acc[j].x += x.x; acc[j].y += x.y; acc[j].z += x.z; acc[j].w += x.w;
+    for (int r = 0; r < R; ++r) {
+      const int m = m0 + r * stride;
+      const float* row = A + (size_t)(r0 + m) * lda;
+#pragma unroll
+      for (int j = 0; j < J; ++j) {
+        const int k = lane * 4 + 128 * j;
+        x[r][j] = z4;
+        if (m < M && k < K) x[r][j] = __ldg(reinterpret_cast<const float4*>(row + k));
       }
     }
-    for (int k = lane * 4 + 512; k < K; k += 128) {        // wider rows (no column sums there)
-      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (m < M) x = __ldg(reinterpret_cast<const float4*>(row + k));
-      planes_store4(dst, r0 + m, k, x, want_lo != 0);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int m = m0 + r * stride;
+      if (m >= Mfill) continue;                              // warp-uniform
+#pragma unroll
+      for (int j = 0; j < J; ++j) {
+        const int k = lane * 4 + 128 * j;
+        if (k < K) {
+          planes_store4(dst, r0 + m, k, x[r][j], want_lo != 0);
+          acc[j].x += x[r][j].x; acc[j].y += x[r][j].y; acc[j].z += x[r][j].z; acc[j].w += x[r][j].w;
+        }
+      }
+      if (J == 4) {
+        const float* row = A + (size_t)(r0 + m) * lda;
+        for (int k = lane * 4 + 512; k < K; k += 128) {      // wider rows (no column sums there)
+          float4 xw = z4;
+          if (m < M) xw = __ldg(reinterpret_cast<const float4*>(row + k));
+          planes_store4(dst, r0 + m, k, xw, want_lo != 0);
+        }
+      }
     }
   }
   if (cs == nullptr) return;                               // block-uniform
   __shared__ float4 part[8][128];
   const int w = threadIdx.x >> 5;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) part[w][lane + 32 * j] = acc[j];
+  for (int j = 0; j < 4; ++j) part[w][lane + 32 * j] = j < J ? acc[j < J ? j : 0] : z4;
   __syncthreads();
   if (threadIdx.x < 128) {
     const int j = threadIdx.x >> 5, ln = threadIdx.x & 31;
@@ -1067,7 +1089,12 @@ int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp&
   const int lim = grp.n > 1 ? 4 * kNumSMs : 16 * kNumSMs;
   if (g > lim) g = lim;
   if (colsum && g > kNumSMs) g = kNumSMs;                    // fewer blocks: fewer same-address atomics at the end
-  split_planes_grp_kernel<<<dim3(g, grp.n), 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, colsum ? *colsum : mutl1(nullptr));
+  const MutL cs = colsum ? *colsum : mutl1(nullptr);
+  const dim3 grid(g, grp.n);
+  if (K <= 128) split_planes_grp_kernel<1, 4><<<grid, 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
+  else if (K <= 256) split_planes_grp_kernel<2, 2><<<grid, 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
+  else if (K <= 384) split_planes_grp_kernel<3, 2><<<grid, 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
+  else split_planes_grp_kernel<4, 1><<<grid, 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
   PATHS_LAUNCH_CK();
   return 0;
 }
