@@ -768,6 +768,172 @@ __global__ void __launch_bounds__(TPB) ln_bwd_kernel(const float* __restrict__ d
   }
 }
 
+// ---- 16-byte forms of the two LayerNorm kernels (d % 4 == 0): a lane owns the float4 column groups lane + 32 q (Q = ceil(d / 128)),
+// a warp works on LNR rows at a time with every load issued before the first use.  The scalar forms above issue four times the
+// instructions and keep one 4-byte load per lane in flight (2.5 TB/s on the grouped launches).
+constexpr int LNR = 2;
+template <int Q>
+__global__ void __launch_bounds__(TPB) res_ln_fwd4_kernel(const float* __restrict__ res, GIdx ri, const float* __restrict__ add, PtrL biasl,
+                                                          PtrL gammal, PtrL betal, float* __restrict__ y, float* __restrict__ xhat,
+                                                          float* __restrict__ rstd, int d, float eps, Grp grp) {
+  const int gi = blockIdx.y;
+  const int M = grp_count(grp, gi);
+  const size_t r0 = pick(grp.roff, gi);
+  const int* ridx = pick(ri.idx.p, gi);
+  if (res) res += (size_t)(ridx ? pick(ri.roff, gi) : r0) * d;
+  if (add) add += r0 * d;
+  y += r0 * d; xhat += r0 * d; rstd += r0;
+  const float* __restrict__ bias = pick(biasl.p, gi); const float* __restrict__ gamma = pick(gammal.p, gi);
+  const float* __restrict__ beta = pick(betal.p, gi);
+  const int lane = threadIdx.x & 31;
+  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 b4[Q], g4[Q], e4[Q];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    const int c = 4 * lane + 128 * q;
+    b4[q] = (bias && c < d) ? ld4(bias + c) : z4;
+    g4[q] = c < d ? ld4(gamma + c) : z4;
+    e4[q] = c < d ? ld4(beta + c) : z4;
+  }
+  const int stride = gridDim.x * WPB;
+  const float inv_d = 1.f / d;
+  for (int m0 = blockIdx.x * WPB + (threadIdx.x >> 5); m0 < M; m0 += LNR * stride) {
+    float4 v[LNR][Q];
+#pragma unroll
+    for (int r = 0; r < LNR; ++r) {
+      const int m = m0 + r * stride;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int c = 4 * lane + 128 * q;
+        float4 x = z4;
+        if (m < M && c < d) {
+          if (res) x = ld4(res + (size_t)(ridx ? ridx[m] : m) * d + c);
+          if (add) { const float4 a = ld4(add + (size_t)m * d + c); x.x += a.x; x.y += a.y; x.z += a.z; x.w += a.w; }
+          x.x += b4[q].x; x.y += b4[q].y; x.z += b4[q].z; x.w += b4[q].w;
+        }
+        v[r][q] = x;
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < LNR; ++r) {
+      const int m = m0 + r * stride;
+      if (m >= M) continue;                                  // warp-uniform
+      float s = 0.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) s += (v[r][q].x + v[r][q].y) + (v[r][q].z + v[r][q].w);
+      const float mean = warp_sum(s) * inv_d;
+      float var = 0.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        if (4 * lane + 128 * q < d) {
+          const float tx = v[r][q].x - mean, ty = v[r][q].y - mean, tz = v[r][q].z - mean, tw = v[r][q].w - mean;
+          var += (tx * tx + ty * ty) + (tz * tz + tw * tw);
+        }
+      }
+      var = warp_sum(var) * inv_d;
+      const float rs = rsqrtf(var + eps);
+      if (lane == 0) rstd[m] = rs;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int c = 4 * lane + 128 * q;
+        if (c < d) {
+          const float4 xh = make_float4((v[r][q].x - mean) * rs, (v[r][q].y - mean) * rs, (v[r][q].z - mean) * rs, (v[r][q].w - mean) * rs);
+          st4(xhat + (size_t)m * d + c, xh);
+          st4(y + (size_t)m * d + c, make_float4(xh.x * g4[q].x + e4[q].x, xh.y * g4[q].y + e4[q].y, xh.z * g4[q].z + e4[q].z,
+                                                  xh.w * g4[q].w + e4[q].w));
+        }
+      }
+    }
+  }
+}
+
+template <int Q>
+__global__ void __launch_bounds__(TPB) ln_bwd4_kernel(const float* __restrict__ dy, const float* __restrict__ dy2,
+                                                      const float* __restrict__ xhat, const float* __restrict__ rstd, PtrL gammal,
+                                                      float* __restrict__ dx, GIdx di, int accum, MutL dgammal, MutL dbetal, MutL dbiasl,
+                                                      int d, Grp grp) {
+  const int gi = blockIdx.y;
+  const int M = grp_count(grp, gi);
+  const size_t r0 = pick(grp.roff, gi);
+  const int* didx = pick(di.idx.p, gi);
+  dy += r0 * d; if (dy2) dy2 += r0 * d;
+  xhat += r0 * d; rstd += r0;
+  dx += (size_t)(didx ? pick(di.roff, gi) : r0) * d;
+  const float* __restrict__ gamma = pick(gammal.p, gi);
+  float* dgamma = pick(dgammal.p, gi); float* dbeta = pick(dbetal.p, gi); float* dbias = pick(dbiasl.p, gi);
+  const int lane = threadIdx.x & 31;
+  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 a_g[Q], a_b[Q], a_x[Q], g4[Q];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { a_g[q] = a_b[q] = a_x[q] = z4; const int c = 4 * lane + 128 * q; g4[q] = c < d ? ld4(gamma + c) : z4; }
+  const int stride = gridDim.x * WPB;
+  const float inv_d = 1.f / d;
+  for (int m0 = blockIdx.x * WPB + (threadIdx.x >> 5); m0 < M; m0 += LNR * stride) {
+    float4 dv[LNR][Q], xh[LNR][Q], ov[LNR][Q];
+    float rs[LNR];
+#pragma unroll
+    for (int r = 0; r < LNR; ++r) {
+      const int m = m0 + r * stride;
+      rs[r] = 0.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int c = 4 * lane + 128 * q;
+        dv[r][q] = xh[r][q] = ov[r][q] = z4;
+        if (m < M && c < d) {
+          dv[r][q] = ld4(dy + (size_t)m * d + c);
+          if (dy2) { const float4 a = ld4(dy2 + (size_t)m * d + c); dv[r][q].x += a.x; dv[r][q].y += a.y; dv[r][q].z += a.z; dv[r][q].w += a.w; }
+          xh[r][q] = ld4(xhat + (size_t)m * d + c);
+          if (accum) ov[r][q] = ld4(dx + (size_t)(didx ? didx[m] : m) * d + c);
+        }
+      }
+      if (m < M) rs[r] = rstd[m];
+    }
+#pragma unroll
+    for (int r = 0; r < LNR; ++r) {
+      const int m = m0 + r * stride;
+      if (m >= M) continue;                                  // warp-uniform
+      float4 g[Q];
+      float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const float4 a = dv[r][q], x = xh[r][q];
+        a_g[q].x += a.x * x.x; a_g[q].y += a.y * x.y; a_g[q].z += a.z * x.z; a_g[q].w += a.w * x.w;
+        a_b[q].x += a.x; a_b[q].y += a.y; a_b[q].z += a.z; a_b[q].w += a.w;
+        g[q] = make_float4(a.x * g4[q].x, a.y * g4[q].y, a.z * g4[q].z, a.w * g4[q].w);
+        s1 += (g[q].x + g[q].y) + (g[q].z + g[q].w);
+        s2 += (g[q].x * x.x + g[q].y * x.y) + (g[q].z * x.z + g[q].w * x.w);
+      }
+      s1 = warp_sum(s1) * inv_d; s2 = warp_sum(s2) * inv_d;
+      float* o = dx + (size_t)(didx ? didx[m] : m) * d;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int c = 4 * lane + 128 * q;
+        if (c < d) {
+          const float4 x = xh[r][q];
+          const float4 vv = make_float4(rs[r] * (g[q].x - s1 - x.x * s2), rs[r] * (g[q].y - s1 - x.y * s2), rs[r] * (g[q].z - s1 - x.z * s2),
+                                        rs[r] * (g[q].w - s1 - x.w * s2));
+          a_x[q].x += vv.x; a_x[q].y += vv.y; a_x[q].z += vv.z; a_x[q].w += vv.w;
+          st4(o + c, make_float4(ov[r][q].x + vv.x, ov[r][q].y + vv.y, ov[r][q].z + vv.z, ov[r][q].w + vv.w));
+        }
+      }
+    }
+  }
+  __shared__ float4 red[WPB][3][32 * Q];
+  const int w = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { red[w][0][lane + 32 * q] = a_g[q]; red[w][1][lane + 32 * q] = a_b[q]; red[w][2][lane + 32 * q] = a_x[q]; }
+  __syncthreads();
+  for (int e = threadIdx.x; e < 3 * 32 * Q; e += TPB) {
+    const int k = e / (32 * Q), c4 = e % (32 * Q), c = 4 * c4;
+    float* o = k == 0 ? dgamma : k == 1 ? dbeta : dbias;
+    if (c >= d || o == nullptr) continue;
+    float4 t = red[0][k][c4];
+#pragma unroll
+    for (int ww = 1; ww < WPB; ++ww) { const float4 u = red[ww][k][c4]; t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+    atomicAdd(o + c, t.x); atomicAdd(o + c + 1, t.y); atomicAdd(o + c + 2, t.z); atomicAdd(o + c + 3, t.w);
+  }
+}
+
 // relu backward in place: dH *= (H > 0)
 // dH *= (H > 0); optionally dbias[c] += sum_m dH[m, c] in the same pass (the bias gradient of the layer that fed the ReLU).
 // ld % 4 == 0; a thread keeps one float4 column group and walks rows, so the column sums need one shared-memory combine
@@ -1151,7 +1317,19 @@ int res_ln_fwd_grp(const float* res, const GIdx& ridx, const float* add, const P
   if (cap <= 0) return 0;
   int g = row_grid(cap);
   if (grp.n > 1 && g > 2 * kNumSMs) g = 2 * kNumSMs;
-  res_ln_fwd_kernel<<<dim3(g, grp.n), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
+  const bool al16 = ((reinterpret_cast<uintptr_t>(res) | reinterpret_cast<uintptr_t>(add) | reinterpret_cast<uintptr_t>(y) |
+                      reinterpret_cast<uintptr_t>(xhat)) & 15) == 0;
+  bool vec = d % 4 == 0 && al16;
+  for (int i = 0; i < grp.n; ++i)
+    vec = vec && ((reinterpret_cast<uintptr_t>(bias.p[i]) | reinterpret_cast<uintptr_t>(gamma.p[i]) | reinterpret_cast<uintptr_t>(beta.p[i])) & 15) == 0;
+  if (vec) {
+    g = (cap + WPB * LNR - 1) / (WPB * LNR);
+    if (g > 4 * kNumSMs) g = 4 * kNumSMs;
+    if (d <= 128) res_ln_fwd4_kernel<1><<<dim3(g, grp.n), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
+    else res_ln_fwd4_kernel<2><<<dim3(g, grp.n), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
+  } else {
+    res_ln_fwd_kernel<<<dim3(g, grp.n), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
+  }
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1167,7 +1345,16 @@ int ln_bwd_grp(const float* dy, const float* dy2, const float* xhat, const float
   int g = row_grid(cap);
   const int lim = grp.n > 1 ? kNumSMs : 2 * kNumSMs;
   if (g > lim) g = lim;
-  ln_bwd_kernel<<<dim3(g, grp.n), TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
+  const bool al16 = ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dy2) | reinterpret_cast<uintptr_t>(dx) |
+                      reinterpret_cast<uintptr_t>(xhat)) & 15) == 0;
+  bool vec = d % 4 == 0 && d <= 256 && al16;
+  for (int i = 0; i < grp.n; ++i) vec = vec && (reinterpret_cast<uintptr_t>(gamma.p[i]) & 15) == 0;
+  if (vec) {
+    if (d <= 128) ln_bwd4_kernel<1><<<dim3(g, grp.n), TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
+    else ln_bwd4_kernel<2><<<dim3(g, grp.n), TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
+  } else {
+    ln_bwd_kernel<<<dim3(g, grp.n), TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
+  }
   PATHS_LAUNCH_CK();
   return 0;
 }
