@@ -88,18 +88,33 @@ __global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(float* __restrict_
   const int ldg = 3 * C + D;
   const int Mw = YP.p ? planes_rows_to_write(YP, M) : M;
   ROW_LOOP(m, Mw) {
-    for (int j4 = lane; j4 < D / 4; j4 += 32) {
-      const int j = 4 * j4;
-      if (m >= M) { planes_store4(YP, m, j, make_float4(0.f, 0.f, 0.f, 0.f), want_lo); continue; }
-      float4 t = ld4(Pt + (size_t)m * D + j);
-      t.x = tanhf(t.x); t.y = tanhf(t.y); t.z = tanhf(t.z); t.w = tanhf(t.w);
-      st4(Pt + (size_t)m * D + j, t);                        // (recomputing tanh in the backward kernel costs more than these 4 KB/row)
-      const float4 o = ld4(G + (size_t)m * ldg + 3 * C + j), x = ld4(X + (size_t)m * D + j);
-      const float4 h = make_float4(o.x * t.x, o.y * t.y, o.z * t.z, o.w * t.w);
-      st4(H + (size_t)m * D + j, h);
-      const float4 y = make_float4(x.x + h.x, x.y + h.y, x.z + h.z, x.w + h.w);
-      if (Y) st4(Y + (size_t)m * D + j, y);
-      if (YP.p) planes_store4(YP, m, j, y, want_lo);
+    if (m >= M) {                                            // zero rows behind the live ones (planes only)
+      for (int j4 = lane; j4 < D / 4; j4 += 32) planes_store4(YP, m, 4 * j4, make_float4(0.f, 0.f, 0.f, 0.f), want_lo);
+      continue;
+    }
+    // four column groups per pass, all twelve 16-byte loads issued before the first store (P is read and written through the
+    // same pointer, so the compiler will not move the loads of a later group above the stores of an earlier one by itself)
+    for (int j0 = lane; j0 < D / 4; j0 += 4 * 32) {
+      float4 t[4], o[4], x[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = 4 * (j0 + 32 * u);
+        t[u] = o[u] = x[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (j < D) { t[u] = ld4(Pt + (size_t)m * D + j); o[u] = ld4(G + (size_t)m * ldg + 3 * C + j); x[u] = ld4(X + (size_t)m * D + j); }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = 4 * (j0 + 32 * u);
+        if (j >= D) continue;
+        float4 tt = t[u];
+        tt.x = tanhf(tt.x); tt.y = tanhf(tt.y); tt.z = tanhf(tt.z); tt.w = tanhf(tt.w);
+        st4(Pt + (size_t)m * D + j, tt);                     // (recomputing tanh in the backward kernel costs more than these 4 KB/row)
+        const float4 h = make_float4(o[u].x * tt.x, o[u].y * tt.y, o[u].z * tt.z, o[u].w * tt.w);
+        st4(H + (size_t)m * D + j, h);
+        const float4 y = make_float4(x[u].x + h.x, x[u].y + h.y, x[u].z + h.z, x[u].w + h.w);
+        if (Y) st4(Y + (size_t)m * D + j, y);
+        if (YP.p) planes_store4(YP, m, j, y, want_lo);
+      }
     }
   }
 }
