@@ -342,6 +342,86 @@ __global__ void __launch_bounds__(TPB) imp_tok_fwd_kernel(float* __restrict__ UV
   }
 }
 
+// mode 0 with 16-byte accesses (I, d multiples of 4, at most 256): a lane owns the float4 column groups lane + 32 q, a warp works on
+// two rows at a time with their loads issued before the first use (same scheme as imp_tok_bwd4_kernel below).
+template <int Q>
+__global__ void __launch_bounds__(TPB) imp_tok_fwd4_kernel(float* __restrict__ UV, const float* __restrict__ b1,
+                                                           const float* __restrict__ w2, const float* __restrict__ b2,
+                                                           const float* __restrict__ bin, const float* __restrict__ div,
+                                                           const int* __restrict__ row_slide, const int* __restrict__ row_xy,
+                                                           const int* __restrict__ seg, float* __restrict__ alpha,
+                                                           float* __restrict__ tok, int I, int d, int imp_mul, int pe_mode,
+                                                           int M_host, const int* M_dev) {
+  constexpr int R = 2;
+  const int M = row_count(M_host, M_dev);
+  const int ld = I + d;
+  const int lane = threadIdx.x & 31;
+  const int wid = blockIdx.x * WPB + (threadIdx.x >> 5), nw = gridDim.x * WPB;
+  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 b14[Q], w24[Q], bin4[Q];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    const int c = 4 * lane + 128 * q;
+    b14[q] = c < I ? ld4(b1 + c) : z4; w24[q] = c < I ? ld4(w2 + c) : z4; bin4[q] = c < d ? ld4(bin + c) : z4;
+  }
+  const float b2v = b2[0];
+  for (int m0 = wid; m0 < M; m0 += R * nw) {
+    float4 u4[R][Q], v4[R][Q];
+    int sl[R], px[R], py[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int m = m0 + r * nw;
+      sl[r] = px[r] = py[r] = 0;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) u4[r][q] = v4[r][q] = z4;
+      if (m < M) {
+        const float* uv = UV + (size_t)m * ld;
+        sl[r] = row_slide[m]; px[r] = row_xy[2 * m]; py[r] = row_xy[2 * m + 1];
+#pragma unroll
+        for (int q = 0; q < Q; ++q) {
+          const int c = 4 * lane + 128 * q;
+          if (c < I) u4[r][q] = ld4(uv + c);
+          if (c < d) v4[r][q] = ld4(uv + I + c);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int m = m0 + r * nw;
+      if (m >= M) continue;                                  // warp-uniform
+      float* uv = UV + (size_t)m * ld;
+      float s = 0.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int j = 4 * lane + 128 * q;
+        if (j < I) {
+          const float4 u = make_float4(fmaxf(u4[r][q].x + b14[q].x, 0.f), fmaxf(u4[r][q].y + b14[q].y, 0.f), fmaxf(u4[r][q].z + b14[q].z, 0.f),
+                                       fmaxf(u4[r][q].w + b14[q].w, 0.f));
+          st4(uv + j, u);
+          s += (u.x * w24[q].x + u.y * w24[q].y) + (u.z * w24[q].z + u.w * w24[q].w);
+        }
+      }
+      s = warp_sum(s) + b2v;
+      const float a = sigmoidf_(s);
+      if (lane == 0) alpha[m] = a;
+      const int i = m - seg[sl[r]];
+      float* t = tok + (size_t)(m + sl[r] + 1) * d;
+      const float sc = imp_mul ? a : 1.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int c = 4 * lane + 128 * q;
+        if (c < d) {
+          const float4 v = v4[r][q];
+          st4(t + c, make_float4(sc * v.x + bin4[q].x + pos_enc(pe_mode, div, d, c, px[r], py[r], i),
+                                 sc * v.y + bin4[q].y + pos_enc(pe_mode, div, d, c + 1, px[r], py[r], i),
+                                 sc * v.z + bin4[q].z + pos_enc(pe_mode, div, d, c + 2, px[r], py[r], i),
+                                 sc * v.w + bin4[q].w + pos_enc(pe_mode, div, d, c + 3, px[r], py[r], i)));
+        }
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(TPB) special_fill_kernel(const float* __restrict__ special, const int* __restrict__ seg,
                                                            float* __restrict__ tok, int d, int B) {
   ROW_LOOP(s, B) {
@@ -1253,8 +1333,18 @@ int imp_tok_fwd(float* UV, const float* b1, const float* w2, const float* b2, co
                 const int* M_dev, cudaStream_t st) {
   PATHS_REQUIRE(I <= 256 && d <= 256, "imp_tok: hidden dims above 256 are not supported (I=%d, d=%d)", I, d);
   if (M_host <= 0) return 0;
-  imp_tok_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul,
-                                                       pe_mode, mode, M_host, M_dev);
+  const bool vec = mode == 0 && I % 4 == 0 && d % 4 == 0 &&
+                   ((reinterpret_cast<uintptr_t>(UV) | reinterpret_cast<uintptr_t>(b1) | reinterpret_cast<uintptr_t>(w2) |
+                     reinterpret_cast<uintptr_t>(bin) | reinterpret_cast<uintptr_t>(tok)) & 15) == 0;
+  if (vec) {
+    int g = (M_host + 2 * WPB - 1) / (2 * WPB);
+    if (g > 8 * kNumSMs) g = 8 * kNumSMs;
+    if (I <= 128 && d <= 128) imp_tok_fwd4_kernel<1><<<g, TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul, pe_mode, M_host, M_dev);
+    else imp_tok_fwd4_kernel<2><<<g, TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul, pe_mode, M_host, M_dev);
+  } else {
+    imp_tok_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul,
+                                                         pe_mode, mode, M_host, M_dev);
+  }
   PATHS_LAUNCH_CK();
   return 0;
 }
