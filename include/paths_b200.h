@@ -27,7 +27,7 @@ extern "C" {
 
 #define PATHS_MAX_LEVELS 8
 #define PATHS_MAX_LAYERS 4
-#define PATHS_ABI_VERSION 4
+#define PATHS_ABI_VERSION 5
 
 /* model_config + the train_config fields the hot path reads (config.py:19-79). */
 typedef struct paths_dims {
@@ -93,6 +93,7 @@ enum paths_buffer {
   PATHS_BUF_HAZARDS, PATHS_BUF_LOSS, PATHS_BUF_DLOGITS, PATHS_BUF_OVERFLOW, PATHS_BUF_DF_IN, PATHS_BUF_DHROW, PATHS_BUF_DCROW,
   PATHS_BUF_LOSS_PER,
   PATHS_BUF_HF0,              /* FFN hidden activations of the level's first aggregator layer, [tokens, 4 * trans_dim] */
+  PATHS_BUF_RISK,             /* [B] survival risk score -sum_k prod_{j<=k} (1 - hazard_j) (eval.py:60-61), written with the loss */
   PATHS_BUF__COUNT
 };
 
@@ -128,8 +129,9 @@ int paths_engine_level_forward(paths_engine_t* e, int level, void* stream);
 /* Top-K select + child expansion + gather into level+1.  Replaces PreprocessedSlide.iter (data_utils/slide.py:277-360)
  * and collate_fn (data_utils/dataset.py:206-243). */
 int paths_engine_select(paths_engine_t* e, int level, void* stream);
-/* hazards/loss (+ dlogits) on the last level's logits: utils.py:263-277, nll_loss utils.py:283-305.
- * scale = 1 / global batch size (the loss is a batch mean). */
+/* hazards/loss (+ dlogits) on the last level's logits: utils.py:263-277, nll_loss utils.py:283-305, and the survival risk
+ * score the evaluator derives from the hazards (eval.py:60-61; PATHS_BUF_RISK).  scale = 1 / global batch size (the loss
+ * is a batch mean). */
 int paths_engine_loss(paths_engine_t* e, const int32_t* ybin, const int32_t* censored, float scale, void* stream);
 /* Backward of one level (autograd of the above); accumulates into the bound grad buffer.  use_dlogits: take the
  * level's PATHS_BUF_DLOGITS as upstream gradient of its logits (set for the last level by paths_engine_loss). */
@@ -144,6 +146,14 @@ int paths_engine_forward_padded(paths_engine_t* e, const int32_t* slide_ids, con
                                 const int32_t* censored, float scale, int with_loss, void* stream);
 /* loss.backward() of train.py:65: levels L-1..0.  zero_grads: clear the grad buffer first. */
 int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream);
+
+/* The no-child fallback of data_utils/slide.py:336-352 ("every non-background cell of the next grid") can give one slide a
+ * bag above the capacities the engine was sized for.  The kernels stay inside their buffers and raise a device flag; this
+ * call waits (host-side) until the LAST select of the latest forward pass has run -- not for the end of the pass -- and
+ * returns the flag and the row count that would have been needed.  A caller that sees the flag re-runs the step on an engine
+ * sized for the worst case before using any output (the Python mirror does; the reference handles the case inline).
+ * The only entry point that blocks the host. */
+int paths_engine_overflow_poll(paths_engine_t* e, int32_t* h_flag, int32_t* h_rows_needed);
 
 int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, size_t* bytes);
 int paths_engine_set_precision(paths_engine_t* e, int precision);
@@ -167,8 +177,8 @@ int paths_engine_profile_read(paths_engine_t* e, int tag, double* total_ms, int6
 
 /* Fused AdamW step over the flat parameter buffer -- torch.optim.AdamW as used by train.py:49,66.  params/exp_avg/exp_avg_sq
  * hold n_total floats, grads n_live; elements [n_live, n_total) (parameters whose gradient is identically zero: the dead
- * encoder / cross-attention weights) only receive the decoupled weight decay.  h_skip: n_skip host pairs [start, end) of
- * elements left untouched (parameters whose .grad the reference leaves at None).  step counts from 1. */
+ * encoder / cross-attention weights) only receive the decoupled weight decay.  h_skip: n_skip (<= 16) host pairs
+ * [start, end) of elements left untouched, in either part (parameters whose .grad the reference leaves at None).  step counts from 1. */
 int paths_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_live, int64_t n_total,
                      const int64_t* h_skip, int n_skip, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                      void* stream);

@@ -1,9 +1,11 @@
 """TEST INFRASTRUCTURE (CPU oracle) -- numpy restatement of the heat-map compositing block of the reference,
 heatmap_visualise.py:66-76 (convert_pix / to_pix_space) and 142-176 (rectangle fill, coarse-to-fine fold, zero fill, alpha).
 
-Parity UNPINNED by execution: the block is inline code of a script function that needs matplotlib / tiatoolbox (absent from
-this image), so it cannot be imported; the restatement follows the source line by line and the GPU kernel is held to it
-bit-exactly (tests/test_gpu_heatmap.py).  Only tests/ may import this module.
+Parity PINNED: the block is inline code of a script function that needs matplotlib / tiatoolbox (absent from this image),
+so it cannot be imported -- tests/golden/make_golden_heatmap.py instead reads the reference file, slices the helper
+definitions and the block (heatmap_visualise.py:68-76, 142-178) as text and executes them with `Rectangle` / `ax` stubbed;
+its outputs are committed (tests/golden/heatmap_ref.npz) and tests/test_heatmap_oracle.py holds this restatement to them
+bit for bit.  The GPU kernel is held to both (tests/test_gpu_heatmap.py).  Only tests/ may import this module.
 
 Note on dtype: `imp[i] + 1e-4` adds a python float to a numpy float32 scalar; under this image's numpy 2 (NEP 50) that is a
 float32 add (under the reference's pinned numpy 1.x it would have been float64).  The value is then stored in the float64

@@ -447,7 +447,7 @@ def end2end(sd: Dict[str, Tensor], cfg: OracleConfig, slides: Sequence[Sequence[
         hazards = torch.sigmoid(logits)
         loss = nll_loss(hazards, survival_bin, censored.to(dtype))
         return hazards, loss, recs
-    loss = F.cross_entropy(logits, subtype)
+    loss = F.cross_entropy(logits, subtype if subtype is not None else survival_bin)      # utils.py:274-278
     return logits, loss, recs
 
 

@@ -150,8 +150,11 @@ struct paths_engine {
   cudaEvent_t ev_tok[PATHS_MAX_LEVELS], ev_z[PATHS_MAX_LEVELS], ev_head[PATHS_MAX_LEVELS], ev_dtok[PATHS_MAX_LEVELS];
   bool have_streams;
   Planes dGP, dPP, dUVP;                                 // gradient planes written by the pointwise backward kernels
-  float *hazards, *loss, *loss_per;
+  float *hazards, *loss, *loss_per, *risk;
   int *overflow, *slide_cnt, *slide_fb;
+  // host-visible copy of the overflow flag: copied to pinned memory right after the LAST select of a forward pass (the rest of
+  // the pass is then still queued), so paths_engine_overflow_poll waits for a point the GPU passes well before the step ends
+  int* h_over; cudaEvent_t ev_sel; bool sel_recorded;
   const int* slide_ids;
   Params P, Gr;                                          // parameters and their gradients (same layout)
   float* grads_base; size_t grads_floats;
@@ -322,6 +325,7 @@ size_t carve(paths_engine* e, char* base) {
     e->dGP = e->dPP = e->dUVP = no_planes();
   }
   e->hazards = b.take<float>((size_t)B * dm.nl); e->loss = b.take<float>(1); e->loss_per = b.take<float>(B);
+  e->risk = b.take<float>(B);
   e->overflow = b.take<int>(2); e->slide_cnt = b.take<int>(B); e->slide_fb = b.take<int>(B);
   {
     size_t pb = dm.lstm ? packed_bytes(3 * C + D, 2 * D) + packed_bytes(D, C) : 0;
@@ -926,7 +930,7 @@ int do_select(paths_engine* e, int l, cudaStream_t st) {
   ProfScope ps_sel(e, PATHS_PROF_SELECT, st);
   SelectArgs a;
   a.alpha = v.alpha; a.seg = v.seg; a.row_xy = v.row_xy; a.count = v.count; a.B = e->B; a.cap = v.cap;
-  a.keep = dm.K[l]; a.kcap = v.kcap;
+  a.keep = dm.K[l]; a.kcap = v.kcap; a.maxseg = v.maxseg; a.n_maxseg = n.maxseg;
   a.gw = e->store.gw; a.gh = e->store.gh; a.occ_off = reinterpret_cast<const unsigned long long*>(e->store.occ_off);
   a.occ = e->store.occ; a.nonbg = e->store.nonbg; a.level = l; a.L = dm.L; a.slide_ids = e->slide_ids;
   a.sel = v.sel; a.sel_count = v.sel_count; a.child_of = v.child_of;
@@ -937,6 +941,14 @@ int do_select(paths_engine* e, int l, cudaStream_t st) {
   tseg_kernel<<<(e->B + 255) / 256, 256, 0, st>>>(n.seg, n.tseg, e->B);
   PATHS_LAUNCH_CK(); e->launches++;
   RUN(gather_rows(e->store.grid_ptr, e->store.gh, l + 1, dm.L, e->slide_ids, n.row_slide, n.row_xy, n.X, dm.D, n.cap, n.count, st));
+  return 0;
+}
+
+// Publishes the overflow flag as it stands after the selects enqueued so far (see paths_engine::h_over).
+int publish_overflow(paths_engine* e, cudaStream_t st) {
+  PATHS_CK(cudaMemcpyAsync(e->h_over, e->overflow, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  PATHS_CK(cudaEventRecord(e->ev_sel, st));
+  e->sel_recorded = true;
   return 0;
 }
 
@@ -958,7 +970,7 @@ int do_begin(paths_engine* e, const int32_t* slide_ids, const float* fts_padded,
 
 int do_loss(paths_engine* e, const int32_t* ybin, const int32_t* cens, float scale, cudaStream_t st) {
   Level& v = e->lv[e->dm.L - 1];
-  RUN(loss_fwd_bwd(v.logits, ybin, cens, e->hazards, e->loss_per, e->loss, v.dlogits, e->dm.nl, e->B, e->dm.task, scale, st));
+  RUN(loss_fwd_bwd(v.logits, ybin, cens, e->hazards, e->loss_per, e->loss, e->risk, v.dlogits, e->dm.nl, e->B, e->dm.task, scale, st));
   e->launches++;
   return 0;
 }
@@ -1051,6 +1063,9 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
     bool ok = cudaStreamCreateWithPriority(&e->mainp, cudaStreamNonBlocking, prio_greatest) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&e->ev_in, cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&e->ev_out, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_sel, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaHostAlloc(reinterpret_cast<void**>(&e->h_over), 2 * sizeof(int), cudaHostAllocDefault) == cudaSuccess;
+    if (ok) { e->h_over[0] = e->h_over[1] = 0; e->sel_recorded = false; }
     if (!ok) {
       set_error("could not create the engine streams / events: %s", cudaGetErrorString(cudaGetLastError()));
       delete e;
@@ -1096,7 +1111,8 @@ void paths_engine_destroy(paths_engine_t* e) {
   if (e->have_streams) {
     cudaStreamSynchronize(e->mainp);
     cudaStreamDestroy(e->mainp);
-    cudaEventDestroy(e->ev_in); cudaEventDestroy(e->ev_out);
+    cudaEventDestroy(e->ev_in); cudaEventDestroy(e->ev_out); cudaEventDestroy(e->ev_sel);
+    cudaFreeHost(e->h_over);
   }
   if (e->have_streams)
     for (int l = 0; l < e->dm.L; ++l) {
@@ -1241,7 +1257,17 @@ int paths_engine_level_forward(paths_engine_t* e, int level, void* stream) {
 
 int paths_engine_select(paths_engine_t* e, int level, void* stream) {
   PATHS_REQUIRE(e, "null engine");
-  return do_select(e, level, static_cast<cudaStream_t>(stream));
+  if (int r = do_select(e, level, static_cast<cudaStream_t>(stream))) return r;
+  return publish_overflow(e, static_cast<cudaStream_t>(stream));
+}
+
+int paths_engine_overflow_poll(paths_engine_t* e, int32_t* h_flag, int32_t* h_rows_needed) {
+  PATHS_REQUIRE(e && h_flag && h_rows_needed, "null argument");
+  *h_flag = 0; *h_rows_needed = 0;
+  if (!e->sel_recorded) return 0;
+  PATHS_CK(cudaEventSynchronize(e->ev_sel));
+  *h_flag = e->h_over[0]; *h_rows_needed = e->h_over[1];
+  return 0;
 }
 
 int paths_engine_loss(paths_engine_t* e, const int32_t* ybin, const int32_t* censored, float scale, void* stream) {
@@ -1293,11 +1319,15 @@ static int forward_impl(paths_engine_t* e, const int32_t* slide_ids, const float
     st = e->mainp;
   }
   if (int r = do_begin(e, slide_ids, fts_padded, N, st)) return r;
+  if (L == 1)
+    if (int r = publish_overflow(e, st)) return r;
   if (!conc) {
     for (int l = 0; l < L; ++l) {
       if (int r = level_forward(e, l, st)) return r;
       if (l < L - 1)
         if (int r = do_select(e, l, st)) return r;
+      if (l == L - 2)
+        if (int r = publish_overflow(e, st)) return r;
     }
   } else {
     for (int l = 0; l < L; ++l) {
@@ -1313,6 +1343,8 @@ static int forward_impl(paths_engine_t* e, const int32_t* slide_ids, const float
       }
       if (l < L - 1)
         if (int r = do_select(e, l, st)) return r;
+      if (l == L - 2)
+        if (int r = publish_overflow(e, st)) return r;
     }
     for (int si = 0; si < e->n_fsets; ++si) PATHS_CK(cudaStreamWaitEvent(st, e->ev_z[si], 0));
     for (int l = 0; l < L; ++l)
@@ -1396,6 +1428,7 @@ int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, siz
     case PATHS_BUF_HAZARDS: p = e->hazards; n = B * dm.nl * f; break;
     case PATHS_BUF_LOSS: p = e->loss; n = f; break;
     case PATHS_BUF_LOSS_PER: p = e->loss_per; n = B * f; break;
+    case PATHS_BUF_RISK: p = e->risk; n = B * f; break;
     case PATHS_BUF_OVERFLOW: p = e->overflow; n = 2 * i4; break;
     case PATHS_BUF_DF_IN: p = v.dFl; n = B * dm.d * f; break;
     case PATHS_BUF_DHROW: p = v.dHrow; n = cap * dm.D * f; break;

@@ -4,13 +4,15 @@
 // Parameters whose gradient the reference leaves at None (classifiers of levels 0..L-2) are skipped entirely, as torch
 // skips them; the dead encoder / cross-attention parameters (exact-zero gradients) sit in the tail [n_live, n_total) and
 // only receive the decoupled weight decay (their moments stay zero), which is bit-identical to torch's update for g = 0.
+// Modules the forward pass never evaluates (procs.0.hctx_mlp of the RNN variant, every hctx_mlp without hierarchical_ctx)
+// also sit in the tail but keep .grad = None in the reference: they arrive in the skip list and are left untouched.
 #include "../../include/paths_b200.h"
 #include "common.cuh"
 
 namespace paths {
 namespace {
 
-struct SkipList { long long a[8], b[8]; int n; };
+struct SkipList { long long a[16], b[16]; int n; };
 
 __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                     float* __restrict__ v, long long n_live, long long n_total, SkipList skip,
@@ -43,10 +45,13 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const
       reinterpret_cast<float4*>(m)[i] = mv;
       reinterpret_cast<float4*>(v)[i] = vv;
     } else {
+      // (n_live is a multiple of 64 floats by construction, so a float4 never straddles the live / dead boundary)
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (e0 + k >= n_live) pe[k] *= (1.f - lr * wd);
-        // (n_live is a multiple of 64 floats by construction, so a float4 never straddles the live / dead boundary)
+      for (int k = 0; k < 4; ++k) {
+        bool sk = e0 + k < n_live;
+        for (int s = 0; s < skip.n; ++s) sk |= (e0 + k >= skip.a[s] && e0 + k < skip.b[s]);   // never-evaluated modules: grad None
+        if (!sk) pe[k] *= (1.f - lr * wd);
+      }
     }
     reinterpret_cast<float4*>(p)[i] = pv;
   }
@@ -61,7 +66,7 @@ extern "C" int paths_adamw_step(float* params, const float* grads, float* exp_av
   using namespace paths;
   PATHS_REQUIRE(params && grads && exp_avg && exp_avg_sq, "adamw: null buffer");
   PATHS_REQUIRE(n_live >= 0 && n_total >= n_live && n_live % 4 == 0 && n_total % 4 == 0, "adamw: sizes must be multiples of 4 floats");
-  PATHS_REQUIRE(n_skip >= 0 && n_skip <= 8 && step >= 1, "adamw: at most 8 skipped ranges; step counts from 1");
+  PATHS_REQUIRE(n_skip >= 0 && n_skip <= 16 && step >= 1, "adamw: at most 16 skipped ranges; step counts from 1");
   SkipList sk; sk.n = n_skip;
   for (int i = 0; i < n_skip; ++i) { sk.a[i] = h_skip[2 * i]; sk.b[i] = h_skip[2 * i + 1]; }
   const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);

@@ -1206,8 +1206,9 @@ __global__ void __launch_bounds__(TPB) head_bwd_kernel(const float* __restrict__
 // survival NLL (utils.py:283-305, alpha=0.4, eps=1e-7, mean over the batch) on hazards = sigmoid(logits) (utils.py:269),
 // and its gradient w.r.t. the logits.  task 1: cross-entropy (utils.py:277).
 __global__ void loss_kernel(const float* __restrict__ logits, const int* __restrict__ ybin, const int* __restrict__ cens,
-                            float* __restrict__ hazards, float* __restrict__ loss_per, float* __restrict__ dlogits,
-                            int nl, int B, int task, float alpha, float eps, float scale /* 1 / global batch */) {
+                            float* __restrict__ hazards, float* __restrict__ loss_per, float* __restrict__ risk,
+                            float* __restrict__ dlogits, int nl, int B, int task, float alpha, float eps,
+                            float scale /* 1 / global batch */) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= B) return;
   const float* lg = logits + (size_t)s * nl;
@@ -1215,9 +1216,11 @@ __global__ void loss_kernel(const float* __restrict__ logits, const int* __restr
   if (task == 0) {
     const float c = (float)cens[s];
     float surv_y = 1.f, surv_y1 = 1.f, hy = 0.f;
+    float surv = 1.f, rk = 0.f;                                         // eval.py:60-61: risk = -sum(cumprod(1 - hazards))
     for (int k = 0; k < nl; ++k) {
       const float h = sigmoidf_(lg[k]);
       hazards[(size_t)s * nl + k] = h;
+      surv *= (1.f - h); rk -= surv;
       if (k < y) surv_y *= (1.f - h);
       if (k <= y) surv_y1 *= (1.f - h);
       if (k == y) hy = h;
@@ -1225,6 +1228,7 @@ __global__ void loss_kernel(const float* __restrict__ logits, const int* __restr
     const float unc = -(1.f - c) * (logf(fmaxf(surv_y, eps)) + logf(fmaxf(hy, eps)));
     const float cen = -c * logf(fmaxf(surv_y1, eps));
     loss_per[s] = (1.f - alpha) * (cen + unc) + alpha * unc;
+    if (risk) risk[s] = rk;
     // d loss / d unc = 1 ; d loss / d cen = (1 - alpha)
     if (dlogits) {
       const float w_sy = (surv_y > eps) ? -(1.f - c) : 0.f;              // coefficient of log S_pad[y]
@@ -1246,6 +1250,7 @@ __global__ void loss_kernel(const float* __restrict__ logits, const int* __restr
     for (int k = 0; k < nl; ++k) se += expf(lg[k] - mx);
     const float lse = mx + logf(se);
     loss_per[s] = lse - lg[y];
+    if (risk) risk[s] = 0.f;                                            // no risk score for the classification task
     for (int k = 0; k < nl; ++k) {
       hazards[(size_t)s * nl + k] = lg[k];
       if (dlogits) dlogits[(size_t)s * nl + k] = scale * (expf(lg[k] - lse) - (k == y ? 1.f : 0.f));
@@ -1535,9 +1540,9 @@ int head_bwd(const float* dlogits, const float* dF_in, const float* Wc, float* d
   PATHS_LAUNCH_CK();
   return 0;
 }
-int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* hazards, float* loss_per, float* loss, float* dlogits, int nl,
-                 int B, int task, float scale, cudaStream_t st) {
-  loss_kernel<<<(B + 127) / 128, 128, 0, st>>>(logits, ybin, cens, hazards, loss_per, dlogits, nl, B, task, 0.4f, 1e-7f, scale);
+int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* hazards, float* loss_per, float* loss, float* risk, float* dlogits,
+                 int nl, int B, int task, float scale, cudaStream_t st) {
+  loss_kernel<<<(B + 127) / 128, 128, 0, st>>>(logits, ybin, cens, hazards, loss_per, risk, dlogits, nl, B, task, 0.4f, 1e-7f, scale);
   PATHS_LAUNCH_CK();
   loss_reduce_kernel<<<1, 256, 0, st>>>(loss_per, loss, B, scale);
   PATHS_LAUNCH_CK();

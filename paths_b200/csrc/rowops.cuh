@@ -75,8 +75,8 @@ int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaS
 int scatter_add_rows(const float* src, const int* idx, float* dst, int d, int B, cudaStream_t st);
 int head_fwd(const float* z, const float* Fprev, const float* Wc, const float* bc, float* F, float* logits, int d, int nl, int B, cudaStream_t st);
 int head_bwd(const float* dlogits, const float* dF_in, const float* Wc, float* dF, int d, int nl, int B, cudaStream_t st);
-int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* hazards, float* loss_per, float* loss, float* dlogits, int nl,
-                 int B, int task, float scale, cudaStream_t st);
+int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* hazards, float* loss_per, float* loss, float* risk, float* dlogits,
+                 int nl, int B, int task, float scale, cudaStream_t st);
 
 // attention.cu -- varlen softmax self-attention over packed token rows.  qkv is [ntok, 3d] (q | k | v), heads of width dh.
 // Slide s owns token rows [seg[s]+s, seg[s+1]+s+1).  nq_mode 0: every token is a query; 1: only token 0 of each slide
@@ -105,6 +105,8 @@ struct SelectArgs {
   const float* alpha; const int* seg; const int* row_xy; const int* count; int B; int cap;
   int keep;                       // K (-1 = keep all)
   int kcap;                       // per-slide bound on kept rows (host): K, or the per-slide row bound when K = -1
+  int maxseg;                     // per-slide bound on the rows of level l the buffers were sized for
+  int n_maxseg;                   // ... and of level l+1
   // pyramid store, level l+1
   const int* gw; const int* gh; const unsigned long long* occ_off; const unsigned int* occ; const int* nonbg; int level; int L;
   const int* slide_ids;

@@ -35,14 +35,17 @@ __device__ __forceinline__ Cand candidate(const SelectArgs& a, int s, int sid, i
 __global__ void __launch_bounds__(ST) select_topk_kernel(SelectArgs a) {
   const int s = blockIdx.x, t = threadIdx.x;
   const int sid = a.slide_ids ? a.slide_ids[s] : s;
-  const int base = a.seg[s], n = a.seg[s + 1] - base;
+  // A bag above the level's per-slide bound (a fallback bag that fitted the batch-wide slack, slide.py:336-352) has already
+  // raised the overflow flag and the host re-runs the step with worst-case buffers: clamp so this pass stays inside sel[] and
+  // the `taken` bitmap whatever the bag holds.
+  const int base = a.seg[s], n = min(a.seg[s + 1] - base, a.keep < 0 ? min(a.maxseg, a.kcap) : min(a.maxseg, MAX_N_BITS));
   const int k = a.keep < 0 ? n : min(n, a.keep);
   __shared__ unsigned int taken[MAX_N_BITS / 32];
   __shared__ float rv[ST / 32];
   __shared__ int ri[ST / 32];
   __shared__ int cnt_red[ST / 32];
 
-  for (int i = t; i < n * 4; i += ST) a.child_of[(size_t)base * 4 + i] = -1;
+  for (int i = t; i < (a.seg[s + 1] - base) * 4; i += ST) a.child_of[(size_t)base * 4 + i] = -1;
 
   if (a.keep < 0) {
     for (int i = t; i < n; i += ST) a.sel[(size_t)s * a.kcap + i] = base + i;           // keep all, original order (slide.py:294)
@@ -103,8 +106,12 @@ __global__ void __launch_bounds__(1024) select_scan_kernel(SelectArgs a) {
   const int t = threadIdx.x;
   const int per = (a.B + 1023) / 1024;
   int loc = 0;
-  for (int i = t * per; i < min(a.B, (t + 1) * per); ++i) loc += a.slide_cnt[i];
+  int big = 0;                                     // largest bag of the next level
+  for (int i = t * per; i < min(a.B, (t + 1) * per); ++i) { loc += a.slide_cnt[i]; big = max(big, a.slide_cnt[i]); }
   part[t] = loc;
+  // one slide's bag above the next level's per-slide bound (the no-child fallback can do that while the batch total still
+  // fits): the attention launches and the next select are sized from that bound, so the step must be re-run
+  if (big > a.n_maxseg) { a.overflow[0] = 1; atomicMax(a.overflow + 1, a.n_cap + big); }
   __syncthreads();
   for (int o = 1; o < 1024; o <<= 1) {             // Hillis-Steele inclusive scan
     const int v = t >= o ? part[t - o] : 0;

@@ -366,5 +366,13 @@ class Engine:
         return [int(self.buffer(l, "COUNT").item()) for l in range(self.dims.L)]
 
     def overflowed(self) -> Tuple[bool, int]:
+        """Overflow flag read straight from the device (full synchronisation; tests / reporting)."""
         o = self.buffer(0, "OVERFLOW").tolist()
         return bool(o[0]), int(o[1])
+
+    def overflow_poll(self) -> Tuple[bool, int]:
+        """Did a slide's bag exceed the capacities this engine was sized for (no-child fallback, slide.py:336-352)?  Waits only
+        until the last select of the latest forward pass has run on the device, not for the end of the pass."""
+        flag, need = C.c_int32(), C.c_int32()
+        L.check(self.lib.paths_engine_overflow_poll(self.handle, C.byref(flag), C.byref(need)), "overflow_poll")
+        return bool(flag.value), int(need.value)

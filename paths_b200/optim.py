@@ -3,8 +3,9 @@
 
 It subclasses torch.optim.Optimizer only so that the reference's `config.get_lr_scheduler(opt)` (ExponentialLR,
 config.py:130-131), `opt.zero_grad()` and `param_groups[0]["lr"]` keep working; the arithmetic is the CUDA kernel.
-Semantics match torch: parameters whose .grad is None (classifiers of levels 0..L-2) are skipped, parameters with
-exact-zero gradients (the dead encoder / cross-attention weights) are only weight-decayed.
+Semantics match torch: parameters whose .grad is None (classifiers of levels 0..L-2, modules the forward pass never
+evaluates such as procs.0.hctx_mlp of the RNN variant) are skipped, parameters with exact-zero gradients (the dead
+encoder / cross-attention weights) are only weight-decayed.
 """
 from __future__ import annotations
 
@@ -37,8 +38,9 @@ class FlatAdamW(torch.optim.Optimizer):
 
     def _skip_ranges(self, lay):
         rng = []
-        for n, prm, off, k in lay.entries:
-            if prm.grad is None:                     # torch skips parameters without a gradient
+        for n, prm, off, k in lay.entries + lay.dead_entries:
+            if prm.grad is None:                     # torch skips parameters without a gradient (in the dead tail: modules the
+                                                     # forward pass never evaluates, e.g. procs.0.hctx_mlp of the RNN variant)
                 if rng and rng[-1][1] == off:
                     rng[-1][1] = off + k
                 else:
@@ -46,7 +48,7 @@ class FlatAdamW(torch.optim.Optimizer):
         # merge ranges separated only by alignment padding
         merged = []
         for a, b in rng:
-            if merged and a - merged[-1][1] < 64 and not any(merged[-1][1] <= o < a for _, _, o, _ in lay.entries):
+            if merged and a - merged[-1][1] < 64 and not any(merged[-1][1] <= o < a for _, _, o, _ in lay.entries + lay.dead_entries):
                 merged[-1][1] = b
             else:
                 merged.append([a, b])
@@ -62,8 +64,8 @@ class FlatAdamW(torch.optim.Optimizer):
             if prm.grad is not None and prm.grad.data_ptr() != lay.gviews[n].data_ptr():
                 lay.gviews[n].copy_(prm.grad)
         skip = self._skip_ranges(lay)
-        if len(skip) > 8:
-            raise RuntimeError(f"FlatAdamW: {len(skip)} gradient-less parameter ranges (at most 8 supported)")
+        if len(skip) > 16:
+            raise RuntimeError(f"FlatAdamW: {len(skip)} gradient-less parameter ranges (at most 16 supported)")
         g = self.param_groups[0]
         self.t += 1
         arr = (C.c_int64 * max(1, 2 * len(skip)))(*[x for ab in skip for x in ab])

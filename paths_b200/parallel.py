@@ -99,10 +99,9 @@ class DataParallelStep:
                 global_batch = int(t.item())
             else:
                 global_batch = B
-        rt.global_batch = global_batch
         keep = [keep_patches] * (rt.dims.L - 1) if isinstance(keep_patches, int) else list(keep_patches)
         with torch.no_grad():
-            hz, loss = rt.end2end(batch, keep)
+            hz, loss = rt.end2end(batch, keep, global_batch=global_batch)
         eng = rt.last_engine
         self.backward(eng)
         return hz, loss

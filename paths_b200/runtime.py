@@ -64,11 +64,9 @@ class ModelRuntime:
         self.anchor = torch.zeros((), device=self.device, requires_grad=True)
         self.engines: Dict[tuple, Engine] = {}
         self.track_hazard_grad = False
-        self.strict_overflow = os.environ.get("PATHS_B200_STRICT_OVERFLOW", "0") == "1"
-        self._pending: Optional[Engine] = None
+        self.overflow_reruns = 0                        # steps re-run with worst-case buffers (no-child fallback, slide.py:336-352)
         self.last_dropout = (0.0, 0)                    # (p, seed) of the latest forward pass (tests rebuild the masks from it)
         self._ids_cache: Dict[tuple, torch.Tensor] = {}
-        self.global_batch: Optional[int] = None        # set by the data-parallel wrapper: loss = sum / global batch
 
     # ------------------------------------------------------------------------------------------------------------
     def set_precision(self, precision) -> None:
@@ -110,21 +108,17 @@ class ModelRuntime:
         eng.set_dropout(p, seed)
         self.last_dropout = (p, seed)
 
-    def _check_pending(self) -> None:
-        if self._pending is not None:
-            eng, self._pending = self._pending, None
-            over, need = eng.overflowed()
-            if over:
-                raise RuntimeError(
-                    f"paths_b200: the previous step overflowed a level's row capacity (needed {need} rows): a slide hit the "
-                    "no-child fallback of data_utils/slide.py:336-352.  Its loss was poisoned; rerun with "
-                    "PATHS_B200_STRICT_OVERFLOW=1 to size buffers for the fallback.")
-
     # ------------------------------------------------------------------------------------------------------------
-    def end2end(self, batch: Dict, keep_patches: Sequence[int], use_batch_fts: bool = True):
+    def end2end(self, batch: Dict, keep_patches: Sequence[int], use_batch_fts: bool = True, global_batch: Optional[int] = None):
         """utils.inference_end2end (utils.py:228-279) on the device.  `batch` is the collated dict of
-        data_utils/dataset.py:229-243 whose "slide" entries are paths_b200 PreprocessedSlide objects."""
-        self._check_pending()
+        data_utils/dataset.py:229-243 whose "slide" entries are paths_b200 PreprocessedSlide objects.  `global_batch` (data
+        parallelism): the loss is this rank's share of the mean over that many slides instead of the mean over the batch.
+
+        Level buffers are sized for the normal case (at most 4 children per kept row).  A slide that takes the reference's
+        no-child fallback (slide.py:336-352: every non-background cell of the next grid) can exceed them: the kernels then raise
+        a device flag, which is read here once the last select of the pass has run (the rest of the pass is still queued, so
+        the wait costs no GPU idle time), and the step is re-run on an engine sized for the worst case BEFORE any output or
+        autograd node of the truncated pass is handed out."""
         slides = batch["slide"]
         B = len(slides)
         store: PyramidStore = slides[0].store
@@ -153,21 +147,28 @@ class ModelRuntime:
             else:
                 ybin = torch.as_tensor(batch["subtype"]).to(dev, dtype=torch.int32, non_blocking=True)
                 cens = None
-            scale = 1.0 / float(self.global_batch if self.global_batch else B)
+            scale = 1.0 / float(global_batch if global_batch else B)
             self._arm_dropout(eng)
             if torch.is_grad_enabled():
                 hz, loss = _StepFn.apply(self.anchor, self, eng, slide_ids, fts, ybin, cens, scale)
             else:
                 hz, loss = _StepFn.forward(_NoCtx(), self.anchor, self, eng, slide_ids, fts, ybin, cens, scale)
-            if self.strict_overflow:
-                over, _ = eng.overflowed()
-                if over and not worst:
-                    worst = True
-                    continue
-            else:
-                self._pending = eng
+            over, need = eng.overflow_poll()
+            if over:
+                if worst:
+                    raise RuntimeError(f"paths_b200: level buffers sized for the worst case still overflowed ({need} rows needed)")
+                worst = True
+                self.overflow_reruns += 1
+                del hz, loss
+                continue
             self.last_engine = eng
             return hz, loss
+
+    def risk(self) -> torch.Tensor:
+        """Survival risk scores of the latest step, -sum(cumprod(1 - hazards)) per slide (eval.py:60-61), written by the loss
+        kernel next to the hazards."""
+        eng = self.last_engine
+        return eng.buffer(0, "RISK")[:eng.B].clone()
 
     # ------------------------------------------------------------------------------------------------------------
     @torch.no_grad()

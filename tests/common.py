@@ -27,7 +27,9 @@ def fixture_inputs(fx, grid_edit=None):
     mc = dict(BASE_MODEL_CONFIG)
     mc.update(fx["overrides"])
     mc.pop("dropout", None)
-    cfg = po.OracleConfig(num_levels=fx["num_levels"], top_k_patches=fx["top_k"], task="survival", nbins=4, **mc)
+    subtype = fx.get("task") == "subtype_classification"       # nbins carries the number of logits (model/paths.py:25)
+    cfg = po.OracleConfig(num_levels=fx["num_levels"], top_k_patches=fx["top_k"], task=fx.get("task", "survival"),
+                          nbins=len(fx["subtypes"]) if subtype else 4, **mc)
     sd = synth.synth_state_dict(fx["shapes"], seed=0)
     slides = []
     for (sid, w0, h0) in fx["slide_specs"]:
@@ -37,6 +39,10 @@ def fixture_inputs(fx, grid_edit=None):
         slides.append(s)
     ybin = torch.tensor([s.survival_bin for s in slides], dtype=torch.long)
     cens = torch.tensor([s.censored for s in slides], dtype=torch.long)
+    if subtype:                                                 # the label slot carries the class index, no censoring
+        for s, y in zip(slides, fx["subtype_labels"].tolist()):
+            s.subtype = int(y)
+        return cfg, sd, slides, fx["subtype_labels"].long(), None
     return cfg, sd, slides, ybin, cens
 
 
@@ -79,6 +85,9 @@ def product_config(fx=None, **over):
         data["model_config"].update(fx["overrides"])
         data["num_levels"] = fx["num_levels"]
         data["top_k_patches"] = list(fx["top_k"])
+        if fx.get("task") == "subtype_classification":
+            data["task"] = fx["task"]
+            data["filter_to_subtypes"] = list(fx["subtypes"])
     data["model_config"]["dropout"] = 0.0
     for k, v in over.items():
         if k in data["model_config"]:
@@ -103,7 +112,8 @@ def product_batch(cfg, model, slides, store=None, device="cuda"):
     items = []
     for s in slides:
         sl = load_patch_preprocessed_slide(f"/x/s{s.slide_id}.svs", cfg.base_power, cfg.model_config.patch_size,
-                                           model.procs[0].ctx_dim(), cfg.num_levels, grids=s.grids, store=store)
+                                           model.procs[0].ctx_dim(), cfg.num_levels, grids=s.grids, store=store,
+                                           subtype=getattr(s, "subtype", None))           # todict() adds it (slide.py:367-368)
         items.append(sl.todict() | {"survival_bin": s.survival_bin, "survival": s.survival, "censored": s.censored,
                                     "slide": sl})
     return collate_fn(items), store

@@ -38,10 +38,16 @@ def sample_idx(numel, n=48, seed=0):
 
 
 def run_case(name, model_dir, slide_specs, overrides=None, top_k=None, num_levels=None, p_bg=0.3,
-             grid_edit=None, full_grads=False, base_seed=1000):
-    """slide_specs: list of (slide_id, w0, h0)."""
+             grid_edit=None, full_grads=False, base_seed=1000, subtypes=None):
+    """slide_specs: list of (slide_id, w0, h0).  subtypes: class names => task "subtype_classification" (utils.py:274-278),
+    slide i labelled i mod len(subtypes) (dataset.py:161-163 stores the index into config.filter_to_subtypes)."""
+    if only and name not in only:
+        return
     cfg = rconfig.Config.load(os.path.join(REF, "models", model_dir), test_mode=True)
     cfg.model_config.dropout = 0.0
+    if subtypes is not None:
+        cfg.task = "subtype_classification"
+        cfg.filter_to_subtypes = list(subtypes)
     for k, v in (overrides or {}).items():
         setattr(cfg.model_config, k, v)
     if num_levels is not None:
@@ -67,7 +73,8 @@ def run_case(name, model_dir, slide_specs, overrides=None, top_k=None, num_level
         for l, g in enumerate(s.grids):
             torch.save(g.clone(), os.path.join(tmp, f"s{sid}_{cfg.base_power * 2 ** l:.3f}.pt"))
         sl = rslide.load_patch_preprocessed_slide(f"/x/s{sid}.svs", cfg.base_power, cfg.model_config.patch_size,
-                                                  model.procs[0].ctx_dim(), cfg.num_levels)
+                                                  model.procs[0].ctx_dim(), cfg.num_levels,
+                                                  subtype=None if subtypes is None else sid % len(subtypes))
         items.append(sl.todict() | {"survival_bin": s.survival_bin, "survival": s.survival,
                                     "censored": s.censored, "slide": sl})
     batch = rdataset.collate_fn(items)
@@ -104,6 +111,10 @@ def run_case(name, model_dir, slide_specs, overrides=None, top_k=None, num_level
         "shapes": shapes, "levels": levels, "hazards": hz.detach().clone(), "loss": loss.detach().clone(),
         "grads": grads, "torch": torch.__version__,
     }
+    if subtypes is not None:
+        fixture["task"] = cfg.task
+        fixture["subtypes"] = list(subtypes)
+        fixture["subtype_labels"] = batch["subtype"].clone()
     torch.save(fixture, os.path.join(HERE, f"{name}.pt"))
     print(name, "loss", float(loss), "levels", [int(l["num_ims"].sum()) for l in levels])
 
@@ -122,6 +133,8 @@ def kill_children_of_all(sid, grids):
 SMALL = {"patch_embed_dim": 64, "trans_dim": 32, "importance_mlp_hidden_dim": 16,
          "hierarchical_ctx_mlp_hidden_dim": 24}
 
+only = set(sys.argv[1:])      # python make_golden.py [case ...]: regenerate only the named fixtures
+
 if __name__ == "__main__":
     # cfg 1 of BASELINE.json: models/sample, one 8x7 slide, L=5, K=20
     run_case("cfg1_sample", "sample", [(0, 8, 7)])
@@ -139,3 +152,6 @@ if __name__ == "__main__":
     run_case("small_concat1d", "sample", [(0, 3, 2), (1, 2, 2)],
              overrides=SMALL | {"slide_ctx_mode": "concat", "pos_encoding_mode": "1d", "importance_mode": "none"},
              top_k=[3, 3], num_levels=3, full_grads=True)
+    # task "subtype_classification" (utils.py:274-278: cross-entropy on the last level's logits, three classes)
+    run_case("small_subtype", "sample", [(i, *synth.brca_shape(i, wrange=(2, 4), hrange=(2, 4))) for i in range(4)],
+             overrides=SMALL, top_k=[4, 4], num_levels=3, full_grads=True, subtypes=["IDC", "ILC", "MDLC"])

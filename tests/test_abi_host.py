@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, sym), f"{sym} is declared in include/paths_b200.h but not exported"
     assert sorted(_lib.SYMBOLS) == decl, "paths_b200/_lib.py:SYMBOLS must list exactly the declared entry points"
     lib.paths_abi_version.restype = ctypes.c_int
-    assert lib.paths_abi_version() == 4
+    assert lib.paths_abi_version() == 5
 
 
 def test_no_cpu_fallback():

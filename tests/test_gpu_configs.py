@@ -41,7 +41,6 @@ def _run(cfg, sd, slides, prec, grad=True):
     model = product_model(cfg, sd)
     rt = model.runtime()
     rt.set_precision(prec)
-    rt.strict_overflow = True
     batch, store = product_batch(cfg, model, slides)
     if grad:
         hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
@@ -102,7 +101,6 @@ def test_cfg4_20k_patch_bag_properties():
     model = product_model(cfg, sd)
     rt = model.runtime()
     rt.set_precision(1)
-    rt.strict_overflow = True
 
     def run(slides):
         batch, store = product_batch(cfg, model, slides)

@@ -24,7 +24,6 @@ def _step(name, prec, p, train=True, seed=11, slide_specs=None):
     model.train(train)
     rt = model.runtime()
     rt.set_precision(prec)
-    rt.strict_overflow = True
     batch, _ = product_batch(cfg, model, slides)
     torch.manual_seed(seed)
     hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)

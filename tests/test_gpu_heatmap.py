@@ -4,29 +4,12 @@ import pytest
 import torch
 
 from oracle import heatmap_oracle as ho
+from tests.heatmap_cases import GOLDEN_CASES, make_case
 
 pytestmark = pytest.mark.gpu
 
 
-def _case(seed, L, P, H, W, n0, keep, overlap=False, offgrid=False):
-    """Hierarchical patch sets like heatmap_visualise.py builds them: level-0 grid cells, then 4 children of the kept patches."""
-    rng = np.random.default_rng(seed)
-    gy, gx = H // P + 1, W // P + 1
-    cells = rng.permutation(gy * gx)[:n0]
-    locs = [np.stack([(cells // gx) * P, (cells % gx) * P], 1).astype(np.int64)]
-    imps = [rng.random(len(cells), dtype=np.float32)]
-    for d in range(1, L):
-        k = min(keep, len(locs[-1]))
-        kept = locs[-1][np.argsort(-imps[-1])[:k]] * 2
-        ch = np.concatenate([kept + np.array([dy, dx]) * P for dy in (0, 1) for dx in (0, 1)])
-        ch = ch[rng.random(len(ch)) > 0.25]
-        if overlap and len(ch) > 2:
-            ch = np.concatenate([ch, ch[:2] + P // 2])          # overlapping rectangles: the later patch must win
-        locs.append(ch.astype(np.int64)); imps.append(rng.random(len(ch), dtype=np.float32))
-    if offgrid:
-        locs[0] = np.concatenate([locs[0], np.array([[-P // 2, -P // 3], [H - P // 4, W - P // 5], [H + 5 * P, 0]])])
-        imps[0] = np.concatenate([imps[0], rng.random(3, dtype=np.float32)])
-    return locs, imps
+_case = make_case
 
 
 @pytest.mark.parametrize("cfg", [
@@ -55,3 +38,16 @@ def test_heatmap_empty_levels():
     want, want_alpha = ho.composite(locs, imps, 256, (64, 48))
     got, alpha = composite_heatmap([torch.from_numpy(l) for l in locs], [torch.from_numpy(i) for i in imps], 256, (64, 48), device="cuda:0")
     assert np.array_equal(got.cpu().numpy(), want) and np.array_equal(alpha.cpu().numpy().astype(np.float64), want_alpha.astype(np.float64))
+
+
+@pytest.mark.parametrize("ci", range(len(GOLDEN_CASES)))
+def test_heatmap_matches_the_reference_outputs(ci):
+    """The CUDA compositing against outputs of the reference's own code (tests/golden/heatmap_ref.npz), bit for bit."""
+    import os
+    from paths_b200.heatmap import composite_heatmap
+    ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "heatmap_ref.npz"))
+    kw = dict(GOLDEN_CASES[ci]); L, P, H, W = kw.pop("L"), kw.pop("P"), kw.pop("H"), kw.pop("W")
+    locs, imps = make_case(L=L, P=P, H=H, W=W, **kw)
+    got, alpha = composite_heatmap([torch.from_numpy(l) for l in locs], [torch.from_numpy(i) for i in imps], P, (H, W), device="cuda:0")
+    assert np.array_equal(got.cpu().numpy().view(np.int64), ref[f"imp{ci}"].view(np.int64))
+    assert np.array_equal(alpha.cpu().numpy().astype(np.float64), ref[f"alpha{ci}"])

@@ -70,7 +70,6 @@ def _run_product(name, prec):
     model = product_model(cfg, sd)
     rt = model.runtime()
     rt.set_precision(prec)
-    rt.strict_overflow = True
     batch, store = product_batch(cfg, model, slides)
     from paths_b200.utils import inference_end2end
     hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
@@ -80,10 +79,87 @@ def _run_product(name, prec):
 
 
 @pytest.mark.parametrize("prec", [0, 1, 2])
-@pytest.mark.parametrize("name", ["small_full", "small_edge", "cfg1_sample", "brca_b4", "small_rnn", "small_concat1d"])
+@pytest.mark.parametrize("name", ["small_full", "small_edge", "cfg1_sample", "brca_b4", "small_rnn", "small_concat1d", "small_subtype"])
 def test_end2end_parity(name, prec):
     fx, ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss = _run_product(name, prec)
     check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, prec)
+    if name == "small_edge":                         # two slides take the no-child fallback (slide.py:336-352): the step was
+        assert rt.overflow_reruns >= 1               # re-run on worst-case buffers before any output was handed out
+    if name == "small_subtype":                      # task "subtype_classification": logits + cross-entropy (utils.py:274-278)
+        assert torch.allclose(hz.detach().cpu(), fx["hazards"], atol=TOL[prec] * float(fx["hazards"].abs().max()))
+        assert abs(float(loss) - float(fx["loss"])) < TOL[prec] * 2
+
+
+def test_risk_scores_match_the_evaluator():
+    """eval.py:60-61: risk = -sum(cumprod(1 - hazards)); the loss kernel writes it next to the hazards."""
+    fx, ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss = _run_product("brca_b4", 0)
+    want = -torch.sum(torch.cumprod(1 - hz.detach(), dim=1), dim=1)
+    assert torch.allclose(rt.risk(), want, rtol=1e-6, atol=1e-6)
+    want_ref = -torch.sum(torch.cumprod(1 - fx["hazards"], dim=1), dim=1)         # from the reference's own hazards
+    assert rel_err(rt.risk().cpu(), want_ref) < 1e-4
+
+
+def fallback_in_slack_batch(fx, ocfg, sd, n_slides=24, victim=7):
+    """24 two-by-two slides (small_edge model: K = [8, 2, -1]).  Level 2 of every slide is edited after a first oracle pass
+    has told which two level-1 rows each slide keeps: ordinary slides keep ONE tissue cell under their best parent (1 row of
+    their 8-row capacity: the batch-wide slack), the victim loses every cell under both kept parents and therefore takes the
+    no-child fallback with the 56 remaining cells -- above the per-slide bound 8, inside the batch total."""
+    import paths_b200.synth as synth
+    slides = [synth.make_slide(100 + i, 2, 2, ocfg.num_levels, ocfg.patch_embed_dim, 0.0, seed=fx["base_seed"]) for i in range(n_slides)]
+    ybin = torch.tensor([s.survival_bin for s in slides]); cens = torch.tensor([s.censored for s in slides])
+    _, _, free = po.end2end(sd, ocfg, [s.grids for s in slides], ybin, cens, record=True)
+    for j, s in enumerate(slides):
+        keep = free[1].keep_inds[j]
+        xy = (free[1].locs[j][keep] // ocfg.patch_size).tolist()          # kept level-1 cells, importance-descending
+        g2 = s.grids[2]
+        if j == victim:
+            for x, y in xy:
+                g2[2 * x:2 * x + 2, 2 * y:2 * y + 2] = 0.0
+        else:
+            one = g2[2 * xy[0][0], 2 * xy[0][1]].clone()
+            g2.zero_()
+            g2[2 * xy[0][0], 2 * xy[0][1]] = one
+    return slides, ybin, cens
+
+
+def test_fallback_slide_inside_a_large_batch():
+    """A slide that takes the no-child fallback (slide.py:336-352) inside a batch whose capacity slack would hide it: the bag
+    exceeds the level's per-slide bound although the batch total fits.  The step must be re-run on worst-case buffers before
+    any output or gradient exists, and match the oracle."""
+    fx = load_fixture("small_edge")
+    ocfg, sd, _, _, _ = fixture_inputs(fx, edge_grid_edit)
+    slides, ybin, cens = fallback_in_slack_batch(fx, ocfg, sd)
+    _, _, free = po.end2end(sd, ocfg, [s.grids for s in slides], ybin, cens, record=True)
+    assert free[1].fallback[7] and sum(free[1].fallback) == 1
+    bags = free[2].num_ims.tolist()
+    assert bags[7] == 56 and sum(bags) <= 8 * len(slides), "the fallback bag must fit the batch total but not the per-slide bound"
+    cfg = product_config(fx)
+    model = product_model(cfg, sd)
+    rt = model.runtime(); rt.set_precision(0)
+    batch, store = product_batch(cfg, model, slides)
+    from paths_b200.utils import inference_end2end
+    hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+    loss.backward()
+    torch.cuda.synchronize()
+    assert rt.overflow_reruns == 1
+    check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, 0)
+
+
+def test_no_gradient_from_an_overflowed_pass():
+    """The truncated pass of an overflowing step never reaches autograd: with the re-run disabled the call raises before
+    returning, and no parameter has a .grad."""
+    fx = load_fixture("small_edge")
+    ocfg, sd, slides, ybin, cens = fixture_inputs(fx, edge_grid_edit)
+    cfg = product_config(fx)
+    model = product_model(cfg, sd)
+    rt = model.runtime(); rt.set_precision(0)
+    batch, store = product_batch(cfg, model, slides)
+    real = store.capacities
+    store.capacities = lambda ids, top_k, worst_case=False: real(ids, top_k, worst_case=False)    # never grant the worst case
+    from paths_b200.utils import inference_end2end
+    with pytest.raises(RuntimeError, match="overflow"):
+        inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+    assert all(p.grad is None for p in model.parameters())
 
 
 @pytest.mark.parametrize("name", ["small_full", "cfg1_sample", "small_rnn", "small_concat1d"])

@@ -46,6 +46,34 @@ def test_flat_adamw_matches_torch_adamw():
     assert abs(opt.param_groups[0]["lr"] - ropt.param_groups[0]["lr"]) < 1e-12
 
 
+def test_flat_adamw_leaves_never_evaluated_modules_alone():
+    """RNN variant: procs.0.hctx_mlp is never evaluated (paths.py:102), its .grad stays None in the reference and
+    torch.optim.AdamW skips it -- no weight decay either; the dead encoder weights (exact-zero gradients) are decayed."""
+    from paths_b200.optim import FlatAdamW
+    from paths_b200.utils import inference_end2end
+    cfg, model, batch = _setup("small_rnn")
+    before = {n: p.detach().clone() for n, p in model.named_parameters()}
+    opt = FlatAdamW(model, lr=1e-2, weight_decay=0.5)
+    ref = {n: p.detach().clone().requires_grad_(True) for n, p in model.named_parameters()}
+    ropt = torch.optim.AdamW(list(ref.values()), lr=1e-2, weight_decay=0.5)
+    for _ in range(2):
+        opt.zero_grad(); ropt.zero_grad()
+        hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+        loss.backward()
+        for n, p in model.named_parameters():
+            ref[n].grad = None if p.grad is None else p.grad.detach().clone()
+        opt.step(); ropt.step()
+    named = dict(model.named_parameters())
+    skipped = [n for n, p in named.items() if p.grad is None]
+    assert any(n.startswith("procs.0.hctx_mlp") for n in skipped)
+    for n in skipped:
+        assert torch.equal(named[n].detach(), before[n]), n
+    enc = "procs.1.global_agg.transformer.encoder.layers.0.linear1.weight"
+    assert not torch.equal(named[enc].detach(), before[enc])
+    for n, p in named.items():
+        assert rel_err(p.detach(), ref[n].detach()) < 2e-6, n
+
+
 def test_checkpoint_round_trip(tmp_path):
     from paths_b200.utils import save_state, load_state, inference_end2end
     cfg, model, batch = _setup()
@@ -85,6 +113,22 @@ def test_dp_step_equals_autograd_step():
         else:
             # weight gradients accumulate with fp32 atomics: order may differ between runs
             assert rel_err(p.grad, want[n]) < 1e-5, n
+
+
+def test_eval_batch_after_a_dp_step_is_a_mean_over_its_own_slides():
+    """A data-parallel training step scales the loss by 1 / global batch; that scale must not leak into the evaluation
+    batches that follow it (train.py:78-83: validation through inference_end2end after the epoch's steps)."""
+    from paths_b200.parallel import DataParallelStep
+    from paths_b200.utils import inference_end2end
+    cfg, model, batch = _setup("brca_b4")
+    with torch.no_grad():
+        _, want = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, copy.copy(batch), cfg.task)
+    dp = DataParallelStep(model)
+    _, part = dp.step(copy.copy(batch), cfg.top_k_patches, global_batch=64)           # this rank's share of a 64-slide batch
+    assert abs(float(part) * 64 / len(batch["slide"]) - float(want)) < 1e-6 * abs(float(want)) + 1e-7
+    with torch.no_grad():
+        _, again = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, copy.copy(batch), cfg.task)
+    assert torch.equal(again, want)
 
 
 def test_device_prefetcher_same_results_as_host_batches():

@@ -1,5 +1,11 @@
-"""CPU checks of the heat-map oracle against hand-computed answers (the reference block cannot be imported: matplotlib)."""
+"""CPU checks of the heat-map oracle: bit for bit against outputs of the reference's own compositing code (executed by
+tests/golden/make_golden_heatmap.py, committed as tests/golden/heatmap_ref.npz), and against hand-computed answers."""
+import os
+
 import numpy as np
+import pytest
+
+from tests.heatmap_cases import GOLDEN_CASES, make_case
 
 from oracle import heatmap_oracle as ho
 
@@ -19,3 +25,13 @@ def test_later_patch_overwrites_and_clipping():
     hi = float(np.float32(0.9) + np.float32(1e-4)); lo = float(np.float32(0.1) + np.float32(1e-4)); mid = float(np.float32(0.3) + np.float32(1e-4))
     assert out[1, 1] == lo and out[3, 3] == hi and out[5, 5] == hi and out[1, 5] == mid and out[0, 4] == lo
     assert ho.convert_pix(-3, 1, 0) == -2 and ho.convert_pix(256, 3, 0) == 32
+
+
+@pytest.mark.parametrize("ci", range(len(GOLDEN_CASES)))
+def test_oracle_reproduces_the_reference_block(ci):
+    ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "heatmap_ref.npz"))
+    kw = dict(GOLDEN_CASES[ci]); L, P, H, W = kw.pop("L"), kw.pop("P"), kw.pop("H"), kw.pop("W")
+    locs, imps = make_case(L=L, P=P, H=H, W=W, **kw)
+    out, alpha = ho.composite(locs, imps, P, (H, W))
+    assert out.dtype == np.float64 and np.array_equal(out.view(np.int64), ref[f"imp{ci}"].view(np.int64))
+    assert np.array_equal(np.asarray(alpha, dtype=np.float64), ref[f"alpha{ci}"])

@@ -6,7 +6,7 @@ import torch
 from oracle import paths_oracle as po
 from tests.common import load_fixture, fixture_inputs, edge_grid_edit, rel_err
 
-CASES = ["cfg1_sample", "brca_b4", "small_full", "small_edge", "small_rnn", "small_concat1d"]
+CASES = ["cfg1_sample", "brca_b4", "small_full", "small_edge", "small_rnn", "small_concat1d", "small_subtype"]
 TOL = 2e-5   # fp32 vs fp32, different op order only
 
 

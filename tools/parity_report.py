@@ -1,46 +1,135 @@
-"""Per-tensor parity report of the CUDA path against the teacher-forced CPU oracle (run on the B200 box).
-Prints, for every precision mode, the worst value errors per level and the gradient errors of every parameter tensor in
-two norms: max|a-b| / max|b| and ||a-b||_2 / ||b||_2."""
-import sys, os, json
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import torch
-from oracle import paths_oracle as po
-from tests.common import load_fixture, fixture_inputs, product_config, product_model, product_batch, rel_err
-from paths_b200.utils import inference_end2end
+"""Per-tensor gradient parity table with an fp64 ground truth (run on the B200 box; output kept in profiles/).
 
-name = sys.argv[1] if len(sys.argv) > 1 else "brca_b4"
-out = {}
-for prec, pname in [(0, "fp32"), (1, "bf16x3"), (2, "bf16")]:
-    fx = load_fixture(name)
-    ocfg, sd, slides, ybin, cens = fixture_inputs(fx)
-    cfg = product_config(fx)
-    model = product_model(cfg, sd)
-    rt = model.runtime(); rt.set_precision(prec); rt.strict_overflow = True
-    batch, store = product_batch(cfg, model, slides)
-    hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
-    loss.backward(); torch.cuda.synchronize()
-    eng = rt.last_engine; B = len(slides)
+    python tools/parity_report.py [case ...]        cases: brca_b4 | cfg3_96 | cfg5 | wide
+
+For every precision mode of the CUDA path and for the fp32 reference arithmetic itself (the CPU oracle in float32, which
+tests/test_oracle_golden.py pins to the unmodified reference at 2e-5), prints each live gradient tensor's error against
+the SAME computation carried out in float64 (oracle, teacher-forced with the CUDA path's selection):
+
+    err(x) = max|x - x64| / max|x64|            (relative to the tensor's own scale)
+
+The float32 reference is not exact either: entries of a gradient tensor are sums over thousands of patches that cancel,
+so its own error against float64 is the yardstick for what "within 1e-4 relative" can mean for a given tensor.
+tests/parity_check.py applies the rule this table justifies: a tensor passes at 1e-4 of its own scale, or at twice the
+float32 reference's own error against float64.
+"""
+import copy
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from oracle import paths_oracle as po  # noqa: E402
+from paths_b200 import synth  # noqa: E402
+from paths_b200.utils import inference_end2end  # noqa: E402
+from tests.common import BASE_CONFIG, load_fixture, fixture_inputs, product_config, product_model, product_batch, rel_err  # noqa: E402
+
+
+def _config(**over):
+    from paths_b200.config import Config
+    data = copy.deepcopy(BASE_CONFIG)
+    for k, v in over.items():
+        if k in data["model_config"]:
+            data["model_config"][k] = v
+        else:
+            data[k] = v
+    data["model_config"]["dropout"] = 0.0
+    return Config.from_dict(data, test_mode=True)
+
+
+def case_inputs(name):
+    if name == "brca_b4":
+        fx = load_fixture(name)
+        ocfg, sd, slides, ybin, cens = fixture_inputs(fx)
+        return product_config(fx), ocfg, sd, slides, ybin, cens
+    if name == "cfg3_96":
+        cfg = _config()
+        slides = synth.make_brca_batch(range(96), cfg.num_levels, cfg.model_config.patch_embed_dim)
+    elif name == "cfg5":
+        cfg = _config(num_levels=6, base_power=0.3125, top_k_patches=[32] * 5)
+        slides = synth.make_brca_batch(range(4), 6, cfg.model_config.patch_embed_dim, wrange=(3, 5), hrange=(2, 4))
+    elif name == "wide":
+        cfg = _config(num_levels=3, top_k_patches=[6, 6], patch_embed_dim=1280, trans_dim=192, importance_mlp_hidden_dim=160,
+                      hierarchical_ctx_mlp_hidden_dim=192)
+        slides = synth.make_brca_batch(range(5), 3, cfg.model_config.patch_embed_dim, wrange=(3, 6), hrange=(2, 5))
+    else:
+        raise SystemExit(f"unknown case {name}")
+    shapes = {k: tuple(v.shape) for k, v in cfg.get_model().state_dict().items()}
+    sd = synth.synth_state_dict(shapes, seed=3)
+    ybin = torch.tensor([s.survival_bin for s in slides], dtype=torch.long)
+    cens = torch.tensor([s.censored for s in slides], dtype=torch.long)
+    return cfg, po.OracleConfig.from_config(cfg), sd, slides, ybin, cens
+
+
+def forced_indices(eng, L, B):
     forced = []
-    for l in range(cfg.num_levels - 1):
+    for l in range(L - 1):
         seg = eng.buffer(l, "SEG")[:B + 1].tolist()
         kcap = eng.buffer(l, "SEL").numel() // B
-        sel = eng.buffer(l, "SEL").view(B, kcap).cpu(); cnt = eng.buffer(l, "SEL_COUNT")[:B].cpu()
+        sel = eng.buffer(l, "SEL").view(B, kcap).cpu()
+        cnt = eng.buffer(l, "SEL_COUNT")[:B].cpu()
         forced.append([(sel[j, :int(cnt[j])] - seg[j]).long() for j in range(B)])
-    ohz, oloss, og, recs = po.grads(sd, ocfg, [s.grids for s in slides], ybin, cens, forced_keep=forced)
-    rep = {"hazards": rel_err(hz.detach().cpu(), ohz), "loss": abs(float(loss) - float(oloss)) / abs(float(oloss))}
-    for l in range(cfg.num_levels):
-        M = int(eng.buffer(l, "COUNT").item())
-        a = eng.buffer(l, "ALPHA")[:M].cpu()
-        ref = torch.cat([recs[l].importance[j, :int(recs[l].num_ims[j])] for j in range(B)])
-        rep[f"importance_l{l}"] = rel_err(a, ref)
-        rep[f"logits_l{l}"] = rel_err(eng.buffer(l, "LOGITS").view(B, -1).cpu(), recs[l].logits)
-    named = dict(model.named_parameters())
-    gm, gl = {}, {}
-    for k, g in og.items():
-        if g is None or float(g.abs().max()) == 0: continue
-        mine = named[k].grad.detach().cpu().double(); g = g.double()
-        gm[k] = float((mine - g).abs().max() / g.abs().max()); gl[k] = float((mine - g).norm() / g.norm())
-    rep["grad_max_norm_worst"] = sorted(gm.items(), key=lambda kv: -kv[1])[:6]
-    rep["grad_l2_worst"] = sorted(gl.items(), key=lambda kv: -kv[1])[:6]
-    out[pname] = rep
-    print(pname, json.dumps(rep, indent=1))
+    return forced
+
+
+def report(name, out):
+    cfg, ocfg, sd, slides, ybin, cens = case_inputs(name)
+    B = len(slides)
+    runs = {}
+    forced = None
+    for prec, pname in [(0, "fp32"), (1, "bf16x3"), (2, "bf16")]:
+        model = product_model(cfg, sd)
+        rt = model.runtime(); rt.set_precision(prec)
+        batch, _ = product_batch(cfg, model, slides)
+        hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+        loss.backward(); torch.cuda.synchronize()
+        f = forced_indices(rt.last_engine, cfg.num_levels, B)
+        if forced is None:
+            forced = f                                  # the fp32 mode's selection is the shared teacher
+        same = all(torch.equal(a, b) for fa, fb in zip(f, forced) for a, b in zip(fa, fb))
+        runs[pname] = (hz.detach().cpu(), float(loss), {k: (p.grad.detach().cpu() if p.grad is not None else None)
+                                                        for k, p in model.named_parameters()}, same)
+        del model, rt, batch
+        torch.cuda.empty_cache()
+    grids = [s.grids for s in slides]
+    hz32, loss32, g32, _ = po.grads(sd, ocfg, grids, ybin, cens, forced_keep=forced)
+    hz64, loss64, g64, _ = po.grads({k: v.double() if v.is_floating_point() else v for k, v in sd.items()}, ocfg,
+                                    [[g.double() for g in gs] for gs in grids], ybin, cens, dtype=torch.float64, forced_keep=forced)
+    cols = ["ref_fp32"] + list(runs)
+    print(f"\n== {name}: {B} slides, L={cfg.num_levels}, K={list(cfg.top_k_patches)}; error vs the float64 oracle, relative to each tensor's max|.|", file=out)
+    print("   same selection as the fp32 mode: " + ", ".join(f"{k}={runs[k][3]}" for k in runs), file=out)
+    print(f"{'tensor':64s} {'numel':>9s} " + " ".join(f"{c:>10s}" for c in cols) + "   bf16x3/ref", file=out)
+    print(f"{'hazards':64s} {hz64.numel():9d} {rel_err(hz32, hz64):10.2e} " + " ".join(f"{rel_err(runs[k][0], hz64):10.2e}" for k in runs), file=out)
+    worst = {c: 0.0 for c in cols}
+    worst_ratio, n_over = 0.0, 0
+    for k, g in g64.items():
+        if g is None or float(g.abs().max()) == 0.0:
+            continue
+        e_ref = rel_err(g32[k], g)
+        row = [e_ref] + [rel_err(runs[p][2][k], g) if runs[p][2][k] is not None else float("nan") for p in runs]
+        for c, e in zip(cols, row):
+            worst[c] = max(worst[c], e)
+        ratio = row[2] / max(e_ref, 1e-12)
+        flag = ""
+        if row[2] > 1e-4:
+            n_over += 1
+            flag = "  > 1e-4" + ("  (<= 2 x ref)" if row[2] <= 2 * e_ref else "  (> 2 x ref)")
+            worst_ratio = max(worst_ratio, ratio)
+        print(f"{k:64s} {g.numel():9d} " + " ".join(f"{e:10.2e}" for e in row) + f"   {ratio:8.2f}{flag}", file=out)
+    print(f"{'worst over tensors':64s} {'':9s} " + " ".join(f"{worst[c]:10.2e}" for c in cols), file=out)
+    print(f"   bf16x3 tensors above 1e-4 of their own scale: {n_over}; worst ratio to the float32 reference's own error among them: {worst_ratio:.2f}", file=out)
+    return {"case": name, "worst": worst, "bf16x3_over_1e-4": n_over, "worst_ratio_over": worst_ratio}
+
+
+if __name__ == "__main__":
+    cases = sys.argv[1:] or ["brca_b4", "cfg3_96", "cfg5", "wide"]
+    dst = os.environ.get("PARITY_REPORT_OUT")
+    out = open(dst, "w") if dst else sys.stdout
+    print(__doc__.split("\n\n")[2], file=out)
+    summary = [report(c, out) for c in cases]
+    print("\n" + json.dumps(summary), file=out)
+    if dst:
+        out.close()
+        print(open(dst).read())
