@@ -144,8 +144,16 @@ int paths_engine_forward(paths_engine_t* e, const int32_t* slide_ids, const int3
  * (data_utils/dataset.py:229-243; device memory) instead of being gathered from the resident pyramid store. */
 int paths_engine_forward_padded(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, const int32_t* ybin,
                                 const int32_t* censored, float scale, int with_loss, void* stream);
+/* ... or as the same rows without the padding: fts_packed [n_rows, D], slide after slide, each slide's cells in the order of
+ * its level-0 bag (slide.py:260-269) -- what a loader that skips dataset.py:217's zero-padding ships across PCIe. */
+int paths_engine_forward_packed(paths_engine_t* e, const int32_t* slide_ids, const float* fts_packed, int n_rows, const int32_t* ybin,
+                                const int32_t* censored, float scale, int with_loss, void* stream);
 /* loss.backward() of train.py:65: levels L-1..0.  zero_grads: clear the grad buffer first. */
 int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream);
+/* Data parallelism (new work; the reference is single-process): makes `stream` wait until every gradient of procs[level]
+ * written by the latest paths_engine_backward is final -- after level 0 also the shared LSTM's -- so the caller can enqueue
+ * that level's all-reduce on `stream` while the backward pass of the shallower levels is still running. */
+int paths_engine_wait_grads(paths_engine_t* e, int level, void* stream);
 
 /* The no-child fallback of data_utils/slide.py:336-352 ("every non-background cell of the next grid") can give one slide a
  * bag above the capacities the engine was sized for.  The kernels stay inside their buffers and raise a device flag; this

@@ -51,7 +51,7 @@ _lib = None
 SYMBOLS = ["paths_last_error", "paths_abi_version", "paths_engine_workspace_bytes", "paths_engine_create",
            "paths_engine_destroy", "paths_engine_bind_params", "paths_engine_bind_store", "paths_engine_refresh_weights", "paths_engine_begin",
            "paths_engine_begin_padded", "paths_engine_level_forward", "paths_engine_select", "paths_engine_loss",
-           "paths_engine_level_backward", "paths_engine_forward", "paths_engine_forward_padded", "paths_engine_backward", "paths_engine_overflow_poll", "paths_engine_buffer",
+           "paths_engine_level_backward", "paths_engine_forward", "paths_engine_forward_padded", "paths_engine_forward_packed", "paths_engine_backward", "paths_engine_wait_grads", "paths_engine_overflow_poll", "paths_engine_buffer",
            "paths_engine_set_precision", "paths_engine_set_dropout", "paths_engine_launch_count", "paths_engine_profile", "paths_engine_profile_read", "paths_build_occupancy", "paths_gemm_nt",
            "paths_gemm_tn", "paths_adamw_step", "paths_heatmap_workspace_bytes", "paths_heatmap_composite"]
 
@@ -84,7 +84,9 @@ def lib() -> C.CDLL:
     L.paths_engine_level_backward.argtypes = [vp, i32, i32, vp]
     L.paths_engine_forward.argtypes = [vp, vp, vp, vp, f32, i32, vp]
     L.paths_engine_forward_padded.argtypes = [vp, vp, vp, i32, vp, vp, f32, i32, vp]
+    L.paths_engine_forward_packed.argtypes = [vp, vp, vp, i32, vp, vp, f32, i32, vp]
     L.paths_engine_backward.argtypes = [vp, i32, vp]
+    L.paths_engine_wait_grads.argtypes = [vp, i32, vp]
     L.paths_engine_overflow_poll.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.paths_engine_buffer.argtypes = [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)]
     L.paths_engine_set_precision.argtypes = [vp, i32]

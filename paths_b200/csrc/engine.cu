@@ -155,6 +155,9 @@ struct paths_engine {
   // host-visible copy of the overflow flag: copied to pinned memory right after the LAST select of a forward pass (the rest of
   // the pass is then still queued), so paths_engine_overflow_poll waits for a point the GPU passes well before the step ends
   int* h_over; cudaEvent_t ev_sel; bool sel_recorded;
+  // ev_grad[l]: recorded by the backward pass once every gradient of procs[l] is final (after level 0: the shared LSTM's too),
+  // so a data-parallel caller can start the level's all-reduce while the shallower levels are still running
+  cudaEvent_t ev_grad[PATHS_MAX_LEVELS];
   const int* slide_ids;
   Params P, Gr;                                          // parameters and their gradients (same layout)
   float* grads_base; size_t grads_floats;
@@ -952,6 +955,8 @@ int publish_overflow(paths_engine* e, cudaStream_t st) {
   return 0;
 }
 
+// N > 0: fts is the collated zero-padded batch [B, N, D];  N < 0: fts holds the level-0 rows already packed ([-N, D], slide-major,
+// cells x-major: exactly the order of the level-0 row table);  fts == nullptr: rows are gathered from the pyramid store.
 int do_begin(paths_engine* e, const int32_t* slide_ids, const float* fts_padded, int N, cudaStream_t st) {
   PATHS_REQUIRE(e->have_store, "begin: no pyramid store bound");
   e->slide_ids = slide_ids;
@@ -963,7 +968,10 @@ int do_begin(paths_engine* e, const int32_t* slide_ids, const float* fts_padded,
   e->launches++;
   tseg_kernel<<<(e->B + 255) / 256, 256, 0, st>>>(v.seg, v.tseg, e->B);
   PATHS_LAUNCH_CK(); e->launches++;
-  if (fts_padded) RUN(pack_padded_rows(fts_padded, N, v.seg, v.row_slide, v.X, e->dm.D, v.cap, v.count, st));
+  if (fts_padded && N < 0) {
+    PATHS_REQUIRE(-N <= v.cap, "begin: %d packed level-0 rows exceed the level's capacity %d", -N, v.cap);
+    PATHS_CK(cudaMemcpyAsync(v.X, fts_padded, (size_t)(-N) * e->dm.D * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  } else if (fts_padded) RUN(pack_padded_rows(fts_padded, N, v.seg, v.row_slide, v.X, e->dm.D, v.cap, v.count, st));
   else RUN(gather_rows(e->store.grid_ptr, e->store.gh, 0, e->dm.L, slide_ids, v.row_slide, v.row_xy, v.X, e->dm.D, v.cap, v.count, st));
   return 0;
 }
@@ -1080,6 +1088,7 @@ int paths_engine_create(paths_engine_t** out, const paths_dims_t* dims, int B, c
     ok = ok && cudaEventCreateWithFlags(&e->ev_z[l], cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&e->ev_head[l], cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&e->ev_dtok[l], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_grad[l], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) {
       set_error("could not create the per-level streams / events: %s", cudaGetErrorString(cudaGetLastError()));
       delete e;
@@ -1119,6 +1128,7 @@ void paths_engine_destroy(paths_engine_t* e) {
       cudaStreamSynchronize(e->side[l]);
       cudaStreamDestroy(e->side[l]);
       cudaEventDestroy(e->ev_tok[l]); cudaEventDestroy(e->ev_z[l]); cudaEventDestroy(e->ev_head[l]); cudaEventDestroy(e->ev_dtok[l]);
+      cudaEventDestroy(e->ev_grad[l]);
     }
   delete e;
 }
@@ -1305,6 +1315,12 @@ int paths_engine_forward_padded(paths_engine_t* e, const int32_t* slide_ids, con
   return forward_impl(e, slide_ids, fts_padded, N, ybin, censored, scale, with_loss, stream);
 }
 
+int paths_engine_forward_packed(paths_engine_t* e, const int32_t* slide_ids, const float* fts_packed, int n_rows, const int32_t* ybin,
+                                const int32_t* censored, float scale, int with_loss, void* stream) {
+  PATHS_REQUIRE(fts_packed && n_rows >= 1, "forward_packed: null feature rows");
+  return forward_impl(e, slide_ids, fts_packed, -n_rows, ybin, censored, scale, with_loss, stream);
+}
+
 static int forward_impl(paths_engine_t* e, const int32_t* slide_ids, const float* fts_padded, int N, const int32_t* ybin,
                         const int32_t* censored, float scale, int with_loss, void* stream) {
   PATHS_REQUIRE(e && e->have_params, "forward: engine has no parameters bound");
@@ -1366,8 +1382,10 @@ int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream) {
   const int L = e->dm.L;
   if (!use_side_streams(e)) {
     if (zero_grads) PATHS_CK(cudaMemsetAsync(e->grads_base, 0, e->grads_floats * sizeof(float), caller));
-    for (int l = L - 1; l >= 0; --l)
+    for (int l = L - 1; l >= 0; --l) {
       if (int r = level_backward(e, l, l == L - 1, caller)) return r;
+      if (e->have_streams) PATHS_CK(cudaEventRecord(e->ev_grad[l], caller));
+    }
     return 0;
   }
   PATHS_CK(cudaEventRecord(e->ev_in, caller));
@@ -1387,9 +1405,16 @@ int paths_engine_backward(paths_engine_t* e, int zero_grads, void* stream) {
   for (int l = L - 1; l >= 0; --l) {
     PATHS_CK(cudaStreamWaitEvent(st, e->ev_dtok[set_of[l]], 0));
     if (int r = lstm_backward(e, l, st)) return r;
+    PATHS_CK(cudaEventRecord(e->ev_grad[l], st));
   }
   PATHS_CK(cudaEventRecord(e->ev_out, st));
   PATHS_CK(cudaStreamWaitEvent(caller, e->ev_out, 0));
+  return 0;
+}
+
+int paths_engine_wait_grads(paths_engine_t* e, int level, void* stream) {
+  PATHS_REQUIRE(e && e->have_streams && level >= 0 && level < e->dm.L, "wait_grads: bad argument");
+  PATHS_CK(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), e->ev_grad[level], 0));
   return 0;
 }
 

@@ -18,7 +18,8 @@ from typing import Dict, Iterable, Iterator, Optional
 
 import torch
 
-_TENSOR_KEYS = ("fts", "survival_bin", "censored", "subtype")
+_TENSOR_KEYS = ("fts", "fts_packed", "survival_bin", "censored", "subtype")
+_BIG = ("fts", "fts_packed")
 
 
 class DevicePrefetcher:
@@ -43,10 +44,13 @@ class DevicePrefetcher:
         with torch.cuda.stream(self.copy_stream):
             # small (pageable) label tensors first: a pageable copy blocks the host until it has run, and behind the feature
             # copy that would be the whole 84 MB transfer
-            for k in sorted(self.keys, key=lambda k: k == "fts"):
+            have_packed = torch.is_tensor(batch.get("fts_packed"))
+            for k in sorted(self.keys, key=lambda k: k in _BIG):
                 v = batch.get(k)
+                if k == "fts" and have_packed:
+                    continue                                   # the step reads the packed rows: the padded copy stays on the host
                 if torch.is_tensor(v) and not v.is_cuda:
-                    if k == "fts" and not v.is_pinned():
+                    if k in _BIG and not v.is_pinned():
                         v = v.pin_memory()                     # pageable memory would serialise the copy with the step
                     out[k] = v.to(self.device, non_blocking=True)
             ev = torch.cuda.Event()

@@ -327,10 +327,15 @@ class Engine:
         L.check(self.lib.paths_engine_level_backward(self.handle, level, int(use_dlogits), _stream()), "level_backward")
 
     def forward(self, slide_ids: torch.Tensor, ybin: Optional[torch.Tensor], cens: Optional[torch.Tensor], scale: float,
-                with_loss: bool = True, fts_padded: Optional[torch.Tensor] = None) -> None:
+                with_loss: bool = True, fts_padded: Optional[torch.Tensor] = None, fts_packed: Optional[torch.Tensor] = None) -> None:
         yb = ybin.data_ptr() if ybin is not None else None
         cs = cens.data_ptr() if cens is not None else None
-        if fts_padded is None:
+        if fts_packed is not None:
+            assert fts_packed.is_cuda and fts_packed.dtype == torch.float32 and fts_packed.is_contiguous() and fts_packed.dim() == 2
+            L.check(self.lib.paths_engine_forward_packed(self.handle, slide_ids.data_ptr(), fts_packed.data_ptr(),
+                                                         int(fts_packed.shape[0]), yb, cs, scale, int(with_loss), _stream()),
+                    "engine_forward_packed")
+        elif fts_padded is None:
             L.check(self.lib.paths_engine_forward(self.handle, slide_ids.data_ptr(), yb, cs, scale, int(with_loss), _stream()),
                     "engine_forward")
         else:
@@ -341,6 +346,11 @@ class Engine:
 
     def backward(self, zero_grads: bool = False) -> None:
         L.check(self.lib.paths_engine_backward(self.handle, int(zero_grads), _stream()), "engine_backward")
+
+    def wait_grads(self, level: int, stream: Optional[torch.cuda.Stream] = None) -> None:
+        """Make `stream` (default: the current one) wait until the latest backward pass has finished procs[level]'s gradients."""
+        s = stream.cuda_stream if stream is not None else _stream()
+        L.check(self.lib.paths_engine_wait_grads(self.handle, level, s), "wait_grads")
 
     def set_precision(self, precision: int) -> None:
         L.check(self.lib.paths_engine_set_precision(self.handle, precision), "set_precision")

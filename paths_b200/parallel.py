@@ -4,8 +4,8 @@ Slides never interact in the forward or backward pass, so a global batch is spli
 GPU, each with a full parameter replica and its own shard of the pyramid store) and the only exchange is one
 all-reduce(sum) of the flat fp32 gradient buffer per step.  The buffer is cut into buckets in BACKWARD order --
 procs[L-1], ..., procs[0], then the shared LSTM (whose gradient is complete only after level 0) -- and each bucket's
-all-reduce is issued as soon as the level's backward kernels have been enqueued, so NCCL (its own stream, NVLink /
-NVSwitch) overlaps the remaining backward.  The loss is a mean over the GLOBAL batch: every rank scales by
+all-reduce is enqueued behind the event the engine records when that level's gradients are final, so NCCL (its own stream,
+NVLink / NVSwitch) overlaps the remaining backward.  The loss is a mean over the GLOBAL batch: every rank scales by
 1 / global_batch (unequal shards stay exact), so the reduction is a plain sum.
 """
 from __future__ import annotations
@@ -70,14 +70,23 @@ class GradBuckets:
 
 
 class DataParallelStep:
-    """One training step across ranks: forward, level-by-level backward with the bucketed all-reduce overlapped.
+    """One training step across ranks: forward, whole-step backward, bucketed all-reduce overlapped with it.
 
         dp = DataParallelStep(model)                      # after dist.init_process_group("nccl")
         hazards, loss = dp.step(batch, top_k)             # batch = this rank's shard (collated, "slide" entries)
         opt.step()
 
-    `loss` is this rank's share of the global mean loss (sum over ranks = global loss); call `dp.global_loss(loss)` for
-    the reduced value.  Gradients land, already summed over ranks, in the parameters' .grad (views of the flat buffer).
+    or, keeping the reference's loop body (train.py:58-66) unchanged:
+
+        dp = DataParallelStep(model).attach(global_batch=B * world)
+        hazards, loss = utils.inference_end2end(...); loss.backward(); opt.step()
+
+    The backward pass is the engine's whole-step one (grouped aggregators on their own streams); it records an event when
+    the gradients of procs[l] are final, and each bucket's all-reduce is enqueued behind its event on a side stream, so NCCL
+    runs while the shallower levels are still computing.  `loss` is this rank's share of the global mean loss (sum over ranks
+    = global loss); `dp.global_loss(loss)` reduces it.  Gradients land, summed over ranks, in the parameters' .grad (views of
+    the flat buffer).  `last_exposed_comm()` returns the device time between the end of the backward pass and the end of the
+    last all-reduce of the latest step: the communication that was NOT hidden.
     """
 
     def __init__(self, model, group=None, overlap: bool = True):
@@ -88,6 +97,20 @@ class DataParallelStep:
         self.buckets = GradBuckets.from_layout(self.rt.layout)
         assert self.buckets.covers_exactly_once()
         self.overlap = overlap
+        self.global_batch: Optional[int] = None
+        self._side = torch.cuda.Stream(self.rt.device) if torch.cuda.is_available() else None
+        self._ev = None
+
+    def attach(self, global_batch: Optional[int] = None) -> "DataParallelStep":
+        """Route `loss.backward()` of utils.inference_end2end through this object's backward (all-reduce included) and scale the
+        loss by 1 / global_batch (None: local batch x world size)."""
+        self.global_batch = global_batch
+        self.rt.grad_sync = self
+        return self
+
+    def detach(self) -> None:
+        if self.rt.grad_sync is self:
+            self.rt.grad_sync = None
 
     def step(self, batch: Dict, keep_patches, global_batch: Optional[int] = None):
         rt = self.rt
@@ -106,28 +129,45 @@ class DataParallelStep:
         self.backward(eng)
         return hz, loss
 
-    def backward(self, eng) -> None:
-        """loss.backward() + gradient all-reduce: levels L-1..0, each level's bucket reduced while the next level runs."""
+    def backward(self, eng, zero: bool = True) -> None:
+        """loss.backward() + gradient all-reduce.  zero=False: the flat gradient buffer was prepared by the caller (autograd
+        accumulation semantics)."""
         rt = self.rt
         gflat = rt.layout.gflat
-        gflat.zero_()
         nl = eng.dims.L
-        works = []
-        for l in reversed(range(nl)):
-            eng.level_backward(l, l == nl - 1)
-            if self.world > 1 and self.overlap:
-                a, b = self.buckets.level_bucket(l)
-                works.append(dist.all_reduce(gflat[a:b], group=self.group, async_op=True))
+        eng.backward(zero)                                  # whole step, enqueued at once; ev_grad[l] recorded inside
         if self.world > 1:
+            cur = torch.cuda.current_stream(rt.device)
+            timing = self._ev is not None
+            if timing:
+                self._ev[0].record(cur)                     # end of this rank's backward compute
+            works = []
             if self.overlap:
-                lb = self.buckets.lstm_bucket()
-                if lb is not None:
-                    works.append(dist.all_reduce(gflat[lb[0]:lb[1]], group=self.group, async_op=True))
+                with torch.cuda.stream(self._side):
+                    for l in reversed(range(nl)):
+                        eng.wait_grads(l, self._side)       # NCCL orders after the side stream, i.e. after the bucket's event
+                        a, b = self.buckets.level_bucket(l)
+                        works.append(dist.all_reduce(gflat[a:b], group=self.group, async_op=True))
+                    lb = self.buckets.lstm_bucket()
+                    if lb is not None:                      # the shared LSTM's gradient is final after level 0
+                        works.append(dist.all_reduce(gflat[lb[0]:lb[1]], group=self.group, async_op=True))
             else:
                 works.append(dist.all_reduce(gflat, group=self.group, async_op=True))
             for w in works:
-                w.wait()
+                w.wait()                                    # the current stream waits for NCCL's; the host does not block
+            if timing:
+                self._ev[1].record(cur)
         rt.layout.attach_grads()
+
+    def time_exposed_comm(self, on: bool = True) -> None:
+        self._ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) if on else None
+
+    def last_exposed_comm(self) -> float:
+        """Milliseconds between the end of the latest backward pass and the end of its last all-reduce (synchronises)."""
+        if self._ev is None or self.world == 1:
+            return 0.0
+        self._ev[1].synchronize()
+        return self._ev[0].elapsed_time(self._ev[1])
 
     def global_loss(self, loss: torch.Tensor) -> torch.Tensor:
         out = loss.detach().clone()

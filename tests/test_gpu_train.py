@@ -131,6 +131,56 @@ def test_eval_batch_after_a_dp_step_is_a_mean_over_its_own_slides():
     assert torch.equal(again, want)
 
 
+def test_packed_level0_rows_equal_the_padded_batch():
+    """collate_fn(packed=True): the step fed with the unpadded level-0 rows computes bit-identical results to the padded batch,
+    directly and through the prefetcher (which then leaves the padded copy on the host)."""
+    from paths_b200.data_utils.dataset import collate_fn
+    from paths_b200.data_utils.prefetch import DevicePrefetcher
+    from paths_b200.data_utils.slide import load_patch_preprocessed_slide
+    from paths_b200.utils import inference_end2end
+    fx = load_fixture("brca_b4")
+    ocfg, sd, slides, ybin, cens = fixture_inputs(fx)
+    cfg = product_config(fx)
+    model = product_model(cfg, sd)
+    batch, store = product_batch(cfg, model, slides)
+    items = [sl.todict() | {"survival_bin": s.survival_bin, "survival": s.survival, "censored": s.censored, "slide": sl}
+             for s, sl in zip(slides, batch["slide"])]
+    pbatch = collate_fn(items, packed=True)
+    assert pbatch["fts_packed"].shape[0] == int(pbatch["num_ims"].sum()) and torch.equal(pbatch["fts"], batch["fts"])
+    with torch.no_grad():
+        hz0, loss0 = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+        hz1, loss1 = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, pbatch, cfg.task)
+        assert torch.equal(hz0, hz1) and torch.equal(loss0, loss1)
+        for b in DevicePrefetcher([pbatch], "cuda"):
+            assert b["fts_packed"].is_cuda and not b["fts"].is_cuda
+            hz2, loss2 = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
+            assert torch.equal(hz0, hz2) and torch.equal(loss0, loss2)
+
+
+def test_attached_dp_step_runs_inside_loss_backward():
+    """DataParallelStep.attach(): the reference's loop body (inference_end2end + loss.backward()) gives the gradients of
+    dp.step(); detach() restores the plain path."""
+    from paths_b200.parallel import DataParallelStep
+    from paths_b200.utils import inference_end2end
+    cfg, model, batch = _setup("brca_b4")
+    dp = DataParallelStep(model)
+    hz, loss = dp.step(copy.copy(batch), cfg.top_k_patches, global_batch=8)
+    want = {n: (None if p.grad is None else p.grad.detach().clone()) for n, p in model.named_parameters()}
+    for p in model.parameters():
+        p.grad = None
+    dp.attach(global_batch=8)
+    hz2, loss2 = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, copy.copy(batch), cfg.task)
+    loss2.backward()
+    dp.detach()
+    assert model.runtime().grad_sync is None
+    assert torch.equal(hz2.detach(), hz)
+    for n, p in model.named_parameters():
+        if want[n] is None:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, n
+        else:
+            assert rel_err(p.grad, want[n]) < 1e-5, n
+
+
 def test_device_prefetcher_same_results_as_host_batches():
     """Batches staged one step ahead by DevicePrefetcher give bit-identical hazards/loss to host batches handed over directly."""
     from paths_b200.data_utils.prefetch import DevicePrefetcher
