@@ -950,7 +950,12 @@ int do_select(paths_engine* e, int l, cudaStream_t st) {
 // Publishes the overflow flag as it stands after the selects enqueued so far (see paths_engine::h_over).
 int publish_overflow(paths_engine* e, cudaStream_t st) {
   PATHS_CK(cudaMemcpyAsync(e->h_over, e->overflow, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-  PATHS_CK(cudaEventRecord(e->ev_sel, st));
+  // inside a stream capture (CUDA-graph replay of the step) a plain record would only become a graph edge: the host waits on
+  // this event, so it must be a real event-record node of the graph
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  PATHS_CK(cudaStreamIsCapturing(st, &cap));
+  if (cap == cudaStreamCaptureStatusActive) PATHS_CK(cudaEventRecordWithFlags(e->ev_sel, st, cudaEventRecordExternal));
+  else PATHS_CK(cudaEventRecord(e->ev_sel, st));
   e->sel_recorded = true;
   return 0;
 }

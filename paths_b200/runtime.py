@@ -25,9 +25,13 @@ class _StepFn(torch.autograd.Function):
     directly into the flat gradient buffer the parameters' .grad are views of (no per-parameter copies)."""
 
     @staticmethod
-    def forward(ctx, anchor, rt, eng, slide_ids, fts_padded, ybin, cens, scale, fts_packed=None):
-        eng.forward(slide_ids, ybin, cens, scale, True, fts_padded, fts_packed)   # whole step: chain + grouped aggregators on the engine's streams
-        ctx.rt, ctx.eng = rt, eng
+    def forward(ctx, anchor, rt, eng, slide_ids, fts_padded, ybin, cens, scale, fts_packed=None, gs=None):
+        if gs is not None:                                  # CUDA-graph replay of the same enqueue (GraphStep)
+            gs.load(slide_ids, ybin, cens, fts_packed)
+            gs.g_fwd.replay()
+        else:
+            eng.forward(slide_ids, ybin, cens, scale, True, fts_padded, fts_packed)   # whole step: chain + grouped aggregators on the engine's streams
+        ctx.rt, ctx.eng, ctx.gs = rt, eng, gs
         hz = eng.buffer(0, "HAZARDS").view(eng.B, eng.dims.nl).clone()
         loss = eng.buffer(0, "LOSS").view(()).clone()
         ctx.save_for_backward(hz)
@@ -47,10 +51,13 @@ class _StepFn(torch.autograd.Function):
         rt.layout.prepare_grads()
         if rt.grad_sync is not None:                    # data parallelism: bucketed all-reduce behind the backward pass
             rt.grad_sync.backward(eng, zero=False)
+        elif ctx.gs is not None and ctx.gs.g_bwd is not None:
+            ctx.gs.g_bwd.replay()
+            rt.layout.attach_grads()
         else:
             eng.backward(False)
             rt.layout.attach_grads()
-        return (None,) * 9
+        return (None,) * 10
 
 
 class ModelRuntime:
@@ -69,6 +76,10 @@ class ModelRuntime:
         self.track_hazard_grad = False
         self.overflow_reruns = 0                        # steps re-run with worst-case buffers (no-child fallback, slide.py:336-352)
         self.grad_sync = None                           # parallel.DataParallelStep.attach(): loss.backward() also all-reduces
+        # CUDA-graph replay of the step (GraphStep) for host batches that carry packed level-0 rows or read the resident store:
+        # the small-batch regime, where ~270 launches per step outrun the host.  Off by default (a graph pins its engine's buffers).
+        self.use_graphs = os.environ.get("PATHS_B200_GRAPHS", "0") == "1"
+        self._graphs: Dict[tuple, "GraphStep"] = {}
         self.last_dropout = (0.0, 0)                    # (p, seed) of the latest forward pass (tests rebuild the masks from it)
         self._ids_cache: Dict[tuple, torch.Tensor] = {}
 
@@ -78,6 +89,7 @@ class ModelRuntime:
         self.dims.precision = self.precision
         for e in self.engines.values():
             e.set_precision(self.precision)
+        self._graphs.clear()
 
     def _dims_for(self, top_k: Sequence[int]) -> L.Dims:
         d = L.Dims.from_buffer_copy(self.dims)
@@ -94,6 +106,7 @@ class ModelRuntime:
                 caps = [max(a, b) for a, b in zip(caps, eng.caps)]
                 maxseg = [max(a, b) for a, b in zip(maxseg, eng.maxseg)]
                 del self.engines[key]
+                self._graphs = {k: g for k, g in self._graphs.items() if g.eng is not eng}     # captured graphs pin its buffers
                 del eng
                 torch.cuda.empty_cache()
             eng = Engine(self._dims_for(top_k), B, caps, maxseg, self.device)
@@ -160,10 +173,13 @@ class ModelRuntime:
                 gb = self.grad_sync.global_batch or B * self.grad_sync.world
             scale = 1.0 / float(gb if gb else B)
             self._arm_dropout(eng)
+            gs = None
+            if self.use_graphs and self.last_dropout[0] == 0.0 and fts is None and self.grad_sync is None:
+                gs = self._graph_for(eng, slide_ids, ybin, cens, scale, pk, torch.is_grad_enabled())
             if torch.is_grad_enabled():
-                hz, loss = _StepFn.apply(self.anchor, self, eng, slide_ids, fts, ybin, cens, scale, pk)
+                hz, loss = _StepFn.apply(self.anchor, self, eng, slide_ids, fts, ybin, cens, scale, pk, gs)
             else:
-                hz, loss = _StepFn.forward(_NoCtx(), self.anchor, self, eng, slide_ids, fts, ybin, cens, scale, pk)
+                hz, loss = _StepFn.forward(_NoCtx(), self.anchor, self, eng, slide_ids, fts, ybin, cens, scale, pk, gs)
             over, need = eng.overflow_poll()
             if over:
                 if worst:
@@ -174,6 +190,30 @@ class ModelRuntime:
                 continue
             self.last_engine = eng
             return hz, loss
+
+    def _graph_for(self, eng, slide_ids, ybin, cens, scale, pk, backward) -> "GraphStep":
+        key = (id(eng), self.precision, float(scale), pk is not None, bool(backward), cens is not None)
+        gs = self._graphs.get(key)
+        if gs is None or gs.eng is not eng:
+            fts = None
+            if pk is not None:                          # static input buffer for the level-0 rows, sized for the engine's capacity
+                fts = torch.zeros(eng.caps[0], pk.shape[1], device=self.device)
+                fts[:pk.shape[0]].copy_(pk)
+            gs = self._graphs[key] = GraphStep(self, eng, slide_ids, ybin, cens, scale, backward=False, fts_packed=fts)
+            if backward:                                # the autograd node replays the backward pass without clearing the gradients
+                self.layout.prepare_grads()
+                st = torch.cuda.Stream(self.device)
+                st.wait_stream(torch.cuda.current_stream(self.device))
+                gs.g_bwd = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gs.g_bwd, stream=st):
+                    eng.backward(False)
+                gs.has_backward = True
+                self.layout.gflat.zero_()
+        return gs
+
+    def graph_step(self, eng, slide_ids, ybin, cens, scale, backward=True, fts_packed=None) -> "GraphStep":
+        """Capture one step of `eng` (forward, optionally backward) as CUDA graphs; see GraphStep."""
+        return GraphStep(self, eng, slide_ids, ybin, cens, scale, backward, fts_packed)
 
     def risk(self) -> torch.Tensor:
         """Survival risk scores of the latest step, -sum(cumprod(1 - hazards)) per slide (eval.py:60-61), written by the loss
@@ -244,6 +284,69 @@ class ModelRuntime:
         return {"logits": eng.buffer(depth, "LOGITS").view(B, dm.nl).clone(),
                 "ctx_slide": eng.buffer(depth, "F").view(B, d).clone(),
                 "ctx_patch": ctx_patch, "importance": out_imp}
+
+
+class GraphStep:
+    """One step of an engine captured as CUDA graphs: the forward pass (begin, L levels, selects, loss) and, optionally, the
+    backward pass.  A step is ~270 dependent launches; at the reference's own batch size (32 slides) most of them run for a
+    few microseconds and the host cannot enqueue them as fast as the GPU retires them -- replaying a captured graph removes
+    the per-launch host cost.  The inputs live in static buffers (`slide_ids`, `ybin`, `cens`, and `fts` for host batches)
+    that `load()` refills before a replay; every row count stays on the device, so the same graph serves any batch of the
+    engine's size.  Dropout is baked into kernel parameters (the per-step seed), so graphs are used with dropout off."""
+
+    def __init__(self, rt, eng, slide_ids, ybin, cens, scale, backward=True, fts_packed=None):
+        self.rt, self.eng, self.scale, self.has_backward = rt, eng, scale, backward
+        self.slide_ids, self.ybin, self.cens, self.fts = slide_ids.clone(), ybin.clone(), (cens.clone() if cens is not None else None), \
+            (fts_packed.clone() if fts_packed is not None else None)
+        eng.set_dropout(0.0, 0)
+        st = torch.cuda.Stream(rt.device)
+        st.wait_stream(torch.cuda.current_stream(rt.device))
+        with torch.cuda.stream(st):                         # warm-up outside the capture: lazy kernel attributes, tensor maps
+            for _ in range(2):
+                self._enqueue_fwd()
+                if backward:
+                    eng.backward(True)
+        torch.cuda.current_stream(rt.device).wait_stream(st)
+        torch.cuda.synchronize(rt.device)
+        l0 = eng.launch_count()
+        self.g_fwd = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.g_fwd, stream=st):
+            self._enqueue_fwd()
+        self.g_bwd = None
+        if backward:
+            self.g_bwd = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.g_bwd, stream=st):
+                eng.backward(True)
+        self.nodes = eng.launch_count() - l0
+        rt.layout.attach_grads()
+
+    def _enqueue_fwd(self):
+        self.eng.forward(self.slide_ids, self.ybin, self.cens, self.scale, True, None, self.fts)
+
+    def load(self, slide_ids=None, ybin=None, cens=None, fts_packed=None):
+        if slide_ids is not None:
+            self.slide_ids.copy_(slide_ids, non_blocking=True)
+        if ybin is not None:
+            self.ybin.copy_(ybin, non_blocking=True)
+        if cens is not None and self.cens is not None:
+            self.cens.copy_(cens, non_blocking=True)
+        if fts_packed is not None:
+            self.fts[:fts_packed.shape[0]].copy_(fts_packed, non_blocking=True)
+
+    def forward(self):
+        self.g_fwd.replay()
+        return self.eng.overflow_poll()
+
+    def backward(self):
+        self.g_bwd.replay()
+
+    def replay(self):
+        """Whole step; raises on a capacity overflow (the caller re-runs eagerly on worst-case buffers)."""
+        over, need = self.forward()
+        if over:
+            raise RuntimeError(f"paths_b200: graph step overflowed the level buffers ({need} rows needed)")
+        if self.has_backward:
+            self.backward()
 
 
 class _NoCtx:

@@ -181,6 +181,51 @@ def test_attached_dp_step_runs_inside_loss_backward():
             assert rel_err(p.grad, want[n]) < 1e-5, n
 
 
+def test_graph_replay_equals_eager_steps():
+    """rt.use_graphs: the step replayed as CUDA graphs (forward graph + backward graph, inputs in static buffers) gives the
+    eager step's hazards, loss and gradients -- on the batch it was captured with and on a different batch of the same size;
+    gradients accumulate across backward calls as autograd's do."""
+    from paths_b200.data_utils.dataset import collate_fn
+    from paths_b200.utils import inference_end2end
+    fx = load_fixture("brca_b4")
+    ocfg, sd, slides, ybin, cens = fixture_inputs(fx)
+    cfg = product_config(fx)
+
+    def batches(model):
+        from tests.common import product_batch as pb
+        b1, store = pb(cfg, model, slides)
+        order = [2, 0, 3, 1]
+        b2, _ = pb(cfg, model, [slides[i] for i in order], store=store)
+        out = []
+        for b in (b1, b2):
+            items = [sl.todict() | {"survival_bin": int(b["survival_bin"][i]), "survival": float(b["survival"][i]),
+                                    "censored": int(b["censored"][i]), "slide": sl} for i, sl in enumerate(b["slide"])]
+            out.append(collate_fn(items, packed=True))
+        return out
+
+    res = {}
+    for mode in ("eager", "graph"):
+        model = product_model(cfg, sd)
+        rt = model.runtime(); rt.set_precision(1); rt.use_graphs = mode == "graph"
+        got = []
+        for b in batches(model) * 2:
+            for p in model.parameters():
+                p.grad = None
+            hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
+            loss.backward()
+            got.append((hz.detach().clone(), loss.detach().clone(), rt.layout.gflat.clone()))
+        hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
+        loss.backward()                                                   # no zero_grad in between: accumulates
+        got.append((hz.detach().clone(), loss.detach().clone(), rt.layout.gflat.clone()))
+        if mode == "graph":
+            assert len(rt._graphs) == 1
+        res[mode] = got
+    for (h0, l0, g0), (h1, l1, g1) in zip(res["eager"], res["graph"]):
+        assert torch.equal(h0, h1) and torch.equal(l0, l1)
+        assert rel_err(g1, g0) < 1e-5
+    assert rel_err(res["graph"][4][2], 2 * res["graph"][3][2]) < 1e-5
+
+
 def test_device_prefetcher_same_results_as_host_batches():
     """Batches staged one step ahead by DevicePrefetcher give bit-identical hazards/loss to host batches handed over directly."""
     from paths_b200.data_utils.prefetch import DevicePrefetcher
