@@ -205,6 +205,19 @@ int paths_heatmap_composite(const int32_t* locs_yx, const float* importance, con
                             int patch_size, int H, int W, void* workspace, size_t workspace_bytes, double* out, float* alpha,
                             void* stream);
 
+/* Stand-alone varlen softmax self-attention over packed tokens -- the self-attention of nn.TransformerDecoderLayer as
+ * model/aggregator.py:70-72 runs it, the key-padding mask replaced by per-slide segments.  qkv: [tokens, 3 d] (q | k | v, `heads`
+ * heads of width d / heads, query scale 1/sqrt(head_dim) applied inside); slide s owns token rows [seg[s] + s, seg[s+1] + s + 1)
+ * (seg: [B + 1] patch-row offsets; each bag has one extra leading token, the aggregator's special token).  out: [tokens, d],
+ * lse: [tokens, heads] log-sum-exp of the scores.  max_bag: upper bound on seg[s+1] - seg[s].  precision 1 / 2 run bags of at
+ * most 128 tokens on the tensor cores (tcgen05: three-term bf16 split / plain bf16), 0 and longer bags on the fp32 SIMT kernels.
+ * dropout_p > 0 drops probabilities by the hash of paths_engine_set_dropout (level 0, layer 0).
+ * bwd: dqkv [tokens, 3 d] receives dq | dk | dv; dvec: [tokens, heads] scratch. */
+int paths_attention_fwd(int precision, const float* qkv, const int32_t* seg, int B, float* out, float* lse, int d, int heads, int max_bag,
+                        float dropout_p, uint64_t dropout_seed, void* stream);
+int paths_attention_bwd(int precision, const float* qkv, const int32_t* seg, int B, const float* out, const float* lse, const float* dout,
+                        float* dqkv, float* dvec, int d, int heads, int max_bag, float dropout_p, uint64_t dropout_seed, void* stream);
+
 /* Stand-alone dense contractions (tests; the engine uses the same kernels).
  * C[M,N] (+)= act(A[M,K] . B^T + bias) with B [N,K] (b_kn = 0) or [K,N] (b_kn = 1); flags: 1 relu, 2 accumulate. */
 int paths_gemm_nt(int precision, const float* A, int lda, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias,

@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpaths_b200.so")
-SOURCES = ["engine.cu", "gemm_simt.cu", "gemm_tc.cu", "rowops.cu", "attention.cu", "select.cu", "optim.cu", "heatmap.cu"]
+SOURCES = ["engine.cu", "gemm_simt.cu", "gemm_tc.cu", "rowops.cu", "attention.cu", "attention_tc.cu", "select.cu", "optim.cu", "heatmap.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
          "--expt-relaxed-constexpr", "-Xptxas", "-v"]
@@ -44,7 +44,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             raise RuntimeError(f"nvcc failed on {src}:\n{out}")
     with open(os.path.join(HERE, "build", "ptxas.log"), "w") as f:
         f.write("\n".join(log))
-    cmd = [NVCC, "-shared", "-o", LIB, *objs, "-lcudart", "-Xlinker", "--no-undefined"]
+    cmd = [NVCC, "-shared", "-o", LIB, *objs, "-lcudart", "-ldl", "-Xlinker", "--no-undefined"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}")

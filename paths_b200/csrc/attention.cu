@@ -18,15 +18,6 @@ constexpr int QB = QW * AW;      // queries per block
 constexpr int KT = 32;           // keys per tile
 constexpr int MAXDH = 64;
 
-// Virtual slide sv of a grouped launch = (group g = sv / B, slide s = sv % B): its tokens are rows roff[g] + seg[g][s] + s ...
-// of the concatenated qkv buffer, its compact (single-query) output row is oroff[g] + s.
-struct Seg { int t0, T, os, g, r0; };            // (+ row group and its first row: dropout hashes level-local token rows)
-__device__ __forceinline__ Seg seg_of(const SegGrp& sg, int sv) {
-  const int g = sv / sg.B, s = sv - g * sg.B;
-  const int* seg = pick(sg.seg, g);
-  Seg r; r.r0 = pick(sg.roff, g); r.g = g; r.t0 = r.r0 + seg[s] + s; r.T = seg[s + 1] - seg[s] + 1; r.os = pick(sg.oroff, g) + s;
-  return r;
-}
 
 // out[q, h*dh + c] = sum_j softmax_j(scale * q.k_j) v_j[c];  lse[q, h] = logsumexp_j(scale * q.k_j)
 __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restrict__ qkv, const SegGrp seg,
@@ -973,7 +964,7 @@ int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, in
   return attn_fwd_grp(qkv, seg_single(seg, B), out, lse, d, heads, max_T, nq_mode, st);
 }
 int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st,
-                 const Drop* drop) {
+                 const Drop* drop, int tc_passes) {
   PATHS_REQUIRE(d % heads == 0 && d / heads <= MAXDH, "attention: head_dim %d unsupported (max %d)", d / heads, MAXDH);
   const int B = seg.n * seg.B;                       // virtual slides
   if (B <= 0) return 0;
@@ -986,8 +977,13 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
     PATHS_LAUNCH_CK();
     return 0;
   }
+  static const bool no_tc = getenv("PATHS_B200_ATTN_SIMT") != nullptr;  // keep the SIMT short-bag kernels in the tensor-core modes
   static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;   // experimental pair-per-row kernels (not faster: off)
-  if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
+  if (tc_passes && !no_tc && !nq_mode && attn_tc_supported(d, heads)) {  // bags of at most 128 tokens on the tensor cores (attention_tc.cu)
+    if (int r = attn_tc_fwd(tc_passes, qkv, seg, out, lse, d, heads, max_T, st, dr)) return r;
+    if (max_T <= SMALL_MAX_T) return 0;
+    skip_T = SMALL_MAX_T;
+  } else if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
     switch (nkc) {
@@ -1026,7 +1022,7 @@ int attn_bwd(const float* qkv, const int* seg, const float* out, const float* ls
   return attn_bwd_grp(qkv, seg_single(seg, B), out, lse, dout, dqkv, Dvec, d, heads, max_T, nq_mode, st);
 }
 int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
-                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop) {
+                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop, int tc_passes) {
   const int B = seg.n * seg.B;
   if (B <= 0) return 0;
   int skip_T = 0;
@@ -1036,8 +1032,13 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
     PATHS_LAUNCH_CK();
     return 0;
   }
+  static const bool no_tc = getenv("PATHS_B200_ATTN_SIMT") != nullptr;
   static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;
-  if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
+  if (tc_passes && !no_tc && !nq_mode && attn_tc_supported(d, heads)) {
+    if (int r = attn_tc_bwd(tc_passes, qkv, seg, out, lse, dout, dqkv, d, heads, max_T, st, dr)) return r;
+    if (max_T <= SMALL_MAX_T) return 0;
+    skip_T = SMALL_MAX_T;
+  } else if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
     switch (nkc) {

@@ -1,0 +1,481 @@
+// Short-bag varlen self-attention on the 5th-generation tensor cores (tcgen05 + TMEM), sm_100a.
+//
+// The self-attention of nn.TransformerDecoderLayer as model/aggregator.py:70-72 uses it (head_dim 32, key-padding mask replaced by
+// per-slide segments), for bags of at most 128 tokens -- every level of the BRCA-shaped workload.  One CTA per (head, slide):
+//
+//   forward    S = (scale Q) K^T          tcgen05.mma, M = 128 query rows, N = padded keys, K = 32
+//              P = exp(S - rowmax)        threads read their accumulator row from TMEM (one TMEM lane per query), write P as bf16 tiles
+//              O = P V / rowsum           tcgen05.mma, N = 32, K = padded keys
+//   backward   S, dP = dO V^T             two products into neighbouring TMEM columns
+//              P = exp(S - lse), dS = P o (dP - D)      (D = dO . O per query, computed while the rows are staged)
+//              dQ = scale dS K,  dK = dS^T (scale Q),  dV = P^T dO      three products; dS and P are read as K-major (dQ) and,
+//              from the same shared-memory tiles, as M-major operands (the transposed products)
+//
+// Precision: every operand is split x = hi + lo (bf16 each); NP = 2 issues hi.hi + hi.lo + lo.hi into the same fp32 TMEM
+// accumulator (~2^-17 per product: the fp32-parity mode), NP = 1 issues hi.hi only (plain bf16: the fast mode).
+//
+// Shared-memory operand tiles (all bf16, 128-byte rows, 8-row / 1024-byte SWIZZLE_128B atoms, written by the CTA's own threads --
+// the rows come from fp32 activations, so there is no TMA on this path):
+//   natural tile  [token rows][hi 32 | lo 32]    K-major over head_dim: Q, K (S), dO, V (dP).  The lo half of a row is the
+//                                                second 64 bytes of the same swizzled row: a descriptor start + 64 B selects it.
+//   transposed    [32 head_dim rows][tokens]     K-major over tokens, one 4 KB block per 64 tokens and plane: V (O), K (dQ),
+//                                                Q (dK), dO (dV) as the N = 32 operand of a product that contracts over tokens.
+//   score tile    [query rows][keys]             one block per 64 keys and plane: P, dS.  K-major operand of O / dQ; read as an
+//                                                M-major operand (M = keys, K = queries) by dK / dV.
+// Two size classes share the code: NKB = 1 (bags up to 64 tokens, 64 threads, 64 TMEM columns forward / 128 backward, several CTAs
+// per SM) and NKB = 2 (65..128 tokens, 128 threads).  A launch covers every (head, slide); CTAs of the other class exit at once.
+#include "common.cuh"
+#include "rowops.cuh"
+#include "tc_ptx.cuh"
+
+namespace paths {
+namespace {
+using namespace tc;
+
+constexpr int DH = 32;
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+// (hi, lo) split of 8 consecutive values into two 16-byte chunks
+__device__ __forceinline__ void split8(const float* x, uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const __nv_bfloat162 hh = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
+    const float2 hf = __bfloat1622float2(hh);
+    h[e] = *reinterpret_cast<const uint32_t*>(&hh);
+    l[e] = pack_bf16(x[2 * e] - hf.x, x[2 * e + 1] - hf.y);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]); lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+// natural tile: row r = [hi(x[0..32)) | lo(x[0..32))], 16-byte chunk c of the row stored at chunk c ^ (r & 7)
+__device__ __forceinline__ void store_natural(uint8_t* tile, int r, const float* x) {
+  uint8_t* row = tile + (r >> 3) * 1024 + (r & 7) * 128;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint4 hi, lo;
+    split8(x + 8 * c, hi, lo);
+    *reinterpret_cast<uint4*>(row + ((c ^ (r & 7)) << 4)) = hi;
+    *reinterpret_cast<uint4*>(row + (((c + 4) ^ (r & 7)) << 4)) = lo;
+  }
+}
+__device__ __forceinline__ void zero_natural(uint8_t* tile, int r) {
+  uint8_t* row = tile + (r >> 3) * 1024 + (r & 7) * 128;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(row + (c << 4)) = make_uint4(0, 0, 0, 0);
+}
+// transposed planes: element (head_dim c, token j) of plane p at  p * plane_bytes + (j / 64) * 4096 + swizzled (row c, column j % 64)
+template <int NP>
+__device__ __forceinline__ void store_transposed(uint8_t* base, int plane_bytes, int j, const float* x) {
+  uint8_t* blk = base + (j >> 6) * 4096 + ((j & 7) << 1);
+  const int jc = (j >> 3) & 7;
+#pragma unroll
+  for (int c = 0; c < DH; ++c) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(x[c]);
+    const uint32_t off = (c >> 3) * 1024 + (c & 7) * 128 + ((jc ^ (c & 7)) << 4);
+    *reinterpret_cast<__nv_bfloat16*>(blk + off) = h;
+    if (NP == 2) *reinterpret_cast<__nv_bfloat16*>(blk + plane_bytes + off) = __float2bfloat16_rn(x[c] - __bfloat162float(h));
+  }
+}
+// score tile: 8 consecutive keys (chunk kc of key block kb) of query row q; block = ROWS x 128 bytes
+template <int NP, int ROWS>
+__device__ __forceinline__ void store_score8(uint8_t* base, int plane_bytes, int q, int kb, int kc, const float* x) {
+  uint8_t* p = base + kb * (ROWS * 128) + (q >> 3) * 1024 + (q & 7) * 128 + ((kc ^ (q & 7)) << 4);
+  uint4 hi, lo;
+  split8(x, hi, lo);
+  *reinterpret_cast<uint4*>(p) = hi;
+  if (NP == 2) *reinterpret_cast<uint4*>(p + plane_bytes) = lo;
+}
+
+// K-major operand over 16 reduction elements starting at byte `koff` of the 128-byte rows (8-row groups 1024 bytes apart)
+__device__ __forceinline__ uint64_t desc_k(uint32_t tile, uint32_t koff) { return umma_desc(tile + koff, 16, 1024); }
+// M-major operand: 16 reduction rows starting at row 16 * ks, output index along the 128-byte rows, 64-wide blocks `lbo` bytes apart
+__device__ __forceinline__ uint64_t desc_m(uint32_t tile, int ks, uint32_t lbo) { return umma_desc(tile + ks * 2048, lbo, 1024); }
+
+// hi.hi (+ hi.lo + lo.hi) of one 16-deep reduction step; *acc tracks whether the accumulator already holds a term
+template <int NP>
+__device__ __forceinline__ void mma_terms(uint32_t d_tmem, uint64_t a_hi, uint64_t a_lo, uint64_t b_hi, uint64_t b_lo, uint32_t idesc,
+                                          uint32_t* acc) {
+  if (NP == 2) {
+    umma_bf16(d_tmem, a_lo, b_hi, idesc, *acc);
+    umma_bf16(d_tmem, a_hi, b_lo, idesc, 1u);
+    umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
+  } else {
+    umma_bf16(d_tmem, a_hi, b_hi, idesc, *acc);
+  }
+  *acc = 1u;
+}
+
+__device__ __forceinline__ void load_row32(const float* p, float* x) {
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p) + c);
+    x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+  }
+}
+__device__ __forceinline__ void store_row32(float* p, const uint32_t* r, float mul) {
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+    reinterpret_cast<float4*>(p)[c] = make_float4(__uint_as_float(r[4 * c]) * mul, __uint_as_float(r[4 * c + 1]) * mul,
+                                                  __uint_as_float(r[4 * c + 2]) * mul, __uint_as_float(r[4 * c + 3]) * mul);
+}
+
+template <int NKB, int NP>
+struct FwdCfg {
+  static constexpr int NT = 64 * NKB;                       // threads = token rows of the class
+  static constexpr int NAT = NT * 128;                      // natural tile bytes
+  static constexpr int VT_PLANE = NKB * 4096;               // transposed V, one plane
+  static constexpr int P_PLANE = NKB * NT * 128;            // score tile, one plane
+  static constexpr int OFF_Q = 0, OFF_K = NAT, OFF_VT = 2 * NAT, OFF_P = OFF_VT + NP * VT_PLANE;
+  static constexpr int SMEM = OFF_P + NP * P_PLANE + 8192 + 1024;     // + slack an M = 128 operand of the 64-row class reads past + alignment
+  static constexpr int TMEM_COLS = 64 * NKB;                // S; O reuses its columns
+};
+
+// ------------------------------------------------------------------------------------------------------------------ forward
+template <int NKB, int NP, bool DROP>
+__global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __restrict__ qkv, const SegGrp seg, float* __restrict__ out,
+                                                               float* __restrict__ lse, int d, int heads, const Drop dr) {
+  using cfg = FwdCfg<NKB, NP>;
+  constexpr int NT = cfg::NT;
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.y);
+  const int T = sg.T;
+  if (T > NT || (NKB == 2 && T <= 64)) return;              // the other class's launch (or the tiled kernels) serves this bag
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int t = threadIdx.x, warp = t >> 5;
+  if (t == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc(&tmem_slot, cfg::TMEM_COLS);
+
+  const float scale = rsqrtf((float)DH);
+  const int ld = 3 * d;
+  {
+    float x[DH];
+    if (t < T) {
+      const float* rp = qkv + (size_t)(sg.t0 + t) * ld + h * DH;
+      load_row32(rp, x);
+#pragma unroll
+      for (int c = 0; c < DH; ++c) x[c] *= scale;
+      store_natural(smem + cfg::OFF_Q, t, x);
+      load_row32(rp + d, x);
+      store_natural(smem + cfg::OFF_K, t, x);
+      load_row32(rp + 2 * d, x);
+    } else {
+      zero_natural(smem + cfg::OFF_Q, t);
+      zero_natural(smem + cfg::OFF_K, t);
+#pragma unroll
+      for (int c = 0; c < DH; ++c) x[c] = 0.f;
+    }
+    store_transposed<NP>(smem + cfg::OFF_VT, cfg::VT_PLANE, t, x);     // rows past the bag: zeros (0 * garbage must stay 0)
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const uint32_t sQ = smem_u32(smem + cfg::OFF_Q), sK = smem_u32(smem + cfg::OFF_K), sVt = smem_u32(smem + cfg::OFF_VT),
+                 sP = smem_u32(smem + cfg::OFF_P);
+  if (t == 0) {                                              // S = (scale Q) K^T : M = 128, N = NT keys, K = 32
+    constexpr uint32_t idesc = umma_idesc(128, NT, 0, 0);
+    uint32_t acc = 0;
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks)
+      mma_terms<NP>(tmem_base, desc_k(sQ, ks * 32), desc_k(sQ, 64 + ks * 32), desc_k(sK, ks * 32), desc_k(sK, 64 + ks * 32), idesc, &acc);
+    umma_commit(&bar);
+  }
+  mbar_wait(&bar, 0);
+  tc_fence_after();
+
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
+  const uint32_t hrow = (uint32_t)(sg.t0 - sg.r0 + t), hcol = (uint32_t)h << 24;
+  float mx = -INFINITY;
+#pragma unroll 1
+  for (int c0 = 0; c0 < NT; c0 += 32) {
+    uint32_t r[32];
+    tmem_ld32(lane_addr + c0, r);
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (c0 + i < T) mx = fmaxf(mx, __uint_as_float(r[i]));
+  }
+  float sum = 0.f;
+#pragma unroll 1
+  for (int c0 = 0; c0 < NT; c0 += 32) {
+    uint32_t r[32];
+    tmem_ld32(lane_addr + c0, r);
+    float p[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float e = (c0 + i < T) ? expf(__uint_as_float(r[i]) - mx) : 0.f;
+      sum += e;                                              // the normaliser sums every probability, the value sum the kept ones
+      p[i] = e;
+      if (DROP) p[i] = drop_keep(dkey, hrow, hcol | (uint32_t)(c0 + i), dr.thresh) ? e * dr.inv_keep : 0.f;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      store_score8<NP, NT>(smem + cfg::OFF_P, cfg::P_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, p + 8 * q);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (t == 0) {                                              // O = P V : M = 128, N = 32, K = NT keys (S's columns are free now)
+    constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0);
+    uint32_t acc = 0;
+#pragma unroll
+    for (int kb = 0; kb < NKB; ++kb)
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        const uint32_t a = sP + kb * (NT * 128), b = sVt + kb * 4096;
+        mma_terms<NP>(tmem_base, desc_k(a, ks * 32), desc_k(a + cfg::P_PLANE, ks * 32), desc_k(b, ks * 32), desc_k(b + cfg::VT_PLANE, ks * 32),
+                      idesc, &acc);
+      }
+    umma_commit(&bar);
+  }
+  mbar_wait(&bar, 1);
+  tc_fence_after();
+  {
+    uint32_t r[32];
+    tmem_ld32(lane_addr, r);
+    if (t < T) {
+      store_row32(out + (size_t)(sg.t0 + t) * d + h * DH, r, 1.f / sum);
+      lse[(size_t)(sg.t0 + t) * heads + h] = mx + logf(sum);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
+}
+
+// ----------------------------------------------------------------------------------------------------------------- backward
+template <int NKB, int NP>
+struct BwdCfg {
+  static constexpr int NT = 64 * NKB;
+  static constexpr int NAT = NT * 128;
+  static constexpr int T_PLANE = NKB * 4096;                // a transposed operand, one plane
+  static constexpr int S_PLANE = NKB * NT * 128;            // a score tile (P or dS), one plane
+  // region 0: natural Q, K, V, dO (operands of S and dP); once those products are done the same bytes (and what follows) hold P, dS
+  static constexpr int R0 = (4 * NAT > 2 * NP * S_PLANE) ? 4 * NAT : 2 * NP * S_PLANE;
+  static constexpr int OFF_Q = 0, OFF_K = NAT, OFF_V = 2 * NAT, OFF_DO = 3 * NAT;
+  static constexpr int OFF_P = 0, OFF_DS = NP * S_PLANE;
+  static constexpr int OFF_KT = R0 + 8192;                  // (slack: an M = 128 operand of the 64-row class reads 64 rows past a block)
+  static constexpr int OFF_QT = OFF_KT + NP * T_PLANE, OFF_DOT = OFF_QT + NP * T_PLANE;
+  static constexpr int SMEM = OFF_DOT + NP * T_PLANE + 1024;
+  static constexpr int TMEM_COLS = 128 * NKB;               // S | dP; dQ, dK, dV reuse the columns
+};
+
+template <int NKB, int NP, bool DROP>
+__global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __restrict__ qkv, const SegGrp seg, const float* __restrict__ out,
+                                                               const float* __restrict__ lse, const float* __restrict__ dout,
+                                                               float* __restrict__ dqkv, int d, int heads, const Drop dr) {
+  using cfg = BwdCfg<NKB, NP>;
+  constexpr int NT = cfg::NT;
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.y);
+  const int T = sg.T;
+  if (T > NT || (NKB == 2 && T <= 64)) return;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int t = threadIdx.x, warp = t >> 5;
+  if (t == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc(&tmem_slot, cfg::TMEM_COLS);
+
+  const float scale = rsqrtf((float)DH);
+  const int ld = 3 * d;
+  float Dq = 0.f, L = 0.f;
+  {
+    float x[DH], y[DH];
+    if (t < T) {
+      const float* rp = qkv + (size_t)(sg.t0 + t) * ld + h * DH;
+      load_row32(rp, x);
+      load_row32(rp + d, y);
+#pragma unroll
+      for (int c = 0; c < DH; ++c) x[c] *= scale;
+      store_natural(smem + cfg::OFF_Q, t, x);
+      store_transposed<NP>(smem + cfg::OFF_QT, cfg::T_PLANE, t, x);
+      store_natural(smem + cfg::OFF_K, t, y);
+      store_transposed<NP>(smem + cfg::OFF_KT, cfg::T_PLANE, t, y);
+      load_row32(rp + 2 * d, x);
+      store_natural(smem + cfg::OFF_V, t, x);
+      const size_t orow = (size_t)(sg.t0 + t) * d + h * DH;
+      load_row32(dout + orow, x);
+      load_row32(out + orow, y);
+#pragma unroll
+      for (int c = 0; c < DH; ++c) Dq = fmaf(x[c], y[c], Dq);
+      store_natural(smem + cfg::OFF_DO, t, x);
+      store_transposed<NP>(smem + cfg::OFF_DOT, cfg::T_PLANE, t, x);
+      L = lse[(size_t)(sg.t0 + t) * heads + h];
+    } else {
+#pragma unroll
+      for (int c = 0; c < DH; ++c) x[c] = 0.f;
+      zero_natural(smem + cfg::OFF_Q, t); zero_natural(smem + cfg::OFF_K, t); zero_natural(smem + cfg::OFF_V, t);
+      zero_natural(smem + cfg::OFF_DO, t);
+      store_transposed<NP>(smem + cfg::OFF_QT, cfg::T_PLANE, t, x);
+      store_transposed<NP>(smem + cfg::OFF_KT, cfg::T_PLANE, t, x);
+      store_transposed<NP>(smem + cfg::OFF_DOT, cfg::T_PLANE, t, x);
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const uint32_t s0 = smem_u32(smem);
+  if (t == 0) {                                              // S = (scale Q) K^T -> columns [0, NT);  dP = dO V^T -> [NT, 2 NT)
+    constexpr uint32_t idesc = umma_idesc(128, NT, 0, 0);
+    uint32_t acc = 0;
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks)
+      mma_terms<NP>(tmem_base, desc_k(s0 + cfg::OFF_Q, ks * 32), desc_k(s0 + cfg::OFF_Q, 64 + ks * 32), desc_k(s0 + cfg::OFF_K, ks * 32),
+                    desc_k(s0 + cfg::OFF_K, 64 + ks * 32), idesc, &acc);
+    acc = 0;
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks)
+      mma_terms<NP>(tmem_base + NT, desc_k(s0 + cfg::OFF_DO, ks * 32), desc_k(s0 + cfg::OFF_DO, 64 + ks * 32), desc_k(s0 + cfg::OFF_V, ks * 32),
+                    desc_k(s0 + cfg::OFF_V, 64 + ks * 32), idesc, &acc);
+    umma_commit(&bar);
+  }
+  mbar_wait(&bar, 0);                                        // both products done: the natural tiles may be overwritten
+  tc_fence_after();
+
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
+  const uint32_t hrow = (uint32_t)(sg.t0 - sg.r0 + t), hcol = (uint32_t)h << 24;
+#pragma unroll 1
+  for (int c0 = 0; c0 < NT; c0 += 32) {
+    uint32_t rs[32], rp[32];
+    tmem_ld32(lane_addr + c0, rs);
+    tmem_ld32(lane_addr + NT + c0, rp);
+    float pv[32], ds[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float p = (t < T && c0 + i < T) ? expf(__uint_as_float(rs[i]) - L) : 0.f;     // rows / columns past the bag: exact zeros
+      float pm = p, dpm = __uint_as_float(rp[i]);            // (they are contracted over by dK / dV, resp. dQ)
+      if (DROP) {
+        const bool keep = drop_keep(dkey, hrow, hcol | (uint32_t)(c0 + i), dr.thresh);
+        pm = keep ? p * dr.inv_keep : 0.f; dpm = keep ? dpm * dr.inv_keep : 0.f;
+      }
+      pv[i] = pm;
+      ds[i] = p * (dpm - Dq);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      store_score8<NP, NT>(smem + cfg::OFF_P, cfg::S_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, pv + 8 * q);
+      store_score8<NP, NT>(smem + cfg::OFF_DS, cfg::S_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, ds + 8 * q);
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (t == 0) {
+    constexpr uint32_t idk = umma_idesc(128, DH, 0, 0);      // A K-major
+    constexpr uint32_t idm = umma_idesc(128, DH, 1, 0);      // A M-major (the transposed products)
+    const uint32_t sP = s0 + cfg::OFF_P, sDS = s0 + cfg::OFF_DS, sKt = s0 + cfg::OFF_KT, sQt = s0 + cfg::OFF_QT, sDOt = s0 + cfg::OFF_DOT;
+    uint32_t acc = 0;                                        // dQ[q, c] = sum_j dS[q, j] K[j, c]        -> columns [0, 32)
+#pragma unroll
+    for (int kb = 0; kb < NKB; ++kb)
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        const uint32_t a = sDS + kb * (NT * 128), b = sKt + kb * 4096;
+        mma_terms<NP>(tmem_base, desc_k(a, ks * 32), desc_k(a + cfg::S_PLANE, ks * 32), desc_k(b, ks * 32), desc_k(b + cfg::T_PLANE, ks * 32), idk,
+                      &acc);
+      }
+    acc = 0;                                                 // dK[j, c] = sum_q dS[q, j] (scale Q)[q, c]   -> columns [32, 64)
+#pragma unroll
+    for (int ks = 0; ks < NT / 16; ++ks) {
+      const uint32_t b = sQt + (ks >> 2) * 4096;
+      mma_terms<NP>(tmem_base + 32, desc_m(sDS, ks, NT * 128), desc_m(sDS + cfg::S_PLANE, ks, NT * 128), desc_k(b, (ks & 3) * 32),
+                    desc_k(b + cfg::T_PLANE, (ks & 3) * 32), idm, &acc);
+    }
+    acc = 0;                                                 // dV[j, c] = sum_q P[q, j] dO[q, c]           -> columns [64, 96)
+#pragma unroll
+    for (int ks = 0; ks < NT / 16; ++ks) {
+      const uint32_t b = sDOt + (ks >> 2) * 4096;
+      mma_terms<NP>(tmem_base + 64, desc_m(sP, ks, NT * 128), desc_m(sP + cfg::S_PLANE, ks, NT * 128), desc_k(b, (ks & 3) * 32),
+                    desc_k(b + cfg::T_PLANE, (ks & 3) * 32), idm, &acc);
+    }
+    umma_commit(&bar);
+  }
+  mbar_wait(&bar, 1);
+  tc_fence_after();
+  {
+    float* rp = dqkv + (size_t)(sg.t0 + t) * ld + h * DH;
+    uint32_t r[32];
+    tmem_ld32(lane_addr, r);
+    if (t < T) store_row32(rp, r, scale);
+    tmem_ld32(lane_addr + 32, r);
+    if (t < T) store_row32(rp + d, r, 1.f);
+    tmem_ld32(lane_addr + 64, r);
+    if (t < T) store_row32(rp + 2 * d, r, 1.f);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
+}
+
+template <typename K>
+int set_smem_once(K kern, int bytes, bool* done) {
+  if (*done) return 0;
+  PATHS_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  *done = true;
+  return 0;
+}
+
+template <int NKB, int NP, bool DROP>
+int launch_fwd(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, cudaStream_t st, const Drop& dr) {
+  static bool done = false;
+  auto kern = attn_tc_fwd_kernel<NKB, NP, DROP>;
+  if (int r = set_smem_once(kern, FwdCfg<NKB, NP>::SMEM, &done)) return r;
+  kern<<<dim3(heads, seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st>>>(qkv, seg, out, lse, d, heads, dr);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+template <int NKB, int NP, bool DROP>
+int launch_bwd(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d, int heads,
+               cudaStream_t st, const Drop& dr) {
+  static bool done = false;
+  auto kern = attn_tc_bwd_kernel<NKB, NP, DROP>;
+  if (int r = set_smem_once(kern, BwdCfg<NKB, NP>::SMEM, &done)) return r;
+  kern<<<dim3(heads, seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, dr);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+
+}  // namespace
+
+bool attn_tc_supported(int d, int heads) { return heads > 0 && d % heads == 0 && d / heads == DH && d % 4 == 0; }
+
+#define ATTN_TC_DISPATCH(FN, NKB_, ...)                                                \
+  do {                                                                                 \
+    int r_;                                                                            \
+    if (passes == 3) r_ = dr.thresh ? FN<NKB_, 2, true>(__VA_ARGS__) : FN<NKB_, 2, false>(__VA_ARGS__); \
+    else r_ = dr.thresh ? FN<NKB_, 1, true>(__VA_ARGS__) : FN<NKB_, 1, false>(__VA_ARGS__);             \
+    if (r_) return r_;                                                                 \
+  } while (0)
+
+int attn_tc_fwd(int passes, const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, cudaStream_t st,
+                const Drop& dr) {
+  PATHS_REQUIRE(attn_tc_supported(d, heads) && (passes == 1 || passes == 3), "attn_tc_fwd: head_dim must be 32");
+  if (seg.n * seg.B <= 0) return 0;
+  ATTN_TC_DISPATCH(launch_fwd, 1, qkv, seg, out, lse, d, heads, st, dr);
+  if (max_T > 64) ATTN_TC_DISPATCH(launch_fwd, 2, qkv, seg, out, lse, d, heads, st, dr);
+  return 0;
+}
+int attn_tc_bwd(int passes, const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d,
+                int heads, int max_T, cudaStream_t st, const Drop& dr) {
+  PATHS_REQUIRE(attn_tc_supported(d, heads) && (passes == 1 || passes == 3), "attn_tc_bwd: head_dim must be 32");
+  if (seg.n * seg.B <= 0) return 0;
+  ATTN_TC_DISPATCH(launch_bwd, 1, qkv, seg, out, lse, dout, dqkv, d, heads, st, dr);
+  if (max_T > 64) ATTN_TC_DISPATCH(launch_bwd, 2, qkv, seg, out, lse, dout, dqkv, d, heads, st, dr);
+  return 0;
+}
+#undef ATTN_TC_DISPATCH
+
+}  // namespace paths

@@ -9,6 +9,8 @@
 #include <new>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>       // header-only NVTX 3: a no-op unless a profiler injects its library
+
 #include "../../include/paths_b200.h"
 #include "common.cuh"
 #include "rowops.cuh"
@@ -413,13 +415,23 @@ inline bool planes_mode(const paths_dims_t& dm) {
   return dm.precision != PREC_FP32_SIMT && dm.lstm && dm.D % 8 == 0 && dm.C % 8 == 0 && (dm.I + dm.d) % 8 == 0;
 }
 
+// One tagged region of a step: an NVTX range on the host thread that enqueues it (the reference has no tracing at
+// all; these are the ranges a timeline of the step is read by) and, while paths_engine_profile is on, a CUDA-event pair on the
+// region's stream.
+static const char* const kProfNames[PATHS_PROF__COUNT] = {"paths/gates_fwd", "paths/gates_dW", "paths/gates_dH", "paths/lstm_fwd",
+                                                          "paths/decoder_fwd", "paths/select_gather", "paths/decoder_bwd", "paths/lstm_bwd"};
+// tensor-core passes of the short-bag attention: 0 in the fp32 SIMT mode, else the contraction modes' split (3) / plain bf16 (1)
+inline int attn_tc_passes(const paths_dims_t& dm) { return dm.precision == PREC_BF16X3_TC ? 3 : dm.precision == PREC_BF16_TC ? 1 : 0; }
+
 struct ProfScope {
-  paths_engine* e; int tag; cudaStream_t st; bool on;
-  ProfScope(paths_engine* e_, int tag_, cudaStream_t st_) : e(e_), tag(tag_), st(st_), on(e_->prof_on) {
+  paths_engine* e; int tag; cudaStream_t st; bool on; bool open;
+  ProfScope(paths_engine* e_, int tag_, cudaStream_t st_) : e(e_), tag(tag_), st(st_), on(e_->prof_on), open(true) {
+    nvtxRangePushA(kProfNames[tag]);
     if (on) { cudaEvent_t a; cudaEventCreate(&a); cudaEventRecord(a, st); e->prof_ev[tag].push_back(a); }
   }
   void end() {
     if (on) { cudaEvent_t b; cudaEventCreate(&b); cudaEventRecord(b, st); e->prof_ev[tag].push_back(b); on = false; }
+    if (open) { nvtxRangePop(); open = false; }
   }
   ~ProfScope() { end(); }
 };
@@ -656,7 +668,7 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
                b2 = PL(S, [&](int l) { return P[l].layer[j].b2; });
     Drop dA;
     if (drop) dA = set_drop(e, S, j, DROP_ATTN);
-    RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr));
+    RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr, attn_tc_passes(dm)));
     RUN(gemm_nt_set(e, S, gr, y.O, d, [&](int l) { return P[l].layer[j].Wo; }, d, 0, A1, d, PL0(), d, d, 0, st, &pO));
     // dropout1(W_o a + b_o), dropout2(b_cross) and dropout3(W_2 h + b_2) are applied to the branch INCLUDING its bias before
     // the residual sum; the cross-attention branch (a bias only) is materialised in Fo, free until the FFN writes it
@@ -821,7 +833,8 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
         RUN(zero_rows(v0.dqkv + (size_t)S.gt.roff[g] * 3 * d, 3 * d, S.gt.hcnt[g], S.gt.cnt[g], 0, st));
     Drop dA;
     if (drop) dA = set_drop(e, S, j, DROP_ATTN);
-    RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, last ? v0.Dvecb : v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr));
+    RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, last ? v0.Dvecb : v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr,
+                     attn_tc_passes(dm)));
     OpPl p3 = oppl(e->dpl3), pT = oppl(saved ? e->svT[j] : e->dplD[0]);
     pT.ready = saved;
     const MutL dbqkv = ML(S, [&](int l) { return Gl(l).bqkv; });
@@ -1530,6 +1543,25 @@ int paths_gemm_nt(int precision, const float* A, int lda, const float* B, int ld
     set_tc_scratch(nullptr, 0, nullptr, 0);
   }
   return rc;
+}
+
+// Stand-alone varlen self-attention (tests, per-op use): the engine's decoder calls the same launchers.
+int paths_attention_fwd(int precision, const float* qkv, const int32_t* seg, int B, float* out, float* lse, int d, int heads, int max_bag,
+                        float dropout_p, uint64_t dropout_seed, void* stream) {
+  PATHS_REQUIRE(qkv && seg && out && lse && B >= 1 && heads >= 1 && d % heads == 0 && precision >= 0 && precision <= 2, "attention_fwd: bad argument");
+  Drop dr = no_drop();
+  if (dropout_p > 0.f) { dr.thresh = drop_thresh(dropout_p); dr.inv_keep = 1.f / (1.f - dropout_p); dr.key[0] = drop_site_key(dropout_seed, 0, 0, DROP_ATTN); }
+  return attn_fwd_grp(qkv, seg_single(seg, B), out, lse, d, heads, max_bag + 1, 0, static_cast<cudaStream_t>(stream), dropout_p > 0.f ? &dr : nullptr,
+                      precision == PREC_BF16X3_TC ? 3 : precision == PREC_BF16_TC ? 1 : 0);
+}
+int paths_attention_bwd(int precision, const float* qkv, const int32_t* seg, int B, const float* out, const float* lse, const float* dout,
+                        float* dqkv, float* dvec, int d, int heads, int max_bag, float dropout_p, uint64_t dropout_seed, void* stream) {
+  PATHS_REQUIRE(qkv && seg && out && lse && dout && dqkv && dvec && B >= 1 && heads >= 1 && d % heads == 0 && precision >= 0 && precision <= 2,
+                "attention_bwd: bad argument");
+  Drop dr = no_drop();
+  if (dropout_p > 0.f) { dr.thresh = drop_thresh(dropout_p); dr.inv_keep = 1.f / (1.f - dropout_p); dr.key[0] = drop_site_key(dropout_seed, 0, 0, DROP_ATTN); }
+  return attn_bwd_grp(qkv, seg_single(seg, B), out, lse, dout, dqkv, dvec, d, heads, max_bag + 1, 0, static_cast<cudaStream_t>(stream),
+                      dropout_p > 0.f ? &dr : nullptr, precision == PREC_BF16X3_TC ? 3 : precision == PREC_BF16_TC ? 1 : 0);
 }
 
 int paths_gemm_tn(int precision, const float* P, int ldp, const float* Q, int ldq, float* C, int ldc, int M, int NI, int NJ, void* stream) {

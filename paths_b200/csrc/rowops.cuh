@@ -88,11 +88,31 @@ inline SegGrp seg_single(const int* seg, int B) {
   g.seg[0] = seg;
   return g;
 }
+#ifdef __CUDACC__
+// Virtual slide sv of a grouped launch = (group g = sv / B, slide s = sv % B): its tokens are rows roff[g] + seg[g][s] + s ...
+// of the concatenated qkv buffer, its compact (single-query) output row is oroff[g] + s.
+struct Seg { int t0, T, os, g, r0; };            // (+ row group and its first row: dropout hashes level-local token rows)
+__device__ __forceinline__ Seg seg_of(const SegGrp& sg, int sv) {
+  const int g = sv / sg.B, s = sv - g * sg.B;
+  const int* seg = pick(sg.seg, g);
+  Seg r; r.r0 = pick(sg.roff, g); r.g = g; r.t0 = r.r0 + seg[s] + s; r.T = seg[s + 1] - seg[s] + 1; r.os = pick(sg.oroff, g) + s;
+  return r;
+}
+#endif
+// Tensor-core (tcgen05) forms of the short-bag attention, attention_tc.cu: head_dim 32, bags of at most 128 tokens, every token
+// a query.  passes = 3: Q K^T, P V and the four backward products as three-term bf16 splits (fp32-parity); 1: plain bf16.
+// Bags above 128 tokens are left untouched (the tiled kernels of attention.cu serve them).
+bool attn_tc_supported(int d, int heads);
+int attn_tc_fwd(int passes, const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, cudaStream_t st,
+                const Drop& dr);
+int attn_tc_bwd(int passes, const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d,
+                int heads, int max_T, cudaStream_t st, const Drop& dr);
 // drop (optional): dropout of the attention probabilities, hashed on (level-local query row, head << 24 | key index)
+// tc_passes: 0 = SIMT fp32 kernels only; 3 / 1 = short bags on the tensor cores (attn_tc_*) in split / plain bf16
 int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st,
-                 const Drop* drop = nullptr);
+                 const Drop* drop = nullptr, int tc_passes = 0);
 int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
-                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop = nullptr);
+                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop = nullptr, int tc_passes = 0);
 int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st);
 bool attn_bwd_writes_all(int d, int heads);
 int attn_bwd(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
