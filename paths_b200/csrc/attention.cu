@@ -23,6 +23,7 @@ constexpr int MAXDH = 64;
 __global__ void __launch_bounds__(AW * 32) attn_fwd_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                            float* __restrict__ out, float* __restrict__ lse, int d, int heads,
                                                            int nq_mode, int skip_T, const Drop dr) {
+  pdl_grid_sync();
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
   if (sg.T <= skip_T) return;                        // short bags belong to the *_small kernels
@@ -105,6 +106,7 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dq_kernel(const float* __res
                                                               const float* __restrict__ dout, float* __restrict__ dqkv,
                                                               float* __restrict__ Dvec, int d, int heads, int nq_mode, int skip_T,
                                                               const Drop dr) {
+  pdl_grid_sync();
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
   if (sg.T <= skip_T) return;
@@ -183,6 +185,7 @@ __global__ void __launch_bounds__(AW * 32) attn_bwd_dkv_kernel(const float* __re
                                                                const float* __restrict__ lse, const float* __restrict__ dout,
                                                                const float* __restrict__ Dvec, float* __restrict__ dqkv, int d,
                                                                int heads, int nq_mode, int skip_T, const Drop dr) {
+  pdl_grid_sync();
   const int s = blockIdx.z, h = blockIdx.y, dh = d / heads;
   const Seg sg = seg_of(seg, s);
   if (sg.T <= skip_T) return;
@@ -395,6 +398,7 @@ template <int NKC, bool DROP>
 __global__ void __launch_bounds__(SW * 32) attn_fwd_small_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                                  float* __restrict__ out, float* __restrict__ lse, int d, int heads,
                                                                  int nq_mode, const Drop dr) {
+  pdl_grid_sync();
   const int T = seg_of(seg, blockIdx.y).T;
   if (NKC >= 2 && T <= 32) attn_fwd_small_body<1, DROP>(qkv, seg, out, lse, d, heads, nq_mode, dr);
   else if (NKC >= 3 && T <= 64) attn_fwd_small_body<2, DROP>(qkv, seg, out, lse, d, heads, nq_mode, dr);
@@ -596,6 +600,7 @@ __global__ void __launch_bounds__(SW * 32) attn_bwd_small_kernel(const float* __
                                                                  const float* __restrict__ out, const float* __restrict__ lse,
                                                                  const float* __restrict__ dout, float* __restrict__ dqkv, int d,
                                                                  int heads, int nq_mode, const Drop dr) {
+  pdl_grid_sync();
   const int T = seg_of(seg, blockIdx.y).T;
   if (NKC >= 2 && T <= 32) attn_bwd_small_body<1, DROP>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
   else if (NKC >= 3 && T <= 64) attn_bwd_small_body<2, DROP>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
@@ -625,6 +630,7 @@ __device__ __forceinline__ float pair_sum(float v) { return v + __shfl_xor_sync(
 template <int NT>
 __global__ void __launch_bounds__(2 * NT) attn_fwd_tq_kernel(const float* __restrict__ qkv, const SegGrp seg, float* __restrict__ out,
                                                              float* __restrict__ lse, int d, int heads) {
+  pdl_grid_sync();
   const int h = blockIdx.x;
   const Seg sg = seg_of(seg, blockIdx.y);
   const int T = sg.T;
@@ -698,6 +704,7 @@ template <int NT>
 __global__ void __launch_bounds__(2 * NT, NT == 96 ? 3 : NT == 128 ? 2 : NT == 64 ? 4 : 8) attn_bwd_tq_kernel(const float* __restrict__ qkv, const SegGrp seg, const float* __restrict__ out,
                                                              const float* __restrict__ lse, const float* __restrict__ dout,
                                                              float* __restrict__ dqkv, int d, int heads) {
+  pdl_grid_sync();
   const int h = blockIdx.x;
   const Seg sg = seg_of(seg, blockIdx.y);
   const int T = sg.T;
@@ -795,7 +802,7 @@ int launch_fwd_tq(const float* qkv, const SegGrp& seg, float* out, float* lse, i
   static bool cfg = false;
   const int bytes = 2 * (NT + 3) * 8 * (int)sizeof(float4);
   if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_fwd_tq_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
-  attn_fwd_tq_kernel<NT><<<dim3(heads, B), 2 * NT, bytes, st>>>(qkv, seg, out, lse, d, heads);
+  pdl(attn_fwd_tq_kernel<NT>, dim3(heads, B), 2 * NT, bytes, st)(qkv, seg, out, lse, d, heads);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -805,7 +812,7 @@ int launch_bwd_tq(const float* qkv, const SegGrp& seg, const float* out, const f
   static bool cfg = false;
   const int bytes = 4 * NT * 8 * (int)sizeof(float4) + 2 * NT * (int)sizeof(float);
   if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_bwd_tq_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
-  attn_bwd_tq_kernel<NT><<<dim3(heads, B), 2 * NT, bytes, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads);
+  pdl(attn_bwd_tq_kernel<NT>, dim3(heads, B), 2 * NT, bytes, st)(qkv, seg, out, lse, dout, dqkv, d, heads);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -818,6 +825,7 @@ namespace {
 // key row), then over the head dims for the value sum (coalesced rows, probabilities by shuffle); online softmax over chunks.
 __global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restrict__ qkv, const SegGrp seg,
                                                            float* __restrict__ out, float* __restrict__ lse, int d, int heads, int B) {
+  pdl_grid_sync();
   const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (wid >= B * heads) return;
   const int s = wid / heads, h = wid % heads;
@@ -869,6 +877,7 @@ __global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restri
                                                            const float* __restrict__ out, const float* __restrict__ lse,
                                                            const float* __restrict__ dout, float* __restrict__ dqkv, int d, int heads,
                                                            int B) {
+  pdl_grid_sync();
   const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (wid >= B * heads) return;
   const int s = wid / heads, h = wid % heads;
@@ -932,7 +941,7 @@ int launch_fwd_small_d(const float* qkv, const SegGrp& seg, float* out, float* l
   static bool cfg = false;
   const int bytes = (int)small_fwd_smem(NKC);
   if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_fwd_small_kernel<NKC, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
-  attn_fwd_small_kernel<NKC, DROP><<<dim3(heads, B), SW * 32, bytes, st>>>(qkv, seg, out, lse, d, heads, nq_mode, dr);
+  pdl(attn_fwd_small_kernel<NKC, DROP>, dim3(heads, B), SW * 32, bytes, st)(qkv, seg, out, lse, d, heads, nq_mode, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -948,7 +957,7 @@ int launch_bwd_small_d(const float* qkv, const SegGrp& seg, const float* out, co
   static bool cfg = false;
   const int bytes = (int)small_bwd_smem(NKC);
   if (!cfg) { PATHS_CK(cudaFuncSetAttribute(attn_bwd_small_kernel<NKC, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); cfg = true; }
-  attn_bwd_small_kernel<NKC, DROP><<<dim3(heads, B), SW * 32, bytes, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
+  pdl(attn_bwd_small_kernel<NKC, DROP>, dim3(heads, B), SW * 32, bytes, st)(qkv, seg, out, lse, dout, dqkv, d, heads, nq_mode, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -973,7 +982,7 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
   PATHS_REQUIRE(!dr.thresh || (max_T < (1 << 24) && heads < 256), "attention dropout: bag of %d tokens / %d heads outside the hash's index range",
                 max_T, heads);
   if (d / heads == 32 && nq_mode && !dr.thresh) {    // (with dropout the short-bag / tiled kernels serve the single-query layer too)
-    attn_fwd_nq1_kernel<<<(B * heads + 3) / 4, 128, 0, st>>>(qkv, seg, out, lse, d, heads, B);
+    pdl(attn_fwd_nq1_kernel, (B * heads + 3) / 4, 128, 0, st)(qkv, seg, out, lse, d, heads, B);
     PATHS_LAUNCH_CK();
     return 0;
   }
@@ -1009,7 +1018,7 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
     skip_T = SMALL_MAX_T;
   }
   dim3 grid(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
-  attn_fwd_kernel<<<grid, AW * 32, 0, st>>>(qkv, seg, out, lse, d, heads, nq_mode, skip_T, dr);
+  pdl(attn_fwd_kernel, grid, AW * 32, 0, st)(qkv, seg, out, lse, d, heads, nq_mode, skip_T, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1028,7 +1037,7 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
   int skip_T = 0;
   const Drop dr = drop ? *drop : no_drop();
   if (d / heads == 32 && nq_mode && !dr.thresh) {    // (with dropout and nq_mode the caller zero-fills dqkv: only query rows get a dq)
-    attn_bwd_nq1_kernel<<<(B * heads + 3) / 4, 128, 0, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, B);
+    pdl(attn_bwd_nq1_kernel, (B * heads + 3) / 4, 128, 0, st)(qkv, seg, out, lse, dout, dqkv, d, heads, B);
     PATHS_LAUNCH_CK();
     return 0;
   }
@@ -1064,10 +1073,10 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
     skip_T = SMALL_MAX_T;
   }
   dim3 gq(nq_mode ? 1 : (max_T + QB - 1) / QB, heads, B);
-  attn_bwd_dq_kernel<<<gq, AW * 32, 0, st>>>(qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, nq_mode, skip_T, dr);
+  pdl(attn_bwd_dq_kernel, gq, AW * 32, 0, st)(qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, nq_mode, skip_T, dr);
   PATHS_LAUNCH_CK();
   dim3 gk((max_T + QB - 1) / QB, heads, B);
-  attn_bwd_dkv_kernel<<<gk, AW * 32, 0, st>>>(qkv, seg, lse, dout, Dvec, dqkv, d, heads, nq_mode, skip_T, dr);
+  pdl(attn_bwd_dkv_kernel, gk, AW * 32, 0, st)(qkv, seg, lse, dout, Dvec, dqkv, d, heads, nq_mode, skip_T, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }

@@ -137,6 +137,7 @@ struct FwdCfg {
 template <int NKB, int NP, bool DROP>
 __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __restrict__ qkv, const SegGrp seg, float* __restrict__ out,
                                                                float* __restrict__ lse, int d, int heads, const Drop dr) {
+  pdl_grid_sync();
   using cfg = FwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
   const int h = blockIdx.x;
@@ -272,6 +273,7 @@ template <int NKB, int NP, bool DROP>
 __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __restrict__ qkv, const SegGrp seg, const float* __restrict__ out,
                                                                const float* __restrict__ lse, const float* __restrict__ dout,
                                                                float* __restrict__ dqkv, int d, int heads, const Drop dr) {
+  pdl_grid_sync();
   using cfg = BwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
   const int h = blockIdx.x;
@@ -433,7 +435,7 @@ int launch_fwd(const float* qkv, const SegGrp& seg, float* out, float* lse, int 
   static bool done = false;
   auto kern = attn_tc_fwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, FwdCfg<NKB, NP>::SMEM, &done)) return r;
-  kern<<<dim3(heads, seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st>>>(qkv, seg, out, lse, d, heads, dr);
+  pdl(kern, dim3(heads, seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, d, heads, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -443,7 +445,7 @@ int launch_bwd(const float* qkv, const SegGrp& seg, const float* out, const floa
   static bool done = false;
   auto kern = attn_tc_bwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, BwdCfg<NKB, NP>::SMEM, &done)) return r;
-  kern<<<dim3(heads, seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st>>>(qkv, seg, out, lse, dout, dqkv, d, heads, dr);
+  pdl(kern, dim3(heads, seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, dout, dqkv, d, heads, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }

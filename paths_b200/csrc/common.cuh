@@ -30,6 +30,40 @@ void set_error(const char* fmt, ...);          // records a message for paths_la
 
 constexpr int kNumSMs = 148;                     // B200
 
+// ---- programmatic dependent launch ---------------------------------------------------------------------------------------
+// A step is ~270 dependent launches, most of them a few tens of microseconds long: the drain of one grid and the fill of the
+// next are a measurable share of it.  Every kernel of the library is launched with the programmatic-stream-serialization
+// attribute and starts with pdl_grid_sync(): `launch_dependents` lets the NEXT kernel of the stream become resident as soon as
+// every CTA of this one has started (its CTAs fill the SMs while ours drain), `wait` blocks until the PREVIOUS kernel has
+// completed and flushed its memory -- so no kernel touches global memory before its predecessor is done, and completion stays
+// transitive because every CTA of every kernel executes the wait before anything else.  PATHS_B200_PDL=0 launches plainly
+// (griddepcontrol is then a no-op).
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_grid_sync() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+#endif
+bool pdl_enabled();
+template <typename... KA>
+struct PdlLaunch {
+  void (*kern)(KA...); dim3 grid, block; size_t smem; cudaStream_t st;
+  template <typename... A>
+  void operator()(A&&... a) const {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, KA(static_cast<A&&>(a))...);        // errors surface through PATHS_LAUNCH_CK()
+  }
+};
+template <typename... KA>
+inline PdlLaunch<KA...> pdl(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st) {
+  return PdlLaunch<KA...>{kern, grid, block, smem, st};
+}
+
 // A-operand row source: logical row m of a [M, K] matrix whose columns [0,k0) come from table p0 and
 // columns [k0,K) from table p1, each optionally through a row-index array (idx < 0 => zero row).
 // This is how [x || h_parent] (model/interface.py:49) and packed-token gathers reach a GEMM without

@@ -17,6 +17,11 @@
 
 namespace paths {
 
+bool pdl_enabled() {
+  static const bool on = [] { const char* v = getenv("PATHS_B200_PDL"); return !(v && v[0] == '0'); }();
+  return on;
+}
+
 static thread_local char g_err[1024] = "";
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -128,6 +133,7 @@ struct LevelP { const float *Wuv, *b1, *w2, *b2, *bin, *special, *nfw, *nfb, *Wc
 struct Params { const float *Wg, *bg, *Wmo, *bmo; LevelP level[PATHS_MAX_LEVELS]; };
 
 __global__ void tseg_kernel(const int* __restrict__ seg, int* __restrict__ tseg, int B) {
+  pdl_grid_sync();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B) tseg[i] = seg[i] + i;
 }
@@ -954,7 +960,7 @@ int do_select(paths_engine* e, int l, cudaStream_t st) {
   a.n_parent_local = n.parent_local; a.n_cap = n.cap; a.n_ntok = n.ntok;
   a.overflow = e->overflow; a.slide_cnt = e->slide_cnt; a.slide_fb = e->slide_fb;
   RUN(select_expand(a, st)); e->launches += 2;
-  tseg_kernel<<<(e->B + 255) / 256, 256, 0, st>>>(n.seg, n.tseg, e->B);
+  pdl(tseg_kernel, (e->B + 255) / 256, 256, 0, st)(n.seg, n.tseg, e->B);
   PATHS_LAUNCH_CK(); e->launches++;
   RUN(gather_rows(e->store.grid_ptr, e->store.gh, l + 1, dm.L, e->slide_ids, n.row_slide, n.row_xy, n.X, dm.D, n.cap, n.count, st));
   return 0;
@@ -984,7 +990,7 @@ int do_begin(paths_engine* e, const int32_t* slide_ids, const float* fts_padded,
   RUN(level0_rows(e->store.gw, e->store.gh, e->dm.L, slide_ids, e->B, v.cap, v.count, v.ntok, v.seg, v.row_slide, v.row_xy,
                   v.row_parent, v.parent_local, e->overflow, st));
   e->launches++;
-  tseg_kernel<<<(e->B + 255) / 256, 256, 0, st>>>(v.seg, v.tseg, e->B);
+  pdl(tseg_kernel, (e->B + 255) / 256, 256, 0, st)(v.seg, v.tseg, e->B);
   PATHS_LAUNCH_CK(); e->launches++;
   if (fts_padded && N < 0) {
     PATHS_REQUIRE(-N <= v.cap, "begin: %d packed level-0 rows exceed the level's capacity %d", -N, v.cap);

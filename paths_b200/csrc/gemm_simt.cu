@@ -31,6 +31,7 @@ template <bool B_KN>
 __global__ void __launch_bounds__(NT) gemm_nt_kernel(RowSrc A, const float* __restrict__ B, int ldb,
                                                      float* __restrict__ C, int ldc, const float* __restrict__ bias,
                                                      int M_host, const int* __restrict__ M_dev, int N, int K, int flags) {
+  pdl_grid_sync();
   __shared__ __align__(16) float As[2][BK][BM + PAD];
   __shared__ __align__(16) float Bs[2][BK][BN + PAD];
   const int M = M_dev ? *M_dev : M_host;
@@ -147,6 +148,7 @@ __global__ void __launch_bounds__(NT) gemm_nt_kernel(RowSrc A, const float* __re
 // ---- C += P^T . Q  (reduction over rows) -------------------------------------------------------------------
 __global__ void __launch_bounds__(NT) gemm_tn_kernel(const float* __restrict__ P, int ldp, RowSrc Q, float* __restrict__ C,
                                                      int ldc, int M_host, const int* __restrict__ M_dev, int NI, int NJ, int pvec) {
+  pdl_grid_sync();
   __shared__ __align__(16) float Ps[2][BK][BM + PAD];
   __shared__ __align__(16) float Qs[2][BK][BN + PAD];
   const int M = M_dev ? *M_dev : M_host;
@@ -220,6 +222,7 @@ __global__ void __launch_bounds__(NT) gemm_tn_kernel(const float* __restrict__ P
 // out[n] += sum_m X[m, n].  Vector path (N % 4 == 0, ld % 4 == 0, N <= 1024): a thread keeps one float4 column group and
 // walks rows (independent loads, unrolled), one shared-memory combine and one atomic per column per block.
 __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, int ld, MutL outl, Grp grp, int N) {
+  pdl_grid_sync();
   const int M = grp_count(grp, blockIdx.y);                // blockIdx.y = row group of the concatenated buffer
   X += (size_t)pick(grp.roff, blockIdx.y) * ld;
   float* out = pick(outl.p, blockIdx.y);
@@ -248,6 +251,7 @@ __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X
 // scalar fallback for odd widths (the 4-wide classifier bias)
 __global__ void __launch_bounds__(256) colsum_scalar_kernel(const float* __restrict__ X, int ld, float* __restrict__ out,
                                                             int M_host, const int* __restrict__ M_dev, int N) {
+  pdl_grid_sync();
   __shared__ float red[8][33];
   const int M = M_dev ? *M_dev : M_host;
   const int n = blockIdx.x * 32 + threadIdx.x % 32, y = threadIdx.x / 32;
@@ -273,8 +277,8 @@ int gemm_nt_simt(const RowSrc& A, const float* B, int ldb, int b_kn, float* C, i
   PATHS_REQUIRE(b_kn || ldb % 4 == 0, "gemm_nt: ldb must be a multiple of 4");
   if (M_host <= 0 || N <= 0) return 0;
   dim3 grid((N + BN - 1) / BN, (M_host + BM - 1) / BM);
-  if (b_kn) gemm_nt_kernel<true><<<grid, NT, 0, st>>>(A, B, ldb, C, ldc, bias, M_host, M_dev, N, K, flags);
-  else gemm_nt_kernel<false><<<grid, NT, 0, st>>>(A, B, ldb, C, ldc, bias, M_host, M_dev, N, K, flags);
+  if (b_kn) pdl(gemm_nt_kernel<true>, grid, NT, 0, st)(A, B, ldb, C, ldc, bias, M_host, M_dev, N, K, flags);
+  else pdl(gemm_nt_kernel<false>, grid, NT, 0, st)(A, B, ldb, C, ldc, bias, M_host, M_dev, N, K, flags);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -290,7 +294,7 @@ int gemm_tn_simt(const float* P, int ldp, const RowSrc& Q, float* C, int ldc, in
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
   dim3 grid((NJ + BN - 1) / BN, (NI + BM - 1) / BM, splits);
-  gemm_tn_kernel<<<grid, NT, 0, st>>>(P, ldp, Q, C, ldc, M_host, M_dev, NI, NJ, ldp % 4 == 0 ? 1 : 0);
+  pdl(gemm_tn_kernel, grid, NT, 0, st)(P, ldp, Q, C, ldc, M_host, M_dev, NI, NJ, ldp % 4 == 0 ? 1 : 0);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -306,7 +310,7 @@ int colsum_accum_grp(const float* X, int ld, const MutL& out, const Grp& grp, in
   int g = (cap + 8 * rpb - 1) / (8 * rpb);                // few blocks: the final same-address atomics serialise in L2
   if (g > 96) g = 96;
   if (g < 1) g = 1;
-  colsum_kernel<<<dim3(g, grp.n), 256, 0, st>>>(X, ld, out, grp, N);
+  pdl(colsum_kernel, dim3(g, grp.n), 256, 0, st)(X, ld, out, grp, N);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -318,7 +322,7 @@ int colsum_accum(const float* X, int ld, float* out, int M_host, const int* M_de
     int splits = (M_host + 255) / 256;
     if (splits > 64) splits = 64;
     dim3 grid((N + 31) / 32, splits);
-    colsum_scalar_kernel<<<grid, 256, 0, st>>>(X, ld, out, M_host, M_dev, N);
+    pdl(colsum_scalar_kernel, grid, 256, 0, st)(X, ld, out, M_host, M_dev, N);
   }
   PATHS_LAUNCH_CK();
   return 0;

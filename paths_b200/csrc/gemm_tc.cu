@@ -73,6 +73,7 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int warp, int 
 // Rows [M, round_up(M, 64)) are zero-filled so a reduction over rows (TN) may run whole 64-row blocks.
 __global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host, const int* __restrict__ M_dev, int K, Planes dst, int col0,
                                                            int want_lo) {
+  pdl_grid_sync();
   const int M = M_dev ? *M_dev : M_host;
   const int Mpad = planes_rows_to_write(dst, M);
   const int lane = threadIdx.x & 31;
@@ -99,6 +100,7 @@ __global__ void __launch_bounds__(256) split_planes_kernel(RowSrc A, int M_host,
 template <int J, int R>
 __global__ void __launch_bounds__(256) split_planes_grp_kernel(const float* __restrict__ A, int lda, int K, Planes dst, Grp grp, int want_lo,
                                                                MutL csum) {
+  pdl_grid_sync();
   const int gi = blockIdx.y;
   const int M = grp_count(grp, gi);
   int mx = 0;
@@ -257,6 +259,7 @@ __global__ void __launch_bounds__((A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA
 gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Operand oa, Operand ob,
                 const RowSrc sa, const RowSrc sb, float* __restrict__ C, int ldc, const GemmGrp gg, int b_grp_rows, int OI_host, int OJ,
                 int R_host, int flags, int segmax) {
+  pdl_grid_sync();
   // Persistent: one CTA per SM walks work units u = blockIdx.x, += gridDim.x; unit = (row tile, column tile, reduction split)
   // with column tiles fastest so CTAs that run together share A rows in L2.  Two TMEM accumulators: the epilogue of unit n
   // drains one while the MMA warp fills the other.
@@ -565,6 +568,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 struct PackJob { const float* src; __nv_bfloat16* dst; int R, Cc, ld, ldp; };
 
 __global__ void __launch_bounds__(256) pack_weights_kernel(const PackJob* __restrict__ jobs) {
+  pdl_grid_sync();
   const PackJob jb = jobs[blockIdx.y];
   const size_t total = (size_t)jb.R * jb.ldp;
   for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
@@ -687,7 +691,7 @@ int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand
   long units = (long)((OJ + BN - 1) / BN) * row_tiles;
   if (units < 1) units = 1;
   const int grid = SK ? grid_sk : (units < kNumSMs ? (int)units : kNumSMs);
-  kern<<<grid, (A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA, Cfg<BN, NP>::SMEM, st>>>(
+  pdl(kern, grid, (A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA, Cfg<BN, NP>::SMEM, st)(
       A_CVT ? dummy : *ma, B_CVT ? dummy : *mb, oa, ob, sa, sb, C, ldc, gg, b_grp_rows, OI_host, OJ, R_host, flags, segmax);
   PATHS_LAUNCH_CK();
   return 0;
@@ -698,6 +702,7 @@ int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand
 template <int BN, int PG>
 __global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict__ ws, const GemmGrp gg, int ldc, int NI, int NJ, int G,
                                                         int segmax) {
+  pdl_grid_sync();
   constexpr int OUT = 256 / PG;
   int R = 0;
 #pragma unroll
@@ -806,7 +811,7 @@ int build_pack_jobs(const float* const* srcs, int n, void* jobs_dev, int* n_jobs
 // ... and re-splits them into bf16 (hi, lo) planes: one launch per step (the weights change with every optimizer step).
 int run_pack_jobs(const void* jobs_dev, int n_jobs, cudaStream_t st) {
   if (n_jobs <= 0) return 0;
-  pack_weights_kernel<<<dim3(296, (unsigned)n_jobs), 256, 0, st>>>(reinterpret_cast<const PackJob*>(jobs_dev));
+  pdl(pack_weights_kernel, dim3(296, (unsigned)n_jobs), 256, 0, st)(reinterpret_cast<const PackJob*>(jobs_dev));
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -836,7 +841,7 @@ int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Plane
                 K, dst.ldp);
   if (M_host <= 0) return 0;
   int g = (planes_pad_rows(M_host) + 7) / 8; if (g > 16 * kNumSMs) g = 16 * kNumSMs;
-  split_planes_kernel<<<g, 256, 0, st>>>(A, M_host, M_dev, K, dst, col0, want_lo ? 1 : 0);
+  pdl(split_planes_kernel, g, 256, 0, st)(A, M_host, M_dev, K, dst, col0, want_lo ? 1 : 0);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -974,10 +979,10 @@ static int tn_impl(int passes, const Planes* P, int p_col0, const Planes* Q, int
                                                                 G, segmax, st);                                                      \
     if (r) return r;                                                                                                                   \
     if (4 * tiles >= G)                                                                                                                \
-      tn_reduce_kernel<BN_, 1><<<dim3(tiles, BM * BN_ / 4 / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(ws), gg, ldc, NI, NJ, \
+      pdl(tn_reduce_kernel<BN_, 1>, dim3(tiles, BM * BN_ / 4 / 256), 256, 0, st)(reinterpret_cast<const float4*>(ws), gg, ldc, NI, NJ, \
                                                                                G, segmax);                                            \
     else                                                                                                                               \
-      tn_reduce_kernel<BN_, 8><<<dim3(tiles, BM * BN_ / 4 / 32), 256, 0, st>>>(reinterpret_cast<const float4*>(ws), gg, ldc, NI, NJ,  \
+      pdl(tn_reduce_kernel<BN_, 8>, dim3(tiles, BM * BN_ / 4 / 32), 256, 0, st)(reinterpret_cast<const float4*>(ws), gg, ldc, NI, NJ,  \
                                                                               G, segmax);                                             \
     PATHS_LAUNCH_CK();                                                                                                                 \
     return 0;                                                                                                                          \
@@ -1005,10 +1010,10 @@ int split_rows_grp(const float* A, int lda, int K, const Planes& dst, const Grp&
   if (colsum && g > kNumSMs) g = kNumSMs;                    // fewer blocks: fewer same-address atomics at the end
   const MutL cs = colsum ? *colsum : mutl1(nullptr);
   const dim3 grid(g, grp.n);
-  if (K <= 128) split_planes_grp_kernel<1, 4><<<grid, 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
-  else if (K <= 256) split_planes_grp_kernel<2, 2><<<grid, 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
-  else if (K <= 384) split_planes_grp_kernel<3, 2><<<grid, 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
-  else split_planes_grp_kernel<4, 1><<<grid, 256, 0, st>>>(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
+  if (K <= 128) pdl(split_planes_grp_kernel<1, 4>, grid, 256, 0, st)(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
+  else if (K <= 256) pdl(split_planes_grp_kernel<2, 2>, grid, 256, 0, st)(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
+  else if (K <= 384) pdl(split_planes_grp_kernel<3, 2>, grid, 256, 0, st)(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
+  else pdl(split_planes_grp_kernel<4, 1>, grid, 256, 0, st)(A, lda, K, dst, grp, want_lo ? 1 : 0, cs);
   PATHS_LAUNCH_CK();
   return 0;
 }

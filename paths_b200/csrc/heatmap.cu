@@ -17,6 +17,7 @@ __device__ __forceinline__ int shr_floor(int v, int d) { return v >> d; }       
 // assignment lets later patches overwrite earlier ones, heatmap_visualise.py:152-165).  One block per patch.
 __global__ void __launch_bounds__(256) heat_owner_kernel(const int* __restrict__ locs_yx, const int* __restrict__ level_off, int L, int P,
                                                          int H, int W, int* __restrict__ owner) {
+  pdl_grid_sync();
   const int i = blockIdx.x;
   int d = 0;
   while (d + 1 < L && i >= level_off[d + 1]) ++d;
@@ -40,6 +41,7 @@ __global__ void __launch_bounds__(256) heat_owner_kernel(const int* __restrict__
 __global__ void __launch_bounds__(256) heat_fold_kernel(const int* __restrict__ owner, const float* __restrict__ imp,
                                                         const int* __restrict__ level_off, int L, int H, int W, double* __restrict__ out,
                                                         unsigned long long* __restrict__ min_bits) {
+  pdl_grid_sync();
   const size_t n = (size_t)H * W;
   unsigned long long local_min = ~0ull;
   for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (size_t)gridDim.x * blockDim.x) {
@@ -60,6 +62,7 @@ __global__ void __launch_bounds__(256) heat_fold_kernel(const int* __restrict__ 
 // Pass 3: alpha = 0.5 where covered (> 0), zeros replaced by the smallest positive value (heatmap_visualise.py:175-176).
 __global__ void __launch_bounds__(256) heat_fill_kernel(double* __restrict__ out, float* __restrict__ alpha, size_t n,
                                                         const unsigned long long* __restrict__ min_bits) {
+  pdl_grid_sync();
   const unsigned long long mb = *min_bits;
   const double mn = mb == ~0ull ? 0.0 : __longlong_as_double((long long)mb);
   for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (size_t)gridDim.x * blockDim.x) {
@@ -91,15 +94,15 @@ int paths_heatmap_composite(const int32_t* locs_yx, const float* importance, con
   PATHS_CK(cudaMemsetAsync(owner, 0, (size_t)L * H * W * sizeof(int), st));
   PATHS_CK(cudaMemsetAsync(min_bits, 0xff, sizeof(unsigned long long), st));
   if (n_patches > 0) {
-    heat_owner_kernel<<<n_patches, 256, 0, st>>>(locs_yx, level_off, L, patch_size, H, W, owner);
+    pdl(heat_owner_kernel, n_patches, 256, 0, st)(locs_yx, level_off, L, patch_size, H, W, owner);
     PATHS_LAUNCH_CK();
   }
   const size_t n = (size_t)H * W;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
-  heat_fold_kernel<<<blocks, 256, 0, st>>>(owner, importance, level_off, L, H, W, out, min_bits);
+  pdl(heat_fold_kernel, blocks, 256, 0, st)(owner, importance, level_off, L, H, W, out, min_bits);
   PATHS_LAUNCH_CK();
-  heat_fill_kernel<<<blocks, 256, 0, st>>>(out, alpha, n, min_bits);
+  pdl(heat_fill_kernel, blocks, 256, 0, st)(out, alpha, n, min_bits);
   PATHS_LAUNCH_CK();
   return 0;
 }

@@ -17,6 +17,7 @@ struct SkipList { long long a[16], b[16]; int n; };
 __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                     float* __restrict__ v, long long n_live, long long n_total, SkipList skip,
                                                     float lr, float b1, float b2, float eps, float wd, float inv_bc1, float inv_sqrt_bc2) {
+  pdl_grid_sync();
   const long long n4 = n_total / 4;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     const long long e0 = i * 4;
@@ -73,7 +74,7 @@ extern "C" int paths_adamw_step(float* params, const float* grads, float* exp_av
   long long blocks = (n_total / 4 + 255) / 256;
   if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
   if (blocks < 1) return 0;
-  adamw_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(params, grads, exp_avg, exp_avg_sq, n_live, n_total, sk, lr,
+  pdl(adamw_kernel, (unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream))(params, grads, exp_avg, exp_avg_sq, n_live, n_total, sk, lr,
                                                                                beta1, beta2, eps, weight_decay, (float)(1.0 / bc1),
                                                                                (float)(1.0 / sqrt(bc2)));
   PATHS_LAUNCH_CK();

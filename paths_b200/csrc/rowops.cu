@@ -23,6 +23,7 @@ __global__ void __launch_bounds__(TPB) gather_rows_kernel(const float* const* __
                                                           int level, int L, const int* __restrict__ slide_ids,
                                                           const int* __restrict__ row_slide, const int* __restrict__ row_xy,
                                                           float* __restrict__ X, int D, int M_host, const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   ROW_LOOP(m, M) {
     const int s = row_slide[m];
@@ -44,6 +45,7 @@ __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<floa
 __global__ void __launch_bounds__(TPB) lstm_point1_fwd_kernel(float* __restrict__ G, const float* __restrict__ Cprev,
                                                               const int* __restrict__ parent, float* __restrict__ Cn, Planes CnP, int want_lo,
                                                               int activated, int D, int C, int M_host, const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   const int ldg = 3 * C + D;
   const int Mw = CnP.p ? planes_rows_to_write(CnP, M) : M;
@@ -84,6 +86,7 @@ __global__ void __launch_bounds__(TPB) lstm_point2_fwd_kernel(float* __restrict_
                                                               const float* __restrict__ X, float* __restrict__ H,
                                                               float* __restrict__ Y, Planes YP, int want_lo, int D, int C, int M_host,
                                                               const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   const int ldg = 3 * C + D;
   const int Mw = YP.p ? planes_rows_to_write(YP, M) : M;
@@ -134,6 +137,7 @@ __global__ void __launch_bounds__(256) lstm_point2_bwd_kernel(const float* __res
                                                               float* __restrict__ dP, Planes dPP, float* __restrict__ dG, Planes dGP,
                                                               float* __restrict__ db_mo, float* __restrict__ db_o, int want_lo, int D, int C,
                                                               int M_host, const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   const int ldg = 3 * C + D;
   const int Mw = dPP.p ? planes_rows_to_write(dPP, M) : M;
@@ -216,6 +220,7 @@ __global__ void __launch_bounds__(256) lstm_point1_bwd_kernel(const float* __res
                                                               const int* __restrict__ parent, float* __restrict__ dG, Planes dGP,
                                                               float* __restrict__ dCrow, float* __restrict__ db_g, int want_lo, int D, int C,
                                                               int M_host, const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   const int ldg = 3 * C + D;
   const int G4 = C / 4, R = 256 / G4;
@@ -274,6 +279,7 @@ __global__ void __launch_bounds__(256) lstm_point1_bwd_kernel(const float* __res
 __global__ void __launch_bounds__(TPB) parent_sum_kernel(const int* __restrict__ child_of, const float* __restrict__ dHrow,
                                                          const float* __restrict__ dCrow, float* __restrict__ dHc,
                                                          float* __restrict__ dCc, int D, int C, int M_host, const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   ROW_LOOP(m, M) {
     int ch[4];
@@ -316,6 +322,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_fwd_kernel(float* __restrict__ UV
                                                           const int* __restrict__ seg, float* __restrict__ alpha,
                                                           float* __restrict__ tok, int I, int d, int imp_mul, int pe_mode,
                                                           int mode, int M_host, const int* M_dev) {
+  pdl_grid_sync();
   // mode 0: importance + token (LSTM path); 1: importance only; 2: token only, unscaled (RNN variant: V = Z.W_in^T)
   const int M = row_count(M_host, M_dev);
   const int ld = I + d;
@@ -352,6 +359,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_fwd4_kernel(float* __restrict__ U
                                                            const int* __restrict__ seg, float* __restrict__ alpha,
                                                            float* __restrict__ tok, int I, int d, int imp_mul, int pe_mode,
                                                            int M_host, const int* M_dev) {
+  pdl_grid_sync();
   constexpr int R = 2;
   const int M = row_count(M_host, M_dev);
   const int ld = I + d;
@@ -424,6 +432,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_fwd4_kernel(float* __restrict__ U
 
 __global__ void __launch_bounds__(TPB) special_fill_kernel(const float* __restrict__ special, const int* __restrict__ seg,
                                                            float* __restrict__ tok, int d, int B) {
+  pdl_grid_sync();
   ROW_LOOP(s, B) {
     float* t = tok + (size_t)(seg[s] + s) * d;
     for (int c = lane; c < d; c += 32) t[c] = special[c];
@@ -438,6 +447,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd_kernel(const float* __restric
                                                           int want_lo, float* __restrict__ db1, float* __restrict__ dw2,
                                                           float* __restrict__ db2, float* __restrict__ dbin, int I, int d, int imp_mul,
                                                           int mode, int M_host, const int* M_dev) {
+  pdl_grid_sync();
   // mode 0: full backward of imp_tok_fwd; 2: token part only (dV = dtok, dbin), the importance head is handled elsewhere
   const int M = row_count(M_host, M_dev);
   const int ld = I + d;
@@ -525,6 +535,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd4_kernel(const float* __restri
                                                            int want_lo, float* __restrict__ db1, float* __restrict__ dw2,
                                                            float* __restrict__ db2, float* __restrict__ dbin, int I, int d, int imp_mul,
                                                            int M_host, const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   const int ld = I + d;
   const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -627,6 +638,7 @@ __global__ void __launch_bounds__(TPB) imp_tok_bwd4_kernel(const float* __restri
 __global__ void __launch_bounds__(TPB) rnn_z_fwd_kernel(const float* __restrict__ X, const float* __restrict__ alpha,
                                                         const float* __restrict__ hctx, float* __restrict__ Z, int D, int imp_mul,
                                                         int M_host, const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   ROW_LOOP(m, M) {
     const float a = imp_mul ? alpha[m] : 1.f;
@@ -645,6 +657,7 @@ __global__ void __launch_bounds__(TPB) rnn_alpha_bwd_kernel(float* __restrict__ 
                                                             float* __restrict__ dUV, float* __restrict__ db1, float* __restrict__ dw2,
                                                             float* __restrict__ db2, int D, int I, int d, int imp_mul, int M_host,
                                                             const int* M_dev) {
+  pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
   const int ld = I + d;
   float a_b1[8], a_w2[8], a_b2 = 0.f;
@@ -700,6 +713,7 @@ __global__ void __launch_bounds__(TPB) rnn_alpha_bwd_kernel(float* __restrict__ 
 // ---- slide_ctx_mode "concat" (paths.py:134-137): logits = Wc . [F_0 | ... | F_l] + bc ------------------------------------
 __global__ void __launch_bounds__(TPB) head_concat_fwd_kernel(FList fl, const float* __restrict__ Wc, const float* __restrict__ bc,
                                                               float* __restrict__ logits, int d, int nl, int B) {
+  pdl_grid_sync();
   const int ldw = fl.n * d;
   ROW_LOOP(s, B) {
     for (int k = 0; k < nl; ++k) {
@@ -714,6 +728,7 @@ __global__ void __launch_bounds__(TPB) head_concat_fwd_kernel(FList fl, const fl
 // dF_j = dlogits . Wc[:, j*d:(j+1)*d] for every level j <= l
 __global__ void __launch_bounds__(TPB) head_concat_bwd_kernel(const float* __restrict__ dlogits, const float* __restrict__ Wc, GList gl,
                                                               int d, int nl, int B) {
+  pdl_grid_sync();
   const int ldw = gl.n * d;
   ROW_LOOP(s, B) {
     for (int j = 0; j < gl.n; ++j)
@@ -728,6 +743,7 @@ __global__ void __launch_bounds__(TPB) head_concat_bwd_kernel(const float* __res
 // dspecial[c] += sum_b dtok[special token of slide b, c]: a block sums 8 slides (one per warp) through shared memory and adds
 // its 8-row partial with one atomic per column.
 __global__ void __launch_bounds__(256) special_grad_kernel(const float* __restrict__ dtok, GIdx sg, MutL dsp, int d, int B) {
+  pdl_grid_sync();
   __shared__ float part[8][256];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int b = blockIdx.x * 8 + w;
@@ -756,6 +772,7 @@ __global__ void __launch_bounds__(256) special_grad_kernel(const float* __restri
 __global__ void __launch_bounds__(TPB) res_ln_fwd_kernel(const float* __restrict__ res, GIdx ri, const float* __restrict__ add, PtrL biasl,
                                                          PtrL gammal, PtrL betal, float* __restrict__ y, float* __restrict__ xhat,
                                                          float* __restrict__ rstd, int d, float eps, Grp grp) {
+  pdl_grid_sync();
   const int gi = blockIdx.y;
   const int M = grp_count(grp, gi);
   const size_t r0 = pick(grp.roff, gi);
@@ -805,6 +822,7 @@ __global__ void __launch_bounds__(TPB) ln_bwd_kernel(const float* __restrict__ d
                                                      const float* __restrict__ xhat, const float* __restrict__ rstd, PtrL gammal,
                                                      float* __restrict__ dx, GIdx di, int accum, MutL dgammal, MutL dbetal, MutL dbiasl,
                                                      int d, Grp grp) {
+  pdl_grid_sync();
   const int gi = blockIdx.y;
   const int M = grp_count(grp, gi);
   const size_t r0 = pick(grp.roff, gi);
@@ -871,6 +889,7 @@ template <int Q>
 __global__ void __launch_bounds__(TPB) res_ln_fwd4_kernel(const float* __restrict__ res, GIdx ri, const float* __restrict__ add, PtrL biasl,
                                                           PtrL gammal, PtrL betal, float* __restrict__ y, float* __restrict__ xhat,
                                                           float* __restrict__ rstd, int d, float eps, Grp grp) {
+  pdl_grid_sync();
   const int gi = blockIdx.y;
   const int M = grp_count(grp, gi);
   const size_t r0 = pick(grp.roff, gi);
@@ -947,6 +966,7 @@ __global__ void __launch_bounds__(TPB) ln_bwd4_kernel(const float* __restrict__ 
                                                       const float* __restrict__ xhat, const float* __restrict__ rstd, PtrL gammal,
                                                       float* __restrict__ dx, GIdx di, int accum, MutL dgammal, MutL dbetal, MutL dbiasl,
                                                       int d, Grp grp) {
+  pdl_grid_sync();
   const int gi = blockIdx.y;
   const int M = grp_count(grp, gi);
   const size_t r0 = pick(grp.roff, gi);
@@ -1037,6 +1057,7 @@ __global__ void __launch_bounds__(TPB) ln_bwd4_kernel(const float* __restrict__ 
 // up to round_up(longest group, 64) like split_planes_grp_kernel) instead of back to dH: its only consumers are contractions.
 __global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, const float* __restrict__ H, int ld, Grp grp, MutL dbiasl,
                                                        Planes outp, int want_lo, float scale) {
+  pdl_grid_sync();
   const int M = grp_count(grp, blockIdx.y);
   const int r0 = pick(grp.roff, blockIdx.y);
   dH += (size_t)r0 * ld; H += (size_t)r0 * ld;
@@ -1086,6 +1107,7 @@ __global__ void __launch_bounds__(256) relu_bwd_kernel(float* __restrict__ dH, c
 
 __global__ void __launch_bounds__(256) dropout_fwd_kernel(const float* __restrict__ in, float* __restrict__ out, int cols, PtrL biasl,
                                                           Grp grp, GIdx hrow, Drop dr) {
+  pdl_grid_sync();
   const int gi = blockIdx.y;
   const int M = grp_count(grp, gi);
   const size_t r0 = (size_t)pick(grp.roff, gi);
@@ -1110,6 +1132,7 @@ __global__ void __launch_bounds__(256) dropout_fwd_kernel(const float* __restric
 
 __global__ void __launch_bounds__(256) dropout_bwd_kernel(const float* __restrict__ g, float* __restrict__ out, int cols, MutL dbiasl,
                                                           Grp grp, GIdx hrow, Drop dr) {
+  pdl_grid_sync();
   const int gi = blockIdx.y;
   const int M = grp_count(grp, gi);
   const size_t r0 = (size_t)pick(grp.roff, gi);
@@ -1146,12 +1169,14 @@ __global__ void __launch_bounds__(256) dropout_bwd_kernel(const float* __restric
 }
 
 __global__ void zero_rows_kernel(float* __restrict__ X, size_t ld, int M_host, const int* M_dev, int M_extra) {
+  pdl_grid_sync();
   const size_t n = (size_t)(row_count(M_host, M_dev) + M_extra) * ld;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) X[i] = 0.f;
 }
 
 // dst[idx[m], :] += src[m, :]   (m < B rows; idx unique)
 __global__ void __launch_bounds__(TPB) scatter_add_rows_kernel(const float* __restrict__ src, GIdx di, float* __restrict__ dst, int d, Grp grp) {
+  pdl_grid_sync();
   const int B = grp_count(grp, blockIdx.y);
   src += (size_t)pick(grp.roff, blockIdx.y) * d;
   dst += (size_t)pick(di.roff, blockIdx.y) * d;
@@ -1167,6 +1192,7 @@ __global__ void __launch_bounds__(TPB) scatter_add_rows_kernel(const float* __re
 __global__ void __launch_bounds__(TPB) head_fwd_kernel(const float* __restrict__ z, const float* __restrict__ Fprev,
                                                        const float* __restrict__ Wc, const float* __restrict__ bc,
                                                        float* __restrict__ F, float* __restrict__ logits, int d, int nl, int B) {
+  pdl_grid_sync();
   ROW_LOOP(s, B) {
     float v[8];
 #pragma unroll
@@ -1188,6 +1214,7 @@ __global__ void __launch_bounds__(TPB) head_fwd_kernel(const float* __restrict__
 // dF = dF_in + dlogits.Wc      (dWc, dbc come from gemm_tn / colsum_accum in the engine)
 __global__ void __launch_bounds__(TPB) head_bwd_kernel(const float* __restrict__ dlogits, const float* __restrict__ dF_in,
                                                        const float* __restrict__ Wc, float* __restrict__ dF, int d, int nl, int B) {
+  pdl_grid_sync();
   ROW_LOOP(s, B) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
@@ -1209,6 +1236,7 @@ __global__ void loss_kernel(const float* __restrict__ logits, const int* __restr
                             float* __restrict__ hazards, float* __restrict__ loss_per, float* __restrict__ risk,
                             float* __restrict__ dlogits, int nl, int B, int task, float alpha, float eps,
                             float scale /* 1 / global batch */) {
+  pdl_grid_sync();
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= B) return;
   const float* lg = logits + (size_t)s * nl;
@@ -1259,6 +1287,7 @@ __global__ void loss_kernel(const float* __restrict__ logits, const int* __restr
 }
 
 __global__ void loss_reduce_kernel(const float* __restrict__ loss_per, float* __restrict__ loss, int B, float scale) {
+  pdl_grid_sync();
   __shared__ float red[256];
   float s = 0.f;
   for (int i = threadIdx.x; i < B; i += 256) s += loss_per[i];
@@ -1277,7 +1306,7 @@ int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, c
                 const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st) {
   PATHS_REQUIRE(D % 4 == 0, "gather_rows: D must be a multiple of 4");
   if (M_host <= 0) return 0;
-  gather_rows_kernel<<<row_grid(M_host), TPB, 0, st>>>(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev);
+  pdl(gather_rows_kernel, row_grid(M_host), TPB, 0, st)(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1286,14 +1315,14 @@ int lstm_point1_fwd(float* G, const float* Cprev, const int* parent, float* Cn, 
                     const int* M_dev, cudaStream_t st) {
   PATHS_REQUIRE(D % 4 == 0 && C % 4 == 0, "lstm: D and C must be multiples of 4");
   if (M_host <= 0) return 0;
-  lstm_point1_fwd_kernel<<<row_grid(M_host + 64), TPB, 0, st>>>(G, Cprev, parent, Cn, CnP, want_lo, activated, D, C, M_host, M_dev);
+  pdl(lstm_point1_fwd_kernel, row_grid(M_host + 64), TPB, 0, st)(G, Cprev, parent, Cn, CnP, want_lo, activated, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int lstm_point2_fwd(float* Pt, const float* G, const float* X, float* H, float* Y, const Planes& YP, int want_lo, int D, int C, int M_host,
                     const int* M_dev, cudaStream_t st) {
   if (M_host <= 0) return 0;
-  lstm_point2_fwd_kernel<<<row_grid(M_host + 64), TPB, 0, st>>>(Pt, G, X, H, Y, YP, want_lo, D, C, M_host, M_dev);
+  pdl(lstm_point2_fwd_kernel, row_grid(M_host + 64), TPB, 0, st)(Pt, G, X, H, Y, YP, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1311,8 +1340,8 @@ int lstm_point2_bwd(const float* dY, const float* dHc, const int* child_of, cons
     if (occ[wide] > 4) occ[wide] = 4;
   }
   int g = (M_host + 64 + P2R - 1) / P2R; if (g > occ[wide] * kNumSMs) g = occ[wide] * kNumSMs;
-  if (wide) lstm_point2_bwd_kernel<CG><<<g, 256, 0, st>>>(dY, dHc, child_of, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
-  else lstm_point2_bwd_kernel<1><<<g, 256, 0, st>>>(dY, dHc, child_of, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
+  if (wide) pdl(lstm_point2_bwd_kernel<CG>, g, 256, 0, st)(dY, dHc, child_of, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
+  else pdl(lstm_point2_bwd_kernel<1>, g, 256, 0, st)(dY, dHc, child_of, Pt, G, dP, dPP, dG, dGP, db_mo, db_o, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1322,14 +1351,14 @@ int lstm_point1_bwd(const float* dCn, const float* dCc, const int* child_of, con
   if (M_host <= 0) return 0;
   const int R = 256 / (C / 4);
   int g = (M_host + 64 + R - 1) / R; if (g > 3 * kNumSMs) g = 3 * kNumSMs;
-  lstm_point1_bwd_kernel<<<g, 256, 0, st>>>(dCn, dCc, child_of, G, Cprev, parent, dG, dGP, dCrow, db_g, want_lo, D, C, M_host, M_dev);
+  pdl(lstm_point1_bwd_kernel, g, 256, 0, st)(dCn, dCc, child_of, G, Cprev, parent, dG, dGP, dCrow, db_g, want_lo, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int parent_sum(const int* child_of, const float* dHrow, const float* dCrow, float* dHc, float* dCc, int D, int C, int M_host,
                const int* M_dev, cudaStream_t st) {
   if (M_host <= 0) return 0;
-  parent_sum_kernel<<<row_grid(M_host), TPB, 0, st>>>(child_of, dHrow, dCrow, dHc, dCc, D, C, M_host, M_dev);
+  pdl(parent_sum_kernel, row_grid(M_host), TPB, 0, st)(child_of, dHrow, dCrow, dHc, dCc, D, C, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1344,17 +1373,17 @@ int imp_tok_fwd(float* UV, const float* b1, const float* w2, const float* b2, co
   if (vec) {
     int g = (M_host + 2 * WPB - 1) / (2 * WPB);
     if (g > 8 * kNumSMs) g = 8 * kNumSMs;
-    if (I <= 128 && d <= 128) imp_tok_fwd4_kernel<1><<<g, TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul, pe_mode, M_host, M_dev);
-    else imp_tok_fwd4_kernel<2><<<g, TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul, pe_mode, M_host, M_dev);
+    if (I <= 128 && d <= 128) pdl(imp_tok_fwd4_kernel<1>, g, TPB, 0, st)(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul, pe_mode, M_host, M_dev);
+    else pdl(imp_tok_fwd4_kernel<2>, g, TPB, 0, st)(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul, pe_mode, M_host, M_dev);
   } else {
-    imp_tok_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul,
+    pdl(imp_tok_fwd_kernel, row_grid(M_host), TPB, 0, st)(UV, b1, w2, b2, bin, div, row_slide, row_xy, seg, alpha, tok, I, d, imp_mul,
                                                          pe_mode, mode, M_host, M_dev);
   }
   PATHS_LAUNCH_CK();
   return 0;
 }
 int special_fill(const float* special, const int* seg, float* tok, int d, int B, cudaStream_t st) {
-  special_fill_kernel<<<row_grid(B), TPB, 0, st>>>(special, seg, tok, d, B);
+  pdl(special_fill_kernel, row_grid(B), TPB, 0, st)(special, seg, tok, d, B);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1375,13 +1404,13 @@ int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const fl
     }
     g = (M_host + 64 + WPB * ITR - 1) / (WPB * ITR);
     if (g > occ[wide] * kNumSMs) g = occ[wide] * kNumSMs;     // one resident wave: each block ends with up to 3 * 256 atomics
-    if (wide) imp_tok_bwd4_kernel<2><<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, M_host, M_dev);
-    else imp_tok_bwd4_kernel<1><<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, M_host, M_dev);
+    if (wide) pdl(imp_tok_bwd4_kernel<2>, g, TPB, 0, st)(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, M_host, M_dev);
+    else pdl(imp_tok_bwd4_kernel<1>, g, TPB, 0, st)(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, M_host, M_dev);
     PATHS_LAUNCH_CK();
     return 0;
   }
   if (g > 2 * kNumSMs) g = 2 * kNumSMs;
-  imp_tok_bwd_kernel<<<g, TPB, 0, st>>>(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, mode, M_host,
+  pdl(imp_tok_bwd_kernel, g, TPB, 0, st)(dtok, UV, alpha, w2, row_slide, dUV, dUVP, want_lo, db1, dw2, db2, dbin, I, d, imp_mul, mode, M_host,
                                         M_dev);
   PATHS_LAUNCH_CK();
   return 0;
@@ -1389,7 +1418,7 @@ int imp_tok_bwd(const float* dtok, const float* UV, const float* alpha, const fl
 int rnn_z_fwd(const float* X, const float* alpha, const float* hctx, float* Z, int D, int imp_mul, int M_host, const int* M_dev,
               cudaStream_t st) {
   if (M_host <= 0) return 0;
-  rnn_z_fwd_kernel<<<row_grid(M_host), TPB, 0, st>>>(X, alpha, hctx, Z, D, imp_mul, M_host, M_dev);
+  pdl(rnn_z_fwd_kernel, row_grid(M_host), TPB, 0, st)(X, alpha, hctx, Z, D, imp_mul, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1397,23 +1426,23 @@ int rnn_alpha_bwd(float* dZ, const float* dZc, const float* X, const float* UV, 
                   float* dw2, float* db2, int D, int I, int d, int imp_mul, int M_host, const int* M_dev, cudaStream_t st) {
   if (M_host <= 0) return 0;
   int g = row_grid(M_host); if (g > 2 * kNumSMs) g = 2 * kNumSMs;
-  rnn_alpha_bwd_kernel<<<g, TPB, 0, st>>>(dZ, dZc, X, UV, alpha, w2, dUV, db1, dw2, db2, D, I, d, imp_mul, M_host, M_dev);
+  pdl(rnn_alpha_bwd_kernel, g, TPB, 0, st)(dZ, dZc, X, UV, alpha, w2, dUV, db1, dw2, db2, D, I, d, imp_mul, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int head_concat_fwd(const FList& fl, const float* Wc, const float* bc, float* logits, int d, int nl, int B, cudaStream_t st) {
-  head_concat_fwd_kernel<<<row_grid(B), TPB, 0, st>>>(fl, Wc, bc, logits, d, nl, B);
+  pdl(head_concat_fwd_kernel, row_grid(B), TPB, 0, st)(fl, Wc, bc, logits, d, nl, B);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int head_concat_bwd(const float* dlogits, const float* Wc, const GList& gl, int d, int nl, int B, cudaStream_t st) {
-  head_concat_bwd_kernel<<<row_grid(B), TPB, 0, st>>>(dlogits, Wc, gl, d, nl, B);
+  pdl(head_concat_bwd_kernel, row_grid(B), TPB, 0, st)(dlogits, Wc, gl, d, nl, B);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int special_grad_grp(const float* dtok, const GIdx& seg, const MutL& dspecial, int d, int B, int ngroups, cudaStream_t st) {
   PATHS_REQUIRE(d <= 256, "special_grad: trans_dim above 256 is not supported (d=%d)", d);
-  special_grad_kernel<<<dim3((B + 7) / 8, ngroups), 256, 0, st>>>(dtok, seg, dspecial, d, B);
+  pdl(special_grad_kernel, dim3((B + 7) / 8, ngroups), 256, 0, st)(dtok, seg, dspecial, d, B);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1435,10 +1464,10 @@ int res_ln_fwd_grp(const float* res, const GIdx& ridx, const float* add, const P
   if (vec) {
     g = (cap + WPB * LNR - 1) / (WPB * LNR);
     if (g > 4 * kNumSMs) g = 4 * kNumSMs;
-    if (d <= 128) res_ln_fwd4_kernel<1><<<dim3(g, grp.n), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
-    else res_ln_fwd4_kernel<2><<<dim3(g, grp.n), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
+    if (d <= 128) pdl(res_ln_fwd4_kernel<1>, dim3(g, grp.n), TPB, 0, st)(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
+    else pdl(res_ln_fwd4_kernel<2>, dim3(g, grp.n), TPB, 0, st)(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
   } else {
-    res_ln_fwd_kernel<<<dim3(g, grp.n), TPB, 0, st>>>(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
+    pdl(res_ln_fwd_kernel, dim3(g, grp.n), TPB, 0, st)(res, ridx, add, bias, gamma, beta, y, xhat, rstd, d, eps, grp);
   }
   PATHS_LAUNCH_CK();
   return 0;
@@ -1460,10 +1489,10 @@ int ln_bwd_grp(const float* dy, const float* dy2, const float* xhat, const float
   bool vec = d % 4 == 0 && d <= 256 && al16;
   for (int i = 0; i < grp.n; ++i) vec = vec && (reinterpret_cast<uintptr_t>(gamma.p[i]) & 15) == 0;
   if (vec) {
-    if (d <= 128) ln_bwd4_kernel<1><<<dim3(g, grp.n), TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
-    else ln_bwd4_kernel<2><<<dim3(g, grp.n), TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
+    if (d <= 128) pdl(ln_bwd4_kernel<1>, dim3(g, grp.n), TPB, 0, st)(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
+    else pdl(ln_bwd4_kernel<2>, dim3(g, grp.n), TPB, 0, st)(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
   } else {
-    ln_bwd_kernel<<<dim3(g, grp.n), TPB, 0, st>>>(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
+    pdl(ln_bwd_kernel, dim3(g, grp.n), TPB, 0, st)(dy, dy2, xhat, rstd, gamma, dx, didx, accum, dgamma, dbeta, dbias, d, grp);
   }
   PATHS_LAUNCH_CK();
   return 0;
@@ -1484,7 +1513,7 @@ int relu_bwd_grp(float* dH, const float* H, int ld, const Grp& grp, const MutL& 
   const int lim = grp.n > 1 ? kNumSMs : 2 * kNumSMs;
   if (g > lim) g = lim;
   PATHS_REQUIRE(outp == nullptr || (outp->p && ld <= outp->ldp), "relu_bwd: output planes narrower than the rows");
-  relu_bwd_kernel<<<dim3(g, grp.n), 256, 0, st>>>(dH, H, ld, grp, dbias, outp ? *outp : no_planes(), want_lo, scale);
+  pdl(relu_bwd_kernel, dim3(g, grp.n), 256, 0, st)(dH, H, ld, grp, dbias, outp ? *outp : no_planes(), want_lo, scale);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1494,7 +1523,7 @@ int dropout_fwd_grp(const float* in, float* out, int cols, const PtrL& bias, con
   if (cap <= 0) return 0;
   size_t g = ((size_t)cap * (cols >> 2) + 255) / 256;
   if (g > (size_t)8 * kNumSMs) g = 8 * kNumSMs;
-  dropout_fwd_kernel<<<dim3((unsigned)g, grp.n), 256, 0, st>>>(in, out, cols, bias, grp, hrow, dr);
+  pdl(dropout_fwd_kernel, dim3((unsigned)g, grp.n), 256, 0, st)(in, out, cols, bias, grp, hrow, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1505,7 +1534,7 @@ int dropout_bwd_grp(const float* g, float* out, int cols, const MutL& dbias, con
   const int rpb = 256 / (cols >> 2) > 0 ? 256 / (cols >> 2) : 1;
   int nb = (cap + rpb - 1) / rpb;
   if (nb > 2 * kNumSMs) nb = 2 * kNumSMs;
-  dropout_bwd_kernel<<<dim3(nb, grp.n), 256, 0, st>>>(g, out, cols, dbias, grp, hrow, dr);
+  pdl(dropout_bwd_kernel, dim3(nb, grp.n), 256, 0, st)(g, out, cols, dbias, grp, hrow, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1515,14 +1544,14 @@ int relu_bwd(float* dH, const float* H, int ld, int M_host, const int* M_dev, in
 }
 int zero_rows(float* X, int ld, int M_host, const int* M_dev, int M_extra, cudaStream_t st) {
   if (M_host + M_extra <= 0) return 0;
-  zero_rows_kernel<<<4 * kNumSMs, 256, 0, st>>>(X, (size_t)ld, M_host, M_dev, M_extra);
+  pdl(zero_rows_kernel, 4 * kNumSMs, 256, 0, st)(X, (size_t)ld, M_host, M_dev, M_extra);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int scatter_add_rows_grp(const float* src, const GIdx& idx, float* dst, int d, const Grp& grp, cudaStream_t st) {
   const int cap = grp_max_rows(grp);
   if (cap <= 0) return 0;
-  scatter_add_rows_kernel<<<dim3(row_grid(cap), grp.n), TPB, 0, st>>>(src, idx, dst, d, grp);
+  pdl(scatter_add_rows_kernel, dim3(row_grid(cap), grp.n), TPB, 0, st)(src, idx, dst, d, grp);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1531,20 +1560,20 @@ int scatter_add_rows(const float* src, const int* idx, float* dst, int d, int B,
 }
 int head_fwd(const float* z, const float* Fprev, const float* Wc, const float* bc, float* F, float* logits, int d, int nl, int B, cudaStream_t st) {
   PATHS_REQUIRE(d <= 256 && nl <= 32, "head: d <= 256 and at most 32 logits supported");
-  head_fwd_kernel<<<row_grid(B), TPB, 0, st>>>(z, Fprev, Wc, bc, F, logits, d, nl, B);
+  pdl(head_fwd_kernel, row_grid(B), TPB, 0, st)(z, Fprev, Wc, bc, F, logits, d, nl, B);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int head_bwd(const float* dlogits, const float* dF_in, const float* Wc, float* dF, int d, int nl, int B, cudaStream_t st) {
-  head_bwd_kernel<<<row_grid(B), TPB, 0, st>>>(dlogits, dF_in, Wc, dF, d, nl, B);
+  pdl(head_bwd_kernel, row_grid(B), TPB, 0, st)(dlogits, dF_in, Wc, dF, d, nl, B);
   PATHS_LAUNCH_CK();
   return 0;
 }
 int loss_fwd_bwd(const float* logits, const int* ybin, const int* cens, float* hazards, float* loss_per, float* loss, float* risk, float* dlogits,
                  int nl, int B, int task, float scale, cudaStream_t st) {
-  loss_kernel<<<(B + 127) / 128, 128, 0, st>>>(logits, ybin, cens, hazards, loss_per, risk, dlogits, nl, B, task, 0.4f, 1e-7f, scale);
+  pdl(loss_kernel, (B + 127) / 128, 128, 0, st)(logits, ybin, cens, hazards, loss_per, risk, dlogits, nl, B, task, 0.4f, 1e-7f, scale);
   PATHS_LAUNCH_CK();
-  loss_reduce_kernel<<<1, 256, 0, st>>>(loss_per, loss, B, scale);
+  pdl(loss_reduce_kernel, 1, 256, 0, st)(loss_per, loss, B, scale);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1557,6 +1586,7 @@ namespace {
 __global__ void __launch_bounds__(256) pack_padded_kernel(const float* __restrict__ fts, int N, const int* __restrict__ seg,
                                                           const int* __restrict__ row_slide, float* __restrict__ X, int D,
                                                           int M_host, const int* M_dev) {
+  pdl_grid_sync();
   const int M = M_dev ? *M_dev : M_host;
   const int lane = threadIdx.x & 31;
   for (int m = blockIdx.x * 8 + (threadIdx.x >> 5); m < M; m += gridDim.x * 8) {
@@ -1571,7 +1601,7 @@ int pack_padded_rows(const float* fts, int N, const int* seg, const int* row_sli
                      cudaStream_t st) {
   if (M_host <= 0) return 0;
   int g = (M_host + 7) / 8; if (g > 8 * kNumSMs) g = 8 * kNumSMs;
-  pack_padded_kernel<<<g, 256, 0, st>>>(fts, N, seg, row_slide, X, D, M_host, M_dev);
+  pdl(pack_padded_kernel, g, 256, 0, st)(fts, N, seg, row_slide, X, D, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -1582,6 +1612,7 @@ namespace paths {
 namespace {
 __global__ void __launch_bounds__(256) occupancy_kernel(const float* __restrict__ grid, int cells, int D, unsigned int* __restrict__ bits,
                                                         int* __restrict__ count) {
+  pdl_grid_sync();
   const int lane = threadIdx.x & 31;
   int local = 0;
   for (int c = blockIdx.x * 8 + (threadIdx.x >> 5); c < cells; c += gridDim.x * 8) {
@@ -1601,7 +1632,7 @@ extern "C" int paths_build_occupancy(const float* grid, int cells, int D, uint32
   PATHS_REQUIRE(D % 4 == 0, "occupancy: D must be a multiple of 4");
   if (cells <= 0) return 0;
   int g = (cells + 7) / 8; if (g > 8 * kNumSMs) g = 8 * kNumSMs;
-  occupancy_kernel<<<g, 256, 0, static_cast<cudaStream_t>(stream)>>>(grid, cells, D, bits, count);
+  pdl(occupancy_kernel, g, 256, 0, static_cast<cudaStream_t>(stream))(grid, cells, D, bits, count);
   PATHS_LAUNCH_CK();
   return 0;
 }

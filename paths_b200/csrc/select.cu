@@ -33,6 +33,7 @@ __device__ __forceinline__ Cand candidate(const SelectArgs& a, int s, int sid, i
 }
 
 __global__ void __launch_bounds__(ST) select_topk_kernel(SelectArgs a) {
+  pdl_grid_sync();
   const int s = blockIdx.x, t = threadIdx.x;
   const int sid = a.slide_ids ? a.slide_ids[s] : s;
   // A bag above the level's per-slide bound (a fallback bag that fitted the batch-wide slack, slide.py:336-352) has already
@@ -102,6 +103,7 @@ __global__ void __launch_bounds__(ST) select_topk_kernel(SelectArgs a) {
 }
 
 __global__ void __launch_bounds__(1024) select_scan_kernel(SelectArgs a) {
+  pdl_grid_sync();
   __shared__ int part[1024];
   const int t = threadIdx.x;
   const int per = (a.B + 1023) / 1024;
@@ -132,6 +134,7 @@ __global__ void __launch_bounds__(1024) select_scan_kernel(SelectArgs a) {
 }
 
 __global__ void __launch_bounds__(ST) select_write_kernel(SelectArgs a) {
+  pdl_grid_sync();
   const int s = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
   const int sid = a.slide_ids ? a.slide_ids[s] : s;
   const int k = a.sel_count[s], fb = a.slide_fb[s];
@@ -177,6 +180,7 @@ __global__ void __launch_bounds__(ST) select_write_kernel(SelectArgs a) {
 __global__ void __launch_bounds__(1024) level0_scan_kernel(const int* __restrict__ gw, const int* __restrict__ gh, int L,
                                                            const int* __restrict__ slide_ids, int B, int cap, int* count, int* ntok,
                                                            int* seg, int* overflow) {
+  pdl_grid_sync();
   __shared__ int part[1024];
   const int t = threadIdx.x;
   const int per = (B + 1023) / 1024;
@@ -206,6 +210,7 @@ __global__ void __launch_bounds__(1024) level0_scan_kernel(const int* __restrict
 __global__ void __launch_bounds__(ST) level0_fill_kernel(const int* __restrict__ gh, int L, const int* __restrict__ slide_ids,
                                                          const int* __restrict__ seg, int cap, int* row_slide, int* row_xy,
                                                          int* row_parent, int* parent_local) {
+  pdl_grid_sync();
   const int s = blockIdx.x;
   const int H = gh[(size_t)(slide_ids ? slide_ids[s] : s) * L];
   const int base = seg[s], n = seg[s + 1] - base;
@@ -223,11 +228,11 @@ __global__ void __launch_bounds__(ST) level0_fill_kernel(const int* __restrict__
 
 int select_expand(const SelectArgs& a, cudaStream_t st) {
   if (a.B <= 0) return 0;
-  select_topk_kernel<<<a.B, ST, 0, st>>>(a);
+  pdl(select_topk_kernel, a.B, ST, 0, st)(a);
   PATHS_LAUNCH_CK();
-  select_scan_kernel<<<1, 1024, 0, st>>>(a);
+  pdl(select_scan_kernel, 1, 1024, 0, st)(a);
   PATHS_LAUNCH_CK();
-  select_write_kernel<<<a.B, ST, 0, st>>>(a);
+  pdl(select_write_kernel, a.B, ST, 0, st)(a);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -235,9 +240,9 @@ int select_expand(const SelectArgs& a, cudaStream_t st) {
 int level0_rows(const int* gw, const int* gh, int L, const int* slide_ids, int B, int cap, int* count, int* ntok, int* seg, int* row_slide,
                 int* row_xy, int* row_parent, int* parent_local, int* overflow, cudaStream_t st) {
   if (B <= 0) return 0;
-  level0_scan_kernel<<<1, 1024, 0, st>>>(gw, gh, L, slide_ids, B, cap, count, ntok, seg, overflow);
+  pdl(level0_scan_kernel, 1, 1024, 0, st)(gw, gh, L, slide_ids, B, cap, count, ntok, seg, overflow);
   PATHS_LAUNCH_CK();
-  level0_fill_kernel<<<B, ST, 0, st>>>(gh, L, slide_ids, seg, cap, row_slide, row_xy, row_parent, parent_local);
+  pdl(level0_fill_kernel, B, ST, 0, st)(gh, L, slide_ids, seg, cap, row_slide, row_xy, row_parent, parent_local);
   PATHS_LAUNCH_CK();
   return 0;
 }

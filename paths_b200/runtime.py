@@ -76,6 +76,8 @@ class ModelRuntime:
         self.track_hazard_grad = False
         self.overflow_reruns = 0                        # steps re-run with worst-case buffers (no-child fallback, slide.py:336-352)
         self.grad_sync = None                           # parallel.DataParallelStep.attach(): loss.backward() also all-reduces
+        # the step as a torch.library custom op (paths_b200::step) or, with PATHS_B200_NO_CUSTOM_OP=1, as a plain autograd.Function
+        self.use_custom_op = os.environ.get("PATHS_B200_NO_CUSTOM_OP", "0") != "1"
         # CUDA-graph replay of the step (GraphStep) for host batches that carry packed level-0 rows or read the resident store:
         # the small-batch regime, where ~270 launches per step outrun the host.  Off by default (a graph pins its engine's buffers).
         self.use_graphs = os.environ.get("PATHS_B200_GRAPHS", "0") == "1"
@@ -176,7 +178,10 @@ class ModelRuntime:
             gs = None
             if self.use_graphs and self.last_dropout[0] == 0.0 and fts is None and self.grad_sync is None:
                 gs = self._graph_for(eng, slide_ids, ybin, cens, scale, pk, torch.is_grad_enabled())
-            if torch.is_grad_enabled():
+            if self.use_custom_op:                      # torch.ops.paths_b200.step (ops.py): the custom-op layer over the C ABI
+                from . import ops
+                hz, loss = ops.step(self.anchor, ops.register_engine(self, eng, gs), slide_ids, fts, pk, ybin, cens, scale, gs is not None)
+            elif torch.is_grad_enabled():
                 hz, loss = _StepFn.apply(self.anchor, self, eng, slide_ids, fts, ybin, cens, scale, pk, gs)
             else:
                 hz, loss = _StepFn.forward(_NoCtx(), self.anchor, self, eng, slide_ids, fts, ybin, cens, scale, pk, gs)

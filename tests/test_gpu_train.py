@@ -181,6 +181,23 @@ def test_attached_dp_step_runs_inside_loss_backward():
             assert rel_err(p.grad, want[n]) < 1e-5, n
 
 
+def test_custom_op_layer_equals_the_autograd_function():
+    """torch.ops.paths_b200.step (paths_b200/ops.py) is the default route of inference_end2end; the plain autograd.Function
+    route (PATHS_B200_NO_CUSTOM_OP=1) must give the same hazards, loss and gradients."""
+    from paths_b200.utils import inference_end2end
+    res = []
+    for custom in (True, False):
+        cfg, model, batch = _setup("brca_b4")
+        rt = model.runtime(); rt.use_custom_op = custom
+        hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, batch, cfg.task)
+        assert loss.requires_grad
+        (2.0 * loss).backward()
+        res.append((hz.detach().clone(), loss.detach().clone(), rt.layout.gflat.clone()))
+    assert torch.ops.paths_b200.step is not None
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+    assert rel_err(res[0][2], res[1][2]) < 1e-5
+
+
 def test_graph_replay_equals_eager_steps():
     """rt.use_graphs: the step replayed as CUDA graphs (forward graph + backward graph, inputs in static buffers) gives the
     eager step's hazards, loss and gradients -- on the batch it was captured with and on a different batch of the same size;
