@@ -205,6 +205,31 @@ int paths_heatmap_composite(const int32_t* locs_yx, const float* importance, con
                             int patch_size, int H, int W, void* workspace, size_t workspace_bytes, double* out, float* alpha,
                             void* stream);
 
+/* ---- per-op entries: the single operations behind the reference's per-module methods ---- */
+/* LSTMCell.forward (model/interface.py:31-58) on M rows: x, h [M, D], c [M, C] -> h_out [M, D], c_out [M, C].  Wg / bg: the gate
+ * parameters stacked [forget_gate; remember_gate; remember_map; out_select_gate] ([3C + D, 2D] / [3C + D]); Wmo [D, C], bmo [D]
+ * (mem_to_out).  Allocates its temporaries and synchronises the stream (stand-alone use; the engine's level step is the fast path). */
+int paths_lstm_cell_fwd(int precision, const float* x, const float* h, const float* c, const float* Wg, const float* bg, const float* Wmo,
+                        const float* bmo, float* h_out, float* c_out, int M, int D, int C, void* stream);
+/* PreprocessedSlide.iter (data_utils/slide.py:277-360) for a batch of B slides: per-slide top-`keep` rows by importance (keep = -1:
+ * all, in order), their 4 children each in the reference's block order, bounds + occupancy filter, order-preserving compaction,
+ * no-child fallback (slide.py:336-352).  Level l in: alpha [rows], seg [B + 1], row_xy [rows, 2] patch coordinates, count [1].
+ * Out: sel [B, kcap] kept rows (importance-descending, -1 padded), sel_count [B], child_of [rows, 4]; level l + 1 tables n_count [1],
+ * n_ntok [1], n_seg [B + 1], n_row_slide / n_row_parent / n_parent_local [n_cap], n_row_xy [n_cap, 2]; overflow [2] = (flag, rows needed)
+ * is raised when n_cap or the per-slide bound n_maxseg is exceeded.  maxseg: per-slide bound of level l; scratch: 2 B ints. */
+int paths_select_expand(const float* alpha, const int32_t* seg, const int32_t* row_xy, const int32_t* count, int B, int cap, int keep, int kcap,
+                        int maxseg, const paths_store_t* h_store, int level, int L, const int32_t* slide_ids, int32_t* sel, int32_t* sel_count,
+                        int32_t* child_of, int32_t* n_count, int32_t* n_ntok, int32_t* n_seg, int32_t* n_row_slide, int32_t* n_row_xy,
+                        int32_t* n_row_parent, int32_t* n_parent_local, int n_cap, int n_maxseg, int32_t* overflow, int32_t* scratch,
+                        void* stream);
+/* The feature gather of slide.py:331: X[m, :] = grid(slide_ids[row_slide[m]], level)[row_xy[m]] for m < M (*M_dev when non-null). */
+int paths_gather_rows(const paths_store_t* h_store, int level, int L, const int32_t* slide_ids, const int32_t* row_slide, const int32_t* row_xy,
+                      float* X, int D, int M, const int32_t* M_dev, void* stream);
+/* TransformerAggregator.forward (model/aggregator.py:58-76) of one level: the caller has placed the projected, position-encoded
+ * tokens in the level's PATHS_BUF_TOK rows (patch row m of slide s at token row m + s + 1) and set COUNT / NTOK / SEG / TSEG; the
+ * special tokens are filled here, the decoder runs over the packed bags, the result lands in PATHS_BUF_Z ([B, d]). */
+int paths_engine_aggregate(paths_engine_t* e, int level, void* stream);
+
 /* Stand-alone varlen softmax self-attention over packed tokens -- the self-attention of nn.TransformerDecoderLayer as
  * model/aggregator.py:70-72 runs it, the key-padding mask replaced by per-slide segments.  qkv: [tokens, 3 d] (q | k | v, `heads`
  * heads of width d / heads, query scale 1/sqrt(head_dim) applied inside); slide s owns token rows [seg[s] + s, seg[s+1] + s + 1)

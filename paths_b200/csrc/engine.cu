@@ -1570,6 +1570,88 @@ int paths_attention_bwd(int precision, const float* qkv, const int32_t* seg, int
                       dropout_p > 0.f ? &dr : nullptr, precision == PREC_BF16X3_TC ? 3 : precision == PREC_BF16_TC ? 1 : 0);
 }
 
+
+// ---- per-op entries: the single operations behind the reference's per-module methods -------------------------
+namespace paths { namespace {
+__global__ void iota_kernel(int* __restrict__ p, int n) {
+  pdl_grid_sync();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = i;
+}
+} }
+
+// LSTMCell.forward (model/interface.py:31-58) on M rows: x, h [M, D], c [M, C] -> h_out [M, D], c_out [M, C].  Wg = the four gate
+// weights stacked [forget; remember; remember_map; out_select] ([3C + D, 2D]), bg likewise; Wmo [D, C].  Temporaries are allocated
+// inside (a stand-alone entry: the engine's own path keeps everything in its workspace).
+int paths_lstm_cell_fwd(int precision, const float* x, const float* h, const float* c, const float* Wg, const float* bg, const float* Wmo,
+                        const float* bmo, float* h_out, float* c_out, int M, int D, int C, void* stream) {
+  PATHS_REQUIRE(x && h && c && Wg && bg && Wmo && bmo && h_out && c_out && M >= 1 && D % 4 == 0 && C % 4 == 0, "lstm_cell_fwd: bad argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int ldg = 3 * C + D;
+  float *xh = nullptr, *G = nullptr, *Pt = nullptr; int* ident = nullptr;
+  PATHS_CK(cudaMalloc(&xh, (size_t)M * 2 * D * sizeof(float)));
+  PATHS_CK(cudaMalloc(&G, (size_t)M * ldg * sizeof(float)));
+  PATHS_CK(cudaMalloc(&Pt, (size_t)M * D * sizeof(float)));
+  PATHS_CK(cudaMalloc(&ident, (size_t)M * sizeof(int)));
+  PATHS_CK(cudaMemcpy2DAsync(xh, 2 * D * sizeof(float), x, D * sizeof(float), D * sizeof(float), M, cudaMemcpyDeviceToDevice, st));
+  PATHS_CK(cudaMemcpy2DAsync(xh + D, 2 * D * sizeof(float), h, D * sizeof(float), D * sizeof(float), M, cudaMemcpyDeviceToDevice, st));
+  pdl(iota_kernel, (M + 255) / 256, 256, 0, st)(ident, M);
+  PATHS_LAUNCH_CK();
+  int rc = paths_gemm_nt(precision, xh, 2 * D, Wg, 2 * D, 0, G, ldg, bg, M, ldg, 2 * D, 0, stream);          // [f | r | m | o] pre-activations
+  if (!rc) rc = lstm_point1_fwd(G, c, ident, c_out, no_planes(), 0, 0, D, C, M, nullptr, st);                // activations in place, c'
+  if (!rc) rc = paths_gemm_nt(precision, c_out, C, Wmo, C, 0, Pt, D, bmo, M, D, C, 0, stream);
+  if (!rc) rc = lstm_point2_fwd(Pt, G, x, h_out, nullptr, no_planes(), 0, D, C, M, nullptr, st);             // h' = o * tanh(P)
+  cudaStreamSynchronize(st);
+  cudaFree(xh); cudaFree(G); cudaFree(Pt); cudaFree(ident);
+  return rc;
+}
+
+// PreprocessedSlide.iter (data_utils/slide.py:277-360) for a batch: per-slide top-K by importance, 4-child expansion, bounds +
+// occupancy filter, order-preserving compaction, no-child fallback.  Integer in, integer out; every array is caller-owned.
+//   level l:   alpha [rows], seg [B + 1], row_xy [rows, 2] (patch coordinates), count [1] = seg[B]
+//   outputs:   sel [B, kcap] kept rows (importance-descending, -1 padded), sel_count [B], child_of [rows, 4];
+//              level l + 1 tables n_count [1], n_ntok [1], n_seg [B + 1], n_row_slide / n_row_parent / n_parent_local [n_cap],
+//              n_row_xy [n_cap, 2]; overflow [2] (flag, rows needed) is raised when n_cap or n_maxseg is exceeded
+//   scratch:   2 * B ints
+int paths_select_expand(const float* alpha, const int32_t* seg, const int32_t* row_xy, const int32_t* count, int B, int cap, int keep, int kcap,
+                        int maxseg, const paths_store_t* h_store, int level, int L, const int32_t* slide_ids, int32_t* sel, int32_t* sel_count,
+                        int32_t* child_of, int32_t* n_count, int32_t* n_ntok, int32_t* n_seg, int32_t* n_row_slide, int32_t* n_row_xy,
+                        int32_t* n_row_parent, int32_t* n_parent_local, int n_cap, int n_maxseg, int32_t* overflow, int32_t* scratch,
+                        void* stream) {
+  PATHS_REQUIRE(alpha && seg && row_xy && count && h_store && sel && sel_count && child_of && n_count && n_ntok && n_seg && n_row_slide &&
+                n_row_xy && n_row_parent && n_parent_local && overflow && scratch && B >= 1 && level >= 0 && level < L - 1,
+                "select_expand: bad argument");
+  PATHS_REQUIRE(keep < 0 || maxseg <= 65536, "select_expand: bags above 65536 rows need keep = -1");
+  SelectArgs a;
+  a.alpha = alpha; a.seg = seg; a.row_xy = row_xy; a.count = count; a.B = B; a.cap = cap; a.keep = keep; a.kcap = kcap; a.maxseg = maxseg;
+  a.n_maxseg = n_maxseg;
+  a.gw = h_store->gw; a.gh = h_store->gh; a.occ_off = reinterpret_cast<const unsigned long long*>(h_store->occ_off); a.occ = h_store->occ;
+  a.nonbg = h_store->nonbg; a.level = level; a.L = L; a.slide_ids = slide_ids;
+  a.sel = sel; a.sel_count = sel_count; a.child_of = child_of;
+  a.n_count = n_count; a.n_seg = n_seg; a.n_row_slide = n_row_slide; a.n_row_xy = n_row_xy; a.n_row_parent = n_row_parent;
+  a.n_parent_local = n_parent_local; a.n_cap = n_cap; a.n_ntok = n_ntok; a.overflow = overflow; a.slide_cnt = scratch; a.slide_fb = scratch + B;
+  return select_expand(a, static_cast<cudaStream_t>(stream));
+}
+
+// X[m, :] = grid(slide_ids[row_slide[m]], level)[row_xy[m]] for m < M: the feature gather of slide.py:331 from the resident store.
+int paths_gather_rows(const paths_store_t* h_store, int level, int L, const int32_t* slide_ids, const int32_t* row_slide, const int32_t* row_xy,
+                      float* X, int D, int M, const int32_t* M_dev, void* stream) {
+  PATHS_REQUIRE(h_store && row_slide && row_xy && X && level >= 0 && level < L, "gather_rows: bad argument");
+  return gather_rows(h_store->grid_ptr, h_store->gh, level, L, slide_ids, row_slide, row_xy, X, D, M, M_dev, static_cast<cudaStream_t>(stream));
+}
+
+// TransformerAggregator.forward (model/aggregator.py:58-76) of one level on tokens the caller has placed in the level's
+// PATHS_BUF_TOK rows (token of patch row m of slide s at row m + s + 1; the special tokens are filled here): decoder layers over
+// the packed bags, result in PATHS_BUF_Z ([B, d]).  Row tables (COUNT, NTOK, SEG, TSEG) must describe the bags.
+int paths_engine_aggregate(paths_engine_t* e, int level, void* stream) {
+  PATHS_REQUIRE(e && e->have_params && level >= 0 && level < e->dm.L, "aggregate: bad argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (int r = ensure_registry(e, st)) return r;
+  Level& v = e->lv[level];
+  RUN(special_fill(e->P.level[level].special, v.seg, v.tok, e->dm.d, e->B, st));
+  return decoder_forward(e, make_set(e, &level, 1), st);
+}
+
 int paths_gemm_tn(int precision, const float* P, int ldp, const float* Q, int ldq, float* C, int ldc, int M, int NI, int NJ, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   void *sa = nullptr, *sb = nullptr, *sw = nullptr;

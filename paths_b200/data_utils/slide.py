@@ -61,10 +61,61 @@ class PreprocessedSlide:
         assert wsi is None
         return
 
-    def iter(self, *args, **kwargs):
-        raise NotImplementedError(
-            "paths_b200 performs the level-to-level recursion for the whole batch on the device (paths_engine_select); "
-            "use utils.inference_end2end rather than PreprocessedSlide.iter")
+    def iter(self, magnification_index: int, npatches: int, locs, ctx_slide, ctx_patch, importance, new_ctx_slide,
+             new_ctx_patch, keep_patches: int = -1, imp_cpu=None):
+        """Data of magnification level `index` -> `index + 1` for THIS slide (reference slide.py:277-360): top-K by importance,
+        4-child expansion, bounds + background filter, feature gather, no-child fallback -- one call of the stand-alone device
+        entries `paths_select_expand` + `paths_gather_rows` with B = 1 (utils.inference_end2end does the same for the whole batch
+        without leaving the device).  Returns the reference's dict; like the reference it floor-divides `locs` in place."""
+        import ctypes as C
+        from .. import _lib as L
+        lib = L.lib()
+        dev = self.store.device
+        i = magnification_index
+        n = int(npatches)
+        locs //= self.patch_size                                            # (in place on the caller's tensor, slide.py:280)
+        imp = (imp_cpu if imp_cpu is not None else importance)[:n].detach().to(dev, torch.float32).contiguous()
+        ctx_patch = ctx_patch[:n]; new_ctx_patch = new_ctx_patch[:n]
+        ctx_slide = torch.cat((ctx_slide, new_ctx_slide[None]), dim=0)
+        hist = torch.cat((ctx_patch, new_ctx_patch[:, None]), dim=1)        # N x (K+1) x D
+        gw, gh = self.grid_shapes[i + 1]
+        cells = gw * gh
+        k = n if keep_patches == -1 else min(n, int(keep_patches))
+        kcap = max(k, 1)
+        i32 = dict(dtype=torch.int32, device=dev)
+        seg = torch.tensor([0, n], **i32); count = torch.tensor([n], **i32)
+        row_xy = locs[:n].to(dev, torch.int32).contiguous()
+        sel = torch.empty(kcap, **i32); sel_count = torch.empty(1, **i32); child_of = torch.empty(max(n, 1) * 4, **i32)
+        n_count = torch.zeros(1, **i32); n_ntok = torch.zeros(1, **i32); n_seg = torch.zeros(2, **i32)
+        n_row_slide = torch.empty(cells, **i32); n_row_xy = torch.empty(cells, 2, **i32)
+        n_row_parent = torch.empty(cells, **i32); n_parent_local = torch.empty(cells, **i32)
+        overflow = torch.zeros(2, **i32); scratch = torch.zeros(2, **i32)
+        sid = torch.tensor([self.store_index], **i32)
+        _, st = self.store.tables()
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        L.check(lib.paths_select_expand(imp.data_ptr(), seg.data_ptr(), row_xy.data_ptr(), count.data_ptr(), 1, max(n, 1), int(keep_patches), kcap,
+                                        max(n, 1), C.byref(st), i, self.store.L, sid.data_ptr(), sel.data_ptr(), sel_count.data_ptr(),
+                                        child_of.data_ptr(), n_count.data_ptr(), n_ntok.data_ptr(), n_seg.data_ptr(), n_row_slide.data_ptr(),
+                                        n_row_xy.data_ptr(), n_row_parent.data_ptr(), n_parent_local.data_ptr(), cells, cells,
+                                        overflow.data_ptr(), scratch.data_ptr(), stream), "select_expand")
+        m = int(n_count.item())
+        assert int(overflow[0].item()) == 0
+        new_fts = torch.empty(m, self.store.D, device=dev)
+        L.check(lib.paths_gather_rows(C.byref(st), i + 1, self.store.L, sid.data_ptr(), n_row_slide.data_ptr(), n_row_xy.data_ptr(),
+                                      new_fts.data_ptr(), self.store.D, m, None, stream), "gather_rows")
+        parent_row = n_row_parent[:m].long()
+        out_dev = hist.device
+        if m and int(parent_row[0].item()) < 0:                             # fallback (slide.py:336-352): zero state, cell indices
+            new_ctx = torch.zeros((m, hist.size(1), hist.size(2)), device=out_dev)
+        else:
+            new_ctx = hist[parent_row.to(out_dev)]                          # a child inherits its parent's whole history (slide.py:318)
+        return {
+            "fts": new_fts,
+            "ctx_patch": new_ctx,
+            "ctx_slide": ctx_slide,
+            "locs": n_row_xy[:m].to(locs.device, locs.dtype) * self.patch_size,
+            "parent_inds": n_parent_local[:m].to(locs.device, locs.dtype),
+        }
 
     def recurse(self, *args, **kwargs):
         raise NotImplementedError

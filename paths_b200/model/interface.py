@@ -21,7 +21,33 @@ class LSTMCell(nn.Module):
         self.mem_to_out = nn.Sequential(nn.Linear(self.cdim, self.hdim), nn.Tanh())
 
     def forward(self, xs, hs, cs):
-        raise NotImplementedError("paths_b200 runs the LSTM cell inside the fused level engine (RecursiveModel.forward)")
+        """One LSTM step (reference model/interface.py:31-58): xs, hs [..., D], cs [..., C] -> (hs', cs').  Runs the stand-alone
+        per-op entry `paths_lstm_cell_fwd` (the gate contraction and the cell's row kernels of the level engine); values only --
+        gradients flow through the whole-step op of utils.inference_end2end, not through this convenience method."""
+        import ctypes as C
+        from .. import _lib as L
+        from ..runtime import default_precision
+        assert xs.shape[-1] == self.xdim and hs.shape[-1] == self.hdim and cs.shape[-1] == self.cdim      # interface.py:44-47
+        assert xs.shape[:-1] == hs.shape[:-1] == cs.shape[:-1]
+        if not xs.is_cuda:
+            raise RuntimeError("paths_b200: LSTMCell.forward needs CUDA tensors; there is no CPU path")
+        lead = xs.shape[:-1]
+        x = xs.detach().reshape(-1, self.xdim).float().contiguous()
+        h = hs.detach().reshape(-1, self.hdim).float().contiguous()
+        c = cs.detach().reshape(-1, self.cdim).float().contiguous()
+        gates = (self.forget_gate, self.remember_gate, self.remember_map, self.out_select_gate)
+        with torch.no_grad():
+            Wg = torch.cat([g[0].weight for g in gates], 0).float().contiguous()
+            bg = torch.cat([g[0].bias for g in gates], 0).float().contiguous()
+            Wmo = self.mem_to_out[0].weight.detach().float().contiguous()
+            bmo = self.mem_to_out[0].bias.detach().float().contiguous()
+        M = x.shape[0]
+        ho = torch.empty(M, self.hdim, device=x.device); co = torch.empty(M, self.cdim, device=x.device)
+        if M:
+            L.check(L.lib().paths_lstm_cell_fwd(default_precision(), x.data_ptr(), h.data_ptr(), c.data_ptr(), Wg.data_ptr(), bg.data_ptr(),
+                                                Wmo.data_ptr(), bmo.data_ptr(), ho.data_ptr(), co.data_ptr(), M, self.xdim, self.cdim,
+                                                torch.cuda.current_stream().cuda_stream), "lstm_cell_fwd")
+        return ho.view(*lead, self.hdim), co.view(*lead, self.cdim)
 
 
 class Processor(ABC):

@@ -38,6 +38,8 @@ class PATHSProcessor(nn.Module, Processor):
         self.global_agg = TransformerAggregator(input_dim=self.dim, model_dim=config.trans_dim, output_dim=self.dim,
                                                 nhead=config.trans_heads, layers=config.trans_layers, dropout=config.dropout)
         self._owner = None
+        import weakref
+        self.global_agg._proc = weakref.ref(self)
 
     def process(self, data, lstm=None) -> Dict:
         if self.config.lstm:

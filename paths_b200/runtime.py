@@ -216,6 +216,10 @@ class ModelRuntime:
                 self.layout.gflat.zero_()
         return gs
 
+    @torch.no_grad()
+    def aggregate(self, depth: int, tokens: torch.Tensor, lengths: Optional[torch.Tensor]) -> torch.Tensor:
+        return _aggregate(self, depth, tokens, lengths)
+
     def graph_step(self, eng, slide_ids, ybin, cens, scale, backward=True, fts_packed=None) -> "GraphStep":
         """Capture one step of `eng` (forward, optionally backward) as CUDA graphs; see GraphStep."""
         return GraphStep(self, eng, slide_ids, ybin, cens, scale, backward, fts_packed)
@@ -289,6 +293,32 @@ class ModelRuntime:
         return {"logits": eng.buffer(depth, "LOGITS").view(B, dm.nl).clone(),
                 "ctx_slide": eng.buffer(depth, "F").view(B, d).clone(),
                 "ctx_patch": ctx_patch, "importance": out_imp}
+
+
+def _aggregate(self, depth: int, tokens: torch.Tensor, lengths: Optional[torch.Tensor]) -> torch.Tensor:
+    """TransformerAggregator.forward of level `depth` on padded tokens [B, N, d] (model/aggregator.py:58-76)."""
+    dm = self.dims
+    B, N, d = tokens.shape
+    assert d == dm.d
+    dev = self.device
+    num = (lengths if lengths is not None else torch.full((B,), N)).to(dev).long()
+    valid = torch.arange(N, device=dev)[None, :] < num[:, None]
+    M = int(num.sum().item())
+    caps = [1] * dm.L; maxseg = [1] * dm.L
+    caps[depth] = max(M, 1); maxseg[depth] = max(N, 1)
+    eng = self.engine_for(B, caps, maxseg, [int(dm.K[i]) for i in range(dm.L - 1)], tag=f"agg{depth}")
+    seg = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+    seg[1:] = torch.cumsum(num, 0).to(torch.int32)
+    ar = torch.arange(B, dtype=torch.int32, device=dev)
+    eng.buffer(depth, "COUNT").fill_(M); eng.buffer(depth, "NTOK").fill_(M + B)
+    eng.buffer(depth, "SEG").copy_(seg); eng.buffer(depth, "TSEG").copy_(seg[:B] + ar)
+    slide_of = ar[:, None].expand(B, N)[valid].long()
+    rows = torch.arange(M, device=dev) + slide_of + 1                    # token row of patch row m of slide s: m + s + 1
+    eng.buffer(depth, "TOK").view(-1, d)[rows] = tokens.detach().to(dev, torch.float32)[valid]
+    eng.refresh_weights()
+    self._arm_dropout(eng)
+    L.check(eng.lib.paths_engine_aggregate(eng.handle, depth, torch.cuda.current_stream().cuda_stream), "engine_aggregate")
+    return eng.buffer(depth, "Z").view(-1, d)[:B].clone()
 
 
 class GraphStep:
