@@ -2,7 +2,7 @@
 # staged GPU job: (1) everything with the SIMT attention and plain launches, (2) the tcgen05 attention on its own,
 # (3) the full suite with tcgen05 attention, (4) the full suite with programmatic dependent launch on top, (5) parity table + bench lines
 O=gpurun_out/r2c; mkdir -p $O
-PATHS_B200_PDL=0 PATHS_B200_ATTN_SIMT=1 timeout 900 python -m pytest tests -m gpu -x -q --deselect tests/test_gpu_attention.py > $O/pytest_simt.txt 2>&1; echo "pytest(simt attn, no pdl) rc=$?"; tail -4 $O/pytest_simt.txt
+PATHS_B200_PDL=0 PATHS_B200_ATTN_SIMT=1 timeout 900 python -m pytest tests -m gpu -q --deselect tests/test_gpu_attention.py > $O/pytest_simt.txt 2>&1; echo "pytest(simt attn, no pdl) rc=$?"; tail -4 $O/pytest_simt.txt
 PATHS_B200_PDL=0 timeout 300 python -m pytest tests/test_gpu_attention.py -q > $O/pytest_attn.txt 2>&1; echo "pytest(attn) rc=$?"; tail -25 $O/pytest_attn.txt
 PATHS_B200_PDL=0 timeout 900 python -m pytest tests -m gpu -q > $O/pytest_tc.txt 2>&1; echo "pytest(tc attn, no pdl) rc=$?"; tail -12 $O/pytest_tc.txt
 timeout 900 python -m pytest tests -m gpu -q > $O/pytest_pdl.txt 2>&1; echo "pytest(tc attn, pdl) rc=$?"; tail -12 $O/pytest_pdl.txt
