@@ -989,9 +989,7 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
   static const bool no_tc = getenv("PATHS_B200_ATTN_SIMT") != nullptr;  // keep the SIMT short-bag kernels in the tensor-core modes
   static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;   // experimental pair-per-row kernels (not faster: off)
   if (tc_passes && !no_tc && !nq_mode && attn_tc_supported(d, heads)) {  // bags of at most 128 tokens on the tensor cores (attention_tc.cu)
-    if (int r = attn_tc_fwd(tc_passes, qkv, seg, out, lse, d, heads, max_T, st, dr)) return r;
-    if (max_T <= SMALL_MAX_T) return 0;
-    skip_T = SMALL_MAX_T;
+    return attn_tc_fwd(tc_passes, qkv, seg, out, lse, d, heads, max_T, st, dr);      // every bag length (short classes + tiled)
   } else if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
@@ -1044,9 +1042,7 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
   static const bool no_tc = getenv("PATHS_B200_ATTN_SIMT") != nullptr;
   static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;
   if (tc_passes && !no_tc && !nq_mode && attn_tc_supported(d, heads)) {
-    if (int r = attn_tc_bwd(tc_passes, qkv, seg, out, lse, dout, dqkv, d, heads, max_T, st, dr)) return r;
-    if (max_T <= SMALL_MAX_T) return 0;
-    skip_T = SMALL_MAX_T;
+    return attn_tc_bwd(tc_passes, qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, max_T, st, dr);
   } else if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;

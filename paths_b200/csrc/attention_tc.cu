@@ -22,7 +22,7 @@
 //                                                Q (dK), dO (dV) as the N = 32 operand of a product that contracts over tokens.
 //   score tile    [query rows][keys]             one block per 64 keys and plane: P, dS.  K-major operand of O / dQ; read as an
 //                                                M-major operand (M = keys, K = queries) by dK / dV.
-// Two size classes share the code: NKB = 1 (bags up to 64 tokens, 64 threads, 64 TMEM columns forward / 128 backward, several CTAs
+// Bags above 128 tokens are tiled (the *_long kernels further down).  Two size classes of short bags share the code: NKB = 1 (bags up to 64 tokens, 64 threads, 64 TMEM columns forward / 128 backward, several CTAs
 // per SM) and NKB = 2 (65..128 tokens, 128 threads).  A launch covers every (head, slide); CTAs of the other class exit at once.
 #include "common.cuh"
 #include "rowops.cuh"
@@ -422,6 +422,459 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
 }
 
+// =====================================================================================================================
+// Long bags (more than 128 tokens: the 20 k-token bag of cfg 4, the 257-token bags K = 64 produces): the same products, tiled.
+// A CTA owns 128 queries (forward, dQ) or 128 keys (dK / dV) and walks the other dimension in blocks of 64; accumulators that need
+// no rescaling (dQ, dK, dV: the log-sum-exp is known) stay in TMEM across blocks, the forward pass keeps its running output row
+// in registers (one query per thread) and rescales it there (online softmax).
+constexpr int LB = 64;                                      // block of the walked dimension
+
+template <int NP>
+struct LongFwdCfg {
+  static constexpr int OFF_Q = 0, OFF_K = 16384, OFF_VT = OFF_K + LB * 128, OFF_P = OFF_VT + NP * 4096;
+  static constexpr int P_PLANE = 128 * 128;
+  static constexpr int SMEM = OFF_P + NP * P_PLANE + 1024;
+  static constexpr int TMEM_COLS = 128;                      // S [0, 64), P V [64, 96)
+};
+
+template <int NP, bool DROP>
+__global__ void __launch_bounds__(128) attn_tc_fwd_long_kernel(const float* __restrict__ qkv, const SegGrp seg, float* __restrict__ out,
+                                                               float* __restrict__ lse, int d, int heads, const Drop dr) {
+  pdl_grid_sync();
+  using cfg = LongFwdCfg<NP>;
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.z);
+  const int T = sg.T, q0 = blockIdx.y * 128;
+  if (T <= 128 || q0 >= T) return;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int t = threadIdx.x, warp = t >> 5;
+  if (t == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc(&tmem_slot, cfg::TMEM_COLS);
+  const float scale = rsqrtf((float)DH);
+  const int ld = 3 * d;
+  const bool live = q0 + t < T;
+  {
+    float x[DH];
+    if (live) {
+      load_row32(qkv + (size_t)(sg.t0 + q0 + t) * ld + h * DH, x);
+#pragma unroll
+      for (int c = 0; c < DH; ++c) x[c] *= scale;
+      store_natural(smem + cfg::OFF_Q, t, x);
+    } else {
+      zero_natural(smem + cfg::OFF_Q, t);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint32_t sQ = smem_u32(smem + cfg::OFF_Q), sK = smem_u32(smem + cfg::OFF_K), sVt = smem_u32(smem + cfg::OFF_VT),
+                 sP = smem_u32(smem + cfg::OFF_P);
+  const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
+  const uint32_t hrow = (uint32_t)(sg.t0 - sg.r0 + q0 + t), hcol = (uint32_t)h << 24;
+  float o[DH];
+#pragma unroll
+  for (int c = 0; c < DH; ++c) o[c] = 0.f;
+  float mx = -INFINITY, sum = 0.f;
+  uint32_t phase = 0;
+#pragma unroll 1
+  for (int k0 = 0; k0 < T; k0 += LB) {
+    if (t < LB) {                                            // stage the block's keys: K natural, V transposed
+      float x[DH];
+      if (k0 + t < T) {
+        const float* rp = qkv + (size_t)(sg.t0 + k0 + t) * ld + h * DH;
+        load_row32(rp + d, x);
+        store_natural(smem + cfg::OFF_K, t, x);
+        load_row32(rp + 2 * d, x);
+      } else {
+        zero_natural(smem + cfg::OFF_K, t);
+#pragma unroll
+        for (int c = 0; c < DH; ++c) x[c] = 0.f;
+      }
+      store_transposed<NP>(smem + cfg::OFF_VT, 4096, t, x);
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (t == 0) {                                            // S = (scale Q) K_blk^T : N = 64
+      constexpr uint32_t idesc = umma_idesc(128, LB, 0, 0);
+      uint32_t acc = 0;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+        mma_terms<NP>(tmem_base, desc_k(sQ, ks * 32), desc_k(sQ, 64 + ks * 32), desc_k(sK, ks * 32), desc_k(sK, 64 + ks * 32), idesc, &acc);
+      umma_commit(&bar);
+    }
+    mbar_wait(&bar, phase); phase ^= 1;
+    tc_fence_after();
+    float bmx = mx;
+#pragma unroll 1
+    for (int c0 = 0; c0 < LB; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld32(lane_addr + c0, r);
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (k0 + c0 + i < T) bmx = fmaxf(bmx, __uint_as_float(r[i]));
+    }
+    const float corr = expf(mx - bmx);                       // exp(-inf) = 0 on the first block
+    mx = bmx;
+    sum *= corr;
+#pragma unroll 1
+    for (int c0 = 0; c0 < LB; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld32(lane_addr + c0, r);
+      float p[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float e = (k0 + c0 + i < T) ? expf(__uint_as_float(r[i]) - mx) : 0.f;
+        sum += e;
+        p[i] = e;
+        if (DROP) p[i] = drop_keep(dkey, hrow, hcol | (uint32_t)(k0 + c0 + i), dr.thresh) ? e * dr.inv_keep : 0.f;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) store_score8<NP, 128>(smem + cfg::OFF_P, cfg::P_PLANE, t, 0, (c0 >> 3) + q, p + 8 * q);
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (t == 0) {                                            // block's P V -> columns [64, 96), fresh
+      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0);
+      uint32_t acc = 0;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks)
+        mma_terms<NP>(tmem_base + 64, desc_k(sP, ks * 32), desc_k(sP + cfg::P_PLANE, ks * 32), desc_k(sVt, ks * 32), desc_k(sVt + 4096, ks * 32),
+                      idesc, &acc);
+      umma_commit(&bar);
+    }
+    mbar_wait(&bar, phase); phase ^= 1;
+    tc_fence_after();
+    {
+      uint32_t r[32];
+      tmem_ld32(lane_addr + 64, r);
+#pragma unroll
+      for (int c = 0; c < DH; ++c) o[c] = fmaf(o[c], corr, __uint_as_float(r[c]));
+    }
+    tc_fence_before();                                       // the next block's MMAs overwrite S / P V and the staged tiles
+    __syncthreads();
+    tc_fence_after();
+  }
+  if (live) {
+    const float inv = 1.f / sum;
+    float* op = out + (size_t)(sg.t0 + q0 + t) * d + h * DH;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) reinterpret_cast<float4*>(op)[c] = make_float4(o[4 * c] * inv, o[4 * c + 1] * inv, o[4 * c + 2] * inv, o[4 * c + 3] * inv);
+    lse[(size_t)(sg.t0 + q0 + t) * heads + h] = mx + logf(sum);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
+}
+
+template <int NP>
+struct LongDqCfg {
+  static constexpr int OFF_Q = 0, OFF_DO = 16384, OFF_K = 32768, OFF_V = OFF_K + LB * 128, OFF_KT = OFF_V + LB * 128, OFF_DS = OFF_KT + NP * 4096;
+  static constexpr int S_PLANE = 128 * 128;
+  static constexpr int SMEM = OFF_DS + NP * S_PLANE + 1024;
+  static constexpr int TMEM_COLS = 256;                      // S [0, 64), dP [64, 128), dQ [128, 160)
+};
+
+// dQ of 128 queries: walks the keys in blocks of 64, dQ accumulates in TMEM.  Also writes D = dO . O of its queries (dvec) for the
+// dK / dV kernel.
+template <int NP, bool DROP>
+__global__ void __launch_bounds__(128) attn_tc_bwd_dq_long_kernel(const float* __restrict__ qkv, const SegGrp seg, const float* __restrict__ out,
+                                                                  const float* __restrict__ lse, const float* __restrict__ dout,
+                                                                  float* __restrict__ dqkv, float* __restrict__ dvec, int d, int heads,
+                                                                  const Drop dr) {
+  pdl_grid_sync();
+  using cfg = LongDqCfg<NP>;
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.z);
+  const int T = sg.T, q0 = blockIdx.y * 128;
+  if (T <= 128 || q0 >= T) return;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int t = threadIdx.x, warp = t >> 5;
+  if (t == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc(&tmem_slot, cfg::TMEM_COLS);
+  const float scale = rsqrtf((float)DH);
+  const int ld = 3 * d;
+  const bool live = q0 + t < T;
+  float Dq = 0.f, L = 0.f;
+  {
+    float x[DH], y[DH];
+    if (live) {
+      load_row32(qkv + (size_t)(sg.t0 + q0 + t) * ld + h * DH, x);
+#pragma unroll
+      for (int c = 0; c < DH; ++c) x[c] *= scale;
+      store_natural(smem + cfg::OFF_Q, t, x);
+      const size_t orow = (size_t)(sg.t0 + q0 + t) * d + h * DH;
+      load_row32(dout + orow, x);
+      load_row32(out + orow, y);
+#pragma unroll
+      for (int c = 0; c < DH; ++c) Dq = fmaf(x[c], y[c], Dq);
+      store_natural(smem + cfg::OFF_DO, t, x);
+      L = lse[(size_t)(sg.t0 + q0 + t) * heads + h];
+      dvec[(size_t)(sg.t0 + q0 + t) * heads + h] = Dq;
+    } else {
+      zero_natural(smem + cfg::OFF_Q, t);
+      zero_natural(smem + cfg::OFF_DO, t);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint32_t s0 = smem_u32(smem);
+  const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
+  const uint32_t hrow = (uint32_t)(sg.t0 - sg.r0 + q0 + t), hcol = (uint32_t)h << 24;
+  uint32_t phase = 0, acc_dq = 0;
+#pragma unroll 1
+  for (int k0 = 0; k0 < T; k0 += LB) {
+    if (t < LB) {
+      float x[DH];
+      if (k0 + t < T) {
+        const float* rp = qkv + (size_t)(sg.t0 + k0 + t) * ld + h * DH;
+        load_row32(rp + d, x);
+        store_natural(smem + cfg::OFF_K, t, x);
+        store_transposed<NP>(smem + cfg::OFF_KT, 4096, t, x);
+        load_row32(rp + 2 * d, x);
+        store_natural(smem + cfg::OFF_V, t, x);
+      } else {
+#pragma unroll
+        for (int c = 0; c < DH; ++c) x[c] = 0.f;
+        zero_natural(smem + cfg::OFF_K, t);
+        zero_natural(smem + cfg::OFF_V, t);
+        store_transposed<NP>(smem + cfg::OFF_KT, 4096, t, x);
+      }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (t == 0) {
+      constexpr uint32_t idesc = umma_idesc(128, LB, 0, 0);
+      uint32_t acc = 0;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+        mma_terms<NP>(tmem_base, desc_k(s0 + cfg::OFF_Q, ks * 32), desc_k(s0 + cfg::OFF_Q, 64 + ks * 32), desc_k(s0 + cfg::OFF_K, ks * 32),
+                      desc_k(s0 + cfg::OFF_K, 64 + ks * 32), idesc, &acc);
+      acc = 0;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+        mma_terms<NP>(tmem_base + 64, desc_k(s0 + cfg::OFF_DO, ks * 32), desc_k(s0 + cfg::OFF_DO, 64 + ks * 32), desc_k(s0 + cfg::OFF_V, ks * 32),
+                      desc_k(s0 + cfg::OFF_V, 64 + ks * 32), idesc, &acc);
+      umma_commit(&bar);
+    }
+    mbar_wait(&bar, phase); phase ^= 1;
+    tc_fence_after();
+#pragma unroll 1
+    for (int c0 = 0; c0 < LB; c0 += 32) {
+      uint32_t rs[32], rp[32];
+      tmem_ld32(lane_addr + c0, rs);
+      tmem_ld32(lane_addr + 64 + c0, rp);
+      float ds[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float p = (live && k0 + c0 + i < T) ? expf(__uint_as_float(rs[i]) - L) : 0.f;
+        float dpm = __uint_as_float(rp[i]);
+        if (DROP) dpm = drop_keep(dkey, hrow, hcol | (uint32_t)(k0 + c0 + i), dr.thresh) ? dpm * dr.inv_keep : 0.f;
+        ds[i] = p * (dpm - Dq);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) store_score8<NP, 128>(smem + cfg::OFF_DS, cfg::S_PLANE, t, 0, (c0 >> 3) + q, ds + 8 * q);
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (t == 0) {                                            // dQ += dS_blk K_blk : columns [128, 160), accumulated over the blocks
+      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0);
+      const uint32_t a = s0 + cfg::OFF_DS, b = s0 + cfg::OFF_KT;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks)
+        mma_terms<NP>(tmem_base + 128, desc_k(a, ks * 32), desc_k(a + cfg::S_PLANE, ks * 32), desc_k(b, ks * 32), desc_k(b + 4096, ks * 32), idesc,
+                      &acc_dq);
+      umma_commit(&bar);
+    }
+    mbar_wait(&bar, phase); phase ^= 1;                      // the staged tiles are free again
+    tc_fence_after();
+  }
+  {
+    uint32_t r[32];
+    tmem_ld32(lane_addr + 128, r);
+    if (live) store_row32(dqkv + (size_t)(sg.t0 + q0 + t) * ld + h * DH, r, scale);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
+}
+
+template <int NP>
+struct LongDkvCfg {
+  static constexpr int OFF_K = 0, OFF_V = 16384, OFF_Q = 32768, OFF_DO = OFF_Q + LB * 128, OFF_QT = OFF_DO + LB * 128, OFF_DOT = OFF_QT + NP * 4096,
+                       OFF_P = OFF_DOT + NP * 4096;
+  static constexpr int S_PLANE = 128 * 128;                  // [128 key rows][64 queries]
+  static constexpr int OFF_DS = OFF_P + NP * S_PLANE;
+  static constexpr int SMEM = OFF_DS + NP * S_PLANE + 1024;
+  static constexpr int TMEM_COLS = 256;                      // S^T [0, 64), dP^T [64, 128), dK [128, 160), dV [160, 192)
+};
+
+// dK, dV of 128 keys: walks the queries in blocks of 64.  The products are formed transposed -- S^T = K (scale Q)^T, dP^T = V dO^T,
+// one TMEM lane per KEY -- so the score tiles P^T, dS^T are written row-wise by the key's thread and are K-major operands of
+// dV += P^T dO and dK += dS^T (scale Q); the per-query log-sum-exp and D = dO . O come from shared memory.
+template <int NP, bool DROP>
+__global__ void __launch_bounds__(128) attn_tc_bwd_dkv_long_kernel(const float* __restrict__ qkv, const SegGrp seg, const float* __restrict__ lse,
+                                                                   const float* __restrict__ dout, const float* __restrict__ dvec,
+                                                                   float* __restrict__ dqkv, int d, int heads, const Drop dr) {
+  pdl_grid_sync();
+  using cfg = LongDkvCfg<NP>;
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.z);
+  const int T = sg.T, j0 = blockIdx.y * 128;
+  if (T <= 128 || j0 >= T) return;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ float sL[LB], sD[LB];
+  const int t = threadIdx.x, warp = t >> 5;
+  if (t == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc(&tmem_slot, cfg::TMEM_COLS);
+  const float scale = rsqrtf((float)DH);
+  const int ld = 3 * d;
+  const bool live = j0 + t < T;                              // this thread's key
+  {
+    float x[DH];
+    if (live) {
+      const float* rp = qkv + (size_t)(sg.t0 + j0 + t) * ld + h * DH;
+      load_row32(rp + d, x);
+      store_natural(smem + cfg::OFF_K, t, x);
+      load_row32(rp + 2 * d, x);
+      store_natural(smem + cfg::OFF_V, t, x);
+    } else {
+      zero_natural(smem + cfg::OFF_K, t);
+      zero_natural(smem + cfg::OFF_V, t);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint32_t s0 = smem_u32(smem);
+  const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
+  const uint32_t hrow0 = (uint32_t)(sg.t0 - sg.r0), hcol = ((uint32_t)h << 24) | (uint32_t)(j0 + t);
+  uint32_t phase = 0, acc_dk = 0, acc_dv = 0;
+#pragma unroll 1
+  for (int q0 = 0; q0 < T; q0 += LB) {
+    if (t < LB) {                                            // stage the block's queries: scale Q and dO, natural + transposed; lse, D
+      float x[DH];
+      if (q0 + t < T) {
+        load_row32(qkv + (size_t)(sg.t0 + q0 + t) * ld + h * DH, x);
+#pragma unroll
+        for (int c = 0; c < DH; ++c) x[c] *= scale;
+        store_natural(smem + cfg::OFF_Q, t, x);
+        store_transposed<NP>(smem + cfg::OFF_QT, 4096, t, x);
+        load_row32(dout + (size_t)(sg.t0 + q0 + t) * d + h * DH, x);
+        store_natural(smem + cfg::OFF_DO, t, x);
+        store_transposed<NP>(smem + cfg::OFF_DOT, 4096, t, x);
+        sL[t] = lse[(size_t)(sg.t0 + q0 + t) * heads + h];
+        sD[t] = dvec[(size_t)(sg.t0 + q0 + t) * heads + h];
+      } else {
+#pragma unroll
+        for (int c = 0; c < DH; ++c) x[c] = 0.f;
+        zero_natural(smem + cfg::OFF_Q, t);
+        zero_natural(smem + cfg::OFF_DO, t);
+        store_transposed<NP>(smem + cfg::OFF_QT, 4096, t, x);
+        store_transposed<NP>(smem + cfg::OFF_DOT, 4096, t, x);
+        sL[t] = 0.f; sD[t] = 0.f;
+      }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (t == 0) {                                            // S^T = K (scale Q_blk)^T, dP^T = V dO_blk^T : M = 128 keys, N = 64 queries
+      constexpr uint32_t idesc = umma_idesc(128, LB, 0, 0);
+      uint32_t acc = 0;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+        mma_terms<NP>(tmem_base, desc_k(s0 + cfg::OFF_K, ks * 32), desc_k(s0 + cfg::OFF_K, 64 + ks * 32), desc_k(s0 + cfg::OFF_Q, ks * 32),
+                      desc_k(s0 + cfg::OFF_Q, 64 + ks * 32), idesc, &acc);
+      acc = 0;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+        mma_terms<NP>(tmem_base + 64, desc_k(s0 + cfg::OFF_V, ks * 32), desc_k(s0 + cfg::OFF_V, 64 + ks * 32), desc_k(s0 + cfg::OFF_DO, ks * 32),
+                      desc_k(s0 + cfg::OFF_DO, 64 + ks * 32), idesc, &acc);
+      umma_commit(&bar);
+    }
+    mbar_wait(&bar, phase); phase ^= 1;
+    tc_fence_after();
+#pragma unroll 1
+    for (int c0 = 0; c0 < LB; c0 += 32) {
+      uint32_t rs[32], rp[32];
+      tmem_ld32(lane_addr + c0, rs);
+      tmem_ld32(lane_addr + 64 + c0, rp);
+      float pv[32], ds[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int q = q0 + c0 + i;
+        const float p = (live && q < T) ? expf(__uint_as_float(rs[i]) - sL[c0 + i]) : 0.f;
+        float pm = p, dpm = __uint_as_float(rp[i]);
+        if (DROP) {
+          const bool keep = drop_keep(dkey, hrow0 + (uint32_t)q, hcol, dr.thresh);
+          pm = keep ? p * dr.inv_keep : 0.f; dpm = keep ? dpm * dr.inv_keep : 0.f;
+        }
+        pv[i] = pm;
+        ds[i] = p * (dpm - sD[c0 + i]);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        store_score8<NP, 128>(smem + cfg::OFF_P, cfg::S_PLANE, t, 0, (c0 >> 3) + q, pv + 8 * q);
+        store_score8<NP, 128>(smem + cfg::OFF_DS, cfg::S_PLANE, t, 0, (c0 >> 3) + q, ds + 8 * q);
+      }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (t == 0) {                                            // dK += dS^T (scale Q_blk), dV += P^T dO_blk : contract over the 64 queries
+      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0);
+      const uint32_t aS = s0 + cfg::OFF_DS, aP = s0 + cfg::OFF_P, bQ = s0 + cfg::OFF_QT, bO = s0 + cfg::OFF_DOT;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks)
+        mma_terms<NP>(tmem_base + 128, desc_k(aS, ks * 32), desc_k(aS + cfg::S_PLANE, ks * 32), desc_k(bQ, ks * 32), desc_k(bQ + 4096, ks * 32), idesc,
+                      &acc_dk);
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks)
+        mma_terms<NP>(tmem_base + 160, desc_k(aP, ks * 32), desc_k(aP + cfg::S_PLANE, ks * 32), desc_k(bO, ks * 32), desc_k(bO + 4096, ks * 32), idesc,
+                      &acc_dv);
+      umma_commit(&bar);
+    }
+    mbar_wait(&bar, phase); phase ^= 1;
+    tc_fence_after();
+  }
+  {
+    float* rp = dqkv + (size_t)(sg.t0 + j0 + t) * ld + h * DH;
+    uint32_t r[32];
+    tmem_ld32(lane_addr + 128, r);
+    if (live) store_row32(rp + d, r, 1.f);
+    tmem_ld32(lane_addr + 160, r);
+    if (live) store_row32(rp + 2 * d, r, 1.f);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
+}
+
 template <typename K>
 int set_smem_once(K kern, int bytes, bool* done) {
   if (*done) return 0;
@@ -450,6 +903,34 @@ int launch_bwd(const float* qkv, const SegGrp& seg, const float* out, const floa
   return 0;
 }
 
+template <int NP, bool DROP>
+int launch_fwd_long(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, cudaStream_t st, const Drop& dr) {
+  static bool done = false;
+  auto kern = attn_tc_fwd_long_kernel<NP, DROP>;
+  if (int r = set_smem_once(kern, LongFwdCfg<NP>::SMEM, &done)) return r;
+  pdl(kern, dim3(heads, (max_T + 127) / 128, seg.n * seg.B), 128, LongFwdCfg<NP>::SMEM, st)(qkv, seg, out, lse, d, heads, dr);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+template <int NP, bool DROP>
+int launch_bwd_long(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* dvec, int d,
+                    int heads, int max_T, cudaStream_t st, const Drop& dr) {
+  static bool done = false;
+  auto kq = attn_tc_bwd_dq_long_kernel<NP, DROP>;
+  auto kk = attn_tc_bwd_dkv_long_kernel<NP, DROP>;
+  if (!done) {
+    PATHS_CK(cudaFuncSetAttribute(kq, cudaFuncAttributeMaxDynamicSharedMemorySize, LongDqCfg<NP>::SMEM));
+    PATHS_CK(cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, LongDkvCfg<NP>::SMEM));
+    done = true;
+  }
+  const dim3 grid(heads, (max_T + 127) / 128, seg.n * seg.B);
+  pdl(kq, grid, 128, LongDqCfg<NP>::SMEM, st)(qkv, seg, out, lse, dout, dqkv, dvec, d, heads, dr);
+  PATHS_LAUNCH_CK();
+  pdl(kk, grid, 128, LongDkvCfg<NP>::SMEM, st)(qkv, seg, lse, dout, dvec, dqkv, d, heads, dr);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+
 }  // namespace
 
 bool attn_tc_supported(int d, int heads) { return heads > 0 && d % heads == 0 && d / heads == DH && d % 4 == 0; }
@@ -468,14 +949,28 @@ int attn_tc_fwd(int passes, const float* qkv, const SegGrp& seg, float* out, flo
   if (seg.n * seg.B <= 0) return 0;
   ATTN_TC_DISPATCH(launch_fwd, 1, qkv, seg, out, lse, d, heads, st, dr);
   if (max_T > 64) ATTN_TC_DISPATCH(launch_fwd, 2, qkv, seg, out, lse, d, heads, st, dr);
+  if (max_T > 128) {                                         // long bags: tiled over keys (attn_tc_fwd_long_kernel)
+    int r;
+    if (passes == 3) r = dr.thresh ? launch_fwd_long<2, true>(qkv, seg, out, lse, d, heads, max_T, st, dr) : launch_fwd_long<2, false>(qkv, seg, out, lse, d, heads, max_T, st, dr);
+    else r = dr.thresh ? launch_fwd_long<1, true>(qkv, seg, out, lse, d, heads, max_T, st, dr) : launch_fwd_long<1, false>(qkv, seg, out, lse, d, heads, max_T, st, dr);
+    if (r) return r;
+  }
   return 0;
 }
-int attn_tc_bwd(int passes, const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d,
-                int heads, int max_T, cudaStream_t st, const Drop& dr) {
+int attn_tc_bwd(int passes, const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* dvec,
+                int d, int heads, int max_T, cudaStream_t st, const Drop& dr) {
   PATHS_REQUIRE(attn_tc_supported(d, heads) && (passes == 1 || passes == 3), "attn_tc_bwd: head_dim must be 32");
   if (seg.n * seg.B <= 0) return 0;
   ATTN_TC_DISPATCH(launch_bwd, 1, qkv, seg, out, lse, dout, dqkv, d, heads, st, dr);
   if (max_T > 64) ATTN_TC_DISPATCH(launch_bwd, 2, qkv, seg, out, lse, dout, dqkv, d, heads, st, dr);
+  if (max_T > 128) {                                         // long bags: dQ per query tile, then dK / dV per key tile
+    int r;
+    if (passes == 3) r = dr.thresh ? launch_bwd_long<2, true>(qkv, seg, out, lse, dout, dqkv, dvec, d, heads, max_T, st, dr)
+                                   : launch_bwd_long<2, false>(qkv, seg, out, lse, dout, dqkv, dvec, d, heads, max_T, st, dr);
+    else r = dr.thresh ? launch_bwd_long<1, true>(qkv, seg, out, lse, dout, dqkv, dvec, d, heads, max_T, st, dr)
+                       : launch_bwd_long<1, false>(qkv, seg, out, lse, dout, dqkv, dvec, d, heads, max_T, st, dr);
+    if (r) return r;
+  }
   return 0;
 }
 #undef ATTN_TC_DISPATCH

@@ -99,14 +99,14 @@ __device__ __forceinline__ Seg seg_of(const SegGrp& sg, int sv) {
   return r;
 }
 #endif
-// Tensor-core (tcgen05) forms of the short-bag attention, attention_tc.cu: head_dim 32, bags of at most 128 tokens, every token
-// a query.  passes = 3: Q K^T, P V and the four backward products as three-term bf16 splits (fp32-parity); 1: plain bf16.
-// Bags above 128 tokens are left untouched (the tiled kernels of attention.cu serve them).
+// Tensor-core (tcgen05) attention, attention_tc.cu: head_dim 32, every token a query; bags of at most 128 tokens as one tile per
+// (head, slide), longer ones tiled.  passes = 3: Q K^T, P V and the four backward products as three-term bf16 splits
+// (fp32-parity); 1: plain bf16.  dvec: [tokens, heads] scratch (D = dO . O of the long bags).
 bool attn_tc_supported(int d, int heads);
 int attn_tc_fwd(int passes, const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, cudaStream_t st,
                 const Drop& dr);
-int attn_tc_bwd(int passes, const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d,
-                int heads, int max_T, cudaStream_t st, const Drop& dr);
+int attn_tc_bwd(int passes, const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* dvec,
+                int d, int heads, int max_T, cudaStream_t st, const Drop& dr);
 // drop (optional): dropout of the attention probabilities, hashed on (level-local query row, head << 24 | key index)
 // tc_passes: 0 = SIMT fp32 kernels only; 3 / 1 = short bags on the tensor cores (attn_tc_*) in split / plain bf16
 int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st,
