@@ -210,7 +210,7 @@ class ModelRuntime:
                 st = torch.cuda.Stream(self.device)
                 st.wait_stream(torch.cuda.current_stream(self.device))
                 gs.g_bwd = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(gs.g_bwd, stream=st):
+                with torch.cuda.graph(gs.g_bwd, stream=st, capture_error_mode="thread_local"):
                     eng.backward(False)
                 gs.has_backward = True
                 self.layout.gflat.zero_()
@@ -345,12 +345,12 @@ class GraphStep:
         torch.cuda.synchronize(rt.device)
         l0 = eng.launch_count()
         self.g_fwd = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.g_fwd, stream=st):
+        with torch.cuda.graph(self.g_fwd, stream=st, capture_error_mode="thread_local"):     # (a prefetch thread may be copying)
             self._enqueue_fwd()
         self.g_bwd = None
         if backward:
             self.g_bwd = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.g_bwd, stream=st):
+            with torch.cuda.graph(self.g_bwd, stream=st, capture_error_mode="thread_local"):
                 eng.backward(True)
         self.nodes = eng.launch_count() - l0
         rt.layout.attach_grads()

@@ -3,6 +3,8 @@
 O=gpurun_out/r2d; mkdir -p $O
 run() { name=$1; shift; timeout 900 python bench.py "$@" > $O/$name.json 2> $O/$name.err; echo "$name rc=$?"; tail -2 $O/$name.err; }
 run bench_cfg2 --workload cfg2 --steps 20 --warmup 5
+run bench_cfg2_graph --workload cfg2 --steps 50 --warmup 5 --no-cpu-baseline --no-e2e --graph
+run bench_cfg2_b1_graph --workload cfg2 --slides-per-gpu 1 --steps 100 --warmup 5 --no-cpu-baseline --no-e2e --graph
 run bench_cfg2_b1 --workload cfg2 --slides-per-gpu 1 --steps 50 --warmup 5 --no-cpu-baseline --no-fast-mode
 run bench_cfg5 --workload cfg5 --steps 10 --warmup 3
 run bench_cfg4 --workload cfg4 --steps 5 --warmup 3 --no-cpu-baseline

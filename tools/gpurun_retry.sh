@@ -1,10 +1,10 @@
 #!/bin/bash
 # usage: tools/gpurun_retry.sh <log> <timeout> <command...>   -- retries while the pod answers "transient" (rc 3)
 log=$1; shift; to=$1; shift
-for i in $(seq 1 40); do
+for i in $(seq 1 150); do
   /usr/local/graft/bin/gpurun --timeout $to -- "$@" > $log 2>&1
   rc=$?
   if [ $rc -ne 3 ]; then exit $rc; fi
-  sleep 90
+  sleep 20
 done
 exit 3
