@@ -242,6 +242,8 @@ def main():
     ap.add_argument("--slides-per-gpu", type=int, default=None)
     ap.add_argument("--dropout", type=float, default=0.0,
                     help="aggregator dropout of the training step (BASELINE.json's workload is quoted at 0.0; the shipped configs train at 0.05)")
+    ap.add_argument("--store-dtype", default="fp32", choices=["fp32", "bf16"],
+                    help="element type of the HBM-resident pyramid store (bf16: features rounded once at load, half the footprint)")
     ap.add_argument("--graph", action="store_true", help="replay the resident step as one CUDA graph (ModelRuntime.graph_step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -280,7 +282,7 @@ def main():
     D, Lv = cfg.model_config.patch_embed_dim, cfg.num_levels
 
     # ---- the rank's shard of the dataset: pyramids resident in HBM
-    store = PyramidStore(Lv, D, dev)
+    store = PyramidStore(Lv, D, dev, dtype=torch.bfloat16 if args.store_dtype == "bf16" else torch.float32)
     items = []
     for i in range(B):
         sid = rank * B + i
@@ -517,7 +519,7 @@ def main():
             "dtype": DTYPES[args.precision], "data": "synthetic",
             "config": {"workload": W["desc"], "slides_per_gpu": B, "global_batch": B * world, "levels": Lv, "top_k": list(cfg.top_k_patches)[0],
                        "packed_rows_per_step_per_gpu": rows, "rows_per_level": counts, "largest_bag_per_level": [max(b) for b in bags],
-                       "parallelism": f"dp{world}", "dropout": args.dropout, "cuda_graph": bool(args.graph),
+                       "parallelism": f"dp{world}", "dropout": args.dropout, "cuda_graph": bool(args.graph), "store_dtype": args.store_dtype,
                        "l2": "per-step working set (activations of the packed rows, gathers from the HBM-resident pyramid store) exceeds the 126 MB L2: no flush needed"
                              if rows * 100e3 > 126e6 else "working set below L2 at this batch size: the per-step weight re-pack and activation writes evict little; stated, not flushed"},
             "host_ms_per_step": host_enqueue_ms, "exposed_comm_ms_per_step": exposed_resident, "consistency": consistency,

@@ -80,6 +80,8 @@ typedef struct paths_store {
   const uint32_t* occ;            /* bitmap words */
   const uint64_t* occ_off;        /* word offset of each grid's bitmap */
   const int32_t* nonbg;           /* number of set bits of each grid (fallback of slide.py:336-352) */
+  int32_t bf16;                   /* 0: grids are float32 (the reference's on-disk format); 1: grids were rounded to bfloat16 at load
+                                     (grid_ptr then points at bfloat16 data: half the footprint and gather traffic) */
 } paths_store_t;
 
 typedef struct paths_engine paths_engine_t;

@@ -42,7 +42,7 @@ class Dims(C.Structure):
 
 class Store(C.Structure):
     _fields_ = [("grid_ptr", C.c_void_p), ("gw", C.c_void_p), ("gh", C.c_void_p), ("occ", C.c_void_p),
-                ("occ_off", C.c_void_p), ("nonbg", C.c_void_p)]
+                ("occ_off", C.c_void_p), ("nonbg", C.c_void_p), ("bf16", C.c_int32)]
 
 
 _lib = None

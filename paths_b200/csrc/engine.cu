@@ -962,7 +962,7 @@ int do_select(paths_engine* e, int l, cudaStream_t st) {
   RUN(select_expand(a, st)); e->launches += 2;
   pdl(tseg_kernel, (e->B + 255) / 256, 256, 0, st)(n.seg, n.tseg, e->B);
   PATHS_LAUNCH_CK(); e->launches++;
-  RUN(gather_rows(e->store.grid_ptr, e->store.gh, l + 1, dm.L, e->slide_ids, n.row_slide, n.row_xy, n.X, dm.D, n.cap, n.count, st));
+  RUN(gather_rows(e->store.grid_ptr, e->store.gh, l + 1, dm.L, e->slide_ids, n.row_slide, n.row_xy, n.X, dm.D, n.cap, n.count, st, e->store.bf16));
   return 0;
 }
 
@@ -996,7 +996,7 @@ int do_begin(paths_engine* e, const int32_t* slide_ids, const float* fts_padded,
     PATHS_REQUIRE(-N <= v.cap, "begin: %d packed level-0 rows exceed the level's capacity %d", -N, v.cap);
     PATHS_CK(cudaMemcpyAsync(v.X, fts_padded, (size_t)(-N) * e->dm.D * sizeof(float), cudaMemcpyDeviceToDevice, st));
   } else if (fts_padded) RUN(pack_padded_rows(fts_padded, N, v.seg, v.row_slide, v.X, e->dm.D, v.cap, v.count, st));
-  else RUN(gather_rows(e->store.grid_ptr, e->store.gh, 0, e->dm.L, slide_ids, v.row_slide, v.row_xy, v.X, e->dm.D, v.cap, v.count, st));
+  else RUN(gather_rows(e->store.grid_ptr, e->store.gh, 0, e->dm.L, slide_ids, v.row_slide, v.row_xy, v.X, e->dm.D, v.cap, v.count, st, e->store.bf16));
   return 0;
 }
 
@@ -1637,7 +1637,7 @@ int paths_select_expand(const float* alpha, const int32_t* seg, const int32_t* r
 int paths_gather_rows(const paths_store_t* h_store, int level, int L, const int32_t* slide_ids, const int32_t* row_slide, const int32_t* row_xy,
                       float* X, int D, int M, const int32_t* M_dev, void* stream) {
   PATHS_REQUIRE(h_store && row_slide && row_xy && X && level >= 0 && level < L, "gather_rows: bad argument");
-  return gather_rows(h_store->grid_ptr, h_store->gh, level, L, slide_ids, row_slide, row_xy, X, D, M, M_dev, static_cast<cudaStream_t>(stream));
+  return gather_rows(h_store->grid_ptr, h_store->gh, level, L, slide_ids, row_slide, row_xy, X, D, M, M_dev, static_cast<cudaStream_t>(stream), h_store->bf16);
 }
 
 // TransformerAggregator.forward (model/aggregator.py:58-76) of one level on tokens the caller has placed in the level's

@@ -19,6 +19,9 @@ __device__ __forceinline__ int row_count(int M_host, const int* M_dev) { return 
 
 // ---------------------------------------------------------------------------------------------------------
 // gather: X[m,:] = grid(slide, level)[x*H + y, :]         (data_utils/slide.py:331 `fts[new_locs[:,0], new_locs[:,1]]`)
+// BF16: the store holds the grids as bfloat16 (PyramidStore(dtype=torch.bfloat16): half the HBM footprint and gather traffic;
+// the features are rounded once, at load) -- rows are widened to fp32 on the way into X.
+template <bool BF16>
 __global__ void __launch_bounds__(TPB) gather_rows_kernel(const float* const* __restrict__ grid_ptr, const int* __restrict__ gh,
                                                           int level, int L, const int* __restrict__ slide_ids,
                                                           const int* __restrict__ row_slide, const int* __restrict__ row_xy,
@@ -28,10 +31,20 @@ __global__ void __launch_bounds__(TPB) gather_rows_kernel(const float* const* __
   ROW_LOOP(m, M) {
     const int s = row_slide[m];
     const int sid = slide_ids ? slide_ids[s] : s;
-    const float* src = grid_ptr[(size_t)sid * L + level] + ((size_t)row_xy[2 * m] * gh[(size_t)sid * L + level] + row_xy[2 * m + 1]) * D;
+    const size_t cell = (size_t)row_xy[2 * m] * gh[(size_t)sid * L + level] + row_xy[2 * m + 1];
     float4* dst = reinterpret_cast<float4*>(X + (size_t)m * D);
-    const float4* s4 = reinterpret_cast<const float4*>(src);
-    for (int c = lane; c < D / 4; c += 32) dst[c] = __ldg(s4 + c);
+    if (BF16) {
+      const uint2* s2 = reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(grid_ptr[(size_t)sid * L + level]) + cell * D);
+      for (int c = lane; c < D / 4; c += 32) {
+        const uint2 v = __ldg(s2 + c);
+        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.x));
+        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.y));
+        dst[c] = make_float4(a.x, a.y, b.x, b.y);
+      }
+    } else {
+      const float4* s4 = reinterpret_cast<const float4*>(grid_ptr[(size_t)sid * L + level] + cell * D);
+      for (int c = lane; c < D / 4; c += 32) dst[c] = __ldg(s4 + c);
+    }
   }
 }
 
@@ -1303,10 +1316,11 @@ inline int row_grid(int M) { int g = (M + WPB - 1) / WPB; if (g > 8 * kNumSMs) g
 
 // ---- host launchers -----------------------------------------------------------------------------------------
 int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, const int* slide_ids, const int* row_slide,
-                const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st) {
+                const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st, int bf16) {
   PATHS_REQUIRE(D % 4 == 0, "gather_rows: D must be a multiple of 4");
   if (M_host <= 0) return 0;
-  pdl(gather_rows_kernel, row_grid(M_host), TPB, 0, st)(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev);
+  if (bf16) pdl(gather_rows_kernel<true>, row_grid(M_host), TPB, 0, st)(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev);
+  else pdl(gather_rows_kernel<false>, row_grid(M_host), TPB, 0, st)(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev);
   PATHS_LAUNCH_CK();
   return 0;
 }

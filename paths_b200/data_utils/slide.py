@@ -54,7 +54,10 @@ class PreprocessedSlide:
         self.locs = torch.stack((ii.reshape(-1), jj.reshape(-1)), dim=1)
         self.ctx_patch = torch.zeros((x * y, 0, ctx_patch_dim))
         self.parent_inds = torch.arange(x * y)
-        self.fts: List[torch.Tensor] = [grids[0].reshape(x * y, dim).float().cpu()] + list(self.store.grids[self.store_index][1:])
+        g0 = grids[0].reshape(x * y, dim)
+        if self.store.dtype == torch.bfloat16:                       # the batch's level-0 rows are the store's (rounded) rows
+            g0 = g0.to(torch.bfloat16)
+        self.fts: List[torch.Tensor] = [g0.float().cpu()] + list(self.store.grids[self.store_index][1:])
         self.size_pixels = None
 
     def load_patches(self, wsi=None):

@@ -175,7 +175,12 @@ class PyramidStore:
     background; preprocess/loader.py:14-18), plus one occupancy bitmap per grid.  Loaded once per slide; a training
     step then only names slides by index."""
 
-    def __init__(self, num_levels: int, dim: int, device):
+    def __init__(self, num_levels: int, dim: int, device, dtype: torch.dtype = torch.float32):
+        """dtype=torch.bfloat16 keeps the grids as bfloat16 (half the HBM footprint and gather traffic; the features are rounded
+        once, at load -- a model fed by such a store equals the reference fed with the rounded features); the occupancy bitmaps
+        are always built from the float32 grids."""
+        assert dtype in (torch.float32, torch.bfloat16)
+        self.dtype = dtype
         self._cap_cache = {}
         self.L, self.D, self.device = num_levels, dim, torch.device(device)
         self.grids: List[List[torch.Tensor]] = []
@@ -199,6 +204,9 @@ class PyramidStore:
             cnt = torch.zeros(1, dtype=torch.int32, device=self.device)
             L.check(lib.paths_build_occupancy(gd.data_ptr(), w * h, self.D, bits.data_ptr(), cnt.data_ptr(), _stream()),
                     "build_occupancy")
+            if self.dtype == torch.bfloat16:
+                torch.cuda.current_stream(self.device).synchronize()      # the bitmap kernel has read the float32 grid
+                gd = gd.to(torch.bfloat16)
             dev_grids.append(gd); shapes.append((w, h)); self.bits.append(bits); self.counts.append(cnt)
         self.grids.append(dev_grids); self.shapes.append(shapes)
         self._tables = None
@@ -219,6 +227,7 @@ class PyramidStore:
             st = L.Store()
             st.grid_ptr, st.gw, st.gh = t["grid_ptr"].data_ptr(), t["gw"].data_ptr(), t["gh"].data_ptr()
             st.occ, st.occ_off, st.nonbg = t["occ"].data_ptr(), t["occ_off"].data_ptr(), t["nonbg"].data_ptr()
+            st.bf16 = 1 if self.dtype == torch.bfloat16 else 0
             self._tables = (t, st)
         return self._tables
 

@@ -181,6 +181,34 @@ def test_attached_dp_step_runs_inside_loss_backward():
             assert rel_err(p.grad, want[n]) < 1e-5, n
 
 
+def test_bfloat16_pyramid_store():
+    """PyramidStore(dtype=bfloat16): half the footprint; the step equals the oracle fed with the features rounded once."""
+    from oracle import paths_oracle as po
+    from paths_b200.engine import PyramidStore
+    from paths_b200.utils import inference_end2end
+    from tests.parity_check import check_against_oracle
+    fx = load_fixture("brca_b4")
+    ocfg, sd, slides, ybin, cens = fixture_inputs(fx)
+    cfg = product_config(fx)
+    model = product_model(cfg, sd)
+    rt = model.runtime(); rt.set_precision(0)
+    store = PyramidStore(cfg.num_levels, cfg.model_config.patch_embed_dim, "cuda", dtype=torch.bfloat16)
+    batch, _ = product_batch(cfg, model, slides, store=store)
+    assert store.grids[0][2].dtype == torch.bfloat16
+    for use_fts in (True, False):                                   # level-0 rows from the batch / gathered from the store
+        b = dict(batch)
+        if not use_fts:
+            b.pop("fts")
+        hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
+        for p in model.parameters():
+            p.grad = None
+        loss.backward()
+        torch.cuda.synchronize()
+        for s in slides:
+            s.grids = [g.to(torch.bfloat16).float() for g in s.grids]
+        check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss, 0)
+
+
 def test_custom_op_layer_equals_the_autograd_function():
     """torch.ops.paths_b200.step (paths_b200/ops.py) is the default route of inference_end2end; the plain autograd.Function
     route (PATHS_B200_NO_CUSTOM_OP=1) must give the same hazards, loss and gradients."""
