@@ -36,8 +36,8 @@ constexpr int kNumSMs = 148;                     // B200
 // attribute and starts with pdl_grid_sync(): `launch_dependents` lets the NEXT kernel of the stream become resident as soon as
 // every CTA of this one has started (its CTAs fill the SMs while ours drain), `wait` blocks until the PREVIOUS kernel has
 // completed and flushed its memory -- so no kernel touches global memory before its predecessor is done, and completion stays
-// transitive because every CTA of every kernel executes the wait before anything else.  PATHS_B200_PDL=0 launches plainly
-// (griddepcontrol is then a no-op).
+// transitive because every CTA of every kernel executes the wait before anything else.  Opt-in: PATHS_B200_PDL=1 (without the
+// launch attribute griddepcontrol is a no-op) -- on the multi-stream step it measured slower, see DESIGN.md §3.7b.
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_grid_sync() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
