@@ -74,9 +74,15 @@ def check_against_oracle(ocfg, sd, slides, ybin, cens, cfg, model, rt, hz, loss,
         return recs
     # 3. gradients on every live parameter; None / zero pattern
     #   fp32   : every tensor within 1e-4 of its own scale (floored at 1e-3 of the largest gradient entry; tensors of a
-    #            handful of elements -- the importance head's output bias -- are pure cancelling sums: floor 1e-2)
-    #   bf16x3 : the whole flat gradient within 1e-4 (max-norm and L2) of the gradient's scale; single tensors, whose entries
-    #            are strongly cancelling sums over patches, within 1e-2 of their own scale (split-bf16 products carry 2^-17)
+    #            handful of elements -- the importance head's output bias -- are pure cancelling sums: floor 1e-2).
+    #            Measured against a float64 oracle the fp32 mode is at 1.5e-5 per tensor (profiles/parity_grads_r2.txt).
+    #   bf16x3 : the whole flat gradient within 1e-4 (max-norm and L2) of the gradient's scale.  Single tensors are held to
+    #            1e-2 of their own scale, and that is the model, not the kernels: the network has kinks (the ReLUs of the
+    #            importance MLP and of the decoders' feed-forward blocks), a pre-activation within 2^-17 of zero flips its
+    #            mask, and the gradient of the weights behind it moves by a whole term of its sum.  The float64 REFERENCE
+    #            with its weights perturbed by a relative 2^-17 shows the same per-tensor deviations (1e-3 .. 6e-3 on the
+    #            same tensors; profiles/parity_grads_r2.txt part A), so no implementation whose forward pass differs at
+    #            that level can hold 1e-4 tensor by tensor; where no mask flips (cfg 5 in that table) bf16x3 is at 4e-5.
     #   bf16   : ReLU / top-K masks may flip for near-zero pre-activations; relative L2 error of the flat gradient < 5e-2
     named = dict(model.named_parameters())
     gmax = max(float(g.abs().max()) for g in ograds.values() if g is not None)
