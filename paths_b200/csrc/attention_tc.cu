@@ -128,8 +128,11 @@ struct FwdCfg {
   static constexpr int NAT = NT * 128;                      // natural tile bytes
   static constexpr int VT_PLANE = NKB * 4096;               // transposed V, one plane
   static constexpr int P_PLANE = NKB * NT * 128;            // score tile, one plane
-  static constexpr int OFF_Q = 0, OFF_K = NAT, OFF_VT = 2 * NAT, OFF_P = OFF_VT + NP * VT_PLANE;
-  static constexpr int SMEM = OFF_P + NP * P_PLANE + 8192 + 1024;     // + slack an M = 128 operand of the 64-row class reads past + alignment
+  static constexpr int OFF_Q = 0, OFF_K = NAT, OFF_VT = 2 * NAT;
+  // 64-row class: P (hi, lo: 2 x 8 KB) takes the place of Q | K once S is done, and the 64 rows an M = 128 operand reads past a
+  // block land in the next plane / the V tile -- 25 KB per CTA, eight CTAs per SM.  128-row class: P has its own 64 KB.
+  static constexpr int OFF_P = NKB == 1 ? 0 : OFF_VT + NP * VT_PLANE;
+  static constexpr int SMEM = (NKB == 1 ? OFF_VT + NP * VT_PLANE : OFF_P + NP * P_PLANE) + 1024;
   static constexpr int TMEM_COLS = 64 * NKB;                // S; O reuses its columns
 };
 
@@ -155,23 +158,23 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   const float scale = rsqrtf((float)DH);
   const int ld = 3 * d;
   {
-    float x[DH];
+    float x[DH], y[DH], z[DH];
     if (t < T) {
       const float* rp = qkv + (size_t)(sg.t0 + t) * ld + h * DH;
       load_row32(rp, x);
+      load_row32(rp + d, y);
+      load_row32(rp + 2 * d, z);
 #pragma unroll
       for (int c = 0; c < DH; ++c) x[c] *= scale;
       store_natural(smem + cfg::OFF_Q, t, x);
-      load_row32(rp + d, x);
-      store_natural(smem + cfg::OFF_K, t, x);
-      load_row32(rp + 2 * d, x);
+      store_natural(smem + cfg::OFF_K, t, y);
     } else {
       zero_natural(smem + cfg::OFF_Q, t);
       zero_natural(smem + cfg::OFF_K, t);
 #pragma unroll
-      for (int c = 0; c < DH; ++c) x[c] = 0.f;
+      for (int c = 0; c < DH; ++c) z[c] = 0.f;
     }
-    store_transposed<NP>(smem + cfg::OFF_VT, cfg::VT_PLANE, t, x);     // rows past the bag: zeros (0 * garbage must stay 0)
+    store_transposed<NP>(smem + cfg::OFF_VT, cfg::VT_PLANE, t, z);     // rows past the bag: zeros (0 * garbage must stay 0)
   }
   fence_proxy_async();
   tc_fence_before();
@@ -295,17 +298,20 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
     float x[DH], y[DH];
     if (t < T) {
       const float* rp = qkv + (size_t)(sg.t0 + t) * ld + h * DH;
-      load_row32(rp, x);
-      load_row32(rp + d, y);
-#pragma unroll
-      for (int c = 0; c < DH; ++c) x[c] *= scale;
-      store_natural(smem + cfg::OFF_Q, t, x);
-      store_transposed<NP>(smem + cfg::OFF_QT, cfg::T_PLANE, t, x);
-      store_natural(smem + cfg::OFF_K, t, y);
-      store_transposed<NP>(smem + cfg::OFF_KT, cfg::T_PLANE, t, y);
-      load_row32(rp + 2 * d, x);
-      store_natural(smem + cfg::OFF_V, t, x);
       const size_t orow = (size_t)(sg.t0 + t) * d + h * DH;
+      {
+        float z[DH];
+        load_row32(rp, x);
+        load_row32(rp + d, y);
+        load_row32(rp + 2 * d, z);
+  #pragma unroll
+        for (int c = 0; c < DH; ++c) x[c] *= scale;
+        store_natural(smem + cfg::OFF_Q, t, x);
+        store_natural(smem + cfg::OFF_K, t, y);
+        store_natural(smem + cfg::OFF_V, t, z);
+      }
+      store_transposed<NP>(smem + cfg::OFF_QT, cfg::T_PLANE, t, x);
+      store_transposed<NP>(smem + cfg::OFF_KT, cfg::T_PLANE, t, y);
       load_row32(dout + orow, x);
       load_row32(out + orow, y);
 #pragma unroll
