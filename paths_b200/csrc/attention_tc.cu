@@ -143,10 +143,10 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   pdl_grid_sync();
   using cfg = FwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
-  const int h = blockIdx.x;
-  const Seg sg = seg_of(seg, blockIdx.y);
-  const int T = sg.T;
-  if (T > NT || (NKB == 2 && T <= 64)) return;              // the other class's launch (or the tiled kernels) serves this bag
+  // Persistent: a CTA walks the (head, slide) items item = blockIdx.x, += gridDim.x and takes those of its size class -- the
+  // barrier, the TMEM columns and the launch itself are paid once per CTA, and a launch for the rarer class costs a scan of the
+  // segment table instead of one CTA (with its shared-memory reservation) per item.
+  const int n_items = heads * seg.n * seg.B;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -157,6 +157,17 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
 
   const float scale = rsqrtf((float)DH);
   const int ld = 3 * d;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  uint32_t phase = 0;
+#pragma unroll 1
+  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+  const int h = item % heads;
+  const Seg sg = seg_of(seg, item / heads);
+  const int T = sg.T;
+  if (T > NT || (NKB == 2 && T <= 64)) continue;            // the other class's launch (or the tiled kernels) serves this bag
   {
     float x[DH], y[DH], z[DH];
     if (t < T) {
@@ -180,7 +191,6 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
   const uint32_t sQ = smem_u32(smem + cfg::OFF_Q), sK = smem_u32(smem + cfg::OFF_K), sVt = smem_u32(smem + cfg::OFF_VT),
                  sP = smem_u32(smem + cfg::OFF_P);
   if (t == 0) {                                              // S = (scale Q) K^T : M = 128, N = NT keys, K = 32
@@ -191,7 +201,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
       mma_terms<NP>(tmem_base, desc_k(sQ, ks * 32), desc_k(sQ, 64 + ks * 32), desc_k(sK, ks * 32), desc_k(sK, 64 + ks * 32), idesc, &acc);
     umma_commit(&bar);
   }
-  mbar_wait(&bar, 0);
+  mbar_wait(&bar, phase); phase ^= 1;
   tc_fence_after();
 
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
@@ -240,7 +250,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
       }
     umma_commit(&bar);
   }
-  mbar_wait(&bar, 1);
+  mbar_wait(&bar, phase); phase ^= 1;
   tc_fence_after();
   {
     uint32_t r[32];
@@ -249,6 +259,10 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
       store_row32(out + (size_t)(sg.t0 + t) * d + h * DH, r, 1.f / sum);
       lse[(size_t)(sg.t0 + t) * heads + h] = mx + logf(sum);
     }
+  }
+  tc_fence_before();                                         // the next item overwrites the tiles and the accumulator columns
+  __syncthreads();
+  tc_fence_after();
   }
   tc_fence_before();
   __syncthreads();
@@ -279,10 +293,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   pdl_grid_sync();
   using cfg = BwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
-  const int h = blockIdx.x;
-  const Seg sg = seg_of(seg, blockIdx.y);
-  const int T = sg.T;
-  if (T > NT || (NKB == 2 && T <= 64)) return;
+  const int n_items = heads * seg.n * seg.B;                 // persistent over the (head, slide) items, as the forward kernel
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -293,6 +304,17 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
 
   const float scale = rsqrtf((float)DH);
   const int ld = 3 * d;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  uint32_t phase = 0;
+#pragma unroll 1
+  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+  const int h = item % heads;
+  const Seg sg = seg_of(seg, item / heads);
+  const int T = sg.T;
+  if (T > NT || (NKB == 2 && T <= 64)) continue;
   float Dq = 0.f, L = 0.f;
   {
     float x[DH], y[DH];
@@ -333,7 +355,6 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
   const uint32_t s0 = smem_u32(smem);
   if (t == 0) {                                              // S = (scale Q) K^T -> columns [0, NT);  dP = dO V^T -> [NT, 2 NT)
     constexpr uint32_t idesc = umma_idesc(128, NT, 0, 0);
@@ -349,7 +370,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
                     desc_k(s0 + cfg::OFF_V, 64 + ks * 32), idesc, &acc);
     umma_commit(&bar);
   }
-  mbar_wait(&bar, 0);                                        // both products done: the natural tiles may be overwritten
+  mbar_wait(&bar, phase); phase ^= 1;                        // both products done: the natural tiles may be overwritten
   tc_fence_after();
 
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
@@ -411,7 +432,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
     }
     umma_commit(&bar);
   }
-  mbar_wait(&bar, 1);
+  mbar_wait(&bar, phase); phase ^= 1;
   tc_fence_after();
   {
     float* rp = dqkv + (size_t)(sg.t0 + t) * ld + h * DH;
@@ -422,6 +443,10 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
     if (t < T) store_row32(rp + d, r, 1.f);
     tmem_ld32(lane_addr + 64, r);
     if (t < T) store_row32(rp + 2 * d, r, 1.f);
+  }
+  tc_fence_before();                                         // the next item overwrites the tiles and the accumulator columns
+  __syncthreads();
+  tc_fence_after();
   }
   tc_fence_before();
   __syncthreads();
@@ -889,12 +914,24 @@ int set_smem_once(K kern, int bytes, bool* done) {
   return 0;
 }
 
+// one resident wave: CTAs per SM by occupancy (shared memory, registers) and by the 512 TMEM columns, times the SMs
+template <typename K>
+int persistent_grid(K kern, int threads, int smem, int tmem_cols, int n_items) {
+  int per_sm = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+  if (per_sm > 512 / tmem_cols) per_sm = 512 / tmem_cols;
+  int g = per_sm * kNumSMs;
+  if (g > n_items) g = n_items;
+  return g < 1 ? 1 : g;
+}
+
 template <int NKB, int NP, bool DROP>
 int launch_fwd(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, cudaStream_t st, const Drop& dr) {
   static bool done = false;
   auto kern = attn_tc_fwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, FwdCfg<NKB, NP>::SMEM, &done)) return r;
-  pdl(kern, dim3(heads, seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, d, heads, dr);
+  pdl(kern, persistent_grid(kern, 64 * NKB, FwdCfg<NKB, NP>::SMEM, FwdCfg<NKB, NP>::TMEM_COLS, heads * seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(
+      qkv, seg, out, lse, d, heads, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -904,7 +941,8 @@ int launch_bwd(const float* qkv, const SegGrp& seg, const float* out, const floa
   static bool done = false;
   auto kern = attn_tc_bwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, BwdCfg<NKB, NP>::SMEM, &done)) return r;
-  pdl(kern, dim3(heads, seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, dout, dqkv, d, heads, dr);
+  pdl(kern, persistent_grid(kern, 64 * NKB, BwdCfg<NKB, NP>::SMEM, BwdCfg<NKB, NP>::TMEM_COLS, heads * seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(
+      qkv, seg, out, lse, dout, dqkv, d, heads, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
