@@ -143,9 +143,6 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   pdl_grid_sync();
   using cfg = FwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
-  // Persistent: a CTA walks the (head, slide) items item = blockIdx.x, += gridDim.x and takes those of its size class -- the
-  // barrier, the TMEM columns and the launch itself are paid once per CTA, and a launch for the rarer class costs a scan of the
-  // segment table instead of one CTA (with its shared-memory reservation) per item.
   const int n_items = heads * seg.n * seg.B;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -162,8 +159,27 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   uint32_t phase = 0;
+  // Items of this CTA.  64-row class (nearly every bag): one CTA per item, scheduled by the hardware.  128-row class (rare): the
+  // launch is one resident wave whose CTAs scan the segment table NT items at a time and keep the matches in a shared list -- it
+  // costs a scan, not a CTA with its shared-memory reservation per item.
+  __shared__ int s_list[NT];
+  __shared__ int s_cnt;
 #pragma unroll 1
-  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+  for (int base = NKB == 2 ? blockIdx.x * NT : blockIdx.x; base < n_items; base += NKB == 2 ? gridDim.x * NT : n_items) {
+  int n_here = 1;
+  if (NKB == 2) {
+    if (t == 0) s_cnt = 0;
+    __syncthreads();
+    if (base + t < n_items) {
+      const int Ti = seg_of(seg, (base + t) / heads).T;
+      if (Ti > 64 && Ti <= NT) s_list[atomicAdd(&s_cnt, 1)] = base + t;
+    }
+    __syncthreads();
+    n_here = s_cnt;
+  }
+#pragma unroll 1
+  for (int k = 0; k < n_here; ++k) {
+  const int item = NKB == 2 ? s_list[k] : base;
   const int h = item % heads;
   const Seg sg = seg_of(seg, item / heads);
   const int T = sg.T;
@@ -264,6 +280,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   __syncthreads();
   tc_fence_after();
   }
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
@@ -293,7 +310,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   pdl_grid_sync();
   using cfg = BwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
-  const int n_items = heads * seg.n * seg.B;                 // persistent over the (head, slide) items, as the forward kernel
+  const int n_items = heads * seg.n * seg.B;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -309,8 +326,27 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   uint32_t phase = 0;
+  // Items of this CTA.  64-row class (nearly every bag): one CTA per item, scheduled by the hardware.  128-row class (rare): the
+  // launch is one resident wave whose CTAs scan the segment table NT items at a time and keep the matches in a shared list -- it
+  // costs a scan, not a CTA with its shared-memory reservation per item.
+  __shared__ int s_list[NT];
+  __shared__ int s_cnt;
 #pragma unroll 1
-  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+  for (int base = NKB == 2 ? blockIdx.x * NT : blockIdx.x; base < n_items; base += NKB == 2 ? gridDim.x * NT : n_items) {
+  int n_here = 1;
+  if (NKB == 2) {
+    if (t == 0) s_cnt = 0;
+    __syncthreads();
+    if (base + t < n_items) {
+      const int Ti = seg_of(seg, (base + t) / heads).T;
+      if (Ti > 64 && Ti <= NT) s_list[atomicAdd(&s_cnt, 1)] = base + t;
+    }
+    __syncthreads();
+    n_here = s_cnt;
+  }
+#pragma unroll 1
+  for (int k = 0; k < n_here; ++k) {
+  const int item = NKB == 2 ? s_list[k] : base;
   const int h = item % heads;
   const Seg sg = seg_of(seg, item / heads);
   const int T = sg.T;
@@ -447,6 +483,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   tc_fence_before();                                         // the next item overwrites the tiles and the accumulator columns
   __syncthreads();
   tc_fence_after();
+  }
   }
   tc_fence_before();
   __syncthreads();
@@ -930,7 +967,7 @@ int launch_fwd(const float* qkv, const SegGrp& seg, float* out, float* lse, int 
   static bool done = false;
   auto kern = attn_tc_fwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, FwdCfg<NKB, NP>::SMEM, &done)) return r;
-  pdl(kern, persistent_grid(kern, 64 * NKB, FwdCfg<NKB, NP>::SMEM, FwdCfg<NKB, NP>::TMEM_COLS, heads * seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(
+  pdl(kern, NKB == 1 ? heads * seg.n * seg.B : persistent_grid(kern, 64 * NKB, FwdCfg<NKB, NP>::SMEM, FwdCfg<NKB, NP>::TMEM_COLS, heads * seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(
       qkv, seg, out, lse, d, heads, dr);
   PATHS_LAUNCH_CK();
   return 0;
@@ -941,7 +978,7 @@ int launch_bwd(const float* qkv, const SegGrp& seg, const float* out, const floa
   static bool done = false;
   auto kern = attn_tc_bwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, BwdCfg<NKB, NP>::SMEM, &done)) return r;
-  pdl(kern, persistent_grid(kern, 64 * NKB, BwdCfg<NKB, NP>::SMEM, BwdCfg<NKB, NP>::TMEM_COLS, heads * seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(
+  pdl(kern, NKB == 1 ? heads * seg.n * seg.B : persistent_grid(kern, 64 * NKB, BwdCfg<NKB, NP>::SMEM, BwdCfg<NKB, NP>::TMEM_COLS, heads * seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(
       qkv, seg, out, lse, dout, dqkv, d, heads, dr);
   PATHS_LAUNCH_CK();
   return 0;

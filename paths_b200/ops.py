@@ -76,7 +76,7 @@ def _backward(ctx, g_hz, g_loss):
     if g_hz is not None and rt.track_hazard_grad:
         dlog.add_(g_hz * hz * (1 - hz) if eng.dims.task == 0 else g_hz)
     rt.layout.prepare_grads()
-    if rt.grad_sync is not None:                            # data parallelism: bucketed all-reduce behind the backward pass
+    if rt.grad_sync is not None and rt.grad_sync.world > 1:  # data parallelism: bucketed all-reduce behind the backward pass
         rt.grad_sync.backward(eng, zero=False)
     elif ctx.graph and gs is not None and gs.g_bwd is not None:
         gs.g_bwd.replay()

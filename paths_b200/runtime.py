@@ -49,7 +49,7 @@ class _StepFn(torch.autograd.Function):
         if g_hz is not None and rt.track_hazard_grad:
             dlog.add_(g_hz * hz * (1 - hz) if eng.dims.task == 0 else g_hz)
         rt.layout.prepare_grads()
-        if rt.grad_sync is not None:                    # data parallelism: bucketed all-reduce behind the backward pass
+        if rt.grad_sync is not None and rt.grad_sync.world > 1:   # data parallelism: bucketed all-reduce behind the backward pass
             rt.grad_sync.backward(eng, zero=False)
         elif ctx.gs is not None and ctx.gs.g_bwd is not None:
             ctx.gs.g_bwd.replay()
@@ -176,7 +176,7 @@ class ModelRuntime:
             scale = 1.0 / float(gb if gb else B)
             self._arm_dropout(eng)
             gs = None
-            if self.use_graphs and self.last_dropout[0] == 0.0 and fts is None and self.grad_sync is None:
+            if self.use_graphs and self.last_dropout[0] == 0.0 and fts is None and (self.grad_sync is None or self.grad_sync.world == 1):
                 gs = self._graph_for(eng, slide_ids, ybin, cens, scale, pk, torch.is_grad_enabled())
             if self.use_custom_op:                      # torch.ops.paths_b200.step (ops.py): the custom-op layer over the C ABI
                 from . import ops
