@@ -143,7 +143,10 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   pdl_grid_sync();
   using cfg = FwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
-  const int n_items = heads * seg.n * seg.B;
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.y);
+  const int T = sg.T;
+  if (T > NT || (NKB == 2 && T <= 64)) return;              // the other class's launch (or the tiled kernels) serves this bag
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -154,36 +157,6 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
 
   const float scale = rsqrtf((float)DH);
   const int ld = 3 * d;
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
-  uint32_t phase = 0;
-  // Items of this CTA.  64-row class (nearly every bag): one CTA per item, scheduled by the hardware.  128-row class (rare): the
-  // launch is one resident wave whose CTAs scan the segment table NT items at a time and keep the matches in a shared list -- it
-  // costs a scan, not a CTA with its shared-memory reservation per item.
-  __shared__ int s_list[NT];
-  __shared__ int s_cnt;
-#pragma unroll 1
-  for (int base = NKB == 2 ? blockIdx.x * NT : blockIdx.x; base < n_items; base += NKB == 2 ? gridDim.x * NT : n_items) {
-  int n_here = 1;
-  if (NKB == 2) {
-    if (t == 0) s_cnt = 0;
-    __syncthreads();
-    if (base + t < n_items) {
-      const int Ti = seg_of(seg, (base + t) / heads).T;
-      if (Ti > 64 && Ti <= NT) s_list[atomicAdd(&s_cnt, 1)] = base + t;
-    }
-    __syncthreads();
-    n_here = s_cnt;
-  }
-#pragma unroll 1
-  for (int k = 0; k < n_here; ++k) {
-  const int item = NKB == 2 ? s_list[k] : base;
-  const int h = item % heads;
-  const Seg sg = seg_of(seg, item / heads);
-  const int T = sg.T;
-  if (T > NT || (NKB == 2 && T <= 64)) continue;            // the other class's launch (or the tiled kernels) serves this bag
   {
     float x[DH], y[DH], z[DH];
     if (t < T) {
@@ -207,6 +180,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
   const uint32_t sQ = smem_u32(smem + cfg::OFF_Q), sK = smem_u32(smem + cfg::OFF_K), sVt = smem_u32(smem + cfg::OFF_VT),
                  sP = smem_u32(smem + cfg::OFF_P);
   if (t == 0) {                                              // S = (scale Q) K^T : M = 128, N = NT keys, K = 32
@@ -217,7 +191,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
       mma_terms<NP>(tmem_base, desc_k(sQ, ks * 32), desc_k(sQ, 64 + ks * 32), desc_k(sK, ks * 32), desc_k(sK, 64 + ks * 32), idesc, &acc);
     umma_commit(&bar);
   }
-  mbar_wait(&bar, phase); phase ^= 1;
+  mbar_wait(&bar, 0);
   tc_fence_after();
 
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
@@ -266,7 +240,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
       }
     umma_commit(&bar);
   }
-  mbar_wait(&bar, phase); phase ^= 1;
+  mbar_wait(&bar, 1);
   tc_fence_after();
   {
     uint32_t r[32];
@@ -275,11 +249,6 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
       store_row32(out + (size_t)(sg.t0 + t) * d + h * DH, r, 1.f / sum);
       lse[(size_t)(sg.t0 + t) * heads + h] = mx + logf(sum);
     }
-  }
-  tc_fence_before();                                         // the next item overwrites the tiles and the accumulator columns
-  __syncthreads();
-  tc_fence_after();
-  }
   }
   tc_fence_before();
   __syncthreads();
@@ -310,7 +279,10 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   pdl_grid_sync();
   using cfg = BwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
-  const int n_items = heads * seg.n * seg.B;
+  const int h = blockIdx.x;
+  const Seg sg = seg_of(seg, blockIdx.y);
+  const int T = sg.T;
+  if (T > NT || (NKB == 2 && T <= 64)) return;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -321,36 +293,6 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
 
   const float scale = rsqrtf((float)DH);
   const int ld = 3 * d;
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
-  uint32_t phase = 0;
-  // Items of this CTA.  64-row class (nearly every bag): one CTA per item, scheduled by the hardware.  128-row class (rare): the
-  // launch is one resident wave whose CTAs scan the segment table NT items at a time and keep the matches in a shared list -- it
-  // costs a scan, not a CTA with its shared-memory reservation per item.
-  __shared__ int s_list[NT];
-  __shared__ int s_cnt;
-#pragma unroll 1
-  for (int base = NKB == 2 ? blockIdx.x * NT : blockIdx.x; base < n_items; base += NKB == 2 ? gridDim.x * NT : n_items) {
-  int n_here = 1;
-  if (NKB == 2) {
-    if (t == 0) s_cnt = 0;
-    __syncthreads();
-    if (base + t < n_items) {
-      const int Ti = seg_of(seg, (base + t) / heads).T;
-      if (Ti > 64 && Ti <= NT) s_list[atomicAdd(&s_cnt, 1)] = base + t;
-    }
-    __syncthreads();
-    n_here = s_cnt;
-  }
-#pragma unroll 1
-  for (int k = 0; k < n_here; ++k) {
-  const int item = NKB == 2 ? s_list[k] : base;
-  const int h = item % heads;
-  const Seg sg = seg_of(seg, item / heads);
-  const int T = sg.T;
-  if (T > NT || (NKB == 2 && T <= 64)) continue;
   float Dq = 0.f, L = 0.f;
   {
     float x[DH], y[DH];
@@ -391,6 +333,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
   const uint32_t s0 = smem_u32(smem);
   if (t == 0) {                                              // S = (scale Q) K^T -> columns [0, NT);  dP = dO V^T -> [NT, 2 NT)
     constexpr uint32_t idesc = umma_idesc(128, NT, 0, 0);
@@ -406,7 +349,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
                     desc_k(s0 + cfg::OFF_V, 64 + ks * 32), idesc, &acc);
     umma_commit(&bar);
   }
-  mbar_wait(&bar, phase); phase ^= 1;                        // both products done: the natural tiles may be overwritten
+  mbar_wait(&bar, 0);                                        // both products done: the natural tiles may be overwritten
   tc_fence_after();
 
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
@@ -468,7 +411,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
     }
     umma_commit(&bar);
   }
-  mbar_wait(&bar, phase); phase ^= 1;
+  mbar_wait(&bar, 1);
   tc_fence_after();
   {
     float* rp = dqkv + (size_t)(sg.t0 + t) * ld + h * DH;
@@ -479,11 +422,6 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
     if (t < T) store_row32(rp + d, r, 1.f);
     tmem_ld32(lane_addr + 64, r);
     if (t < T) store_row32(rp + 2 * d, r, 1.f);
-  }
-  tc_fence_before();                                         // the next item overwrites the tiles and the accumulator columns
-  __syncthreads();
-  tc_fence_after();
-  }
   }
   tc_fence_before();
   __syncthreads();
@@ -951,24 +889,12 @@ int set_smem_once(K kern, int bytes, bool* done) {
   return 0;
 }
 
-// one resident wave: CTAs per SM by occupancy (shared memory, registers) and by the 512 TMEM columns, times the SMs
-template <typename K>
-int persistent_grid(K kern, int threads, int smem, int tmem_cols, int n_items) {
-  int per_sm = 1;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
-  if (per_sm > 512 / tmem_cols) per_sm = 512 / tmem_cols;
-  int g = per_sm * kNumSMs;
-  if (g > n_items) g = n_items;
-  return g < 1 ? 1 : g;
-}
-
 template <int NKB, int NP, bool DROP>
 int launch_fwd(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, cudaStream_t st, const Drop& dr) {
   static bool done = false;
   auto kern = attn_tc_fwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, FwdCfg<NKB, NP>::SMEM, &done)) return r;
-  pdl(kern, NKB == 1 ? heads * seg.n * seg.B : persistent_grid(kern, 64 * NKB, FwdCfg<NKB, NP>::SMEM, FwdCfg<NKB, NP>::TMEM_COLS, heads * seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(
-      qkv, seg, out, lse, d, heads, dr);
+  pdl(kern, dim3(heads, seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, d, heads, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -978,8 +904,7 @@ int launch_bwd(const float* qkv, const SegGrp& seg, const float* out, const floa
   static bool done = false;
   auto kern = attn_tc_bwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, BwdCfg<NKB, NP>::SMEM, &done)) return r;
-  pdl(kern, NKB == 1 ? heads * seg.n * seg.B : persistent_grid(kern, 64 * NKB, BwdCfg<NKB, NP>::SMEM, BwdCfg<NKB, NP>::TMEM_COLS, heads * seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(
-      qkv, seg, out, lse, dout, dqkv, d, heads, dr);
+  pdl(kern, dim3(heads, seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, dout, dqkv, d, heads, dr);
   PATHS_LAUNCH_CK();
   return 0;
 }
