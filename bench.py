@@ -344,6 +344,7 @@ def main():
                     with torch.no_grad():
                         hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
                 losses.append(float(loss.item()))
+                step_wall.append(time.perf_counter())
                 if world > 1 and train:
                     exposed.append(dp.last_exposed_comm())
         finally:
@@ -354,6 +355,13 @@ def main():
 
     host_ms = [0.0]
     e2e_losses = []
+    step_wall = []
+    # The synthetic dataset is hundreds of thousands of live Python objects; a full garbage-collector pass over them costs tens of
+    # milliseconds, and the end-to-end loop (which waits for the loss every step) pays such a pause in full.  Freeze what exists
+    # now (the objects of set-up never die): later collections only look at what the steps themselves allocate.
+    import gc
+    gc.collect()
+    gc.freeze()
 
     def timed(fn, steps, warmup, profile=False, multi=False):
         if multi:
@@ -465,7 +473,9 @@ def main():
     e2e = None
     if not args.no_e2e:
         exposed.clear()
-        e_ms, _, _ = timed(run_e2e, args.steps, 3, multi=True)
+        e_ms, _, _ = timed(run_e2e, args.steps, max(5, args.warmup), multi=True)
+        w = step_wall[-args.steps:]
+        per = sorted((b - a) * 1e3 for a, b in zip(w[:-1], w[1:]))
         h2d = batch["fts_packed"].numel() * 4 + B * 4 * 2
         e2e = {"value": B * world * args.steps / (e_ms / 1e3), "unit": "slides/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 4 + 8, "ms_per_step": e_ms / args.steps,
@@ -473,9 +483,10 @@ def main():
                       "loss.item() -- host batch to gradients (no optimizer step); level-0 rows cross PCIe unpadded (collate_fn(packed=True): "
                       f"{h2d} bytes against {padded_bytes} for the padded tensor); the pinned-host -> HBM copy of step i+1 overlaps step i; "
                       "d2h = the loss + the 8-byte overflow flag",
-               "exposed_comm_ms_per_step": (sum(exposed[-args.steps:]) / max(1, len(exposed[-args.steps:]))) if exposed else 0.0}
+               "exposed_comm_ms_per_step": (sum(exposed[-args.steps:]) / max(1, len(exposed[-args.steps:]))) if exposed else 0.0,
+               "host_wall_ms_per_step": {"min": per[0], "median": per[len(per) // 2], "max": per[-1]} if per else None}
         if train:
-            o_ms, _, _ = timed(lambda n: run_e2e(n, with_opt=True), args.steps, 3, multi=True)
+            o_ms, _, _ = timed(lambda n: run_e2e(n, with_opt=True), args.steps, max(5, args.warmup), multi=True)
             e2e["with_optimizer"] = {"value": B * world * args.steps / (o_ms / 1e3), "unit": "slides/s", "ms_per_step": o_ms / args.steps,
                                      "what": "the same loop with opt.step() (fused flat AdamW, train.py:66) after loss.backward()"}
 
