@@ -823,21 +823,13 @@ namespace {
 // Single-query attention (nq_mode 1: the last decoder layer is read at the special token only, aggregator.py:75), head_dim 32.
 // One warp per (slide, head), any bag length: lanes run over the keys of a 32-key chunk for the scores (each lane reads its
 // key row), then over the head dims for the value sum (coalesced rows, probabilities by shuffle); online softmax over chunks.
-__global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restrict__ qkv, const SegGrp seg,
-                                                           float* __restrict__ out, float* __restrict__ lse, int d, int heads, int B) {
-  pdl_grid_sync();
-  const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (wid >= B * heads) return;
-  const int s = wid / heads, h = wid % heads;
-  const Seg sg = seg_of(seg, s);
-  const int ld = 3 * d;
-  const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
-  const float qv = base[lane] * rsqrtf(32.f);
-  float m = -INFINITY, l = 0.f, o = 0.f;
-  for (int j0 = 0; j0 < sg.T; j0 += 32) {
+// keys j0 = first, first + stride, ... in chunks of 32: running max m, normaliser l, value sum o (this lane's head dim)
+__device__ __forceinline__ void nq1_fwd_chunks(const float* __restrict__ base, int ld, int d, int T, int first, int stride, float qv, int lane,
+                                               float& m, float& l, float& o) {
+  for (int j0 = first; j0 < T; j0 += stride) {
     const int j = j0 + lane;
     float4 k4[8];
-    if (j < sg.T) {
+    if (j < T) {
       const float4* kr = reinterpret_cast<const float4*>(base + (size_t)j * ld + d);
 #pragma unroll
       for (int c = 0; c < 8; ++c) k4[c] = __ldg(kr + c);
@@ -853,13 +845,13 @@ __global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restri
       sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 2), k4[c].z, sc);
       sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 3), k4[c].w, sc);
     }
-    if (j >= sg.T) sc = -INFINITY;
+    if (j >= T) sc = -INFINITY;
     const float mn = fmaxf(m, warp_max(sc));
-    const float p = (j < sg.T) ? expf(sc - mn) : 0.f;
+    const float p = (j < T) ? expf(sc - mn) : 0.f;
     const float corr = expf(m - mn);
     l = l * corr + warp_sum(p);
     o *= corr;
-    const int jmax = min(32, sg.T - j0);
+    const int jmax = min(32, T - j0);
 #pragma unroll 8
     for (int jj = 0; jj < 32; ++jj) {                    // fixed trip count: the value-row loads of a chunk are all in flight
       const float vv = (jj < jmax) ? __ldg(base + (size_t)(j0 + jj) * ld + 2 * d + lane) : 0.f;
@@ -867,35 +859,73 @@ __global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restri
     }
     m = mn;
   }
-  out[(size_t)sg.os * d + h * 32 + lane] = o / l;
-  if (lane == 0) lse[(size_t)sg.os * heads + h] = m + logf(l);
 }
 
-// Backward of the single-query attention; writes the q, k and v parts of every dqkv row of the slide (q part is zero
-// except at the special token), so the caller needs no zero-fill.
-__global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restrict__ qkv, const SegGrp seg,
-                                                           const float* __restrict__ out, const float* __restrict__ lse,
-                                                           const float* __restrict__ dout, float* __restrict__ dqkv, int d, int heads,
-                                                           int B) {
+constexpr int NQ1_WIDE_T = 1024;     // bags above this many tokens get a whole CTA per (slide, head) instead of one warp
+constexpr int NQ1_WIDE_WARPS = 32;
+
+__global__ void __launch_bounds__(128) attn_fwd_nq1_kernel(const float* __restrict__ qkv, const SegGrp seg,
+                                                           float* __restrict__ out, float* __restrict__ lse, int d, int heads, int B,
+                                                           int skip_above) {
   pdl_grid_sync();
   const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (wid >= B * heads) return;
   const int s = wid / heads, h = wid % heads;
   const Seg sg = seg_of(seg, s);
+  if (sg.T > skip_above) return;                         // the wide kernel's bag
   const int ld = 3 * d;
-  const float scale = rsqrtf(32.f);
   const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
-  float* dbase = dqkv + (size_t)sg.t0 * ld + h * 32;
-  const float qv = base[lane] * scale;
-  const float g = dout[(size_t)sg.os * d + h * 32 + lane];
-  const float Dq = warp_sum(g * out[(size_t)sg.os * d + h * 32 + lane]);
-  const float L = lse[(size_t)sg.os * heads + h];
+  const float qv = base[lane] * rsqrtf(32.f);
+  float m = -INFINITY, l = 0.f, o = 0.f;
+  nq1_fwd_chunks(base, ld, d, sg.T, 0, 32, qv, lane, m, l, o);
+  out[(size_t)sg.os * d + h * 32 + lane] = o / l;
+  if (lane == 0) lse[(size_t)sg.os * heads + h] = m + logf(l);
+}
+
+// Long bags (the 20 k-token bag of cfg 4): one CTA of 32 warps per (slide, head), the warps take interleaved 32-key chunks with
+// their own running (m, l, o) and are merged through shared memory.
+__global__ void __launch_bounds__(NQ1_WIDE_WARPS * 32) attn_fwd_nq1_wide_kernel(const float* __restrict__ qkv, const SegGrp seg,
+                                                                                float* __restrict__ out, float* __restrict__ lse, int d,
+                                                                                int heads) {
+  pdl_grid_sync();
+  const int s = blockIdx.x / heads, h = blockIdx.x % heads;
+  const Seg sg = seg_of(seg, s);
+  if (sg.T <= NQ1_WIDE_T) return;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int ld = 3 * d;
+  const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
+  const float qv = base[lane] * rsqrtf(32.f);
+  float m = -INFINITY, l = 0.f, o = 0.f;
+  nq1_fwd_chunks(base, ld, d, sg.T, w * 32, NQ1_WIDE_WARPS * 32, qv, lane, m, l, o);
+  __shared__ float sm[NQ1_WIDE_WARPS], sl[NQ1_WIDE_WARPS], so[NQ1_WIDE_WARPS][32];
+  if (lane == 0) { sm[w] = m; sl[w] = l; }
+  so[w][lane] = o;
+  __syncthreads();
+  if (w == 0) {
+    float M = -INFINITY;
+    for (int k = 0; k < NQ1_WIDE_WARPS; ++k) M = fmaxf(M, sm[k]);
+    float Ls = 0.f, O = 0.f;
+    for (int k = 0; k < NQ1_WIDE_WARPS; ++k) {           // fixed order: deterministic
+      const float c = expf(sm[k] - M);                   // warps that saw no key: exp(-inf) = 0
+      Ls = fmaf(sl[k], c, Ls); O = fmaf(so[k][lane], c, O);
+    }
+    out[(size_t)sg.os * d + h * 32 + lane] = O / Ls;
+    if (lane == 0) lse[(size_t)sg.os * heads + h] = M + logf(Ls);
+  }
+}
+
+// Backward of the single-query attention; writes the q, k and v parts of every dqkv row of the slide (q part is zero
+// except at the special token), so the caller needs no zero-fill.
+// keys j0 = first, first + stride, ...: dk, dv of every key row (and zeros in the q part of the non-query rows); returns this
+// lane's share of dq (unscaled)
+__device__ __forceinline__ float nq1_bwd_chunks(const float* __restrict__ base, float* __restrict__ dbase, int ld, int d, int T, int first,
+                                                int stride, float qv, float g, float Dq, float L, int lane) {
   float dq = 0.f;
-  for (int j0 = 0; j0 < sg.T; j0 += 32) {
+  for (int j0 = first; j0 < T; j0 += stride) {
     const int j = j0 + lane;
     float sc = 0.f, dp = 0.f;
     float4 k4[8], v4[8];
-    if (j < sg.T) {
+    if (j < T) {
       const float4* kr = reinterpret_cast<const float4*>(base + (size_t)j * ld + d);
       const float4* vr = reinterpret_cast<const float4*>(base + (size_t)j * ld + 2 * d);
 #pragma unroll
@@ -911,9 +941,9 @@ __global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restri
       sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 2), k4[c].z, sc); dp = fmaf(__shfl_sync(0xffffffffu, g, 4 * c + 2), v4[c].z, dp);
       sc = fmaf(__shfl_sync(0xffffffffu, qv, 4 * c + 3), k4[c].w, sc); dp = fmaf(__shfl_sync(0xffffffffu, g, 4 * c + 3), v4[c].w, dp);
     }
-    const float p = (j < sg.T) ? expf(sc - L) : 0.f;
+    const float p = (j < T) ? expf(sc - L) : 0.f;
     const float ds = p * (dp - Dq);
-    const int jmax = min(32, sg.T - j0);
+    const int jmax = min(32, T - j0);
 #pragma unroll 8
     for (int jj = 0; jj < 32; ++jj) {
       const float pj = __shfl_sync(0xffffffffu, p, jj), dsj = __shfl_sync(0xffffffffu, ds, jj);
@@ -926,7 +956,58 @@ __global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restri
       }
     }
   }
+  return dq;
+}
+
+__global__ void __launch_bounds__(128) attn_bwd_nq1_kernel(const float* __restrict__ qkv, const SegGrp seg,
+                                                           const float* __restrict__ out, const float* __restrict__ lse,
+                                                           const float* __restrict__ dout, float* __restrict__ dqkv, int d, int heads,
+                                                           int B, int skip_above) {
+  pdl_grid_sync();
+  const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (wid >= B * heads) return;
+  const int s = wid / heads, h = wid % heads;
+  const Seg sg = seg_of(seg, s);
+  if (sg.T > skip_above) return;
+  const int ld = 3 * d;
+  const float scale = rsqrtf(32.f);
+  const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
+  float* dbase = dqkv + (size_t)sg.t0 * ld + h * 32;
+  const float qv = base[lane] * scale;
+  const float g = dout[(size_t)sg.os * d + h * 32 + lane];
+  const float Dq = warp_sum(g * out[(size_t)sg.os * d + h * 32 + lane]);
+  const float L = lse[(size_t)sg.os * heads + h];
+  const float dq = nq1_bwd_chunks(base, dbase, ld, d, sg.T, 0, 32, qv, g, Dq, L, lane);
   dbase[lane] = dq * scale;
+}
+
+// ... and for the long bags: a CTA of 32 warps per (slide, head), warps over interleaved chunks, dq merged in a fixed order
+__global__ void __launch_bounds__(NQ1_WIDE_WARPS * 32) attn_bwd_nq1_wide_kernel(const float* __restrict__ qkv, const SegGrp seg,
+                                                                                const float* __restrict__ out, const float* __restrict__ lse,
+                                                                                const float* __restrict__ dout, float* __restrict__ dqkv,
+                                                                                int d, int heads) {
+  pdl_grid_sync();
+  const int s = blockIdx.x / heads, h = blockIdx.x % heads;
+  const Seg sg = seg_of(seg, s);
+  if (sg.T <= NQ1_WIDE_T) return;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int ld = 3 * d;
+  const float scale = rsqrtf(32.f);
+  const float* base = qkv + (size_t)sg.t0 * ld + h * 32;
+  float* dbase = dqkv + (size_t)sg.t0 * ld + h * 32;
+  const float qv = base[lane] * scale;
+  const float g = dout[(size_t)sg.os * d + h * 32 + lane];
+  const float Dq = warp_sum(g * out[(size_t)sg.os * d + h * 32 + lane]);
+  const float L = lse[(size_t)sg.os * heads + h];
+  const float dq = nq1_bwd_chunks(base, dbase, ld, d, sg.T, w * 32, NQ1_WIDE_WARPS * 32, qv, g, Dq, L, lane);
+  __shared__ float sd[NQ1_WIDE_WARPS][32];
+  sd[w][lane] = dq;
+  __syncthreads();                                        // (also orders every warp's zero-fill of row 0's q part before the write below)
+  if (w == 0) {
+    float t = 0.f;
+    for (int k = 0; k < NQ1_WIDE_WARPS; ++k) t += sd[k][lane];
+    dbase[lane] = t * scale;
+  }
 }
 }  // namespace
 
@@ -982,8 +1063,12 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
   PATHS_REQUIRE(!dr.thresh || (max_T < (1 << 24) && heads < 256), "attention dropout: bag of %d tokens / %d heads outside the hash's index range",
                 max_T, heads);
   if (d / heads == 32 && nq_mode && !dr.thresh) {    // (with dropout the short-bag / tiled kernels serve the single-query layer too)
-    pdl(attn_fwd_nq1_kernel, (B * heads + 3) / 4, 128, 0, st)(qkv, seg, out, lse, d, heads, B);
+    pdl(attn_fwd_nq1_kernel, (B * heads + 3) / 4, 128, 0, st)(qkv, seg, out, lse, d, heads, B, max_T > NQ1_WIDE_T ? NQ1_WIDE_T : 0x7fffffff);
     PATHS_LAUNCH_CK();
+    if (max_T > NQ1_WIDE_T) {
+      pdl(attn_fwd_nq1_wide_kernel, B * heads, NQ1_WIDE_WARPS * 32, 0, st)(qkv, seg, out, lse, d, heads);
+      PATHS_LAUNCH_CK();
+    }
     return 0;
   }
   static const bool no_tc = getenv("PATHS_B200_ATTN_SIMT") != nullptr;  // keep the SIMT short-bag kernels in the tensor-core modes
@@ -1035,8 +1120,12 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
   int skip_T = 0;
   const Drop dr = drop ? *drop : no_drop();
   if (d / heads == 32 && nq_mode && !dr.thresh) {    // (with dropout and nq_mode the caller zero-fills dqkv: only query rows get a dq)
-    pdl(attn_bwd_nq1_kernel, (B * heads + 3) / 4, 128, 0, st)(qkv, seg, out, lse, dout, dqkv, d, heads, B);
+    pdl(attn_bwd_nq1_kernel, (B * heads + 3) / 4, 128, 0, st)(qkv, seg, out, lse, dout, dqkv, d, heads, B, max_T > NQ1_WIDE_T ? NQ1_WIDE_T : 0x7fffffff);
     PATHS_LAUNCH_CK();
+    if (max_T > NQ1_WIDE_T) {
+      pdl(attn_bwd_nq1_wide_kernel, B * heads, NQ1_WIDE_WARPS * 32, 0, st)(qkv, seg, out, lse, dout, dqkv, d, heads);
+      PATHS_LAUNCH_CK();
+    }
     return 0;
   }
   static const bool no_tc = getenv("PATHS_B200_ATTN_SIMT") != nullptr;
