@@ -326,6 +326,8 @@ def main():
     from paths_b200.optim import FlatAdamW
     opt = FlatAdamW(model, lr=cfg.lr)
 
+    prefetcher = DevicePrefetcher([], dev)
+
     def run_e2e(steps, with_opt=False):
         # the reference's train-loop body (train.py:58-66) over host batches; the loader wrapper stages batch i+1 into HBM
         # (pinned host -> device, on a copy stream) while step i runs.  Every step copies its own inputs and reads its loss.
@@ -333,7 +335,8 @@ def main():
         if train:
             dp.attach(global_batch=B * world)
         try:
-            for b in DevicePrefetcher((batch for _ in range(steps)), dev):
+            prefetcher.loader = (batch for _ in range(steps))      # one prefetcher for the run, as around a DataLoader: its device
+            for b in prefetcher:                                   # ring is allocated once, not per epoch
                 if train:
                     opt.zero_grad()                                # train.py:59
                     hz, loss = inference_end2end(cfg.num_levels, cfg.top_k_patches, model, cfg.base_power, b, cfg.task)
