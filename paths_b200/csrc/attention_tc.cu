@@ -33,6 +33,10 @@ namespace {
 using namespace tc;
 
 constexpr int DH = 32;
+// V as the N = 32 operand of O = P V straight from its natural tile ([token rows][hi 32 | lo 32], read M-major: reduction index =
+// the rows, output index along the row, the lo half at descriptor start + 64 B) instead of a transposed copy written with 2-byte
+// stores -- the staging of the short-bag kernels is L1 / shared-memory bound (profiles/r2_attn_tc_full_672.ncu_summary.txt).
+constexpr bool V_NATURAL = true;
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
@@ -126,13 +130,14 @@ template <int NKB, int NP>
 struct FwdCfg {
   static constexpr int NT = 64 * NKB;                       // threads = token rows of the class
   static constexpr int NAT = NT * 128;                      // natural tile bytes
-  static constexpr int VT_PLANE = NKB * 4096;               // transposed V, one plane
+  static constexpr int VT_PLANE = NKB * 4096;               // transposed V, one plane (V_NATURAL == false)
   static constexpr int P_PLANE = NKB * NT * 128;            // score tile, one plane
   static constexpr int OFF_Q = 0, OFF_K = NAT, OFF_VT = 2 * NAT;
   // 64-row class: P (hi, lo: 2 x 8 KB) takes the place of Q | K once S is done, and the 64 rows an M = 128 operand reads past a
   // block land in the next plane / the V tile -- 25 KB per CTA, eight CTAs per SM.  128-row class: P has its own 64 KB.
-  static constexpr int OFF_P = NKB == 1 ? 0 : OFF_VT + NP * VT_PLANE;
-  static constexpr int SMEM = (NKB == 1 ? OFF_VT + NP * VT_PLANE : OFF_P + NP * P_PLANE) + 1024;
+  static constexpr int V_BYTES = V_NATURAL ? NAT : NP * VT_PLANE;
+  static constexpr int OFF_P = NKB == 1 ? 0 : OFF_VT + V_BYTES;
+  static constexpr int SMEM = (NKB == 1 ? OFF_VT + V_BYTES : OFF_P + NP * P_PLANE) + 1024;
   static constexpr int TMEM_COLS = 64 * NKB;                // S; O reuses its columns
 };
 
@@ -174,7 +179,8 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
 #pragma unroll
       for (int c = 0; c < DH; ++c) z[c] = 0.f;
     }
-    store_transposed<NP>(smem + cfg::OFF_VT, cfg::VT_PLANE, t, z);     // rows past the bag: zeros (0 * garbage must stay 0)
+    if (V_NATURAL) store_natural(smem + cfg::OFF_VT, t, z);            // rows past the bag: zeros (0 * garbage must stay 0)
+    else store_transposed<NP>(smem + cfg::OFF_VT, cfg::VT_PLANE, t, z);
   }
   fence_proxy_async();
   tc_fence_before();
@@ -228,15 +234,21 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   __syncthreads();
   tc_fence_after();
   if (t == 0) {                                              // O = P V : M = 128, N = 32, K = NT keys (S's columns are free now)
-    constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0);
+    constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0), idesc_bm = umma_idesc(128, DH, 0, 1);
     uint32_t acc = 0;
 #pragma unroll
     for (int kb = 0; kb < NKB; ++kb)
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks) {
-        const uint32_t a = sP + kb * (NT * 128), b = sVt + kb * 4096;
-        mma_terms<NP>(tmem_base, desc_k(a, ks * 32), desc_k(a + cfg::P_PLANE, ks * 32), desc_k(b, ks * 32), desc_k(b + cfg::VT_PLANE, ks * 32),
-                      idesc, &acc);
+        const uint32_t a = sP + kb * (NT * 128);
+        if (V_NATURAL) {
+          const uint32_t b = sVt + (kb * 64 + ks * 16) * 128;              // 16 token rows of the natural tile
+          mma_terms<NP>(tmem_base, desc_k(a, ks * 32), desc_k(a + cfg::P_PLANE, ks * 32), desc_m(b, 0, 8192), desc_m(b + 64, 0, 8192), idesc_bm, &acc);
+        } else {
+          const uint32_t b = sVt + kb * 4096;
+          mma_terms<NP>(tmem_base, desc_k(a, ks * 32), desc_k(a + cfg::P_PLANE, ks * 32), desc_k(b, ks * 32), desc_k(b + cfg::VT_PLANE, ks * 32),
+                        idesc, &acc);
+        }
       }
     umma_commit(&bar);
   }
