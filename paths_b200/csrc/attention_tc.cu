@@ -272,15 +272,12 @@ template <int NKB, int NP>
 struct BwdCfg {
   static constexpr int NT = 64 * NKB;
   static constexpr int NAT = NT * 128;
-  static constexpr int T_PLANE = NKB * 4096;                // a transposed operand, one plane
   static constexpr int S_PLANE = NKB * NT * 128;            // a score tile (P or dS), one plane
-  // region 0: natural Q, K, V, dO (operands of S and dP); once those products are done the same bytes (and what follows) hold P, dS
-  static constexpr int R0 = (4 * NAT > 2 * NP * S_PLANE) ? 4 * NAT : 2 * NP * S_PLANE;
+  // natural Q, K, V, dO: K-major operands of S and dP, and (K, Q, dO) the M-major N = 32 operands of dQ, dK, dV -- no transposed
+  // copies; then the score tiles P, dS (+ the 64 rows an M = 128 operand of the 64-row class reads past the last block)
   static constexpr int OFF_Q = 0, OFF_K = NAT, OFF_V = 2 * NAT, OFF_DO = 3 * NAT;
-  static constexpr int OFF_P = 0, OFF_DS = NP * S_PLANE;
-  static constexpr int OFF_KT = R0 + 8192;                  // (slack: an M = 128 operand of the 64-row class reads 64 rows past a block)
-  static constexpr int OFF_QT = OFF_KT + NP * T_PLANE, OFF_DOT = OFF_QT + NP * T_PLANE;
-  static constexpr int SMEM = OFF_DOT + NP * T_PLANE + 1024;
+  static constexpr int OFF_P = 4 * NAT, OFF_DS = OFF_P + NP * S_PLANE;
+  static constexpr int SMEM = OFF_DS + NP * S_PLANE + (NKB == 1 ? 8192 : 0) + 1024;
   static constexpr int TMEM_COLS = 128 * NKB;               // S | dP; dQ, dK, dV reuse the columns
 };
 
@@ -322,23 +319,17 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
         store_natural(smem + cfg::OFF_K, t, y);
         store_natural(smem + cfg::OFF_V, t, z);
       }
-      store_transposed<NP>(smem + cfg::OFF_QT, cfg::T_PLANE, t, x);
-      store_transposed<NP>(smem + cfg::OFF_KT, cfg::T_PLANE, t, y);
       load_row32(dout + orow, x);
       load_row32(out + orow, y);
 #pragma unroll
       for (int c = 0; c < DH; ++c) Dq = fmaf(x[c], y[c], Dq);
       store_natural(smem + cfg::OFF_DO, t, x);
-      store_transposed<NP>(smem + cfg::OFF_DOT, cfg::T_PLANE, t, x);
       L = lse[(size_t)(sg.t0 + t) * heads + h];
     } else {
 #pragma unroll
       for (int c = 0; c < DH; ++c) x[c] = 0.f;
       zero_natural(smem + cfg::OFF_Q, t); zero_natural(smem + cfg::OFF_K, t); zero_natural(smem + cfg::OFF_V, t);
       zero_natural(smem + cfg::OFF_DO, t);
-      store_transposed<NP>(smem + cfg::OFF_QT, cfg::T_PLANE, t, x);
-      store_transposed<NP>(smem + cfg::OFF_KT, cfg::T_PLANE, t, x);
-      store_transposed<NP>(smem + cfg::OFF_DOT, cfg::T_PLANE, t, x);
     }
   }
   fence_proxy_async();
@@ -395,31 +386,30 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   __syncthreads();
   tc_fence_after();
   if (t == 0) {
-    constexpr uint32_t idk = umma_idesc(128, DH, 0, 0);      // A K-major
-    constexpr uint32_t idm = umma_idesc(128, DH, 1, 0);      // A M-major (the transposed products)
-    const uint32_t sP = s0 + cfg::OFF_P, sDS = s0 + cfg::OFF_DS, sKt = s0 + cfg::OFF_KT, sQt = s0 + cfg::OFF_QT, sDOt = s0 + cfg::OFF_DOT;
+    constexpr uint32_t idk = umma_idesc(128, DH, 0, 1);      // A K-major, B M-major
+    constexpr uint32_t idm = umma_idesc(128, DH, 1, 1);      // A M-major (the transposed products), B M-major
+    const uint32_t sP = s0 + cfg::OFF_P, sDS = s0 + cfg::OFF_DS, sK = s0 + cfg::OFF_K, sQ = s0 + cfg::OFF_Q, sDO = s0 + cfg::OFF_DO;
     uint32_t acc = 0;                                        // dQ[q, c] = sum_j dS[q, j] K[j, c]        -> columns [0, 32)
 #pragma unroll
     for (int kb = 0; kb < NKB; ++kb)
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks) {
-        const uint32_t a = sDS + kb * (NT * 128), b = sKt + kb * 4096;
-        mma_terms<NP>(tmem_base, desc_k(a, ks * 32), desc_k(a + cfg::S_PLANE, ks * 32), desc_k(b, ks * 32), desc_k(b + cfg::T_PLANE, ks * 32), idk,
-                      &acc);
+        const uint32_t a = sDS + kb * (NT * 128), b = sK + (kb * 64 + ks * 16) * 128;      // 16 key rows of the natural tile
+        mma_terms<NP>(tmem_base, desc_k(a, ks * 32), desc_k(a + cfg::S_PLANE, ks * 32), desc_m(b, 0, 8192), desc_m(b + 64, 0, 8192), idk, &acc);
       }
     acc = 0;                                                 // dK[j, c] = sum_q dS[q, j] (scale Q)[q, c]   -> columns [32, 64)
 #pragma unroll
     for (int ks = 0; ks < NT / 16; ++ks) {
-      const uint32_t b = sQt + (ks >> 2) * 4096;
-      mma_terms<NP>(tmem_base + 32, desc_m(sDS, ks, NT * 128), desc_m(sDS + cfg::S_PLANE, ks, NT * 128), desc_k(b, (ks & 3) * 32),
-                    desc_k(b + cfg::T_PLANE, (ks & 3) * 32), idm, &acc);
+      const uint32_t b = sQ + ks * 16 * 128;
+      mma_terms<NP>(tmem_base + 32, desc_m(sDS, ks, NT * 128), desc_m(sDS + cfg::S_PLANE, ks, NT * 128), desc_m(b, 0, 8192), desc_m(b + 64, 0, 8192),
+                    idm, &acc);
     }
     acc = 0;                                                 // dV[j, c] = sum_q P[q, j] dO[q, c]           -> columns [64, 96)
 #pragma unroll
     for (int ks = 0; ks < NT / 16; ++ks) {
-      const uint32_t b = sDOt + (ks >> 2) * 4096;
-      mma_terms<NP>(tmem_base + 64, desc_m(sP, ks, NT * 128), desc_m(sP + cfg::S_PLANE, ks, NT * 128), desc_k(b, (ks & 3) * 32),
-                    desc_k(b + cfg::T_PLANE, (ks & 3) * 32), idm, &acc);
+      const uint32_t b = sDO + ks * 16 * 128;
+      mma_terms<NP>(tmem_base + 64, desc_m(sP, ks, NT * 128), desc_m(sP + cfg::S_PLANE, ks, NT * 128), desc_m(b, 0, 8192), desc_m(b + 64, 0, 8192),
+                    idm, &acc);
     }
     umma_commit(&bar);
   }
