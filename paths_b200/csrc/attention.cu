@@ -1054,7 +1054,7 @@ int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, in
   return attn_fwd_grp(qkv, seg_single(seg, B), out, lse, d, heads, max_T, nq_mode, st);
 }
 int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st,
-                 const Drop* drop, int tc_passes) {
+                 const Drop* drop, int tc_passes, int* cls) {
   PATHS_REQUIRE(d % heads == 0 && d / heads <= MAXDH, "attention: head_dim %d unsupported (max %d)", d / heads, MAXDH);
   const int B = seg.n * seg.B;                       // virtual slides
   if (B <= 0) return 0;
@@ -1074,7 +1074,7 @@ int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, in
   static const bool no_tc = getenv("PATHS_B200_ATTN_SIMT") != nullptr;  // keep the SIMT short-bag kernels in the tensor-core modes
   static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;   // experimental pair-per-row kernels (not faster: off)
   if (tc_passes && !no_tc && !nq_mode && attn_tc_supported(d, heads)) {  // bags of at most 128 tokens on the tensor cores (attention_tc.cu)
-    return attn_tc_fwd(tc_passes, qkv, seg, out, lse, d, heads, max_T, st, dr);      // every bag length (short classes + tiled)
+    return attn_tc_fwd(tc_passes, qkv, seg, out, lse, d, heads, max_T, st, dr, cls);      // every bag length (short classes + tiled)
   } else if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;
@@ -1114,7 +1114,7 @@ int attn_bwd(const float* qkv, const int* seg, const float* out, const float* ls
   return attn_bwd_grp(qkv, seg_single(seg, B), out, lse, dout, dqkv, Dvec, d, heads, max_T, nq_mode, st);
 }
 int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
-                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop, int tc_passes) {
+                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop, int tc_passes, int* cls) {
   const int B = seg.n * seg.B;
   if (B <= 0) return 0;
   int skip_T = 0;
@@ -1131,7 +1131,7 @@ int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const fl
   static const bool no_tc = getenv("PATHS_B200_ATTN_SIMT") != nullptr;
   static const bool use_tq = getenv("PATHS_B200_ATTN_TQ") != nullptr;
   if (tc_passes && !no_tc && !nq_mode && attn_tc_supported(d, heads)) {
-    return attn_tc_bwd(tc_passes, qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, max_T, st, dr);
+    return attn_tc_bwd(tc_passes, qkv, seg, out, lse, dout, dqkv, Dvec, d, heads, max_T, st, dr, cls);
   } else if (use_tq && d / heads == 32 && d % 4 == 0 && !nq_mode && !dr.thresh) {
     const int nkc = max_T <= 32 ? 1 : max_T <= 64 ? 2 : max_T <= 96 ? 3 : 4;
     int r = 0;

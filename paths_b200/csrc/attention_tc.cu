@@ -70,6 +70,65 @@ __device__ __forceinline__ void zero_natural(uint8_t* tile, int r) {
 #pragma unroll
   for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(row + (c << 4)) = make_uint4(0, 0, 0, 0);
 }
+// cooperative staging of an NT-row natural tile by NT threads from rows src + r * ld (32 floats each): item i = (row i / 4, 8-float
+// group i % 4), so a warp reads 8 whole 128-byte rows per pass (four passes) instead of 32 rows 16 bytes at a time
+template <int NT>
+__device__ __forceinline__ void stage_natural(uint8_t* tile, const float* __restrict__ src, int ld, int T, int t, float mul) {
+  float4 a[4], b[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int i = t + k * NT, r = i >> 2, g = i & 3;
+    if (r < T) {
+      const float4* p = reinterpret_cast<const float4*>(src + (size_t)r * ld + g * 8);
+      a[k] = __ldg(p); b[k] = __ldg(p + 1);
+    } else {
+      a[k] = make_float4(0.f, 0.f, 0.f, 0.f); b[k] = a[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int i = t + k * NT, r = i >> 2, g = i & 3;
+    const float x[8] = {a[k].x * mul, a[k].y * mul, a[k].z * mul, a[k].w * mul, b[k].x * mul, b[k].y * mul, b[k].z * mul, b[k].w * mul};
+    uint4 hi, lo;
+    split8(x, hi, lo);
+    uint8_t* row = tile + (r >> 3) * 1024 + (r & 7) * 128;
+    *reinterpret_cast<uint4*>(row + ((g ^ (r & 7)) << 4)) = hi;
+    *reinterpret_cast<uint4*>(row + (((g + 4) ^ (r & 7)) << 4)) = lo;
+  }
+}
+// the same for dO, with rowdot[r] = sum_c dO[r][c] * O[r][c] left in shared memory (the four lanes of a row are adjacent)
+template <int NT>
+__device__ __forceinline__ void stage_natural_dot(uint8_t* tile, const float* __restrict__ src, const float* __restrict__ oth, int ld,
+                                                  int T, int t, float* rowdot) {
+  float4 a[4], b[4], oa[4], ob[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int i = t + k * NT, r = i >> 2, g = i & 3;
+    if (r < T) {
+      const float4* p = reinterpret_cast<const float4*>(src + (size_t)r * ld + g * 8);
+      const float4* q = reinterpret_cast<const float4*>(oth + (size_t)r * ld + g * 8);
+      a[k] = __ldg(p); b[k] = __ldg(p + 1); oa[k] = __ldg(q); ob[k] = __ldg(q + 1);
+    } else {
+      a[k] = make_float4(0.f, 0.f, 0.f, 0.f); b[k] = a[k]; oa[k] = a[k]; ob[k] = a[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int i = t + k * NT, r = i >> 2, g = i & 3;
+    const float x[8] = {a[k].x, a[k].y, a[k].z, a[k].w, b[k].x, b[k].y, b[k].z, b[k].w};
+    float dot = a[k].x * oa[k].x;
+    dot = fmaf(a[k].y, oa[k].y, dot); dot = fmaf(a[k].z, oa[k].z, dot); dot = fmaf(a[k].w, oa[k].w, dot);
+    dot = fmaf(b[k].x, ob[k].x, dot); dot = fmaf(b[k].y, ob[k].y, dot); dot = fmaf(b[k].z, ob[k].z, dot); dot = fmaf(b[k].w, ob[k].w, dot);
+    dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+    dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+    if (g == 0) rowdot[r] = dot;
+    uint4 hi, lo;
+    split8(x, hi, lo);
+    uint8_t* row = tile + (r >> 3) * 1024 + (r & 7) * 128;
+    *reinterpret_cast<uint4*>(row + ((g ^ (r & 7)) << 4)) = hi;
+    *reinterpret_cast<uint4*>(row + (((g + 4) ^ (r & 7)) << 4)) = lo;
+  }
+}
 // transposed planes: element (head_dim c, token j) of plane p at  p * plane_bytes + (j / 64) * 4096 + swizzled (row c, column j % 64)
 template <int NP>
 __device__ __forceinline__ void store_transposed(uint8_t* base, int plane_bytes, int j, const float* x) {
@@ -144,14 +203,21 @@ struct FwdCfg {
 // ------------------------------------------------------------------------------------------------------------------ forward
 template <int NKB, int NP, bool DROP>
 __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __restrict__ qkv, const SegGrp seg, float* __restrict__ out,
-                                                               float* __restrict__ lse, int d, int heads, const Drop dr) {
+                                                               float* __restrict__ lse, int d, int heads, const Drop dr,
+                                                               const int* __restrict__ list) {
   pdl_grid_sync();
   using cfg = FwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
   const int h = blockIdx.x;
-  const Seg sg = seg_of(seg, blockIdx.y);
-  const int T = sg.T;
-  if (T > NT || (NKB == 2 && T <= 64)) return;              // the other class's launch (or the tiled kernels) serves this bag
+  // list (attn_tc_classify_kernel): the bags of this class, served by a grid of resident CTAs; without one, CTA y = bag y
+  int n_items = gridDim.y;
+  if (list) {
+    n_items = list[0];
+    if ((int)blockIdx.y >= n_items) return;
+  } else {
+    const int T0 = seg_of(seg, blockIdx.y).T;
+    if (T0 > NT || (NKB == 2 && T0 <= 64)) return;          // the other class's launch (or the tiled kernels) serves this bag
+  }
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -162,25 +228,15 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
 
   const float scale = rsqrtf((float)DH);
   const int ld = 3 * d;
+#pragma unroll 1
+  for (int it = blockIdx.y; it < n_items; it += gridDim.y) {
+  const Seg sg = seg_of(seg, list ? list[2 + it] : it);
+  const int T = sg.T;
   {
-    float x[DH], y[DH], z[DH];
-    if (t < T) {
-      const float* rp = qkv + (size_t)(sg.t0 + t) * ld + h * DH;
-      load_row32(rp, x);
-      load_row32(rp + d, y);
-      load_row32(rp + 2 * d, z);
-#pragma unroll
-      for (int c = 0; c < DH; ++c) x[c] *= scale;
-      store_natural(smem + cfg::OFF_Q, t, x);
-      store_natural(smem + cfg::OFF_K, t, y);
-    } else {
-      zero_natural(smem + cfg::OFF_Q, t);
-      zero_natural(smem + cfg::OFF_K, t);
-#pragma unroll
-      for (int c = 0; c < DH; ++c) z[c] = 0.f;
-    }
-    if (V_NATURAL) store_natural(smem + cfg::OFF_VT, t, z);            // rows past the bag: zeros (0 * garbage must stay 0)
-    else store_transposed<NP>(smem + cfg::OFF_VT, cfg::VT_PLANE, t, z);
+    const float* rp = qkv + (size_t)sg.t0 * ld + h * DH;
+    stage_natural<NT>(smem + cfg::OFF_Q, rp, ld, T, t, scale);
+    stage_natural<NT>(smem + cfg::OFF_K, rp + d, ld, T, t, 1.f);
+    stage_natural<NT>(smem + cfg::OFF_VT, rp + 2 * d, ld, T, t, 1.f);   // rows past the bag: zeros (0 * garbage must stay 0)
   }
   fence_proxy_async();
   tc_fence_before();
@@ -264,7 +320,8 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
+  }                                                          // next bag of the list: same barrier phases (two commits per bag)
+  if (warp == 0) tmem_dealloc(tmem_slot, cfg::TMEM_COLS);
 }
 
 // ----------------------------------------------------------------------------------------------------------------- backward
@@ -284,14 +341,20 @@ struct BwdCfg {
 template <int NKB, int NP, bool DROP>
 __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __restrict__ qkv, const SegGrp seg, const float* __restrict__ out,
                                                                const float* __restrict__ lse, const float* __restrict__ dout,
-                                                               float* __restrict__ dqkv, int d, int heads, const Drop dr) {
+                                                               float* __restrict__ dqkv, int d, int heads, const Drop dr,
+                                                               const int* __restrict__ list) {
   pdl_grid_sync();
   using cfg = BwdCfg<NKB, NP>;
   constexpr int NT = cfg::NT;
   const int h = blockIdx.x;
-  const Seg sg = seg_of(seg, blockIdx.y);
-  const int T = sg.T;
-  if (T > NT || (NKB == 2 && T <= 64)) return;
+  int n_items = gridDim.y;
+  if (list) {
+    n_items = list[0];
+    if ((int)blockIdx.y >= n_items) return;
+  } else {
+    const int T0 = seg_of(seg, blockIdx.y).T;
+    if (T0 > NT || (NKB == 2 && T0 <= 64)) return;
+  }
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -302,40 +365,25 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
 
   const float scale = rsqrtf((float)DH);
   const int ld = 3 * d;
-  float Dq = 0.f, L = 0.f;
+  __shared__ float s_rowdot[NT];
+#pragma unroll 1
+  for (int it = blockIdx.y; it < n_items; it += gridDim.y) {
+  const Seg sg = seg_of(seg, list ? list[2 + it] : it);
+  const int T = sg.T;
   {
-    float x[DH], y[DH];
-    if (t < T) {
-      const float* rp = qkv + (size_t)(sg.t0 + t) * ld + h * DH;
-      const size_t orow = (size_t)(sg.t0 + t) * d + h * DH;
-      {
-        float z[DH];
-        load_row32(rp, x);
-        load_row32(rp + d, y);
-        load_row32(rp + 2 * d, z);
-  #pragma unroll
-        for (int c = 0; c < DH; ++c) x[c] *= scale;
-        store_natural(smem + cfg::OFF_Q, t, x);
-        store_natural(smem + cfg::OFF_K, t, y);
-        store_natural(smem + cfg::OFF_V, t, z);
-      }
-      load_row32(dout + orow, x);
-      load_row32(out + orow, y);
-#pragma unroll
-      for (int c = 0; c < DH; ++c) Dq = fmaf(x[c], y[c], Dq);
-      store_natural(smem + cfg::OFF_DO, t, x);
-      L = lse[(size_t)(sg.t0 + t) * heads + h];
-    } else {
-#pragma unroll
-      for (int c = 0; c < DH; ++c) x[c] = 0.f;
-      zero_natural(smem + cfg::OFF_Q, t); zero_natural(smem + cfg::OFF_K, t); zero_natural(smem + cfg::OFF_V, t);
-      zero_natural(smem + cfg::OFF_DO, t);
-    }
+    const float* rp = qkv + (size_t)sg.t0 * ld + h * DH;
+    const size_t o0 = (size_t)sg.t0 * d + h * DH;
+    stage_natural<NT>(smem + cfg::OFF_Q, rp, ld, T, t, scale);
+    stage_natural<NT>(smem + cfg::OFF_K, rp + d, ld, T, t, 1.f);
+    stage_natural<NT>(smem + cfg::OFF_V, rp + 2 * d, ld, T, t, 1.f);
+    stage_natural_dot<NT>(smem + cfg::OFF_DO, dout + o0, out + o0, d, T, t, s_rowdot);
   }
+  const float L = t < T ? lse[(size_t)(sg.t0 + t) * heads + h] : 0.f;
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  const float Dq = s_rowdot[t];
   const uint32_t tmem_base = tmem_slot;
   const uint32_t s0 = smem_u32(smem);
   if (t == 0) {                                              // S = (scale Q) K^T -> columns [0, NT);  dP = dO V^T -> [NT, 2 NT)
@@ -427,7 +475,8 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem_base, cfg::TMEM_COLS);
+  }
+  if (warp == 0) tmem_dealloc(tmem_slot, cfg::TMEM_COLS);
 }
 
 // =====================================================================================================================
@@ -891,22 +940,69 @@ int set_smem_once(K kern, int bytes, bool* done) {
   return 0;
 }
 
+// CTAs of `kern` the device holds at once (occupancy x SMs), cached in *slots
+template <typename K>
+int resident_slots(K kern, int threads, int smem, int* slots) {
+  if (*slots) return 0;
+  int dev = 0, sms = 0, per_sm = 0;
+  PATHS_CK(cudaGetDevice(&dev));
+  PATHS_CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  PATHS_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+  *slots = sms * (per_sm > 0 ? per_sm : 1);
+  return 0;
+}
+// grid rows (CTAs per head): one per bag without a class list; with one, as many as stay resident -- they walk the list
+inline int list_rows(const int* list, int bags, int resident, int heads) {
+  if (!list) return bags;
+  const int rows = resident / heads > 0 ? resident / heads : 1;
+  return rows < bags ? rows : bags;
+}
+
+// Bags of the 65..128-token class (list[0] of them, list[2 ...]) and of the tiled class (list[1], list[2 + bags ...]) of a grouped
+// launch: the bag lengths live on the device, and a grid over every bag spends more time retiring the CTAs of the other classes
+// (each holds its shared memory until its segment offsets arrive) than computing.  One block; order is irrelevant to the results.
+__global__ void __launch_bounds__(1024) attn_tc_classify_kernel(const SegGrp seg, int* __restrict__ list) {
+  pdl_grid_sync();
+  __shared__ int n_mid, n_long;
+  if (threadIdx.x == 0) { n_mid = 0; n_long = 0; }
+  __syncthreads();
+  const int bags = seg.n * seg.B;
+  for (int sv = threadIdx.x; sv < bags; sv += blockDim.x) {
+    const int T = seg_of(seg, sv).T;
+    if (T > 128) list[2 + bags + atomicAdd(&n_long, 1)] = sv;
+    else if (T > 64) list[2 + atomicAdd(&n_mid, 1)] = sv;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) { list[0] = n_mid; list[1] = n_long; }
+}
+int classify(const SegGrp& seg, int* list, cudaStream_t st) {
+  pdl(attn_tc_classify_kernel, 1, 1024, 0, st)(seg, list);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+
 template <int NKB, int NP, bool DROP>
-int launch_fwd(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, cudaStream_t st, const Drop& dr) {
+int launch_fwd(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, cudaStream_t st, const Drop& dr, const int* list) {
   static bool done = false;
+  static int resident = 0;
   auto kern = attn_tc_fwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, FwdCfg<NKB, NP>::SMEM, &done)) return r;
-  pdl(kern, dim3(heads, seg.n * seg.B), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, d, heads, dr);
+  if (int r = resident_slots(kern, 64 * NKB, FwdCfg<NKB, NP>::SMEM, &resident)) return r;
+  pdl(kern, dim3(heads, list_rows(list, seg.n * seg.B, resident, heads)), 64 * NKB, FwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, d, heads, dr,
+                                                                                                             list);
   PATHS_LAUNCH_CK();
   return 0;
 }
 template <int NKB, int NP, bool DROP>
 int launch_bwd(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, int d, int heads,
-               cudaStream_t st, const Drop& dr) {
+               cudaStream_t st, const Drop& dr, const int* list) {
   static bool done = false;
+  static int resident = 0;
   auto kern = attn_tc_bwd_kernel<NKB, NP, DROP>;
   if (int r = set_smem_once(kern, BwdCfg<NKB, NP>::SMEM, &done)) return r;
-  pdl(kern, dim3(heads, seg.n * seg.B), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, dout, dqkv, d, heads, dr);
+  if (int r = resident_slots(kern, 64 * NKB, BwdCfg<NKB, NP>::SMEM, &resident)) return r;
+  pdl(kern, dim3(heads, list_rows(list, seg.n * seg.B, resident, heads)), 64 * NKB, BwdCfg<NKB, NP>::SMEM, st)(qkv, seg, out, lse, dout, dqkv, d,
+                                                                                                             heads, dr, list);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -952,11 +1048,14 @@ bool attn_tc_supported(int d, int heads) { return heads > 0 && d % heads == 0 &&
   } while (0)
 
 int attn_tc_fwd(int passes, const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, cudaStream_t st,
-                const Drop& dr) {
+                const Drop& dr, int* cls) {
   PATHS_REQUIRE(attn_tc_supported(d, heads) && (passes == 1 || passes == 3), "attn_tc_fwd: head_dim must be 32");
   if (seg.n * seg.B <= 0) return 0;
-  ATTN_TC_DISPATCH(launch_fwd, 1, qkv, seg, out, lse, d, heads, st, dr);
-  if (max_T > 64) ATTN_TC_DISPATCH(launch_fwd, 2, qkv, seg, out, lse, d, heads, st, dr);
+  if (cls && max_T > 64)
+    if (int r = classify(seg, cls, st)) return r;
+  const int* none = nullptr;
+  ATTN_TC_DISPATCH(launch_fwd, 1, qkv, seg, out, lse, d, heads, st, dr, none);
+  if (max_T > 64) ATTN_TC_DISPATCH(launch_fwd, 2, qkv, seg, out, lse, d, heads, st, dr, cls);
   if (max_T > 128) {                                         // long bags: tiled over keys (attn_tc_fwd_long_kernel)
     int r;
     if (passes == 3) r = dr.thresh ? launch_fwd_long<2, true>(qkv, seg, out, lse, d, heads, max_T, st, dr) : launch_fwd_long<2, false>(qkv, seg, out, lse, d, heads, max_T, st, dr);
@@ -966,11 +1065,14 @@ int attn_tc_fwd(int passes, const float* qkv, const SegGrp& seg, float* out, flo
   return 0;
 }
 int attn_tc_bwd(int passes, const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* dvec,
-                int d, int heads, int max_T, cudaStream_t st, const Drop& dr) {
+                int d, int heads, int max_T, cudaStream_t st, const Drop& dr, int* cls) {
   PATHS_REQUIRE(attn_tc_supported(d, heads) && (passes == 1 || passes == 3), "attn_tc_bwd: head_dim must be 32");
   if (seg.n * seg.B <= 0) return 0;
-  ATTN_TC_DISPATCH(launch_bwd, 1, qkv, seg, out, lse, dout, dqkv, d, heads, st, dr);
-  if (max_T > 64) ATTN_TC_DISPATCH(launch_bwd, 2, qkv, seg, out, lse, dout, dqkv, d, heads, st, dr);
+  if (cls && max_T > 64)
+    if (int r = classify(seg, cls, st)) return r;
+  const int* none = nullptr;
+  ATTN_TC_DISPATCH(launch_bwd, 1, qkv, seg, out, lse, dout, dqkv, d, heads, st, dr, none);
+  if (max_T > 64) ATTN_TC_DISPATCH(launch_bwd, 2, qkv, seg, out, lse, dout, dqkv, d, heads, st, dr, cls);
   if (max_T > 128) {                                         // long bags: dQ per query tile, then dK / dV per key tile
     int r;
     if (passes == 3) r = dr.thresh ? launch_bwd_long<2, true>(qkv, seg, out, lse, dout, dqkv, dvec, d, heads, max_T, st, dr)

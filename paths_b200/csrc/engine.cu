@@ -124,6 +124,7 @@ struct Level {
   float *A1b, *Fob;                                      // ... and their [B, d] counterparts (last layer: special-token rows only)
   float *ga, *gb, *gO, *gt, *dqkv, *dHf, *Dvec;          // backward, token-shaped
   float* Dvecb;                                          // dO.O of the single-query (last) layer, slide-shaped
+  int* attn_cls;                                         // bag-class list of the set this level leads (rowops.cuh: attn_cls_ints)
   float *gab, *gbb, *gOb, *dHfb;                         // backward, slide-shaped (last layer)
   float *dFl, *dy3s;                                     // [B, d]: d loss / d F_l, gradient entering the last decoder layer
 };
@@ -308,6 +309,7 @@ size_t carve(paths_engine* e, char* base) {
     v.parent_local = b.take<int>(cap);
     v.sel = b.take<int>((size_t)B * (v.kcap > 0 ? v.kcap : 1)); v.sel_count = b.take<int>(B);
     v.child_of = b.take<int>(4 * cap);
+    v.attn_cls = b.take<int>(attn_cls_ints(dm.L * B));
     v.X = b.take<float>(cap * D); v.G = b.take<float>(dm.lstm ? cap * (3 * C + D) : 4); v.Cn = b.take<float>(cap * C);
     v.Pt = b.take<float>(cap * D); v.H = b.take<float>(cap * D); v.Y = b.take<float>(cap * D);
     v.UV = b.take<float>(cap * (I + d)); v.alpha = b.take<float>(cap);
@@ -674,7 +676,7 @@ int decoder_forward(paths_engine* e, const DecSet& S, cudaStream_t st) {
                b2 = PL(S, [&](int l) { return P[l].layer[j].b2; });
     Drop dA;
     if (drop) dA = set_drop(e, S, j, DROP_ATTN);
-    RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr, attn_tc_passes(dm)));
+    RUN(attn_fwd_grp(y.qkv, S.sg, y.O, y.lse, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr, attn_tc_passes(dm), e->lv[S.lv[0]].attn_cls));
     RUN(gemm_nt_set(e, S, gr, y.O, d, [&](int l) { return P[l].layer[j].Wo; }, d, 0, A1, d, PL0(), d, d, 0, st, &pO));
     // dropout1(W_o a + b_o), dropout2(b_cross) and dropout3(W_2 h + b_2) are applied to the branch INCLUDING its bias before
     // the residual sum; the cross-attention branch (a bias only) is materialised in Fo, free until the FFN writes it
@@ -840,7 +842,7 @@ int decoder_backward(paths_engine* e, const DecSet& S, int ws_slot, cudaStream_t
     Drop dA;
     if (drop) dA = set_drop(e, S, j, DROP_ATTN);
     RUN(attn_bwd_grp(y.qkv, S.sg, y.O, y.lse, gO, v0.dqkv, last ? v0.Dvecb : v0.Dvec, d, dm.heads, S.max_T, last ? 1 : 0, st, drop ? &dA : nullptr,
-                     attn_tc_passes(dm)));
+                     attn_tc_passes(dm), e->lv[S.lv[0]].attn_cls));
     OpPl p3 = oppl(e->dpl3), pT = oppl(saved ? e->svT[j] : e->dplD[0]);
     pT.ready = saved;
     const MutL dbqkv = ML(S, [&](int l) { return Gl(l).bqkv; });

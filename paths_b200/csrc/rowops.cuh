@@ -103,16 +103,18 @@ __device__ __forceinline__ Seg seg_of(const SegGrp& sg, int sv) {
 // (head, slide), longer ones tiled.  passes = 3: Q K^T, P V and the four backward products as three-term bf16 splits
 // (fp32-parity); 1: plain bf16.  dvec: [tokens, heads] scratch (D = dO . O of the long bags).
 bool attn_tc_supported(int d, int heads);
+// cls (optional): attn_cls_ints(bags) ints of scratch -- the bags of 65..128 tokens are listed there first and served by a resident grid
+inline size_t attn_cls_ints(int bags) { return 2 + 2 * (size_t)bags; }
 int attn_tc_fwd(int passes, const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, cudaStream_t st,
-                const Drop& dr);
+                const Drop& dr, int* cls = nullptr);
 int attn_tc_bwd(int passes, const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* dvec,
-                int d, int heads, int max_T, cudaStream_t st, const Drop& dr);
+                int d, int heads, int max_T, cudaStream_t st, const Drop& dr, int* cls = nullptr);
 // drop (optional): dropout of the attention probabilities, hashed on (level-local query row, head << 24 | key index)
 // tc_passes: 0 = SIMT fp32 kernels only; 3 / 1 = short bags on the tensor cores (attn_tc_*) in split / plain bf16
 int attn_fwd_grp(const float* qkv, const SegGrp& seg, float* out, float* lse, int d, int heads, int max_T, int nq_mode, cudaStream_t st,
-                 const Drop* drop = nullptr, int tc_passes = 0);
+                 const Drop* drop = nullptr, int tc_passes = 0, int* cls = nullptr);
 int attn_bwd_grp(const float* qkv, const SegGrp& seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
-                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop = nullptr, int tc_passes = 0);
+                 int heads, int max_T, int nq_mode, cudaStream_t st, const Drop* drop = nullptr, int tc_passes = 0, int* cls = nullptr);
 int attn_fwd(const float* qkv, const int* seg, float* out, float* lse, int d, int heads, int B, int max_T, int nq_mode, cudaStream_t st);
 bool attn_bwd_writes_all(int d, int heads);
 int attn_bwd(const float* qkv, const int* seg, const float* out, const float* lse, const float* dout, float* dqkv, float* Dvec, int d,
