@@ -183,11 +183,17 @@ inline IdxL idxl1(const int* p) { IdxL l; for (int i = 0; i < kMaxGroups; ++i) l
 // Grouped contraction: group g reads/writes rows of the concatenated activation buffers per `rows`, contracts against the
 // g-th member of a stacked packed weight (wlev[g] = index inside the stack), adds bias[g]; the weight-gradient form (TN)
 // reduces over the group's rows into cout[g].
+// RowAdd: rows gathered into the NT epilogue before bias / activation: C[i, :] = act(acc + add[idx[i], :] + bias), idx[i] < 0 = none.
+// What the gate contraction of a child level uses for the h_parent half of [x || h_parent] . W^T: the four children of a patch
+// share that product, so it is computed once per selected parent and added here (interface.py:49).
+struct RowAdd { const float* p; const int* idx; int ld; };
+inline RowAdd no_row_add() { RowAdd a; a.p = nullptr; a.idx = nullptr; a.ld = 0; return a; }
 struct GemmGrp {
   Grp rows;
   int wlev[kMaxGroups];
   const float* bias[kMaxGroups];
   float* cout[kMaxGroups];
+  RowAdd add{nullptr, nullptr, 0};
 };
 
 // ---- dropout (nn.Transformer(dropout=p) in training mode, model/aggregator.py:25-33) ------------------------------------

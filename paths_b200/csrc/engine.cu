@@ -41,7 +41,7 @@ int gemm_tn_tc(int passes, const float* P, int ldp, const RowSrc& Q, float* C, i
 bool gemm_tc_supported_nt(const RowSrc& A, const float* B, int ldb, int b_kn, int ldc, int N, int K);
 bool gemm_tc_supported_tn(int ldp, const RowSrc& Q, int ldc, int NI, int NJ);
 int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
-                 const int* M_dev, int N, int K, int flags, cudaStream_t st);
+                 const int* M_dev, int N, int K, int flags, cudaStream_t st, const RowAdd* add = nullptr);
 int gemm_tn_tc_p(int passes, const Planes& P, int p_col0, const Planes& Q, int q_col0, float* C, int ldc, int M_host, const int* M_dev, int NI,
                  int NJ, cudaStream_t st);
 int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Planes& dst, int col0, bool want_lo, cudaStream_t st);
@@ -80,10 +80,10 @@ int gemm_tn(int prec, const float* P, int ldp, const RowSrc& Q, float* C, int ld
 
 // Contractions on activations that may already exist as tensor-core planes (written by their producer kernel).
 int gemm_nt_act(int prec, const Act& A, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host, const int* M_dev,
-                int N, int K, int flags, cudaStream_t st) {
+                int N, int K, int flags, cudaStream_t st, const RowAdd* add = nullptr) {
   if (prec != PREC_FP32_SIMT && A.pl.p)
-    return gemm_nt_tc_p(prec == PREC_BF16X3_TC ? 3 : 1, A.pl, A.col0, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
-  PATHS_REQUIRE(A.f, "gemm_nt: activation has neither fp32 rows nor planes");
+    return gemm_nt_tc_p(prec == PREC_BF16X3_TC ? 3 : 1, A.pl, A.col0, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st, add);
+  PATHS_REQUIRE(A.f && !add, "gemm_nt: activation has neither fp32 rows nor planes (row addends need the planes form)");
   return gemm_nt(prec, row_src(A.f + A.col0, A.ld, K), B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
 }
 int gemm_tn_act(int prec, const Act& P, const Act& Q, const RowSrc* Qsrc, float* C, int ldc, int M_host, const int* M_dev, int NI, int NJ,
@@ -116,6 +116,14 @@ struct Level {
   float *xhf, *rsf, *z, *F, *logits, *dlogits, *dHrow, *dCrow;
   float *dFc;                        // slide_ctx_mode "concat": d loss / d F_l written by the last level's head backward
   Planes AxhP, CnP, YP;              // tensor-core operand planes written by the producers: [x || h_parent], c', Y
+  // shared-parent gate contraction (rowops.cu: parent_slots_kernel): W_h h_parent once per selected parent of level l - 1 ("slot")
+  bool shared;                       // this level (l >= 1) runs it: tensor-core modes, fewer parent slots than child rows
+  bool tables_ok;                    // the slot tables describe the level's current rows (built by do_select; dropped when a caller takes
+                                     // the level's ROW_PARENT buffer to fill the tables by hand, as the level API of runtime.py does)
+  bool ran_pl, ran_shared;           // what the last lstm_forward of the level used: its backward (and its parent's) must match
+  int *slot4, *sel_rows;             // as the parent level: [cap, 4] slot of a row with surviving children; [B * kcap] row of a slot
+  int* add_idx;                      // as the child level: [cap] slot of the row's parent
+  Planes HselP;                      // as the child level: h of the selected parents, [B * kcap(l-1), D] planes (kept for dW)
   // decoder buffers.  Every token-shaped ([tokens, *]) and slide-shaped ([B, *]) decoder buffer of the L levels is ONE allocation
   // with the levels back to back (level l at rows tok_off[l] resp. l * B): lv[0]'s pointer is the base of the concatenated
   // buffer, lv[l]'s the level's slice, so the same kernels serve one level or, in a single grouped launch, any set of levels.
@@ -159,6 +167,8 @@ struct paths_engine {
   cudaEvent_t ev_tok[PATHS_MAX_LEVELS], ev_z[PATHS_MAX_LEVELS], ev_head[PATHS_MAX_LEVELS], ev_dtok[PATHS_MAX_LEVELS];
   bool have_streams;
   Planes dGP, dPP, dUVP;                                 // gradient planes written by the pointwise backward kernels
+  float* Gh;                                             // shared-parent gate term W_h h_parent, [slots, 3C + D] (one level at a time)
+  Planes dGsumP;                                         // ... and the child-summed gate gradient of the slots
   float *hazards, *loss, *loss_per, *risk;
   int *overflow, *slide_cnt, *slide_fb;
   // host-visible copy of the overflow flag: copied to pinned memory right after the LAST select of a forward pass (the rest of
@@ -216,7 +226,7 @@ size_t carve(paths_engine* e, char* base) {
   const paths_dims_t& dm = e->dm;
   const int B = e->B, D = dm.D, C = dm.C, d = dm.d, I = dm.I, F = dm.F;
   Bump b{base, 0};
-  int maxcap = 0;
+  int maxcap = 0, max_slots = 0;
   // uniform region stride (a multiple of 64 rows): a level's region can be zero-filled up to the longest level's row count
   // without touching its neighbour (what the grouped weight-gradient contraction on TMA-fed planes needs)
   int S = 64;
@@ -310,6 +320,7 @@ size_t carve(paths_engine* e, char* base) {
     v.sel = b.take<int>((size_t)B * (v.kcap > 0 ? v.kcap : 1)); v.sel_count = b.take<int>(B);
     v.child_of = b.take<int>(4 * cap);
     v.attn_cls = b.take<int>(attn_cls_ints(dm.L * B));
+    v.slot4 = b.take<int>(4 * cap); v.sel_rows = b.take<int>((size_t)B * (v.kcap > 0 ? v.kcap : 1)); v.add_idx = b.take<int>(cap);
     v.X = b.take<float>(cap * D); v.G = b.take<float>(dm.lstm ? cap * (3 * C + D) : 4); v.Cn = b.take<float>(cap * C);
     v.Pt = b.take<float>(cap * D); v.H = b.take<float>(cap * D); v.Y = b.take<float>(cap * D);
     v.UV = b.take<float>(cap * (I + d)); v.alpha = b.take<float>(cap);
@@ -317,12 +328,17 @@ size_t carve(paths_engine* e, char* base) {
     v.dHrow = b.take<float>(cap * D); v.dCrow = b.take<float>(cap * C);
     v.dFc = b.take<float>((size_t)B * d);
     if (dm.lstm) {
-      v.AxhP = planes_at(b.take<char>(planes_bytes(v.cap, 2 * D)), v.cap, 2 * D);
+      // shared-parent levels keep x only (the h half lives once per slot in HselP)
+      const int xcols = (v.shared || l == 0) ? D : 2 * D;
+      v.AxhP = planes_at(b.take<char>(planes_bytes(v.cap, xcols)), v.cap, xcols);
       v.CnP = planes_at(b.take<char>(planes_bytes(v.cap, C)), v.cap, C);
       v.YP = planes_at(b.take<char>(planes_bytes(v.cap, D)), v.cap, D);
-      if (!base) { v.AxhP.p = nullptr; v.CnP.p = nullptr; v.YP.p = nullptr; }
+      const int slots = v.shared ? B * e->lv[l - 1].kcap : 0;
+      v.HselP = slots ? planes_at(b.take<char>(planes_bytes(slots, D)), slots, D) : no_planes();
+      if (slots > max_slots) max_slots = slots;
+      if (!base) { v.AxhP.p = nullptr; v.CnP.p = nullptr; v.YP.p = nullptr; v.HselP.p = nullptr; }
     } else {
-      v.AxhP = v.CnP = v.YP = no_planes();
+      v.AxhP = v.CnP = v.YP = v.HselP = no_planes();
     }
   }
   e->maxcap = maxcap; e->maxtok = maxcap + B;
@@ -332,10 +348,14 @@ size_t carve(paths_engine* e, char* base) {
   e->dUV = b.take<float>(mc * (I + d));
   if (dm.lstm) {
     e->dGP = planes_at(b.take<char>(planes_bytes(maxcap, 3 * C + D)), maxcap, 3 * C + D);
+    e->Gh = max_slots ? b.take<float>((size_t)max_slots * (3 * C + D)) : nullptr;
+    e->dGsumP = max_slots ? planes_at(b.take<char>(planes_bytes(max_slots, 3 * C + D)), max_slots, 3 * C + D) : no_planes();
+    if (!base) e->dGsumP.p = nullptr;
     e->dPP = planes_at(b.take<char>(planes_bytes(maxcap, D)), maxcap, D);
     e->dUVP = planes_at(b.take<char>(planes_bytes(maxcap, I + d)), maxcap, I + d);
   } else {
-    e->dGP = e->dPP = e->dUVP = no_planes();
+    e->dGP = e->dPP = e->dUVP = e->dGsumP = no_planes();
+    e->Gh = nullptr;
   }
   e->hazards = b.take<float>((size_t)B * dm.nl); e->loss = b.take<float>(1); e->loss_per = b.take<float>(B);
   e->risk = b.take<float>(B);
@@ -356,7 +376,7 @@ size_t carve(paths_engine* e, char* base) {
     e->tc_scratch_each = tc_scratch_bytes(e->maxtok, cols);
     e->tc_scratch[0] = b.take<char>(e->tc_scratch_each);
     e->tc_scratch[1] = b.take<char>(e->tc_scratch_each);
-    const int tn_shapes[][2] = {{3 * C + D, 2 * D}, {D, C}, {C, D}, {I + d, D}, {I, D}, {d, D}, {3 * d, d}, {d, d}, {F, d}, {d, F}};
+    const int tn_shapes[][2] = {{3 * C + D, 2 * D}, {3 * C + D, D}, {D, C}, {C, D}, {I + d, D}, {I, D}, {d, D}, {3 * d, d}, {d, d}, {F, d}, {d, F}};
     size_t tnb = 0;
     for (const auto& sh : tn_shapes) {
       const size_t need = tn_workspace_bytes(sh[0], sh[1], e->maxtok, 1);
@@ -395,6 +415,13 @@ void fill_level_meta(paths_engine* e, const int32_t* caps, const int32_t* maxseg
     const int K = e->dm.K[l];
     v.kcap = (l == e->dm.L - 1) ? 1 : (K < 0 ? maxseg[l] : (K < maxseg[l] ? K : maxseg[l]));
   }
+  // shared-parent gate contraction (decided on the dimensions alone: the precision mode can change during the engine's life):
+  // it pays when a level has fewer parent slots than rows, which is what top-K selection with four children per patch gives
+  static const bool off = getenv("PATHS_B200_NO_SHARED_PARENT") != nullptr;
+  const paths_dims_t& dm = e->dm;
+  const bool dims_ok = dm.lstm && dm.D % 8 == 0 && dm.C % 8 == 0 && (dm.I + dm.d) % 8 == 0;
+  for (int l = 0; l < dm.L; ++l)
+    e->lv[l].shared = !off && dims_ok && l >= 1 && (long)e->B * e->lv[l - 1].kcap <= (long)e->lv[l].cap;
 }
 
 void bind(Params& P, const float* base, const int64_t* off, const paths_dims_t& dm) {
@@ -483,12 +510,24 @@ int lstm_forward(paths_engine* e, int l, cudaStream_t st) {
     // ---- LSTM cell step for every patch (interface.py:49-56).  In the tensor-core modes every contraction operand of this
     // block lives as bf16 planes written by its producer: [x || h_parent] by one split pass that also performs the parent
     // gather (kept for the weight gradient), c' and Y by the gate kernels.
-    const bool pl = planes_mode(dm);
+    // (a shared-parent level whose tables were filled by hand has no slot tables and only x-wide planes: fp32-row operands)
+    const bool pl = planes_mode(dm) && !(has_parent && v.shared && !v.tables_ok);
     const int lo = prec == PREC_BF16X3_TC ? 1 : 0;
     const int Kx = has_parent ? 2 * D : D;
     RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
-    if (pl) RUN(split_rows(Axh, M, Md, Kx, v.AxhP, 0, lo != 0, st));
-    {
+    const bool shp = pl && has_parent && v.shared;       // W_h h_parent once per selected parent, added by the gate epilogue
+    v.ran_pl = pl; v.ran_shared = shp;
+    if (shp) {
+      Level& pv = e->lv[l - 1];
+      const int slots = B * pv.kcap;
+      RUN(split_rows(row_src(pv.H, D, D, pv.sel_rows), slots, nullptr, D, v.HselP, 0, lo != 0, st));
+      RUN(split_rows(row_src(v.X, D, D), M, Md, D, v.AxhP, 0, lo != 0, st));
+      ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
+      RUN(gemm_nt_act(prec, act(nullptr, 0, v.HselP), e->P.Wg + D, 2 * D, 0, e->Gh, ldg, nullptr, slots, nullptr, ldg, D, 0, st));
+      RowAdd ra; ra.p = e->Gh; ra.idx = v.add_idx; ra.ld = ldg;
+      RUN(gemm_nt_act(prec, act(nullptr, 0, v.AxhP), e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, D, GEMM_GATES | (C << 8), st, &ra));
+    } else {
+      if (pl) RUN(split_rows(Axh, M, Md, Kx, v.AxhP, 0, lo != 0, st));
       ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
       // tensor-core path: the epilogue applies the gate non-linearities, G reaches HBM activated (written once)
       if (pl) RUN(gemm_nt_act(prec, act(nullptr, 0, v.AxhP), e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, Kx, GEMM_GATES | (C << 8), st));
@@ -906,7 +945,7 @@ int lstm_backward(paths_engine* e, int l, cudaStream_t st) {
     }
     return 0;
   }
-  const bool pl = planes_mode(dm);
+  const bool pl = v.ran_pl;
   const int lo = prec == PREC_BF16X3_TC ? 1 : 0;
   const Planes none = no_planes();
   RUN(imp_tok_bwd(dtok, v.UV, v.alpha, p.w2, v.row_slide, pl ? nullptr : e->dUV, pl ? e->dUVP : none, lo, W_(g.b1), W_(g.w2), W_(g.b2),
@@ -918,7 +957,9 @@ int lstm_backward(paths_engine* e, int l, cudaStream_t st) {
   // ---- LSTM cell (the pointwise kernels sum the state gradients of a row's children (slide.py:318-329) as they read them, and
   //      accumulate the bias gradients of mem_to_out and of the four gates)
   const int* kids = has_children ? v.child_of : nullptr;
-  RUN(lstm_point2_bwd(e->dY, has_children ? e->lv[l + 1].dHrow : nullptr, kids, v.Pt, v.G, pl ? nullptr : e->dP, pl ? e->dPP : none, pl ? nullptr : e->dG,
+  // (a shared-parent child level leaves ONE dH row per slot: slot4 is the child table that reads it)
+  const int* kids_h = has_children ? (e->lv[l + 1].ran_shared ? v.slot4 : v.child_of) : nullptr;
+  RUN(lstm_point2_bwd(e->dY, has_children ? e->lv[l + 1].dHrow : nullptr, kids_h, v.Pt, v.G, pl ? nullptr : e->dP, pl ? e->dPP : none, pl ? nullptr : e->dG,
                       pl ? e->dGP : none, W_(e->Gr.bmo), W_(e->Gr.bg) + 3 * C, lo, D, C, M, Md, st));
   const Act aP = act(e->dP, D, pl ? e->dPP : none), aCn = act(v.Cn, C, pl ? v.CnP : none);
   RUN(gemm_nt_act(prec, aP, e->P.Wmo, C, 1, e->dCn, C, nullptr, M, Md, C, D, 0, st));
@@ -927,6 +968,21 @@ int lstm_backward(paths_engine* e, int l, cudaStream_t st) {
                       has_parent ? v.row_parent : nullptr, pl ? nullptr : e->dG, pl ? e->dGP : none, has_parent ? v.dCrow : nullptr,
                       W_(e->Gr.bg), lo, D, C, M, Md, st));
   const Act aG = act(e->dG, ldg, pl ? e->dGP : none);
+  if (v.ran_shared) {
+    // dH_parent = (sum of dG over the parent's children) W_h and dW_h = (that sum)^T h_parent: slot-shaped, not row-shaped
+    Level& pv = e->lv[l - 1];
+    const int slots = e->B * pv.kcap;
+    RUN(child_sum_planes(e->dGP, pv.child_of, pv.sel_rows, slots, ldg, e->dGsumP, lo, st));
+    const Act aGs = act(nullptr, 0, e->dGsumP);
+    {
+      ProfScope ps(e, PATHS_PROF_GATES_DH, st);
+      RUN(gemm_nt_act(prec, aGs, e->P.Wg + D, 2 * D, 1, v.dHrow, D, nullptr, slots, nullptr, D, ldg, 0, st));
+    }
+    ProfScope ps(e, PATHS_PROF_GATES_DW, st);
+    RUN(gemm_tn_act(prec, aG, act(nullptr, 0, v.AxhP), nullptr, W_(e->Gr.Wg), 2 * D, M, Md, ldg, D, st));
+    RUN(gemm_tn_act(prec, aGs, act(nullptr, 0, v.HselP), nullptr, W_(e->Gr.Wg) + D, 2 * D, slots, nullptr, ldg, D, st));
+    return 0;
+  }
   if (has_parent) {
     ProfScope ps(e, PATHS_PROF_GATES_DH, st);
     RUN(gemm_nt_act(prec, aG, e->P.Wg + D, 2 * D, 1, v.dHrow, D, nullptr, M, Md, D, ldg, 0, st));
@@ -965,6 +1021,10 @@ int do_select(paths_engine* e, int l, cudaStream_t st) {
   pdl(tseg_kernel, (e->B + 255) / 256, 256, 0, st)(n.seg, n.tseg, e->B);
   PATHS_LAUNCH_CK(); e->launches++;
   RUN(gather_rows(e->store.grid_ptr, e->store.gh, l + 1, dm.L, e->slide_ids, n.row_slide, n.row_xy, n.X, dm.D, n.cap, n.count, st, e->store.bf16));
+  n.tables_ok = n.shared;
+  if (n.shared)
+    RUN(parent_slots(v.child_of, v.count, v.cap, v.sel, v.sel_count, e->B, v.kcap, n.row_slide, n.row_parent, n.parent_local, n.count, n.cap,
+                     v.slot4, v.sel_rows, n.add_idx, st));
   return 0;
 }
 
@@ -1458,7 +1518,7 @@ int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, siz
     case PATHS_BUF_TSEG: p = v.tseg; n = B * i4; break;
     case PATHS_BUF_ROW_SLIDE: p = v.row_slide; n = cap * i4; break;
     case PATHS_BUF_ROW_XY: p = v.row_xy; n = 2 * cap * i4; break;
-    case PATHS_BUF_ROW_PARENT: p = v.row_parent; n = cap * i4; break;
+    case PATHS_BUF_ROW_PARENT: p = v.row_parent; n = cap * i4; v.tables_ok = false; break;
     case PATHS_BUF_PARENT_LOCAL: p = v.parent_local; n = cap * i4; break;
     case PATHS_BUF_SEL: p = v.sel; n = B * (size_t)(v.kcap > 0 ? v.kcap : 1) * i4; break;
     case PATHS_BUF_SEL_COUNT: p = v.sel_count; n = B * i4; break;

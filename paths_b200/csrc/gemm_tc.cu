@@ -532,6 +532,14 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           if (i >= oi_lim || nn >= oj_lim) continue;
           float* cp = Cb + (size_t)i * ldo + nn;
           if (!SK) {
+            if (gg.add.p) {                                  // shared-parent term of the gate pre-activations (RowAdd)
+              const int ai = __ldg(gg.add.idx + i);
+              if (ai >= 0) {
+                const float* ap = gg.add.p + (size_t)ai * gg.add.ld + nn;
+                if (nn + 3 < oj_lim) { const float4 a4 = __ldg(reinterpret_cast<const float4*>(ap)); w.x += a4.x; w.y += a4.y; w.z += a4.z; w.w += a4.w; }
+                else { w.x += ap[0]; if (nn + 1 < oj_lim) w.y += ap[1]; if (nn + 2 < oj_lim) w.z += ap[2]; }
+              }
+            }
             w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
             if (flags & GEMM_RELU) { w.x = fmaxf(w.x, 0.f); w.y = fmaxf(w.y, 0.f); w.z = fmaxf(w.z, 0.f); w.w = fmaxf(w.w, 0.f); }
             if (flags & GEMM_GATES) {                        // column ranges are multiples of 4: one branch per float4
@@ -848,7 +856,8 @@ int split_rows(const RowSrc& A, int M_host, const int* M_dev, int K, const Plane
 
 // C[M,N] (+)= act(A . B^T + bias); A either as planes (columns [a_col0, a_col0 + K)) or as fp32 rows converted in-kernel
 static int nt_impl(int passes, const Planes* A, int a_col0, const RowSrc* Asrc, const float* B, int ldb, int b_kn, float* C, int ldc,
-                   const float* bias, int M_host, const int* M_dev, int N, int K, int flags, cudaStream_t st, const GemmGrp* grp = nullptr) {
+                   const float* bias, int M_host, const int* M_dev, int N, int K, int flags, cudaStream_t st, const GemmGrp* grp = nullptr,
+                   const RowAdd* add = nullptr) {
   if (M_host <= 0 || N <= 0) return 0;
   GemmGrp gg;
   if (grp) gg = *grp;
@@ -856,6 +865,8 @@ static int nt_impl(int passes, const Planes* A, int a_col0, const RowSrc* Asrc, 
     gg.rows = grp_single(M_host, M_dev);
     for (int i = 0; i < kMaxGroups; ++i) { gg.wlev[i] = 0; gg.bias[i] = nullptr; gg.cout[i] = nullptr; }
     gg.bias[0] = bias;
+    gg.add = add ? *add : no_row_add();
+    PATHS_REQUIRE(!gg.add.p || (gg.add.idx && gg.add.ld % 4 == 0 && !(reinterpret_cast<uintptr_t>(gg.add.p) & 15)), "gemm_nt_tc: bad row addend");
   }
   const Packed* pk; int r0, c0;
   {
@@ -897,8 +908,8 @@ static int nt_impl(int passes, const Planes* A, int a_col0, const RowSrc* Asrc, 
 }
 
 int gemm_nt_tc_p(int passes, const Planes& A, int a_col0, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias, int M_host,
-                 const int* M_dev, int N, int K, int flags, cudaStream_t st) {
-  return nt_impl(passes, &A, a_col0, nullptr, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
+                 const int* M_dev, int N, int K, int flags, cudaStream_t st, const RowAdd* add) {
+  return nt_impl(passes, &A, a_col0, nullptr, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st, nullptr, add);
 }
 
 // fp32 rows qualify for the in-kernel conversion when every 8-element chunk lies inside one 16-byte-aligned source row
@@ -913,7 +924,7 @@ int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, f
   if (cvt_ok(A)) return nt_impl(passes, nullptr, 0, &A, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
   Planes pa;
   if (int r = split_to_scratch(0, A, M_host, M_dev, K, passes == 3, &pa, st)) return r;
-  return gemm_nt_tc_p(passes, pa, 0, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st);
+  return gemm_nt_tc_p(passes, pa, 0, B, ldb, b_kn, C, ldc, bias, M_host, M_dev, N, K, flags, st, nullptr);
 }
 
 // Stream-K plan of a weight-gradient contraction: CTAs and workspace slots per CTA.

@@ -1314,6 +1314,72 @@ inline int row_grid(int M) { int g = (M + WPB - 1) / WPB; if (g > 8 * kNumSMs) g
 
 }  // namespace
 
+// ---- shared-parent form of the gate contraction (interface.py:49: gates = W [x || h_parent]) -------------------------------------
+// The (up to) four children of a selected patch see the same h_parent, so W_h h_parent is one product per SELECTED PARENT ("slot"
+// s * kcap + position in the slide's selected list), not per child.  Index tables of one level pair, one launch:
+//   slot4[m]   (rows of the parent level)  = (slot of row m, -1, -1, -1) if any child of m survived, else all -1 -- the layout
+//                                            lstm_point2_bwd's child gather reads, so it picks up ONE row of the slot-shaped dH table
+//   sel_rows[i] (slots)                    = the parent row of slot i, -1 for the holes of slides with fewer selected rows
+//   add_idx[r] (rows of the child level)   = slot of row r's parent, -1 for the rows of a fallback slide (no parent, slide.py:336-352)
+__global__ void __launch_bounds__(256) parent_slots_kernel(const int* __restrict__ child_of, const int* __restrict__ count, int cap,
+                                                           const int* __restrict__ sel, const int* __restrict__ sel_count, int B, int kcap,
+                                                           const int* __restrict__ n_row_slide, const int* __restrict__ n_row_parent,
+                                                           const int* __restrict__ n_parent_local, const int* __restrict__ n_count, int n_cap,
+                                                           int* __restrict__ slot4, int* __restrict__ sel_rows, int* __restrict__ add_idx) {
+  pdl_grid_sync();
+  const int M = min(count[0], cap), Mn = min(n_count[0], n_cap), slots = B * kcap;
+  const int total = max(max(M, Mn), slots);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    if (i < M) {
+      const int4 ch = __ldg(reinterpret_cast<const int4*>(child_of) + i);
+      const int kid = ch.x >= 0 ? ch.x : ch.y >= 0 ? ch.y : ch.z >= 0 ? ch.z : ch.w;
+      const int slot = (kid >= 0 && kid < Mn) ? n_row_slide[kid] * kcap + n_parent_local[kid] : -1;
+      reinterpret_cast<int4*>(slot4)[i] = make_int4(slot, -1, -1, -1);
+    }
+    if (i < slots) {
+      const int sl = i / kcap, j = i - sl * kcap;
+      sel_rows[i] = j < sel_count[sl] ? sel[i] : -1;
+    }
+    if (i < Mn) add_idx[i] = n_row_parent[i] >= 0 ? n_row_slide[i] * kcap + n_parent_local[i] : -1;
+  }
+}
+// dGsum[slot] = sum of dG over the surviving children of the slot's parent row, planes in, planes out (hi + lo summed in fp32 and
+// split again); every slot row is written (holes and the padding rows up to a multiple of 64 as zeros).
+__global__ void __launch_bounds__(256) child_sum_planes_kernel(const Planes src, const int* __restrict__ child_of, const int* __restrict__ sel_rows,
+                                                               int slots, int cols, Planes dst, int want_lo) {
+  pdl_grid_sync();
+  const int rows_w = planes_rows_to_write(dst, slots);
+  for (int i = blockIdx.x; i < rows_w; i += gridDim.x) {
+    int4 ch = make_int4(-1, -1, -1, -1);
+    if (i < slots) {
+      const int pr = __ldg(sel_rows + i);
+      if (pr >= 0) ch = __ldg(reinterpret_cast<const int4*>(child_of) + pr);
+    }
+    const int kid[4] = {ch.x, ch.y, ch.z, ch.w};
+    for (int k = 4 * threadIdx.x; k < cols; k += 4 * blockDim.x) {
+      uint2 hv[4], lv[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        hv[q] = lv[q] = make_uint2(0u, 0u);
+        if (kid[q] >= 0) {
+          hv[q] = __ldg(reinterpret_cast<const uint2*>(src.p + (size_t)kid[q] * src.ldp + k));
+          if (want_lo) lv[q] = __ldg(reinterpret_cast<const uint2*>(src.p + ((size_t)src.rows + kid[q]) * src.ldp + k));
+        }
+      }
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        // bf16 -> fp32 is a 16-bit shift; hi + lo is exact in fp32 (lo has at most 8 significant bits below hi's last)
+        acc.x += __uint_as_float(hv[q].x << 16) + __uint_as_float(lv[q].x << 16);
+        acc.y += __uint_as_float(hv[q].x & 0xffff0000u) + __uint_as_float(lv[q].x & 0xffff0000u);
+        acc.z += __uint_as_float(hv[q].y << 16) + __uint_as_float(lv[q].y << 16);
+        acc.w += __uint_as_float(hv[q].y & 0xffff0000u) + __uint_as_float(lv[q].y & 0xffff0000u);
+      }
+      planes_store4(dst, i, k, acc, want_lo != 0);
+    }
+  }
+}
+
 // ---- host launchers -----------------------------------------------------------------------------------------
 int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, const int* slide_ids, const int* row_slide,
                 const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st, int bf16) {
@@ -1366,6 +1432,26 @@ int lstm_point1_bwd(const float* dCn, const float* dCc, const int* child_of, con
   const int R = 256 / (C / 4);
   int g = (M_host + 64 + R - 1) / R; if (g > 3 * kNumSMs) g = 3 * kNumSMs;
   pdl(lstm_point1_bwd_kernel, g, 256, 0, st)(dCn, dCc, child_of, G, Cprev, parent, dG, dGP, dCrow, db_g, want_lo, D, C, M_host, M_dev);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int parent_slots(const int* child_of, const int* count, int cap, const int* sel, const int* sel_count, int B, int kcap, const int* n_row_slide,
+                 const int* n_row_parent, const int* n_parent_local, const int* n_count, int n_cap, int* slot4, int* sel_rows, int* add_idx,
+                 cudaStream_t st) {
+  int total = cap > n_cap ? cap : n_cap;
+  if (B * kcap > total) total = B * kcap;
+  int g = (total + 255) / 256; if (g > 4 * kNumSMs) g = 4 * kNumSMs;
+  pdl(parent_slots_kernel, g, 256, 0, st)(child_of, count, cap, sel, sel_count, B, kcap, n_row_slide, n_row_parent, n_parent_local, n_count, n_cap,
+                                          slot4, sel_rows, add_idx);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+int child_sum_planes(const Planes& src, const int* child_of, const int* sel_rows, int slots, int cols, const Planes& dst, int want_lo,
+                     cudaStream_t st) {
+  PATHS_REQUIRE(src.p && dst.p && cols % 4 == 0 && cols <= src.ldp && cols <= dst.ldp && slots <= dst.rows, "child_sum_planes: bad planes");
+  if (slots <= 0) return 0;
+  int g = slots + 64; if (g > 8 * kNumSMs) g = 8 * kNumSMs;
+  pdl(child_sum_planes_kernel, g, 256, 0, st)(src, child_of, sel_rows, slots, cols, dst, want_lo);
   PATHS_LAUNCH_CK();
   return 0;
 }

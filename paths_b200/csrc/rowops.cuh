@@ -31,6 +31,12 @@ int lstm_point2_bwd(const float* dY, const float* dHc, const int* child_of, cons
                     float* dG, const Planes& dGP, float* db_mo, float* db_o, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st);
 int lstm_point1_bwd(const float* dCn, const float* dCc, const int* child_of, const float* G, const float* Cprev, const int* parent, float* dG,
                     const Planes& dGP, float* dCrow, float* db_g, int want_lo, int D, int C, int M_host, const int* M_dev, cudaStream_t st);
+// shared-parent gate contraction (rowops.cu: parent_slots_kernel, child_sum_planes_kernel)
+int parent_slots(const int* child_of, const int* count, int cap, const int* sel, const int* sel_count, int B, int kcap, const int* n_row_slide,
+                 const int* n_row_parent, const int* n_parent_local, const int* n_count, int n_cap, int* slot4, int* sel_rows, int* add_idx,
+                 cudaStream_t st);
+int child_sum_planes(const Planes& src, const int* child_of, const int* sel_rows, int slots, int cols, const Planes& dst, int want_lo,
+                     cudaStream_t st);
 int parent_sum(const int* child_of, const float* dHrow, const float* dCrow, float* dHc, float* dCc, int D, int C, int M_host,
                const int* M_dev, cudaStream_t st);
 int imp_tok_fwd(float* UV, const float* b1, const float* w2, const float* b2, const float* bin, const float* div, const int* row_slide,
