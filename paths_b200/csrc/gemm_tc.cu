@@ -509,10 +509,34 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         Cb = C; ldo = ldc; oi_lim = a_olim(u); oj_lim = OJ; ci0 = i0; cj0 = j0;
       }
       const bool vec = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+      // RowAdd: this lane's 8 output rows are the same for every column chunk of the tile -- their slots are read once, and each
+      // chunk's addends are requested before the accumulator chunk is fetched and transposed (the gather latency hides behind it)
+      const bool has_add = !SK && gg.add.p != nullptr;
+      int ai[8];
+      if (has_add) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int i = ci0 + q * 32 + 4 * k + orow;
+          ai[k] = i < oi_lim ? __ldg(gg.add.idx + i) : -1;
+        }
+      }
 #pragma unroll 1
       for (int c0 = 0; c0 < BN / 2; c0 += 32) {
         uint32_t r[32];
         const int col = half * (BN / 2) + c0;
+        float4 a4[8];
+        if (has_add) {
+          const int nn = cj0 + col + oq * 4;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            a4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ai[k] >= 0 && nn < oj_lim) {
+              const float* ap = gg.add.p + (size_t)ai[k] * gg.add.ld + nn;
+              if (nn + 3 < oj_lim) a4[k] = __ldg(reinterpret_cast<const float4*>(ap));
+              else { a4[k].x = ap[0]; if (nn + 1 < oj_lim) a4[k].y = ap[1]; if (nn + 2 < oj_lim) a4[k].z = ap[2]; }
+            }
+          }
+        }
         tmem_ld32(tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)col, r);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
@@ -532,14 +556,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           if (i >= oi_lim || nn >= oj_lim) continue;
           float* cp = Cb + (size_t)i * ldo + nn;
           if (!SK) {
-            if (gg.add.p) {                                  // shared-parent term of the gate pre-activations (RowAdd)
-              const int ai = __ldg(gg.add.idx + i);
-              if (ai >= 0) {
-                const float* ap = gg.add.p + (size_t)ai * gg.add.ld + nn;
-                if (nn + 3 < oj_lim) { const float4 a4 = __ldg(reinterpret_cast<const float4*>(ap)); w.x += a4.x; w.y += a4.y; w.z += a4.z; w.w += a4.w; }
-                else { w.x += ap[0]; if (nn + 1 < oj_lim) w.y += ap[1]; if (nn + 2 < oj_lim) w.z += ap[2]; }
-              }
-            }
+            if (has_add) { const float4 a = a4[r4 >> 2]; w.x += a.x; w.y += a.y; w.z += a.z; w.w += a.w; }   // shared-parent term (RowAdd)
             w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
             if (flags & GEMM_RELU) { w.x = fmaxf(w.x, 0.f); w.y = fmaxf(w.y, 0.f); w.z = fmaxf(w.z, 0.f); w.w = fmaxf(w.w, 0.f); }
             if (flags & GEMM_GATES) {                        // column ranges are multiples of 4: one branch per float4
