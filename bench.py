@@ -439,6 +439,14 @@ def main():
     # ---- roofline of the dominant kernel: the LSTM gate contraction G = [x || h_parent] . Wg^T  (tcgen05, TMEM accumulators)
     C = cfg.model_config.hierarchical_ctx_mlp_hidden_dim
     flops_per_step = sum(2.0 * m * (3 * C + D) * (D if l == 0 else 2 * D) for l, m in enumerate(counts))
+    # what the kernels execute: in the tensor-core modes a level with fewer parent slots (slides x kept rows) than rows computes
+    # W_h h_parent once per slot and adds it in the gate epilogue (engine.cu: Level::shared) -- the algorithmic count above stays the
+    # reference's (no credit for the shortcut in `achieved`), the issue fraction below is of the executed products
+    topk = list(cfg.top_k_patches)
+    slots = [0] + [B * min(topk[l - 1], eng.maxseg[l - 1]) if topk[l - 1] >= 0 else B * eng.maxseg[l - 1] for l in range(1, Lv)]
+    shared = [args.precision != "fp32" and l >= 1 and slots[l] <= eng.caps[l] and "PATHS_B200_NO_SHARED_PARENT" not in os.environ
+              and bool(cfg.model_config.lstm) for l in range(Lv)]
+    executed_flops = sum(2.0 * (3 * C + D) * D * ((m + slots[l]) if shared[l] else (m if l == 0 else 2 * m)) for l, m in enumerate(counts))
     pk, pk_src = peaks()
     peak = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops"))
     hbm = pk.get("hbm_gbs", 6650.0)
@@ -462,7 +470,9 @@ def main():
                 "traffic": traffic, "kernel": "gemm_tma_kernel (LSTM gate contraction, fwd)" if passes else "gemm_nt_kernel (fp32 SIMT)",
                 "peak_source": pk_src + ", bf16 dense sustained", "kernel_ms_per_step": gate_ms / args.steps,
                 "kernel_share_of_step": gate_ms / ms, "algorithmic_flops_per_step": flops_per_step,
-                "mma_passes": passes, "tensor_issue_frac": (achieved * passes / peak) if (passes and peak and achieved) else None,
+                "executed_flops_per_step": executed_flops, "shared_parent_levels": [l for l in range(Lv) if shared[l]],
+                "mma_passes": passes,
+                "tensor_issue_frac": (achieved * executed_flops / flops_per_step * passes / peak) if (passes and peak and achieved) else None,
                 "dW_kernel_tflops": (flops_per_step * args.steps / (dw_ms / 1e3) / 1e12) if dw_ms > 0 else None,
                 "region_ms_per_step": regions,
                 # whole step against the roofline, reference-equivalent algorithmic work (9.18 MFLOP + 1024 T per row
