@@ -40,7 +40,9 @@ constexpr int kNumSMs = 148;                     // B200
 // launch attribute griddepcontrol is a no-op) -- on the multi-stream step it measured slower, see DESIGN.md §3.7b.
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_grid_sync() {
+#ifdef PATHS_PDL_EARLY                                    // early trigger: dependents become resident while this grid still runs
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif                                                    // default: implicit trigger as each CTA exits (dependents fill the tail only)
   asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 #endif

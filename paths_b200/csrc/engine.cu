@@ -18,7 +18,7 @@
 namespace paths {
 
 bool pdl_enabled() {
-  static const bool on = [] { const char* v = getenv("PATHS_B200_PDL"); return v && v[0] == '1'; }();   // opt-in (measured: see DESIGN §3.7b)
+  static const bool on = [] { const char* v = getenv("PATHS_B200_PDL"); return !(v && v[0] == '0'); }();   // on unless PATHS_B200_PDL=0
   return on;
 }
 
