@@ -273,17 +273,24 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
   for (int c0 = 0; c0 < NT; c0 += 32) {
     uint32_t r[32];
     tmem_ld32(lane_addr + c0, r);
-    float p[32];
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const float e = (c0 + i < T) ? expf(__uint_as_float(r[i]) - mx) : 0.f;
-      sum += e;                                              // the normaliser sums every probability, the value sum the kept ones
-      p[i] = e;
-      if (DROP) p[i] = drop_keep(dkey, hrow, hcol | (uint32_t)(c0 + i), dr.thresh) ? e * dr.inv_keep : 0.f;
+    for (int q = 0; q < 4; ++q) {                            // 8 keys at a time; groups past the bag (uniform per CTA) store zeros
+      float p[8];
+      if (c0 + 8 * q >= T) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) p[i] = 0.f;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int j = c0 + 8 * q + i;
+          const float e = (j < T) ? __expf(__uint_as_float(r[8 * q + i]) - mx) : 0.f;
+          sum += e;                                          // the normaliser sums every probability, the value sum the kept ones
+          p[i] = e;
+          if (DROP) p[i] = drop_keep(dkey, hrow, hcol | (uint32_t)j, dr.thresh) ? e * dr.inv_keep : 0.f;
+        }
+      }
+      store_score8<NP, NT>(smem + cfg::OFF_P, cfg::P_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, p);
     }
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-      store_score8<NP, NT>(smem + cfg::OFF_P, cfg::P_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, p + 8 * q);
   }
   fence_proxy_async();
   tc_fence_before();
@@ -411,22 +418,28 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
     uint32_t rs[32], rp[32];
     tmem_ld32(lane_addr + c0, rs);
     tmem_ld32(lane_addr + NT + c0, rp);
-    float pv[32], ds[32];
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const float p = (t < T && c0 + i < T) ? expf(__uint_as_float(rs[i]) - L) : 0.f;     // rows / columns past the bag: exact zeros
-      float pm = p, dpm = __uint_as_float(rp[i]);            // (they are contracted over by dK / dV, resp. dQ)
-      if (DROP) {
-        const bool keep = drop_keep(dkey, hrow, hcol | (uint32_t)(c0 + i), dr.thresh);
-        pm = keep ? p * dr.inv_keep : 0.f; dpm = keep ? dpm * dr.inv_keep : 0.f;
+    for (int q = 0; q < 4; ++q) {                            // 8 keys at a time; groups past the bag (uniform per CTA) store zeros
+      float pv[8], ds[8];
+      if (c0 + 8 * q >= T) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) pv[i] = ds[i] = 0.f;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int j = c0 + 8 * q + i;
+          const float p = (t < T && j < T) ? __expf(__uint_as_float(rs[8 * q + i]) - L) : 0.f;   // rows / columns past the bag: exact zeros
+          float pm = p, dpm = __uint_as_float(rp[8 * q + i]);  // (they are contracted over by dK / dV, resp. dQ)
+          if (DROP) {
+            const bool keep = drop_keep(dkey, hrow, hcol | (uint32_t)j, dr.thresh);
+            pm = keep ? p * dr.inv_keep : 0.f; dpm = keep ? dpm * dr.inv_keep : 0.f;
+          }
+          pv[i] = pm;
+          ds[i] = p * (dpm - Dq);
+        }
       }
-      pv[i] = pm;
-      ds[i] = p * (dpm - Dq);
-    }
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      store_score8<NP, NT>(smem + cfg::OFF_P, cfg::S_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, pv + 8 * q);
-      store_score8<NP, NT>(smem + cfg::OFF_DS, cfg::S_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, ds + 8 * q);
+      store_score8<NP, NT>(smem + cfg::OFF_P, cfg::S_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, pv);
+      store_score8<NP, NT>(smem + cfg::OFF_DS, cfg::S_PLANE, t, c0 >> 6, ((c0 & 63) >> 3) + q, ds);
     }
   }
   fence_proxy_async();
@@ -587,7 +600,7 @@ __global__ void __launch_bounds__(128) attn_tc_fwd_long_kernel(const float* __re
       float p[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        const float e = (k0 + c0 + i < T) ? expf(__uint_as_float(r[i]) - mx) : 0.f;
+        const float e = (k0 + c0 + i < T) ? __expf(__uint_as_float(r[i]) - mx) : 0.f;
         sum += e;
         p[i] = e;
         if (DROP) p[i] = drop_keep(dkey, hrow, hcol | (uint32_t)(k0 + c0 + i), dr.thresh) ? e * dr.inv_keep : 0.f;
@@ -740,7 +753,7 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dq_long_kernel(const float* _
       float ds[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        const float p = (live && k0 + c0 + i < T) ? expf(__uint_as_float(rs[i]) - L) : 0.f;
+        const float p = (live && k0 + c0 + i < T) ? __expf(__uint_as_float(rs[i]) - L) : 0.f;
         float dpm = __uint_as_float(rp[i]);
         if (DROP) dpm = drop_keep(dkey, hrow, hcol | (uint32_t)(k0 + c0 + i), dr.thresh) ? dpm * dr.inv_keep : 0.f;
         ds[i] = p * (dpm - Dq);
@@ -884,7 +897,7 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dkv_long_kernel(const float* 
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
         const int q = q0 + c0 + i;
-        const float p = (live && q < T) ? expf(__uint_as_float(rs[i]) - sL[c0 + i]) : 0.f;
+        const float p = (live && q < T) ? __expf(__uint_as_float(rs[i]) - sL[c0 + i]) : 0.f;
         float pm = p, dpm = __uint_as_float(rp[i]);
         if (DROP) {
           const bool keep = drop_keep(dkey, hrow0 + (uint32_t)q, hcol, dr.thresh);

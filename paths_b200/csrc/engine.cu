@@ -121,6 +121,7 @@ struct Level {
   bool tables_ok;                    // the slot tables describe the level's current rows (built by do_select; dropped when a caller takes
                                      // the level's ROW_PARENT buffer to fill the tables by hand, as the level API of runtime.py does)
   bool ran_pl, ran_shared;           // what the last lstm_forward of the level used: its backward (and its parent's) must match
+  bool x_planes;                     // the gather of this pass already wrote x into AxhP (lstm_forward skips its split pass over X)
   int *slot4, *sel_rows;             // as the parent level: [cap, 4] slot of a row with surviving children; [B * kcap] row of a slot
   int* add_idx;                      // as the child level: [cap] slot of the row's parent
   Planes HselP;                      // as the child level: h of the selected parents, [B * kcap(l-1), D] planes (kept for dW)
@@ -517,17 +518,19 @@ int lstm_forward(paths_engine* e, int l, cudaStream_t st) {
     RowSrc Axh = has_parent ? row_src2(v.X, D, nullptr, D, e->lv[l - 1].H, D, v.row_parent) : row_src(v.X, D, D);
     const bool shp = pl && has_parent && v.shared;       // W_h h_parent once per selected parent, added by the gate epilogue
     v.ran_pl = pl; v.ran_shared = shp;
+    const bool x_ready = v.x_planes && pl;               // consumed by this pass: a later pass without a gather splits again
+    v.x_planes = false;
     if (shp) {
       Level& pv = e->lv[l - 1];
       const int slots = B * pv.kcap;
       RUN(split_rows(row_src(pv.H, D, D, pv.sel_rows), slots, nullptr, D, v.HselP, 0, lo != 0, st));
-      RUN(split_rows(row_src(v.X, D, D), M, Md, D, v.AxhP, 0, lo != 0, st));
+      if (!x_ready) RUN(split_rows(row_src(v.X, D, D), M, Md, D, v.AxhP, 0, lo != 0, st));
       ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
       RUN(gemm_nt_act(prec, act(nullptr, 0, v.HselP), e->P.Wg + D, 2 * D, 0, e->Gh, ldg, nullptr, slots, nullptr, ldg, D, 0, st));
       RowAdd ra; ra.p = e->Gh; ra.idx = v.add_idx; ra.ld = ldg;
       RUN(gemm_nt_act(prec, act(nullptr, 0, v.AxhP), e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, D, GEMM_GATES | (C << 8), st, &ra));
     } else {
-      if (pl) RUN(split_rows(Axh, M, Md, Kx, v.AxhP, 0, lo != 0, st));
+      if (pl && !(x_ready && !has_parent)) RUN(split_rows(Axh, M, Md, Kx, v.AxhP, 0, lo != 0, st));
       ProfScope ps(e, PATHS_PROF_GATES_FWD, st);
       // tensor-core path: the epilogue applies the gate non-linearities, G reaches HBM activated (written once)
       if (pl) RUN(gemm_nt_act(prec, act(nullptr, 0, v.AxhP), e->P.Wg, 2 * D, 0, v.G, ldg, e->P.bg, M, Md, ldg, Kx, GEMM_GATES | (C << 8), st));
@@ -1020,7 +1023,10 @@ int do_select(paths_engine* e, int l, cudaStream_t st) {
   RUN(select_expand(a, st)); e->launches += 2;
   pdl(tseg_kernel, (e->B + 255) / 256, 256, 0, st)(n.seg, n.tseg, e->B);
   PATHS_LAUNCH_CK(); e->launches++;
-  RUN(gather_rows(e->store.grid_ptr, e->store.gh, l + 1, dm.L, e->slide_ids, n.row_slide, n.row_xy, n.X, dm.D, n.cap, n.count, st, e->store.bf16));
+  // a shared-parent level's operand planes hold x alone: the gather writes them as it goes
+  n.x_planes = n.shared && planes_mode(dm);
+  RUN(gather_rows(e->store.grid_ptr, e->store.gh, l + 1, dm.L, e->slide_ids, n.row_slide, n.row_xy, n.X, dm.D, n.cap, n.count, st, e->store.bf16,
+                  n.x_planes ? &n.AxhP : nullptr, dm.precision == PREC_BF16X3_TC));
   n.tables_ok = n.shared;
   if (n.shared)
     RUN(parent_slots(v.child_of, v.count, v.cap, v.sel, v.sel_count, e->B, v.kcap, n.row_slide, n.row_parent, n.parent_local, n.count, n.cap,
@@ -1054,11 +1060,16 @@ int do_begin(paths_engine* e, const int32_t* slide_ids, const float* fts_padded,
   e->launches++;
   pdl(tseg_kernel, (e->B + 255) / 256, 256, 0, st)(v.seg, v.tseg, e->B);
   PATHS_LAUNCH_CK(); e->launches++;
+  v.x_planes = false;
   if (fts_padded && N < 0) {
     PATHS_REQUIRE(-N <= v.cap, "begin: %d packed level-0 rows exceed the level's capacity %d", -N, v.cap);
     PATHS_CK(cudaMemcpyAsync(v.X, fts_padded, (size_t)(-N) * e->dm.D * sizeof(float), cudaMemcpyDeviceToDevice, st));
   } else if (fts_padded) RUN(pack_padded_rows(fts_padded, N, v.seg, v.row_slide, v.X, e->dm.D, v.cap, v.count, st));
-  else RUN(gather_rows(e->store.grid_ptr, e->store.gh, 0, e->dm.L, slide_ids, v.row_slide, v.row_xy, v.X, e->dm.D, v.cap, v.count, st, e->store.bf16));
+  else {
+    v.x_planes = planes_mode(e->dm);
+    RUN(gather_rows(e->store.grid_ptr, e->store.gh, 0, e->dm.L, slide_ids, v.row_slide, v.row_xy, v.X, e->dm.D, v.cap, v.count, st, e->store.bf16,
+                    v.x_planes ? &v.AxhP : nullptr, e->dm.precision == PREC_BF16X3_TC));
+  }
   return 0;
 }
 
@@ -1523,7 +1534,7 @@ int paths_engine_buffer(paths_engine_t* e, int level, int which, void** ptr, siz
     case PATHS_BUF_SEL: p = v.sel; n = B * (size_t)(v.kcap > 0 ? v.kcap : 1) * i4; break;
     case PATHS_BUF_SEL_COUNT: p = v.sel_count; n = B * i4; break;
     case PATHS_BUF_CHILD_OF: p = v.child_of; n = 4 * cap * i4; break;
-    case PATHS_BUF_X: p = v.X; n = cap * dm.D * f; break;
+    case PATHS_BUF_X: p = v.X; n = cap * dm.D * f; v.x_planes = false; break;
     case PATHS_BUF_G: p = v.G; n = cap * (3 * (size_t)dm.C + dm.D) * f; break;
     case PATHS_BUF_CN: p = v.Cn; n = cap * dm.C * f; break;
     case PATHS_BUF_PT: p = v.Pt; n = cap * dm.D * f; break;

@@ -25,10 +25,18 @@ template <bool BF16>
 __global__ void __launch_bounds__(TPB) gather_rows_kernel(const float* const* __restrict__ grid_ptr, const int* __restrict__ gh,
                                                           int level, int L, const int* __restrict__ slide_ids,
                                                           const int* __restrict__ row_slide, const int* __restrict__ row_xy,
-                                                          float* __restrict__ X, int D, int M_host, const int* M_dev) {
+                                                          float* __restrict__ X, int D, int M_host, const int* M_dev, Planes XP,
+                                                          int want_lo) {
   pdl_grid_sync();
   const int M = row_count(M_host, M_dev);
-  ROW_LOOP(m, M) {
+  // XP (optional): the rows also leave as the bf16 (hi, lo) operand planes of the gate contraction, with the zero rows up to the
+  // next multiple of 64 the weight-gradient form reads -- the split pass over X then never runs
+  const int Mw = XP.p ? planes_rows_to_write(XP, M) : M;
+  ROW_LOOP(m, Mw) {
+    if (m >= M) {
+      for (int c = lane; c < D / 4; c += 32) planes_store4(XP, m, 4 * c, make_float4(0.f, 0.f, 0.f, 0.f), want_lo != 0);
+      continue;
+    }
     const int s = row_slide[m];
     const int sid = slide_ids ? slide_ids[s] : s;
     const size_t cell = (size_t)row_xy[2 * m] * gh[(size_t)sid * L + level] + row_xy[2 * m + 1];
@@ -39,11 +47,17 @@ __global__ void __launch_bounds__(TPB) gather_rows_kernel(const float* const* __
         const uint2 v = __ldg(s2 + c);
         const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.x));
         const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.y));
-        dst[c] = make_float4(a.x, a.y, b.x, b.y);
+        const float4 x = make_float4(a.x, a.y, b.x, b.y);
+        dst[c] = x;
+        if (XP.p) planes_store4(XP, m, 4 * c, x, want_lo != 0);
       }
     } else {
       const float4* s4 = reinterpret_cast<const float4*>(grid_ptr[(size_t)sid * L + level] + cell * D);
-      for (int c = lane; c < D / 4; c += 32) dst[c] = __ldg(s4 + c);
+      for (int c = lane; c < D / 4; c += 32) {
+        const float4 x = __ldg(s4 + c);
+        dst[c] = x;
+        if (XP.p) planes_store4(XP, m, 4 * c, x, want_lo != 0);
+      }
     }
   }
 }
@@ -1382,11 +1396,14 @@ __global__ void __launch_bounds__(256) child_sum_planes_kernel(const Planes src,
 
 // ---- host launchers -----------------------------------------------------------------------------------------
 int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, const int* slide_ids, const int* row_slide,
-                const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st, int bf16) {
+                const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st, int bf16, const Planes* XP, int want_lo) {
   PATHS_REQUIRE(D % 4 == 0, "gather_rows: D must be a multiple of 4");
   if (M_host <= 0) return 0;
-  if (bf16) pdl(gather_rows_kernel<true>, row_grid(M_host), TPB, 0, st)(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev);
-  else pdl(gather_rows_kernel<false>, row_grid(M_host), TPB, 0, st)(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev);
+  const Planes xp = XP ? *XP : no_planes();
+  PATHS_REQUIRE(!xp.p || (D <= xp.ldp && M_host <= xp.rows), "gather_rows: operand planes too small");
+  const int g = row_grid(M_host + (xp.p ? 64 : 0));
+  if (bf16) pdl(gather_rows_kernel<true>, g, TPB, 0, st)(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev, xp, want_lo);
+  else pdl(gather_rows_kernel<false>, g, TPB, 0, st)(grid_ptr, gh, level, L, slide_ids, row_slide, row_xy, X, D, M_host, M_dev, xp, want_lo);
   PATHS_LAUNCH_CK();
   return 0;
 }

@@ -16,7 +16,8 @@ inline GIdx gidx1(const int* idx, int roff = 0) {
 }
 
 int gather_rows(const float* const* grid_ptr, const int* gh, int level, int L, const int* slide_ids, const int* row_slide,
-                const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st, int bf16 = 0);
+                const int* row_xy, float* X, int D, int M_host, const int* M_dev, cudaStream_t st, int bf16 = 0, const Planes* XP = nullptr,
+                int want_lo = 0);
 int pack_padded_rows(const float* fts, int N, const int* seg, const int* row_slide, float* X, int D, int M_host, const int* M_dev,
                      cudaStream_t st);
 // Outputs come as fp32 rows (pointer may be null) and/or bf16 (hi, lo) planes (Planes.p may be null); want_lo = 0 skips the
