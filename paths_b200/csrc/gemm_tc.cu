@@ -42,6 +42,12 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int elem /* 0..63 */) {
   return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((elem >> 3) ^ (row & 7))) << 4) + (elem & 7) * 2);
 }
 
+// Gate non-linearities of the epilogue (tensor-core modes only; the fp32 mode's row kernels keep expf / tanhf): ex2.approx and
+// rcp.approx, ~2e-7 absolute -- two orders below the split-bf16 products they are applied to -- at a quarter of the instructions
+// and without tanhf's range branches.
+__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float tanh_fast(float x) { return 1.f - __fdividef(2.f, 1.f + __expf(2.f * x)); }
+
 template <int BN, int NP>
 struct Cfg {
   static constexpr int A_PLANE = BM * BK * 2;
@@ -561,8 +567,8 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             if (flags & GEMM_RELU) { w.x = fmaxf(w.x, 0.f); w.y = fmaxf(w.y, 0.f); w.z = fmaxf(w.z, 0.f); w.w = fmaxf(w.w, 0.f); }
             if (flags & GEMM_GATES) {                        // column ranges are multiples of 4: one branch per float4
               const int gc = flags >> 8;
-              if (nn >= 2 * gc && nn < 3 * gc) { w.x = tanhf(w.x); w.y = tanhf(w.y); w.z = tanhf(w.z); w.w = tanhf(w.w); }
-              else { w.x = sigmoidf_(w.x); w.y = sigmoidf_(w.y); w.z = sigmoidf_(w.z); w.w = sigmoidf_(w.w); }
+              if (nn >= 2 * gc && nn < 3 * gc) { w.x = tanh_fast(w.x); w.y = tanh_fast(w.y); w.z = tanh_fast(w.z); w.w = tanh_fast(w.w); }
+              else { w.x = sigmoid_fast(w.x); w.y = sigmoid_fast(w.y); w.z = sigmoid_fast(w.z); w.w = sigmoid_fast(w.w); }
             }
           }
           if (vec && nn + 3 < oj_lim) {
