@@ -245,6 +245,20 @@ int paths_attention_fwd(int precision, const float* qkv, const int32_t* seg, int
 int paths_attention_bwd(int precision, const float* qkv, const int32_t* seg, int B, const float* out, const float* lse, const float* dout,
                         float* dqkv, float* dvec, int d, int heads, int max_bag, float dropout_p, uint64_t dropout_seed, void* stream);
 
+/* Allocation-free variant of paths_attention_bwd.  This entry point has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same arguments and results as paths_attention_bwd, except that the [tokens, heads] `dvec`
+ * scratch is a file-scope device array inside the library (4 MiB, held by every GPU that loads the library until the process
+ * exits) and the caller states `tokens` (rows of qkv = seg[B] + B) so the size can be checked on the host: the call fails with a
+ * clear error, launching nothing, when tokens * heads > PATHS_ATTENTION_BWD_STATIC_MAX_FLOATS.  It calls no cudaMalloc / cudaFree
+ * or allocating library routine.  Every call on a device shares the one array (it keeps the last call's contents; each call
+ * writes every element it later reads, nothing needs clearing): calls that OVERLAP on the GPU -- different streams or host
+ * threads -- race on it; serialise them or use paths_attention_bwd with separate dvec buffers. */
+#define PATHS_ATTENTION_BWD_STATIC_MAX_FLOATS (1 << 20)
+int paths_attention_bwd_static(int precision, const float* qkv, const int32_t* seg, int B, int tokens, const float* out, const float* lse,
+                               const float* dout, float* dqkv, int d, int heads, int max_bag, float dropout_p, uint64_t dropout_seed,
+                               void* stream);
+
 /* Stand-alone dense contractions (tests; the engine uses the same kernels).
  * C[M,N] (+)= act(A[M,K] . B^T + bias) with B [N,K] (b_kn = 0) or [K,N] (b_kn = 1); flags: 1 relu, 2 accumulate. */
 int paths_gemm_nt(int precision, const float* A, int lda, const float* B, int ldb, int b_kn, float* C, int ldc, const float* bias,

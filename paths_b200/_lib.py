@@ -52,7 +52,7 @@ SYMBOLS = ["paths_last_error", "paths_abi_version", "paths_engine_workspace_byte
            "paths_engine_destroy", "paths_engine_bind_params", "paths_engine_bind_store", "paths_engine_refresh_weights", "paths_engine_begin",
            "paths_engine_begin_padded", "paths_engine_level_forward", "paths_engine_select", "paths_engine_loss",
            "paths_engine_level_backward", "paths_engine_forward", "paths_engine_forward_padded", "paths_engine_forward_packed", "paths_engine_backward", "paths_engine_wait_grads", "paths_engine_overflow_poll", "paths_engine_buffer",
-           "paths_engine_set_precision", "paths_engine_set_dropout", "paths_engine_launch_count", "paths_engine_profile", "paths_engine_profile_read", "paths_build_occupancy", "paths_attention_fwd", "paths_attention_bwd", "paths_lstm_cell_fwd", "paths_select_expand", "paths_gather_rows", "paths_engine_aggregate", "paths_gemm_nt",
+           "paths_engine_set_precision", "paths_engine_set_dropout", "paths_engine_launch_count", "paths_engine_profile", "paths_engine_profile_read", "paths_build_occupancy", "paths_attention_fwd", "paths_attention_bwd", "paths_attention_bwd_static", "paths_lstm_cell_fwd", "paths_select_expand", "paths_gather_rows", "paths_engine_aggregate", "paths_gemm_nt",
            "paths_gemm_tn", "paths_adamw_step", "paths_heatmap_workspace_bytes", "paths_heatmap_composite"]
 
 
@@ -98,6 +98,7 @@ def lib() -> C.CDLL:
     L.paths_build_occupancy.argtypes = [vp, i32, i32, vp, vp, vp]
     L.paths_attention_fwd.argtypes = [i32, vp, vp, i32, vp, vp, i32, i32, i32, f32, C.c_uint64, vp]
     L.paths_attention_bwd.argtypes = [i32, vp, vp, i32, vp, vp, vp, vp, vp, i32, i32, i32, f32, C.c_uint64, vp]
+    L.paths_attention_bwd_static.argtypes = [i32, vp, vp, i32, i32, vp, vp, vp, vp, i32, i32, i32, f32, C.c_uint64, vp]
     L.paths_lstm_cell_fwd.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp]
     L.paths_select_expand.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, C.POINTER(Store), i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp,
                                       vp, i32, i32, vp, vp, vp]

@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -1637,6 +1638,53 @@ int paths_attention_bwd(int precision, const float* qkv, const int32_t* seg, int
                         float* dqkv, float* dvec, int d, int heads, int max_bag, float dropout_p, uint64_t dropout_seed, void* stream) {
   PATHS_REQUIRE(qkv && seg && out && lse && dout && dqkv && dvec && B >= 1 && heads >= 1 && d % heads == 0 && precision >= 0 && precision <= 2,
                 "attention_bwd: bad argument");
+  Drop dr = no_drop();
+  if (dropout_p > 0.f) { dr.thresh = drop_thresh(dropout_p); dr.inv_keep = 1.f / (1.f - dropout_p); dr.key[0] = drop_site_key(dropout_seed, 0, 0, DROP_ATTN); }
+  return attn_bwd_grp(qkv, seg_single(seg, B), out, lse, dout, dqkv, dvec, d, heads, max_bag + 1, 0, static_cast<cudaStream_t>(stream),
+                      dropout_p > 0.f ? &dr : nullptr, precision == PREC_BF16X3_TC ? 3 : precision == PREC_BF16_TC ? 1 : 0);
+}
+
+
+// ---- allocation-free variant of paths_attention_bwd ------------------------------------------------------------------------------
+// For callers that cannot allocate device memory (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc): the
+// [tokens, heads] scratch of the backward pass (D = dO . O per query row and head, written by the dq kernel and read by the dk/dv
+// kernel) lives in a file-scope device array instead of a caller buffer.  Every GPU that loads the library holds the array until
+// the process exits.  In host code the array's NAME is only a host-side stand-in: its device address comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.  All calls share the array (it keeps the last call's
+// contents; every element a call reads is written by that call first, so nothing has to be cleared): calls that overlap on the GPU
+// -- different streams, or different host threads -- race on it.
+static __device__ __align__(256) float g_attn_bwd_scratch[PATHS_ATTENTION_BWD_STATIC_MAX_FLOATS];
+namespace paths { namespace {
+constexpr int kMaxDevices = 64;
+float* g_attn_bwd_scratch_ptr[kMaxDevices] = {};
+std::mutex g_attn_bwd_scratch_mu;
+// device address of g_attn_bwd_scratch on the current device (no allocation: the array is part of the loaded module)
+int attn_bwd_scratch(float** out) {
+  int dev = -1;
+  PATHS_CK(cudaGetDevice(&dev));
+  PATHS_REQUIRE(dev >= 0 && dev < kMaxDevices, "attention_bwd_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lk(g_attn_bwd_scratch_mu);
+  if (!g_attn_bwd_scratch_ptr[dev]) {
+    float* ptr = nullptr;
+    PATHS_CK(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_attn_bwd_scratch));
+    PATHS_REQUIRE(ptr != nullptr, "attention_bwd_static: cudaGetSymbolAddress returned a null device address");
+    g_attn_bwd_scratch_ptr[dev] = ptr;
+  }
+  *out = g_attn_bwd_scratch_ptr[dev];
+  return 0;
+}
+}}  // namespace paths::(anonymous)
+
+int paths_attention_bwd_static(int precision, const float* qkv, const int32_t* seg, int B, int tokens, const float* out, const float* lse,
+                               const float* dout, float* dqkv, int d, int heads, int max_bag, float dropout_p, uint64_t dropout_seed,
+                               void* stream) {
+  PATHS_REQUIRE(qkv && seg && out && lse && dout && dqkv && B >= 1 && tokens >= B && heads >= 1 && d % heads == 0 && precision >= 0 &&
+                precision <= 2, "attention_bwd_static: bad argument");
+  PATHS_REQUIRE((long long)tokens * heads <= (long long)PATHS_ATTENTION_BWD_STATIC_MAX_FLOATS,
+                "attention_bwd_static: tokens * heads = %lld exceeds the static scratch of %d floats (PATHS_ATTENTION_BWD_STATIC_MAX_FLOATS); "
+                "use paths_attention_bwd with a caller-provided dvec", (long long)tokens * heads, PATHS_ATTENTION_BWD_STATIC_MAX_FLOATS);
+  float* dvec = nullptr;
+  if (int r = paths::attn_bwd_scratch(&dvec)) return r;
   Drop dr = no_drop();
   if (dropout_p > 0.f) { dr.thresh = drop_thresh(dropout_p); dr.inv_keep = 1.f / (1.f - dropout_p); dr.key[0] = drop_site_key(dropout_seed, 0, 0, DROP_ATTN); }
   return attn_bwd_grp(qkv, seg_single(seg, B), out, lse, dout, dqkv, dvec, d, heads, max_bag + 1, 0, static_cast<cudaStream_t>(stream),
