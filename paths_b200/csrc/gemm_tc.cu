@@ -48,10 +48,11 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int elem /* 0..63 */) {
 __device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 __device__ __forceinline__ float tanh_fast(float x) { return 1.f - __fdividef(2.f, 1.f + __expf(2.f * x)); }
 
-template <int BN, int NP>
+// CG = 2: CTA pair (cta_group::2) -- the pair's tile is 256 x BN, each CTA stages its 128 rows of A and HALF of the B tile
+template <int BN, int NP, int CG = 1>
 struct Cfg {
   static constexpr int A_PLANE = BM * BK * 2;
-  static constexpr int B_PLANE = BN * BK * 2;
+  static constexpr int B_PLANE = (BN / CG) * BK * 2;
   static constexpr int STAGE = NP * (A_PLANE + B_PLANE);
   static constexpr int NS = (200 * 1024) / STAGE >= 4 ? 4 : (200 * 1024) / STAGE;
   static constexpr int EPI_STAGE = 8 * 4096;                 // per-epilogue-warp 32 x 32 fp32 transpose buffers
@@ -260,7 +261,13 @@ __device__ __forceinline__ void cvt_store(const CvtRegs& g, uint8_t* dst, int pl
 // CTA order into C: deterministic, no atomics.
 // A_CVT / B_CVT: the operand comes as fp32 rows (RowSrc sa / sb) and is converted by the loader warps instead of arriving as
 // TMA boxes of pre-split planes.
-template <int BN, int NP, bool A_MN, bool B_MN, bool SK, bool A_CVT, bool B_CVT>
+// CG = 2 (NT form with both operands TMA-fed): the CTAs of a 2-cluster work as a pair on a 256 x BN tile with ONE
+// tcgen05.mma.cta_group::2 per step, issued by rank 0.  What bounds the single-CTA form is the L2 -> shared-memory fill rate
+// (A 128 x 64 + B BN x 64 per 64-deep k-block and SM: 48 B/clk/SM at the 76 % tensor activity the gate contraction reaches, the
+// chip's L2 -> SM ceiling); the pair halves the B bytes each SM has to pull.  Protocol: both TMA warps load into their own
+// shared memory and count bytes on rank 0's full barrier; rank 0's commit multicasts "stage free" / "accumulator full" to both
+// CTAs; the epilogue warps of both CTAs release the accumulator on rank 0's barrier.
+template <int BN, int NP, bool A_MN, bool B_MN, bool SK, bool A_CVT, bool B_CVT, int CG = 1>
 __global__ void __launch_bounds__((A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA, 1)
 gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Operand oa, Operand ob,
                 const RowSrc sa, const RowSrc sb, float* __restrict__ C, int ldc, const GemmGrp gg, int b_grp_rows, int OI_host, int OJ,
@@ -269,9 +276,12 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   // Persistent: one CTA per SM walks work units u = blockIdx.x, += gridDim.x; unit = (row tile, column tile, reduction split)
   // with column tiles fastest so CTAs that run together share A rows in L2.  Two TMEM accumulators: the epilogue of unit n
   // drains one while the MMA warp fills the other.
-  using cfg = Cfg<BN, NP>;
+  static_assert(CG == 1 || (CG == 2 && !SK && !A_CVT && !B_CVT && BN == 256), "CTA pairs: NT form, TMA-fed operands, BN = 256");
+  using cfg = Cfg<BN, NP, CG>;
   constexpr int NS = cfg::NS;
+  constexpr int TM = BM * CG;                                // rows of a work unit's tile
   constexpr uint32_t TMA_BYTES = (A_CVT ? 0 : NP * cfg::A_PLANE) + (B_CVT ? 0 : NP * cfg::B_PLANE);
+  const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;    // rank 0 leads the pair
   constexpr uint32_t FULL_COUNT = (TMA_BYTES ? 1 : 0) + ((A_CVT || B_CVT) ? LOADER_WARPS : 0);
   // Row groups (common.cuh): the NT form walks the live 128-row tiles of every group of the concatenated activation buffer
   // (weights / bias of the tile's group); the TN form (SK) produces one [OI_host x OJ] output per group, reducing over the
@@ -285,7 +295,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     for (int g = 0; g < kMaxGroups; ++g) {                 // compile-time indices into the parameter struct (see pick())
       const int c = g < gg.rows.n ? (gg.rows.cnt[g] ? *gg.rows.cnt[g] : gg.rows.hcnt[g]) : 0;
       g_cnt[g] = c; g_roff[g] = gg.rows.roff[g]; g_wlev[g] = gg.wlev[g]; g_bias[g] = gg.bias[g];
-      cum += (c + BM - 1) / BM;
+      cum += (c + TM - 1) / TM;
       g_cum[g + 1] = cum;
       mx = c > mx ? c : mx;
     }
@@ -300,12 +310,13 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) { mbar_init(&full_bar[s], FULL_COUNT); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], EPI_WARPS); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], EPI_WARPS * CG); }
     fence_barrier_init();
   }
-  if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 2 * BN);
+  if (warp == MMA_WARP) { if (CG == 2) tmem_alloc_pair(&tmem_slot, 2 * BN); else tmem_alloc(&tmem_slot, 2 * BN); }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();                           // the peer's barriers exist before anything is signalled across
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   const int tiles_i = SK ? (OI_host + BM - 1) / BM : g_cum[kMaxGroups], tiles_j = (OJ + BN - 1) / BN;
@@ -348,7 +359,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         kb_begin = (int)(b - t_lo); kb_end = (int)(e - t_lo);
       }
     } else {
-      t = blockIdx.x + n * gridDim.x;
+      t = (int)(blockIdx.x / CG) + n * (int)(gridDim.x / CG);
       if (t >= units || nkb_total == 0) return false;
       kb_begin = 0; kb_end = nkb_total;
     }
@@ -361,7 +372,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int g = 0;
       for (int k = 1; k < gg.rows.n; ++k) g = r >= g_cum[k] ? k : g;
       u.g = g;
-      u.j0 = (t % tiles_j) * BN; u.i0 = g_roff[g] + (r - g_cum[g]) * BM;
+      u.j0 = (t % tiles_j) * BN; u.i0 = g_roff[g] + (r - g_cum[g]) * TM + (int)rank * BM;
     }
     return true;
   };
@@ -429,9 +440,31 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const int s = it % NS;
           const uint32_t ph = (it / NS) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full_bar[s], TMA_BYTES);
           uint8_t* a_base = smem + (size_t)s * cfg::STAGE;
           uint8_t* b_base = a_base + NP * cfg::A_PLANE;
+          if (CG == 2) {
+            // both CTAs load their A rows and their half of the B tile; every byte is counted on the leader's barrier
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[s], 2 * TMA_BYTES);
+            const uint32_t fb = mapa_rank(smem_u32(&full_bar[s]), 0);
+            const int jh = j0 + (int)rank * (BN / 2);
+#pragma unroll
+            for (int pl = 0; pl < NP; ++pl) {
+#pragma unroll
+              for (int bx = 0; bx < BM / 64; ++bx) {
+                uint8_t* dst = a_base + pl * cfg::A_PLANE + bx * 8192;
+                if (!A_MN) tma_load_2d_pair(dst, &tmA, oa.col0 + kb * BK, pl * oa.plane_rows + oa.row0 + i0 + bx * 64, fb);
+                else       tma_load_2d_pair(dst, &tmA, oa.col0 + i0 + bx * 64, pl * oa.plane_rows + oa.row0 + rb + kb * BK, fb);
+              }
+#pragma unroll
+              for (int bx = 0; bx < BN / 2 / 64; ++bx) {
+                uint8_t* dst = b_base + pl * cfg::B_PLANE + bx * 8192;
+                if (!B_MN) tma_load_2d_pair(dst, &tmB, ob.col0 + kb * BK, pl * ob.plane_rows + b_row0 + jh + bx * 64, fb);
+                else       tma_load_2d_pair(dst, &tmB, ob.col0 + jh + bx * 64, pl * ob.plane_rows + b_row0 + rb + kb * BK, fb);
+              }
+            }
+            continue;
+          }
+          mbar_arrive_expect_tx(&full_bar[s], TMA_BYTES);
 #pragma unroll
           for (int pl = 0; pl < NP; ++pl) {
 #pragma unroll
@@ -451,8 +484,8 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else if (warp == MMA_WARP) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = umma_idesc(TM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       uint32_t it = 0, tcount = 0;
       Unit u;
       for (int n = 0; get_unit(n, u); ++n) {
@@ -478,16 +511,23 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                                          : umma_desc(a_addr + cfg::A_PLANE + ks * 32, 16, 1024);
               const uint64_t b_lo = B_MN ? umma_desc(b_addr + cfg::B_PLANE + ks * 2048, 8192, 1024)
                                          : umma_desc(b_addr + cfg::B_PLANE + ks * 32, 16, 1024);
-              umma_bf16(d_tmem, a_lo, b_hi, idesc, acc0);
-              umma_bf16(d_tmem, a_hi, b_lo, idesc, 1u);
-              umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
+              if (CG == 2) {
+                umma_bf16_pair(d_tmem, a_lo, b_hi, idesc, acc0);
+                umma_bf16_pair(d_tmem, a_hi, b_lo, idesc, 1u);
+                umma_bf16_pair(d_tmem, a_hi, b_hi, idesc, 1u);
+              } else {
+                umma_bf16(d_tmem, a_lo, b_hi, idesc, acc0);
+                umma_bf16(d_tmem, a_hi, b_lo, idesc, 1u);
+                umma_bf16(d_tmem, a_hi, b_hi, idesc, 1u);
+              }
             } else {
-              umma_bf16(d_tmem, a_hi, b_hi, idesc, acc0);
+              if (CG == 2) umma_bf16_pair(d_tmem, a_hi, b_hi, idesc, acc0);
+              else umma_bf16(d_tmem, a_hi, b_hi, idesc, acc0);
             }
           }
-          umma_commit(&empty_bar[s]);
+          if (CG == 2) umma_commit_pair(&empty_bar[s], 3); else umma_commit(&empty_bar[s]);
         }
-        umma_commit(&acc_full[buf]);
+        if (CG == 2) umma_commit_pair(&acc_full[buf], 3); else umma_commit(&acc_full[buf]);
         ++tcount;
       }
     }
@@ -585,13 +625,17 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_cluster(mapa_rank(smem_u32(&acc_empty[buf]), 0));   // the leader's MMA warp waits for both CTAs
+        else mbar_arrive(&acc_empty[buf]);
+      }
       ++tcount;
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == MMA_WARP) tmem_dealloc(tmem_base, 2 * BN);
+  if (CG == 2) cluster_sync_all();                           // no signal may still be under way to a CTA that has exited
+  if (warp == MMA_WARP) { if (CG == 2) tmem_dealloc_pair(tmem_base, 2 * BN); else tmem_dealloc(tmem_base, 2 * BN); }
 }
 
 // ---------------------------------------------------------------------------------------------- packed weights
@@ -724,6 +768,50 @@ int launch_tma(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand
   const int grid = SK ? grid_sk : (units < kNumSMs ? (int)units : kNumSMs);
   pdl(kern, grid, (A_CVT || B_CVT) ? NTHREADS_CVT : NTHREADS_TMA, Cfg<BN, NP>::SMEM, st)(
       A_CVT ? dummy : *ma, B_CVT ? dummy : *mb, oa, ob, sa, sb, C, ldc, gg, b_grp_rows, OI_host, OJ, R_host, flags, segmax);
+  PATHS_LAUNCH_CK();
+  return 0;
+}
+
+// CTA-pair launch (gemm_tma_kernel<..., CG = 2>): clusters of 2, one pair per TPC.  Off with PATHS_B200_NO_PAIR=1 (A/B runs).
+bool pair_enabled() {
+  static const bool on = getenv("PATHS_B200_NO_PAIR") == nullptr;
+  return on;
+}
+// fewest 256 x 256 tiles worth a pair launch: half a wave; PATHS_B200_FORCE_PAIR=1 (tests) sends every eligible contraction there
+long pair_min_units() {
+  static const long n = getenv("PATHS_B200_FORCE_PAIR") ? 1 : kNumSMs / 2;
+  return n;
+}
+template <int NP, bool B_MN>
+int launch_pair(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand ob, float* C, int ldc, const GemmGrp& gg, int b_grp_rows,
+                int OI_host, int OJ, int R_host, int flags, cudaStream_t st) {
+  constexpr int BN = 256;
+  auto kern = gemm_tma_kernel<BN, NP, false, B_MN, false, false, false, 2>;
+  static int max_pairs = 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(NTHREADS_TMA); cfg.dynamicSmemBytes = Cfg<BN, NP, 2>::SMEM; cfg.stream = st;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  if (!max_pairs) {
+    if (int r = set_smem(kern, Cfg<BN, NP, 2>::SMEM)) return r;
+    cfg.gridDim = dim3(kNumSMs); cfg.numAttrs = 1;
+    int nc = 0;
+    PATHS_CK(cudaOccupancyMaxActiveClusters(&nc, kern, &cfg));
+    PATHS_REQUIRE(nc >= 1, "gemm_nt_tc: the device cannot co-schedule a CTA pair of the contraction kernel");
+    max_pairs = nc < kNumSMs / 2 ? nc : kNumSMs / 2;
+  }
+  long row_tiles = 0;
+  for (int g = 0; g < gg.rows.n; ++g) row_tiles += (gg.rows.hcnt[g] + 2 * BM - 1) / (2 * BM);
+  long units = (long)((OJ + BN - 1) / BN) * row_tiles;
+  if (units < 1) units = 1;
+  const int pairs = units < max_pairs ? (int)units : max_pairs;
+  cfg.gridDim = dim3(2 * pairs); cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  static const RowSrc none = row_src(nullptr, 0, 0);
+  cudaLaunchKernelEx(&cfg, kern, *ma, *mb, oa, ob, none, none, C, ldc, gg, b_grp_rows, OI_host, OJ, R_host, flags, 0);
   PATHS_LAUNCH_CK();
   return 0;
 }
@@ -912,6 +1000,16 @@ static int nt_impl(int passes, const Planes* A, int a_col0, const RowSrc* Asrc, 
       PATHS_REQUIRE(gg.wlev[g] >= 0 && gg.wlev[g] < (pk->nstack > 1 ? pk->nstack : 1), "gemm_nt_tc: group %d addresses member %d of a %d-stack",
                     g, gg.wlev[g], pk->nstack);
   const bool big = N > 128;
+  // CTA pairs for the wide outputs with TMA-fed operands, when there are enough 256-row tiles to keep the pairs busy
+  long pair_tiles = 0;
+  for (int g = 0; g < gg.rows.n; ++g) pair_tiles += (gg.rows.hcnt[g] + 2 * BM - 1) / (2 * BM);
+  const bool pair = A && big && pair_enabled() && pair_tiles * ((N + 255) / 256) >= pair_min_units();
+  if (pair) {
+    if (passes == 3) return b_kn ? launch_pair<2, true>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, st)
+                                 : launch_pair<2, false>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, st);
+    return b_kn ? launch_pair<1, true>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, st)
+                : launch_pair<1, false>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, st);
+  }
 #define NT_CASE(BN_, NP_, MN_)                                                                                                         \
   do {                                                                                                                                 \
     if (A) return launch_tma<BN_, NP_, false, MN_, false, false, false>(ma, &pk->map, oa, ob, none, none, C, ldc, gg, bgr, M_host,     \
