@@ -276,7 +276,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   // Persistent: one CTA per SM walks work units u = blockIdx.x, += gridDim.x; unit = (row tile, column tile, reduction split)
   // with column tiles fastest so CTAs that run together share A rows in L2.  Two TMEM accumulators: the epilogue of unit n
   // drains one while the MMA warp fills the other.
-  static_assert(CG == 1 || (CG == 2 && !SK && !A_CVT && !B_CVT && BN == 256), "CTA pairs: NT form, TMA-fed operands, BN = 256");
+  static_assert(CG == 1 || (CG == 2 && !A_CVT && !B_CVT && BN == 256), "CTA pairs: TMA-fed operands, BN = 256");
   using cfg = Cfg<BN, NP, CG>;
   constexpr int NS = cfg::NS;
   constexpr int TM = BM * CG;                                // rows of a work unit's tile
@@ -319,12 +319,14 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (CG == 2) cluster_sync_all();                           // the peer's barriers exist before anything is signalled across
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
-  const int tiles_i = SK ? (OI_host + BM - 1) / BM : g_cum[kMaxGroups], tiles_j = (OJ + BN - 1) / BN;
+  // (stream-K over pairs: the plan below is the single-CTA one with the pair as the "CTA" and the 256-row tile as the tile)
+  const int vcta = (int)(blockIdx.x / CG), vG = (int)(gridDim.x / CG);
+  const int tiles_i = SK ? (OI_host + TM - 1) / TM : g_cum[kMaxGroups], tiles_j = (OJ + BN - 1) / BN;
   const int nkb_total = ((SK ? g_max : R_host) + BK - 1) / BK;
   const int units = SK ? gg.rows.n * tiles_i * tiles_j : tiles_i * tiles_j;
   const long long sk_total = (long long)units * nkb_total;
-  const long long sk_q = (sk_total + gridDim.x - 1) / gridDim.x;
-  const long long sk_lo = (long long)blockIdx.x * sk_q;
+  const long long sk_q = (sk_total + vG - 1) / vG;
+  const long long sk_lo = (long long)vcta * sk_q;
   const long long sk_hi = sk_lo + sk_q < sk_total ? sk_lo + sk_q : sk_total;
 
   // n-th work unit of this CTA: (output tile origin, k-block range); false when the CTA has no more work
@@ -333,15 +335,15 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     int& kb_begin = u.kb_begin; int& kb_end = u.kb_end;
     if (SK) {
       if (nkb_total == 0) return false;
-      const SkPlan pl = sk_plan(units, nkb_total, (int)gridDim.x);
+      const SkPlan pl = sk_plan(units, nkb_total, vG);
       if (pl.k1 >= 0) {
         // more CTAs than tiles: CTA t < tiles sweeps k-blocks [0, k1) of tile t in lock step with the others (all of them read
         // the same reduction rows at the same time: operands stay L2-resident); the remaining CTAs stream over the tails
-        if ((int)blockIdx.x < units) {
+        if (vcta < units) {
           if (n > 0 || pl.k1 == 0) return false;
-          t = blockIdx.x; kb_begin = 0; kb_end = pl.k1;
+          t = vcta; kb_begin = 0; kb_end = pl.k1;
         } else {
-          const long long lo = (long long)(blockIdx.x - units) * pl.q, hi0 = lo + pl.q;
+          const long long lo = (long long)(vcta - units) * pl.q, hi0 = lo + pl.q;
           const long long hi = hi0 < pl.total ? hi0 : pl.total;
           t = (int)(lo / pl.tl) + n;
           const long long t_lo = (long long)t * pl.tl;
@@ -359,14 +361,14 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         kb_begin = (int)(b - t_lo); kb_end = (int)(e - t_lo);
       }
     } else {
-      t = (int)(blockIdx.x / CG) + n * (int)(gridDim.x / CG);
+      t = vcta + n * vG;
       if (t >= units || nkb_total == 0) return false;
       kb_begin = 0; kb_end = nkb_total;
     }
     if (SK) {
       const int tpg = tiles_i * tiles_j, tt = t % tpg;
       u.g = t / tpg;
-      u.j0 = (tt % tiles_j) * BN; u.i0 = (tt / tiles_j) * BM;
+      u.j0 = (tt % tiles_j) * BN; u.i0 = (tt / tiles_j) * TM + (int)rank * BM;
     } else {
       const int r = t / tiles_j;
       int g = 0;
@@ -550,7 +552,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       tc_fence_after();
       float* Cb; int ldo, oi_lim, oj_lim, ci0, cj0;
       if (SK) {                                              // partial tile -> workspace slot, row-major [BM][BN]
-        Cb = C + ((size_t)blockIdx.x * segmax + n) * (BM * BN); ldo = BN; oi_lim = BM; oj_lim = BN; ci0 = 0; cj0 = 0;
+        Cb = C + (((size_t)vcta * segmax + n) * CG + rank) * (BM * BN); ldo = BN; oi_lim = BM; oj_lim = BN; ci0 = 0; cj0 = 0;
       } else {
         Cb = C; ldo = ldc; oi_lim = a_olim(u); oj_lim = OJ; ci0 = i0; cj0 = j0;
       }
@@ -782,11 +784,28 @@ long pair_min_units() {
   static const long n = getenv("PATHS_B200_FORCE_PAIR") ? 1 : kNumSMs / 2;
   return n;
 }
-template <int NP, bool B_MN>
+// maximum number of co-resident pairs of a kernel instance (clusters of 2 at one CTA per SM)
+template <typename K>
+int pair_capacity(K kern, int smem, int* out) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(NTHREADS_TMA); cfg.dynamicSmemBytes = smem; cfg.gridDim = dim3(kNumSMs);
+  cudaLaunchAttribute at;
+  at.id = cudaLaunchAttributeClusterDimension;
+  at.val.clusterDim.x = 2; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+  cfg.attrs = &at; cfg.numAttrs = 1;
+  if (int r = set_smem(kern, smem)) return r;
+  int nc = 0;
+  PATHS_CK(cudaOccupancyMaxActiveClusters(&nc, kern, &cfg));
+  PATHS_REQUIRE(nc >= 1, "gemm_tc: the device cannot co-schedule a CTA pair of the contraction kernel");
+  *out = nc < kNumSMs / 2 ? nc : kNumSMs / 2;
+  return 0;
+}
+// SK = true: pairs_sk pairs share the stream-K plan (tn_plan with cg = 2)
+template <int NP, bool A_MN, bool B_MN, bool SK>
 int launch_pair(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operand ob, float* C, int ldc, const GemmGrp& gg, int b_grp_rows,
-                int OI_host, int OJ, int R_host, int flags, cudaStream_t st) {
+                int OI_host, int OJ, int R_host, int flags, int pairs_sk, int segmax, cudaStream_t st) {
   constexpr int BN = 256;
-  auto kern = gemm_tma_kernel<BN, NP, false, B_MN, false, false, false, 2>;
+  auto kern = gemm_tma_kernel<BN, NP, A_MN, B_MN, SK, false, false, 2>;
   static int max_pairs = 0;
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(NTHREADS_TMA); cfg.dynamicSmemBytes = Cfg<BN, NP, 2>::SMEM; cfg.stream = st;
@@ -796,29 +815,31 @@ int launch_pair(const CUtensorMap* ma, const CUtensorMap* mb, Operand oa, Operan
   at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
-  if (!max_pairs) {
-    if (int r = set_smem(kern, Cfg<BN, NP, 2>::SMEM)) return r;
-    cfg.gridDim = dim3(kNumSMs); cfg.numAttrs = 1;
-    int nc = 0;
-    PATHS_CK(cudaOccupancyMaxActiveClusters(&nc, kern, &cfg));
-    PATHS_REQUIRE(nc >= 1, "gemm_nt_tc: the device cannot co-schedule a CTA pair of the contraction kernel");
-    max_pairs = nc < kNumSMs / 2 ? nc : kNumSMs / 2;
+  if (!max_pairs)
+    if (int r = pair_capacity(kern, Cfg<BN, NP, 2>::SMEM, &max_pairs)) return r;
+  int pairs;
+  if (SK) {
+    PATHS_REQUIRE(pairs_sk >= 1, "gemm_tn_tc: empty stream-K plan");
+    pairs = pairs_sk;                                        // fixed by the host's plan (slot layout); segments are independent
+  } else {
+    long row_tiles = 0;
+    for (int g = 0; g < gg.rows.n; ++g) row_tiles += (gg.rows.hcnt[g] + 2 * BM - 1) / (2 * BM);
+    long units = (long)((OJ + BN - 1) / BN) * row_tiles;
+    if (units < 1) units = 1;
+    pairs = units < max_pairs ? (int)units : max_pairs;
   }
-  long row_tiles = 0;
-  for (int g = 0; g < gg.rows.n; ++g) row_tiles += (gg.rows.hcnt[g] + 2 * BM - 1) / (2 * BM);
-  long units = (long)((OJ + BN - 1) / BN) * row_tiles;
-  if (units < 1) units = 1;
-  const int pairs = units < max_pairs ? (int)units : max_pairs;
   cfg.gridDim = dim3(2 * pairs); cfg.numAttrs = pdl_enabled() ? 2 : 1;
   static const RowSrc none = row_src(nullptr, 0, 0);
-  cudaLaunchKernelEx(&cfg, kern, *ma, *mb, oa, ob, none, none, C, ldc, gg, b_grp_rows, OI_host, OJ, R_host, flags, 0);
+  cudaLaunchKernelEx(&cfg, kern, *ma, *mb, oa, ob, none, none, C, ldc, gg, b_grp_rows, OI_host, OJ, R_host, flags, segmax);
   PATHS_LAUNCH_CK();
   return 0;
 }
 
 // C[tile] += sum over the stream-K segments of the tile, in a fixed order (deterministic).  A block owns 256 / PG consecutive
 // float4 outputs of one tile; PG thread groups each sum every PG-th segment and are combined through shared memory.
-template <int BN, int PG>
+// CG = 2: the partial tiles were produced by CTA pairs -- plan and slots are those of the 256-row pair tile T that holds this
+// 128-row tile, whose partials sit at [slot of T][half = i-tile & 1]; G counts pairs.
+template <int BN, int PG, int CG = 1>
 __global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict__ ws, const GemmGrp gg, int ldc, int NI, int NJ, int G,
                                                         int segmax) {
   pdl_grid_sync();
@@ -832,11 +853,14 @@ __global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict
   const int nkb = (R + BK - 1) / BK;
   if (nkb == 0) return;
   const int tiles_j = (NJ + BN - 1) / BN;
-  const int t = blockIdx.x;
   const int tpg = ((NI + BM - 1) / BM) * tiles_j;            // output tiles per group
-  const int units = gg.rows.n * tpg;
-  float* __restrict__ C = pick(gg.cout, t / tpg);
-  const int tt = t % tpg;
+  float* __restrict__ C = pick(gg.cout, blockIdx.x / tpg);
+  const int tt = blockIdx.x % tpg;
+  // t, units: the tile this block sums and the tile count IN THE PRODUCER'S PLAN (pair tiles when CG = 2)
+  const int tpg_p = ((NI + BM * CG - 1) / (BM * CG)) * tiles_j;
+  const int t = CG == 1 ? (int)blockIdx.x : (int)(blockIdx.x / tpg) * tpg_p + (tt / tiles_j / 2) * tiles_j + tt % tiles_j;
+  const int half = CG == 1 ? 0 : (tt / tiles_j) & 1;
+  const int units = gg.rows.n * tpg_p;
   const SkPlan pl = sk_plan(units, nkb, G);
   const int o = threadIdx.x % OUT, g = threadIdx.x / OUT;
   const int elem = blockIdx.y * OUT + o;                 // float4 index inside the tile, row-major
@@ -853,7 +877,7 @@ __global__ void __launch_bounds__(256) tn_reduce_kernel(const float4* __restrict
       const int c = c_first + (k - extra);
       slot = (size_t)(c_base + c) * segmax + (t - (int)(((long long)c * pl.q) / pl.tl));
     }
-    const float4 v = __ldcs(ws + slot * (BM * BN / 4) + elem);
+    const float4 v = __ldcs(ws + (slot * CG + half) * (BM * BN / 4) + elem);
     acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
   }
   if (PG > 1) {
@@ -1005,10 +1029,10 @@ static int nt_impl(int passes, const Planes* A, int a_col0, const RowSrc* Asrc, 
   for (int g = 0; g < gg.rows.n; ++g) pair_tiles += (gg.rows.hcnt[g] + 2 * BM - 1) / (2 * BM);
   const bool pair = A && big && pair_enabled() && pair_tiles * ((N + 255) / 256) >= pair_min_units();
   if (pair) {
-    if (passes == 3) return b_kn ? launch_pair<2, true>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, st)
-                                 : launch_pair<2, false>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, st);
-    return b_kn ? launch_pair<1, true>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, st)
-                : launch_pair<1, false>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, st);
+    if (passes == 3) return b_kn ? launch_pair<2, false, true, false>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, 0, 0, st)
+                                 : launch_pair<2, false, false, false>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, 0, 0, st);
+    return b_kn ? launch_pair<1, false, true, false>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, 0, 0, st)
+                : launch_pair<1, false, false, false>(ma, &pk->map, oa, ob, C, ldc, gg, bgr, M_host, N, K, flags, 0, 0, st);
   }
 #define NT_CASE(BN_, NP_, MN_)                                                                                                         \
   do {                                                                                                                                 \
@@ -1049,12 +1073,13 @@ int gemm_nt_tc(int passes, const RowSrc& A, const float* B, int ldb, int b_kn, f
 }
 
 // Stream-K plan of a weight-gradient contraction: CTAs and workspace slots per CTA.
-static void tn_plan(int NI, int NJ, int M_host, int ngroups, int* G, int* segmax) {
+// cg = 2: the plan of CTA pairs (tiles of 256 rows, G pairs)
+static void tn_plan(int NI, int NJ, int M_host, int ngroups, int* G, int* segmax, int cg = 1) {
   const int BN = NJ > 128 ? 256 : 128;
-  const int tiles = ngroups * ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
+  const int tiles = ngroups * ((NI + BM * cg - 1) / (BM * cg)) * ((NJ + BN - 1) / BN);
   const long total = (long)tiles * ((M_host + BK - 1) / BK);
   long g = total / 4;                            // at least ~4 k-blocks per CTA
-  if (g > kNumSMs) g = kNumSMs;
+  if (g > kNumSMs / cg) g = kNumSMs / cg;
   if (g < 1) g = 1;
   *G = (int)g;
   *segmax = (tiles + *G - 1) / *G + 2;
@@ -1063,10 +1088,17 @@ static void tn_plan(int NI, int NJ, int M_host, int ngroups, int* G, int* segmax
     if (s2 > *segmax) *segmax = s2;
   }
 }
+static bool tn_pair_ok(int NI, int NJ) { return NJ > 128 && NI % (2 * BM) == 0 && pair_enabled(); }
 size_t tn_workspace_bytes(int NI, int NJ, int M_host, int ngroups) {
   int G, segmax;
   tn_plan(NI, NJ, M_host, ngroups, &G, &segmax);
-  return (size_t)G * segmax * BM * (NJ > 128 ? 256 : 128) * sizeof(float);
+  size_t need = (size_t)G * segmax * BM * (NJ > 128 ? 256 : 128) * sizeof(float);
+  if (tn_pair_ok(NI, NJ)) {                                  // the pair plan: two half-tiles per slot
+    tn_plan(NI, NJ, M_host, ngroups, &G, &segmax, 2);
+    const size_t n2 = (size_t)G * segmax * 2 * BM * 256 * sizeof(float);
+    if (n2 > need) need = n2;
+  }
+  return need;
 }
 void set_tn_workspace(void* p, size_t bytes) { g_tn_ws.p = p; g_tn_ws.bytes = bytes; }
 
@@ -1098,10 +1130,23 @@ static int tn_impl(int passes, const Planes* P, int p_col0, const Planes* Q, int
   const int BN = big ? 256 : 128;
   const int tiles = ng * ((NI + BM - 1) / BM) * ((NJ + BN - 1) / BN);
   int G, segmax;
-  tn_plan(NI, NJ, M_host, ng, &G, &segmax);
-  const size_t need = (size_t)G * segmax * BM * BN * sizeof(float);
+  // CTA pairs when both operands are TMA-fed planes and the output rows tile by 256 (the LSTM block's weight gradients)
+  const bool pair = P && tn_pair_ok(NI, NJ) && (long)tiles * ((M_host + BK - 1) / BK) / 8 >= pair_min_units();
+  tn_plan(NI, NJ, M_host, ng, &G, &segmax, pair ? 2 : 1);
+  const size_t need = (size_t)G * segmax * (pair ? 2 : 1) * BM * BN * sizeof(float);
   PATHS_REQUIRE(g_tn_ws.p && need <= g_tn_ws.bytes, "gemm_tn_tc: stream-K workspace too small: need %zu bytes, have %zu", need, g_tn_ws.bytes);
   float* ws = static_cast<float*>(g_tn_ws.p);
+  if (pair) {
+    int r = passes == 3 ? launch_pair<2, true, true, true>(ma, mb, oa, ob, ws, 0, gg, 0, NI, NJ, M_host, 0, G, segmax, st)
+                        : launch_pair<1, true, true, true>(ma, mb, oa, ob, ws, 0, gg, 0, NI, NJ, M_host, 0, G, segmax, st);
+    if (r) return r;
+    if (4 * tiles >= 2 * G)
+      pdl(tn_reduce_kernel<256, 1, 2>, dim3(tiles, BM * 256 / 4 / 256), 256, 0, st)(reinterpret_cast<const float4*>(ws), gg, ldc, NI, NJ, G, segmax);
+    else
+      pdl(tn_reduce_kernel<256, 8, 2>, dim3(tiles, BM * 256 / 4 / 32), 256, 0, st)(reinterpret_cast<const float4*>(ws), gg, ldc, NI, NJ, G, segmax);
+    PATHS_LAUNCH_CK();
+    return 0;
+  }
 #define TN_CASE(BN_, NP_)                                                                                                              \
   do {                                                                                                                                 \
     int r;                                                                                                                             \
