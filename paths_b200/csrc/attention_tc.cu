@@ -129,6 +129,35 @@ __device__ __forceinline__ void stage_natural_dot(uint8_t* tile, const float* __
     *reinterpret_cast<uint4*>(row + (((g + 4) ^ (r & 7)) << 4)) = lo;
   }
 }
+// Block staging of the tiled (long-bag) kernels: a block of 64 token rows x 32 floats is read by the CTA's 128 threads, two items
+// (row, 8-float group) each -- a warp covers 8 whole 128-byte rows per pass -- into registers (Blk), and written to its natural tile
+// later: the loads of block j + 1 are issued before block j's products are waited for, so the global round trip is off the
+// per-block dependency chain.  rows_live <= 0 gives a block of zeros.
+struct Blk { float4 a[2], b[2]; };
+__device__ __forceinline__ void blk_load(Blk& g, const float* __restrict__ src, int ld, int rows_live, int t) {
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int i = t + 128 * k, r = i >> 2, grp = i & 3;
+    if (r < rows_live) {
+      const float4* p = reinterpret_cast<const float4*>(src + (size_t)r * ld + grp * 8);
+      g.a[k] = __ldg(p); g.b[k] = __ldg(p + 1);
+    } else {
+      g.a[k] = make_float4(0.f, 0.f, 0.f, 0.f); g.b[k] = g.a[k];
+    }
+  }
+}
+__device__ __forceinline__ void blk_store(const Blk& g, uint8_t* tile, int t, float mul) {
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int i = t + 128 * k, r = i >> 2, grp = i & 3;
+    const float x[8] = {g.a[k].x * mul, g.a[k].y * mul, g.a[k].z * mul, g.a[k].w * mul, g.b[k].x * mul, g.b[k].y * mul, g.b[k].z * mul, g.b[k].w * mul};
+    uint4 hi, lo;
+    split8(x, hi, lo);
+    uint8_t* row = tile + (r >> 3) * 1024 + (r & 7) * 128;
+    *reinterpret_cast<uint4*>(row + ((grp ^ (r & 7)) << 4)) = hi;
+    *reinterpret_cast<uint4*>(row + (((grp + 4) ^ (r & 7)) << 4)) = lo;
+  }
+}
 // transposed planes: element (head_dim c, token j) of plane p at  p * plane_bytes + (j / 64) * 4096 + swizzled (row c, column j % 64)
 template <int NP>
 __device__ __forceinline__ void store_transposed(uint8_t* base, int plane_bytes, int j, const float* x) {
@@ -501,7 +530,7 @@ constexpr int LB = 64;                                      // block of the walk
 
 template <int NP>
 struct LongFwdCfg {
-  static constexpr int OFF_Q = 0, OFF_K = 16384, OFF_VT = OFF_K + LB * 128, OFF_P = OFF_VT + NP * 4096;
+  static constexpr int OFF_Q = 0, OFF_K = 16384, OFF_V = OFF_K + LB * 128, OFF_P = OFF_V + LB * 128;    // K, V: natural 64-row tiles
   static constexpr int P_PLANE = 128 * 128;
   static constexpr int SMEM = OFF_P + NP * P_PLANE + 1024;
   static constexpr int TMEM_COLS = 128;                      // S [0, 64), P V [64, 96)
@@ -542,7 +571,7 @@ __global__ void __launch_bounds__(128) attn_tc_fwd_long_kernel(const float* __re
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
-  const uint32_t sQ = smem_u32(smem + cfg::OFF_Q), sK = smem_u32(smem + cfg::OFF_K), sVt = smem_u32(smem + cfg::OFF_VT),
+  const uint32_t sQ = smem_u32(smem + cfg::OFF_Q), sK = smem_u32(smem + cfg::OFF_K), sV = smem_u32(smem + cfg::OFF_V),
                  sP = smem_u32(smem + cfg::OFF_P);
   const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
   const uint32_t hrow = (uint32_t)(sg.t0 - sg.r0 + q0 + t), hcol = (uint32_t)h << 24;
@@ -551,21 +580,17 @@ __global__ void __launch_bounds__(128) attn_tc_fwd_long_kernel(const float* __re
   for (int c = 0; c < DH; ++c) o[c] = 0.f;
   float mx = -INFINITY, sum = 0.f;
   uint32_t phase = 0;
+  const float* kbase = qkv + (size_t)sg.t0 * ld + h * DH + d;  // K rows of the bag; V rows are d floats further
+  Blk gK, gV;
+  blk_load(gK, kbase, ld, T, t);
+  blk_load(gV, kbase + d, ld, T, t);
 #pragma unroll 1
   for (int k0 = 0; k0 < T; k0 += LB) {
-    if (t < LB) {                                            // stage the block's keys: K natural, V transposed
-      float x[DH];
-      if (k0 + t < T) {
-        const float* rp = qkv + (size_t)(sg.t0 + k0 + t) * ld + h * DH;
-        load_row32(rp + d, x);
-        store_natural(smem + cfg::OFF_K, t, x);
-        load_row32(rp + 2 * d, x);
-      } else {
-        zero_natural(smem + cfg::OFF_K, t);
-#pragma unroll
-        for (int c = 0; c < DH; ++c) x[c] = 0.f;
-      }
-      store_transposed<NP>(smem + cfg::OFF_VT, 4096, t, x);
+    blk_store(gK, smem + cfg::OFF_K, t, 1.f);                // the block's keys and values (natural tiles: V is read M-major)
+    blk_store(gV, smem + cfg::OFF_V, t, 1.f);
+    if (k0 + LB < T) {                                       // next block's rows: in flight while this block's products run
+      blk_load(gK, kbase + (size_t)(k0 + LB) * ld, ld, T - k0 - LB, t);
+      blk_load(gV, kbase + d + (size_t)(k0 + LB) * ld, ld, T - k0 - LB, t);
     }
     fence_proxy_async();
     tc_fence_before();
@@ -613,12 +638,14 @@ __global__ void __launch_bounds__(128) attn_tc_fwd_long_kernel(const float* __re
     __syncthreads();
     tc_fence_after();
     if (t == 0) {                                            // block's P V -> columns [64, 96), fresh
-      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0);
+      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 1);  // B = 16 value rows of the natural tile, M-major
       uint32_t acc = 0;
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks)
-        mma_terms<NP>(tmem_base + 64, desc_k(sP, ks * 32), desc_k(sP + cfg::P_PLANE, ks * 32), desc_k(sVt, ks * 32), desc_k(sVt + 4096, ks * 32),
-                      idesc, &acc);
+      for (int ks = 0; ks < 4; ++ks) {
+        const uint32_t b = sV + ks * 16 * 128;
+        mma_terms<NP>(tmem_base + 64, desc_k(sP, ks * 32), desc_k(sP + cfg::P_PLANE, ks * 32), desc_m(b, 0, 8192), desc_m(b + 64, 0, 8192), idesc,
+                      &acc);
+      }
       umma_commit(&bar);
     }
     mbar_wait(&bar, phase); phase ^= 1;
@@ -647,7 +674,7 @@ __global__ void __launch_bounds__(128) attn_tc_fwd_long_kernel(const float* __re
 
 template <int NP>
 struct LongDqCfg {
-  static constexpr int OFF_Q = 0, OFF_DO = 16384, OFF_K = 32768, OFF_V = OFF_K + LB * 128, OFF_KT = OFF_V + LB * 128, OFF_DS = OFF_KT + NP * 4096;
+  static constexpr int OFF_Q = 0, OFF_DO = 16384, OFF_K = 32768, OFF_V = OFF_K + LB * 128, OFF_DS = OFF_V + LB * 128;
   static constexpr int S_PLANE = 128 * 128;
   static constexpr int SMEM = OFF_DS + NP * S_PLANE + 1024;
   static constexpr int TMEM_COLS = 256;                      // S [0, 64), dP [64, 128), dQ [128, 160)
@@ -706,24 +733,17 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dq_long_kernel(const float* _
   const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
   const uint32_t hrow = (uint32_t)(sg.t0 - sg.r0 + q0 + t), hcol = (uint32_t)h << 24;
   uint32_t phase = 0, acc_dq = 0;
+  const float* kbase = qkv + (size_t)sg.t0 * ld + h * DH + d;
+  Blk gK, gV;
+  blk_load(gK, kbase, ld, T, t);
+  blk_load(gV, kbase + d, ld, T, t);
 #pragma unroll 1
   for (int k0 = 0; k0 < T; k0 += LB) {
-    if (t < LB) {
-      float x[DH];
-      if (k0 + t < T) {
-        const float* rp = qkv + (size_t)(sg.t0 + k0 + t) * ld + h * DH;
-        load_row32(rp + d, x);
-        store_natural(smem + cfg::OFF_K, t, x);
-        store_transposed<NP>(smem + cfg::OFF_KT, 4096, t, x);
-        load_row32(rp + 2 * d, x);
-        store_natural(smem + cfg::OFF_V, t, x);
-      } else {
-#pragma unroll
-        for (int c = 0; c < DH; ++c) x[c] = 0.f;
-        zero_natural(smem + cfg::OFF_K, t);
-        zero_natural(smem + cfg::OFF_V, t);
-        store_transposed<NP>(smem + cfg::OFF_KT, 4096, t, x);
-      }
+    blk_store(gK, smem + cfg::OFF_K, t, 1.f);                // natural tiles: K is the K-major operand of S and the M-major one of dQ
+    blk_store(gV, smem + cfg::OFF_V, t, 1.f);
+    if (k0 + LB < T) {
+      blk_load(gK, kbase + (size_t)(k0 + LB) * ld, ld, T - k0 - LB, t);
+      blk_load(gV, kbase + d + (size_t)(k0 + LB) * ld, ld, T - k0 - LB, t);
     }
     fence_proxy_async();
     tc_fence_before();
@@ -766,12 +786,14 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dq_long_kernel(const float* _
     __syncthreads();
     tc_fence_after();
     if (t == 0) {                                            // dQ += dS_blk K_blk : columns [128, 160), accumulated over the blocks
-      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0);
-      const uint32_t a = s0 + cfg::OFF_DS, b = s0 + cfg::OFF_KT;
+      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 1);
+      const uint32_t a = s0 + cfg::OFF_DS;
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks)
-        mma_terms<NP>(tmem_base + 128, desc_k(a, ks * 32), desc_k(a + cfg::S_PLANE, ks * 32), desc_k(b, ks * 32), desc_k(b + 4096, ks * 32), idesc,
+      for (int ks = 0; ks < 4; ++ks) {
+        const uint32_t b = s0 + cfg::OFF_K + ks * 16 * 128;  // 16 key rows of the natural tile
+        mma_terms<NP>(tmem_base + 128, desc_k(a, ks * 32), desc_k(a + cfg::S_PLANE, ks * 32), desc_m(b, 0, 8192), desc_m(b + 64, 0, 8192), idesc,
                       &acc_dq);
+      }
       umma_commit(&bar);
     }
     mbar_wait(&bar, phase); phase ^= 1;                      // the staged tiles are free again
@@ -789,8 +811,7 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dq_long_kernel(const float* _
 
 template <int NP>
 struct LongDkvCfg {
-  static constexpr int OFF_K = 0, OFF_V = 16384, OFF_Q = 32768, OFF_DO = OFF_Q + LB * 128, OFF_QT = OFF_DO + LB * 128, OFF_DOT = OFF_QT + NP * 4096,
-                       OFF_P = OFF_DOT + NP * 4096;
+  static constexpr int OFF_K = 0, OFF_V = 16384, OFF_Q = 32768, OFF_DO = OFF_Q + LB * 128, OFF_P = OFF_DO + LB * 128;
   static constexpr int S_PLANE = 128 * 128;                  // [128 key rows][64 queries]
   static constexpr int OFF_DS = OFF_P + NP * S_PLANE;
   static constexpr int SMEM = OFF_DS + NP * S_PLANE + 1024;
@@ -843,30 +864,27 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dkv_long_kernel(const float* 
   const uint64_t dkey = DROP ? pick(dr.key, sg.g) : 0;
   const uint32_t hrow0 = (uint32_t)(sg.t0 - sg.r0), hcol = ((uint32_t)h << 24) | (uint32_t)(j0 + t);
   uint32_t phase = 0, acc_dk = 0, acc_dv = 0;
+  const float* qbase = qkv + (size_t)sg.t0 * ld + h * DH;
+  const float* obase = dout + (size_t)sg.t0 * d + h * DH;
+  const float* lbase = lse + (size_t)sg.t0 * heads + h;
+  const float* dbase = dvec + (size_t)sg.t0 * heads + h;
+  Blk gQ, gO;
+  float gL = 0.f, gD = 0.f;                                  // (threads t < 64: the block's per-query log-sum-exp and D)
+  blk_load(gQ, qbase, ld, T, t);
+  blk_load(gO, obase, d, T, t);
+  if (t < LB && t < T) { gL = __ldg(lbase + (size_t)t * heads); gD = __ldg(dbase + (size_t)t * heads); }
 #pragma unroll 1
   for (int q0 = 0; q0 < T; q0 += LB) {
-    if (t < LB) {                                            // stage the block's queries: scale Q and dO, natural + transposed; lse, D
-      float x[DH];
-      if (q0 + t < T) {
-        load_row32(qkv + (size_t)(sg.t0 + q0 + t) * ld + h * DH, x);
-#pragma unroll
-        for (int c = 0; c < DH; ++c) x[c] *= scale;
-        store_natural(smem + cfg::OFF_Q, t, x);
-        store_transposed<NP>(smem + cfg::OFF_QT, 4096, t, x);
-        load_row32(dout + (size_t)(sg.t0 + q0 + t) * d + h * DH, x);
-        store_natural(smem + cfg::OFF_DO, t, x);
-        store_transposed<NP>(smem + cfg::OFF_DOT, 4096, t, x);
-        sL[t] = lse[(size_t)(sg.t0 + q0 + t) * heads + h];
-        sD[t] = dvec[(size_t)(sg.t0 + q0 + t) * heads + h];
-      } else {
-#pragma unroll
-        for (int c = 0; c < DH; ++c) x[c] = 0.f;
-        zero_natural(smem + cfg::OFF_Q, t);
-        zero_natural(smem + cfg::OFF_DO, t);
-        store_transposed<NP>(smem + cfg::OFF_QT, 4096, t, x);
-        store_transposed<NP>(smem + cfg::OFF_DOT, 4096, t, x);
-        sL[t] = 0.f; sD[t] = 0.f;
-      }
+    // the block's queries: scale Q and dO as natural tiles (K-major operands of S^T / dP^T, M-major ones of dK / dV); lse, D
+    blk_store(gQ, smem + cfg::OFF_Q, t, scale);
+    blk_store(gO, smem + cfg::OFF_DO, t, 1.f);
+    if (t < LB) { sL[t] = gL; sD[t] = gD; }
+    if (q0 + LB < T) {
+      const int nq = q0 + LB;
+      blk_load(gQ, qbase + (size_t)nq * ld, ld, T - nq, t);
+      blk_load(gO, obase + (size_t)nq * d, d, T - nq, t);
+      gL = 0.f; gD = 0.f;
+      if (t < LB && nq + t < T) { gL = __ldg(lbase + (size_t)(nq + t) * heads); gD = __ldg(dbase + (size_t)(nq + t) * heads); }
     }
     fence_proxy_async();
     tc_fence_before();
@@ -917,16 +935,20 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dkv_long_kernel(const float* 
     __syncthreads();
     tc_fence_after();
     if (t == 0) {                                            // dK += dS^T (scale Q_blk), dV += P^T dO_blk : contract over the 64 queries
-      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 0);
-      const uint32_t aS = s0 + cfg::OFF_DS, aP = s0 + cfg::OFF_P, bQ = s0 + cfg::OFF_QT, bO = s0 + cfg::OFF_DOT;
+      constexpr uint32_t idesc = umma_idesc(128, DH, 0, 1);
+      const uint32_t aS = s0 + cfg::OFF_DS, aP = s0 + cfg::OFF_P;
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks)
-        mma_terms<NP>(tmem_base + 128, desc_k(aS, ks * 32), desc_k(aS + cfg::S_PLANE, ks * 32), desc_k(bQ, ks * 32), desc_k(bQ + 4096, ks * 32), idesc,
+      for (int ks = 0; ks < 4; ++ks) {
+        const uint32_t b = s0 + cfg::OFF_Q + ks * 16 * 128;  // 16 query rows of the natural tile
+        mma_terms<NP>(tmem_base + 128, desc_k(aS, ks * 32), desc_k(aS + cfg::S_PLANE, ks * 32), desc_m(b, 0, 8192), desc_m(b + 64, 0, 8192), idesc,
                       &acc_dk);
+      }
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks)
-        mma_terms<NP>(tmem_base + 160, desc_k(aP, ks * 32), desc_k(aP + cfg::S_PLANE, ks * 32), desc_k(bO, ks * 32), desc_k(bO + 4096, ks * 32), idesc,
+      for (int ks = 0; ks < 4; ++ks) {
+        const uint32_t b = s0 + cfg::OFF_DO + ks * 16 * 128;
+        mma_terms<NP>(tmem_base + 160, desc_k(aP, ks * 32), desc_k(aP + cfg::S_PLANE, ks * 32), desc_m(b, 0, 8192), desc_m(b + 64, 0, 8192), idesc,
                       &acc_dv);
+      }
       umma_commit(&bar);
     }
     mbar_wait(&bar, phase); phase ^= 1;
