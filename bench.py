@@ -32,6 +32,7 @@ import os
 import subprocess
 import sys
 import tempfile
+import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -80,7 +81,41 @@ def peaks():
 
 
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md's clocks line).  NVML from a thread of this
+    process (first sample immediately, then every 10 ms: a 20-step region is ~0.3 s, and a freshly spawned nvidia-smi can take longer
+    than that to print its first row); `nvidia-smi -lms` as the fallback when NVML cannot be loaded."""
+    REASONS = [("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)]
+
     def __init__(self, index):
+        self.rows, self.p, self.f, self.th = [], None, None, None
+        self.stop_flag = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            uuid = torch.cuda.get_device_properties(index).uuid
+            try:
+                h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode())
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                h = pynvml.nvmlDeviceGetHandleByIndex(int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+
+            def loop():
+                while True:
+                    try:
+                        self.rows.append((float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)),
+                                          int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h))
+                                          if hasattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons")
+                                          else int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))))
+                    except Exception:
+                        pass
+                    if self.stop_flag.wait(0.01):
+                        return
+            self.th = threading.Thread(target=loop, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.th = None
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -91,6 +126,15 @@ class ClockSampler:
             self.p = None
 
     def stop(self):
+        if self.th is not None:
+            self.stop_flag.set()
+            self.th.join(timeout=2)
+            sm = sorted(r[0] for r in self.rows)
+            bits = 0
+            for r in self.rows:
+                bits |= r[1]
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.mx,
+                    "reasons": sorted(n for n, m in self.REASONS if bits & m), "samples": len(sm), "source": "nvml"}
         if self.p is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.p.terminate()
@@ -112,7 +156,7 @@ class ClockSampler:
                 pass
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
 # ---------------------------------------------------------------------------------------------------------------------
