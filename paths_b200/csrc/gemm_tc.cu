@@ -47,6 +47,9 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int elem /* 0..63 */) {
 // and without tanhf's range branches.
 __device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 __device__ __forceinline__ float tanh_fast(float x) { return 1.f - __fdividef(2.f, 1.f + __expf(2.f * x)); }
+// the plain-bf16 mode (stated tolerance 1e-2): one MUFU.TANH per element (tanh.approx.f32, ~5e-4 absolute), sigmoid through it
+__device__ __forceinline__ float tanh_mufu(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigmoid_mufu(float x) { return fmaf(0.5f, tanh_mufu(0.5f * x), 0.5f); }
 
 // CG = 2: CTA pair (cta_group::2) -- the pair's tile is 256 x BN, each CTA stages its 128 rows of A and HALF of the B tile
 template <int BN, int NP, int CG = 1>
@@ -609,7 +612,10 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             if (flags & GEMM_RELU) { w.x = fmaxf(w.x, 0.f); w.y = fmaxf(w.y, 0.f); w.z = fmaxf(w.z, 0.f); w.w = fmaxf(w.w, 0.f); }
             if (flags & GEMM_GATES) {                        // column ranges are multiples of 4: one branch per float4
               const int gc = flags >> 8;
-              if (nn >= 2 * gc && nn < 3 * gc) { w.x = tanh_fast(w.x); w.y = tanh_fast(w.y); w.z = tanh_fast(w.z); w.w = tanh_fast(w.w); }
+              if (NP == 1) {
+                if (nn >= 2 * gc && nn < 3 * gc) { w.x = tanh_mufu(w.x); w.y = tanh_mufu(w.y); w.z = tanh_mufu(w.z); w.w = tanh_mufu(w.w); }
+                else { w.x = sigmoid_mufu(w.x); w.y = sigmoid_mufu(w.y); w.z = sigmoid_mufu(w.z); w.w = sigmoid_mufu(w.w); }
+              } else if (nn >= 2 * gc && nn < 3 * gc) { w.x = tanh_fast(w.x); w.y = tanh_fast(w.y); w.z = tanh_fast(w.z); w.w = tanh_fast(w.w); }
               else { w.x = sigmoid_fast(w.x); w.y = sigmoid_fast(w.y); w.z = sigmoid_fast(w.z); w.w = sigmoid_fast(w.w); }
             }
           }
