@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_fwd_kernel(const float* __re
     if (T0 > NT || (NKB == 2 && T0 <= 64)) return;          // the other class's launch (or the tiled kernels) serves this bag
   }
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // offset from the __shared__ array: stays STS / LDS
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
   const int t = threadIdx.x, warp = t >> 5;
@@ -392,7 +392,7 @@ __global__ void __launch_bounds__(64 * NKB) attn_tc_bwd_kernel(const float* __re
     if (T0 > NT || (NKB == 2 && T0 <= 64)) return;
   }
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // offset from the __shared__ array: stays STS / LDS
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
   const int t = threadIdx.x, warp = t >> 5;
@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(128) attn_tc_fwd_long_kernel(const float* __re
   const int T = sg.T, q0 = blockIdx.y * 128;
   if (T <= 128 || q0 >= T) return;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // offset from the __shared__ array: stays STS / LDS
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
   const int t = threadIdx.x, warp = t >> 5;
@@ -694,7 +694,7 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dq_long_kernel(const float* _
   const int T = sg.T, q0 = blockIdx.y * 128;
   if (T <= 128 || q0 >= T) return;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // offset from the __shared__ array: stays STS / LDS
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
   const int t = threadIdx.x, warp = t >> 5;
@@ -832,7 +832,7 @@ __global__ void __launch_bounds__(128) attn_tc_bwd_dkv_long_kernel(const float* 
   const int T = sg.T, j0 = blockIdx.y * 128;
   if (T <= 128 || j0 >= T) return;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // offset from the __shared__ array: stays STS / LDS
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
   __shared__ float sL[LB], sD[LB];
