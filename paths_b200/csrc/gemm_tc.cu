@@ -575,8 +575,17 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int c0 = 0; c0 < BN / 2; c0 += 32) {
         uint32_t r[32];
         const int col = half * (BN / 2) + c0;
+        // interior chunk (warp-uniform): all 32 rows and 32 columns inside the output, 16-byte stores possible -- the lean path
+        // below.  The general path costs ~1300 issued instructions per 32 x 32 chunk (bounds, tails and every epilogue variant
+        // predicated per store step), which made the epilogue the pace of every contraction with a short reduction.
+        const bool interior = vec && (ci0 + q * 32 + 32 <= oi_lim) && (cj0 + col + 32 <= oj_lim);
         float4 a4[8];
-        if (has_add) {
+        if (has_add && interior) {
+          const float* ap0 = gg.add.p + (cj0 + col + oq * 4);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            a4[k] = ai[k] >= 0 ? __ldg(reinterpret_cast<const float4*>(ap0 + (size_t)ai[k] * gg.add.ld)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else if (has_add) {
           const int nn = cj0 + col + oq * 4;
 #pragma unroll
           for (int k = 0; k < 8; ++k) {
@@ -594,6 +603,36 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           *reinterpret_cast<uint4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
         __syncwarp();
         const int nn = cj0 + col + oq * 4;                   // first of this lane's 4 output columns
+        if (interior) {
+          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (!SK && bias) bv = make_float4(bias[nn], bias[nn + 1], bias[nn + 2], bias[nn + 3]);
+          const bool relu = !SK && (flags & GEMM_RELU), accum = !SK && (flags & GEMM_ACCUM), gates = !SK && (flags & GEMM_GATES);
+          const int gc = flags >> 8;
+          const bool as_tanh = nn >= 2 * gc && nn < 3 * gc;
+          float* cp = Cb + (size_t)(ci0 + q * 32 + orow) * ldo + nn;
+          const size_t step = (size_t)4 * ldo;
+#pragma unroll
+          for (int k = 0; k < 8; ++k, cp += step) {
+            const int row = 4 * k + orow;
+            float4 w = *reinterpret_cast<const float4*>(stg + row * 32 + ((oq ^ (row & 7)) << 2));
+            if (!SK) {
+              if (has_add) { w.x += a4[k].x; w.y += a4[k].y; w.z += a4[k].z; w.w += a4[k].w; }
+              w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
+              if (relu) { w.x = fmaxf(w.x, 0.f); w.y = fmaxf(w.y, 0.f); w.z = fmaxf(w.z, 0.f); w.w = fmaxf(w.w, 0.f); }
+              if (gates) {
+                if (NP == 1) {
+                  if (as_tanh) { w.x = tanh_mufu(w.x); w.y = tanh_mufu(w.y); w.z = tanh_mufu(w.z); w.w = tanh_mufu(w.w); }
+                  else { w.x = sigmoid_mufu(w.x); w.y = sigmoid_mufu(w.y); w.z = sigmoid_mufu(w.z); w.w = sigmoid_mufu(w.w); }
+                } else if (as_tanh) { w.x = tanh_fast(w.x); w.y = tanh_fast(w.y); w.z = tanh_fast(w.z); w.w = tanh_fast(w.w); }
+                else { w.x = sigmoid_fast(w.x); w.y = sigmoid_fast(w.y); w.z = sigmoid_fast(w.z); w.w = sigmoid_fast(w.w); }
+              }
+              if (accum) { const float4 c = *reinterpret_cast<const float4*>(cp); w.x += c.x; w.y += c.y; w.z += c.z; w.w += c.w; }
+            }
+            *reinterpret_cast<float4*>(cp) = w;
+          }
+          __syncwarp();
+          continue;
+        }
         float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
         if (!SK && bias) {
           if (nn + 3 < oj_lim) bv = make_float4(bias[nn], bias[nn + 1], bias[nn + 2], bias[nn + 3]);
